@@ -1,0 +1,210 @@
+/*
+ * prestogpu.h — the drop-in boundary: a plain C ABI for the B200-native
+ * scan -> filter -> project -> (hash-)aggregate pipeline.
+ *
+ * Nothing like this exists in the reference (Trino 359 is 100 % Java); every entry point
+ * below names the reference interface it stands in for (paths under /root/reference/):
+ *   main/ = core/trino-main/src/main/java/io/trino/
+ *   spi/  = core/trino-spi/src/main/java/io/trino/spi/
+ *
+ * A `pgpu_pipeline` is ONE operator instance (single owner, called by one thread at a time,
+ * possibly a different thread per call — exactly the Driver contract, main/operator/Driver.java:60-62,
+ * 284-305).  It fuses what the reference runs as
+ *     FilterAndProjectOperator / ScanFilterAndProjectOperator  (main/operator/FilterAndProjectOperator.java:42-88)
+ *  -> AggregationOperator                                      (main/operator/AggregationOperator.java:93-186)
+ *   | HashAggregationOperator                                  (main/operator/HashAggregationOperator.java:367-518)
+ * Any of the stages may be absent from the plan, so each reference operator is also available alone.
+ *
+ * There is no CPU fallback: a plan outside the supported subset fails in pgpu_pipeline_create
+ * with PGPU_NOT_SUPPORTED (the Java shim maps it to TrinoException(NOT_SUPPORTED)).
+ */
+#ifndef PRESTOGPU_H
+#define PRESTOGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Status codes. The non-zero ones map 1:1 onto io.trino.spi.StandardErrorCode values raised on this
+ * path (SURVEY.md §8(b) "Errors"). */
+typedef enum pgpu_status {
+    PGPU_OK = 0,
+    PGPU_NOT_SUPPORTED = 1,               /* NOT_SUPPORTED: plan-time rejection                         */
+    PGPU_INVALID_ARGUMENT = 2,            /* GENERIC_INTERNAL_ERROR: malformed plan / page              */
+    PGPU_NUMERIC_VALUE_OUT_OF_RANGE = 3,  /* main/type/BigintOperators.java:60-110, Decimal overflow    */
+    PGPU_DIVISION_BY_ZERO = 4,            /* main/type/BigintOperators.java:86-110                      */
+    PGPU_INSUFFICIENT_RESOURCES = 5,      /* main/operator/BigintGroupByHash.java:265-267               */
+    PGPU_COMPILER_ERROR = 6,              /* main/sql/gen/ExpressionCompiler.java:137                   */
+    PGPU_CUDA_ERROR = 7,                  /* GENERIC_INTERNAL_ERROR: device failure                     */
+    PGPU_INVALID_STATE = 8,               /* checkState(...) failures, e.g. addInput after finish       */
+    PGPU_INVALID_CAST_ARGUMENT = 9        /* main/type/DoubleOperators.java:155-165                     */
+} pgpu_status;
+
+/* Block encodings (spi/block/...): flat arrays, DictionaryBlock, RunLengthEncodedBlock. */
+typedef enum pgpu_encoding {
+    PGPU_ENC_PLAIN = 0,       /* LongArrayBlock / IntArrayBlock / ByteArrayBlock / Int128ArrayBlock / VariableWidthBlock */
+    PGPU_ENC_DICTIONARY = 1,  /* spi/block/DictionaryBlock.java:40-48 : ids[] into `dictionary`                          */
+    PGPU_ENC_RLE = 2          /* spi/block/RunLengthEncodedBlock.java:45-48 : single-position `dictionary` repeated       */
+} pgpu_encoding;
+
+/* Logical types of the supported subset (spi/type/...). Physical layout in a block:
+ *   BOOLEAN  -> ByteArrayBlock   (int8 per position)
+ *   INTEGER, DATE -> IntArrayBlock (int32)
+ *   BIGINT, DOUBLE (raw IEEE bits, spi/type/DoubleType.java:98-106), DECIMAL(p<=18) -> LongArrayBlock (int64)
+ *   DECIMAL(p>18) -> Int128ArrayBlock: 2 x int64 per position, sign-magnitude, low word first,
+ *                    sign = top bit of word 1 (spi/type/UnscaledDecimal128Arithmetic.java:30-56)
+ *   VARCHAR, VARBINARY -> VariableWidthBlock: bytes + int32 offsets[n+1]                              */
+typedef enum pgpu_type_kind {
+    PGPU_BOOLEAN = 0,
+    PGPU_BIGINT = 1,
+    PGPU_INTEGER = 2,
+    PGPU_DATE = 3,
+    PGPU_DOUBLE = 4,
+    PGPU_DECIMAL = 5,
+    PGPU_VARCHAR = 6,
+    PGPU_VARBINARY = 7
+} pgpu_type_kind;
+
+/* One Block (spi/block/Block.java). Pointers are HOST pointers for pgpu_add_page / pgpu_get_output
+ * and DEVICE pointers for pgpu_add_device_page / pgpu_get_output_device. */
+typedef struct pgpu_column {
+    int32_t encoding;        /* pgpu_encoding                                                           */
+    int32_t type_kind;       /* pgpu_type_kind                                                          */
+    int32_t precision;       /* DECIMAL precision; VARCHAR bound (0 = unbounded); else 0                */
+    int32_t scale;           /* DECIMAL scale; else 0                                                   */
+    int64_t position_count;  /* positions in THIS block                                                 */
+    const void* values;      /* PLAIN: element array (see layout above); var-width: the byte slice      */
+    const uint8_t* nulls;    /* PLAIN: Java boolean[] valueIsNull, 1 byte/position, or NULL = no nulls  */
+    const int32_t* offsets;  /* PLAIN var-width only: position_count+1 offsets into `values`            */
+    const int32_t* ids;      /* DICTIONARY: position_count ids into `dictionary`                        */
+    const struct pgpu_column* dictionary; /* DICTIONARY: the dictionary block (PLAIN); RLE: 1-position value block (PLAIN) */
+} pgpu_column;
+
+typedef struct pgpu_pipeline pgpu_pipeline;
+
+/* Flags for pgpu_add_page. */
+#define PGPU_PAGE_PINNED 1u /* caller guarantees all buffers are page-locked and stay unchanged until
+                               pgpu_sync(); the library then skips its staging copy and DMAs directly. */
+
+/* Library / environment ------------------------------------------------------------------------- */
+const char* pgpu_version(void);
+/* Number of visible CUDA devices (0 when there is no GPU; never an error). */
+int32_t pgpu_device_count(void);
+/* Last error text of calls that have no pipeline handle (create failures). Thread-local. */
+const char* pgpu_last_global_error(void);
+
+/* Plan compilation — replaces ExpressionCompiler.compilePageProcessor (main/sql/gen/ExpressionCompiler.java:
+ * 98-137) + AccumulatorCompiler (main/operator/aggregation/AccumulatorCompiler.java:80-140) + the factory
+ * constructors LocalExecutionPlanner calls (main/sql/planner/LocalExecutionPlanner.java:1680,1699,3389,3492).
+ * `plan` is the textual plan described in DESIGN.md §"Plan language". `device` < 0 compiles only
+ * (no GPU needed: used by the CPU test-suite and by build() to warm the kernel cache). */
+pgpu_status pgpu_pipeline_create(const uint8_t* plan, size_t plan_len, int32_t device, pgpu_pipeline** out);
+/* Pre-compile the kernel variant for one page signature (per channel: pgpu_encoding, and whether the block /
+ * its dictionary carries a null vector). Variants are otherwise compiled lazily by the first page that needs
+ * them; this entry point lets plan-time code (and the CPU-only test-suite) pay for it up front. */
+pgpu_status pgpu_compile_signature(pgpu_pipeline* p, const int32_t* encodings, const uint8_t* nullable, int32_t ncols);
+/* Operator.close() (main/operator/Operator.java:97-102). */
+void pgpu_pipeline_destroy(pgpu_pipeline* p);
+/* Error text for the last failing call on `p` (TrinoException message). */
+const char* pgpu_last_error(const pgpu_pipeline* p);
+
+/* Operator protocol (main/operator/Operator.java:21-103) ------------------------------------------- */
+/* Operator.needsInput(): 1 / 0. HashAggregationOperator.needsInput (main/operator/HashAggregationOperator.java:367-378). */
+int32_t pgpu_needs_input(const pgpu_pipeline* p);
+/* Operator.addInput(Page): columns are copied (or DMA'd) before the call returns control of unpinned buffers. */
+pgpu_status pgpu_add_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows, uint32_t flags);
+/* Same, with device-resident blocks (no copy). Buffers must stay valid until pgpu_sync(). */
+pgpu_status pgpu_add_device_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows);
+/* Operator.finish(): no more input; may be called repeatedly (main/operator/Driver.java:368-372). */
+pgpu_status pgpu_finish(pgpu_pipeline* p);
+/* Operator.isFinished(). */
+int32_t pgpu_is_finished(const pgpu_pipeline* p);
+/* Operator.getOutput(): *rows = -1 means "no page now" (Java null). Output blocks live in library-owned
+ * pinned host memory and stay valid until the next pgpu_get_output / pgpu_pipeline_destroy on `p`.
+ * Device-side arithmetic faults (overflow, division by zero) surface here or in pgpu_finish. */
+pgpu_status pgpu_get_output(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows);
+/* As pgpu_get_output but the blocks stay in HBM (device pointers). */
+pgpu_status pgpu_get_output_device(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows);
+/* Block until all device work queued by `p` is complete; reports sticky device-side errors. */
+pgpu_status pgpu_sync(pgpu_pipeline* p);
+/* Drop all aggregation state and return to the just-created state (new TaskContext per benchmark
+ * iteration, testing/trino-benchmark/.../AbstractOperatorBenchmark.java:279-335). */
+pgpu_status pgpu_reset(pgpu_pipeline* p);
+
+/* Introspection --------------------------------------------------------------------------------- */
+/* Output schema: number of output channels and their types. */
+int32_t pgpu_output_channel_count(const pgpu_pipeline* p);
+pgpu_status pgpu_output_channel_type(const pgpu_pipeline* p, int32_t channel, int32_t* type_kind, int32_t* precision, int32_t* scale);
+/* Generated CUDA source of the most recently compiled kernel variant (for reviews / profiles). */
+const char* pgpu_generated_source(const pgpu_pipeline* p);
+/* Counters: kernels launched / bytes copied H2D and D2H / device-time (ms, CUDA events, only when
+ * timing was enabled with pgpu_set_timing) since creation or the last pgpu_reset. */
+typedef struct pgpu_stats {
+    int64_t kernel_launches;
+    int64_t h2d_bytes;
+    int64_t d2h_bytes;
+    int64_t input_rows;
+    int64_t input_pages;
+    int64_t jit_compiles;
+    int64_t jit_cache_hits;
+    double  device_ms;      /* sum over timed page kernels */
+    int64_t table_capacity; /* slots of the HBM hash table (0 = none) */
+    int64_t table_rehashes;
+} pgpu_stats;
+pgpu_status pgpu_get_stats(const pgpu_pipeline* p, pgpu_stats* out);
+pgpu_status pgpu_set_timing(pgpu_pipeline* p, int32_t enabled);
+/* The CUDA stream (cudaStream_t) the pipeline launches on, so callers can bracket it with events. */
+void* pgpu_stream(const pgpu_pipeline* p);
+
+/* Partial -> final exchange (multi-GPU) -----------------------------------------------------------
+ * Mirrors PartitionedOutputOperator (main/operator/PartitionedOutputOperator.java:56-133) between a
+ * Step.PARTIAL and a Step.FINAL HashAggregationOperator. The collectives themselves (NCCL all-reduce /
+ * all-to-all) are issued by the host runtime on the buffers these calls expose. */
+/* Hash-partition the partial output of a PARTIAL-step pipeline into `nparts` contiguous row ranges
+ * (device-resident). After the call out_cols describe ONE device page sorted by partition and
+ * part_row_offsets[nparts+1] (host) gives the row ranges. */
+pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_column* out_cols, int32_t max_cols,
+                                         int32_t* ncols, int64_t* part_row_offsets);
+/* Dense partial state for low-cardinality all-reduce: see DESIGN.md §"Multi-GPU". Exposes the device
+ * buffer of the pipeline's compact state image (int64/double cells) for in-place ncclAllReduce. */
+pgpu_status pgpu_dense_state_device(pgpu_pipeline* p, void** dev_ptr, int64_t* n_i64_cells, int64_t* n_f64_cells);
+
+/* Pinned host memory helpers (what the JNI shim stages heap arrays into). */
+void* pgpu_host_alloc(size_t bytes);
+void pgpu_host_free(void* ptr);
+/* Device memory helpers for callers without torch. */
+void* pgpu_device_alloc(int32_t device, size_t bytes);
+void pgpu_device_free(int32_t device, void* ptr);
+
+/* Synthetic TPC-H lineitem columns generated directly in HBM (SURVEY.md §8(d) distributions; the
+ * reference's generator io.trino.tpch:tpch:1.1 is not in its tree). Column ids: see PGPU_LI_* below.
+ * Row r of a column depends only on (seed, r): pgpu_gen_lineitem_host produces the identical bytes on the CPU. */
+#define PGPU_LI_ORDERKEY 0      /* int64  */
+#define PGPU_LI_QUANTITY 1      /* double */
+#define PGPU_LI_EXTENDEDPRICE 2 /* double */
+#define PGPU_LI_DISCOUNT 3      /* double */
+#define PGPU_LI_TAX 4           /* double */
+#define PGPU_LI_SHIPDATE 5      /* int32 days since epoch */
+#define PGPU_LI_RETURNFLAG 6    /* 1 byte per row (varchar(1) payload) */
+#define PGPU_LI_LINESTATUS 7    /* 1 byte per row */
+#define PGPU_LI_IOTA_OFFSETS 8  /* int32 offsets 0..rows (rows+1 entries) for varchar(1) blocks */
+#define PGPU_LI_DISCOUNT_ID 9   /* int32 dictionary id of discount (0..10) */
+#define PGPU_LI_TAX_ID 10       /* int32 dictionary id of tax (0..8) */
+#define PGPU_LI_QUANTITY_ID 11  /* int32 dictionary id of quantity (0..49) */
+#define PGPU_LI_RETURNFLAG_ID 12/* int32 dictionary id of returnflag (A,N,R) */
+#define PGPU_LI_LINESTATUS_ID 13/* int32 dictionary id of linestatus (F,O) */
+#define PGPU_LI_ORDERKEY_SHUFFLED 14 /* int64, uniform random over the same key domain */
+pgpu_status pgpu_gen_lineitem_device(int32_t device, int32_t column, uint64_t seed, int64_t first_row, int64_t rows,
+                                     int64_t total_rows, void* dev_out);
+pgpu_status pgpu_gen_lineitem_host(int32_t column, uint64_t seed, int64_t first_row, int64_t rows,
+                                   int64_t total_rows, void* host_out);
+/* Write `bytes` of device memory (L2 flush between timed iterations). */
+pgpu_status pgpu_flush_l2(int32_t device, void* dev_scratch, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PRESTOGPU_H */

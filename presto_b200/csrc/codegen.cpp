@@ -1,0 +1,1217 @@
+// codegen.cpp — turns a validated Plan plus the encodings of the incoming page into CUDA source:
+// a traits struct `P` that the kernel templates of device/pgpu_device.cuh are instantiated with.
+// Reference semantics followed, node by node:
+//   AND/OR        main/sql/gen/AndCodeGenerator.java, OrCodeGenerator.java (short circuit + SQL three-valued logic)
+//   BETWEEN       main/sql/gen/BetweenCodeGenerator.java (value >= min AND value <= max)
+//   IN            main/sql/gen/InCodeGenerator.java (NULL if no match and any NULL operand)
+//   IF/COALESCE   main/sql/gen/IfCodeGenerator.java, CoalesceCodeGenerator.java
+//   calls         null-on-null convention of main/sql/gen/BytecodeUtils.java generateInvocation; operator bodies from
+//                 main/type/{Bigint,Integer,Double,Decimal}Operators.java
+//   filter        NULL => not selected, main/sql/gen/PageFunctionCompiler.java:542
+//   accumulators  main/operator/aggregation/{DoubleSum,LongSum,Count,CountColumn,Average,DecimalSum,DecimalAverage}*.java,
+//                 AbstractMinMaxAggregationFunction.java:274-306 + main/util/MinMaxCompare.java
+#include "codegen.h"
+
+#include <algorithm>
+#include <map>
+#include <set>
+#include <sstream>
+
+#include "../../include/prestogpu.h"
+
+namespace pgpu {
+namespace {
+
+[[noreturn]] void unsupported(const std::string& m) { throw PlanError(PGPU_NOT_SUPPORTED, "not supported on the GPU path: " + m); }
+
+struct Val {
+    std::string v;   // value expression (C identifier or literal)
+    std::string n;   // null flag expression; empty = never null
+    std::string hi;  // second word for 16-byte var-width cells
+    Type type;
+    bool nullable() const { return !n.empty(); }
+};
+
+std::string ctype(const Type& t) {
+    switch (t.kind) {
+        case TypeKind::BOOLEAN: return "bool";
+        case TypeKind::INTEGER:
+        case TypeKind::DATE: return "i32";
+        case TypeKind::BIGINT: return "i64";
+        case TypeKind::DOUBLE: return "double";
+        case TypeKind::DECIMAL: return t.precision <= 18 ? "i64" : "i128";
+        default: return "u64";
+    }
+}
+
+// storage element type of a flat block
+std::string stype(const Type& t) {
+    switch (t.kind) {
+        case TypeKind::BOOLEAN: return "u8";
+        case TypeKind::INTEGER:
+        case TypeKind::DATE: return "i32";
+        case TypeKind::BIGINT: return "i64";
+        case TypeKind::DOUBLE: return "double";
+        case TypeKind::DECIMAL: return t.precision <= 18 ? "i64" : "raw128";
+        default: return "u8";
+    }
+}
+
+std::string i128Literal(i128 v) {
+    bool neg = v < 0;
+    u128 m = neg ? (u128)0 - (u128)v : (u128)v;
+    std::ostringstream o;
+    o << "(" << (neg ? "-" : "") << "(i128)(((u128)0x" << std::hex << (uint64_t)(m >> 64) << "ull << 64) | 0x" << (uint64_t)m << "ull))";
+    return o.str();
+}
+
+std::string i64Literal(int64_t v) {
+    if (v == INT64_MIN) return "((i64)0x8000000000000000ull)";
+    return "((i64)" + std::to_string(v) + "ll)";
+}
+
+bool canRaise(const Expr& e) {
+    switch (e.kind) {
+        case ExprKind::INPUT:
+        case ExprKind::CONST: return false;
+        case ExprKind::CALL:
+            switch (e.op) {
+                case Op::ADD:
+                case Op::SUBTRACT:
+                case Op::MULTIPLY:
+                case Op::NEGATE:
+                    if (e.type.kind != TypeKind::DOUBLE && !(e.type.isShortDecimal())) return true;
+                    break;
+                case Op::DIVIDE:
+                case Op::MODULUS:
+                    if (e.type.kind != TypeKind::DOUBLE) return true;
+                    break;
+                case Op::CAST:
+                    if (e.type != e.args[0]->type && !(e.type.kind == TypeKind::DOUBLE) && !(e.type.kind == TypeKind::BIGINT && e.args[0]->type.kind == TypeKind::INTEGER)) return true;
+                    break;
+                default: break;
+            }
+            break;
+        default: break;
+    }
+    for (auto& a : e.args)
+        if (canRaise(*a)) return true;
+    return false;
+}
+
+void collectChannels(const Expr& e, std::set<int>& s) {
+    if (e.kind == ExprKind::INPUT) s.insert(e.channel);
+    for (auto& a : e.args) collectChannels(*a, s);
+}
+
+// Can the value be NULL for some page? (inputs are assumed nullable: the accumulator/key LAYOUT must not depend on
+// which pages happen to carry null vectors, only the generated code does.)
+bool mayBeNull(const Expr& e) {
+    switch (e.kind) {
+        case ExprKind::INPUT: return true;
+        case ExprKind::CONST: return e.isNull;
+        case ExprKind::IS_NULL: return false;
+        case ExprKind::IF: return mayBeNull(*e.args[1]) || mayBeNull(*e.args[2]);
+        case ExprKind::COALESCE:
+            for (auto& a : e.args)
+                if (!mayBeNull(*a)) return false;
+            return true;
+        default:
+            for (auto& a : e.args)
+                if (mayBeNull(*a)) return true;
+            return false;
+    }
+}
+
+struct Cell {
+    std::string kind;  // cnt, cntw (wide), sumd, sumi, sumdec, max, min
+    int word = 0;      // first word
+    int nwords = 1;
+    std::vector<std::string> contrib;  // per word: expression of the u64 contribution of the current row
+};
+
+struct Gen {
+    const Plan& plan;
+    const std::vector<ColSig>& sig;
+    std::ostringstream out;   // current code sink
+    int tmpId = 0;
+    int indent = 2;
+
+    Gen(const Plan& p, const std::vector<ColSig>& s) : plan(p), sig(s) {}
+
+    std::string tmp(const char* p) { return std::string(p) + std::to_string(tmpId++); }
+    void line(const std::string& s) { out << std::string(indent * 4, ' ') << s << "\n"; }
+
+    // ------------------------------------------------------------------ column loads
+    void emitTileLoads(const std::set<int>& chans) {
+        for (int c : chans) {
+            const Type& t = plan.input[c];
+            const ColSig& cs = sig[c];
+            std::string C = std::to_string(c);
+            if (cs.encoding == PGPU_ENC_RLE) continue;  // loaded in the row prologue (uniform)
+            if (cs.encoding == PGPU_ENC_DICTIONARY) {
+                line("i32 id" + C + "[4]; load_tile4<i32>(a.c[" + C + "].ids, base, nrows, full, id" + C + ");");
+                continue;
+            }
+            if (t.isVarWidth()) {
+                line("i32 o" + C + "[5];");
+                line("if (full) { i32 t4[4]; load_tile4<i32>(a.c[" + C + "].offsets, base, nrows, true, t4); o" + C + "[0] = t4[0]; o" + C + "[1] = t4[1]; o" + C +
+                     "[2] = t4[2]; o" + C + "[3] = t4[3]; o" + C + "[4] = a.c[" + C + "].offsets[base + 4]; }");
+                line("else { for (int q = 0; q < 5; q++) { i64 ix = base + q < nrows ? base + q : nrows; o" + C + "[q] = a.c[" + C + "].offsets[ix]; } }");
+            } else {
+                std::string st = stype(t);
+                line(st + " c" + C + "[4]; load_tile4<" + st + ">((const " + st + "*)a.c[" + C + "].values, base, nrows, full, c" + C + ");");
+            }
+            if (cs.nullable) line("u8 n" + C + "[4]; load_tile4<u8>(a.c[" + C + "].nulls, base, nrows, full, n" + C + ");");
+        }
+    }
+
+    // per-row temps x<c> (value), y<c> (2nd word of var-width), z<c> (null flag)
+    void emitRowPrologue(const std::set<int>& chans) {
+        for (int c : chans) {
+            const Type& t = plan.input[c];
+            const ColSig& cs = sig[c];
+            std::string C = std::to_string(c);
+            std::string ct = ctype(t), st = stype(t);
+            auto conv = [&](const std::string& raw) -> std::string {
+                if (t.kind == TypeKind::BOOLEAN) return "(" + raw + " != 0)";
+                if (t.isLongDecimal()) return "dec_from_raw(" + raw + ")";
+                return raw;
+            };
+            if (cs.encoding == PGPU_ENC_PLAIN) {
+                if (t.isVarWidth()) {
+                    int n = t.kind == TypeKind::VARCHAR ? t.precision : 0;
+                    if (t.kind == TypeKind::VARCHAR) {
+                        line("u64 x" + C + ", y" + C + "; pack_varchar<" + std::to_string(n) + ">((const u8*)a.c[" + C + "].values, o" + C + "[r], o" + C + "[r + 1] - o" + C + "[r], x" + C + ", y" + C + ", err);");
+                    } else {
+                        line("const u8* x" + C + " = (const u8*)a.c[" + C + "].values + o" + C + "[r];");
+                    }
+                } else {
+                    line("const " + ct + " x" + C + " = " + conv("c" + C + "[r]") + ";");
+                }
+                if (cs.nullable) line("const bool z" + C + " = n" + C + "[r] != 0;");
+            } else {
+                std::string idx = cs.encoding == PGPU_ENC_DICTIONARY ? "id" + C + "[r]" : "0";
+                if (t.isVarWidth()) {
+                    if (t.kind == TypeKind::VARCHAR) {
+                        line("u64 x" + C + ", y" + C + "; { const i32 q0 = a.c[" + C + "].doffsets[" + idx + "], q1 = a.c[" + C + "].doffsets[" + idx + " + 1]; pack_varchar<" +
+                             std::to_string(t.precision) + ">((const u8*)a.c[" + C + "].dvalues, q0, q1 - q0, x" + C + ", y" + C + ", err); }");
+                    } else {
+                        line("const u8* x" + C + " = (const u8*)a.c[" + C + "].dvalues + a.c[" + C + "].doffsets[" + idx + "];");
+                    }
+                } else {
+                    line("const " + ct + " x" + C + " = " + conv("((const " + st + "*)a.c[" + C + "].dvalues)[" + idx + "]") + ";");
+                }
+                if (cs.nullable) line("const bool z" + C + " = a.c[" + C + "].dnulls[" + idx + "] != 0;");
+            }
+        }
+    }
+
+    Val colVal(int c) {
+        Val v;
+        std::string C = std::to_string(c);
+        v.type = plan.input[c];
+        v.v = "x" + C;
+        if (v.type.kind == TypeKind::VARCHAR) v.hi = "y" + C;
+        if (sig[c].nullable) v.n = "z" + C;
+        return v;
+    }
+
+    // ------------------------------------------------------------------ expressions
+    Val constant(const Expr& e) {
+        Val v;
+        v.type = e.type;
+        if (e.isNull) {
+            v.n = "true";
+            v.v = e.type.kind == TypeKind::DOUBLE ? "0.0" : (e.type.kind == TypeKind::BOOLEAN ? "false" : "(" + ctype(e.type) + ")0");
+            return v;
+        }
+        switch (e.type.kind) {
+            case TypeKind::BOOLEAN: v.v = e.i64 ? "true" : "false"; break;
+            case TypeKind::INTEGER:
+            case TypeKind::DATE: v.v = "((i32)" + std::to_string(e.i64) + ")"; break;
+            case TypeKind::BIGINT: v.v = i64Literal(e.i64); break;
+            case TypeKind::DOUBLE: {
+                std::ostringstream o;
+                o << "u2d(0x" << std::hex << (uint64_t)e.i64 << "ull)";
+                v.v = o.str();
+                break;
+            }
+            case TypeKind::DECIMAL: v.v = e.type.isShortDecimal() ? i64Literal((int64_t)e.dec) : i128Literal(e.dec); break;
+            default: unsupported("constant of type " + e.type.str());
+        }
+        return v;
+    }
+
+    static std::string nullOr(const std::string& a, const std::string& b) {
+        if (a.empty()) return b;
+        if (b.empty()) return a;
+        return "(" + a + " || " + b + ")";
+    }
+
+    Val compare(Op op, const Val& a, const Val& b) {
+        Val r;
+        r.type = Type::boolean();
+        const char* o = "==";
+        switch (op) {
+            case Op::EQ: o = "=="; break;
+            case Op::NE: o = "!="; break;
+            case Op::LT: o = "<"; break;
+            case Op::LE: o = "<="; break;
+            case Op::GT: o = ">"; break;
+            case Op::GE: o = ">="; break;
+            default: break;
+        }
+        std::string t = tmp("b");
+        line("const bool " + t + " = (" + a.v + " " + o + " " + b.v + ");");
+        r.v = t;
+        r.n = nullOr(a.n, b.n);
+        return r;
+    }
+
+    // three-valued AND / OR over already evaluated operands
+    Val logic(bool isAnd, const std::vector<Val>& ops) {
+        Val r;
+        r.type = Type::boolean();
+        bool anyNullable = false;
+        for (auto& o : ops) anyNullable |= o.nullable();
+        std::string t = tmp("b");
+        if (!anyNullable) {
+            std::string e;
+            for (size_t i = 0; i < ops.size(); i++) e += (i ? (isAnd ? " && " : " || ") : "") + ops[i].v;
+            line("const bool " + t + " = (" + e + ");");
+            r.v = t;
+            return r;
+        }
+        // decisive = some operand is definitely false (AND) / true (OR)
+        std::string dec, anyn;
+        for (size_t i = 0; i < ops.size(); i++) {
+            std::string d = isAnd ? "!" + ops[i].v : ops[i].v;
+            if (ops[i].nullable()) d = "(!" + ops[i].n + " && " + d + ")";
+            dec += (i ? " || " : "") + d;
+            if (ops[i].nullable()) anyn += (anyn.empty() ? "" : " || ") + ops[i].n;
+        }
+        std::string td = tmp("b"), tn = tmp("b");
+        line("const bool " + td + " = (" + dec + ");");
+        line("const bool " + tn + " = !" + td + " && (" + anyn + ");");
+        line("const bool " + t + " = " + (isAnd ? "!" + td + " && !" + tn : td) + ";");
+        r.v = t;
+        r.n = tn;
+        return r;
+    }
+
+    Val genLogic(const Expr& e) {
+        bool isAnd = e.kind == ExprKind::AND;
+        bool guard = false;
+        for (size_t i = 1; i < e.args.size(); i++) guard |= canRaise(*e.args[i]);
+        if (!guard) {
+            std::vector<Val> ops;
+            for (auto& a : e.args) ops.push_back(gen(*a));
+            return logic(isAnd, ops);
+        }
+        // short circuit: later operands are only evaluated while no decisive value was seen
+        std::string td = tmp("b"), tn = tmp("b");
+        line("bool " + td + " = false, " + tn + " = false;");
+        int opened = 0;
+        for (size_t i = 0; i < e.args.size(); i++) {
+            if (i > 0) {
+                line("if (!" + td + ") {");
+                indent++;
+                opened++;
+            }
+            Val o = gen(*e.args[i]);
+            std::string d = isAnd ? "!" + o.v : o.v;
+            if (o.nullable()) {
+                line("if (" + o.n + ") " + tn + " = true; else if (" + d + ") " + td + " = true;");
+            } else {
+                line("if (" + d + ") " + td + " = true;");
+            }
+        }
+        while (opened--) {
+            indent--;
+            line("}");
+        }
+        Val r;
+        r.type = Type::boolean();
+        std::string t = tmp("b"), t2 = tmp("b");
+        line("const bool " + t2 + " = !" + td + " && " + tn + ";");
+        line("const bool " + t + " = " + (isAnd ? "!" + td + " && !" + tn : td) + ";");
+        r.v = t;
+        r.n = t2;
+        return r;
+    }
+
+    Val genIf(const Expr& e) {
+        Val c = gen(*e.args[0]);
+        std::string cond = c.nullable() ? "(" + c.v + " && !" + c.n + ")" : c.v;
+        std::string ct = ctype(e.type);
+        std::string t = tmp("v"), tn = tmp("b");
+        line(ct + " " + t + " = " + (e.type.kind == TypeKind::DOUBLE ? "0.0" : "(" + ct + ")0") + "; bool " + tn + " = false;");
+        line("if (" + cond + ") {");
+        indent++;
+        Val a = gen(*e.args[1]);
+        line(t + " = " + a.v + ";" + (a.nullable() ? " " + tn + " = " + a.n + ";" : ""));
+        indent--;
+        line("} else {");
+        indent++;
+        Val b = gen(*e.args[2]);
+        line(t + " = " + b.v + ";" + (b.nullable() ? " " + tn + " = " + b.n + ";" : ""));
+        indent--;
+        line("}");
+        Val r;
+        r.type = e.type;
+        r.v = t;
+        if (a.nullable() || b.nullable()) r.n = tn;
+        return r;
+    }
+
+    Val genCoalesce(const Expr& e) {
+        std::string ct = ctype(e.type);
+        std::string t = tmp("v"), tn = tmp("b");
+        line(ct + " " + t + " = " + (e.type.kind == TypeKind::DOUBLE ? "0.0" : "(" + ct + ")0") + "; bool " + tn + " = true;");
+        int opened = 0;
+        bool certain = false;
+        for (size_t i = 0; i < e.args.size() && !certain; i++) {
+            if (i > 0) {
+                line("if (" + tn + ") {");
+                indent++;
+                opened++;
+            }
+            Val a = gen(*e.args[i]);
+            if (a.nullable()) {
+                line("if (!" + a.n + ") { " + t + " = " + a.v + "; " + tn + " = false; }");
+            } else {
+                line(t + " = " + a.v + "; " + tn + " = false;");
+                certain = true;
+            }
+        }
+        while (opened--) {
+            indent--;
+            line("}");
+        }
+        Val r;
+        r.type = e.type;
+        r.v = t;
+        if (!certain) r.n = tn;
+        return r;
+    }
+
+    Val genIn(const Expr& e) {
+        Val v = gen(*e.args[0]);
+        std::string match, anyNull;
+        for (size_t i = 1; i < e.args.size(); i++) {
+            Val c = constant(*e.args[i]);
+            if (e.args[i]->isNull) {
+                anyNull = "true";
+                continue;
+            }
+            match += (match.empty() ? "" : " || ") + std::string("(") + v.v + " == " + c.v + ")";
+        }
+        if (match.empty()) match = "false";
+        std::string t = tmp("b");
+        line("const bool " + t + " = (" + match + ");");
+        Val r;
+        r.type = Type::boolean();
+        r.v = t;
+        std::string n = v.n;
+        if (!anyNull.empty()) {
+            std::string tn = tmp("b");
+            line("const bool " + tn + " = " + (v.nullable() ? "(" + v.n + " || !" + t + ")" : "!" + t) + ";");
+            n = tn;
+        }
+        r.n = n;
+        return r;
+    }
+
+    Val toI128(const Val& a) {
+        if (a.type.isLongDecimal()) return a;
+        Val r = a;
+        r.v = "((i128)" + a.v + ")";
+        return r;
+    }
+
+    Val genDecimalArith(const Expr& e, const Val& a, const Val& b) {
+        const Type &ta = a.type, &tb = b.type, &tr = e.type;
+        Val r;
+        r.type = tr;
+        r.n = nullOr(a.n, b.n);
+        std::string t = tmp("v");
+        if (e.op == Op::ADD || e.op == Op::SUBTRACT) {
+            int s = tr.scale;
+            const char* o = e.op == Op::ADD ? "+" : "-";
+            if (tr.isShortDecimal()) {  // DecimalOperators.addShortShortShort :103-106, subtractShortShortShort :208-211
+                line("const i64 " + t + " = " + a.v + " * " + i64Literal((int64_t)pow10_i128(s - ta.scale)) + " " + o + " " + b.v + " * " + i64Literal((int64_t)pow10_i128(s - tb.scale)) + ";");
+            } else {  // internalAddLongLongLong :151-172: rescale, add, throwIfOverflows
+                std::string la = toI128(a).v, lb = toI128(b).v;
+                if (s > ta.scale) la = "dec_upscale(" + la + ", " + i128Literal(pow10_i128(s - ta.scale)) + ", err)";
+                if (s > tb.scale) lb = "dec_upscale(" + lb + ", " + i128Literal(pow10_i128(s - tb.scale)) + ", err)";
+                line("const i128 " + t + " = " + la + " " + o + " " + lb + "; if (dec_overflows(" + t + ")) err |= PGPU_ERR_OVERFLOW;");
+            }
+        } else if (e.op == Op::MULTIPLY) {
+            if (tr.isShortDecimal()) line("const i64 " + t + " = " + a.v + " * " + b.v + ";");  // multiplyShortShortShort :281-284
+            else line("const i128 " + t + " = dec_mul(" + toI128(a).v + ", " + toI128(b).v + ", err);");
+        } else {
+            unsupported(std::string("decimal ") + opName(e.op));
+        }
+        r.v = t;
+        return r;
+    }
+
+    Val genCall(const Expr& e) {
+        std::vector<Val> a;
+        for (auto& x : e.args) a.push_back(gen(*x));
+        Val r;
+        r.type = e.type;
+        for (auto& x : a) r.n = nullOr(r.n, x.n);
+        std::string t = tmp("v");
+        std::string ct = ctype(e.type);
+        switch (e.op) {
+            case Op::EQ:
+            case Op::NE:
+            case Op::LT:
+            case Op::LE:
+            case Op::GT:
+            case Op::GE: return compare(e.op, a[0], a[1]);
+            case Op::NOT:
+                line("const bool " + t + " = !" + a[0].v + ";");
+                r.v = t;
+                return r;
+            case Op::NEGATE:
+                if (e.type.kind == TypeKind::DOUBLE || e.type.kind == TypeKind::DECIMAL) line("const " + ct + " " + t + " = -" + a[0].v + ";");
+                else if (e.type.kind == TypeKind::BIGINT) line("const i64 " + t + " = neg_i64_checked(" + a[0].v + ", err);");
+                else line("const i32 " + t + " = narrow_i32_checked(-(i64)" + a[0].v + ", err);");
+                r.v = t;
+                return r;
+            case Op::ADD:
+            case Op::SUBTRACT:
+            case Op::MULTIPLY:
+            case Op::DIVIDE:
+            case Op::MODULUS: {
+                if (e.type.kind == TypeKind::DECIMAL) return genDecimalArith(e, a[0], a[1]);
+                const char* o = e.op == Op::ADD ? "+" : e.op == Op::SUBTRACT ? "-" : e.op == Op::MULTIPLY ? "*" : "/";
+                if (e.type.kind == TypeKind::DOUBLE) {
+                    if (e.op == Op::MODULUS) line("const double " + t + " = fmod(" + a[0].v + ", " + a[1].v + ");");
+                    else line("const double " + t + " = " + a[0].v + " " + o + " " + a[1].v + ";");
+                } else if (e.type.kind == TypeKind::BIGINT) {
+                    const char* f = e.op == Op::ADD ? "add" : e.op == Op::SUBTRACT ? "sub" : e.op == Op::MULTIPLY ? "mul" : e.op == Op::DIVIDE ? "div" : "mod";
+                    line("const i64 " + t + " = " + f + "_i64_checked(" + a[0].v + ", " + a[1].v + ", err);");
+                } else {  // INTEGER (main/type/IntegerOperators.java:45-103)
+                    if (e.op == Op::DIVIDE) line("const i32 " + t + " = div_i32_checked(" + a[0].v + ", " + a[1].v + ", err);");
+                    else if (e.op == Op::MODULUS) line("const i32 " + t + " = mod_i32_checked(" + a[0].v + ", " + a[1].v + ", err);");
+                    else line("const i32 " + t + " = narrow_i32_checked((i64)" + a[0].v + " " + o + " (i64)" + a[1].v + ", err);");
+                }
+                r.v = t;
+                return r;
+            }
+            case Op::CAST: {
+                const Type &f = a[0].type, &to = e.type;
+                if (f == to) return a[0];
+                auto k = [](const Type& x) { return x.kind; };
+                if (k(f) == TypeKind::INTEGER && k(to) == TypeKind::BIGINT) line("const i64 " + t + " = (i64)" + a[0].v + ";");
+                else if ((k(f) == TypeKind::INTEGER || k(f) == TypeKind::BIGINT) && k(to) == TypeKind::DOUBLE) line("const double " + t + " = (double)" + a[0].v + ";");
+                else if (k(f) == TypeKind::BIGINT && k(to) == TypeKind::INTEGER) line("const i32 " + t + " = narrow_i32_checked(" + a[0].v + ", err);");
+                else if (k(f) == TypeKind::DOUBLE && k(to) == TypeKind::BIGINT) line("const i64 " + t + " = cast_f64_i64(" + a[0].v + ", err);");
+                else if (k(f) == TypeKind::BOOLEAN && (k(to) == TypeKind::BIGINT || k(to) == TypeKind::INTEGER)) line("const " + ct + " " + t + " = " + a[0].v + " ? 1 : 0;");
+                else if (k(f) == TypeKind::BOOLEAN && k(to) == TypeKind::DOUBLE) line("const double " + t + " = " + a[0].v + " ? 1.0 : 0.0;");
+                else if ((k(f) == TypeKind::BIGINT || k(f) == TypeKind::INTEGER) && k(to) == TypeKind::BOOLEAN) line("const bool " + t + " = " + a[0].v + " != 0;");
+                else if (k(f) == TypeKind::DOUBLE && k(to) == TypeKind::BOOLEAN) line("const bool " + t + " = " + a[0].v + " != 0.0;");
+                else if ((k(f) == TypeKind::BIGINT || k(f) == TypeKind::INTEGER) && k(to) == TypeKind::DECIMAL) {
+                    // main/type/DecimalCasts.java bigintToShortDecimal / bigintToLongDecimal: value * 10^scale, precision check
+                    if (to.isShortDecimal()) {
+                        std::string lim = i64Literal((int64_t)pow10_i128(to.precision - to.scale));
+                        line("const i64 " + t + " = (i64)" + a[0].v + " * " + i64Literal((int64_t)pow10_i128(to.scale)) + "; if ((i64)" + a[0].v + " >= " + lim + " || (i64)" + a[0].v + " <= -" + lim + ") err |= PGPU_ERR_OVERFLOW;");
+                    } else {
+                        std::string lim = i128Literal(pow10_i128(to.precision));
+                        line("const i128 " + t + " = (i128)" + a[0].v + " * " + i128Literal(pow10_i128(to.scale)) + "; if (" + t + " >= " + lim + " || " + t + " <= -" + lim + ") err |= PGPU_ERR_OVERFLOW;");
+                    }
+                } else if (k(f) == TypeKind::DECIMAL && k(to) == TypeKind::DECIMAL) {
+                    // main/type/DecimalToDecimalCasts.java: rescale (HALF_UP when narrowing) then precision check
+                    std::string src = toI128(a[0]).v, w = tmp("v");
+                    if (to.scale >= f.scale) line("const i128 " + w + " = " + src + " * " + i128Literal(pow10_i128(to.scale - f.scale)) + ";");
+                    else line("const i128 " + w + " = dec_div_round(" + src + ", " + i128Literal(pow10_i128(f.scale - to.scale)) + ");");
+                    std::string lim = i128Literal(pow10_i128(to.precision));
+                    line("if (" + w + " >= " + lim + " || " + w + " <= -" + lim + ") err |= PGPU_ERR_OVERFLOW;");
+                    if (f.precision - f.scale + to.scale > 38) unsupported("decimal cast whose intermediate exceeds 38 digits");
+                    line("const " + ct + " " + t + " = (" + ct + ")" + w + ";");
+                } else {
+                    unsupported("cast " + f.str() + " -> " + to.str());
+                }
+                r.v = t;
+                return r;
+            }
+        }
+        unsupported("operator");
+    }
+
+    Val gen(const Expr& e) {
+        switch (e.kind) {
+            case ExprKind::INPUT: return colVal(e.channel);
+            case ExprKind::CONST: return constant(e);
+            case ExprKind::CALL: return genCall(e);
+            case ExprKind::AND:
+            case ExprKind::OR: return genLogic(e);
+            case ExprKind::BETWEEN: {
+                Val v = gen(*e.args[0]), lo = gen(*e.args[1]), hi = gen(*e.args[2]);
+                Val ge = compare(Op::GE, v, lo), le = compare(Op::LE, v, hi);
+                return logic(true, {ge, le});
+            }
+            case ExprKind::IN: return genIn(e);
+            case ExprKind::IS_NULL: {
+                Val v = gen(*e.args[0]);
+                Val r;
+                r.type = Type::boolean();
+                r.v = v.nullable() ? v.n : "false";
+                return r;
+            }
+            case ExprKind::IF: return genIf(e);
+            case ExprKind::COALESCE: return genCoalesce(e);
+        }
+        unsupported("expression");
+    }
+};
+
+// ---------------------------------------------------------------------------------------------- key packing
+struct KeyPart {
+    std::string expr;  // u64 expression (already masked to nbytes)
+    int nbytes;
+};
+
+struct KeyField {
+    int projChannel;
+    Type type;
+    bool nullable;
+    int nullBit = -1;      // bit in the null bytes
+    int byteOffset = 0;    // of the value bytes
+    int nbytes = 0;
+};
+
+int keyBytes(const Type& t) {
+    switch (t.kind) {
+        case TypeKind::BOOLEAN: return 1;
+        case TypeKind::INTEGER:
+        case TypeKind::DATE: return 4;
+        case TypeKind::BIGINT:
+        case TypeKind::DOUBLE: return 8;
+        case TypeKind::DECIMAL: return t.precision <= 18 ? 8 : 16;
+        case TypeKind::VARCHAR: return t.precision + 1;
+        default: return 0;
+    }
+}
+
+std::string maskOf(int nbytes) {
+    if (nbytes >= 8) return "0xffffffffffffffffull";
+    std::ostringstream o;
+    o << "0x" << std::hex << ((1ull << (8 * nbytes)) - 1) << "ull";
+    return o.str();
+}
+
+}  // namespace
+
+GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
+    if (sig.size() != plan.input.size()) throw PlanError(PGPU_INVALID_ARGUMENT, "page has " + std::to_string(sig.size()) + " channels, plan expects " + std::to_string(plan.input.size()));
+    GenResult res;
+    res.NC = (int)plan.input.size();
+    Gen g(plan, sig);
+    std::vector<Type> proj = plan.projectedTypes();
+    const bool finalStep = plan.hasAgg && plan.step == Step::FINAL;
+
+    // which projected channels does the consumer need?
+    std::set<int> neededProj;
+    if (plan.hasAgg) {
+        for (int c : plan.groupChannels) neededProj.insert(c);
+        for (auto& a : plan.aggs) {
+            if (a.hasArg) {
+                int n = finalStep ? (int)Plan::intermediateTypes(a).size() : 1;
+                for (int j = 0; j < n; j++) neededProj.insert(a.arg + j);
+            }
+            if (a.mask >= 0) neededProj.insert(a.mask);
+        }
+    } else {
+        for (size_t c = 0; c < proj.size(); c++) neededProj.insert((int)c);
+    }
+    std::set<int> filterChans, restChans;
+    if (plan.filter) collectChannels(*plan.filter, filterChans);
+    for (int c : neededProj) collectChannels(*plan.projections[c], restChans);
+    std::set<int> phase2Loads;
+    for (int c : restChans)
+        if (!filterChans.count(c)) phase2Loads.insert(c);
+    for (int c : filterChans) res.usedChannels.push_back(c);
+    for (int c : phase2Loads) res.usedChannels.push_back(c);
+    for (int c : res.usedChannels) {
+        const Type& t = plan.input[c];
+        if (t.kind == TypeKind::VARCHAR && (t.precision == 0 || t.precision > 15))
+            unsupported("reading " + t.str() + " values (GPU var-width cells hold varchar(n), n <= 15)");
+        if (t.kind == TypeKind::VARBINARY && !finalStep) unsupported("varbinary input outside FINAL-step intermediate states");
+    }
+    bool projRaises = false;
+    for (int c : neededProj) projRaises |= canRaise(*plan.projections[c]);
+
+    std::ostringstream src;
+    src << "// generated by presto_b200 codegen — plan:\n";
+    {
+        std::istringstream pt(plan.text);
+        std::string l;
+        while (std::getline(pt, l)) src << "//   " << l << "\n";
+    }
+    src << "#include \"pgpu_device.cuh\"\n\n";
+
+    // ---------------------------------------------------------------- eval prologue shared by all modes
+    std::ostringstream evalFilter;  // code: loads + per-row filter -> sel[]
+    {
+        g.out.str("");
+        g.indent = 2;
+        g.line("const bool full = base + 4 <= nrows;");
+        g.emitTileLoads(filterChans);
+        g.line("bool any = false;");
+        g.line("#pragma unroll");
+        g.line("for (int r = 0; r < 4; r++) {");
+        g.indent++;
+        g.line("const bool live = base + r < nrows;");
+        if (plan.filter) {
+            bool fr = canRaise(*plan.filter);
+            if (fr) {
+                g.line("bool f = false;");
+                g.line("if (live) {");
+                g.indent++;
+            }
+            g.emitRowPrologue(filterChans);
+            Val f = g.gen(*plan.filter);
+            std::string fe = f.nullable() ? "(" + f.v + " && !" + f.n + ")" : f.v;
+            if (fr) {
+                g.line("f = " + fe + ";");
+                g.indent--;
+                g.line("}");
+                g.line("sel[r] = f;");
+            } else {
+                g.line("sel[r] = live && " + fe + ";");
+            }
+        } else {
+            g.line("sel[r] = live;");
+        }
+        g.line("any |= sel[r];");
+        g.indent--;
+        g.line("}");
+        g.line("if (!any) return;");
+        g.emitTileLoads(phase2Loads);
+        evalFilter << g.out.str();
+    }
+
+    auto genProjections = [&](std::map<int, Val>& pv) {
+        g.emitRowPrologue(restChans);
+        for (int c : neededProj) pv[c] = g.gen(*plan.projections[c]);
+    };
+
+    if (!plan.hasAgg) {
+        // ============================================================ COMPACT
+        res.mode = KernelMode::COMPACT;
+        res.NO = (int)proj.size();
+        for (auto& t : proj) {
+            OutColDesc d;
+            d.type = t;
+            if (t.kind == TypeKind::VARCHAR) {
+                d.stride = 16;
+                d.varWidth = true;
+                d.lenPrefixed = true;
+            } else {
+                d.stride = t.width();
+            }
+            res.out.push_back(d);
+        }
+        src << "struct P {\n";
+        src << "    static constexpr int NC = " << res.NC << ", NO = " << res.NO << ", KW = 0, NW = 0, SLOTW = 4;\n";
+        src << "    struct Proj {\n";
+        for (size_t c = 0; c < proj.size(); c++) {
+            src << "        " << ctype(proj[c]) << " v" << c << ";" << (proj[c].kind == TypeKind::VARCHAR ? " u64 w" + std::to_string(c) + ";" : "") << " bool n" << c << ";\n";
+        }
+        src << "    };\n";
+        src << "    PGPU_DEV static void eval_project(const PageArgs<NC>& a, i64 base, i64 nrows, bool (&sel)[4], Proj (&pv)[4], u32& err) {\n";
+        src << evalFilter.str();
+        g.out.str("");
+        g.indent = 2;
+        g.line("#pragma unroll");
+        g.line("for (int r = 0; r < 4; r++) {");
+        g.indent++;
+        g.line("if (sel[r]) {");
+        g.indent++;
+        std::map<int, Val> pv;
+        genProjections(pv);
+        for (size_t c = 0; c < proj.size(); c++) {
+            const Val& v = pv[(int)c];
+            std::string C = std::to_string(c);
+            g.line("pv[r].v" + C + " = " + v.v + ";" + (proj[c].kind == TypeKind::VARCHAR ? " pv[r].w" + C + " = " + v.hi + ";" : "") + " pv[r].n" + C + " = " + (v.nullable() ? v.n : "false") + ";");
+        }
+        g.indent--;
+        g.line("}");
+        g.indent--;
+        g.line("}");
+        src << g.out.str();
+        src << "    }\n";
+        src << "    PGPU_DEV static void store_row(const OutArgs<NO>& out, i64 pos, const Proj& p) {\n";
+        for (size_t c = 0; c < proj.size(); c++) {
+            std::string C = std::to_string(c);
+            const Type& t = proj[c];
+            if (t.kind == TypeKind::VARCHAR) src << "        { raw128 q; q.lo = p.v" << C << "; q.hi = p.w" << C << "; ((raw128*)out.c[" << C << "].values)[pos] = q; }\n";
+            else if (t.isLongDecimal()) src << "        ((raw128*)out.c[" << C << "].values)[pos] = dec_to_raw(p.v" << C << ");\n";
+            else if (t.kind == TypeKind::BOOLEAN) src << "        ((u8*)out.c[" << C << "].values)[pos] = p.v" << C << " ? 1 : 0;\n";
+            else src << "        ((" << stype(t) << "*)out.c[" << C << "].values)[pos] = p.v" << C << ";\n";
+            src << "        out.c[" << C << "].nulls[pos] = p.n" << C << " ? 1 : 0;\n";
+        }
+        src << "    }\n";
+        src << "};\n\n";
+        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, OutArgs<P::NO> out, Scratch sc) { body_compact<P>(a, out, sc); }\n";
+        res.source = src.str();
+        return res;
+    }
+
+    // ================================================================ aggregation modes
+    res.mode = plan.groupChannels.empty() ? KernelMode::AGG_GLOBAL : KernelMode::AGG_HASH;
+
+    // The row body is generated first into a buffer because cells are discovered while generating it.
+    g.out.str("");
+    g.indent = 4;
+    std::map<int, Val> pv;
+    genProjections(pv);
+
+    // ---- keys
+    std::vector<KeyField> fields;
+    int nullBits = 0;
+    for (int c : plan.groupChannels) {
+        KeyField f;
+        f.projChannel = c;
+        f.type = proj[c];
+        f.nullable = mayBeNull(*plan.projections[c]);
+        if (f.nullable) f.nullBit = nullBits++;
+        f.nbytes = keyBytes(f.type);
+        fields.push_back(f);
+    }
+    int off = (nullBits + 7) / 8;
+    for (auto& f : fields) {
+        f.byteOffset = off;
+        off += f.nbytes;
+    }
+    const int keyLen = off;
+    res.KW = (keyLen + 7) / 8;
+    if (res.KW > 8) unsupported("group key wider than 64 bytes");
+    if (res.mode == KernelMode::AGG_HASH) {
+        for (int w = 0; w < res.KW; w++) g.line("u64 kw" + std::to_string(w) + " = 0;");
+        auto put = [&](const std::string& e, int byteOff, int nbytes) {
+            // e is a u64 expression already masked to nbytes
+            int w = byteOff / 8, sh = (byteOff % 8) * 8;
+            g.line("kw" + std::to_string(w) + " |= (" + e + ")" + (sh ? " << " + std::to_string(sh) : "") + ";");
+            if (sh + nbytes * 8 > 64) g.line("kw" + std::to_string(w + 1) + " |= (" + e + ") >> " + std::to_string(64 - sh) + ";");
+        };
+        for (auto& f : fields) {
+            const Val& v = pv[f.projChannel];
+            if (f.nullable && v.nullable()) put("(u64)(" + v.n + " ? 1 : 0) << " + std::to_string(f.nullBit % 8), f.nullBit / 8, 1);
+            std::string lo, hi;
+            switch (f.type.kind) {
+                case TypeKind::BOOLEAN: lo = "(u64)(" + v.v + " ? 1 : 0)"; break;
+                case TypeKind::INTEGER:
+                case TypeKind::DATE: lo = "(u64)(u32)" + v.v; break;
+                case TypeKind::BIGINT: lo = "(u64)" + v.v; break;
+                case TypeKind::DOUBLE: lo = "f64_group_bits(" + v.v + ")"; break;
+                case TypeKind::DECIMAL:
+                    if (f.type.isShortDecimal()) lo = "(u64)" + v.v;
+                    else { lo = "(u64)(u128)" + v.v; hi = "(u64)((u128)" + v.v + " >> 64)"; }
+                    break;
+                case TypeKind::VARCHAR: lo = v.v; hi = v.hi; break;
+                default: unsupported("group key type");
+            }
+            auto nz = [&](const std::string& e) { return v.nullable() ? "(" + v.n + " ? 0ull : " + e + ")" : e; };
+            if (f.nbytes <= 8) {
+                put(nz(lo), f.byteOffset, f.nbytes);
+            } else {
+                put(nz(lo), f.byteOffset, 8);
+                put(nz("(" + hi + " & " + maskOf(f.nbytes - 8) + ")"), f.byteOffset + 8, f.nbytes - 8);
+            }
+        }
+        for (int w = 0; w < res.KW; w++) g.line("key[r][" + std::to_string(w) + "] = kw" + std::to_string(w) + ";");
+    }
+
+    // ---- cells
+    std::vector<Cell> cells;
+    std::map<std::string, int> cellIndex;
+    int nw = 0;
+    auto getCell = [&](const std::string& kind, const std::string& ident, int nwords, const std::vector<std::string>& contrib) -> int {
+        std::string k = kind + "|" + ident;
+        auto it = cellIndex.find(k);
+        if (it != cellIndex.end()) return it->second;
+        Cell c;
+        c.kind = kind;
+        c.word = nw;
+        c.nwords = nwords;
+        c.contrib = contrib;
+        nw += nwords;
+        cells.push_back(c);
+        cellIndex[k] = (int)cells.size() - 1;
+        return (int)cells.size() - 1;
+    };
+    auto sel1 = [](const std::string& cond, const std::string& e, const std::string& zero) { return cond == "true" ? e : "(" + cond + " ? " + e + " : " + zero + ")"; };
+
+    struct AggCells {
+        int cnt = -1, sum = -1, ext = -1;
+    };
+    std::vector<AggCells> aggCells;
+    for (auto& a : plan.aggs) {
+        AggCells ac;
+        if (!finalStep) {
+            std::string cond = "true";
+            if (a.mask >= 0) {
+                const Val& m = pv[a.mask];
+                cond = m.nullable() ? "(" + m.v + " && !" + m.n + ")" : m.v;
+            }
+            Val x;
+            if (a.hasArg) {
+                x = pv[a.arg];
+                if (x.nullable()) cond = cond == "true" ? "!" + x.n : "(" + cond + " && !" + x.n + ")";
+            }
+            const int argId = (a.hasArg && mayBeNull(*plan.projections[a.arg])) ? a.arg : -1;
+            const std::string cid = "arg=" + std::to_string(argId) + "|mask=" + std::to_string(a.mask);
+            const std::string vid = "arg=" + std::to_string(a.arg) + "|mask=" + std::to_string(a.mask);
+            ac.cnt = getCell("cnt", cid, 1, {sel1(cond, "1ull", "0ull")});
+            const Type& t = a.inType;
+            switch (a.fn) {
+                case AggFn::COUNT: break;
+                case AggFn::SUM:
+                case AggFn::AVG:
+                    if (t.kind == TypeKind::DOUBLE || (a.fn == AggFn::AVG && t.kind == TypeKind::BIGINT)) {
+                        std::string xv = t.kind == TypeKind::DOUBLE ? x.v : "(double)" + x.v;
+                        ac.sum = getCell("sumd", vid + (t.kind == TypeKind::DOUBLE ? "" : "|cast"), 1, {"d2u(" + sel1(cond, xv, "0.0") + ")"});
+                    } else if (t.kind == TypeKind::BIGINT) {
+                        ac.sum = getCell("sumi", vid, 2,
+                                         {sel1(cond, "(u64)(u32)" + x.v, "0ull"), sel1(cond, "(u64)(" + x.v + " >> 32)", "0ull")});
+                    } else if (t.kind == TypeKind::DECIMAL) {
+                        std::string w = "(i128)" + x.v;
+                        ac.sum = getCell("sumdec", vid, 4,
+                                         {sel1(cond, "(u64)(u32)(u128)(" + w + ")", "0ull"), sel1(cond, "(u64)(u32)((u128)(" + w + ") >> 32)", "0ull"),
+                                          sel1(cond, "(u64)(u32)((u128)(" + w + ") >> 64)", "0ull"), sel1(cond, "(u64)(i64)((" + w + ") >> 96)", "0ull")});
+                    }
+                    break;
+                case AggFn::MIN:
+                case AggFn::MAX: {
+                    bool isMax = a.fn == AggFn::MAX;
+                    std::string k;  // signed order key
+                    if (t.kind == TypeKind::DOUBLE) {
+                        // MinMaxCompare.maxDouble: (value > state) || isNaN(state) => NaN is the smallest for max;
+                        // min uses Double.compare (NaN largest)
+                        k = isMax ? "((" + x.v + " != " + x.v + ") ? (i64)0x8000000000000000ull : f64_order_key(" + x.v + "))" : "f64_order_key(" + x.v + ")";
+                    } else if (t.kind == TypeKind::BOOLEAN) {
+                        k = "(i64)(" + x.v + " ? 1 : 0)";
+                    } else if (t.isLongDecimal()) {
+                        unsupported(std::string(aggName(a.fn)) + "(" + t.str() + ")");
+                    } else {
+                        k = "(i64)" + x.v;
+                    }
+                    std::string enc = isMax ? "((u64)" + k + " ^ 0x8000000000000000ull)" : "(~((u64)" + k + " ^ 0x8000000000000000ull))";
+                    ac.ext = getCell(isMax ? "max" : "min", vid, 1, {sel1(cond, enc, "0ull")});
+                    break;
+                }
+            }
+        } else {
+            // FINAL: contributions come from the intermediate channels (AccumulatorCompiler.java:674-767 addIntermediate -> combine)
+            const Type& t = a.inType;
+            auto nn = [&](const Val& v) { return v.nullable() ? "!" + v.n : std::string("true"); };
+            switch (a.fn) {
+                case AggFn::COUNT: {
+                    const Val& c0 = pv[a.arg];
+                    ac.cnt = getCell("cntw", "F" + std::to_string(a.arg), 1, {sel1(nn(c0), "(u64)" + c0.v, "0ull")});
+                    break;
+                }
+                case AggFn::SUM:
+                case AggFn::AVG: {
+                    if (t.kind == TypeKind::DECIMAL) {
+                        // VARBINARY state: [count:8 (avg only)] overflow:8 value:16 (sign-magnitude)
+                        const Val& s0 = pv[a.arg];
+                        std::string p = s0.v;
+                        int o = a.fn == AggFn::AVG ? 1 : 0;
+                        std::string cond = nn(s0);
+                        std::string q = "((const u64*)" + p + ")";
+                        std::string val = "dec_from_raw(raw128{" + q + "[" + std::to_string(o + 1) + "], " + q + "[" + std::to_string(o + 2) + "]})";
+                        std::string ov = "(i64)" + q + "[" + std::to_string(o) + "]";
+                        if (a.fn == AggFn::AVG) ac.cnt = getCell("cntw", "F" + std::to_string(a.arg), 1, {sel1(cond, q + "[0]", "0ull")});
+                        else ac.cnt = getCell("cnt", "F" + std::to_string(a.arg), 1, {sel1(cond, "1ull", "0ull")});
+                        ac.sum = getCell("sumdec", "F" + std::to_string(a.arg), 4,
+                                         {sel1(cond, "(u64)(u32)(u128)(" + val + ")", "0ull"), sel1(cond, "(u64)(u32)((u128)(" + val + ") >> 32)", "0ull"),
+                                          sel1(cond, "(u64)(u32)((u128)(" + val + ") >> 64)", "0ull"),
+                                          sel1(cond, "(u64)((i64)((" + val + ") >> 96) + (" + ov + " << 31))", "0ull")});
+                    } else if (a.fn == AggFn::AVG) {
+                        const Val &s0 = pv[a.arg], &c1 = pv[a.arg + 1];
+                        ac.sum = getCell("sumd", "F" + std::to_string(a.arg), 1, {"d2u(" + sel1(nn(s0), s0.v, "0.0") + ")"});
+                        ac.cnt = getCell("cntw", "F" + std::to_string(a.arg + 1), 1, {sel1(nn(c1), "(u64)" + c1.v, "0ull")});
+                    } else {
+                        const Val &c0 = pv[a.arg], &s1 = pv[a.arg + 1];
+                        ac.cnt = getCell("cntw", "F" + std::to_string(a.arg), 1, {sel1(nn(c0), "(u64)" + c0.v, "0ull")});
+                        if (t.kind == TypeKind::DOUBLE) ac.sum = getCell("sumd", "F" + std::to_string(a.arg + 1), 1, {"d2u(" + sel1(nn(s1), s1.v, "0.0") + ")"});
+                        else ac.sum = getCell("sumi", "F" + std::to_string(a.arg + 1), 2, {sel1(nn(s1), "(u64)(u32)" + s1.v, "0ull"), sel1(nn(s1), "(u64)(" + s1.v + " >> 32)", "0ull")});
+                    }
+                    break;
+                }
+                case AggFn::MIN:
+                case AggFn::MAX: {
+                    bool isMax = a.fn == AggFn::MAX;
+                    const Val& x = pv[a.arg];
+                    std::string cond = nn(x), k;
+                    if (t.kind == TypeKind::DOUBLE) k = isMax ? "((" + x.v + " != " + x.v + ") ? (i64)0x8000000000000000ull : f64_order_key(" + x.v + "))" : "f64_order_key(" + x.v + ")";
+                    else if (t.kind == TypeKind::BOOLEAN) k = "(i64)(" + x.v + " ? 1 : 0)";
+                    else if (t.isLongDecimal()) unsupported(std::string(aggName(a.fn)) + "(" + t.str() + ")");
+                    else k = "(i64)" + x.v;
+                    std::string enc = isMax ? "((u64)" + k + " ^ 0x8000000000000000ull)" : "(~((u64)" + k + " ^ 0x8000000000000000ull))";
+                    ac.cnt = getCell("cnt", "F" + std::to_string(a.arg), 1, {sel1(cond, "1ull", "0ull")});
+                    ac.ext = getCell(isMax ? "max" : "min", "F" + std::to_string(a.arg), 1, {sel1(cond, enc, "0ull")});
+                    break;
+                }
+            }
+        }
+        aggCells.push_back(ac);
+    }
+    for (auto& c : cells)
+        for (int j = 0; j < c.nwords; j++) g.line("cw[r][" + std::to_string(c.word + j) + "] = " + c.contrib[j] + ";");
+    std::string rowBody = g.out.str();
+
+    res.NW = nw;
+    for (auto& c : cells)
+        for (int j = 0; j < c.nwords; j++) res.cellKinds.push_back(c.kind == "sumd" ? 1 : (c.kind == "max" || c.kind == "min") ? 2 : c.kind == "cnt" ? 3 : 0);
+    const int NW = res.NW, KW = res.KW;
+    const int NWA = std::max(NW, 1), KWA = std::max(KW, 1);
+    res.SLOTW = ((1 + KW + NW) + 3) / 4 * 4;
+
+    // directory sizing (shared memory): 8 warps x DCAP x NW words + keys + tags
+    res.useDir = res.mode == KernelMode::AGG_HASH && plan.expectedGroups <= 4096 && NW > 0;
+    res.dirCap = 0;
+    if (res.useDir) {
+        int cap = 128;
+        while (cap > 16 && (8 * cap * NWA * 8 + cap * KW * 8 + cap * 4 + 16) > 40 * 1024) cap /= 2;
+        res.dirCap = cap;
+        res.smemBytes = 8 * cap * NWA * 8 + cap * KW * 8 + cap * 4 + 16;
+    }
+
+    // ---- outputs
+    std::vector<Type> outTypes = plan.outputTypes();
+    res.NO = (int)outTypes.size();
+    for (auto& t : outTypes) {
+        OutColDesc d;
+        d.type = t;
+        if (t.kind == TypeKind::VARCHAR) {
+            d.stride = 16;
+            d.varWidth = true;
+            d.lenPrefixed = true;
+        } else if (t.kind == TypeKind::VARBINARY) {
+            d.varWidth = true;
+            d.stride = 0;  // fixed below per aggregate
+        } else {
+            d.stride = t.width();
+        }
+        res.out.push_back(d);
+    }
+
+    src << "struct P {\n";
+    src << "    static constexpr int NC = " << res.NC << ", NO = " << res.NO << ", KW = " << KW << ", NW = " << NW << ", SLOTW = " << res.SLOTW << ";\n";
+    src << "    static constexpr int KWA = " << KWA << ", NWA = " << NWA << ";\n";
+    src << "    static constexpr bool USE_DIR = " << (res.useDir ? "true" : "false") << ";\n";
+    src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 4;\n";
+    auto kindName = [&](int k) { return k == 0 ? "CK_ADD_U64" : k == 1 ? "CK_ADD_F64" : k == 2 ? "CK_MAX_U64" : "CK_CNT"; };
+    src << "    PGPU_DEV static void identity(u64 (&a)[NWA]) {\n";
+    for (int w = 0; w < NWA; w++) src << "        a[" << w << "] = 0ull;\n";
+    src << "    }\n";
+    src << "    PGPU_DEV static void identity_ptr(u64* a) {\n";
+    for (int w = 0; w < NW; w++) src << "        a[" << w << "] = 0ull;\n";
+    src << "    }\n";
+    auto emitCombine = [&](const char* name, const char* sigA, const char* sigB) {
+        src << "    PGPU_DEV static void " << name << "(" << sigA << ", " << sigB << ") {\n";
+        for (int w = 0; w < NW; w++) src << "        a[" << w << "] = cell_combine<" << kindName(res.cellKinds[w]) << ">(a[" << w << "], b[" << w << "]);\n";
+        src << "    }\n";
+    };
+    emitCombine("combine", "u64 (&a)[NWA]", "const u64 (&b)[NWA]");
+    emitCombine("combine_ptr", "u64* a", "const u64 (&b)[NWA]");
+    emitCombine("combine_ptr_to", "u64 (&a)[NWA]", "const u64* b");
+    src << "    PGPU_DEV static void warp_reduce_cells(u64 (&a)[NWA]) {\n";
+    for (int w = 0; w < NW; w++) src << "        a[" << w << "] = warp_reduce<" << kindName(res.cellKinds[w]) << ">(a[" << w << "]);\n";
+    src << "    }\n";
+    src << "    PGPU_DEV static void atomic_cells(u64* cells, const u64 (&cw)[NWA]) {\n";
+    for (int w = 0; w < NW; w++) src << "        cell_atomic<" << kindName(res.cellKinds[w]) << ">(cells + " << w << ", cw[" << w << "]);\n";
+    src << "    }\n";
+
+    // ---- eval
+    src << "    PGPU_DEV static void eval(const PageArgs<NC>& a, i64 base, i64 nrows, bool (&sel)[4], u64 (&key)[4][KWA], u64 (&cw)[4][NWA], u32& err) {\n";
+    src << evalFilter.str();
+    src << "        #pragma unroll\n";
+    src << "        for (int r = 0; r < 4; r++) {\n";
+    src << "            if (sel[r]) {\n";
+    src << rowBody;
+    src << "            }\n";
+    src << "        }\n";
+    src << "    }\n";
+    (void)projRaises;
+
+    // ---- emit (finalisation of one group)
+    {
+        std::ostringstream em;
+        auto L = [&](const std::string& s) { em << "        " << s << "\n"; };
+        int oc = 0;
+        // keys
+        for (auto& f : fields) {
+            std::string O = std::to_string(oc);
+            auto get = [&](int byteOff, int nbytes) -> std::string {
+                int w = byteOff / 8, sh = (byteOff % 8) * 8;
+                std::string e = "(key[" + std::to_string(w) + "]" + (sh ? " >> " + std::to_string(sh) : "") + ")";
+                if (sh + nbytes * 8 > 64) e = "(" + e + " | (key[" + std::to_string(w + 1) + "] << " + std::to_string(64 - sh) + "))";
+                if (nbytes < 8) e = "(" + e + " & " + maskOf(nbytes) + ")";
+                return e;
+            };
+            if (f.nullable) L("out.c[" + O + "].nulls[pos] = (u8)(" + get(f.nullBit / 8, 1) + " >> " + std::to_string(f.nullBit % 8) + ") & 1;");
+            else L("out.c[" + O + "].nulls[pos] = 0;");
+            switch (f.type.kind) {
+                case TypeKind::BOOLEAN: L("((u8*)out.c[" + O + "].values)[pos] = (u8)" + get(f.byteOffset, 1) + ";"); break;
+                case TypeKind::INTEGER:
+                case TypeKind::DATE: L("((i32*)out.c[" + O + "].values)[pos] = (i32)(u32)" + get(f.byteOffset, 4) + ";"); break;
+                case TypeKind::BIGINT:
+                case TypeKind::DOUBLE: L("((u64*)out.c[" + O + "].values)[pos] = " + get(f.byteOffset, 8) + ";"); break;
+                case TypeKind::DECIMAL:
+                    if (f.type.isShortDecimal()) L("((u64*)out.c[" + O + "].values)[pos] = " + get(f.byteOffset, 8) + ";");
+                    else L("((raw128*)out.c[" + O + "].values)[pos] = dec_to_raw((i128)(((u128)" + get(f.byteOffset + 8, 8) + " << 64) | (u128)" + get(f.byteOffset, 8) + "));");
+                    break;
+                case TypeKind::VARCHAR: {
+                    std::string lo = get(f.byteOffset, std::min(8, f.nbytes));
+                    std::string hi = f.nbytes > 8 ? get(f.byteOffset + 8, f.nbytes - 8) : "0ull";
+                    L("{ raw128 q; q.lo = " + lo + "; q.hi = " + hi + "; ((raw128*)out.c[" + O + "].values)[pos] = q; }");
+                    break;
+                }
+                default: break;
+            }
+            oc++;
+        }
+        // aggregates
+        auto cw = [&](int cell, int j) { return "cells[" + std::to_string(cells[cell].word + j) + "]"; };
+        auto sum128 = [&](int cell) {  // 4 limbs of 32 bits (top limb signed 64) -> i128 + fits flag in `fit`
+            std::string c0 = cw(cell, 0), c1 = cw(cell, 1), c2 = cw(cell, 2), c3 = cw(cell, 3);
+            L("i128 s128; bool fit;");
+            L("{ u128 t0 = (u128)" + c0 + " + ((u128)" + c1 + " << 32) + ((u128)" + c2 + " << 64); i128 hi = (i128)(i64)" + c3 + " + (i128)(u64)(t0 >> 96);");
+            L("  fit = (hi >= -((i128)1 << 31)) && (hi < ((i128)1 << 31)); s128 = (i128)(((u128)hi << 96) | (t0 & (((u128)1 << 96) - 1))); }");
+        };
+        for (size_t ai = 0; ai < plan.aggs.size(); ai++) {
+            const AggSpec& a = plan.aggs[ai];
+            const AggCells& ac = aggCells[ai];
+            const Type& t = a.inType;
+            std::string cnt = ac.cnt >= 0 ? cw(ac.cnt, 0) : "0ull";
+            auto O = [&](int k) { return std::to_string(oc + k); };
+            auto setNull = [&](int k, const std::string& cond) { L("out.c[" + O(k) + "].nulls[pos] = (" + cond + ") ? 1 : 0;"); };
+            L("{");
+            auto extDecode = [&](bool isMax) -> std::string {
+                std::string raw = cw(ac.ext, 0);
+                return isMax ? "(i64)(" + raw + " ^ 0x8000000000000000ull)" : "(i64)((~" + raw + ") ^ 0x8000000000000000ull)";
+            };
+            auto storeMinMax = [&](int k, bool isMax) {
+                std::string kx = extDecode(isMax);
+                if (t.kind == TypeKind::DOUBLE) {
+                    if (isMax) L("{ i64 kx = " + kx + "; ((double*)out.c[" + O(k) + "].values)[pos] = (kx == (i64)0x8000000000000000ull) ? u2d(0x7ff8000000000000ull) : f64_from_order_key(kx); }");
+                    else L("((double*)out.c[" + O(k) + "].values)[pos] = f64_from_order_key(" + kx + ");");
+                } else if (t.kind == TypeKind::BOOLEAN) L("((u8*)out.c[" + O(k) + "].values)[pos] = (u8)" + kx + ";");
+                else if (t.isInt32()) L("((i32*)out.c[" + O(k) + "].values)[pos] = (i32)" + kx + ";");
+                else L("((i64*)out.c[" + O(k) + "].values)[pos] = " + kx + ";");
+            };
+            const bool partial = plan.step == Step::PARTIAL;
+            switch (a.fn) {
+                case AggFn::COUNT:
+                    L("((i64*)out.c[" + O(0) + "].values)[pos] = (i64)" + cnt + ";");
+                    setNull(0, "false");
+                    oc += 1;
+                    break;
+                case AggFn::SUM:
+                case AggFn::AVG:
+                    if (t.kind == TypeKind::DECIMAL) {
+                        sum128(ac.sum);
+                        if (partial) {
+                            // VARBINARY [count] overflow value (LongDecimalWithOverflow[AndLong]StateSerializer); canonical form: overflow = 0 when the sum fits
+                            int stride = a.fn == AggFn::AVG ? 32 : 24;
+                            res.out[oc].stride = stride;
+                            std::string base = "((u64*)((u8*)out.c[" + O(0) + "].values + pos * " + std::to_string(stride) + "))";
+                            L("{ i64 ovf = 0; i128 v = s128;");
+                            L("  if (!fit) { /* |sum| >= 2^127: split into overflow * 2^127 + remainder */");
+                            std::string c3 = cw(ac.sum, 3);
+                            L("    u128 t0 = (u128)" + cw(ac.sum, 0) + " + ((u128)" + cw(ac.sum, 1) + " << 32) + ((u128)" + cw(ac.sum, 2) + " << 64); i128 hi = (i128)(i64)" + c3 + " + (i128)(u64)(t0 >> 96);");
+                            L("    ovf = (i64)(hi >> 31); i128 rem = hi - ((i128)ovf << 31); v = (i128)(((u128)rem << 96) | (t0 & (((u128)1 << 96) - 1))); }");
+                            L("  raw128 q = dec_to_raw(v); u64* o = " + base + ";");
+                            if (a.fn == AggFn::AVG) L("  o[0] = " + cnt + "; o[1] = (u64)ovf; o[2] = q.lo; o[3] = q.hi; }");
+                            else L("  o[0] = (u64)ovf; o[1] = q.lo; o[2] = q.hi; }");
+                            setNull(0, cnt + " == 0ull");
+                            oc += 1;
+                        } else if (a.fn == AggFn::SUM) {
+                            // DecimalSumAggregation.outputLongDecimal :177-189
+                            L("if (" + cnt + " != 0ull && (!fit || dec_overflows(s128))) err |= PGPU_ERR_OVERFLOW;");
+                            L("((raw128*)out.c[" + O(0) + "].values)[pos] = dec_to_raw(s128);");
+                            setNull(0, cnt + " == 0ull");
+                            oc += 1;
+                        } else {
+                            // DecimalAverageAggregation.average :218-227: sum / count, HALF_UP at the type's scale
+                            L("i128 avg = 0; if (" + cnt + " != 0ull) { if (!fit) err |= PGPU_ERR_OVERFLOW; else avg = dec_div_round(s128, (i128)" + cnt + "); }");
+                            if (a.outType.isShortDecimal()) L("((i64*)out.c[" + O(0) + "].values)[pos] = (i64)avg;");
+                            else L("((raw128*)out.c[" + O(0) + "].values)[pos] = dec_to_raw(avg);");
+                            setNull(0, cnt + " == 0ull");
+                            oc += 1;
+                        }
+                    } else if (a.fn == AggFn::AVG) {
+                        std::string s = "u2d(" + cw(ac.sum, 0) + ")";
+                        if (partial) {  // ROW(double sum, bigint count)
+                            L("((double*)out.c[" + O(0) + "].values)[pos] = " + s + "; ((i64*)out.c[" + O(1) + "].values)[pos] = (i64)" + cnt + ";");
+                            setNull(0, "false");
+                            setNull(1, "false");
+                            oc += 2;
+                        } else {  // AverageAggregations.output :66-79
+                            L("((double*)out.c[" + O(0) + "].values)[pos] = " + cnt + " ? " + s + " / (double)(i64)" + cnt + " : 0.0;");
+                            setNull(0, cnt + " == 0ull");
+                            oc += 1;
+                        }
+                    } else if (t.kind == TypeKind::DOUBLE) {
+                        std::string s = "u2d(" + cw(ac.sum, 0) + ")";
+                        if (partial) {  // ROW(bigint count, double sum)
+                            L("((i64*)out.c[" + O(0) + "].values)[pos] = (i64)" + cnt + "; ((double*)out.c[" + O(1) + "].values)[pos] = " + s + ";");
+                            setNull(0, "false");
+                            setNull(1, "false");
+                            oc += 2;
+                        } else {  // DoubleSumAggregation.output :54-62
+                            L("((double*)out.c[" + O(0) + "].values)[pos] = " + s + ";");
+                            setNull(0, cnt + " == 0ull");
+                            oc += 1;
+                        }
+                    } else {  // sum(bigint): LongSumAggregation — exact; NUMERIC_VALUE_OUT_OF_RANGE when the total leaves int64
+                        L("i128 tot = (i128)(u128)" + cw(ac.sum, 0) + " + ((i128)(i64)" + cw(ac.sum, 1) + " << 32);");
+                        L("if (tot > (i128)0x7fffffffffffffffll || tot < -(i128)0x7fffffffffffffffll - 1) err |= PGPU_ERR_OVERFLOW;");
+                        if (partial) {
+                            L("((i64*)out.c[" + O(0) + "].values)[pos] = (i64)" + cnt + "; ((i64*)out.c[" + O(1) + "].values)[pos] = (i64)tot;");
+                            setNull(0, "false");
+                            setNull(1, "false");
+                            oc += 2;
+                        } else {
+                            L("((i64*)out.c[" + O(0) + "].values)[pos] = (i64)tot;");
+                            setNull(0, cnt + " == 0ull");
+                            oc += 1;
+                        }
+                    }
+                    break;
+                case AggFn::MIN:
+                case AggFn::MAX:
+                    storeMinMax(0, a.fn == AggFn::MAX);
+                    setNull(0, cnt + " == 0ull");
+                    oc += 1;
+                    break;
+            }
+            L("}");
+        }
+        src << "    PGPU_DEV static void emit(const u64* key, const u64* cells, const OutArgs<NO>& out, i64 pos, u32& err) {\n";
+        src << em.str();
+        src << "    }\n";
+    }
+    src << "};\n\n";
+    if (res.mode == KernelMode::AGG_GLOBAL) {
+        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, Scratch sc) { body_agg_global<P>(a, sc); }\n";
+        src << "extern \"C\" __global__ void pgpu_k_emit(Scratch sc, OutArgs<P::NO> out) { body_emit_global<P>(sc, out); }\n";
+    } else {
+        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, TableArgs t, Scratch sc) { body_agg_hash<P>(a, t, sc); }\n";
+        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots) { body_materialize<P>(t, out, sc, first_slot, nslots); }\n";
+        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_rehash(TableArgs from, TableArgs to, Scratch sc) { body_rehash<P>(from, to, sc); }\n";
+    }
+    res.source = src.str();
+    return res;
+}
+
+}  // namespace pgpu

@@ -1,0 +1,45 @@
+// codegen.h — Plan + page-encoding signature -> CUDA source for NVRTC.
+//
+// Replaces the reference's bytecode generators for this path: main/sql/gen/PageFunctionCompiler.java:219-365
+// (projections), :459-544 (filter), main/sql/gen/RowExpressionCompiler.java:78-229 and the special-form generators,
+// main/operator/aggregation/AccumulatorCompiler.java:261-330,490-569 (accumulator loops).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "plan.h"
+
+namespace pgpu {
+
+// How one input channel arrives in a page. Kernel variants are specialised (and cached) per signature.
+struct ColSig {
+    int encoding = 0;        // pgpu_encoding
+    bool nullable = false;   // PLAIN: valueIsNull present; DICTIONARY/RLE: the dictionary/value block has nulls
+    bool operator==(const ColSig& o) const { return encoding == o.encoding && nullable == o.nullable; }
+};
+
+enum class KernelMode { COMPACT, AGG_GLOBAL, AGG_HASH };
+
+struct OutColDesc {
+    Type type;
+    int stride = 0;          // bytes per row in the device output buffer
+    bool varWidth = false;   // device buffer holds fixed-stride cells that the host turns into offsets + bytes
+    bool lenPrefixed = false;// varchar key cells: byte 0 = length, bytes 1.. = data; else `stride` payload bytes
+};
+
+struct GenResult {
+    std::string source;
+    KernelMode mode = KernelMode::COMPACT;
+    int NC = 0, KW = 0, NW = 0, SLOTW = 0, NO = 0;
+    bool useDir = false;
+    int dirCap = 0;
+    int smemBytes = 0;         // dynamic shared memory of the page kernel
+    std::vector<int> cellKinds;  // NW entries (CK_*)
+    std::vector<OutColDesc> out;
+    std::vector<int> usedChannels;  // input channels the kernels dereference
+};
+
+// throws PlanError(PGPU_NOT_SUPPORTED) for expression forms that parse but have no GPU implementation
+GenResult generate(const Plan& plan, const std::vector<ColSig>& sig);
+
+}  // namespace pgpu

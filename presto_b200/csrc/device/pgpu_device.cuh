@@ -1,0 +1,734 @@
+// pgpu_device.cuh — hand-written sm_100a device library of the fused scan -> filter -> project -> aggregate
+// pipeline. The plan compiler (codegen.cpp) emits a small traits struct `P` (column loads, the RowExpression
+// subset as straight-line CUDA, key packing, accumulator contributions, output finalisation) and instantiates
+// the kernel templates below with it; NVRTC compiles the result for sm_100a (jit.cpp).
+//
+// What the kernels replace in the reference (paths under core/trino-main/src/main/java/io/trino/):
+//   k_agg_global   PageProcessor (operator/project/PageProcessor.java:111-137,307-347) + AggregationOperator.addInput
+//                  (operator/AggregationOperator.java:145-161) fused: one pass, no SelectedPositions materialised.
+//   k_agg_hash     PageProcessor + InMemoryHashAggregationBuilder.processPage (operator/aggregation/builder/
+//                  InMemoryHashAggregationBuilder.java:139-155): GroupByHash.getGroupIds (operator/BigintGroupByHash.java:
+//                  213-244, MultiChannelGroupByHash.java:281-342) and every GroupedAccumulator.addInput
+//                  (operator/aggregation/AccumulatorCompiler.java:490-569) in one pass; no GroupByIdBlock.
+//   k_compact      PageFilter.positionsArrayToSelectedPositions (operator/project/PageFilter.java:27-50) +
+//                  PageProjection.project at the selected positions (sql/gen/PageFunctionCompiler.java:283-319).
+//   k_materialize  InMemoryHashAggregationBuilder.buildResult (…/InMemoryHashAggregationBuilder.java:272-298).
+//   k_rehash       BigintGroupByHash.tryRehash (operator/BigintGroupByHash.java:262-313).
+//
+// Memory-system design (HBM-bound integer/fp64 work, no tensor cores): every thread owns R consecutive rows so
+// each fixed-width column is read with 128-bit, fully coalesced, L1-bypassing loads (ld.global.nc.L1::no_allocate);
+// grids are persistent (a multiple of the SM count, host side) and stride over tiles; accumulators live in
+// registers (global aggregation), in warp-private shared-memory tables keyed through a block-shared key directory
+// (low cardinality), or in an open-addressing table in HBM updated with fire-and-forget RED atomics (high cardinality).
+#pragma once
+
+typedef long long i64;
+typedef unsigned long long u64;
+typedef int i32;
+typedef unsigned int u32;
+typedef unsigned char u8;
+typedef signed char i8;
+typedef __int128 i128;
+typedef unsigned __int128 u128;
+
+#define PGPU_DEV __device__ __forceinline__
+#define FULLMASK 0xffffffffu
+
+// sticky error bits (host maps them to pgpu_status / TrinoException codes)
+#define PGPU_ERR_OVERFLOW 1u     // NUMERIC_VALUE_OUT_OF_RANGE
+#define PGPU_ERR_DIVZERO 2u      // DIVISION_BY_ZERO
+#define PGPU_ERR_TABLE_FULL 4u   // internal: probe chain exhausted (host sizes tables so this cannot happen)
+#define PGPU_ERR_VARCHAR_LEN 8u  // a varchar(n) key longer than n bytes
+#define PGPU_ERR_OUTPUT_FULL 16u // internal: output buffer too small
+#define PGPU_ERR_INVALID_CAST 32u// INVALID_CAST_ARGUMENT
+
+// One input Block as the kernels see it (device pointers). Plain blocks use values/nulls/offsets;
+// dictionary blocks use ids + d*; RLE blocks use d* with a single position.
+struct ColArg {
+    const void* values;
+    const u8* nulls;
+    const i32* offsets;
+    const i32* ids;
+    const void* dvalues;
+    const u8* dnulls;
+    const i32* doffsets;
+};
+
+template <int NC>
+struct PageArgs {
+    ColArg c[NC];
+    i64 rows;
+};
+
+// Open-addressing table in HBM. Slot = [tag][key words][cell words], SLOTW 64-bit words, 32-byte aligned.
+struct TableArgs {
+    u64* slots;
+    u64 capacity;    // slots
+    u64* counters;   // [0] = groups inserted, [1] = failed inserts
+};
+
+// Per-pipeline device scratch shared by all kernels.
+struct Scratch {
+    u32* err;        // sticky error bits
+    u64* partials;   // k_agg_global: [grid][NW] block partials
+    u32* ticket;     // k_agg_global / k_compact: block tickets (zeroed by the finishing block)
+    u64* state;      // k_agg_global: the single accumulator slot [NW]
+    u64* tile_status;// k_compact: decoupled look-back descriptors
+    u64* out_count;  // k_compact / k_materialize: rows written
+};
+
+struct OutCol {
+    void* values;    // fixed width: element array; var-width: 16-byte cells (len byte + 15 data bytes)
+    u8* nulls;       // 1 byte / position
+};
+
+template <int NO>
+struct OutArgs {
+    OutCol c[NO];
+    i64 capacity;    // rows the buffers can hold
+};
+
+// ------------------------------------------------------------------------------------------------ loads
+PGPU_DEV int4 ld_stream16(const void* p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+PGPU_DEV u32 ld_stream4(const void* p) {
+    u32 r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+PGPU_DEV u64 ld_stream8(const void* p) {
+    u64 r;
+    asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(r) : "l"(p));
+    return r;
+}
+
+// Load the R (=4) consecutive elements [base, base+4) of a flat column. `full` = the whole tile is in range and the
+// column pointer is 16-byte aligned (host guarantees alignment; base is a multiple of 4).
+template <typename T>
+PGPU_DEV void load_tile4(const T* __restrict__ p, i64 base, i64 nrows, bool full, T (&v)[4]) {
+    if (full) {
+        if (sizeof(T) == 8) {
+            int4 a = ld_stream16(p + base), b = ld_stream16(p + base + 2);
+            u64 w[4];
+            w[0] = ((u64)(u32)a.y << 32) | (u32)a.x;
+            w[1] = ((u64)(u32)a.w << 32) | (u32)a.z;
+            w[2] = ((u64)(u32)b.y << 32) | (u32)b.x;
+            w[3] = ((u64)(u32)b.w << 32) | (u32)b.z;
+#pragma unroll
+            for (int r = 0; r < 4; r++) v[r] = *reinterpret_cast<T*>(&w[r]);
+        } else if (sizeof(T) == 4) {
+            int4 a = ld_stream16(p + base);
+            u32 w[4] = {(u32)a.x, (u32)a.y, (u32)a.z, (u32)a.w};
+#pragma unroll
+            for (int r = 0; r < 4; r++) v[r] = *reinterpret_cast<T*>(&w[r]);
+        } else if (sizeof(T) == 1) {
+            u32 a = ld_stream4(p + base);
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                u8 b = (u8)(a >> (8 * r));
+                v[r] = *reinterpret_cast<T*>(&b);
+            }
+        } else {  // 16-byte elements (Int128ArrayBlock)
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                int4 a = ld_stream16(p + base + r);
+                v[r] = *reinterpret_cast<T*>(&a);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            if (base + r < nrows) v[r] = p[base + r];
+            else v[r] = T();
+        }
+    }
+}
+
+struct raw128 {
+    u64 lo, hi;
+};
+
+// Int128ArrayBlock element (sign-magnitude, low word first, sign = top bit of word 1;
+// spi/type/UnscaledDecimal128Arithmetic.java:30-56) <-> two's complement.
+PGPU_DEV i128 dec_from_raw(raw128 r) {
+    u128 mag = ((u128)(r.hi & 0x7fffffffffffffffull) << 64) | r.lo;
+    return (r.hi >> 63) ? -(i128)mag : (i128)mag;
+}
+PGPU_DEV raw128 dec_to_raw(i128 v) {
+    bool neg = v < 0;
+    u128 mag = neg ? (u128)0 - (u128)v : (u128)v;
+    raw128 r;
+    r.lo = (u64)mag;
+    r.hi = (u64)(mag >> 64) | (neg ? 0x8000000000000000ull : 0ull);
+    return r;
+}
+// |v| > 10^38 - 1  (Decimals.MAX_UNSCALED_DECIMAL; UnscaledDecimal128Arithmetic.throwIfOverflows)
+PGPU_DEV bool dec_overflows(i128 v) {
+    const u128 lim = ((u128)0x4b3b4ca85a86c47aull << 64) | 0x098a224000000000ull;  // 10^38
+    u128 mag = v < 0 ? (u128)0 - (u128)v : (u128)v;
+    return mag >= lim;
+}
+// exact 128-bit product with overflow detection (UnscaledDecimal128Arithmetic.multiply + throwIfOverflows)
+PGPU_DEV i128 dec_mul(i128 a, i128 b, u32& err) {
+    bool neg = (a < 0) != (b < 0);
+    u128 ma = a < 0 ? (u128)0 - (u128)a : (u128)a, mb = b < 0 ? (u128)0 - (u128)b : (u128)b;
+    u64 a0 = (u64)ma, a1 = (u64)(ma >> 64), b0 = (u64)mb, b1 = (u64)(mb >> 64);
+    bool ovf = (a1 != 0 && b1 != 0);
+    u128 lo = (u128)a0 * b0;
+    u128 c1 = (u128)a0 * b1, c2 = (u128)a1 * b0;
+    ovf |= (c1 >> 64) != 0 || (c2 >> 64) != 0;
+    u128 mid = (u128)(u64)c1 + (u128)(u64)c2 + (lo >> 64);
+    ovf |= (mid >> 63) != 0;
+    u128 m = ((u128)(u64)mid << 64) | (u64)lo;
+    i128 r = neg ? -(i128)m : (i128)m;
+    if (ovf || dec_overflows(r)) err |= PGPU_ERR_OVERFLOW;
+    return r;
+}
+// a * 10^k with overflow detection (UnscaledDecimal128Arithmetic.rescale, upscale direction); p10 = 10^k
+PGPU_DEV i128 dec_upscale(i128 a, i128 p10, u32& err) { return dec_mul(a, p10, err); }
+// HALF_UP division by 10^k (rescale down / avg): round half away from zero
+PGPU_DEV i128 dec_div_round(i128 a, i128 d) {
+    bool neg = (a < 0) != (d < 0);
+    u128 ma = a < 0 ? (u128)0 - (u128)a : (u128)a, md = d < 0 ? (u128)0 - (u128)d : (u128)d;
+    u128 q = ma / md, rem = ma % md;
+    if (rem >= md - rem) q += 1;  // 2*rem >= md without overflow
+    return neg ? -(i128)q : (i128)q;
+}
+
+// ------------------------------------------------------------------------------------------------ scalars
+PGPU_DEV u64 d2u(double d) { return (u64)__double_as_longlong(d); }
+PGPU_DEV double u2d(u64 u) { return __longlong_as_double((i64)u); }
+PGPU_DEV i64 add_i64_checked(i64 a, i64 b, u32& err) {  // Math.addExact (main/type/BigintOperators.java:47-56)
+    i64 r = (i64)((u64)a + (u64)b);
+    if (((a ^ r) & (b ^ r)) < 0) err |= PGPU_ERR_OVERFLOW;
+    return r;
+}
+PGPU_DEV i64 sub_i64_checked(i64 a, i64 b, u32& err) {
+    i64 r = (i64)((u64)a - (u64)b);
+    if (((a ^ b) & (a ^ r)) < 0) err |= PGPU_ERR_OVERFLOW;
+    return r;
+}
+PGPU_DEV i64 mul_i64_checked(i64 a, i64 b, u32& err) {
+    i64 lo = (i64)((u64)a * (u64)b);
+    i64 hi = __mul64hi(a, b);
+    if (hi != (lo >> 63)) err |= PGPU_ERR_OVERFLOW;
+    return lo;
+}
+PGPU_DEV i64 div_i64_checked(i64 a, i64 b, u32& err) {  // BigintOperators.divide :84-96
+    if (b == 0) { err |= PGPU_ERR_DIVZERO; return 0; }
+    if (a == (i64)0x8000000000000000ull && b == -1) { err |= PGPU_ERR_OVERFLOW; return 0; }
+    return a / b;
+}
+PGPU_DEV i64 mod_i64_checked(i64 a, i64 b, u32& err) {  // BigintOperators.modulus :98-108 (Java: MIN % -1 == 0)
+    if (b == 0) { err |= PGPU_ERR_DIVZERO; return 0; }
+    if (b == -1) return 0;
+    return a % b;
+}
+PGPU_DEV i64 neg_i64_checked(i64 a, u32& err) {
+    if (a == (i64)0x8000000000000000ull) err |= PGPU_ERR_OVERFLOW;
+    return (i64)(0 - (u64)a);
+}
+PGPU_DEV i32 narrow_i32_checked(i64 v, u32& err) {  // Math.toIntExact / IntegerOperators addExact family
+    if (v != (i64)(i32)v) err |= PGPU_ERR_OVERFLOW;
+    return (i32)v;
+}
+PGPU_DEV i32 div_i32_checked(i32 a, i32 b, u32& err) {  // IntegerOperators.divide: Java int division, MIN / -1 wraps
+    if (b == 0) { err |= PGPU_ERR_DIVZERO; return 0; }
+    if (b == -1) return (i32)(0u - (u32)a);
+    return a / b;
+}
+PGPU_DEV i32 mod_i32_checked(i32 a, i32 b, u32& err) {
+    if (b == 0) { err |= PGPU_ERR_DIVZERO; return 0; }
+    if (b == -1) return 0;
+    return a % b;
+}
+// DoubleOperators.castToLong (main/type/DoubleOperators.java:155-165): Guava DoubleMath.roundToLong(value, HALF_UP)
+// = round half away from zero; NaN, infinities and values outside [-2^63, 2^63) are INVALID_CAST_ARGUMENT.
+PGPU_DEV i64 cast_f64_i64(double v, u32& err) {
+    if (!(v == v) || fabs(v) == __longlong_as_double(0x7ff0000000000000ll)) { err |= PGPU_ERR_INVALID_CAST; return 0; }
+    double r = trunc(v);
+    if (fabs(v - r) >= 0.5) r += (v < 0.0 ? -1.0 : 1.0);
+    if (!(r >= -9223372036854775808.0 && r < 9223372036854775808.0)) { err |= PGPU_ERR_INVALID_CAST; return 0; }
+    return (i64)r;
+}
+// Double.compare total order as a signed integer (NaNs canonicalised, -0.0 < +0.0)
+PGPU_DEV i64 f64_order_key(double v) {
+    if (v != v) return 0x7ff8000000000000ll;
+    i64 b = __double_as_longlong(v);
+    return b ^ ((b >> 63) & 0x7fffffffffffffffll);
+}
+PGPU_DEV double f64_from_order_key(i64 k) { return __longlong_as_double(k ^ ((k >> 63) & 0x7fffffffffffffffll)); }
+// grouping canonical form of a DOUBLE key (IS DISTINCT FROM semantics, spi/type/DoubleType.java:163-195)
+PGPU_DEV u64 f64_group_bits(double v) {
+    if (v != v) return 0x7ff8000000000000ull;
+    if (v == 0.0) return 0ull;
+    return d2u(v);
+}
+
+// Pack a var-width value of at most N (<=15) bytes into 16 bytes: byte 0 = length, bytes 1.. = data.
+template <int N>
+PGPU_DEV void pack_varchar(const u8* __restrict__ bytes, i32 off, i32 len, u64& lo, u64& hi, u32& err) {
+    lo = 0; hi = 0;
+    if (len > N) { err |= PGPU_ERR_VARCHAR_LEN; len = N; }
+    if (len < 0) len = 0;
+    lo = (u64)(u32)len;
+#pragma unroll
+    for (int k = 0; k < N; k++) {
+        if (k < len) {
+            u64 b = bytes[off + k];
+            if (k < 7) lo |= b << (8 * (k + 1));
+            else hi |= b << (8 * (k - 7));
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ hashing / warp ops
+PGPU_DEV u64 mix64(u64 x) {  // splitmix64 finaliser; table placement only, never observable
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
+    x ^= x >> 27; x *= 0x94d049bb133111ebull;
+    x ^= x >> 31;
+    return x;
+}
+template <int KW>
+PGPU_DEV u64 hash_key(const u64 (&k)[KW > 0 ? KW : 1]) {
+    u64 h = 0x9e3779b97f4a7c15ull;
+#pragma unroll
+    for (int i = 0; i < KW; i++) h = mix64(h ^ k[i]);
+    return h;
+}
+
+// cell-word kinds
+#define CK_ADD_U64 0
+#define CK_ADD_F64 1
+#define CK_MAX_U64 2
+#define CK_CNT 3  // ADD_U64 whose per-lane contribution is a small row count (< 2^26): warp-reduced with one REDUX
+
+template <int KIND>
+PGPU_DEV u64 cell_combine(u64 a, u64 b) {
+    if (KIND == CK_ADD_U64 || KIND == CK_CNT) return a + b;
+    if (KIND == CK_ADD_F64) return d2u(u2d(a) + u2d(b));
+    return a > b ? a : b;
+}
+PGPU_DEV u64 cell_combine_dyn(int kind, u64 a, u64 b) {
+    if (kind == CK_ADD_U64 || kind == CK_CNT) return a + b;
+    if (kind == CK_ADD_F64) return d2u(u2d(a) + u2d(b));
+    return a > b ? a : b;
+}
+PGPU_DEV u64 shfl_xor_u64(u64 v, int m) {
+    u32 lo = __shfl_xor_sync(FULLMASK, (u32)v, m), hi = __shfl_xor_sync(FULLMASK, (u32)(v >> 32), m);
+    return ((u64)hi << 32) | lo;
+}
+PGPU_DEV u64 shfl_u64(u64 v, int src) {
+    u32 lo = __shfl_sync(FULLMASK, (u32)v, src), hi = __shfl_sync(FULLMASK, (u32)(v >> 32), src);
+    return ((u64)hi << 32) | lo;
+}
+template <int KIND>
+PGPU_DEV u64 warp_reduce(u64 v) {
+    if (KIND == CK_CNT) return (u64)__reduce_add_sync(FULLMASK, (u32)v);
+#pragma unroll
+    for (int m = 16; m >= 1; m >>= 1) v = cell_combine<KIND>(v, shfl_xor_u64(v, m));
+    return v;
+}
+template <int KIND>
+PGPU_DEV void cell_atomic(u64* addr, u64 v) {
+    if (KIND == CK_ADD_U64 || KIND == CK_CNT) { if (v) atomicAdd(addr, v); }
+    else if (KIND == CK_ADD_F64) atomicAdd(reinterpret_cast<double*>(addr), u2d(v));
+    else { if (v) atomicMax(addr, v); }
+}
+
+// ------------------------------------------------------------------------------------------------ HBM hash table
+#define TAG_EMPTY 0ull
+#define TAG_LOCKED 1ull
+#define TAG_FULL 2ull
+
+PGPU_DEV u64 ld_volatile_u64(const u64* p) {
+    u64 v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+PGPU_DEV u64 ld_acquire_u64(const u64* p) {
+    u64 v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+PGPU_DEV void st_release_u64(u64* p, u64 v) { asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+
+// Find the slot of `key` or claim an empty one (BigintGroupByHash.putIfAbsent :213-244, linear probing).
+// Returns the slot base pointer, or nullptr when the probe chain is exhausted.
+template <int KW, int SLOTW>
+PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h) {
+    u64 pos = __umul64hi(h, t.capacity);
+    const u64 tagv = TAG_FULL | (h << 8);
+    for (u64 probes = 0; probes < t.capacity; probes++) {
+        u64* s = t.slots + pos * SLOTW;
+        for (;;) {
+            u64 tag = ld_acquire_u64(s);
+            if (tag == TAG_EMPTY) {
+                u64 old = atomicCAS(s, TAG_EMPTY, TAG_LOCKED);
+                if (old == TAG_EMPTY) {
+#pragma unroll
+                    for (int i = 0; i < KW; i++) s[1 + i] = key[i];
+                    st_release_u64(s, tagv);
+                    atomicAdd(t.counters, 1ull);
+                    return s;
+                }
+                continue;  // somebody else got it: re-read
+            }
+            if (tag == TAG_LOCKED) { __nanosleep(20); continue; }
+            if (tag == tagv) {
+                bool eq = true;
+#pragma unroll
+                for (int i = 0; i < KW; i++) eq &= (s[1 + i] == key[i]);
+                if (eq) return s;
+            }
+            break;  // occupied by another key
+        }
+        pos++;
+        if (pos == t.capacity) pos = 0;
+    }
+    atomicAdd(t.counters + 1, 1ull);
+    return nullptr;
+}
+
+template <class P>
+PGPU_DEV void table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::KW : 1], const u64 (&cw)[P::NW > 0 ? P::NW : 1], u32& err) {
+    u64* s = table_upsert<P::KW, P::SLOTW>(t, key, hash_key<P::KW>(key));
+    if (!s) { err |= PGPU_ERR_TABLE_FULL; return; }
+    P::atomic_cells(s + 1 + P::KW, cw);
+}
+
+// ------------------------------------------------------------------------------------------------ global aggregation
+// One accumulator slot (no GROUP BY). Every thread reduces its rows in registers, blocks reduce through warp
+// shuffles + shared memory into partials[block][NW]; the last block to finish (ticket) folds the block partials
+// in block order into the persistent state, so results are deterministic run to run.
+template <class P>
+PGPU_DEV void body_agg_global(const PageArgs<P::NC>& a, const Scratch& sc) {
+    constexpr int NW = P::NW;
+    constexpr int NWA = NW > 0 ? NW : 1;
+    u64 acc[NWA];
+    P::identity(acc);
+    u32 err = 0;
+    const i64 tile_rows = (i64)blockDim.x * 4;
+    const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
+    for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
+        bool sel[4];
+        u64 key[4][1];
+        u64 cw[4][NWA];
+        P::eval(a, base, a.rows, sel, key, cw, err);
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+            if (sel[r]) P::combine(acc, cw[r]);
+    }
+    // block reduction
+    __shared__ u64 sm[32][NWA];
+    P::warp_reduce_cells(acc);
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int w = 0; w < NW; w++) sm[warp][w] = acc[w];
+    }
+    if (err) atomicOr(sc.err, err);
+    __syncthreads();
+    __shared__ bool is_last;
+    if (threadIdx.x == 0) {
+        u64 tot[NWA];
+        P::identity(tot);
+        for (int k = 0; k < nwarps; k++) P::combine(tot, sm[k]);
+#pragma unroll
+        for (int w = 0; w < NW; w++) sc.partials[(u64)blockIdx.x * NWA + w] = tot[w];
+        __threadfence();
+        u32 t = atomicAdd(sc.ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last && threadIdx.x == 0) {
+        __threadfence();
+        u64 tot[NWA];
+#pragma unroll
+        for (int w = 0; w < NW; w++) tot[w] = sc.state[w];
+        for (u32 b = 0; b < gridDim.x; b++) {
+            u64 part[NWA];
+#pragma unroll
+            for (int w = 0; w < NW; w++) part[w] = ld_volatile_u64(sc.partials + (u64)b * NWA + w);
+            P::combine(tot, part);
+        }
+#pragma unroll
+        for (int w = 0; w < NW; w++) sc.state[w] = tot[w];
+        *sc.ticket = 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ hash aggregation
+// Level 1 (P::USE_DIR): a block-shared key directory in shared memory maps keys to small slot numbers; each warp
+// owns a private accumulator table indexed by that slot, updated without atomics after a warp-level reduction over
+// lanes holding the same slot. Level 2: the HBM table, for directory misses and for the end-of-kernel flush.
+template <class P>
+PGPU_DEV int dir_lookup(u64* dkeys, u32* dtags, u32* dcount, const u64 (&key)[P::KW], u64 h) {
+    constexpr int KW = P::KW, DCAP = P::DCAP;
+    u32 pos = (u32)(h >> 40) % DCAP;
+    const u32 tagv = 2u | ((u32)h << 8);
+    for (int probes = 0; probes < DCAP; probes++) {
+        for (;;) {
+            u32 tag = *((volatile u32*)&dtags[pos]);
+            if (tag == 0u) {
+                if (*((volatile u32*)dcount) >= (u32)P::DLIMIT) return -1;  // directory full: go to HBM
+                u32 old = atomicCAS(&dtags[pos], 0u, 1u);
+                if (old == 0u) {
+#pragma unroll
+                    for (int i = 0; i < KW; i++) dkeys[pos * KW + i] = key[i];
+                    __threadfence_block();
+                    *((volatile u32*)&dtags[pos]) = tagv;
+                    atomicAdd(dcount, 1u);
+                    return (int)pos;
+                }
+                continue;
+            }
+            if (tag == 1u) continue;
+            if (tag == tagv) {
+                bool eq = true;
+#pragma unroll
+                for (int i = 0; i < KW; i++) eq &= (((volatile u64*)dkeys)[pos * KW + i] == key[i]);
+                if (eq) return (int)pos;
+            }
+            break;
+        }
+        pos = pos + 1 == (u32)DCAP ? 0u : pos + 1;
+    }
+    return -1;
+}
+
+template <class P>
+PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc) {
+    constexpr int KW = P::KW, NW = P::NW, DCAP = P::DCAP, NWARP = P::NWARP;
+    constexpr int NWA = NW > 0 ? NW : 1;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    // layout: wacc[NWARP][DCAP][NWA] u64 | dkeys[DCAP][KW] u64 | dtags[DCAP] u32 | dcount u32
+    u64* wacc = reinterpret_cast<u64*>(smem_raw);
+    u64* dkeys = wacc + (P::USE_DIR ? NWARP * DCAP * NWA : 0);
+    u32* dtags = reinterpret_cast<u32*>(dkeys + (P::USE_DIR ? DCAP * KW : 0));
+    u32* dcount = dtags + (P::USE_DIR ? DCAP : 0);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (P::USE_DIR) {
+        for (int i = threadIdx.x; i < NWARP * DCAP; i += blockDim.x) P::identity_ptr(wacc + (size_t)i * NWA);
+        for (int i = threadIdx.x; i < DCAP; i += blockDim.x) dtags[i] = 0u;
+        if (threadIdx.x == 0) *dcount = 0u;
+        __syncthreads();
+    }
+    u32 err = 0;
+    const i64 tile_rows = (i64)blockDim.x * 4;
+    const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
+    u64* myacc = wacc + (size_t)warp * DCAP * NWA;
+    for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
+        bool sel[4];
+        u64 key[4][KW];
+        u64 cw[4][NWA];
+        P::eval(a, base, a.rows, sel, key, cw, err);
+        // fold the thread's consecutive rows with equal keys (l_orderkey-style runs) into the first of the run
+#pragma unroll
+        for (int r = 3; r >= 1; r--) {
+            bool same = sel[r] && sel[r - 1];
+#pragma unroll
+            for (int i = 0; i < KW; i++) same &= (key[r][i] == key[r - 1][i]);
+            if (same) {
+                P::combine(cw[r - 1], cw[r]);
+                sel[r] = false;
+            }
+        }
+        if (P::USE_DIR) {
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                if (!__any_sync(FULLMASK, sel[r])) continue;
+                int slot = -1;
+                if (sel[r]) slot = dir_lookup<P>(dkeys, dtags, dcount, key[r], hash_key<KW>(key[r]));
+                u32 peers = __match_any_sync(FULLMASK, slot);
+                u32 leaders = __ballot_sync(FULLMASK, slot >= 0 && lane == __ffs(peers) - 1);
+                if (__popc(leaders) <= P::MAX_WARP_GROUPS) {
+                    while (leaders) {
+                        int leader = __ffs(leaders) - 1;
+                        leaders &= leaders - 1;
+                        int ls = __shfl_sync(FULLMASK, slot, leader);
+                        u64 v[NWA];
+                        if (slot == ls) {
+#pragma unroll
+                            for (int w = 0; w < NW; w++) v[w] = cw[r][w];
+                        } else {
+                            P::identity(v);
+                        }
+                        P::warp_reduce_cells(v);
+                        if (lane == leader) P::combine_ptr(myacc + (size_t)ls * NWA, v);
+                    }
+                    if (sel[r] && slot < 0) table_update<P>(t, key[r], cw[r], err);
+                } else {
+                    // many distinct groups in this warp: fire-and-forget atomics on the HBM table
+                    if (sel[r]) table_update<P>(t, key[r], cw[r], err);
+                }
+                __syncwarp();
+            }
+        } else {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                if (sel[r]) table_update<P>(t, key[r], cw[r], err);
+        }
+    }
+    if (P::USE_DIR) {
+        __syncthreads();
+        // flush: fold the warp-private tables in warp order and push each live directory entry to HBM
+        for (int s = threadIdx.x; s < DCAP; s += blockDim.x) {
+            if (dtags[s] < 2u) continue;
+            u64 tot[NWA];
+            P::identity(tot);
+            for (int k = 0; k < NWARP; k++) P::combine_ptr_to(tot, wacc + ((size_t)k * DCAP + s) * NWA);
+            u64 key[KW];
+#pragma unroll
+            for (int i = 0; i < KW; i++) key[i] = dkeys[s * KW + i];
+            table_update<P>(t, key, tot, err);
+        }
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
+// ------------------------------------------------------------------------------------------------ ordered compaction
+// Single-pass stream compaction with decoupled look-back: tiles are handed out in order by a ticket so every
+// predecessor of a tile is resident or finished. tile_status[i] = (flag << 62) | value; flag 1 = tile aggregate,
+// 2 = inclusive prefix. Output rows keep input order (SelectedPositions are ascending: PageFilter.java:36-48).
+template <class P>
+PGPU_DEV void body_compact(const PageArgs<P::NC>& a, const OutArgs<P::NO>& out, const Scratch& sc) {
+    __shared__ i64 s_tile;
+    __shared__ u32 s_warp[32];
+    __shared__ u64 s_prefix;
+    u32 err = 0;
+    const i64 tile_rows = (i64)blockDim.x * 4;
+    const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_tile = (i64)atomicAdd(sc.ticket, 1u);
+        __syncthreads();
+        const i64 tile = s_tile;
+        if (tile >= ntiles) break;
+        i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
+        bool sel[4];
+        typename P::Proj pv[4];
+        P::eval_project(a, base, a.rows, sel, pv, err);
+        u32 cnt = (u32)sel[0] + (u32)sel[1] + (u32)sel[2] + (u32)sel[3];
+        // block exclusive scan of cnt
+        u32 incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            u32 n = __shfl_up_sync(FULLMASK, incl, d);
+            if (lane >= d) incl += n;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            u32 w = lane < nwarps ? s_warp[lane] : 0u;
+            u32 wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                u32 n = __shfl_up_sync(FULLMASK, wi, d);
+                if (lane >= d) wi += n;
+            }
+            s_warp[lane] = wi - w;  // exclusive warp offsets
+            u32 total = __shfl_sync(FULLMASK, wi, 31);
+            // publish + look back
+            u64 excl = 0;
+            if (tile == 0) {
+                if (lane == 0) st_release_u64(sc.tile_status, (2ull << 62) | (u64)total);
+            } else {
+                if (lane == 0) st_release_u64(sc.tile_status + tile, (1ull << 62) | (u64)total);
+                i64 look = tile - 1;
+                for (;;) {
+                    i64 idx = look - lane;
+                    u64 st = 0;
+                    if (idx >= 0) {
+                        do { st = ld_acquire_u64(sc.tile_status + idx); } while ((st >> 62) == 0);
+                    } else {
+                        st = 2ull << 62;  // before the first tile: inclusive prefix 0
+                    }
+                    u32 has_incl = __ballot_sync(FULLMASK, (st >> 62) == 2);
+                    u64 val = st & 0x3fffffffffffffffull;
+                    int first_incl = has_incl ? __ffs(has_incl) - 1 : 32;
+                    if (lane > first_incl) val = 0;
+#pragma unroll
+                    for (int m = 16; m >= 1; m >>= 1) val += shfl_xor_u64(val, m);
+                    excl += val;
+                    if (has_incl) break;
+                    look -= 32;
+                }
+                if (lane == 0) st_release_u64(sc.tile_status + tile, (2ull << 62) | (excl + total));
+            }
+            if (lane == 0) s_prefix = excl;
+            if (tile == ntiles - 1 && lane == 0) *sc.out_count = excl + total;
+        }
+        __syncthreads();
+        u64 pos = s_prefix + s_warp[warp] + (incl - cnt);
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            if (sel[r]) {
+                if ((i64)pos < out.capacity) P::store_row(out, (i64)pos, pv[r]);
+                else err |= PGPU_ERR_OUTPUT_FULL;
+                pos++;
+            }
+        }
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
+// ------------------------------------------------------------------------------------------------ table output / rehash
+template <class P>
+PGPU_DEV void body_materialize(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, i64 first_slot, i64 nslots) {
+    u32 err = 0;
+    const int lane = threadIdx.x & 31;
+    i64 end = first_slot + nslots;
+    if (end > (i64)t.capacity) end = (i64)t.capacity;
+    for (i64 s0 = first_slot + ((i64)blockIdx.x * blockDim.x + threadIdx.x) - lane; s0 < end; s0 += (i64)gridDim.x * blockDim.x) {
+        i64 s = s0 + lane;
+        const u64* slot = t.slots + (u64)s * P::SLOTW;
+        bool live = s < end && (slot[0] & 0xffull) == TAG_FULL;
+        u32 m = __ballot_sync(FULLMASK, live);
+        if (!m) continue;
+        u64 basepos = 0;
+        if (lane == 0) basepos = atomicAdd(sc.out_count, (u64)__popc(m));
+        basepos = shfl_u64(basepos, 0);
+        if (live) {
+            i64 pos = (i64)(basepos + __popc(m & ((1u << lane) - 1u)));
+            if (pos < out.capacity) P::emit(slot + 1, slot + 1 + P::KW, out, pos, err);
+            else err |= PGPU_ERR_OUTPUT_FULL;
+        }
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
+template <class P>
+PGPU_DEV void body_rehash(const TableArgs& from, const TableArgs& to, const Scratch& sc) {
+    u32 err = 0;
+    for (u64 s = (u64)blockIdx.x * blockDim.x + threadIdx.x; s < from.capacity; s += (u64)gridDim.x * blockDim.x) {
+        const u64* slot = from.slots + s * P::SLOTW;
+        if ((slot[0] & 0xffull) != TAG_FULL) continue;
+        u64 key[P::KW > 0 ? P::KW : 1];
+#pragma unroll
+        for (int i = 0; i < P::KW; i++) key[i] = slot[1 + i];
+        u64* d = table_upsert<P::KW, P::SLOTW>(to, key, hash_key<P::KW>(key));
+        if (!d) { err |= PGPU_ERR_TABLE_FULL; continue; }
+#pragma unroll
+        for (int w = 0; w < P::NW; w++) d[1 + P::KW + w] = slot[1 + P::KW + w];  // keys are distinct: plain stores
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
+// Single-slot output of a global aggregation (AggregationOperator.getOutput, operator/AggregationOperator.java:164-186).
+template <class P>
+PGPU_DEV void body_emit_global(const Scratch& sc, const OutArgs<P::NO>& out) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        u32 err = 0;
+        u64 nokey[1] = {0};
+        P::emit(nokey, sc.state, out, 0, err);
+        *sc.out_count = 1;
+        if (err) atomicOr(sc.err, err);
+    }
+}

@@ -1,0 +1,1116 @@
+// pipeline.cpp — the C ABI of include/prestogpu.h: one native operator instance per pgpu_pipeline.
+//
+// Host-side state machine follows the reference operators it stands in for:
+//   needsInput/addInput/getOutput/finish/isFinished  main/operator/HashAggregationOperator.java:367-518,
+//                                                    main/operator/AggregationOperator.java:120-186,
+//                                                    main/operator/WorkProcessorOperatorAdapter.java:170-209 (filter/project)
+//   table growth                                     main/operator/BigintGroupByHash.java:262-313 (tryRehash)
+// Device work is queued on one CUDA stream per pipeline; nothing here is thread-local, so the Driver may call
+// from a different thread each quantum (main/operator/Driver.java:284-305).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/prestogpu.h"
+#include "codegen.h"
+#include "jit.h"
+#include "plan.h"
+
+using namespace pgpu;
+
+namespace {
+
+// device-side structs (must match device/pgpu_device.cuh)
+struct ColArg {
+    const void* values;
+    const uint8_t* nulls;
+    const int32_t* offsets;
+    const int32_t* ids;
+    const void* dvalues;
+    const uint8_t* dnulls;
+    const int32_t* doffsets;
+};
+struct TableArgs {
+    uint64_t* slots;
+    uint64_t capacity;
+    uint64_t* counters;
+};
+struct Scratch {
+    uint32_t* err;
+    uint64_t* partials;
+    uint32_t* ticket;
+    uint64_t* state;
+    uint64_t* tile_status;
+    uint64_t* out_count;
+};
+struct OutCol {
+    void* values;
+    uint8_t* nulls;
+};
+
+constexpr int kThreads = 256;
+constexpr int64_t kTileRows = kThreads * 4;
+constexpr int64_t kHashChunkRows = 32ll << 20;  // rows per launch while the HBM table may still have to grow
+constexpr int64_t kHostChunkRows = 8ll << 20;   // rows per staged H2D chunk
+
+thread_local std::string g_lastGlobalError;
+
+struct Variant {
+    GenResult gen;
+    cudaLibrary_t lib = nullptr;
+    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr;
+    int blocksPerSM = 1;
+};
+
+struct DeviceBuf {
+    void* ptr = nullptr;
+    size_t cap = 0;
+};
+
+struct StageSlot {
+    DeviceBuf dev;
+    void* host = nullptr;  // pinned
+    size_t hostCap = 0;
+    cudaEvent_t done = nullptr;  // kernel that consumed the slot finished
+    bool inFlight = false;
+};
+
+struct HostOut {
+    void* ptr = nullptr;
+    size_t cap = 0;
+};
+
+}  // namespace
+
+struct pgpu_pipeline {
+    std::unique_ptr<Plan> plan;
+    int device = -1;
+    int numSMs = 148;
+    cudaStream_t stream = nullptr;
+    std::map<std::string, Variant> variants;
+    GenResult layout;  // layout fields (KW/NW/SLOTW/out/mode) are signature independent
+    bool haveLayout = false;
+    std::string lastSource;
+    std::string err;
+    pgpu_stats stats{};
+    bool timing = false;
+    cudaEvent_t evA = nullptr, evB = nullptr;
+
+    // operator state
+    bool finishing = false, finished = false;
+    bool sawInput = false;
+    bool outputReady = false;      // COMPACT: a page result is pending; aggregation: result materialised
+    int64_t outRowsTotal = 0, outRowsServed = 0;
+
+    // device scratch
+    uint32_t* dErr = nullptr;
+    uint32_t* dTicket = nullptr;
+    uint64_t* dOutCount = nullptr;
+    uint64_t* dCounters = nullptr;
+    uint64_t* dState = nullptr;
+    uint64_t* dPartials = nullptr;
+    size_t partialsCap = 0;
+    DeviceBuf tileStatus;
+    uint64_t* hostScalars = nullptr;  // pinned: [0] out_count, [1..2] counters, [3] err
+
+    // table
+    uint64_t* dSlots = nullptr;
+    uint64_t capacity = 0;
+    int64_t groupsKnown = 0, rowsSinceKnown = 0;
+
+    // staging + output
+    StageSlot slots[3];
+    int nextSlot = 0;
+    std::vector<DeviceBuf> outDev;       // per output column: values
+    std::vector<DeviceBuf> outDevNulls;
+    std::vector<HostOut> outHost, outHostNulls, outHostAux;  // aux: offsets for var-width
+    int64_t outCapacityRows = 0;
+};
+
+namespace {
+
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess) {                                                                          \
+            p->err = std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #call;                 \
+            return PGPU_CUDA_ERROR;                                                                       \
+        }                                                                                                 \
+    } while (0)
+
+pgpu_status fail(pgpu_pipeline* p, pgpu_status st, const std::string& m) {
+    p->err = m;
+    return st;
+}
+
+pgpu_status ensureDev(pgpu_pipeline* p, DeviceBuf& b, size_t bytes) {
+    if (b.cap >= bytes && b.ptr) return PGPU_OK;
+    if (b.ptr) {
+        CU(cudaStreamSynchronize(p->stream));
+        CU(cudaFree(b.ptr));
+        b.ptr = nullptr;
+        b.cap = 0;
+    }
+    size_t want = std::max<size_t>(bytes, 256);
+    want = (want + 255) / 256 * 256;
+    CU(cudaMalloc(&b.ptr, want));
+    b.cap = want;
+    return PGPU_OK;
+}
+
+pgpu_status ensureHost(pgpu_pipeline* p, HostOut& b, size_t bytes) {
+    if (b.cap >= bytes && b.ptr) return PGPU_OK;
+    if (b.ptr) {
+        CU(cudaFreeHost(b.ptr));
+        b.ptr = nullptr;
+        b.cap = 0;
+    }
+    size_t want = std::max<size_t>(bytes, 64);
+    CU(cudaMallocHost(&b.ptr, want));
+    b.cap = want;
+    return PGPU_OK;
+}
+
+std::string sigKey(const std::vector<ColSig>& s) {
+    std::string k;
+    for (auto& c : s) {
+        k.push_back((char)('0' + c.encoding));
+        k.push_back(c.nullable ? 'n' : '-');
+    }
+    return k;
+}
+
+pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant** out) {
+    std::string key = sigKey(sig);
+    auto it = p->variants.find(key);
+    if (it != p->variants.end()) {
+        *out = &it->second;
+        return PGPU_OK;
+    }
+    Variant v;
+    try {
+        v.gen = generate(*p->plan, sig);
+        JitResult jr = jitCompile(v.gen.source);
+        if (jr.cacheHit) p->stats.jit_cache_hits++;
+        else p->stats.jit_compiles++;
+        p->lastSource = v.gen.source;
+        if (!p->haveLayout) {
+            p->layout = v.gen;
+            p->layout.source.clear();
+            p->haveLayout = true;
+        } else if (p->layout.KW != v.gen.KW || p->layout.NW != v.gen.NW || p->layout.SLOTW != v.gen.SLOTW || p->layout.cellKinds != v.gen.cellKinds) {
+            return fail(p, PGPU_COMPILER_ERROR, "internal: accumulator layout depends on the page signature");
+        }
+        if (p->device >= 0) {
+            CU(cudaSetDevice(p->device));
+            CU(cudaLibraryLoadData(&v.lib, jr.cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0));
+            CU(cudaLibraryGetKernel(&v.kPage, v.lib, "pgpu_k_page"));
+            if (v.gen.mode != KernelMode::COMPACT) CU(cudaLibraryGetKernel(&v.kEmit, v.lib, "pgpu_k_emit"));
+            if (v.gen.mode == KernelMode::AGG_HASH) CU(cudaLibraryGetKernel(&v.kRehash, v.lib, "pgpu_k_rehash"));
+            int nb = 0;
+            cudaError_t oe = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v.kPage, kThreads, (size_t)v.gen.smemBytes);
+            if (oe != cudaSuccess || nb < 1) {
+                cudaGetLastError();
+                nb = 2;
+            }
+            v.blocksPerSM = nb;
+        }
+    } catch (const PlanError& e) {
+        return fail(p, (pgpu_status)e.status, e.what());
+    }
+    auto ins = p->variants.emplace(key, std::move(v));
+    *out = &ins.first->second;
+    return PGPU_OK;
+}
+
+Scratch scratchOf(pgpu_pipeline* p) {
+    Scratch s;
+    s.err = p->dErr;
+    s.partials = p->dPartials;
+    s.ticket = p->dTicket;
+    s.state = p->dState;
+    s.tile_status = (uint64_t*)p->tileStatus.ptr;
+    s.out_count = p->dOutCount;
+    return s;
+}
+
+TableArgs tableOf(pgpu_pipeline* p) {
+    TableArgs t;
+    t.slots = p->dSlots;
+    t.capacity = p->capacity;
+    t.counters = p->dCounters;
+    return t;
+}
+
+pgpu_status launch(pgpu_pipeline* p, cudaKernel_t k, int grid, int block, size_t smem, void** args) {
+    if (grid < 1) grid = 1;
+    if (p->timing) CU(cudaEventRecord(p->evA, p->stream));
+    CU(cudaLaunchKernel((const void*)k, dim3((unsigned)grid), dim3((unsigned)block), args, smem, p->stream));
+    if (p->timing) {
+        CU(cudaEventRecord(p->evB, p->stream));
+        CU(cudaEventSynchronize(p->evB));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, p->evA, p->evB));
+        p->stats.device_ms += ms;
+    }
+    p->stats.kernel_launches++;
+    return PGPU_OK;
+}
+
+pgpu_status checkDeviceErrors(pgpu_pipeline* p) {
+    // caller has synchronised the stream
+    uint32_t e = 0;
+    CU(cudaMemcpyAsync(&p->hostScalars[3], p->dErr, 4, cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    e = (uint32_t)p->hostScalars[3];
+    if (!e) return PGPU_OK;
+    if (e & 2u) return fail(p, PGPU_DIVISION_BY_ZERO, "Division by zero");
+    if (e & 1u) return fail(p, PGPU_NUMERIC_VALUE_OUT_OF_RANGE, "numeric value out of range (integer or decimal overflow)");
+    if (e & 32u) return fail(p, PGPU_INVALID_CAST_ARGUMENT, "Unable to cast double to bigint");
+    if (e & 8u) return fail(p, PGPU_INVALID_ARGUMENT, "varchar(n) value longer than n bytes");
+    if (e & 4u) return fail(p, PGPU_INSUFFICIENT_RESOURCES, "internal: hash table full");
+    return fail(p, PGPU_CUDA_ERROR, "internal: output buffer overflow");
+}
+
+// ------------------------------------------------------------------------------------------- table management
+pgpu_status allocTable(pgpu_pipeline* p, uint64_t cap, uint64_t** slotsOut) {
+    size_t bytes = (size_t)cap * p->layout.SLOTW * 8;
+    void* ptr = nullptr;
+    cudaError_t e = cudaMalloc(&ptr, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(p, PGPU_INSUFFICIENT_RESOURCES, "cannot allocate a hash table of " + std::to_string(cap) + " slots (" + std::to_string(bytes >> 20) + " MiB)");
+    }
+    CU(cudaMemsetAsync(ptr, 0, bytes, p->stream));
+    *slotsOut = (uint64_t*)ptr;
+    return PGPU_OK;
+}
+
+pgpu_status refreshGroupCount(pgpu_pipeline* p) {
+    CU(cudaMemcpyAsync(&p->hostScalars[1], p->dCounters, 16, cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    p->groupsKnown = (int64_t)p->hostScalars[1];
+    p->rowsSinceKnown = 0;
+    return PGPU_OK;
+}
+
+pgpu_status growTable(pgpu_pipeline* p, Variant* v, uint64_t newCap) {
+    uint64_t* fresh = nullptr;
+    pgpu_status st = allocTable(p, newCap, &fresh);
+    if (st) return st;
+    if (p->dSlots && p->groupsKnown > 0) {
+        TableArgs from = tableOf(p);
+        TableArgs to{fresh, newCap, p->dCounters};
+        // rehash re-counts groups: zero the counter first
+        CU(cudaMemsetAsync(p->dCounters, 0, 16, p->stream));
+        Scratch sc = scratchOf(p);
+        void* args[] = {&from, &to, &sc};
+        int grid = (int)std::min<uint64_t>((from.capacity + kThreads - 1) / kThreads, (uint64_t)p->numSMs * 8);
+        st = launch(p, v->kRehash, grid, kThreads, 0, args);
+        if (st) return st;
+        p->stats.table_rehashes++;
+    }
+    if (p->dSlots) {
+        CU(cudaStreamSynchronize(p->stream));
+        CU(cudaFree(p->dSlots));
+    }
+    p->dSlots = fresh;
+    p->capacity = newCap;
+    p->stats.table_capacity = (int64_t)newCap;
+    return PGPU_OK;
+}
+
+// make sure `rows` more rows cannot overfill the table (load factor <= 0.75 even if every row is a new group)
+pgpu_status reserveGroups(pgpu_pipeline* p, Variant* v, int64_t rows) {
+    auto fits = [&](int64_t groups) { return (double)(groups + rows) <= 0.75 * (double)p->capacity; };
+    if (p->dSlots && fits(p->groupsKnown + p->rowsSinceKnown)) return PGPU_OK;
+    if (p->dSlots) {
+        pgpu_status st = refreshGroupCount(p);
+        if (st) return st;
+        if (fits(p->groupsKnown)) return PGPU_OK;
+    }
+    uint64_t need = (uint64_t)((double)(p->groupsKnown + rows) / 0.6) + 1024;
+    uint64_t hint = (uint64_t)((double)p->plan->expectedGroups / 0.6) + 1024;
+    uint64_t cap = std::max<uint64_t>({need, hint, p->capacity * 2});
+    return growTable(p, v, cap);
+}
+
+// ------------------------------------------------------------------------------------------- page processing
+struct DevPage {
+    std::vector<ColArg> cols;
+    int64_t rows = 0;
+};
+
+pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
+    const GenResult& g = v->gen;
+    // kernel parameter block: PageArgs<NC> = ColArg[NC] + rows
+    std::vector<unsigned char> pa(sizeof(ColArg) * g.NC + 8);
+    memcpy(pa.data(), pg.cols.data(), sizeof(ColArg) * g.NC);
+    memcpy(pa.data() + sizeof(ColArg) * g.NC, &pg.rows, 8);
+    int64_t ntiles = (pg.rows + kTileRows - 1) / kTileRows;
+    int grid = (int)std::min<int64_t>(ntiles, (int64_t)p->numSMs * v->blocksPerSM);
+    Scratch sc = scratchOf(p);
+    if (g.mode == KernelMode::AGG_GLOBAL) {
+        size_t need = (size_t)grid * std::max(g.NW, 1) * 8;
+        if (p->partialsCap < need) {
+            if (p->dPartials) {
+                CU(cudaStreamSynchronize(p->stream));
+                CU(cudaFree(p->dPartials));
+            }
+            size_t cap = (size_t)p->numSMs * 32 * std::max(g.NW, 1) * 8;
+            cap = std::max(cap, need);
+            CU(cudaMalloc((void**)&p->dPartials, cap));
+            p->partialsCap = cap;
+            sc = scratchOf(p);
+        }
+        void* args[] = {pa.data(), &sc};
+        return launch(p, v->kPage, grid, kThreads, 0, args);
+    }
+    if (g.mode == KernelMode::AGG_HASH) {
+        TableArgs t = tableOf(p);
+        void* args[] = {pa.data(), &t, &sc};
+        return launch(p, v->kPage, grid, kThreads, (size_t)g.smemBytes, args);
+    }
+    return fail(p, PGPU_INVALID_STATE, "internal: launchPageKernel in COMPACT mode");
+}
+
+pgpu_status ensureOutBuffers(pgpu_pipeline* p, int64_t rows) {
+    const GenResult& g = p->layout;
+    if ((int)p->outDev.size() != g.NO) {
+        p->outDev.resize(g.NO);
+        p->outDevNulls.resize(g.NO);
+        p->outHost.resize(g.NO);
+        p->outHostNulls.resize(g.NO);
+        p->outHostAux.resize(g.NO);
+    }
+    int64_t r = std::max<int64_t>(rows, 1);
+    for (int c = 0; c < g.NO; c++) {
+        pgpu_status st = ensureDev(p, p->outDev[c], (size_t)r * std::max(g.out[c].stride, 1));
+        if (st) return st;
+        st = ensureDev(p, p->outDevNulls[c], (size_t)r);
+        if (st) return st;
+    }
+    p->outCapacityRows = r;
+    return PGPU_OK;
+}
+
+std::vector<unsigned char> outArgsBlock(pgpu_pipeline* p) {
+    const GenResult& g = p->layout;
+    std::vector<unsigned char> oa(sizeof(OutCol) * g.NO + 8);
+    for (int c = 0; c < g.NO; c++) {
+        OutCol oc{p->outDev[c].ptr, (uint8_t*)p->outDevNulls[c].ptr};
+        memcpy(oa.data() + sizeof(OutCol) * c, &oc, sizeof oc);
+    }
+    memcpy(oa.data() + sizeof(OutCol) * g.NO, &p->outCapacityRows, 8);
+    return oa;
+}
+
+pgpu_status runCompact(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
+    const GenResult& g = v->gen;
+    pgpu_status st = ensureOutBuffers(p, pg.rows);
+    if (st) return st;
+    int64_t ntiles = (pg.rows + kTileRows - 1) / kTileRows;
+    st = ensureDev(p, p->tileStatus, (size_t)ntiles * 8);
+    if (st) return st;
+    CU(cudaMemsetAsync(p->tileStatus.ptr, 0, (size_t)ntiles * 8, p->stream));
+    CU(cudaMemsetAsync(p->dTicket, 0, 4, p->stream));
+    CU(cudaMemsetAsync(p->dOutCount, 0, 8, p->stream));
+    std::vector<unsigned char> pa(sizeof(ColArg) * g.NC + 8);
+    memcpy(pa.data(), pg.cols.data(), sizeof(ColArg) * g.NC);
+    memcpy(pa.data() + sizeof(ColArg) * g.NC, &pg.rows, 8);
+    std::vector<unsigned char> oa = outArgsBlock(p);
+    Scratch sc = scratchOf(p);
+    int grid = (int)std::min<int64_t>(ntiles, (int64_t)p->numSMs * v->blocksPerSM);
+    void* args[] = {pa.data(), oa.data(), &sc};
+    st = launch(p, v->kPage, grid, kThreads, 0, args);
+    if (st) return st;
+    CU(cudaMemcpyAsync(&p->hostScalars[0], p->dOutCount, 8, cudaMemcpyDeviceToHost, p->stream));
+    p->outputReady = true;
+    p->outRowsTotal = -1;  // read after sync
+    p->outRowsServed = 0;
+    return PGPU_OK;
+}
+
+// slices a device-resident page into row ranges and runs the aggregation kernels over them
+pgpu_status processDevicePage(pgpu_pipeline* p, Variant* v, const pgpu_column* cols, int64_t rows) {
+    const GenResult& g = v->gen;
+    const Plan& plan = *p->plan;
+    auto colArgsFor = [&](int64_t r0, std::vector<ColArg>& out) {
+        out.assign(g.NC, ColArg{});
+        for (int c : g.usedChannels) {
+            const pgpu_column& col = cols[c];
+            const Type& t = plan.input[c];
+            ColArg a{};
+            if (col.encoding == PGPU_ENC_PLAIN) {
+                if (t.isVarWidth()) {
+                    a.values = col.values;
+                    a.offsets = col.offsets + r0;
+                } else {
+                    a.values = (const char*)col.values + (size_t)r0 * t.width();
+                }
+                a.nulls = col.nulls ? col.nulls + r0 : nullptr;
+            } else {
+                const pgpu_column* d = col.dictionary;
+                if (col.encoding == PGPU_ENC_DICTIONARY) a.ids = col.ids + r0;
+                a.dvalues = d->values;
+                a.dnulls = d->nulls;
+                a.doffsets = d->offsets;
+            }
+            out[c] = a;
+        }
+    };
+    if (g.mode == KernelMode::COMPACT) {
+        DevPage pg;
+        pg.rows = rows;
+        colArgsFor(0, pg.cols);
+        return runCompact(p, v, pg);
+    }
+    int64_t chunk = g.mode == KernelMode::AGG_HASH ? kHashChunkRows : rows;
+    for (int64_t r0 = 0; r0 < rows; r0 += chunk) {
+        int64_t n = std::min(chunk, rows - r0);
+        if (g.mode == KernelMode::AGG_HASH) {
+            pgpu_status st = reserveGroups(p, v, n);
+            if (st) return st;
+            p->rowsSinceKnown += n;
+        }
+        DevPage pg;
+        pg.rows = n;
+        colArgsFor(r0, pg.cols);
+        pgpu_status st = launchPageKernel(p, v, pg);
+        if (st) return st;
+    }
+    return PGPU_OK;
+}
+
+pgpu_status validatePage(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows, std::vector<ColSig>& sig) {
+    const Plan& plan = *p->plan;
+    if (!cols || ncols != (int)plan.input.size()) return fail(p, PGPU_INVALID_ARGUMENT, "page has " + std::to_string(ncols) + " channels, plan expects " + std::to_string(plan.input.size()));
+    if (rows < 0) return fail(p, PGPU_INVALID_ARGUMENT, "negative position count");
+    sig.resize(ncols);
+    for (int c = 0; c < ncols; c++) {
+        const pgpu_column& col = cols[c];
+        const Type& t = plan.input[c];
+        if (col.type_kind != (int)t.kind || (t.kind == TypeKind::DECIMAL && (col.precision != t.precision || col.scale != t.scale)))
+            return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " type does not match the plan (" + t.str() + ")");
+        if (col.position_count != rows) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " position count differs from the page");
+        sig[c].encoding = col.encoding;
+        if (col.encoding == PGPU_ENC_PLAIN) {
+            sig[c].nullable = col.nulls != nullptr;
+            if (rows > 0 && !col.values && !(t.isVarWidth())) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " has no values");
+            if (t.isVarWidth() && !col.offsets) return fail(p, PGPU_INVALID_ARGUMENT, "var-width channel " + std::to_string(c) + " has no offsets");
+        } else if (col.encoding == PGPU_ENC_DICTIONARY || col.encoding == PGPU_ENC_RLE) {
+            const pgpu_column* d = col.dictionary;
+            if (!d || d->encoding != PGPU_ENC_PLAIN) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: nested dictionary/RLE encodings (channel " + std::to_string(c) + ")");
+            if (col.encoding == PGPU_ENC_DICTIONARY && !col.ids && rows > 0) return fail(p, PGPU_INVALID_ARGUMENT, "dictionary channel without ids");
+            if (col.encoding == PGPU_ENC_RLE && d->position_count != 1) return fail(p, PGPU_INVALID_ARGUMENT, "RLE value block must have exactly one position");
+            sig[c].nullable = d->nulls != nullptr;
+        } else {
+            return fail(p, PGPU_INVALID_ARGUMENT, "unknown block encoding");
+        }
+    }
+    return PGPU_OK;
+}
+
+size_t align256(size_t x) { return (x + 255) / 256 * 256; }
+
+// Stage rows [r0, r0+n) of a host page into a ring slot and return device-side column descriptors.
+pgpu_status stageChunk(pgpu_pipeline* p, Variant* v, const pgpu_column* cols, int64_t r0, int64_t n, bool pinned, StageSlot& slot, std::vector<ColArg>& out) {
+    const GenResult& g = v->gen;
+    const Plan& plan = *p->plan;
+    struct Piece {
+        const void* src;
+        size_t bytes;
+        size_t off;
+    };
+    std::vector<Piece> pieces;
+    size_t total = 0;
+    auto add = [&](const void* src, size_t bytes) -> size_t {
+        size_t off = total;
+        pieces.push_back({src, bytes, off});
+        total += align256(std::max<size_t>(bytes, 1));
+        return off;
+    };
+    struct ColOff {
+        size_t values = 0, nulls = 0, offsets = 0, ids = 0, dvalues = 0, dnulls = 0, doffsets = 0;
+        bool hasNulls = false, hasDnulls = false;
+        int64_t byteBase = 0;
+    };
+    std::vector<ColOff> offs(g.NC);
+    for (int c : g.usedChannels) {
+        const pgpu_column& col = cols[c];
+        const Type& t = plan.input[c];
+        ColOff& o = offs[c];
+        if (col.encoding == PGPU_ENC_PLAIN) {
+            if (t.isVarWidth()) {
+                int32_t b0 = col.offsets[r0], b1 = col.offsets[r0 + n];
+                o.byteBase = b0;
+                o.offsets = add(col.offsets + r0, (size_t)(n + 1) * 4);
+                o.values = add((const char*)col.values + b0, (size_t)(b1 - b0));
+            } else {
+                o.values = add((const char*)col.values + (size_t)r0 * t.width(), (size_t)n * t.width());
+            }
+            if (col.nulls) {
+                o.hasNulls = true;
+                o.nulls = add(col.nulls + r0, (size_t)n);
+            }
+        } else {
+            const pgpu_column* d = col.dictionary;
+            if (col.encoding == PGPU_ENC_DICTIONARY) o.ids = add(col.ids + r0, (size_t)n * 4);
+            int64_t dn = d->position_count;
+            if (t.isVarWidth()) {
+                o.doffsets = add(d->offsets, (size_t)(dn + 1) * 4);
+                o.dvalues = add(d->values, (size_t)d->offsets[dn]);
+            } else {
+                o.dvalues = add(d->values, (size_t)dn * t.width());
+            }
+            if (d->nulls) {
+                o.hasDnulls = true;
+                o.dnulls = add(d->nulls, (size_t)dn);
+            }
+        }
+    }
+    pgpu_status st = ensureDev(p, slot.dev, total);
+    if (st) return st;
+    char* dbase = (char*)slot.dev.ptr;
+    if (pinned) {
+        for (auto& pc : pieces)
+            if (pc.bytes) CU(cudaMemcpyAsync(dbase + pc.off, pc.src, pc.bytes, cudaMemcpyHostToDevice, p->stream));
+    } else {
+        if (slot.hostCap < total) {
+            if (slot.host) CU(cudaFreeHost(slot.host));
+            slot.host = nullptr;
+            CU(cudaMallocHost(&slot.host, total));
+            slot.hostCap = total;
+        }
+        for (auto& pc : pieces)
+            if (pc.bytes) memcpy((char*)slot.host + pc.off, pc.src, pc.bytes);
+        CU(cudaMemcpyAsync(dbase, slot.host, total, cudaMemcpyHostToDevice, p->stream));
+    }
+    for (auto& pc : pieces) p->stats.h2d_bytes += (int64_t)pc.bytes;
+    out.assign(g.NC, ColArg{});
+    for (int c : g.usedChannels) {
+        const pgpu_column& col = cols[c];
+        const Type& t = plan.input[c];
+        const ColOff& o = offs[c];
+        ColArg a{};
+        if (col.encoding == PGPU_ENC_PLAIN) {
+            if (t.isVarWidth()) {
+                a.offsets = (const int32_t*)(dbase + o.offsets);
+                a.values = dbase + o.values - o.byteBase;  // offsets stay absolute
+            } else {
+                a.values = dbase + o.values;
+            }
+            if (o.hasNulls) a.nulls = (const uint8_t*)(dbase + o.nulls);
+        } else {
+            if (col.encoding == PGPU_ENC_DICTIONARY) a.ids = (const int32_t*)(dbase + o.ids);
+            a.dvalues = dbase + o.dvalues;
+            if (t.isVarWidth()) a.doffsets = (const int32_t*)(dbase + o.doffsets);
+            if (o.hasDnulls) a.dnulls = (const uint8_t*)(dbase + o.dnulls);
+        }
+        out[c] = a;
+    }
+    return PGPU_OK;
+}
+
+pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows, bool onDevice, uint32_t flags) {
+    if (p->device < 0) return fail(p, PGPU_INVALID_STATE, "pipeline was created compile-only (device < 0)");
+    if (p->finishing) return fail(p, PGPU_INVALID_STATE, "Operator is already finishing");
+    if (!pgpu_needs_input(p)) return fail(p, PGPU_INVALID_STATE, "Operator does not need input");
+    std::vector<ColSig> sig;
+    pgpu_status st = validatePage(p, cols, ncols, rows, sig);
+    if (st) return st;
+    CU(cudaSetDevice(p->device));
+    p->sawInput = true;
+    p->stats.input_pages++;
+    p->stats.input_rows += rows;
+    if (rows == 0) return PGPU_OK;
+    Variant* v = nullptr;
+    st = getVariant(p, sig, &v);
+    if (st) return st;
+    if (onDevice) {
+        for (int c : v->gen.usedChannels) {
+            const pgpu_column& col = cols[c];
+            auto mis = [](const void* q, size_t a) { return q && ((uintptr_t)q % a) != 0; };
+            if (mis(col.values, 16) || mis(col.ids, 16) || mis(col.offsets, 16) || mis(col.nulls, 4))
+                return fail(p, PGPU_INVALID_ARGUMENT, "device blocks must be 16-byte aligned (nulls: 4-byte)");
+        }
+        return processDevicePage(p, v, cols, rows);
+    }
+    // host page: stage in chunks through the ring, then run as device chunks
+    const bool pinned = (flags & PGPU_PAGE_PINNED) != 0;
+    const bool compact = v->gen.mode == KernelMode::COMPACT;
+    int64_t chunk = compact ? rows : kHostChunkRows;
+    for (int64_t r0 = 0; r0 < rows; r0 += chunk) {
+        int64_t n = std::min(chunk, rows - r0);
+        StageSlot& slot = p->slots[p->nextSlot];
+        p->nextSlot = (p->nextSlot + 1) % 3;
+        if (slot.inFlight) {
+            CU(cudaEventSynchronize(slot.done));
+            slot.inFlight = false;
+        }
+        DevPage pg;
+        pg.rows = n;
+        st = stageChunk(p, v, cols, r0, n, pinned, slot, pg.cols);
+        if (st) return st;
+        if (compact) {
+            st = runCompact(p, v, pg);
+        } else {
+            if (v->gen.mode == KernelMode::AGG_HASH) {
+                st = reserveGroups(p, v, n);
+                if (st) return st;
+                p->rowsSinceKnown += n;
+            }
+            st = launchPageKernel(p, v, pg);
+        }
+        if (st) return st;
+        if (!slot.done) CU(cudaEventCreateWithFlags(&slot.done, cudaEventDisableTiming));
+        CU(cudaEventRecord(slot.done, p->stream));
+        slot.inFlight = true;
+    }
+    return PGPU_OK;
+}
+
+// PARTIAL step: once the row-count upper bound crosses the flush threshold, learn the real group count
+pgpu_status updatePartialFill(pgpu_pipeline* p) {
+    const Plan& plan = *p->plan;
+    if (plan.hasAgg && plan.step == Step::PARTIAL && plan.maxPartialGroups > 0 && !plan.groupChannels.empty() && p->dSlots &&
+        p->groupsKnown + p->rowsSinceKnown >= plan.maxPartialGroups)
+        return refreshGroupCount(p);
+    return PGPU_OK;
+}
+
+// materialise the aggregation result into the device output buffers
+pgpu_status buildAggOutput(pgpu_pipeline* p) {
+    const GenResult& g = p->layout;
+    CU(cudaSetDevice(p->device));
+    // any compiled variant has the emit kernels (layout is signature independent)
+    Variant* v = nullptr;
+    if (p->variants.empty()) {
+        std::vector<ColSig> sig(p->plan->input.size());
+        pgpu_status st = getVariant(p, sig, &v);
+        if (st) return st;
+    } else {
+        v = &p->variants.begin()->second;
+    }
+    CU(cudaMemsetAsync(p->dOutCount, 0, 8, p->stream));
+    if (g.mode == KernelMode::AGG_GLOBAL) {
+        pgpu_status st = ensureOutBuffers(p, 1);
+        if (st) return st;
+        std::vector<unsigned char> oa = outArgsBlock(p);
+        Scratch sc = scratchOf(p);
+        void* args[] = {&sc, oa.data()};
+        st = launch(p, v->kEmit, 1, 32, 0, args);
+        if (st) return st;
+        p->outRowsTotal = 1;
+    } else {
+        if (!p->dSlots) {
+            p->outRowsTotal = 0;
+        } else {
+            pgpu_status st = refreshGroupCount(p);
+            if (st) return st;
+            st = ensureOutBuffers(p, p->groupsKnown);
+            if (st) return st;
+            std::vector<unsigned char> oa = outArgsBlock(p);
+            Scratch sc = scratchOf(p);
+            TableArgs t = tableOf(p);
+            int64_t first = 0, nslots = (int64_t)p->capacity;
+            void* args[] = {&t, oa.data(), &sc, &first, &nslots};
+            int grid = (int)std::min<uint64_t>((p->capacity + kThreads - 1) / kThreads, (uint64_t)p->numSMs * 8);
+            st = launch(p, v->kEmit, grid, kThreads, 0, args);
+            if (st) return st;
+            p->outRowsTotal = p->groupsKnown;
+        }
+    }
+    CU(cudaStreamSynchronize(p->stream));
+    pgpu_status st = checkDeviceErrors(p);
+    if (st) return st;
+    p->outputReady = true;
+    p->outRowsServed = 0;
+    return PGPU_OK;
+}
+
+void resetAggState(pgpu_pipeline* p) {
+    if (p->device < 0) return;
+    cudaSetDevice(p->device);
+    if (p->dState) cudaMemsetAsync(p->dState, 0, 8 * 64, p->stream);
+    if (p->dCounters) cudaMemsetAsync(p->dCounters, 0, 16, p->stream);
+    if (p->dSlots) cudaMemsetAsync(p->dSlots, 0, (size_t)p->capacity * p->layout.SLOTW * 8, p->stream);
+    if (p->dErr) cudaMemsetAsync(p->dErr, 0, 4, p->stream);
+    if (p->dTicket) cudaMemsetAsync(p->dTicket, 0, 4, p->stream);
+    p->groupsKnown = 0;
+    p->rowsSinceKnown = 0;
+}
+
+bool isPartialFlushDue(const pgpu_pipeline* p) {
+    return p->plan->hasAgg && p->plan->step == Step::PARTIAL && p->plan->maxPartialGroups > 0 && !p->plan->groupChannels.empty() &&
+           (p->groupsKnown + p->rowsSinceKnown) >= p->plan->maxPartialGroups;
+}
+
+}  // namespace
+
+// ================================================================================================ C ABI
+extern "C" {
+
+const char* pgpu_version(void) { return "prestogpu 0.1 (sm_100a)"; }
+
+int32_t pgpu_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+const char* pgpu_last_global_error(void) { return g_lastGlobalError.c_str(); }
+
+pgpu_status pgpu_pipeline_create(const uint8_t* plan, size_t plan_len, int32_t device, pgpu_pipeline** out) {
+    if (!plan || !out) {
+        g_lastGlobalError = "null argument";
+        return PGPU_INVALID_ARGUMENT;
+    }
+    *out = nullptr;
+    auto p = std::make_unique<pgpu_pipeline>();
+    try {
+        p->plan = parsePlan(std::string((const char*)plan, plan_len));
+    } catch (const PlanError& e) {
+        g_lastGlobalError = e.what();
+        return (pgpu_status)e.status;
+    }
+    p->device = device;
+    pgpu_pipeline* pp = p.get();
+    auto cuFail = [&](cudaError_t e, const char* what) {
+        g_lastGlobalError = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
+        return PGPU_CUDA_ERROR;
+    };
+    if (device >= 0) {
+        cudaError_t e;
+        if ((e = cudaSetDevice(device)) != cudaSuccess) return cuFail(e, "cudaSetDevice");
+        cudaDeviceProp prop;
+        if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return cuFail(e, "cudaGetDeviceProperties");
+        if (prop.major != 10) {
+            g_lastGlobalError = std::string("prestogpu kernels are built for sm_100a only; device is sm_") + std::to_string(prop.major) + std::to_string(prop.minor);
+            return PGPU_NOT_SUPPORTED;
+        }
+        p->numSMs = prop.multiProcessorCount;
+        if ((e = cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking)) != cudaSuccess) return cuFail(e, "cudaStreamCreate");
+        if ((e = cudaEventCreate(&p->evA)) != cudaSuccess) return cuFail(e, "cudaEventCreate");
+        if ((e = cudaEventCreate(&p->evB)) != cudaSuccess) return cuFail(e, "cudaEventCreate");
+        void* scratch = nullptr;
+        // err(4) ticket(4) out_count(8) counters(16) state(64*8)
+        if ((e = cudaMalloc(&scratch, 1024)) != cudaSuccess) return cuFail(e, "cudaMalloc");
+        if ((e = cudaMemset(scratch, 0, 1024)) != cudaSuccess) return cuFail(e, "cudaMemset");
+        char* s = (char*)scratch;
+        p->dErr = (uint32_t*)s;
+        p->dTicket = (uint32_t*)(s + 8);
+        p->dOutCount = (uint64_t*)(s + 16);
+        p->dCounters = (uint64_t*)(s + 32);
+        p->dState = (uint64_t*)(s + 64);
+        if ((e = cudaMallocHost((void**)&p->hostScalars, 64)) != cudaSuccess) return cuFail(e, "cudaMallocHost");
+        memset(p->hostScalars, 0, 64);
+    }
+    // compile the default variant now: plan-time rejection (NOT_SUPPORTED / COMPILER_ERROR) happens here
+    std::vector<ColSig> sig(p->plan->input.size());
+    Variant* v = nullptr;
+    pgpu_status st = getVariant(pp, sig, &v);
+    if (st) {
+        g_lastGlobalError = p->err;
+        pgpu_pipeline_destroy(p.release());
+        return st;
+    }
+    if (p->layout.NW > 60) {
+        g_lastGlobalError = "not supported on the GPU path: more than 60 accumulator words";
+        pgpu_pipeline_destroy(p.release());
+        return PGPU_NOT_SUPPORTED;
+    }
+    *out = p.release();
+    return PGPU_OK;
+}
+
+void pgpu_pipeline_destroy(pgpu_pipeline* p) {
+    if (!p) return;
+    if (p->device >= 0) {
+        cudaSetDevice(p->device);
+        if (p->stream) cudaStreamSynchronize(p->stream);
+        for (auto& kv : p->variants)
+            if (kv.second.lib) cudaLibraryUnload(kv.second.lib);
+        if (p->dErr) cudaFree(p->dErr);
+        if (p->dPartials) cudaFree(p->dPartials);
+        if (p->tileStatus.ptr) cudaFree(p->tileStatus.ptr);
+        if (p->dSlots) cudaFree(p->dSlots);
+        if (p->hostScalars) cudaFreeHost(p->hostScalars);
+        for (auto& s : p->slots) {
+            if (s.dev.ptr) cudaFree(s.dev.ptr);
+            if (s.host) cudaFreeHost(s.host);
+            if (s.done) cudaEventDestroy(s.done);
+        }
+        for (auto& b : p->outDev)
+            if (b.ptr) cudaFree(b.ptr);
+        for (auto& b : p->outDevNulls)
+            if (b.ptr) cudaFree(b.ptr);
+        for (auto* vec : {&p->outHost, &p->outHostNulls, &p->outHostAux})
+            for (auto& b : *vec)
+                if (b.ptr) cudaFreeHost(b.ptr);
+        if (p->evA) cudaEventDestroy(p->evA);
+        if (p->evB) cudaEventDestroy(p->evB);
+        if (p->stream) cudaStreamDestroy(p->stream);
+    }
+    delete p;
+}
+
+const char* pgpu_last_error(const pgpu_pipeline* p) { return p ? p->err.c_str() : "null pipeline"; }
+
+int32_t pgpu_needs_input(const pgpu_pipeline* p) {
+    if (!p || p->finishing || p->finished) return 0;
+    if (p->outputReady) return 0;  // HashAggregationOperator.needsInput: outputPages != null => false
+    if (isPartialFlushDue(p)) return 0;  // aggregationBuilder.isFull()
+    return 1;
+}
+
+pgpu_status pgpu_add_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows, uint32_t flags) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    pgpu_status st = addPageCommon(p, cols, ncols, rows, false, flags);
+    return st ? st : updatePartialFill(p);
+}
+
+pgpu_status pgpu_add_device_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    pgpu_status st = addPageCommon(p, cols, ncols, rows, true, 0);
+    return st ? st : updatePartialFill(p);
+}
+
+pgpu_status pgpu_finish(pgpu_pipeline* p) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    p->finishing = true;
+    return PGPU_OK;
+}
+
+int32_t pgpu_is_finished(const pgpu_pipeline* p) { return p && p->finished ? 1 : 0; }
+
+static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows, bool toHost) {
+    if (!p || !ncols || !rows) return PGPU_INVALID_ARGUMENT;
+    *rows = -1;
+    *ncols = 0;
+    if (p->finished) return PGPU_OK;
+    if (p->device < 0) return fail(p, PGPU_INVALID_STATE, "pipeline was created compile-only (device < 0)");
+    const GenResult& g = p->layout;
+    const Plan& plan = *p->plan;
+    CU(cudaSetDevice(p->device));
+    if (g.mode == KernelMode::COMPACT) {
+        if (!p->outputReady) {
+            if (p->finishing) p->finished = true;
+            return PGPU_OK;
+        }
+        CU(cudaStreamSynchronize(p->stream));
+        pgpu_status st = checkDeviceErrors(p);
+        if (st) return st;
+        p->outRowsTotal = (int64_t)p->hostScalars[0];
+    } else {
+        if (!p->outputReady) {
+            const bool flush = isPartialFlushDue(p);
+            if (!p->finishing && !flush) return PGPU_OK;  // only flush if we are finishing or the builder is full
+            const bool global = plan.groupChannels.empty();
+            if (!global && !p->sawInput) {  // HashAggregationOperator.getOutput: no input, no default output for grouped aggregation
+                p->finished = true;
+                return PGPU_OK;
+            }
+            pgpu_status st = buildAggOutput(p);
+            if (st) return st;
+        }
+    }
+    if (max_cols < g.NO || !out_cols) return fail(p, PGPU_INVALID_ARGUMENT, "out_cols too small: need " + std::to_string(g.NO));
+    int64_t remaining = p->outRowsTotal - p->outRowsServed;
+    int64_t n = remaining;
+    if (plan.maxOutputRows > 0) n = std::min<int64_t>(n, plan.maxOutputRows);
+    const int64_t r0 = p->outRowsServed;
+    if (remaining <= 0 && g.mode != KernelMode::COMPACT) {
+        // nothing (left) to serve
+        p->outputReady = false;
+        if (p->finishing) p->finished = true;
+        else resetAggState(p);
+        return PGPU_OK;
+    }
+    for (int c = 0; c < g.NO; c++) {
+        const OutColDesc& d = g.out[c];
+        pgpu_column& oc = out_cols[c];
+        memset(&oc, 0, sizeof oc);
+        oc.encoding = PGPU_ENC_PLAIN;
+        oc.type_kind = (int32_t)d.type.kind;
+        oc.precision = d.type.precision;
+        oc.scale = d.type.scale;
+        oc.position_count = n;
+        const char* dv = (const char*)p->outDev[c].ptr + (size_t)r0 * d.stride;
+        const uint8_t* dn = (const uint8_t*)p->outDevNulls[c].ptr + r0;
+        if (!toHost) {
+            if (d.varWidth) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: device-resident var-width output");
+            oc.values = dv;
+            oc.nulls = dn;
+            continue;
+        }
+        pgpu_status st = ensureHost(p, p->outHost[c], (size_t)std::max<int64_t>(n, 1) * std::max(d.stride, 1));
+        if (st) return st;
+        st = ensureHost(p, p->outHostNulls[c], (size_t)std::max<int64_t>(n, 1));
+        if (st) return st;
+        if (n > 0) {
+            CU(cudaMemcpyAsync(p->outHost[c].ptr, dv, (size_t)n * d.stride, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaMemcpyAsync(p->outHostNulls[c].ptr, dn, (size_t)n, cudaMemcpyDeviceToHost, p->stream));
+            p->stats.d2h_bytes += n * d.stride + n;
+        }
+        oc.values = p->outHost[c].ptr;
+        oc.nulls = (const uint8_t*)p->outHostNulls[c].ptr;
+    }
+    if (toHost) {
+        CU(cudaStreamSynchronize(p->stream));
+        // var-width cells -> VariableWidthBlock layout (offsets + bytes), in place
+        for (int c = 0; c < g.NO; c++) {
+            const OutColDesc& d = g.out[c];
+            if (!d.varWidth) continue;
+            pgpu_status st = ensureHost(p, p->outHostAux[c], (size_t)(n + 1) * 4);
+            if (st) return st;
+            int32_t* offs = (int32_t*)p->outHostAux[c].ptr;
+            unsigned char* cells = (unsigned char*)p->outHost[c].ptr;
+            const uint8_t* nulls = (const uint8_t*)p->outHostNulls[c].ptr;
+            int32_t w = 0;
+            offs[0] = 0;
+            for (int64_t i = 0; i < n; i++) {
+                const unsigned char* cell = cells + (size_t)i * d.stride;
+                int len = d.lenPrefixed ? cell[0] : d.stride;
+                if (nulls[i]) len = 0;
+                memmove(cells + w, cell + (d.lenPrefixed ? 1 : 0), (size_t)len);  // w <= i*stride: never overtakes the read cursor
+                w += len;
+                offs[i + 1] = w;
+            }
+            out_cols[c].offsets = offs;
+        }
+    }
+    *ncols = g.NO;
+    *rows = n;
+    p->outRowsServed += n;
+    if (g.mode == KernelMode::COMPACT) {
+        p->outputReady = false;
+    } else if (p->outRowsServed >= p->outRowsTotal) {
+        p->outputReady = false;
+        if (p->finishing) p->finished = true;
+        else resetAggState(p);  // partial flush: start a fresh table (HashAggregationOperator.closeAggregationBuilder)
+    }
+    return PGPU_OK;
+}
+
+pgpu_status pgpu_get_output(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows) {
+    return getOutputImpl(p, out_cols, max_cols, ncols, rows, true);
+}
+
+pgpu_status pgpu_get_output_device(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows) {
+    return getOutputImpl(p, out_cols, max_cols, ncols, rows, false);
+}
+
+pgpu_status pgpu_sync(pgpu_pipeline* p) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    if (p->device < 0) return PGPU_OK;
+    CU(cudaSetDevice(p->device));
+    CU(cudaStreamSynchronize(p->stream));
+    for (auto& s : p->slots) s.inFlight = false;
+    return checkDeviceErrors(p);
+}
+
+pgpu_status pgpu_reset(pgpu_pipeline* p) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    if (p->device >= 0) {
+        CU(cudaSetDevice(p->device));
+        resetAggState(p);
+        CU(cudaStreamSynchronize(p->stream));
+    }
+    p->finishing = p->finished = p->sawInput = p->outputReady = false;
+    p->outRowsTotal = p->outRowsServed = 0;
+    int64_t cap = p->stats.table_capacity;
+    p->stats = pgpu_stats{};
+    p->stats.table_capacity = cap;
+    p->err.clear();
+    return PGPU_OK;
+}
+
+int32_t pgpu_output_channel_count(const pgpu_pipeline* p) { return p ? (int32_t)p->plan->outputTypes().size() : 0; }
+
+pgpu_status pgpu_output_channel_type(const pgpu_pipeline* p, int32_t channel, int32_t* type_kind, int32_t* precision, int32_t* scale) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    std::vector<Type> t = p->plan->outputTypes();
+    if (channel < 0 || channel >= (int)t.size()) return PGPU_INVALID_ARGUMENT;
+    if (type_kind) *type_kind = (int32_t)t[channel].kind;
+    if (precision) *precision = t[channel].precision;
+    if (scale) *scale = t[channel].scale;
+    return PGPU_OK;
+}
+
+const char* pgpu_generated_source(const pgpu_pipeline* p) { return p ? p->lastSource.c_str() : ""; }
+
+pgpu_status pgpu_get_stats(const pgpu_pipeline* p, pgpu_stats* out) {
+    if (!p || !out) return PGPU_INVALID_ARGUMENT;
+    *out = p->stats;
+    return PGPU_OK;
+}
+
+pgpu_status pgpu_set_timing(pgpu_pipeline* p, int32_t enabled) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    p->timing = enabled != 0;
+    return PGPU_OK;
+}
+
+void* pgpu_stream(const pgpu_pipeline* p) { return p ? (void*)p->stream : nullptr; }
+
+pgpu_status pgpu_compile_signature(pgpu_pipeline* p, const int32_t* encodings, const uint8_t* nullable, int32_t ncols) {
+    if (!p || !encodings || !nullable) return PGPU_INVALID_ARGUMENT;
+    if (ncols != (int)p->plan->input.size()) return fail(p, PGPU_INVALID_ARGUMENT, "signature length differs from the plan's input channels");
+    std::vector<ColSig> sig(ncols);
+    for (int c = 0; c < ncols; c++) {
+        sig[c].encoding = encodings[c];
+        sig[c].nullable = nullable[c] != 0;
+    }
+    Variant* v = nullptr;
+    return getVariant(p, sig, &v);
+}
+
+void* pgpu_host_alloc(size_t bytes) {
+    void* q = nullptr;
+    if (cudaMallocHost(&q, bytes ? bytes : 1) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return q;
+}
+
+void pgpu_host_free(void* ptr) {
+    if (ptr) cudaFreeHost(ptr);
+}
+
+void* pgpu_device_alloc(int32_t device, size_t bytes) {
+    void* q = nullptr;
+    if (cudaSetDevice(device) != cudaSuccess || cudaMalloc(&q, bytes ? bytes : 1) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return q;
+}
+
+void pgpu_device_free(int32_t device, void* ptr) {
+    if (!ptr) return;
+    cudaSetDevice(device);
+    cudaFree(ptr);
+}
+
+pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t, pgpu_column*, int32_t, int32_t*, int64_t*) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    return fail(p, PGPU_NOT_SUPPORTED, "partitioned output: not built yet");
+}
+
+pgpu_status pgpu_dense_state_device(pgpu_pipeline* p, void**, int64_t*, int64_t*) {
+    if (!p) return PGPU_INVALID_ARGUMENT;
+    return fail(p, PGPU_NOT_SUPPORTED, "dense state: not built yet");
+}
+
+}  // extern "C"
