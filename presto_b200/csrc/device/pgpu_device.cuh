@@ -171,8 +171,9 @@ PGPU_DEV bool dec_overflows(i128 v) {
     u128 mag = v < 0 ? (u128)0 - (u128)v : (u128)v;
     return mag >= lim;
 }
-// exact 128-bit product with overflow detection (UnscaledDecimal128Arithmetic.multiply + throwIfOverflows)
-PGPU_DEV i128 dec_mul(i128 a, i128 b, u32& err) {
+// exact 127-bit-magnitude product (UnscaledDecimal128Arithmetic.multiply :452-650: throws when the magnitude
+// needs more than 127 bits); `check38` adds throwIfOverflows (|r| >= 10^38) as DecimalOperators.multiply* do.
+PGPU_DEV i128 dec_mul_impl(i128 a, i128 b, bool check38, u32& err) {
     bool neg = (a < 0) != (b < 0);
     u128 ma = a < 0 ? (u128)0 - (u128)a : (u128)a, mb = b < 0 ? (u128)0 - (u128)b : (u128)b;
     u64 a0 = (u64)ma, a1 = (u64)(ma >> 64), b0 = (u64)mb, b1 = (u64)(mb >> 64);
@@ -184,11 +185,12 @@ PGPU_DEV i128 dec_mul(i128 a, i128 b, u32& err) {
     ovf |= (mid >> 63) != 0;
     u128 m = ((u128)(u64)mid << 64) | (u64)lo;
     i128 r = neg ? -(i128)m : (i128)m;
-    if (ovf || dec_overflows(r)) err |= PGPU_ERR_OVERFLOW;
+    if (ovf || (check38 && dec_overflows(r))) err |= PGPU_ERR_OVERFLOW;
     return r;
 }
-// a * 10^k with overflow detection (UnscaledDecimal128Arithmetic.rescale, upscale direction); p10 = 10^k
-PGPU_DEV i128 dec_upscale(i128 a, i128 p10, u32& err) { return dec_mul(a, p10, err); }
+PGPU_DEV i128 dec_mul(i128 a, i128 b, u32& err) { return dec_mul_impl(a, b, true, err); }
+// a * 10^k (UnscaledDecimal128Arithmetic.rescale :218-232, upscale direction: overflow only past 127 bits); p10 = 10^k
+PGPU_DEV i128 dec_upscale(i128 a, i128 p10, u32& err) { return dec_mul_impl(a, p10, false, err); }
 // HALF_UP division by 10^k (rescale down / avg): round half away from zero
 PGPU_DEV i128 dec_div_round(i128 a, i128 d) {
     bool neg = (a < 0) != (d < 0);
