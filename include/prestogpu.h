@@ -178,6 +178,9 @@ void pgpu_host_free(void* ptr);
 /* Device memory helpers for callers without torch. */
 void* pgpu_device_alloc(int32_t device, size_t bytes);
 void pgpu_device_free(int32_t device, void* ptr);
+/* Synchronous copies between host and device memory (test / bench plumbing for callers without torch). */
+pgpu_status pgpu_memcpy_h2d(int32_t device, void* dev_dst, const void* host_src, size_t bytes);
+pgpu_status pgpu_memcpy_d2h(int32_t device, void* host_dst, const void* dev_src, size_t bytes);
 
 /* Synthetic TPC-H lineitem columns generated directly in HBM (SURVEY.md §8(d) distributions; the
  * reference's generator io.trino.tpch:tpch:1.1 is not in its tree). Column ids: see PGPU_LI_* below.

@@ -70,6 +70,8 @@ SYMBOLS = [
     ("pgpu_host_free", None, [ctypes.c_void_p]),
     ("pgpu_device_alloc", ctypes.c_void_p, [ctypes.c_int32, ctypes.c_size_t]),
     ("pgpu_device_free", None, [ctypes.c_int32, ctypes.c_void_p]),
+    ("pgpu_memcpy_h2d", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]),
+    ("pgpu_memcpy_d2h", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]),
     ("pgpu_gen_lineitem_device", ctypes.c_int32, [ctypes.c_int32, ctypes.c_int32, ctypes.c_uint64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p]),
     ("pgpu_gen_lineitem_host", ctypes.c_int32, [ctypes.c_int32, ctypes.c_uint64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p]),
     ("pgpu_flush_l2", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p, ctypes.c_size_t]),

@@ -976,7 +976,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     res.SLOTW = ((1 + KW + NW) + 3) / 4 * 4;
 
     // directory sizing (shared memory): 8 warps x DCAP x NW words + keys + tags
-    res.useDir = res.mode == KernelMode::AGG_HASH && plan.expectedGroups <= 4096 && NW > 0;
+    res.useDir = res.mode == KernelMode::AGG_HASH && plan.expectedGroups <= (1 << 20) && NW > 0;
     res.dirCap = 0;
     if (res.useDir) {
         int cap = 128;

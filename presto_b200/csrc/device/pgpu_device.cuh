@@ -524,6 +524,7 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
     const i64 tile_rows = (i64)blockDim.x * 4;
     const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
     u64* myacc = wacc + (size_t)warp * DCAP * NWA;
+    bool use_dir = P::USE_DIR;  // warp-uniform
     for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
         bool sel[4];
@@ -541,7 +542,8 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
                 sel[r] = false;
             }
         }
-        if (P::USE_DIR) {
+        if (P::USE_DIR && use_dir) {
+            int hits = 0, misses = 0;
 #pragma unroll
             for (int r = 0; r < 4; r++) {
                 if (!__any_sync(FULLMASK, sel[r])) continue;
@@ -549,6 +551,8 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
                 if (sel[r]) slot = dir_lookup<P>(dkeys, dtags, dcount, key[r], hash_key<KW>(key[r]));
                 u32 peers = __match_any_sync(FULLMASK, slot);
                 u32 leaders = __ballot_sync(FULLMASK, slot >= 0 && lane == __ffs(peers) - 1);
+                hits += __popc(__ballot_sync(FULLMASK, slot >= 0));
+                misses += __popc(__ballot_sync(FULLMASK, sel[r] && slot < 0));
                 if (__popc(leaders) <= P::MAX_WARP_GROUPS) {
                     while (leaders) {
                         int leader = __ffs(leaders) - 1;
@@ -568,9 +572,13 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
                 } else {
                     // many distinct groups in this warp: fire-and-forget atomics on the HBM table
                     if (sel[r]) table_update<P>(t, key[r], cw[r], err);
+                    misses += 32;
                 }
                 __syncwarp();
             }
+            // adaptive bypass: once most rows miss the (full) directory, stop paying for lookups. Bypassing is always
+            // correct because the directory accumulators and the HBM table are merged additively at the end.
+            if (misses > 2 * hits) use_dir = false;
         } else {
 #pragma unroll
             for (int r = 0; r < 4; r++)

@@ -1103,6 +1103,16 @@ void pgpu_device_free(int32_t device, void* ptr) {
     cudaFree(ptr);
 }
 
+pgpu_status pgpu_memcpy_h2d(int32_t device, void* dev_dst, const void* host_src, size_t bytes) {
+    if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
+    return cudaMemcpy(dev_dst, host_src, bytes, cudaMemcpyHostToDevice) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
+}
+
+pgpu_status pgpu_memcpy_d2h(int32_t device, void* host_dst, const void* dev_src, size_t bytes) {
+    if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
+    return cudaMemcpy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
+}
+
 pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t, pgpu_column*, int32_t, int32_t*, int64_t*) {
     if (!p) return PGPU_INVALID_ARGUMENT;
     return fail(p, PGPU_NOT_SUPPORTED, "partitioned output: not built yet");
