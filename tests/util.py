@@ -90,3 +90,51 @@ def assert_rows_equal_ordered(actual, expected, rtol=0.0):
     for i, (a, e) in enumerate(zip(actual, expected)):
         for j, (x, y) in enumerate(zip(a, e)):
             assert value_equal(x, y, rtol), "row %d column %d: %r != %r" % (i, j, x, y)
+
+
+# ---------------------------------------------------------------------------------------------- exact references
+# DOUBLE sums depend on the summation order: the reference adds sequentially in position order (error grows like
+# n * 2^-53), the GPU adds in a tree. Both are therefore compared with the correctly rounded sum (math.fsum) of
+# the same per-row values; the per-row projections are plain IEEE operations and are bit-identical everywhere.
+def sequential_bound(n):
+    """relative error bound of a sequential double sum of n same-signed terms"""
+    return max(DOUBLE_RTOL, n * 2.0 ** -53)
+
+
+def exact_q1(pages):
+    import numpy as np
+    groups = {}
+    for p in pages:
+        rf, ls = p.blocks[0].to_pylist(), p.blocks[1].to_pylist()
+        col = lambda c: np.array(p.blocks[c].to_pylist(), dtype=np.float64)
+        q, e, d, t = col(2), col(3), col(4), col(5)
+        ship = np.array(p.blocks[6].to_pylist())
+        dp = e * (1.0 - d)
+        ch = dp * (1.0 + t)
+        sel = ship <= 10471
+        keys = np.array([a + b for a, b in zip(rf, ls)])
+        for k in np.unique(keys[sel]):
+            m = sel & (keys == k)
+            g = groups.setdefault(k, [[], [], [], [], [], 0])
+            for i, v in enumerate((q, e, dp, ch, d)):
+                g[i].append(v[m])
+            g[5] += int(m.sum())
+    rows = []
+    for k, g in groups.items():
+        s = [math.fsum(np.concatenate(x).tolist()) for x in g[:5]]
+        n = g[5]
+        rows.append((k[0], k[1], s[0], s[1], s[2], s[3], s[0] / n, s[1] / n, s[4] / n, n))
+    return rows
+
+
+def exact_q6(pages):
+    import numpy as np
+    parts = []
+    for p in pages:
+        col = lambda c: np.array(p.blocks[c].to_pylist(), dtype=np.float64)
+        e, d, q = col(0), col(1), col(3)
+        ship = np.array(p.blocks[2].to_pylist())
+        sel = (ship >= 8766) & (ship < 9131) & (d >= 0.05) & (d <= 0.07) & (q < 24.0)
+        parts.append((e * d)[sel])
+    v = np.concatenate(parts)
+    return [(math.fsum(v.tolist()) if len(v) else None,)], len(v)
