@@ -1,0 +1,423 @@
+#!/usr/bin/env python
+"""bench.py — TPC-H Q1 (BASELINE.json configs[1]) lineitem rows/s on N B200s, with the kernel roofline and a CPU
+baseline. One "step" = one full pass of the fused scan->filter->project->hash-aggregate pipeline over the
+synthetic lineitem table (device-resident for `value`, pinned host pages for `e2e`).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload q1|q6|highcard|q1dict]
+                  [--rows R]
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SF100_ROWS = 600_037_902  # TPC-H lineitem at sf100
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="q1", choices=["q1", "q6", "highcard", "highcard_shuffled", "q1dict"])
+    ap.add_argument("--rows", type=int, default=SF100_ROWS, help="lineitem rows per GPU")
+    ap.add_argument("--e2e-rows", type=int, default=0, help="rows of the end-to-end (host pages) leg; 0 = same as --rows if RAM allows")
+    ap.add_argument("--cpu-rows-per-core", type=int, default=4_000_000)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def workload_def(name, rows):
+    from presto_b200 import tpch
+    from presto_b200.spi import DOUBLE, LongArrayBlock, VariableWidthBlock
+    import numpy as np
+    if name == "q1":
+        return dict(plan=tpch.q1_plan, spec=tpch.Q1_DEVICE_SPEC, bytes_per_row=tpch.Q1_BYTES_PER_ROW, page=tpch.q1_page,
+                    label="TPC-H Q1 (GROUP BY returnflag, linestatus; 8 aggregates) over synthetic lineitem", nkeys=2)
+    if name == "q1dict":
+        rf = VariableWidthBlock.from_values(tpch.VARCHAR1, ["A", "N", "R"])
+        ls = VariableWidthBlock.from_values(tpch.VARCHAR1, ["F", "O"])
+        qty = LongArrayBlock(DOUBLE, np.arange(1, 51, dtype=np.float64))
+        disc = LongArrayBlock(DOUBLE, np.arange(0, 11, dtype=np.float64) / 100.0)
+        tax = LongArrayBlock(DOUBLE, np.arange(0, 9, dtype=np.float64) / 100.0)
+        from presto_b200.spi import DATE
+        spec = [(tpch.VARCHAR1, "dict", "returnflag_id", rf), (tpch.VARCHAR1, "dict", "linestatus_id", ls),
+                (DOUBLE, "dict", "quantity_id", qty), (DOUBLE, "plain", "extendedprice"), (DOUBLE, "dict", "discount_id", disc),
+                (DOUBLE, "dict", "tax_id", tax), (DATE, "plain", "shipdate")]
+        return dict(plan=tpch.q1_plan, spec=spec, bytes_per_row=32, page=tpch.q1_page_encoded,
+                    label="TPC-H Q1 over dictionary-encoded lineitem pages (config 4)", nkeys=2)
+    if name == "q6":
+        return dict(plan=tpch.q6_plan, spec=tpch.Q6_DEVICE_SPEC, bytes_per_row=tpch.Q6_BYTES_PER_ROW, page=tpch.q6_page,
+                    label="TPC-H Q6 (filter + project + global SUM) over synthetic lineitem", nkeys=None)
+    shuffled = name == "highcard_shuffled"
+    return dict(plan=lambda step="single": tpch.highcard_plan(max(rows // 4, 1000), step),
+                spec=tpch.HC_SHUFFLED_DEVICE_SPEC if shuffled else tpch.HC_DEVICE_SPEC, bytes_per_row=tpch.HC_BYTES_PER_ROW,
+                page=lambda a, b, c: tpch.highcard_page(a, b, c, shuffled),
+                label="GROUP BY l_orderkey SUM(l_quantity), %s keys (config 3)" % ("shuffled" if shuffled else "clustered"), nkeys=1)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+        sm, mx, reasons = [], 0.0, set()
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = max(mx, float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s; MEASURED_PEAKS.json absent)"
+
+
+# ------------------------------------------------------------------------------------------------ CPU baseline
+def cpu_run(wl, rows_per_core, cores, repeats=1):
+    """The CPU oracle (oracle/, the C++ restatement of the reference's loops — the reference itself is Java and there
+    is no JVM on this box) on all host cores: one PARTIAL pipeline per thread over its own row range, page-at-a-time
+    (1 M-row pages), then one FINAL pipeline over the partial outputs (the analogue of task_concurrency drivers +
+    the partial->final exchange). Data generation is outside the timed region. Returns rows/s."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle_op import OracleOperator
+    from presto_b200.operators import toPages
+    from presto_b200.spi import Page
+    total = rows_per_core * cores
+    page_rows = 1_000_000
+    shards = []
+    for t in range(cores):
+        pages, r0 = [], t * rows_per_core
+        end = r0 + rows_per_core
+        while r0 < end:
+            n = min(page_rows, end - r0)
+            pages.append(wl["page"](r0, n, total))
+            r0 += n
+        shards.append(pages)
+    partial_plan = wl["plan"]("partial")
+    best = None
+    result = None
+    for _ in range(repeats):
+        outs = [None] * cores
+
+        def work(t):
+            op = OracleOperator(partial_plan)
+            outs[t] = toPages(op, shards[t])
+            op.close()
+
+        t0 = time.perf_counter()
+        th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        # FINAL step over the partial pages
+        from presto_b200.tpch import plan_text  # noqa: F401
+        final_plan = final_plan_for(wl, partial_plan)
+        fop = OracleOperator(final_plan)
+        pages = [p for o in outs for p in o]
+        result = toPages(fop, pages)
+        fop.close()
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return total / best, total, result
+
+
+def final_plan_for(wl, partial_plan):
+    """FINAL-step plan whose input channels are the PARTIAL plan's output channels."""
+    from presto_b200.operators import Aggregation, GpuPipelineOperator, plan_text
+    import re
+    from presto_b200 import tpch
+    from presto_b200.spi import BIGINT, DOUBLE
+    name = wl["name"]
+    if name in ("q1", "q1dict"):
+        # partial output: returnflag, linestatus, then per aggregate its intermediate channels
+        inp = [tpch.VARCHAR1, tpch.VARCHAR1] + [BIGINT, DOUBLE] * 4 + [DOUBLE, BIGINT] * 3 + [BIGINT]
+        aggs = [Aggregation("sum", DOUBLE, 2, DOUBLE), Aggregation("sum", DOUBLE, 4, DOUBLE), Aggregation("sum", DOUBLE, 6, DOUBLE),
+                Aggregation("sum", DOUBLE, 8, DOUBLE), Aggregation("avg", DOUBLE, 10, DOUBLE), Aggregation("avg", DOUBLE, 12, DOUBLE),
+                Aggregation("avg", DOUBLE, 14, DOUBLE), Aggregation("count", BIGINT, 16, BIGINT)]
+        return plan_text(inp, step="final", groupByChannels=[0, 1], aggregations=aggs)
+    if name == "q6":
+        return plan_text([BIGINT, DOUBLE], step="final", aggregations=[Aggregation("sum", DOUBLE, 0, DOUBLE)])
+    return plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0], aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)],
+                     expectedGroups=10_000_000)
+
+
+# ------------------------------------------------------------------------------------------------ GPU legs
+def run_device_steps(args, wl, device, dist):
+    """`value`: inputs resident in HBM before the timed region. Times each step with CUDA events on the pipeline's
+    stream; the barrier + synchronize bracket and the max over ranks follow the bench contract."""
+    import torch
+    from presto_b200 import _native as N
+    from presto_b200 import tpch
+    from presto_b200.operators import GpuPipelineOperator
+    L = N.lib()
+    rows = args.rows
+    first = dist["rank"] * rows
+    total = rows * dist["world"]
+    dp = tpch.DevicePage(device, wl["spec"], rows, first_row=first, total_rows=total)
+    op = GpuPipelineOperator(wl["plan"]("single" if dist["world"] == 1 else "partial"), device)
+    stream = torch.cuda.ExternalStream(L.pgpu_stream(op._h), device=torch.device("cuda", device))
+    ncol = len(wl["spec"])
+
+    def one_step():
+        op.reset()
+        op.addDeviceInput(dp.cols, ncol, rows)
+        op.finish()
+        out = []
+        while not op.isFinished():
+            p = op.getOutput()
+            if p is not None:
+                out.append(p)
+        return out
+
+    def barrier():
+        if dist["world"] > 1:
+            import torch.distributed as td
+            td.barrier()
+        torch.cuda.synchronize(device)
+
+    result = None
+    for _ in range(args.warmup):
+        result = one_step()
+    sampler = ClockSampler(device)
+    sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record(stream)
+    launches = 0
+    for _ in range(args.steps):
+        result = one_step()
+        launches += op.stats().kernel_launches
+    e1.record(stream)
+    barrier()
+    wall = time.perf_counter() - t0
+    dev_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    # dominant kernel alone: per-launch CUDA-event durations (pgpu_set_timing brackets every page-kernel launch)
+    op.setTiming(True)
+    kern_ms, kern_launches = 0.0, 0
+    for _ in range(max(3, min(args.steps, 5))):
+        one_step()
+        st = op.stats()
+        kern_ms += st.device_ms
+        kern_launches += st.kernel_launches
+    op.setTiming(False)
+    info = dict(dev_ms=dev_ms, wall_s=wall, launches=launches, clocks=clocks, kern_ms=kern_ms, kern_launches=kern_launches,
+                kern_steps=max(3, min(args.steps, 5)), result=result, table_capacity=op.stats().table_capacity)
+    return info, dp, op
+
+
+def run_e2e_steps(args, wl, device, dp_device, steps, warmup):
+    """`e2e`: the same pass through pgpu_add_page with HOST pages in pinned memory; H2D copies and the D2H read of the
+    result are inside the timed region (wall clock around the public API call sequence)."""
+    import numpy as np
+    from presto_b200 import _native as N
+    from presto_b200 import tpch
+    from presto_b200.operators import GpuPipelineOperator
+    L = N.lib()
+    rows = args.e2e_rows or args.rows
+    # bound by available host memory (pinned): keep below 40 % of MemAvailable
+    need = rows * wl["bytes_per_row"] * 1.05
+    try:
+        avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
+    except Exception:
+        avail = 64 << 30
+    if need > 0.4 * avail:
+        rows = int(0.4 * avail / (wl["bytes_per_row"] * 1.05))
+    rows = min(rows, dp_device.rows)
+    # host pages = the device columns copied back into pinned host buffers (identical bytes, no slow host generation)
+    cols = (N.Column * len(wl["spec"]))()
+    hostbufs = []
+    h2d = 0
+
+    def pinned_copy(dev_ptr, nbytes):
+        nonlocal h2d
+        hp = L.pgpu_host_alloc(max(nbytes, 16))
+        if not hp:
+            raise MemoryError("pinned allocation of %d bytes failed" % nbytes)
+        hostbufs.append(hp)
+        if L.pgpu_memcpy_d2h(device, hp, dev_ptr, nbytes):
+            raise RuntimeError("d2h copy failed")
+        h2d += nbytes
+        return hp
+
+    width = {0: 1, 1: 8, 2: 4, 3: 4, 4: 8}
+    dict_cols = []
+    for i, s in enumerate(wl["spec"]):
+        src, dst = dp_device.cols[i], cols[i]
+        ctypes.memmove(ctypes.byref(dst), ctypes.byref(src), ctypes.sizeof(N.Column))
+        dst.position_count = rows
+        t = s[0]
+        if s[1] == "plain":
+            dst.values = pinned_copy(src.values, rows * width[t.kind])
+        elif s[1] == "varchar1":
+            dst.values = pinned_copy(src.values, rows)
+            dst.offsets = pinned_copy(src.offsets, (rows + 1) * 4)
+        else:  # dict: ids from device, dictionary block straight from the host block
+            dst.ids = pinned_copy(src.ids, rows * 4)
+            d = N.Column()
+            keep = []
+            s[3]._fill(d, keep)
+            dict_cols.append((d, keep))
+            dst.dictionary = ctypes.pointer(d)
+    op = GpuPipelineOperator(wl["plan"]("single"), device)
+
+    def one_step():
+        op.reset()
+        op._check(L.pgpu_add_page(op._h, cols, len(wl["spec"]), rows, N.PAGE_PINNED))
+        op.finish()
+        out = []
+        while not op.isFinished():
+            p = op.getOutput()
+            if p is not None:
+                out.append(p)
+        return out
+
+    for _ in range(warmup):
+        one_step()
+    t0 = time.perf_counter()
+    d2h = 0
+    for _ in range(steps):
+        one_step()
+        d2h = op.stats().d2h_bytes
+    dt = time.perf_counter() - t0
+    st = op.stats()
+    op.close()
+    for hp in hostbufs:
+        L.pgpu_host_free(hp)
+    return dict(rows=rows, seconds=dt, steps=steps, h2d_bytes_per_step=int(st.h2d_bytes), d2h_bytes_per_step=int(d2h))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    wl = workload_def(args.workload, args.rows)
+    wl["name"] = args.workload
+    cores = os.cpu_count() or 1
+    metric = "lineitem_rows_per_second"
+    config = {"workload": wl["label"], "rows_per_gpu": args.rows, "scale_factor_equivalent": round(args.rows / 6_001_215, 2),
+              "bytes_per_row": wl["bytes_per_row"], "partitioning": "row-range shard per GPU, partial -> final aggregation",
+              "l2_policy": "inputs (%.1f GB per GPU) are far larger than the 126 MB L2: no flush needed" % (args.rows * wl["bytes_per_row"] / 1e9)}
+
+    if args.impl == "reference":
+        # the reference's CPU implementation of the path: Java, no JVM here -> the oracle port on all host cores
+        if rank != 0:
+            return
+        from __graft_entry__ import build
+        build()
+        per_core = args.cpu_rows_per_core
+        vals = []
+        for i in range(args.warmup + args.steps):
+            v, total, _ = cpu_run(wl, per_core, cores)
+            if i >= args.warmup:
+                vals.append(v)
+        value = sum(vals) / len(vals)
+        sample = "%d rows (%d per core x %d cores) of the same synthetic lineitem per step, 1 M-row pages, partial per thread + final merge" % (per_core * cores, per_core, cores)
+        line = {"impl": "reference", "metric": metric, "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1000.0 * per_core * cores / value, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port", "sample": sample},
+                "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "note": "reference Java benchmarks (HandTpchQuery1/6) cannot run: no JVM in this image; this is the C++ oracle port"}
+        print(json.dumps(line))
+        return
+
+    import torch
+    device = local_rank
+    torch.cuda.set_device(device)
+    dist = {"rank": rank, "world": world}
+    if world > 1:
+        import torch.distributed as td
+        td.init_process_group("nccl", device_id=torch.device("cuda", device))
+    info, dp, op = run_device_steps(args, wl, device, dist)
+    ms_per_step = info["dev_ms"] / args.steps
+    if world > 1:
+        import torch.distributed as td
+        t = torch.tensor([ms_per_step], device="cuda", dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        ms_per_step = float(t.item())
+    value = args.rows * world / (ms_per_step / 1000.0)
+    peak, peak_src = measured_peak()
+    kern_rows = args.rows * info["kern_steps"]
+    achieved = kern_rows * wl["bytes_per_row"] / (info["kern_ms"] / 1000.0) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "kernel": "pgpu_k_page (fused scan+filter+project+hash-aggregate)", "peak_source": peak_src,
+                "launches_timed": info["kern_launches"], "algorithmic_bytes_per_row": wl["bytes_per_row"]}
+    e2e = None
+    if not args.no_e2e and world == 1:
+        e = run_e2e_steps(args, wl, device, dp, steps=max(2, min(args.steps, 5)), warmup=1)
+        e2e = {"value": e["rows"] * e["steps"] / e["seconds"], "unit": "rows/s", "h2d_bytes_per_step": e["h2d_bytes_per_step"],
+               "d2h_bytes_per_step": e["d2h_bytes_per_step"], "rows_per_step": e["rows"], "steps": e["steps"],
+               "gb_per_s": e["h2d_bytes_per_step"] * e["steps"] / e["seconds"] / 1e9}
+    op.close()
+    dp.free()
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        v, total, _ = cpu_run(wl, args.cpu_rows_per_core, cores)
+        cpu = {"value": v, "unit": "rows/s", "cores": cores, "kind": "port",
+               "sample": "%d rows (%d per core) of the same synthetic lineitem, 1 M-row pages, partial per thread + final merge" % (total, args.cpu_rows_per_core)}
+    if rank == 0:
+        line = {"metric": metric, "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": config, "gb_per_s": value * wl["bytes_per_row"] / 1e9,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": info["launches"], "clocks": info["clocks"],
+                "table_capacity_slots": info["table_capacity"]}
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as td
+        td.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
+
+
+

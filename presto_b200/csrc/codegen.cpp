@@ -1209,6 +1209,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, TableArgs t, Scratch sc) { body_agg_hash<P>(a, t, sc); }\n";
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots) { body_materialize<P>(t, out, sc, first_slot, nslots); }\n";
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_rehash(TableArgs from, TableArgs to, Scratch sc) { body_rehash<P>(from, to, sc); }\n";
+        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";
     }
     res.source = src.str();
     return res;

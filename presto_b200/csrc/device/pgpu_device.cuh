@@ -64,7 +64,10 @@ struct PageArgs {
 struct TableArgs {
     u64* slots;
     u64 capacity;    // slots
-    u64* counters;   // [0] = groups inserted, [1] = failed inserts
+    u64* counters;   // [0] = groups inserted, [1] = rows deferred because the table reached `limit`
+    u64 limit;       // new groups are only claimed while counters[0] < limit (load-factor guard)
+    u64* faillog;    // chunk-relative indices of deferred rows; replayed by k_replay after the host grew the table
+    u64 faillog_cap;
 };
 
 // Per-pipeline device scratch shared by all kernels.
@@ -361,7 +364,7 @@ PGPU_DEV void st_release_u64(u64* p, u64 v) { asm volatile("st.release.gpu.globa
 // Find the slot of `key` or claim an empty one (BigintGroupByHash.putIfAbsent :213-244, linear probing).
 // Returns the slot base pointer, or nullptr when the probe chain is exhausted.
 template <int KW, int SLOTW>
-PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h) {
+PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool force) {
     u64 pos = __umul64hi(h, t.capacity);
     const u64 tagv = TAG_FULL | (h << 8);
     for (u64 probes = 0; probes < t.capacity; probes++) {
@@ -369,6 +372,7 @@ PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1]
         for (;;) {
             u64 tag = ld_acquire_u64(s);
             if (tag == TAG_EMPTY) {
+                if (!force && ld_volatile_u64(t.counters) >= t.limit) return nullptr;  // full enough: defer this row
                 u64 old = atomicCAS(s, TAG_EMPTY, TAG_LOCKED);
                 if (old == TAG_EMPTY) {
 #pragma unroll
@@ -391,15 +395,25 @@ PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1]
         pos++;
         if (pos == t.capacity) pos = 0;
     }
-    atomicAdd(t.counters + 1, 1ull);
     return nullptr;
 }
 
+// Update the group of `key` with the contributions `cw`. Returns false when the row has to be deferred.
 template <class P>
-PGPU_DEV void table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::KW : 1], const u64 (&cw)[P::NW > 0 ? P::NW : 1], u32& err) {
-    u64* s = table_upsert<P::KW, P::SLOTW>(t, key, hash_key<P::KW>(key));
-    if (!s) { err |= PGPU_ERR_TABLE_FULL; return; }
+PGPU_DEV bool table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::KW : 1], const u64 (&cw)[P::NW > 0 ? P::NW : 1], bool force) {
+    u64* s = table_upsert<P::KW, P::SLOTW>(t, key, hash_key<P::KW>(key), force);
+    if (!s) return false;
     P::atomic_cells(s + 1 + P::KW, cw);
+    return true;
+}
+
+// Defer rows [row, row + nrows): they are re-evaluated by k_replay once the host has grown the table.
+PGPU_DEV void defer_rows(const TableArgs& t, i64 row, int nrows, u32& err) {
+    u64 at = atomicAdd(t.counters + 1, (u64)nrows);
+    for (int k = 0; k < nrows; k++) {
+        if (at + k < t.faillog_cap) t.faillog[at + k] = (u64)(row + k);
+        else err |= PGPU_ERR_TABLE_FULL;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ global aggregation
@@ -531,7 +545,9 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
         u64 key[4][KW];
         u64 cw[4][NWA];
         P::eval(a, base, a.rows, sel, key, cw, err);
-        // fold the thread's consecutive rows with equal keys (l_orderkey-style runs) into the first of the run
+        // fold the thread's consecutive rows with equal keys (l_orderkey-style runs) into the first of the run;
+        // span[r] = rows folded into r (needed to defer the whole run if the table is full)
+        int span[4] = {1, 1, 1, 1};
 #pragma unroll
         for (int r = 3; r >= 1; r--) {
             bool same = sel[r] && sel[r - 1];
@@ -539,6 +555,7 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
             for (int i = 0; i < KW; i++) same &= (key[r][i] == key[r - 1][i]);
             if (same) {
                 P::combine(cw[r - 1], cw[r]);
+                span[r - 1] += span[r];
                 sel[r] = false;
             }
         }
@@ -568,10 +585,10 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
                         P::warp_reduce_cells(v);
                         if (lane == leader) P::combine_ptr(myacc + (size_t)ls * NWA, v);
                     }
-                    if (sel[r] && slot < 0) table_update<P>(t, key[r], cw[r], err);
+                    if (sel[r] && slot < 0 && !table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, span[r], err);
                 } else {
                     // many distinct groups in this warp: fire-and-forget atomics on the HBM table
-                    if (sel[r]) table_update<P>(t, key[r], cw[r], err);
+                    if (sel[r] && !table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, span[r], err);
                     misses += 32;
                 }
                 __syncwarp();
@@ -582,7 +599,7 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
         } else {
 #pragma unroll
             for (int r = 0; r < 4; r++)
-                if (sel[r]) table_update<P>(t, key[r], cw[r], err);
+                if (sel[r] && !table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, span[r], err);
         }
     }
     if (P::USE_DIR) {
@@ -596,8 +613,28 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
             u64 key[KW];
 #pragma unroll
             for (int i = 0; i < KW; i++) key[i] = dkeys[s * KW + i];
-            table_update<P>(t, key, tot, err);
+            // the host keeps gridDim * DLIMIT slots in reserve below the load-factor limit for this flush
+            if (!table_update<P>(t, key, tot, true)) err |= PGPU_ERR_TABLE_FULL;
         }
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
+// Re-run deferred rows (one row per thread) against the grown table.
+template <class P>
+PGPU_DEV void body_replay(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc, const u64* rows, u64 n) {
+    constexpr int NWA = P::NW > 0 ? P::NW : 1;
+    u32 err = 0;
+    for (u64 k = (u64)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (u64)gridDim.x * blockDim.x) {
+        i64 row = (i64)rows[k];
+        i64 base = row & ~3ll;
+        bool sel[4];
+        u64 key[4][P::KW > 0 ? P::KW : 1];
+        u64 cw[4][NWA];
+        u32 ignored = 0;  // arithmetic errors of this tile were already reported by the first pass
+        P::eval(a, base, a.rows, sel, key, cw, ignored);
+        int r = (int)(row & 3);
+        if (sel[r] && !table_update<P>(t, key[r], cw[r], true)) err |= PGPU_ERR_TABLE_FULL;
     }
     if (err) atomicOr(sc.err, err);
 }
@@ -723,7 +760,7 @@ PGPU_DEV void body_rehash(const TableArgs& from, const TableArgs& to, const Scra
         u64 key[P::KW > 0 ? P::KW : 1];
 #pragma unroll
         for (int i = 0; i < P::KW; i++) key[i] = slot[1 + i];
-        u64* d = table_upsert<P::KW, P::SLOTW>(to, key, hash_key<P::KW>(key));
+        u64* d = table_upsert<P::KW, P::SLOTW>(to, key, hash_key<P::KW>(key), true);
         if (!d) { err |= PGPU_ERR_TABLE_FULL; continue; }
 #pragma unroll
         for (int w = 0; w < P::NW; w++) d[1 + P::KW + w] = slot[1 + P::KW + w];  // keys are distinct: plain stores

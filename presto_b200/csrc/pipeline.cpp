@@ -40,6 +40,9 @@ struct TableArgs {
     uint64_t* slots;
     uint64_t capacity;
     uint64_t* counters;
+    uint64_t limit;
+    uint64_t* faillog;
+    uint64_t faillog_cap;
 };
 struct Scratch {
     uint32_t* err;
@@ -56,7 +59,7 @@ struct OutCol {
 
 constexpr int kThreads = 256;
 constexpr int64_t kTileRows = kThreads * 4;
-constexpr int64_t kHashChunkRows = 32ll << 20;  // rows per launch while the HBM table may still have to grow
+constexpr int64_t kHashChunkRows = 64ll << 20;  // rows per launch of the hash-aggregation kernel (bounds the deferred-row log)
 constexpr int64_t kHostChunkRows = 8ll << 20;   // rows per staged H2D chunk
 
 thread_local std::string g_lastGlobalError;
@@ -64,7 +67,7 @@ thread_local std::string g_lastGlobalError;
 struct Variant {
     GenResult gen;
     cudaLibrary_t lib = nullptr;
-    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr;
+    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr;
     int blocksPerSM = 1;
 };
 
@@ -117,6 +120,7 @@ struct pgpu_pipeline {
     uint64_t* dPartials = nullptr;
     size_t partialsCap = 0;
     DeviceBuf tileStatus;
+    DeviceBuf failLog;   // deferred rows of the current hash-aggregation chunk
     uint64_t* hostScalars = nullptr;  // pinned: [0] out_count, [1..2] counters, [3] err
 
     // table
@@ -212,7 +216,10 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
             CU(cudaLibraryLoadData(&v.lib, jr.cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0));
             CU(cudaLibraryGetKernel(&v.kPage, v.lib, "pgpu_k_page"));
             if (v.gen.mode != KernelMode::COMPACT) CU(cudaLibraryGetKernel(&v.kEmit, v.lib, "pgpu_k_emit"));
-            if (v.gen.mode == KernelMode::AGG_HASH) CU(cudaLibraryGetKernel(&v.kRehash, v.lib, "pgpu_k_rehash"));
+            if (v.gen.mode == KernelMode::AGG_HASH) {
+                CU(cudaLibraryGetKernel(&v.kRehash, v.lib, "pgpu_k_rehash"));
+                CU(cudaLibraryGetKernel(&v.kReplay, v.lib, "pgpu_k_replay"));
+            }
             int nb = 0;
             cudaError_t oe = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v.kPage, kThreads, (size_t)v.gen.smemBytes);
             if (oe != cudaSuccess || nb < 1) {
@@ -245,6 +252,9 @@ TableArgs tableOf(pgpu_pipeline* p) {
     t.slots = p->dSlots;
     t.capacity = p->capacity;
     t.counters = p->dCounters;
+    t.limit = ~0ull;  // no load-factor guard unless the caller sets one
+    t.faillog = (uint64_t*)p->failLog.ptr;
+    t.faillog_cap = 0;
     return t;
 }
 
@@ -304,11 +314,12 @@ pgpu_status growTable(pgpu_pipeline* p, Variant* v, uint64_t newCap) {
     uint64_t* fresh = nullptr;
     pgpu_status st = allocTable(p, newCap, &fresh);
     if (st) return st;
+    if (p->dSlots) CU(cudaMemsetAsync(p->dCounters, 0, 16, p->stream));  // groups are re-counted, deferred rows cleared
     if (p->dSlots && p->groupsKnown > 0) {
         TableArgs from = tableOf(p);
-        TableArgs to{fresh, newCap, p->dCounters};
-        // rehash re-counts groups: zero the counter first
-        CU(cudaMemsetAsync(p->dCounters, 0, 16, p->stream));
+        TableArgs to = from;
+        to.slots = fresh;
+        to.capacity = newCap;
         Scratch sc = scratchOf(p);
         void* args[] = {&from, &to, &sc};
         int grid = (int)std::min<uint64_t>((from.capacity + kThreads - 1) / kThreads, (uint64_t)p->numSMs * 8);
@@ -326,19 +337,10 @@ pgpu_status growTable(pgpu_pipeline* p, Variant* v, uint64_t newCap) {
     return PGPU_OK;
 }
 
-// make sure `rows` more rows cannot overfill the table (load factor <= 0.75 even if every row is a new group)
-pgpu_status reserveGroups(pgpu_pipeline* p, Variant* v, int64_t rows) {
-    auto fits = [&](int64_t groups) { return (double)(groups + rows) <= 0.75 * (double)p->capacity; };
-    if (p->dSlots && fits(p->groupsKnown + p->rowsSinceKnown)) return PGPU_OK;
-    if (p->dSlots) {
-        pgpu_status st = refreshGroupCount(p);
-        if (st) return st;
-        if (fits(p->groupsKnown)) return PGPU_OK;
-    }
-    uint64_t need = (uint64_t)((double)(p->groupsKnown + rows) / 0.6) + 1024;
-    uint64_t hint = (uint64_t)((double)p->plan->expectedGroups / 0.6) + 1024;
-    uint64_t cap = std::max<uint64_t>({need, hint, p->capacity * 2});
-    return growTable(p, v, cap);
+// slots kept free below the load-factor limit for the end-of-kernel directory flush of every resident block
+uint64_t flushReserve(pgpu_pipeline* p, const Variant* v) {
+    if (!v->gen.useDir) return 0;
+    return (uint64_t)p->numSMs * (uint64_t)v->blocksPerSM * (uint64_t)std::max(v->gen.dirCap * 3 / 4, 1);
 }
 
 // ------------------------------------------------------------------------------------------- page processing
@@ -373,9 +375,48 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         return launch(p, v->kPage, grid, kThreads, 0, args);
     }
     if (g.mode == KernelMode::AGG_HASH) {
+        // Table sizing follows BigintGroupByHash (expectedSize / fill ratio, operator/BigintGroupByHash.java:78-101) and
+        // grows on demand (:262-313). A chunk whose rows could push the table past its load-factor limit runs with a
+        // deferred-row log: rows that would need a new slot beyond the limit are logged instead of inserted, the host then
+        // grows the table (rehash) and replays exactly those rows. Nothing is dropped, nothing is over-allocated.
+        const uint64_t reserve = flushReserve(p, v);
+        if (!p->dSlots) {
+            uint64_t cap = (uint64_t)((double)p->plan->expectedGroups / 0.6) + 1024;
+            cap = std::max<uint64_t>(cap, reserve * 4 + 4096);
+            pgpu_status st = growTable(p, v, cap);
+            if (st) return st;
+        }
+        const int64_t n = pg.rows;
+        const uint64_t limit = (uint64_t)(0.75 * (double)p->capacity) - reserve;
+        const bool risky = (uint64_t)(p->groupsKnown + p->rowsSinceKnown + n) > limit;
+        if (risky) {
+            pgpu_status st = ensureDev(p, p->failLog, (size_t)n * 8);
+            if (st) return st;
+        }
         TableArgs t = tableOf(p);
+        t.limit = limit;
+        t.faillog_cap = risky ? (uint64_t)n : 0;
         void* args[] = {pa.data(), &t, &sc};
-        return launch(p, v->kPage, grid, kThreads, (size_t)g.smemBytes, args);
+        pgpu_status st = launch(p, v->kPage, grid, kThreads, (size_t)g.smemBytes, args);
+        if (st) return st;
+        p->rowsSinceKnown += n;
+        if (!risky) return PGPU_OK;
+        st = refreshGroupCount(p);  // synchronises; hostScalars[2] = deferred rows
+        if (st) return st;
+        uint64_t deferred = p->hostScalars[2];
+        if (deferred == 0) return PGPU_OK;
+        if (deferred > (uint64_t)n) return fail(p, PGPU_CUDA_ERROR, "internal: deferred-row log overflow");
+        uint64_t cap = std::max<uint64_t>(p->capacity * 2, (uint64_t)((double)(p->groupsKnown + (int64_t)deferred) / 0.6) + reserve * 4 + 4096);
+        st = growTable(p, v, cap);  // rehash re-counts the groups and clears the deferred counter
+        if (st) return st;
+        TableArgs t2 = tableOf(p);  // limit = none: the grown table holds every deferred row even if all are new groups
+        uint64_t* log = (uint64_t*)p->failLog.ptr;
+        void* rargs[] = {pa.data(), &t2, &sc, &log, &deferred};
+        int rgrid = (int)std::min<uint64_t>((deferred + kThreads - 1) / kThreads, (uint64_t)p->numSMs * 8);
+        st = launch(p, v->kReplay, rgrid, kThreads, 0, rargs);
+        if (st) return st;
+        p->rowsSinceKnown += (int64_t)deferred;
+        return PGPU_OK;
     }
     return fail(p, PGPU_INVALID_STATE, "internal: launchPageKernel in COMPACT mode");
 }
@@ -474,11 +515,6 @@ pgpu_status processDevicePage(pgpu_pipeline* p, Variant* v, const pgpu_column* c
     int64_t chunk = g.mode == KernelMode::AGG_HASH ? kHashChunkRows : rows;
     for (int64_t r0 = 0; r0 < rows; r0 += chunk) {
         int64_t n = std::min(chunk, rows - r0);
-        if (g.mode == KernelMode::AGG_HASH) {
-            pgpu_status st = reserveGroups(p, v, n);
-            if (st) return st;
-            p->rowsSinceKnown += n;
-        }
         DevPage pg;
         pg.rows = n;
         colArgsFor(r0, pg.cols);
@@ -661,11 +697,6 @@ pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
         if (compact) {
             st = runCompact(p, v, pg);
         } else {
-            if (v->gen.mode == KernelMode::AGG_HASH) {
-                st = reserveGroups(p, v, n);
-                if (st) return st;
-                p->rowsSinceKnown += n;
-            }
             st = launchPageKernel(p, v, pg);
         }
         if (st) return st;
@@ -843,6 +874,7 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
         if (p->dErr) cudaFree(p->dErr);
         if (p->dPartials) cudaFree(p->dPartials);
         if (p->tileStatus.ptr) cudaFree(p->tileStatus.ptr);
+        if (p->failLog.ptr) cudaFree(p->failLog.ptr);
         if (p->dSlots) cudaFree(p->dSlots);
         if (p->hostScalars) cudaFreeHost(p->hostScalars);
         for (auto& s : p->slots) {
