@@ -158,6 +158,8 @@ struct Gen {
                 line("if (full) { i32 t4[4]; load_tile4<i32>(a.c[" + C + "].offsets, base, nrows, true, t4); o" + C + "[0] = t4[0]; o" + C + "[1] = t4[1]; o" + C +
                      "[2] = t4[2]; o" + C + "[3] = t4[3]; o" + C + "[4] = a.c[" + C + "].offsets[base + 4]; }");
                 line("else { for (int q = 0; q < 5; q++) { i64 ix = base + q < nrows ? base + q : nrows; o" + C + "[q] = a.c[" + C + "].offsets[ix]; } }");
+                if (t.kind == TypeKind::VARCHAR && t.precision <= 4)  // the 4 rows' payload is one window of <= 16 bytes
+                    line("u64 wl" + C + ", wh" + C + "; load_byte_window((const u8*)a.c[" + C + "].values, o" + C + "[0], o" + C + "[4] - o" + C + "[0], wl" + C + ", wh" + C + ", err);");
             } else {
                 std::string st = stype(t);
                 line(st + " c" + C + "[4]; load_tile4<" + st + ">((const " + st + "*)a.c[" + C + "].values, base, nrows, full, c" + C + ");");
@@ -181,7 +183,9 @@ struct Gen {
             if (cs.encoding == PGPU_ENC_PLAIN) {
                 if (t.isVarWidth()) {
                     int n = t.kind == TypeKind::VARCHAR ? t.precision : 0;
-                    if (t.kind == TypeKind::VARCHAR) {
+                    if (t.kind == TypeKind::VARCHAR && n <= 4) {
+                        line("u64 x" + C + ", y" + C + " = 0; window_varchar<" + std::to_string(n) + ">(wl" + C + ", wh" + C + ", o" + C + "[r] - o" + C + "[0], o" + C + "[r + 1] - o" + C + "[r], x" + C + ", err);");
+                    } else if (t.kind == TypeKind::VARCHAR) {
                         line("u64 x" + C + ", y" + C + "; pack_varchar<" + std::to_string(n) + ">((const u8*)a.c[" + C + "].values, o" + C + "[r], o" + C + "[r + 1] - o" + C + "[r], x" + C + ", y" + C + ", err);");
                     } else {
                         line("const u8* x" + C + " = (const u8*)a.c[" + C + "].values + o" + C + "[r];");
@@ -964,13 +968,32 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         }
         aggCells.push_back(ac);
     }
-    for (auto& c : cells)
-        for (int j = 0; j < c.nwords; j++) g.line("cw[r][" + std::to_string(c.word + j) + "] = " + c.contrib[j] + ";");
-    std::string rowBody = g.out.str();
-
     res.NW = nw;
     for (auto& c : cells)
         for (int j = 0; j < c.nwords; j++) res.cellKinds.push_back(c.kind == "sumd" ? 1 : (c.kind == "max" || c.kind == "min") ? 2 : c.kind == "cnt" ? 3 : 0);
+    // hot words: cells with the same kind and the same per-row contribution expression share one word in the scan loop
+    std::vector<int> hotOf((size_t)nw, 0), hotKinds;
+    {
+        std::map<std::string, int> hotIndex;
+        for (auto& c : cells) {
+            for (int j = 0; j < c.nwords; j++) {
+                int w = c.word + j;
+                std::string k = std::to_string(res.cellKinds[w]) + "|" + c.contrib[j];
+                auto it = hotIndex.find(k);
+                if (it == hotIndex.end()) {
+                    int h = (int)hotKinds.size();
+                    hotIndex[k] = h;
+                    hotKinds.push_back(res.cellKinds[w]);
+                    g.line("cw[r][" + std::to_string(h) + "] = " + c.contrib[j] + ";");
+                    hotOf[w] = h;
+                } else {
+                    hotOf[w] = it->second;
+                }
+            }
+        }
+    }
+    std::string rowBody = g.out.str();
+    const int NH = (int)hotKinds.size(), NHA = std::max(NH, 1);
     const int NW = res.NW, KW = res.KW;
     const int NWA = std::max(NW, 1), KWA = std::max(KW, 1);
     res.SLOTW = ((1 + KW + NW) + 3) / 4 * 4;
@@ -980,9 +1003,9 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     res.dirCap = 0;
     if (res.useDir) {
         int cap = 128;
-        while (cap > 16 && (8 * cap * NWA * 8 + cap * KW * 8 + cap * 4 + 16) > 40 * 1024) cap /= 2;
+        while (cap > 16 && (8 * cap * NHA * 8 + cap * KW * 8 + cap * 4 + 16) > 40 * 1024) cap /= 2;
         res.dirCap = cap;
-        res.smemBytes = 8 * cap * NWA * 8 + cap * KW * 8 + cap * 4 + 16;
+        res.smemBytes = 8 * cap * NHA * 8 + cap * KW * 8 + cap * 4 + 16;
     }
 
     // ---- outputs
@@ -1006,33 +1029,37 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
 
     src << "struct P {\n";
     src << "    static constexpr int NC = " << res.NC << ", NO = " << res.NO << ", KW = " << KW << ", NW = " << NW << ", SLOTW = " << res.SLOTW << ";\n";
-    src << "    static constexpr int KWA = " << KWA << ", NWA = " << NWA << ";\n";
+    src << "    static constexpr int KWA = " << KWA << ", NWA = " << NWA << ", NH = " << NH << ", NHA = " << NHA << ";\n";
     src << "    static constexpr bool USE_DIR = " << (res.useDir ? "true" : "false") << ";\n";
-    src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 4;\n";
+    src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 8;\n";
     auto kindName = [&](int k) { return k == 0 ? "CK_ADD_U64" : k == 1 ? "CK_ADD_F64" : k == 2 ? "CK_MAX_U64" : "CK_CNT"; };
-    src << "    PGPU_DEV static void identity(u64 (&a)[NWA]) {\n";
-    for (int w = 0; w < NWA; w++) src << "        a[" << w << "] = 0ull;\n";
+    src << "    PGPU_DEV static void identity(u64 (&a)[NHA]) {\n";
+    for (int w = 0; w < NHA; w++) src << "        a[" << w << "] = 0ull;\n";
     src << "    }\n";
     src << "    PGPU_DEV static void identity_ptr(u64* a) {\n";
-    for (int w = 0; w < NW; w++) src << "        a[" << w << "] = 0ull;\n";
+    for (int w = 0; w < NH; w++) src << "        a[" << w << "] = 0ull;\n";
     src << "    }\n";
     auto emitCombine = [&](const char* name, const char* sigA, const char* sigB) {
         src << "    PGPU_DEV static void " << name << "(" << sigA << ", " << sigB << ") {\n";
-        for (int w = 0; w < NW; w++) src << "        a[" << w << "] = cell_combine<" << kindName(res.cellKinds[w]) << ">(a[" << w << "], b[" << w << "]);\n";
+        for (int w = 0; w < NH; w++) src << "        a[" << w << "] = cell_combine<" << kindName(hotKinds[w]) << ">(a[" << w << "], b[" << w << "]);\n";
         src << "    }\n";
     };
-    emitCombine("combine", "u64 (&a)[NWA]", "const u64 (&b)[NWA]");
-    emitCombine("combine_ptr", "u64* a", "const u64 (&b)[NWA]");
-    emitCombine("combine_ptr_to", "u64 (&a)[NWA]", "const u64* b");
-    src << "    PGPU_DEV static void warp_reduce_cells(u64 (&a)[NWA]) {\n";
-    for (int w = 0; w < NW; w++) src << "        a[" << w << "] = warp_reduce<" << kindName(res.cellKinds[w]) << ">(a[" << w << "]);\n";
+    emitCombine("combine", "u64 (&a)[NHA]", "const u64 (&b)[NHA]");
+    emitCombine("combine_ptr", "u64* a", "const u64 (&b)[NHA]");
+    emitCombine("combine_ptr_to", "u64 (&a)[NHA]", "const u64* b");
+    src << "    PGPU_DEV static void warp_reduce_cells(u64 (&a)[NHA]) {\n";
+    for (int w = 0; w < NH; w++) src << "        a[" << w << "] = warp_reduce<" << kindName(hotKinds[w]) << ">(a[" << w << "]);\n";
     src << "    }\n";
-    src << "    PGPU_DEV static void atomic_cells(u64* cells, const u64 (&cw)[NWA]) {\n";
-    for (int w = 0; w < NW; w++) src << "        cell_atomic<" << kindName(res.cellKinds[w]) << ">(cells + " << w << ", cw[" << w << "]);\n";
+    // hot -> cells expansion: atomically into a table slot, or plainly into the global-aggregation state
+    src << "    PGPU_DEV static void atomic_cells(u64* cells, const u64 (&hot)[NHA]) {\n";
+    for (int w = 0; w < NW; w++) src << "        cell_atomic<" << kindName(res.cellKinds[w]) << ">(cells + " << w << ", hot[" << hotOf[w] << "]);\n";
+    src << "    }\n";
+    src << "    PGPU_DEV static void merge_cells(u64* cells, const u64 (&hot)[NHA]) {\n";
+    for (int w = 0; w < NW; w++) src << "        cells[" << w << "] = cell_combine<" << kindName(res.cellKinds[w]) << ">(cells[" << w << "], hot[" << hotOf[w] << "]);\n";
     src << "    }\n";
 
     // ---- eval
-    src << "    PGPU_DEV static void eval(const PageArgs<NC>& a, i64 base, i64 nrows, bool (&sel)[4], u64 (&key)[4][KWA], u64 (&cw)[4][NWA], u32& err) {\n";
+    src << "    PGPU_DEV static void eval(const PageArgs<NC>& a, i64 base, i64 nrows, bool (&sel)[4], u64 (&key)[4][KWA], u64 (&cw)[4][NHA], u32& err) {\n";
     src << evalFilter.str();
     src << "        #pragma unroll\n";
     src << "        for (int r = 0; r < 4; r++) {\n";

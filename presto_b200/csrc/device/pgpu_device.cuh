@@ -290,6 +290,35 @@ PGPU_DEV void pack_varchar(const u8* __restrict__ bytes, i32 off, i32 len, u64& 
     }
 }
 
+// The <= 16 bytes [start, start + nbytes) of a byte slice as 128 bits (little endian), fetched with aligned 32-bit
+// loads: the var-width payload of a thread's 4 consecutive short rows is one contiguous window of the slice.
+PGPU_DEV void load_byte_window(const u8* __restrict__ bytes, i32 start, i32 nbytes, u64& lo, u64& hi, u32& err) {
+    lo = 0; hi = 0;
+    if (nbytes <= 0) return;
+    if (nbytes > 16) { err |= PGPU_ERR_VARCHAR_LEN; nbytes = 16; }
+    const u32* wp = reinterpret_cast<const u32*>(bytes + (start & ~3));
+    const u32 sh = (u32)(start & 3) * 8u;
+    const int nwords = ((start & 3) + nbytes + 3) >> 2;  // 1..5
+    u32 w[5];
+#pragma unroll
+    for (int k = 0; k < 5; k++) w[k] = k < nwords ? __ldg(wp + k) : 0u;
+    u32 o0 = __funnelshift_r(w[0], w[1], sh), o1 = __funnelshift_r(w[1], w[2], sh);
+    u32 o2 = __funnelshift_r(w[2], w[3], sh), o3 = __funnelshift_r(w[3], w[4], sh);
+    lo = ((u64)o1 << 32) | o0;
+    hi = ((u64)o3 << 32) | o2;
+}
+// Row value out of a window: bytes [rel, rel + len) -> packed cell (byte 0 = length, bytes 1.. = data), N <= 4
+template <int N>
+PGPU_DEV void window_varchar(u64 wlo, u64 whi, i32 rel, i32 len, u64& x, u32& err) {
+    if (len > N) { err |= PGPU_ERR_VARCHAR_LEN; len = N; }
+    if (len < 0) len = 0;
+    u64 d;
+    if (rel < 8) d = (wlo >> (8 * rel)) | (rel ? (whi << (64 - 8 * rel)) : 0ull);
+    else d = whi >> (8 * (rel - 8));
+    d &= (len >= 8) ? ~0ull : ((1ull << (8 * len)) - 1ull);
+    x = (u64)(u32)len | (d << 8);
+}
+
 // ------------------------------------------------------------------------------------------------ hashing / warp ops
 PGPU_DEV u64 mix64(u64 x) {  // splitmix64 finaliser; table placement only, never observable
     x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
@@ -367,6 +396,7 @@ template <int KW, int SLOTW>
 PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool force) {
     u64 pos = __umul64hi(h, t.capacity);
     const u64 tagv = TAG_FULL | (h << 8);
+#pragma unroll 1
     for (u64 probes = 0; probes < t.capacity; probes++) {
         u64* s = t.slots + pos * SLOTW;
         for (;;) {
@@ -398,12 +428,17 @@ PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1]
     return nullptr;
 }
 
-// Update the group of `key` with the contributions `cw`. Returns false when the row has to be deferred.
+// Accumulator words come in two layouts. CELLS (P::NW words) is the persistent layout of a table slot / the global
+// state; it never depends on which pages carry null vectors. HOT (P::NH words) is what the scan loop carries: cells
+// whose per-row contribution is the same expression (e.g. every count when no input is NULL) share one hot word and are
+// expanded back to cells only when a partial result is merged into a slot (P::atomic_cells / P::merge_cells).
+
+// Update the group of `key` with the hot contributions `hot`. Returns false when the row has to be deferred.
 template <class P>
-PGPU_DEV bool table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::KW : 1], const u64 (&cw)[P::NW > 0 ? P::NW : 1], bool force) {
+PGPU_DEV bool table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::KW : 1], const u64 (&hot)[P::NHA], bool force) {
     u64* s = table_upsert<P::KW, P::SLOTW>(t, key, hash_key<P::KW>(key), force);
     if (!s) return false;
-    P::atomic_cells(s + 1 + P::KW, cw);
+    P::atomic_cells(s + 1 + P::KW, hot);
     return true;
 }
 
@@ -418,13 +453,12 @@ PGPU_DEV void defer_rows(const TableArgs& t, i64 row, int nrows, u32& err) {
 
 // ------------------------------------------------------------------------------------------------ global aggregation
 // One accumulator slot (no GROUP BY). Every thread reduces its rows in registers, blocks reduce through warp
-// shuffles + shared memory into partials[block][NW]; the last block to finish (ticket) folds the block partials
+// shuffles + shared memory into partials[block][NH]; the last block to finish (ticket) folds the block partials
 // in block order into the persistent state, so results are deterministic run to run.
 template <class P>
 PGPU_DEV void body_agg_global(const PageArgs<P::NC>& a, const Scratch& sc) {
-    constexpr int NW = P::NW;
-    constexpr int NWA = NW > 0 ? NW : 1;
-    u64 acc[NWA];
+    constexpr int NH = P::NH, NHA = P::NHA;
+    u64 acc[NHA];
     P::identity(acc);
     u32 err = 0;
     const i64 tile_rows = (i64)blockDim.x * 4;
@@ -433,29 +467,28 @@ PGPU_DEV void body_agg_global(const PageArgs<P::NC>& a, const Scratch& sc) {
         i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
         bool sel[4];
         u64 key[4][1];
-        u64 cw[4][NWA];
+        u64 cw[4][NHA];
         P::eval(a, base, a.rows, sel, key, cw, err);
 #pragma unroll
         for (int r = 0; r < 4; r++)
             if (sel[r]) P::combine(acc, cw[r]);
     }
-    // block reduction
-    __shared__ u64 sm[32][NWA];
+    __shared__ u64 sm[32][NHA];
     P::warp_reduce_cells(acc);
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
     if (lane == 0) {
 #pragma unroll
-        for (int w = 0; w < NW; w++) sm[warp][w] = acc[w];
+        for (int w = 0; w < NH; w++) sm[warp][w] = acc[w];
     }
     if (err) atomicOr(sc.err, err);
     __syncthreads();
     __shared__ bool is_last;
     if (threadIdx.x == 0) {
-        u64 tot[NWA];
+        u64 tot[NHA];
         P::identity(tot);
         for (int k = 0; k < nwarps; k++) P::combine(tot, sm[k]);
 #pragma unroll
-        for (int w = 0; w < NW; w++) sc.partials[(u64)blockIdx.x * NWA + w] = tot[w];
+        for (int w = 0; w < NH; w++) sc.partials[(u64)blockIdx.x * NHA + w] = tot[w];
         __threadfence();
         u32 t = atomicAdd(sc.ticket, 1u);
         is_last = (t == gridDim.x - 1);
@@ -463,17 +496,15 @@ PGPU_DEV void body_agg_global(const PageArgs<P::NC>& a, const Scratch& sc) {
     __syncthreads();
     if (is_last && threadIdx.x == 0) {
         __threadfence();
-        u64 tot[NWA];
-#pragma unroll
-        for (int w = 0; w < NW; w++) tot[w] = sc.state[w];
+        u64 tot[NHA];
+        P::identity(tot);
         for (u32 b = 0; b < gridDim.x; b++) {
-            u64 part[NWA];
+            u64 part[NHA];
 #pragma unroll
-            for (int w = 0; w < NW; w++) part[w] = ld_volatile_u64(sc.partials + (u64)b * NWA + w);
+            for (int w = 0; w < NH; w++) part[w] = ld_volatile_u64(sc.partials + (u64)b * NHA + w);
             P::combine(tot, part);
         }
-#pragma unroll
-        for (int w = 0; w < NW; w++) sc.state[w] = tot[w];
+        P::merge_cells(sc.state, tot);
         *sc.ticket = 0;
     }
 }
@@ -487,6 +518,7 @@ PGPU_DEV int dir_lookup(u64* dkeys, u32* dtags, u32* dcount, const u64 (&key)[P:
     constexpr int KW = P::KW, DCAP = P::DCAP;
     u32 pos = (u32)(h >> 40) % DCAP;
     const u32 tagv = 2u | ((u32)h << 8);
+#pragma unroll 1
     for (int probes = 0; probes < DCAP; probes++) {
         for (;;) {
             u32 tag = *((volatile u32*)&dtags[pos]);
@@ -519,17 +551,16 @@ PGPU_DEV int dir_lookup(u64* dkeys, u32* dtags, u32* dcount, const u64 (&key)[P:
 
 template <class P>
 PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc) {
-    constexpr int KW = P::KW, NW = P::NW, DCAP = P::DCAP, NWARP = P::NWARP;
-    constexpr int NWA = NW > 0 ? NW : 1;
+    constexpr int KW = P::KW, NH = P::NH, NHA = P::NHA, DCAP = P::DCAP, NWARP = P::NWARP;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    // layout: wacc[NWARP][DCAP][NWA] u64 | dkeys[DCAP][KW] u64 | dtags[DCAP] u32 | dcount u32
+    // layout: wacc[NWARP][DCAP][NHA] u64 | dkeys[DCAP][KW] u64 | dtags[DCAP] u32 | dcount u32
     u64* wacc = reinterpret_cast<u64*>(smem_raw);
-    u64* dkeys = wacc + (P::USE_DIR ? NWARP * DCAP * NWA : 0);
+    u64* dkeys = wacc + (P::USE_DIR ? NWARP * DCAP * NHA : 0);
     u32* dtags = reinterpret_cast<u32*>(dkeys + (P::USE_DIR ? DCAP * KW : 0));
     u32* dcount = dtags + (P::USE_DIR ? DCAP : 0);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (P::USE_DIR) {
-        for (int i = threadIdx.x; i < NWARP * DCAP; i += blockDim.x) P::identity_ptr(wacc + (size_t)i * NWA);
+        for (int i = threadIdx.x; i < NWARP * DCAP; i += blockDim.x) P::identity_ptr(wacc + (size_t)i * NHA);
         for (int i = threadIdx.x; i < DCAP; i += blockDim.x) dtags[i] = 0u;
         if (threadIdx.x == 0) *dcount = 0u;
         __syncthreads();
@@ -537,66 +568,83 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
     u32 err = 0;
     const i64 tile_rows = (i64)blockDim.x * 4;
     const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
-    u64* myacc = wacc + (size_t)warp * DCAP * NWA;
+    u64* myacc = wacc + (size_t)warp * DCAP * NHA;
     bool use_dir = P::USE_DIR;  // warp-uniform
     for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
         bool sel[4];
         u64 key[4][KW];
-        u64 cw[4][NWA];
+        u64 cw[4][NHA];
         P::eval(a, base, a.rows, sel, key, cw, err);
-        // fold the thread's consecutive rows with equal keys (l_orderkey-style runs) into the first of the run;
-        // span[r] = rows folded into r (needed to defer the whole run if the table is full)
-        int span[4] = {1, 1, 1, 1};
-#pragma unroll
-        for (int r = 3; r >= 1; r--) {
-            bool same = sel[r] && sel[r - 1];
-#pragma unroll
-            for (int i = 0; i < KW; i++) same &= (key[r][i] == key[r - 1][i]);
-            if (same) {
-                P::combine(cw[r - 1], cw[r]);
-                span[r - 1] += span[r];
-                sel[r] = false;
-            }
-        }
         if (P::USE_DIR && use_dir) {
-            int hits = 0, misses = 0;
+            // 1. directory slot of every selected row (block-shared keys in shared memory)
+            int slot[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) slot[r] = sel[r] ? dir_lookup<P>(dkeys, dtags, dcount, key[r], hash_key<KW>(key[r])) : -1;
+            // 2. rows whose key is not in the (full) directory go straight to the HBM table
+            int nmiss = 0;
 #pragma unroll
             for (int r = 0; r < 4; r++) {
-                if (!__any_sync(FULLMASK, sel[r])) continue;
-                int slot = -1;
-                if (sel[r]) slot = dir_lookup<P>(dkeys, dtags, dcount, key[r], hash_key<KW>(key[r]));
-                u32 peers = __match_any_sync(FULLMASK, slot);
-                u32 leaders = __ballot_sync(FULLMASK, slot >= 0 && lane == __ffs(peers) - 1);
-                hits += __popc(__ballot_sync(FULLMASK, slot >= 0));
-                misses += __popc(__ballot_sync(FULLMASK, sel[r] && slot < 0));
-                if (__popc(leaders) <= P::MAX_WARP_GROUPS) {
-                    while (leaders) {
-                        int leader = __ffs(leaders) - 1;
-                        leaders &= leaders - 1;
-                        int ls = __shfl_sync(FULLMASK, slot, leader);
-                        u64 v[NWA];
-                        if (slot == ls) {
-#pragma unroll
-                            for (int w = 0; w < NW; w++) v[w] = cw[r][w];
-                        } else {
-                            P::identity(v);
-                        }
-                        P::warp_reduce_cells(v);
-                        if (lane == leader) P::combine_ptr(myacc + (size_t)ls * NWA, v);
-                    }
-                    if (sel[r] && slot < 0 && !table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, span[r], err);
-                } else {
-                    // many distinct groups in this warp: fire-and-forget atomics on the HBM table
-                    if (sel[r] && !table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, span[r], err);
-                    misses += 32;
+                if (sel[r] && slot[r] < 0) {
+                    nmiss++;
+                    if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
                 }
-                __syncwarp();
             }
+            // 3. one warp reduction per distinct directory slot held by this warp's 128 rows: every lane first adds up its
+            //    own rows of that slot, the elected lane then adds the warp total to the warp-private table (no atomics)
+            __syncwarp();
+            int hits = 0, rounds = 0;
+#pragma unroll 1
+            for (;;) {
+                int cand = slot[0] >= 0 ? slot[0] : slot[1] >= 0 ? slot[1] : slot[2] >= 0 ? slot[2] : slot[3];
+                u32 have = __ballot_sync(FULLMASK, cand >= 0);
+                if (!have) break;
+                if (rounds++ >= P::MAX_WARP_GROUPS) {
+                    // too many distinct groups in one warp for the reduction to pay: fire-and-forget atomics instead
+#pragma unroll
+                    for (int r = 0; r < 4; r++) {
+                        if (slot[r] >= 0) {
+                            if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
+                            nmiss++;
+                        }
+                    }
+                    break;
+                }
+                const int leader = __ffs(have) - 1;
+                const int g = __shfl_sync(FULLMASK, cand, leader);
+                u64 v[NHA];
+                P::identity(v);
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    if (slot[r] == g) {
+                        P::combine(v, cw[r]);
+                        slot[r] = -1;
+                        hits++;
+                    }
+                }
+                P::warp_reduce_cells(v);
+                if (lane == leader) P::combine_ptr(myacc + (size_t)g * NHA, v);
+            }
+            __syncwarp();
             // adaptive bypass: once most rows miss the (full) directory, stop paying for lookups. Bypassing is always
             // correct because the directory accumulators and the HBM table are merged additively at the end.
-            if (misses > 2 * hits) use_dir = false;
+            int wh = __reduce_add_sync(FULLMASK, hits), wm = __reduce_add_sync(FULLMASK, nmiss);
+            if (wm > 2 * wh) use_dir = false;
         } else {
+            // high cardinality: fold the thread's consecutive rows with equal keys (l_orderkey-style runs) into the
+            // first row of the run, then update the HBM table; span = rows folded (to defer the whole run if needed)
+            int span[4] = {1, 1, 1, 1};
+#pragma unroll
+            for (int r = 3; r >= 1; r--) {
+                bool same = sel[r] && sel[r - 1];
+#pragma unroll
+                for (int i = 0; i < KW; i++) same &= (key[r][i] == key[r - 1][i]);
+                if (same) {
+                    P::combine(cw[r - 1], cw[r]);
+                    span[r - 1] += span[r];
+                    sel[r] = false;
+                }
+            }
 #pragma unroll
             for (int r = 0; r < 4; r++)
                 if (sel[r] && !table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, span[r], err);
@@ -607,9 +655,9 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
         // flush: fold the warp-private tables in warp order and push each live directory entry to HBM
         for (int s = threadIdx.x; s < DCAP; s += blockDim.x) {
             if (dtags[s] < 2u) continue;
-            u64 tot[NWA];
+            u64 tot[NHA];
             P::identity(tot);
-            for (int k = 0; k < NWARP; k++) P::combine_ptr_to(tot, wacc + ((size_t)k * DCAP + s) * NWA);
+            for (int k = 0; k < NWARP; k++) P::combine_ptr_to(tot, wacc + ((size_t)k * DCAP + s) * NHA);
             u64 key[KW];
 #pragma unroll
             for (int i = 0; i < KW; i++) key[i] = dkeys[s * KW + i];
@@ -623,14 +671,13 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
 // Re-run deferred rows (one row per thread) against the grown table.
 template <class P>
 PGPU_DEV void body_replay(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc, const u64* rows, u64 n) {
-    constexpr int NWA = P::NW > 0 ? P::NW : 1;
     u32 err = 0;
     for (u64 k = (u64)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (u64)gridDim.x * blockDim.x) {
         i64 row = (i64)rows[k];
         i64 base = row & ~3ll;
         bool sel[4];
         u64 key[4][P::KW > 0 ? P::KW : 1];
-        u64 cw[4][NWA];
+        u64 cw[4][P::NHA];
         u32 ignored = 0;  // arithmetic errors of this tile were already reported by the first pass
         P::eval(a, base, a.rows, sel, key, cw, ignored);
         int r = (int)(row & 3);
