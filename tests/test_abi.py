@@ -1,0 +1,130 @@
+"""The C ABI boundary without a GPU: the library loads, exports every symbol include/prestogpu.h declares, compiles
+plans (device = -1) and rejects everything outside the supported subset at plan time (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from presto_b200 import _native as N
+from presto_b200 import tpch
+from presto_b200.operators import (Aggregation, GpuFilterAndProjectOperator, GpuHashAggregationOperator, GpuOperatorFactory,
+                                   GpuPipelineOperator, TrinoException, plan_text)
+from presto_b200.relational import CallExpression, SpecialForm, call, compare, constant, field
+from presto_b200.spi import BIGINT, BOOLEAN, DOUBLE, VARCHAR, Page, block_of, createDecimalType, createVarcharType
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "prestogpu.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(pgpu_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 30
+    handle = ctypes.CDLL(N.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(handle, name), "libprestogpu.so does not export %s" % name
+    bound = {s[0] for s in N.SYMBOLS}
+    assert declared == bound, "ctypes binding and header disagree: %s" % sorted(declared ^ bound)
+
+
+def test_no_device_means_zero_devices_not_an_error():
+    L = N.lib()
+    assert L.pgpu_device_count() >= 0
+    assert b"sm_100a" in L.pgpu_version()
+
+
+def test_product_never_touches_the_oracle():
+    # the product package must not import, link or execute anything under oracle/
+    pkg = os.path.join(ROOT, "presto_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cpp", ".cu", ".h", ".cuh")):
+                src = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "oracle/" not in src and "liboracle" not in src and "oracle_op" not in src, f
+
+
+def test_compile_only_pipeline_refuses_pages():
+    op = GpuPipelineOperator(tpch.q6_plan(), device=-1)
+    assert "pgpu_k_page" in op.generatedSource()
+    with pytest.raises(TrinoException) as e:
+        op.addInput(tpch.q6_page(0, 10, 10))
+    assert e.value.code == "INVALID_STATE"
+    op.close()
+
+
+def test_canonical_plans_compile_for_every_page_signature():
+    for plan in (tpch.q1_plan(), tpch.q1_plan("partial"), tpch.q6_plan(), tpch.highcard_plan(1000), tpch.highcard_plan(1000, "partial")):
+        op = GpuPipelineOperator(plan, device=-1)
+        n = len(re.search(r"\(input ([^\n]*)\)\n", plan).group(1).replace("(varchar 1)", "v").split())
+        op.compileSignature([1] * n, [True] * n)      # all dictionary blocks with null vectors
+        op.compileSignature([2] * n, [False] * n)     # all RLE
+        assert op.stats().jit_compiles + op.stats().jit_cache_hits >= 3
+        op.close()
+
+
+def test_output_schema():
+    op = GpuPipelineOperator(tpch.q1_plan(), device=-1)
+    kinds = [t.kind for t in op.outputTypes()]
+    assert kinds == [6, 6, 4, 4, 4, 4, 4, 4, 4, 1]
+    op.close()
+    op = GpuPipelineOperator(tpch.q1_plan("partial"), device=-1)
+    # PARTIAL: keys, then per aggregate its intermediate channels (StateCompiler ROW order): sum -> (count, sum), avg -> (sum, count)
+    assert [t.kind for t in op.outputTypes()] == [6, 6] + [1, 4] * 4 + [4, 1] * 3 + [1]
+    op.close()
+    d = createDecimalType(12, 2)
+    op = GpuHashAggregationOperator([BIGINT, d], [0], "single", [Aggregation("sum", createDecimalType(38, 2), 1, d), Aggregation("avg", d, 1, d)], device=-1)
+    t = op.outputTypes()
+    assert (t[1].kind, t[1].precision, t[1].scale) == (5, 38, 2) and (t[2].precision, t[2].scale) == (12, 2)
+    op.close()
+
+
+REJECTED = [
+    ("unbounded varchar key", lambda: plan_text([VARCHAR, BIGINT], step="single", groupByChannels=[0], aggregations=[Aggregation("count", BIGINT)])),
+    ("varchar(64) key", lambda: plan_text([createVarcharType(64), BIGINT], step="single", groupByChannels=[0], aggregations=[Aggregation("count", BIGINT)])),
+    ("unknown special form", lambda: plan_text([BIGINT], SpecialForm("NULL_IF", BOOLEAN, [field(0, BIGINT), constant(1, BIGINT)]), [field(0, BIGINT)])),
+    ("unknown function", lambda: plan_text([DOUBLE], None, [CallExpression("sqrt", DOUBLE, [field(0, DOUBLE)])])),
+    ("unknown aggregate", lambda: plan_text([DOUBLE], step="single", aggregations=[Aggregation("approx_distinct", BIGINT, 0, DOUBLE)])),
+    ("decimal division", lambda: plan_text([createDecimalType(10, 2)], None, [call("divide", createDecimalType(10, 2), field(0, createDecimalType(10, 2)), field(0, createDecimalType(10, 2)))])),
+    ("intermediate step", lambda: plan_text([BIGINT], step="intermediate", aggregations=[Aggregation("count", BIGINT)])),
+]
+
+
+@pytest.mark.parametrize("what,make", REJECTED, ids=[r[0] for r in REJECTED])
+def test_plan_time_rejection(what, make):
+    with pytest.raises(TrinoException) as e:
+        GpuPipelineOperator(make(), device=-1)
+    assert e.value.code in ("NOT_SUPPORTED", "INVALID_ARGUMENT"), e.value
+    assert str(e.value)
+
+
+def test_malformed_plan_is_invalid_argument():
+    for bad in ("", "(plan", "(plan (input bigint) (filter (in 3 bigint)))", "(plan (input bigint) (project (call add bigint (in 0 bigint))))"):
+        with pytest.raises(TrinoException) as e:
+            GpuPipelineOperator(bad, device=-1)
+        assert e.value.code in ("INVALID_ARGUMENT", "NOT_SUPPORTED")
+
+
+def test_operator_factory_contract():
+    # OperatorFactory.java:18-50: createOperator after noMoreOperators is an error; duplicate() gives a fresh factory
+    f = GpuOperatorFactory(0, tpch.q6_plan(), device=-1)
+    op = f.createOperator()
+    assert op.needsInput() and not op.isFinished()
+    op.close()
+    g = f.duplicate()
+    f.noMoreOperators()
+    with pytest.raises(TrinoException):
+        f.createOperator()
+    g.createOperator().close()
+    with pytest.raises(TrinoException):
+        GpuOperatorFactory(1, plan_text([VARCHAR], step="single", groupByChannels=[0], aggregations=[Aggregation("count", BIGINT)]), device=-1)
+
+
+def test_null_arguments_do_not_crash():
+    L = N.lib()
+    assert L.pgpu_pipeline_create(None, 0, -1, None) == N.INVALID_ARGUMENT
+    assert L.pgpu_needs_input(None) == 0
+    assert L.pgpu_is_finished(None) == 0
+    assert L.pgpu_finish(None) == N.INVALID_ARGUMENT
+    L.pgpu_pipeline_destroy(None)
+    assert L.pgpu_output_channel_count(None) == 0
