@@ -13,6 +13,7 @@
 #include "codegen.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <map>
 #include <set>
 #include <sstream>
@@ -136,6 +137,11 @@ struct Gen {
     std::ostringstream out;   // current code sink
     int tmpId = 0;
     int indent = 2;
+    // staged mode: tile loads come from a shared-memory stage `st` (thread's first row = trow) instead of global memory
+    bool stagedLoads = false;
+    int SR = 2;  // rows per thread of the staged variant (the direct variants use 4)
+    struct StageOff { int values = -1, nulls = -1, offsets = -1, vbytes = -1, vbase = -1, vcap = 0; };
+    std::map<int, StageOff> soff;
 
     Gen(const Plan& p, const std::vector<ColSig>& s) : plan(p), sig(s) {}
 
@@ -149,6 +155,28 @@ struct Gen {
             const ColSig& cs = sig[c];
             std::string C = std::to_string(c);
             if (cs.encoding == PGPU_ENC_RLE) continue;  // loaded in the row prologue (uniform)
+            if (stagedLoads) {
+                const StageOff& so = soff[c];
+                auto at = [](int off) { return "st + " + std::to_string(off); };
+                const std::string R = std::to_string(SR);
+                if (cs.encoding == PGPU_ENC_DICTIONARY) {
+                    line("i32 id" + C + "[" + R + "]; lds_tile<i32, " + R + ">(" + at(so.values) + ", trow, id" + C + ");");
+                    continue;
+                }
+                if (t.isVarWidth()) {
+                    line("i32 o" + C + "[" + R + " + 1]; { i32 tq[" + R + "]; lds_tile<i32, " + R + ">(" + at(so.offsets) + ", trow, tq); for (int q = 0; q < " + R + "; q++) o" + C + "[q] = tq[q]; o" + C + "[" + R +
+                         "] = *reinterpret_cast<const i32*>(" + at(so.offsets) + " + (trow + " + R + ") * 4); }");
+                    line("const i32 vb" + C + " = *reinterpret_cast<const i32*>(" + at(so.vbase) + ");");
+                    if (t.kind == TypeKind::VARCHAR && t.precision <= 4)
+                        line("u64 wl" + C + ", wh" + C + "; lds_byte_window<" + std::to_string(SR * t.precision) + ">(" + at(so.vbytes) + ", o" + C + "[0] - vb" + C + ", o" + C + "[" + R + "] - o" + C + "[0], wl" + C + ", wh" +
+                             C + ", err);");
+                } else {
+                    std::string st = stype(t);
+                    line(st + " c" + C + "[" + R + "]; lds_tile<" + st + ", " + R + ">(" + at(so.values) + ", trow, c" + C + ");");
+                }
+                if (cs.nullable) line("u8 n" + C + "[" + R + "]; lds_tile<u8, " + R + ">(" + at(so.nulls) + ", trow, n" + C + ");");
+                continue;
+            }
             if (cs.encoding == PGPU_ENC_DICTIONARY) {
                 line("i32 id" + C + "[4]; load_tile4<i32>(a.c[" + C + "].ids, base, nrows, full, id" + C + ");");
                 continue;
@@ -159,7 +187,7 @@ struct Gen {
                      "[2] = t4[2]; o" + C + "[3] = t4[3]; o" + C + "[4] = a.c[" + C + "].offsets[base + 4]; }");
                 line("else { for (int q = 0; q < 5; q++) { i64 ix = base + q < nrows ? base + q : nrows; o" + C + "[q] = a.c[" + C + "].offsets[ix]; } }");
                 if (t.kind == TypeKind::VARCHAR && t.precision <= 4)  // the 4 rows' payload is one window of <= 16 bytes
-                    line("u64 wl" + C + ", wh" + C + "; load_byte_window((const u8*)a.c[" + C + "].values, o" + C + "[0], o" + C + "[4] - o" + C + "[0], wl" + C + ", wh" + C + ", err);");
+                    line("u64 wl" + C + ", wh" + C + "; load_byte_window<" + std::to_string(4 * t.precision) + ">((const u8*)a.c[" + C + "].values, o" + C + "[0], o" + C + "[4] - o" + C + "[0], wl" + C + ", wh" + C + ", err);");
             } else {
                 std::string st = stype(t);
                 line(st + " c" + C + "[4]; load_tile4<" + st + ">((const " + st + "*)a.c[" + C + "].values, base, nrows, full, c" + C + ");");
@@ -184,7 +212,9 @@ struct Gen {
                 if (t.isVarWidth()) {
                     int n = t.kind == TypeKind::VARCHAR ? t.precision : 0;
                     if (t.kind == TypeKind::VARCHAR && n <= 4) {
-                        line("u64 x" + C + ", y" + C + " = 0; window_varchar<" + std::to_string(n) + ">(wl" + C + ", wh" + C + ", o" + C + "[r] - o" + C + "[0], o" + C + "[r + 1] - o" + C + "[r], x" + C + ", err);");
+                        line("u64 x" + C + ", y" + C + " = 0; window_varchar<" + std::to_string(n) + ", " + std::to_string((stagedLoads ? SR : 4) * n) + ">(wl" + C + ", wh" + C + ", o" + C + "[r] - o" + C + "[0], o" + C + "[r + 1] - o" + C + "[r], x" + C + ", err);");
+                    } else if (t.kind == TypeKind::VARCHAR && stagedLoads) {
+                        line("u64 x" + C + ", y" + C + "; pack_varchar<" + std::to_string(n) + ">((const u8*)(st + " + std::to_string(soff[c].vbytes) + "), o" + C + "[r] - vb" + C + ", o" + C + "[r + 1] - o" + C + "[r], x" + C + ", y" + C + ", err);");
                     } else if (t.kind == TypeKind::VARCHAR) {
                         line("u64 x" + C + ", y" + C + "; pack_varchar<" + std::to_string(n) + ">((const u8*)a.c[" + C + "].values, o" + C + "[r], o" + C + "[r + 1] - o" + C + "[r], x" + C + ", y" + C + ", err);");
                     } else {
@@ -660,15 +690,77 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     src << "#include \"pgpu_device.cuh\"\n\n";
 
     // ---------------------------------------------------------------- eval prologue shared by all modes
-    std::ostringstream evalFilter;  // code: loads + per-row filter -> sel[]
+    // ---- stage layout of the staged variant: one region per used array, 128-byte aligned
+    constexpr int kStagedWarps = 15;               // consumer warps (+ 1 producer warp = 512 threads, 128 registers each)
+    const int kTile = kStagedWarps * 32 * g.SR;    // rows per stage: every consumer thread owns SR consecutive rows
+    bool stagedPossible = true;
+    int stageBytes = 0, tailGuard = 0;
+    std::ostringstream issueVar, issueCopies;  // stage_issue(): var-width byte ranges; the bulk copies of lane 0
+    unsigned fixedTx = 0;
     {
+        auto region = [&](int bytes) {
+            int off = stageBytes;
+            stageBytes += (bytes + 127) / 128 * 128;
+            return off;
+        };
+        auto copy = [&](int off, const std::string& src, int bytes) {
+            issueCopies << "            bulk_g2s(st + " << off << ", " << src << ", " << bytes << ", bar);\n";
+            fixedTx += (unsigned)bytes;
+        };
+        for (int c : res.usedChannels) {
+            const Type& t = plan.input[c];
+            const ColSig& cs = sig[c];
+            std::string C = std::to_string(c);
+            Gen::StageOff so;
+            if (cs.encoding == PGPU_ENC_RLE) continue;
+            if (cs.encoding == PGPU_ENC_DICTIONARY) {
+                so.values = region(kTile * 4);
+                copy(so.values, "(const char*)a.c[" + C + "].ids + row0 * 4", kTile * 4);
+            } else if (t.isVarWidth()) {
+                if (t.kind != TypeKind::VARCHAR || t.precision > 4) { stagedPossible = false; break; }
+                tailGuard = 3;
+                so.offsets = region(kTile * 4 + 16);
+                copy(so.offsets, "(const char*)a.c[" + C + "].offsets + row0 * 4", kTile * 4 + 16);
+                so.vcap = (kTile * t.precision + 15) / 16 * 16 + 16;
+                so.vbytes = region(so.vcap + 32);
+                so.vbase = region(16);
+                // byte range of the tile: 16-byte aligned body by bulk copy, the < 16 trailing bytes by the producer lanes
+                issueVar << "        const i32 vb0_" << C << " = a.c[" << C << "].offsets[row0], vb1_" << C << " = a.c[" << C << "].offsets[row0 + " << kTile << "];\n";
+                issueVar << "        i32 s0_" << C << " = vb0_" << C << " & ~15, e1_" << C << " = vb1_" << C << " & ~15;\n";
+                issueVar << "        if (e1_" << C << " < s0_" << C << ") e1_" << C << " = s0_" << C << ";\n";
+                issueVar << "        if (e1_" << C << " - s0_" << C << " > " << so.vcap << ") { err |= PGPU_ERR_VARCHAR_LEN; e1_" << C << " = s0_" << C << " + " << so.vcap << "; }\n";
+                issueVar << "        { const i32 q = e1_" << C << " + lane; if (lane < 16 && q < vb1_" << C << " && q - s0_" << C << " < " << (so.vcap + 16) << ") st[" << so.vbytes << " + (q - s0_" << C
+                         << ")] = ((const u8*)a.c[" << C << "].values)[q]; }\n";
+                issueVar << "        if (lane == 0) *reinterpret_cast<i32*>(st + " << so.vbase << ") = s0_" << C << ";\n";
+                issueVar << "        tx += (u32)(e1_" << C << " - s0_" << C << ");\n";
+                issueCopies << "            if (e1_" << C << " > s0_" << C << ") bulk_g2s(st + " << so.vbytes << ", (const char*)a.c[" << C << "].values + s0_" << C << ", (u32)(e1_" << C << " - s0_" << C << "), bar);\n";
+            } else {
+                so.values = region(kTile * t.width());
+                copy(so.values, "(const char*)a.c[" + C + "].values + row0 * " + std::to_string(t.width()), kTile * t.width());
+            }
+            if (cs.encoding == PGPU_ENC_PLAIN && cs.nullable) {
+                so.nulls = region(kTile);
+                copy(so.nulls, "(const char*)a.c[" + C + "].nulls + row0", kTile);
+            }
+            g.soff[c] = so;
+        }
+        if (res.usedChannels.empty()) stagedPossible = false;
+    }
+
+    std::ostringstream evalFilter, evalFilterEager, evalFilterStaged;  // code: loads + per-row filter -> sel[]
+    for (int eager = 0; eager < 3; eager++) {
+        if (eager == 2 && !stagedPossible) break;
+        g.stagedLoads = eager == 2;
         g.out.str("");
         g.indent = 2;
-        g.line("const bool full = base + 4 <= nrows;");
+        const std::string R = std::to_string(eager == 2 ? g.SR : 4);
+        if (eager == 2) g.line("const i64 base = 0, nrows = " + R + ";  // staged tiles are always complete");
+        g.line("const bool full = base + " + R + " <= nrows;");
         g.emitTileLoads(filterChans);
+        if (eager) g.emitTileLoads(phase2Loads);
         g.line("bool any = false;");
         g.line("#pragma unroll");
-        g.line("for (int r = 0; r < 4; r++) {");
+        g.line("for (int r = 0; r < " + R + "; r++) {");
         g.indent++;
         g.line("const bool live = base + r < nrows;");
         if (plan.filter) {
@@ -696,9 +788,10 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         g.indent--;
         g.line("}");
         g.line("if (!any) return;");
-        g.emitTileLoads(phase2Loads);
-        evalFilter << g.out.str();
+        if (!eager) g.emitTileLoads(phase2Loads);
+        (eager == 2 ? evalFilterStaged : eager ? evalFilterEager : evalFilter) << g.out.str();
     }
+    g.stagedLoads = false;
 
     auto genProjections = [&](std::map<int, Val>& pv) {
         g.emitRowPrologue(restChans);
@@ -787,6 +880,19 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         if (f.nullable) f.nullBit = nullBits++;
         f.nbytes = keyBytes(f.type);
         fields.push_back(f);
+    }
+    // distinct-key bound from the key types alone (BOOLEAN, short VARCHAR): lets the host size the table once and skip
+    // the per-chunk "could this chunk overflow the table" hand-shake
+    {
+        double dom = fields.empty() ? 0 : 1;
+        for (auto& f : fields) {
+            double d = 0;
+            if (f.type.kind == TypeKind::BOOLEAN) d = 2;
+            else if (f.type.kind == TypeKind::VARCHAR && f.type.precision <= 2) d = f.type.precision == 1 ? 257 : 65793;
+            if (d == 0) { dom = 0; break; }
+            dom *= d + (f.nullable ? 1 : 0);
+        }
+        res.keyDomain = dom;
     }
     int off = (nullBits + 7) / 8;
     for (auto& f : fields) {
@@ -1003,9 +1109,22 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     res.dirCap = 0;
     if (res.useDir) {
         int cap = 128;
-        while (cap > 16 && (8 * cap * NHA * 8 + cap * KW * 8 + cap * 4 + 16) > 40 * 1024) cap /= 2;
+        const int nwarps = stagedPossible ? kStagedWarps : 8;  // the staged variant keeps one warp-private table per consumer warp
+        while (cap > 16 && (nwarps * cap * NHA * 8 + cap * KW * 8 + cap * 12 + 16) > 40 * 1024) cap /= 2;
         res.dirCap = cap;
-        res.smemBytes = 8 * cap * NHA * 8 + cap * KW * 8 + cap * 4 + 16;
+        res.smemBytes = 8 * cap * NHA * 8 + cap * KW * 8 + cap * 12 + 16;
+    }
+
+    // staged variant: low-cardinality hash aggregation whose stage ring (>= 2 stages) fits beside the directory
+    {
+        const int kBudget = 220 * 1024;
+        int cap = std::max(res.dirCap, 1);
+        int dirBytes = res.useDir ? kStagedWarps * cap * NHA * 8 + cap * KW * 8 + cap * 12 + 16 : 0;
+        res.stagedTile = kTile;
+        res.stagedThreads = (kStagedWarps + 1) * 32;
+        res.stagedFixedSmem = (dirBytes + 127) / 128 * 128 + 128;
+        res.stageBytes = stageBytes;
+        res.staged = stagedPossible && res.useDir && !getenv("PGPU_TUNE_NOSTAGE") && stageBytes > 0 && res.stagedFixedSmem + 2 * stageBytes <= kBudget;
     }
 
     // ---- outputs
@@ -1032,6 +1151,11 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     src << "    static constexpr int KWA = " << KWA << ", NWA = " << NWA << ", NH = " << NH << ", NHA = " << NHA << ";\n";
     src << "    static constexpr bool USE_DIR = " << (res.useDir ? "true" : "false") << ";\n";
     src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 8;\n";
+    // register-resident groups: as many as fit in ~28 64-bit accumulator registers per thread, at most 4
+    int rg = res.useDir ? std::min(4, 28 / NHA) : 0;
+    if (const char* e = getenv("PGPU_TUNE_RG")) rg = res.useDir ? std::min(atoi(e), 8) : 0;  // tuning knob (bench sweeps)
+    src << "    static constexpr int RG = " << rg << ";\n";
+    src << "    static constexpr int EAGER_LANES = " << (getenv("PGPU_TUNE_EAGER") ? atoi(getenv("PGPU_TUNE_EAGER")) : 16) << ";\n";
     auto kindName = [&](int k) { return k == 0 ? "CK_ADD_U64" : k == 1 ? "CK_ADD_F64" : k == 2 ? "CK_MAX_U64" : "CK_CNT"; };
     src << "    PGPU_DEV static void identity(u64 (&a)[NHA]) {\n";
     for (int w = 0; w < NHA; w++) src << "        a[" << w << "] = 0ull;\n";
@@ -1059,16 +1183,43 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     src << "    }\n";
 
     // ---- eval
-    src << "    PGPU_DEV static void eval(const PageArgs<NC>& a, i64 base, i64 nrows, bool (&sel)[4], u64 (&key)[4][KWA], u64 (&cw)[4][NHA], u32& err) {\n";
-    src << evalFilter.str();
-    src << "        #pragma unroll\n";
-    src << "        for (int r = 0; r < 4; r++) {\n";
-    src << "            if (sel[r]) {\n";
-    src << rowBody;
-    src << "            }\n";
-    src << "        }\n";
-    src << "    }\n";
+    // eval: filter channels first, the remaining channels only when some row of the thread passed (selective filters
+    // never read them: Q6 skips most of extendedprice). eval_eager: every load issued up front, one memory round trip
+    // per tile (the kernels switch to it while most lanes pass the filter: Q1).
+    for (int eager = 0; eager < 2; eager++) {
+        src << "    PGPU_DEV static void " << (eager ? "eval_eager" : "eval") << "(const PageArgs<NC>& a, i64 base, i64 nrows, bool (&sel)[4], u64 (&key)[4][KWA], u64 (&cw)[4][NHA], u32& err) {\n";
+        src << (eager ? evalFilterEager.str() : evalFilter.str());
+        src << "        #pragma unroll\n";
+        src << "        for (int r = 0; r < 4; r++) {\n";
+        src << "            if (sel[r]) {\n";
+        src << rowBody;
+        src << "            }\n";
+        src << "        }\n";
+        src << "    }\n";
+    }
     (void)projRaises;
+    if (res.staged) {
+        src << "    static constexpr int SR = " << g.SR << ", CWARPS = " << kStagedWarps << ", TILE = " << kTile << ", STAGE_BYTES = " << stageBytes << ", TAIL_GUARD = " << tailGuard << ";\n";
+        src << "    PGPU_DEV static void eval_staged(const PageArgs<NC>& a, const unsigned char* st, int trow, bool (&sel)[SR], u64 (&key)[SR][KWA], u64 (&cw)[SR][NHA], u32& err) {\n";
+        src << evalFilterStaged.str();
+        src << "        #pragma unroll\n";
+        src << "        for (int r = 0; r < SR; r++) {\n";
+        src << "            if (sel[r]) {\n";
+        src << rowBody;
+        src << "            }\n";
+        src << "        }\n";
+        src << "    }\n";
+        // producer warp: arm the stage's full barrier with the byte count, then hand the copies to the TMA engine
+        src << "    PGPU_DEV static void stage_issue(const PageArgs<NC>& a, i64 row0, unsigned char* st, u64* bar, int lane, u32& err) {\n";
+        src << "        u32 tx = " << fixedTx << "u;\n";
+        src << issueVar.str();
+        src << "        __syncwarp();\n";
+        src << "        if (lane == 0) {\n";
+        src << "            mbar_arrive_expect_tx(bar, tx);\n";
+        src << issueCopies.str();
+        src << "        }\n";
+        src << "    }\n";
+    }
 
     // ---- emit (finalisation of one group)
     {
@@ -1233,7 +1384,9 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, Scratch sc) { body_agg_global<P>(a, sc); }\n";
         src << "extern \"C\" __global__ void pgpu_k_emit(Scratch sc, OutArgs<P::NO> out) { body_emit_global<P>(sc, out); }\n";
     } else {
-        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, TableArgs t, Scratch sc) { body_agg_hash<P>(a, t, sc); }\n";
+        src << "extern \"C\" __global__ void __launch_bounds__(256, " << (getenv("PGPU_TUNE_MINBLOCKS") ? atoi(getenv("PGPU_TUNE_MINBLOCKS")) : 2) << ") pgpu_k_page(PageArgs<P::NC> a, TableArgs t, Scratch sc) { body_agg_hash<P>(a, t, sc); }\n";
+        if (res.staged)
+            src << "extern \"C\" __global__ void __launch_bounds__(512, 1) pgpu_k_page_staged(PageArgs<P::NC> a, TableArgs t, Scratch sc, int nstages) { body_agg_hash_staged<P>(a, t, sc, nstages); }\n";
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots) { body_materialize<P>(t, out, sc, first_slot, nslots); }\n";
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_rehash(TableArgs from, TableArgs to, Scratch sc) { body_rehash<P>(from, to, sc); }\n";
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";

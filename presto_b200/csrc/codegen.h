@@ -34,6 +34,13 @@ struct GenResult {
     bool useDir = false;
     int dirCap = 0;
     int smemBytes = 0;         // dynamic shared memory of the page kernel
+    // staged variant (pgpu_k_page_staged): bulk-async copies of column tiles into a shared-memory ring
+    bool staged = false;
+    int stagedThreads = 544;   // 2 x 8 consumer warps + 1 producer warp
+    int stagedTile = 1024;     // rows per stage
+    int stageBytes = 0;        // bytes of one stage
+    int stagedFixedSmem = 0;   // directory + warp tables + mbarriers in front of the stages
+    double keyDomain = 0;      // upper bound of distinct group keys when the key types bound it (0 = unbounded)
     std::vector<int> cellKinds;  // NW entries (CK_*)
     std::vector<OutColDesc> out;
     std::vector<int> usedChannels;  // input channels the kernels dereference

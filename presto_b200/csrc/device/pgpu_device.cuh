@@ -68,6 +68,7 @@ struct TableArgs {
     u64 limit;       // new groups are only claimed while counters[0] < limit (load-factor guard)
     u64* faillog;    // chunk-relative indices of deferred rows; replayed by k_replay after the host grew the table
     u64 faillog_cap;
+    u64 row_bias;    // added to the kernel's row numbers when logging (a kernel launched on the tail of a chunk)
 };
 
 // Per-pipeline device scratch shared by all kernels.
@@ -290,32 +291,43 @@ PGPU_DEV void pack_varchar(const u8* __restrict__ bytes, i32 off, i32 len, u64& 
     }
 }
 
-// The <= 16 bytes [start, start + nbytes) of a byte slice as 128 bits (little endian), fetched with aligned 32-bit
-// loads: the var-width payload of a thread's 4 consecutive short rows is one contiguous window of the slice.
+// The <= MAXB (<= 16) bytes [start, start + nbytes) of a byte slice as 128 bits (little endian), fetched with aligned
+// 32-bit loads: the var-width payload of a thread's 4 consecutive short rows is one contiguous window of the slice.
+// MAXB = 4 * n for varchar(n): short windows need fewer words (varchar(1): two loads and one funnel shift).
+template <int MAXB>
 PGPU_DEV void load_byte_window(const u8* __restrict__ bytes, i32 start, i32 nbytes, u64& lo, u64& hi, u32& err) {
     lo = 0; hi = 0;
     if (nbytes <= 0) return;
-    if (nbytes > 16) { err |= PGPU_ERR_VARCHAR_LEN; nbytes = 16; }
+    if (nbytes > MAXB) { err |= PGPU_ERR_VARCHAR_LEN; nbytes = MAXB; }
     const u32* wp = reinterpret_cast<const u32*>(bytes + (start & ~3));
     const u32 sh = (u32)(start & 3) * 8u;
-    const int nwords = ((start & 3) + nbytes + 3) >> 2;  // 1..5
-    u32 w[5];
+    const int nwords = ((start & 3) + nbytes + 3) >> 2;  // 1 .. (MAXB + 6) / 4
+    constexpr int MAXW = (MAXB + 6) / 4;
+    u32 w[5] = {0u, 0u, 0u, 0u, 0u};
 #pragma unroll
-    for (int k = 0; k < 5; k++) w[k] = k < nwords ? __ldg(wp + k) : 0u;
-    u32 o0 = __funnelshift_r(w[0], w[1], sh), o1 = __funnelshift_r(w[1], w[2], sh);
-    u32 o2 = __funnelshift_r(w[2], w[3], sh), o3 = __funnelshift_r(w[3], w[4], sh);
+    for (int k = 0; k < MAXW; k++) w[k] = k < nwords ? __ldg(wp + k) : 0u;
+    u32 o0 = __funnelshift_r(w[0], w[1], sh);
+    u32 o1 = MAXB > 4 ? __funnelshift_r(w[1], w[2], sh) : 0u;
     lo = ((u64)o1 << 32) | o0;
-    hi = ((u64)o3 << 32) | o2;
+    if (MAXB > 8) {
+        u32 o2 = __funnelshift_r(w[2], w[3], sh), o3 = __funnelshift_r(w[3], w[4], sh);
+        hi = ((u64)o3 << 32) | o2;
+    }
 }
-// Row value out of a window: bytes [rel, rel + len) -> packed cell (byte 0 = length, bytes 1.. = data), N <= 4
-template <int N>
+// Row value out of a window of at most WB bytes: bytes [rel, rel + len) -> packed cell (byte 0 = length, bytes 1.. =
+// data), N <= 4
+template <int N, int WB>
 PGPU_DEV void window_varchar(u64 wlo, u64 whi, i32 rel, i32 len, u64& x, u32& err) {
     if (len > N) { err |= PGPU_ERR_VARCHAR_LEN; len = N; }
     if (len < 0) len = 0;
     u64 d;
-    if (rel < 8) d = (wlo >> (8 * rel)) | (rel ? (whi << (64 - 8 * rel)) : 0ull);
-    else d = whi >> (8 * (rel - 8));
-    d &= (len >= 8) ? ~0ull : ((1ull << (8 * len)) - 1ull);
+    if (WB <= 8) {
+        d = wlo >> (8 * (rel & 7));  // the whole window lives in the low word
+    } else {
+        if (rel < 8) d = (wlo >> (8 * rel)) | (rel ? (whi << (64 - 8 * rel)) : 0ull);
+        else d = whi >> (8 * (rel - 8));
+    }
+    d &= (1ull << (8 * len)) - 1ull;  // len <= N <= 4
     x = (u64)(u32)len | (d << 8);
 }
 
@@ -446,7 +458,7 @@ PGPU_DEV bool table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::K
 PGPU_DEV void defer_rows(const TableArgs& t, i64 row, int nrows, u32& err) {
     u64 at = atomicAdd(t.counters + 1, (u64)nrows);
     for (int k = 0; k < nrows; k++) {
-        if (at + k < t.faillog_cap) t.faillog[at + k] = (u64)(row + k);
+        if (at + k < t.faillog_cap) t.faillog[at + k] = (u64)(row + k) + t.row_bias;
         else err |= PGPU_ERR_TABLE_FULL;
     }
 }
@@ -461,6 +473,7 @@ PGPU_DEV void body_agg_global(const PageArgs<P::NC>& a, const Scratch& sc) {
     u64 acc[NHA];
     P::identity(acc);
     u32 err = 0;
+    bool eager = false;  // warp-uniform, see body_agg_hash
     const i64 tile_rows = (i64)blockDim.x * 4;
     const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
     for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -468,7 +481,9 @@ PGPU_DEV void body_agg_global(const PageArgs<P::NC>& a, const Scratch& sc) {
         bool sel[4];
         u64 key[4][1];
         u64 cw[4][NHA];
-        P::eval(a, base, a.rows, sel, key, cw, err);
+        if (eager) P::eval_eager(a, base, a.rows, sel, key, cw, err);
+        else P::eval(a, base, a.rows, sel, key, cw, err);
+        eager = __popc(__ballot_sync(FULLMASK, sel[0] | sel[1] | sel[2] | sel[3])) >= P::EAGER_LANES;
 #pragma unroll
         for (int r = 0; r < 4; r++)
             if (sel[r]) P::combine(acc, cw[r]);
@@ -510,132 +525,181 @@ PGPU_DEV void body_agg_global(const PageArgs<P::NC>& a, const Scratch& sc) {
 }
 
 // ------------------------------------------------------------------------------------------------ hash aggregation
+// Level 0 (P::RG > 0): the first RG groups a block meets live in REGISTERS: every thread keeps private accumulators
+// for them and adds its rows with predicated adds — no shuffles, no shared memory, no atomics in the scan loop; the
+// threads' copies are folded by warp shuffles once, when the block has consumed its last tile. TPC-H Q1 (4 groups)
+// runs entirely at this level.
 // Level 1 (P::USE_DIR): a block-shared key directory in shared memory maps keys to small slot numbers; each warp
 // owns a private accumulator table indexed by that slot, updated without atomics after a warp-level reduction over
 // lanes holding the same slot. Level 2: the HBM table, for directory misses and for the end-of-kernel flush.
+template <int KW>
+PGPU_DEV u32 dir_hash(const u64 (&k)[KW > 0 ? KW : 1]) {  // cheap 32-bit multiplicative hash: directory placement only
+    u32 h = 0x9e3779b9u;
+#pragma unroll
+    for (int i = 0; i < KW; i++) h = (h ^ (u32)k[i] ^ (u32)(k[i] >> 32)) * 0x85ebca6bu;
+    return h ^ (h >> 15);
+}
+// Returns (dense id << 16) | directory position, or -1 when the key is not in the directory and the directory is full.
+// Dense ids count insertions (0, 1, 2, ... per block); ids < P::RG are the register-resident groups.
 template <class P>
-PGPU_DEV int dir_lookup(u64* dkeys, u32* dtags, u32* dcount, const u64 (&key)[P::KW], u64 h) {
+PGPU_DEV int dir_lookup(u64* dkeys, u32* dtags, u32* dids, u32* dpos, u32* dcount, const u64 (&key)[P::KW], u32 h) {
     constexpr int KW = P::KW, DCAP = P::DCAP;
-    u32 pos = (u32)(h >> 40) % DCAP;
-    const u32 tagv = 2u | ((u32)h << 8);
+    u32 pos = (h >> 8) & (u32)(DCAP - 1);
+    const u32 tagv = 2u | (h << 8);
 #pragma unroll 1
     for (int probes = 0; probes < DCAP; probes++) {
         for (;;) {
             u32 tag = *((volatile u32*)&dtags[pos]);
-            if (tag == 0u) {
-                if (*((volatile u32*)dcount) >= (u32)P::DLIMIT) return -1;  // directory full: go to HBM
-                u32 old = atomicCAS(&dtags[pos], 0u, 1u);
-                if (old == 0u) {
-#pragma unroll
-                    for (int i = 0; i < KW; i++) dkeys[pos * KW + i] = key[i];
-                    __threadfence_block();
-                    *((volatile u32*)&dtags[pos]) = tagv;
-                    atomicAdd(dcount, 1u);
-                    return (int)pos;
-                }
-                continue;
-            }
-            if (tag == 1u) continue;
             if (tag == tagv) {
                 bool eq = true;
 #pragma unroll
                 for (int i = 0; i < KW; i++) eq &= (((volatile u64*)dkeys)[pos * KW + i] == key[i]);
-                if (eq) return (int)pos;
+                if (eq) return (int)((*((volatile u32*)&dids[pos]) << 16) | pos);
+                break;
             }
-            break;
+            if (tag == 0u) {
+                if (*((volatile u32*)dcount) >= (u32)P::DLIMIT) return -1;  // directory full: go to HBM
+                u32 old = atomicCAS(&dtags[pos], 0u, 1u);
+                if (old == 0u) {
+                    u32 id = atomicAdd(dcount, 1u);
+#pragma unroll
+                    for (int i = 0; i < KW; i++) dkeys[pos * KW + i] = key[i];
+                    dids[pos] = id;
+                    if (id < (u32)DCAP) dpos[id] = pos;
+                    __threadfence_block();
+                    *((volatile u32*)&dtags[pos]) = tagv;
+                    return (int)((id << 16) | pos);
+                }
+                continue;
+            }
+            if (tag == 1u) continue;
+            break;  // occupied by another key
         }
-        pos = pos + 1 == (u32)DCAP ? 0u : pos + 1;
+        pos = (pos + 1) & (u32)(DCAP - 1);
     }
     return -1;
 }
 
 template <class P>
-PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc) {
-    constexpr int KW = P::KW, NH = P::NH, NHA = P::NHA, DCAP = P::DCAP, NWARP = P::NWARP;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    // layout: wacc[NWARP][DCAP][NHA] u64 | dkeys[DCAP][KW] u64 | dtags[DCAP] u32 | dcount u32
-    u64* wacc = reinterpret_cast<u64*>(smem_raw);
-    u64* dkeys = wacc + (P::USE_DIR ? NWARP * DCAP * NHA : 0);
-    u32* dtags = reinterpret_cast<u32*>(dkeys + (P::USE_DIR ? DCAP * KW : 0));
-    u32* dcount = dtags + (P::USE_DIR ? DCAP : 0);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (P::USE_DIR) {
-        for (int i = threadIdx.x; i < NWARP * DCAP; i += blockDim.x) P::identity_ptr(wacc + (size_t)i * NHA);
-        for (int i = threadIdx.x; i < DCAP; i += blockDim.x) dtags[i] = 0u;
-        if (threadIdx.x == 0) *dcount = 0u;
-        __syncthreads();
+PGPU_DEV void reg_accumulate(u64 (&racc)[P::RG > 0 ? P::RG : 1][P::NHA], int id, const u64 (&b)[P::NHA]) {
+#pragma unroll
+    for (int g = 0; g < P::RG; g++)
+        if (id == g) P::combine(racc[g], b);
+}
+
+// Everything a thread needs to consume evaluated rows: directory + warp-private table pointers, the HBM table, the
+// register-resident group accumulators. One instance per thread, fully scalarised by the compiler.
+template <class P>
+struct HashCtx {
+    static constexpr int KW = P::KW, NH = P::NH, NHA = P::NHA, DCAP = P::DCAP, RG = P::RG;
+    u64 *wacc, *dkeys, *myacc;
+    u32 *dtags, *dids, *dpos, *dcount;
+    u64 racc[RG > 0 ? RG : 1][NHA];
+    bool use_dir;  // warp-uniform
+    u32 err;
+
+    // shared-memory layout: wacc[nwarps][DCAP][NHA] u64 | dkeys[DCAP][KW] u64 | dtags | dids | dpos [DCAP] u32 | dcount u32
+    static constexpr int dir_bytes(int nwarps) { return P::USE_DIR ? nwarps * DCAP * NHA * 8 + DCAP * KW * 8 + DCAP * 12 + 16 : 0; }
+
+    PGPU_DEV void init(unsigned char* smem, int nwarps, int warp) {
+        wacc = reinterpret_cast<u64*>(smem);
+        dkeys = wacc + (P::USE_DIR ? nwarps * DCAP * NHA : 0);
+        dtags = reinterpret_cast<u32*>(dkeys + (P::USE_DIR ? DCAP * KW : 0));
+        dids = dtags + (P::USE_DIR ? DCAP : 0);
+        dpos = dids + (P::USE_DIR ? DCAP : 0);
+        dcount = dpos + (P::USE_DIR ? DCAP : 0);
+        myacc = wacc + (size_t)warp * DCAP * NHA;
+        use_dir = P::USE_DIR;
+        err = 0;
+#pragma unroll
+        for (int g = 0; g < (RG > 0 ? RG : 1); g++) P::identity(racc[g]);
+        if (P::USE_DIR) {  // whole block participates; caller synchronises afterwards
+            for (int i = threadIdx.x; i < nwarps * DCAP; i += blockDim.x) P::identity_ptr(wacc + (size_t)i * NHA);
+            for (int i = threadIdx.x; i < DCAP; i += blockDim.x) dtags[i] = 0u;
+            if (threadIdx.x == 0) *dcount = 0u;
+        }
     }
-    u32 err = 0;
-    const i64 tile_rows = (i64)blockDim.x * 4;
-    const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
-    u64* myacc = wacc + (size_t)warp * DCAP * NHA;
-    bool use_dir = P::USE_DIR;  // warp-uniform
-    for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
-        bool sel[4];
-        u64 key[4][KW];
-        u64 cw[4][NHA];
-        P::eval(a, base, a.rows, sel, key, cw, err);
+
+    // Consume the R evaluated rows of this thread (global row numbers base .. base+R-1). Must be called by all 32 lanes.
+    template <int R>
+    PGPU_DEV void consume(const TableArgs& t, i64 base, bool (&sel)[R], u64 (&key)[R][KW], u64 (&cw)[R][NHA]) {
+        const int lane = threadIdx.x & 31;
         if (P::USE_DIR && use_dir) {
-            // 1. directory slot of every selected row (block-shared keys in shared memory)
-            int slot[4];
+            // 1. directory entry of every selected row; rows of the register-resident groups are consumed right here
+            int slot[R];
+            int nmiss = 0, hits = 0;
+            bool slow = false;
 #pragma unroll
-            for (int r = 0; r < 4; r++) slot[r] = sel[r] ? dir_lookup<P>(dkeys, dtags, dcount, key[r], hash_key<KW>(key[r])) : -1;
-            // 2. rows whose key is not in the (full) directory go straight to the HBM table
-            int nmiss = 0;
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                if (sel[r] && slot[r] < 0) {
-                    nmiss++;
-                    if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
+            for (int r = 0; r < R; r++) {
+                slot[r] = -1;
+                if (sel[r]) {
+                    const int e = dir_lookup<P>(dkeys, dtags, dids, dpos, dcount, key[r], dir_hash<KW>(key[r]));
+                    if (e < 0) {  // 2. not in the (full) directory: straight to the HBM table
+                        nmiss++;
+                        if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
+                    } else if (RG > 0 && (e >> 16) < RG) {
+                        reg_accumulate<P>(racc, e >> 16, cw[r]);
+                        hits++;
+                    } else {
+                        slot[r] = e & 0xffff;
+                        slow = true;
+                    }
                 }
             }
-            // 3. one warp reduction per distinct directory slot held by this warp's 128 rows: every lane first adds up its
-            //    own rows of that slot, the elected lane then adds the warp total to the warp-private table (no atomics)
-            __syncwarp();
-            int hits = 0, rounds = 0;
+            // 3. remaining rows: one warp reduction per distinct directory slot held by this warp's 128 rows: every lane
+            //    first adds up its own rows of that slot, the elected lane then adds the warp total to the warp-private
+            //    table (no atomics)
+            if (__any_sync(FULLMASK, slow)) {
+                int rounds = 0;
 #pragma unroll 1
-            for (;;) {
-                int cand = slot[0] >= 0 ? slot[0] : slot[1] >= 0 ? slot[1] : slot[2] >= 0 ? slot[2] : slot[3];
-                u32 have = __ballot_sync(FULLMASK, cand >= 0);
-                if (!have) break;
-                if (rounds++ >= P::MAX_WARP_GROUPS) {
-                    // too many distinct groups in one warp for the reduction to pay: fire-and-forget atomics instead
+                for (;;) {
+                    int cand = -1;
 #pragma unroll
-                    for (int r = 0; r < 4; r++) {
-                        if (slot[r] >= 0) {
-                            if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
-                            nmiss++;
+                    for (int r = R - 1; r >= 0; r--) cand = slot[r] >= 0 ? slot[r] : cand;
+                    u32 have = __ballot_sync(FULLMASK, cand >= 0);
+                    if (!have) break;
+                    if (rounds++ >= P::MAX_WARP_GROUPS) {
+                        // too many distinct groups in one warp for the reduction to pay: fire-and-forget atomics instead
+#pragma unroll
+                        for (int r = 0; r < R; r++) {
+                            if (slot[r] >= 0) {
+                                if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
+                                nmiss++;
+                            }
+                        }
+                        break;
+                    }
+                    const int leader = __ffs(have) - 1;
+                    const int g = __shfl_sync(FULLMASK, cand, leader);
+                    u64 v[NHA];
+                    P::identity(v);
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        if (slot[r] == g) {
+                            P::combine(v, cw[r]);
+                            slot[r] = -1;
+                            hits++;
                         }
                     }
-                    break;
+                    P::warp_reduce_cells(v);
+                    if (lane == leader) P::combine_ptr(myacc + (size_t)g * NHA, v);
                 }
-                const int leader = __ffs(have) - 1;
-                const int g = __shfl_sync(FULLMASK, cand, leader);
-                u64 v[NHA];
-                P::identity(v);
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    if (slot[r] == g) {
-                        P::combine(v, cw[r]);
-                        slot[r] = -1;
-                        hits++;
-                    }
-                }
-                P::warp_reduce_cells(v);
-                if (lane == leader) P::combine_ptr(myacc + (size_t)g * NHA, v);
+                __syncwarp();
             }
-            __syncwarp();
             // adaptive bypass: once most rows miss the (full) directory, stop paying for lookups. Bypassing is always
             // correct because the directory accumulators and the HBM table are merged additively at the end.
-            int wh = __reduce_add_sync(FULLMASK, hits), wm = __reduce_add_sync(FULLMASK, nmiss);
-            if (wm > 2 * wh) use_dir = false;
+            if (__any_sync(FULLMASK, nmiss > 0)) {
+                int wh = __reduce_add_sync(FULLMASK, hits), wm = __reduce_add_sync(FULLMASK, nmiss);
+                if (wm > 2 * wh) use_dir = false;
+            }
         } else {
             // high cardinality: fold the thread's consecutive rows with equal keys (l_orderkey-style runs) into the
             // first row of the run, then update the HBM table; span = rows folded (to defer the whole run if needed)
-            int span[4] = {1, 1, 1, 1};
+            int span[R];
 #pragma unroll
-            for (int r = 3; r >= 1; r--) {
+            for (int r = 0; r < R; r++) span[r] = 1;
+#pragma unroll
+            for (int r = R - 1; r >= 1; r--) {
                 bool same = sel[r] && sel[r - 1];
 #pragma unroll
                 for (int i = 0; i < KW; i++) same &= (key[r][i] == key[r - 1][i]);
@@ -646,18 +710,36 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
                 }
             }
 #pragma unroll
-            for (int r = 0; r < 4; r++)
+            for (int r = 0; r < R; r++)
                 if (sel[r] && !table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, span[r], err);
         }
     }
-    if (P::USE_DIR) {
+
+    // End of kernel, whole block: fold register groups -> warp tables -> HBM table. `accwarps` = warps that own a wacc table
+    // and hold register accumulators (the compute warps); other warps only take part in the barriers.
+    PGPU_DEV void flush(const TableArgs& t, int accwarps) {
+        if (!P::USE_DIR) return;
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         __syncthreads();
-        // flush: fold the warp-private tables in warp order and push each live directory entry to HBM
+        if (RG > 0) {
+            const int ngroups = (int)min(*((volatile u32*)dcount), (u32)RG);
+            if (warp < accwarps) {
+#pragma unroll
+                for (int g = 0; g < RG; g++) {
+                    if (g < ngroups) {  // block-uniform
+                        P::warp_reduce_cells(racc[g]);
+                        if (lane == 0) P::combine_ptr(myacc + (size_t)dpos[g] * NHA, racc[g]);
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        // fold the warp-private tables in warp order and push each live directory entry to HBM
         for (int s = threadIdx.x; s < DCAP; s += blockDim.x) {
             if (dtags[s] < 2u) continue;
             u64 tot[NHA];
             P::identity(tot);
-            for (int k = 0; k < NWARP; k++) P::combine_ptr_to(tot, wacc + ((size_t)k * DCAP + s) * NHA);
+            for (int k = 0; k < accwarps; k++) P::combine_ptr_to(tot, wacc + ((size_t)k * DCAP + s) * NHA);
             u64 key[KW];
 #pragma unroll
             for (int i = 0; i < KW; i++) key[i] = dkeys[s * KW + i];
@@ -665,7 +747,161 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
             if (!table_update<P>(t, key, tot, true)) err |= PGPU_ERR_TABLE_FULL;
         }
     }
-    if (err) atomicOr(sc.err, err);
+};
+
+// Direct variant: every thread loads its own rows from global memory (128-bit streaming loads). Used for high
+// cardinality plans (the table atomics are the bound there), for short pages and for the ragged tail of staged pages.
+template <class P>
+PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc) {
+    constexpr int KW = P::KW, NHA = P::NHA;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashCtx<P> cx;
+    cx.init(smem_raw, P::NWARP, threadIdx.x >> 5);
+    if (P::USE_DIR) __syncthreads();
+    const i64 tile_rows = (i64)blockDim.x * 4;
+    const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
+    bool eager = false;  // warp-uniform: most lanes passed the filter in the previous tile -> issue all loads at once
+    for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
+        bool sel[4];
+        u64 key[4][KW];
+        u64 cw[4][NHA];
+        if (eager) P::eval_eager(a, base, a.rows, sel, key, cw, cx.err);
+        else P::eval(a, base, a.rows, sel, key, cw, cx.err);
+        eager = __popc(__ballot_sync(FULLMASK, sel[0] | sel[1] | sel[2] | sel[3])) >= P::EAGER_LANES;
+        cx.template consume<4>(t, base, sel, key, cw);
+    }
+    cx.flush(t, P::NWARP);
+    if (cx.err) atomicOr(sc.err, cx.err);
+}
+
+// ------------------------------------------------------------------------------------------------ staged variant
+// Bulk-async (TMA engine, cp.async.bulk) staging of column tiles into a shared-memory ring, mbarrier full/empty
+// hand-shake, one producer warp + 2 groups of 8 consumer warps per SM. Memory-level parallelism no longer depends on
+// how many loads the consumer threads can keep in flight in registers: S stages x TILE rows x bytes/row are in flight
+// per SM (Q1: 4 x 46 KB) while the consumers evaluate rows out of shared memory.
+PGPU_DEV u32 smem_addr(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+PGPU_DEV void mbar_init(u64* bar, u32 count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory"); }
+PGPU_DEV void mbar_arrive(u64* bar) { asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(smem_addr(bar)) : "memory"); }
+PGPU_DEV void mbar_arrive_expect_tx(u64* bar, u32 bytes) {
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1; }" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+PGPU_DEV void mbar_wait(u64* bar, u32 parity) {
+    u32 done = 0;
+    const u32 addr = smem_addr(bar);
+    while (!done) {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    }
+}
+// global -> shared bulk copy; dst/src 16-byte aligned, bytes a multiple of 16; completes `bytes` of tx on `bar`
+PGPU_DEV void bulk_g2s(void* dst, const void* src, u32 bytes, u64* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)), "l"(src), "r"(bytes),
+                 "r"(smem_addr(bar))
+                 : "memory");
+}
+
+// Shared-memory tile loads: the thread's R consecutive elements of a staged column (trow = first row within the tile),
+// fetched with the widest aligned loads (R * sizeof(T) is a power of two; regions are 128-byte aligned).
+template <typename T, int R>
+PGPU_DEV void lds_tile(const unsigned char* col, int trow, T (&v)[R]) {
+    constexpr int BYTES = R * (int)sizeof(T);
+    const unsigned char* p = col + (size_t)trow * sizeof(T);
+    union { T t[R]; int4 q[(BYTES + 15) / 16]; int2 d; u32 w; unsigned short h; u8 b; } u;
+    if (BYTES >= 16) {
+#pragma unroll
+        for (int k = 0; k < BYTES / 16; k++) u.q[k] = *reinterpret_cast<const int4*>(p + 16 * k);
+    } else if (BYTES == 8) {
+        u.d = *reinterpret_cast<const int2*>(p);
+    } else if (BYTES == 4) {
+        u.w = *reinterpret_cast<const u32*>(p);
+    } else if (BYTES == 2) {
+        u.h = *reinterpret_cast<const unsigned short*>(p);
+    } else {
+        u.b = *p;
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) v[r] = u.t[r];
+}
+// load_byte_window over a staged byte region (`start` is relative to the 16-byte aligned region base)
+template <int MAXB>
+PGPU_DEV void lds_byte_window(const unsigned char* bytes, i32 start, i32 nbytes, u64& lo, u64& hi, u32& err) {
+    lo = 0; hi = 0;
+    if (nbytes <= 0) return;
+    if (nbytes > MAXB) { err |= PGPU_ERR_VARCHAR_LEN; nbytes = MAXB; }
+    const u32* wp = reinterpret_cast<const u32*>(bytes + (start & ~3));
+    const u32 sh = (u32)(start & 3) * 8u;
+    const int nwords = ((start & 3) + nbytes + 3) >> 2;
+    constexpr int MAXW = (MAXB + 6) / 4;
+    u32 w[5] = {0u, 0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int k = 0; k < MAXW; k++) w[k] = k < nwords ? wp[k] : 0u;
+    u32 o0 = __funnelshift_r(w[0], w[1], sh);
+    u32 o1 = MAXB > 4 ? __funnelshift_r(w[1], w[2], sh) : 0u;
+    lo = ((u64)o1 << 32) | o0;
+    if (MAXB > 8) {
+        u32 o2 = __funnelshift_r(w[2], w[3], sh), o3 = __funnelshift_r(w[3], w[4], sh);
+        hi = ((u64)o3 << 32) | o2;
+    }
+}
+
+// P supplies: SR (rows per consumer thread), CWARPS (consumer warps), TILE = CWARPS * 32 * SR rows per stage,
+// STAGE_BYTES, stage_issue(a, row0, stage, bar, lane, err) executed by the producer warp and
+// eval_staged(a, stage, trow, sel, key, cw, err) executed by the consumer threads.
+// Block = CWARPS consumer warps + 1 producer warp (512 threads, one block per SM, 128 registers per thread: the
+// accumulators of the register-resident groups must not spill — with most of the SM's L1 carved out as shared memory
+// a spill goes to L2). Every consumer warp takes its 32 * SR-row slice of every tile of the block.
+// `nstages` (2..4) is chosen by the host from the shared-memory budget.
+template <class P>
+PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc, int nstages) {
+    constexpr int KW = P::KW, NHA = P::NHA, CW = P::CWARPS, TILE = P::TILE, SR = P::SR;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    // layout: [directory + warp tables][full[4] empty[4] mbarriers][pad to 128][stages]
+    constexpr int DIRB = (HashCtx<P>::dir_bytes(CW) + 127) / 128 * 128;
+    u64* full = reinterpret_cast<u64*>(smem_raw + DIRB);
+    u64* empty = full + 4;
+    unsigned char* stages = smem_raw + DIRB + 128;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    HashCtx<P> cx;
+    cx.init(smem_raw, CW, warp < CW ? warp : 0);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 4; s++) {
+            mbar_init(full + s, 1);    // the producer's arrive.expect_tx; the copies complete the transaction bytes
+            mbar_init(empty + s, CW);  // one arrival per consumer warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    // a.rows is a whole number of tiles (the host runs the ragged tail through the direct kernel); var-width columns read
+    // up to 3 offsets past the last tile, which the host keeps in range
+    const i64 nfull = a.rows / TILE;
+    const i64 mine = blockIdx.x < nfull ? (nfull - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;  // tiles of this block
+    if (warp == CW) {
+        // ---- producer
+        for (i64 it = 0; it < mine; it++) {
+            const int s = (int)(it % nstages);
+            const i64 use = it / nstages;
+            if (use > 0) mbar_wait(empty + s, (u32)((use - 1) & 1));
+            const i64 row0 = (blockIdx.x + it * gridDim.x) * TILE;
+            P::stage_issue(a, row0, stages + (size_t)s * P::STAGE_BYTES, full + s, lane, cx.err);
+        }
+    } else {
+        // ---- consumers
+        const int trow = (warp * 32 + lane) * SR;
+        for (i64 it = 0; it < mine; it++) {
+            const int s = (int)(it % nstages);
+            mbar_wait(full + s, (u32)((it / nstages) & 1));
+            const i64 base = (blockIdx.x + it * gridDim.x) * TILE + trow;
+            bool sel[SR];
+            u64 key[SR][KW];
+            u64 cw[SR][NHA];
+            P::eval_staged(a, stages + (size_t)s * P::STAGE_BYTES, trow, sel, key, cw, cx.err);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty + s);  // this warp is done reading the stage
+            cx.template consume<SR>(t, base, sel, key, cw);
+        }
+    }
+    cx.flush(t, CW);
+    if (cx.err) atomicOr(sc.err, cx.err);
 }
 
 // Re-run deferred rows (one row per thread) against the grown table.

@@ -43,6 +43,7 @@ struct TableArgs {
     uint64_t limit;
     uint64_t* faillog;
     uint64_t faillog_cap;
+    uint64_t row_bias;
 };
 struct Scratch {
     uint32_t* err;
@@ -67,8 +68,10 @@ thread_local std::string g_lastGlobalError;
 struct Variant {
     GenResult gen;
     cudaLibrary_t lib = nullptr;
-    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr;
+    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr;
     int blocksPerSM = 1;
+    int stagedStages = 0;      // stages of the shared-memory ring (0 = staged variant unavailable)
+    size_t stagedSmem = 0;
 };
 
 struct DeviceBuf {
@@ -220,6 +223,19 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
                 CU(cudaLibraryGetKernel(&v.kRehash, v.lib, "pgpu_k_rehash"));
                 CU(cudaLibraryGetKernel(&v.kReplay, v.lib, "pgpu_k_replay"));
             }
+            if (v.gen.staged) {
+                // ring depth from the opt-in shared memory of the device (227 KB on sm_100), at most 4 stages
+                int optin = 0;
+                CU(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
+                int stages = (int)std::min<long>(4, ((long)optin - 1024 - v.gen.stagedFixedSmem) / std::max(v.gen.stageBytes, 1));
+                if (const char* e = getenv("PGPU_TUNE_STAGES")) stages = std::min(stages, atoi(e));
+                if (stages >= 2) {
+                    CU(cudaLibraryGetKernel(&v.kPageStaged, v.lib, "pgpu_k_page_staged"));
+                    v.stagedStages = stages;
+                    v.stagedSmem = (size_t)v.gen.stagedFixedSmem + (size_t)stages * v.gen.stageBytes;
+                    CU(cudaFuncSetAttribute((const void*)v.kPageStaged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.stagedSmem));
+                }
+            }
             int nb = 0;
             cudaError_t oe = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v.kPage, kThreads, (size_t)v.gen.smemBytes);
             if (oe != cudaSuccess || nb < 1) {
@@ -255,6 +271,7 @@ TableArgs tableOf(pgpu_pipeline* p) {
     t.limit = ~0ull;  // no load-factor guard unless the caller sets one
     t.faillog = (uint64_t*)p->failLog.ptr;
     t.faillog_cap = 0;
+    t.row_bias = 0;
     return t;
 }
 
@@ -383,12 +400,15 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         if (!p->dSlots) {
             uint64_t cap = (uint64_t)((double)p->plan->expectedGroups / 0.6) + 1024;
             cap = std::max<uint64_t>(cap, reserve * 4 + 4096);
+            // key types that bound the number of groups (<= 1 M): size the table for the whole domain, once
+            if (g.keyDomain > 0 && g.keyDomain <= (double)(1 << 20)) cap = std::max<uint64_t>(cap, (uint64_t)(g.keyDomain / 0.7) + reserve * 2 + 4096);
             pgpu_status st = growTable(p, v, cap);
             if (st) return st;
         }
         const int64_t n = pg.rows;
         const uint64_t limit = (uint64_t)(0.75 * (double)p->capacity) - reserve;
-        const bool risky = (uint64_t)(p->groupsKnown + p->rowsSinceKnown + n) > limit;
+        const bool bounded = g.keyDomain > 0 && (uint64_t)g.keyDomain <= limit;  // the table can hold every possible key
+        const bool risky = !bounded && (uint64_t)(p->groupsKnown + p->rowsSinceKnown + n) > limit;
         if (risky) {
             pgpu_status st = ensureDev(p, p->failLog, (size_t)n * 8);
             if (st) return st;
@@ -396,8 +416,47 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         TableArgs t = tableOf(p);
         t.limit = limit;
         t.faillog_cap = risky ? (uint64_t)n : 0;
-        void* args[] = {pa.data(), &t, &sc};
-        pgpu_status st = launch(p, v->kPage, grid, kThreads, (size_t)g.smemBytes, args);
+        pgpu_status st;
+        // staged variant (bulk-async ring in shared memory) for pages long enough to fill the ring on every SM and whose
+        // arrays are 16-byte aligned (cp.async.bulk); short or unaligned pages take the direct-load kernel
+        bool staged = v->kPageStaged && n >= (int64_t)g.stagedTile * p->numSMs * 2;
+        if (staged) {
+            for (int c : g.usedChannels) {
+                const ColArg& ca = pg.cols[c];
+                if (((uintptr_t)ca.values | (uintptr_t)ca.nulls | (uintptr_t)ca.offsets | (uintptr_t)ca.ids) & 15) staged = false;
+            }
+        }
+        if (staged) {
+            // whole tiles through the staged kernel, the ragged tail (and the 3 offsets a var-width tile reads past its end)
+            // through the direct kernel: same table, same stream
+            const int64_t nst = (n - 3) / g.stagedTile * g.stagedTile;
+            std::vector<unsigned char> ps = pa;
+            memcpy(ps.data() + sizeof(ColArg) * g.NC, &nst, 8);
+            int nstages = v->stagedStages;
+            void* args[] = {ps.data(), &t, &sc, &nstages};
+            st = launch(p, v->kPageStaged, p->numSMs, g.stagedThreads, v->stagedSmem, args);
+            if (st) return st;
+            const int64_t nt = n - nst;
+            std::vector<ColArg> tc = pg.cols;
+            for (int c : g.usedChannels) {
+                ColArg& ca = tc[c];
+                const Type& ty = p->plan->input[c];
+                if (ca.ids) ca.ids += nst;
+                if (ca.offsets) ca.offsets += nst;                                   // var-width: values stay (offsets are absolute)
+                else if (ca.values) ca.values = (const char*)ca.values + (size_t)nst * ty.width();
+                if (ca.nulls) ca.nulls += nst;
+            }
+            memcpy(ps.data(), tc.data(), sizeof(ColArg) * g.NC);
+            memcpy(ps.data() + sizeof(ColArg) * g.NC, &nt, 8);
+            TableArgs tt = t;
+            tt.row_bias = (uint64_t)nst;  // deferred rows are logged with chunk-relative numbers (the replay runs on the chunk)
+            int tgrid = (int)std::min<int64_t>((nt + kTileRows - 1) / kTileRows, (int64_t)p->numSMs * v->blocksPerSM);
+            void* targs[] = {ps.data(), &tt, &sc};
+            st = launch(p, v->kPage, tgrid, kThreads, (size_t)g.smemBytes, targs);
+        } else {
+            void* args[] = {pa.data(), &t, &sc};
+            st = launch(p, v->kPage, grid, kThreads, (size_t)g.smemBytes, args);
+        }
         if (st) return st;
         p->rowsSinceKnown += n;
         if (!risky) return PGPU_OK;
@@ -584,7 +643,9 @@ pgpu_status stageChunk(pgpu_pipeline* p, Variant* v, const pgpu_column* cols, in
         ColOff& o = offs[c];
         if (col.encoding == PGPU_ENC_PLAIN) {
             if (t.isVarWidth()) {
-                int32_t b0 = col.offsets[r0], b1 = col.offsets[r0 + n];
+                // the slice starts at a 16-byte aligned byte offset so that device pointer + offset keeps the alignment the
+                // bulk-copy path needs
+                int32_t b0 = col.offsets[r0] & ~15, b1 = col.offsets[r0 + n];
                 o.byteBase = b0;
                 o.offsets = add(col.offsets + r0, (size_t)(n + 1) * 4);
                 o.values = add((const char*)col.values + b0, (size_t)(b1 - b0));
