@@ -167,7 +167,7 @@ struct Gen {
                     line("i32 o" + C + "[" + R + " + 1]; { i32 tq[" + R + "]; lds_tile<i32, " + R + ">(" + at(so.offsets) + ", trow, tq); for (int q = 0; q < " + R + "; q++) o" + C + "[q] = tq[q]; o" + C + "[" + R +
                          "] = *reinterpret_cast<const i32*>(" + at(so.offsets) + " + (trow + " + R + ") * 4); }");
                     line("const i32 vb" + C + " = *reinterpret_cast<const i32*>(" + at(so.vbase) + ");");
-                    if (t.kind == TypeKind::VARCHAR && t.precision <= 4)
+                    if (false && t.kind == TypeKind::VARCHAR && t.precision <= 4)
                         line("u64 wl" + C + ", wh" + C + "; lds_byte_window<" + std::to_string(SR * t.precision) + ">(" + at(so.vbytes) + ", o" + C + "[0] - vb" + C + ", o" + C + "[" + R + "] - o" + C + "[0], wl" + C + ", wh" +
                              C + ", err);");
                 } else {
@@ -211,7 +211,9 @@ struct Gen {
             if (cs.encoding == PGPU_ENC_PLAIN) {
                 if (t.isVarWidth()) {
                     int n = t.kind == TypeKind::VARCHAR ? t.precision : 0;
-                    if (t.kind == TypeKind::VARCHAR && n <= 4) {
+                    if (t.kind == TypeKind::VARCHAR && n <= 4 && stagedLoads) {
+                        line("u64 x" + C + ", y" + C + " = 0; lds_varchar<" + std::to_string(n) + ">(st + " + std::to_string(soff[c].vbytes) + ", o" + C + "[r] - vb" + C + ", o" + C + "[r + 1] - o" + C + "[r], x" + C + ", err);");
+                    } else if (t.kind == TypeKind::VARCHAR && n <= 4) {
                         line("u64 x" + C + ", y" + C + " = 0; window_varchar<" + std::to_string(n) + ", " + std::to_string((stagedLoads ? SR : 4) * n) + ">(wl" + C + ", wh" + C + ", o" + C + "[r] - o" + C + "[0], o" + C + "[r + 1] - o" + C + "[r], x" + C + ", err);");
                     } else if (t.kind == TypeKind::VARCHAR && stagedLoads) {
                         line("u64 x" + C + ", y" + C + "; pack_varchar<" + std::to_string(n) + ">((const u8*)(st + " + std::to_string(soff[c].vbytes) + "), o" + C + "[r] - vb" + C + ", o" + C + "[r + 1] - o" + C + "[r], x" + C + ", y" + C + ", err);");
@@ -695,7 +697,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     const int kTile = kStagedWarps * 32 * g.SR;    // rows per stage: every consumer thread owns SR consecutive rows
     bool stagedPossible = true;
     int stageBytes = 0, tailGuard = 0;
-    std::ostringstream issueVar, issueCopies;  // stage_issue(): var-width byte ranges; the bulk copies of lane 0
+    std::ostringstream issueLoad, issueVar, issueCopies;  // stage_issue(): global loads before the stage is free; stores into the stage; bulk copies of lane 0
     unsigned fixedTx = 0;
     {
         auto region = [&](int bytes) {
@@ -725,12 +727,13 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
                 so.vbytes = region(so.vcap + 32);
                 so.vbase = region(16);
                 // byte range of the tile: 16-byte aligned body by bulk copy, the < 16 trailing bytes by the producer lanes
-                issueVar << "        const i32 vb0_" << C << " = a.c[" << C << "].offsets[row0], vb1_" << C << " = a.c[" << C << "].offsets[row0 + " << kTile << "];\n";
-                issueVar << "        i32 s0_" << C << " = vb0_" << C << " & ~15, e1_" << C << " = vb1_" << C << " & ~15;\n";
-                issueVar << "        if (e1_" << C << " < s0_" << C << ") e1_" << C << " = s0_" << C << ";\n";
-                issueVar << "        if (e1_" << C << " - s0_" << C << " > " << so.vcap << ") { err |= PGPU_ERR_VARCHAR_LEN; e1_" << C << " = s0_" << C << " + " << so.vcap << "; }\n";
-                issueVar << "        { const i32 q = e1_" << C << " + lane; if (lane < 16 && q < vb1_" << C << " && q - s0_" << C << " < " << (so.vcap + 16) << ") st[" << so.vbytes << " + (q - s0_" << C
-                         << ")] = ((const u8*)a.c[" << C << "].values)[q]; }\n";
+                issueLoad << "        const i32 vb0_" << C << " = a.c[" << C << "].offsets[row0], vb1_" << C << " = a.c[" << C << "].offsets[row0 + " << kTile << "];\n";
+                issueLoad << "        i32 s0_" << C << " = vb0_" << C << " & ~15, e1_" << C << " = vb1_" << C << " & ~15;\n";
+                issueLoad << "        if (e1_" << C << " < s0_" << C << ") e1_" << C << " = s0_" << C << ";\n";
+                issueLoad << "        if (e1_" << C << " - s0_" << C << " > " << so.vcap << ") { err |= PGPU_ERR_VARCHAR_LEN; e1_" << C << " = s0_" << C << " + " << so.vcap << "; }\n";
+                issueLoad << "        const i32 tq_" << C << " = e1_" << C << " + lane; const bool tl_" << C << " = lane < 16 && tq_" << C << " < vb1_" << C << " && tq_" << C << " - s0_" << C << " < " << (so.vcap + 16) << ";\n";
+                issueLoad << "        u8 tb_" << C << " = 0; if (tl_" << C << ") tb_" << C << " = ((const u8*)a.c[" << C << "].values)[tq_" << C << "];\n";
+                issueVar << "        if (tl_" << C << ") st[" << so.vbytes << " + (tq_" << C << " - s0_" << C << ")] = tb_" << C << ";\n";
                 issueVar << "        if (lane == 0) *reinterpret_cast<i32*>(st + " << so.vbase << ") = s0_" << C << ";\n";
                 issueVar << "        tx += (u32)(e1_" << C << " - s0_" << C << ");\n";
                 issueCopies << "            if (e1_" << C << " > s0_" << C << ") bulk_g2s(st + " << so.vbytes << ", (const char*)a.c[" << C << "].values + s0_" << C << ", (u32)(e1_" << C << " - s0_" << C << "), bar);\n";
@@ -864,10 +867,22 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     res.mode = plan.groupChannels.empty() ? KernelMode::AGG_GLOBAL : KernelMode::AGG_HASH;
 
     // The row body is generated first into a buffer because cells are discovered while generating it.
-    g.out.str("");
+    // (its per-row column prologue exists twice: values from registers loaded out of global memory / out of a stage)
+    std::string rowPrologue, rowPrologueStaged;
     g.indent = 4;
+    g.out.str("");
+    g.emitRowPrologue(restChans);
+    rowPrologue = g.out.str();
+    if (stagedPossible) {
+        g.out.str("");
+        g.stagedLoads = true;
+        g.emitRowPrologue(restChans);
+        g.stagedLoads = false;
+        rowPrologueStaged = g.out.str();
+    }
+    g.out.str("");
     std::map<int, Val> pv;
-    genProjections(pv);
+    for (int c : neededProj) pv[c] = g.gen(*plan.projections[c]);
 
     // ---- keys
     std::vector<KeyField> fields;
@@ -1192,7 +1207,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         src << "        #pragma unroll\n";
         src << "        for (int r = 0; r < 4; r++) {\n";
         src << "            if (sel[r]) {\n";
-        src << rowBody;
+        src << rowPrologue << rowBody;
         src << "            }\n";
         src << "        }\n";
         src << "    }\n";
@@ -1205,13 +1220,15 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         src << "        #pragma unroll\n";
         src << "        for (int r = 0; r < SR; r++) {\n";
         src << "            if (sel[r]) {\n";
-        src << rowBody;
+        src << rowPrologueStaged << rowBody;
         src << "            }\n";
         src << "        }\n";
         src << "    }\n";
         // producer warp: arm the stage's full barrier with the byte count, then hand the copies to the TMA engine
-        src << "    PGPU_DEV static void stage_issue(const PageArgs<NC>& a, i64 row0, unsigned char* st, u64* bar, int lane, u32& err) {\n";
+        src << "    PGPU_DEV static void stage_issue(const PageArgs<NC>& a, i64 row0, unsigned char* st, u64* bar, int lane, u32& err, u64* empty_bar, bool wait_empty, u32 empty_parity) {\n";
         src << "        u32 tx = " << fixedTx << "u;\n";
+        src << issueLoad.str();
+        src << "        if (wait_empty) mbar_wait(empty_bar, empty_parity);\n";
         src << issueVar.str();
         src << "        __syncwarp();\n";
         src << "        if (lane == 0) {\n";

@@ -595,6 +595,8 @@ struct HashCtx {
     u64 *wacc, *dkeys, *myacc;
     u32 *dtags, *dids, *dpos, *dcount;
     u64 racc[RG > 0 ? RG : 1][NHA];
+    u64 rkey[RG > 0 ? RG : 1][KW > 0 ? KW : 1];  // keys of the register-resident groups this thread has met (rmask bit g)
+    u32 rmask;
     bool use_dir;  // warp-uniform
     u32 err;
 
@@ -611,6 +613,7 @@ struct HashCtx {
         myacc = wacc + (size_t)warp * DCAP * NHA;
         use_dir = P::USE_DIR;
         err = 0;
+        rmask = 0;
 #pragma unroll
         for (int g = 0; g < (RG > 0 ? RG : 1); g++) P::identity(racc[g]);
         if (P::USE_DIR) {  // whole block participates; caller synchronises afterwards
@@ -633,12 +636,36 @@ struct HashCtx {
             for (int r = 0; r < R; r++) {
                 slot[r] = -1;
                 if (sel[r]) {
+                    // fast path: the key is one of the register-resident groups this thread already knows — compare and add,
+                    // no hashing, no shared memory
+                    bool hit = false;
+#pragma unroll
+                    for (int g = 0; g < RG; g++) {
+                        bool m = (rmask >> g) & 1u;
+#pragma unroll
+                        for (int i = 0; i < KW; i++) m &= (key[r][i] == rkey[g][i]);
+                        if (m) P::combine(racc[g], cw[r]);
+                        hit |= m;
+                    }
+                    if (hit) {
+                        hits++;
+                        continue;
+                    }
                     const int e = dir_lookup<P>(dkeys, dtags, dids, dpos, dcount, key[r], dir_hash<KW>(key[r]));
                     if (e < 0) {  // 2. not in the (full) directory: straight to the HBM table
                         nmiss++;
                         if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
                     } else if (RG > 0 && (e >> 16) < RG) {
-                        reg_accumulate<P>(racc, e >> 16, cw[r]);
+                        const int id = e >> 16;
+                        reg_accumulate<P>(racc, id, cw[r]);
+#pragma unroll
+                        for (int g = 0; g < RG; g++) {
+                            if (id == g) {
+#pragma unroll
+                                for (int i = 0; i < KW; i++) rkey[g][i] = key[r][i];
+                            }
+                        }
+                        rmask |= 1u << id;
                         hits++;
                     } else {
                         slot[r] = e & 0xffff;
@@ -822,6 +849,17 @@ PGPU_DEV void lds_tile(const unsigned char* col, int trow, T (&v)[R]) {
 #pragma unroll
     for (int r = 0; r < R; r++) v[r] = u.t[r];
 }
+// Short varchar value straight out of a staged byte region: N (<= 4) predicated byte loads, no window arithmetic
+template <int N>
+PGPU_DEV void lds_varchar(const unsigned char* bytes, i32 off, i32 len, u64& x, u32& err) {
+    if (len > N) { err |= PGPU_ERR_VARCHAR_LEN; len = N; }
+    if (len < 0) len = 0;
+    u64 d = 0;
+#pragma unroll
+    for (int k = 0; k < N; k++)
+        if (k < len) d |= (u64)bytes[off + k] << (8 * k);
+    x = (u64)(u32)len | (d << 8);
+}
 // load_byte_window over a staged byte region (`start` is relative to the 16-byte aligned region base)
 template <int MAXB>
 PGPU_DEV void lds_byte_window(const unsigned char* bytes, i32 start, i32 nbytes, u64& lo, u64& hi, u32& err) {
@@ -877,19 +915,22 @@ PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t,
     const i64 mine = blockIdx.x < nfull ? (nfull - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;  // tiles of this block
     if (warp == CW) {
         // ---- producer
+        int s = 0;
+        u32 use = 0;  // how many times the ring has wrapped
         for (i64 it = 0; it < mine; it++) {
-            const int s = (int)(it % nstages);
-            const i64 use = it / nstages;
-            if (use > 0) mbar_wait(empty + s, (u32)((use - 1) & 1));
             const i64 row0 = (blockIdx.x + it * gridDim.x) * TILE;
-            P::stage_issue(a, row0, stages + (size_t)s * P::STAGE_BYTES, full + s, lane, cx.err);
+            // stage_issue first loads what it needs from global memory (var-width byte ranges), then waits for the stage
+            // to be free, then arms the barrier and issues the copies
+            P::stage_issue(a, row0, stages + (size_t)s * P::STAGE_BYTES, full + s, lane, cx.err, empty + s, use > 0, (use - 1) & 1u);
+            if (++s == nstages) { s = 0; use++; }
         }
     } else {
         // ---- consumers
         const int trow = (warp * 32 + lane) * SR;
+        int s = 0;
+        u32 phase = 0;
         for (i64 it = 0; it < mine; it++) {
-            const int s = (int)(it % nstages);
-            mbar_wait(full + s, (u32)((it / nstages) & 1));
+            mbar_wait(full + s, phase);
             const i64 base = (blockIdx.x + it * gridDim.x) * TILE + trow;
             bool sel[SR];
             u64 key[SR][KW];
@@ -898,6 +939,7 @@ PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t,
             __syncwarp();
             if (lane == 0) mbar_arrive(empty + s);  // this warp is done reading the stage
             cx.template consume<SR>(t, base, sel, key, cw);
+            if (++s == nstages) { s = 0; phase ^= 1u; }
         }
     }
     cx.flush(t, CW);
