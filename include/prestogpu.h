@@ -161,16 +161,21 @@ void* pgpu_stream(const pgpu_pipeline* p);
 
 /* Partial -> final exchange (multi-GPU) -----------------------------------------------------------
  * Mirrors PartitionedOutputOperator (main/operator/PartitionedOutputOperator.java:56-133) between a
- * Step.PARTIAL and a Step.FINAL HashAggregationOperator. The collectives themselves (NCCL all-reduce /
- * all-to-all) are issued by the host runtime on the buffers these calls expose. */
-/* Hash-partition the partial output of a PARTIAL-step pipeline into `nparts` contiguous row ranges
- * (device-resident). After the call out_cols describe ONE device page sorted by partition and
- * part_row_offsets[nparts+1] (host) gives the row ranges. */
+ * Step.PARTIAL and a Step.FINAL HashAggregationOperator. The collectives themselves (NCCL all-gather /
+ * all-to-all) are issued by the host runtime on the device buffers these calls expose
+ * (presto_b200/exchange.py; DESIGN.md "Multi-GPU"). */
+/* Hash-partition the complete output of a finishing PARTIAL-step pipeline into `nparts` (<= 64) contiguous
+ * row ranges, device resident. After the call out_cols describe ONE device page sorted by partition and
+ * part_row_offsets[nparts+1] (host) gives the row ranges; the pipeline is finished afterwards.
+ * The partition function is the reference's: (rawHash & 0x7fff_ffff_ffff_ffff) % nparts with
+ * rawHash = 31 * previous + hash(key channel) (main/operator/HashGenerator.java:24-35,
+ * InterpretedHashGenerator.java:66-74, spi/type/AbstractLongType.java:126-130). Key types: BIGINT, INTEGER,
+ * DATE, DOUBLE; other key types are rejected with PGPU_NOT_SUPPORTED (VARCHAR keys hash with airlift's
+ * XxHash64, which is not in the reference tree). */
 pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_column* out_cols, int32_t max_cols,
                                          int32_t* ncols, int64_t* part_row_offsets);
-/* Dense partial state for low-cardinality all-reduce: see DESIGN.md §"Multi-GPU". Exposes the device
- * buffer of the pipeline's compact state image (int64/double cells) for in-place ncclAllReduce. */
-pgpu_status pgpu_dense_state_device(pgpu_pipeline* p, void** dev_ptr, int64_t* n_i64_cells, int64_t* n_f64_cells);
+/* The same partition function for ONE row on the host (kinds: 0 = int64, 1 = int32, 2 = double bits). */
+int32_t pgpu_partition_of(const int64_t* key_bits, const uint8_t* is_null, const int32_t* kinds, int32_t nkeys, int32_t nparts);
 
 /* Pinned host memory helpers (what the JNI shim stages heap arrays into). */
 void* pgpu_host_alloc(size_t bytes);

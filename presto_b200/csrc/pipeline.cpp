@@ -19,6 +19,7 @@
 
 #include "../../include/prestogpu.h"
 #include "codegen.h"
+#include "exchange.h"
 #include "jit.h"
 #include "plan.h"
 
@@ -138,6 +139,10 @@ struct pgpu_pipeline {
     std::vector<DeviceBuf> outDevNulls;
     std::vector<HostOut> outHost, outHostNulls, outHostAux;  // aux: offsets for var-width
     int64_t outCapacityRows = 0;
+    // partitioned output (exchange)
+    std::vector<DeviceBuf> partDev, partDevNulls;
+    DeviceBuf partPid, partDst, partCounts;
+    unsigned long long* hostPart = nullptr;  // pinned: counts[64] + cursors[64]
 };
 
 namespace {
@@ -947,6 +952,12 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
             if (b.ptr) cudaFree(b.ptr);
         for (auto& b : p->outDevNulls)
             if (b.ptr) cudaFree(b.ptr);
+        for (auto* vec : {&p->partDev, &p->partDevNulls})
+            for (auto& b : *vec)
+                if (b.ptr) cudaFree(b.ptr);
+        for (auto* b : {&p->partPid, &p->partDst, &p->partCounts})
+            if (b->ptr) cudaFree(b->ptr);
+        if (p->hostPart) cudaFreeHost(p->hostPart);
         for (auto* vec : {&p->outHost, &p->outHostNulls, &p->outHostAux})
             for (auto& b : *vec)
                 if (b.ptr) cudaFreeHost(b.ptr);
@@ -1206,14 +1217,104 @@ pgpu_status pgpu_memcpy_d2h(int32_t device, void* host_dst, const void* dev_src,
     return cudaMemcpy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
 }
 
-pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t, pgpu_column*, int32_t, int32_t*, int64_t*) {
-    if (!p) return PGPU_INVALID_ARGUMENT;
-    return fail(p, PGPU_NOT_SUPPORTED, "partitioned output: not built yet");
+pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* part_row_offsets) {
+    if (!p || !ncols || !part_row_offsets) return PGPU_INVALID_ARGUMENT;
+    if (p->device < 0) return fail(p, PGPU_INVALID_STATE, "pipeline was created compile-only (device < 0)");
+    const Plan& plan = *p->plan;
+    const GenResult& g = p->layout;
+    if (!plan.hasAgg || plan.groupChannels.empty()) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: partitioned output of a pipeline without grouping keys");
+    if (nparts < 1 || nparts > kMaxParts) return fail(p, PGPU_INVALID_ARGUMENT, "partition count must be in [1, 64]");
+    if (!p->finishing) return fail(p, PGPU_INVALID_STATE, "partitioned output needs finish() first");
+    const int nkeys = (int)plan.groupChannels.size();
+    if (nkeys > kMaxPartKeys) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: more than 8 partitioning channels");
+    if (max_cols < g.NO || !out_cols) return fail(p, PGPU_INVALID_ARGUMENT, "out_cols too small: need " + std::to_string(g.NO));
+    PartKeys keys{};
+    keys.nkeys = nkeys;
+    keys.nparts = nparts;
+    for (int k = 0; k < nkeys; k++) {
+        const Type& t = g.out[k].type;
+        if (t.kind == TypeKind::BIGINT) keys.k[k].kind = PART_KEY_I64;
+        else if (t.kind == TypeKind::INTEGER || t.kind == TypeKind::DATE) keys.k[k].kind = PART_KEY_I32;
+        else if (t.kind == TypeKind::DOUBLE) keys.k[k].kind = PART_KEY_F64;
+        else return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: hash partitioning on " + t.str() + " keys");
+    }
+    for (int c = 0; c < g.NO; c++)
+        if (g.out[c].varWidth && g.out[c].lenPrefixed) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: device-resident var-width output");
+    CU(cudaSetDevice(p->device));
+    for (int i = 0; i <= nparts; i++) part_row_offsets[i] = 0;
+    *ncols = g.NO;
+    int64_t rows = 0;
+    if (!p->finished && (p->outputReady || p->sawInput)) {
+        if (!p->outputReady) {
+            pgpu_status st = buildAggOutput(p);
+            if (st) return st;
+        }
+        rows = p->outRowsTotal - p->outRowsServed;
+    }
+    const int64_t r0 = p->outRowsServed;
+    if ((int)p->partDev.size() != g.NO) {
+        p->partDev.resize(g.NO);
+        p->partDevNulls.resize(g.NO);
+    }
+    if (!p->hostPart) CU(cudaMallocHost((void**)&p->hostPart, 2 * kMaxParts * sizeof(unsigned long long)));
+    const int64_t rr = std::max<int64_t>(rows, 1);
+    pgpu_status st;
+    if ((st = ensureDev(p, p->partPid, (size_t)rr))) return st;
+    if ((st = ensureDev(p, p->partDst, (size_t)rr * 8))) return st;
+    if ((st = ensureDev(p, p->partCounts, 2 * kMaxParts * sizeof(unsigned long long)))) return st;
+    for (int c = 0; c < g.NO; c++) {
+        if ((st = ensureDev(p, p->partDev[c], (size_t)rr * std::max(g.out[c].stride, 1)))) return st;
+        if ((st = ensureDev(p, p->partDevNulls[c], (size_t)rr))) return st;
+    }
+    if (rows > 0) {
+        for (int k = 0; k < nkeys; k++) {
+            keys.k[k].values = (const char*)p->outDev[k].ptr + (size_t)r0 * g.out[k].stride;
+            keys.k[k].nulls = (const uint8_t*)p->outDevNulls[k].ptr + r0;
+        }
+        unsigned long long* dCounts = (unsigned long long*)p->partCounts.ptr;
+        unsigned long long* dCursors = dCounts + kMaxParts;
+        CU(cudaMemsetAsync(dCounts, 0, 2 * kMaxParts * sizeof(unsigned long long), p->stream));
+        CU(partitionCount(p->stream, p->numSMs, keys, rows, (uint8_t*)p->partPid.ptr, dCounts));
+        CU(cudaMemcpyAsync(p->hostPart, dCounts, kMaxParts * sizeof(unsigned long long), cudaMemcpyDeviceToHost, p->stream));
+        CU(cudaStreamSynchronize(p->stream));
+        unsigned long long acc = 0;
+        for (int i = 0; i < nparts; i++) {
+            p->hostPart[kMaxParts + i] = acc;
+            part_row_offsets[i] = (int64_t)acc;
+            acc += p->hostPart[i];
+        }
+        part_row_offsets[nparts] = (int64_t)acc;
+        if ((int64_t)acc != rows) return fail(p, PGPU_CUDA_ERROR, "internal: partition counts do not add up");
+        CU(cudaMemcpyAsync(dCursors, p->hostPart + kMaxParts, kMaxParts * sizeof(unsigned long long), cudaMemcpyHostToDevice, p->stream));
+        CU(partitionAssign(p->stream, p->numSMs, nparts, rows, (const uint8_t*)p->partPid.ptr, dCursors, (int64_t*)p->partDst.ptr));
+        for (int c = 0; c < g.NO; c++) {
+            const int stride = g.out[c].stride;
+            CU(partitionScatter(p->stream, p->numSMs, rows, (const int64_t*)p->partDst.ptr, (const char*)p->outDev[c].ptr + (size_t)r0 * stride, p->partDev[c].ptr, stride));
+            CU(partitionScatter(p->stream, p->numSMs, rows, (const int64_t*)p->partDst.ptr, (const uint8_t*)p->outDevNulls[c].ptr + r0, p->partDevNulls[c].ptr, 1));
+        }
+        p->stats.kernel_launches += 2 + 2 * g.NO;
+        CU(cudaStreamSynchronize(p->stream));
+    }
+    for (int c = 0; c < g.NO; c++) {
+        pgpu_column& oc = out_cols[c];
+        memset(&oc, 0, sizeof oc);
+        oc.encoding = PGPU_ENC_PLAIN;
+        oc.type_kind = (int32_t)g.out[c].type.kind;
+        oc.precision = g.out[c].type.precision;
+        oc.scale = g.out[c].type.scale;
+        oc.position_count = rows;
+        oc.values = p->partDev[c].ptr;
+        oc.nulls = (const uint8_t*)p->partDevNulls[c].ptr;
+    }
+    p->outRowsServed = p->outRowsTotal;
+    p->outputReady = false;
+    p->finished = true;
+    return PGPU_OK;
 }
 
-pgpu_status pgpu_dense_state_device(pgpu_pipeline* p, void**, int64_t*, int64_t*) {
-    if (!p) return PGPU_INVALID_ARGUMENT;
-    return fail(p, PGPU_NOT_SUPPORTED, "dense state: not built yet");
+int32_t pgpu_partition_of(const int64_t* key_bits, const uint8_t* is_null, const int32_t* kinds, int32_t nkeys, int32_t nparts) {
+    if (!key_bits || !is_null || !kinds || nkeys < 0 || nparts < 1) return -1;
+    return partitionOfHost(key_bits, is_null, kinds, nkeys, nparts);
 }
 
 }  // extern "C"

@@ -1,0 +1,213 @@
+"""Partial -> final aggregation exchange across the GPUs of one box (one process per GPU, torch.distributed).
+
+Mirrors what the reference runs between a Step.PARTIAL and a Step.FINAL HashAggregationOperator:
+PartitionedOutputOperator -> exchange -> final operator (core/trino-main/src/main/java/io/trino/operator/
+PartitionedOutputOperator.java:56-133, HashAggregationOperator.java:367-518 with Step.FINAL, whose addIntermediate is
+deserialize + combine, operator/aggregation/AccumulatorCompiler.java:674-767).
+
+Two shapes:
+  * gather  — small group count (Q1, Q6): every rank's partial page is a few rows; they are all-gathered (one padded
+              NCCL all_gather_into_tensor after a size exchange) and every rank runs the FINAL step over all of them,
+              so every rank ends with the final result (the all-reduce shape, without assuming keys line up by slot).
+  * repartition — large group count: rows of the partial output are hash-partitioned on the device by the reference's
+              own partition function (pgpu_partition_output_device), exchanged column by column with
+              all_to_all_single over NVLink, and merged by a FINAL pipeline on the receiving GPU; the result stays
+              partitioned by key, as the output of Trino's final stage does.
+The host logic is backend agnostic (NCCL on GPUs, gloo in the CPU test-suite).
+"""
+from __future__ import annotations
+
+import ctypes
+import pickle
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import _native as N
+from .spi import Block, Page, Type, block_of
+
+PART_KIND = {1: 0, 2: 1, 3: 1, 4: 2}  # type kind -> pgpu_partition_of kind (BIGINT, INTEGER, DATE, DOUBLE)
+
+
+# ------------------------------------------------------------------------------------------------ helpers
+class _DeviceBytes:
+    """Zero-copy view of library-owned device memory for torch (torch.as_tensor understands __cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def device_bytes_tensor(ptr: int, nbytes: int, device):
+    import torch
+    if nbytes == 0 or not ptr:
+        return torch.empty(0, dtype=torch.uint8, device=device)
+    return torch.as_tensor(_DeviceBytes(ptr, nbytes), device=device)
+
+
+def _pages_to_blob(pages: Sequence[Page]) -> bytes:
+    payload = []
+    for p in pages:
+        cols = []
+        for b in p.blocks:
+            cols.append((b.type.kind, b.type.precision, b.type.scale, b.to_pylist()))
+        payload.append((p.position_count, cols))
+    return pickle.dumps(payload, protocol=4)
+
+
+def _blob_to_pages(blob: bytes) -> List[Page]:
+    out = []
+    for rows, cols in pickle.loads(blob):
+        blocks = [block_of(Type(k, pr, sc), vals) for k, pr, sc, vals in cols]
+        out.append(Page(*blocks, positionCount=rows))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ gather (small)
+def gather_partial_pages(pages: Sequence[Page], device=None, group=None) -> List[Page]:
+    """All ranks receive the partial pages of all ranks, in rank order (small group counts: the pages are a few rows)."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return list(pages)
+    world = dist.get_world_size(group)
+    dev = device if device is not None else torch.device("cpu")
+    blob = np.frombuffer(_pages_to_blob(pages), dtype=np.uint8)
+    size = torch.tensor([blob.size], dtype=torch.int64, device=dev)
+    sizes = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(sizes, size, group=group)
+    sizes_h = sizes.cpu().tolist()
+    cap = max(sizes_h)
+    send = torch.zeros(cap, dtype=torch.uint8, device=dev)
+    send[:blob.size] = torch.from_numpy(blob.copy()).to(dev)
+    recv = torch.empty(world * cap, dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    recv_h = recv.cpu().numpy()
+    out: List[Page] = []
+    for r in range(world):
+        out.extend(_blob_to_pages(recv_h[r * cap:r * cap + sizes_h[r]].tobytes()))
+    return out
+
+
+def final_over_pages(final_operator, pages: Sequence[Page]) -> List[Page]:
+    from .operators import toPages
+    return toPages(final_operator, [p for p in pages if p.position_count])
+
+
+# ------------------------------------------------------------------------------------------------ repartition (host logic)
+def partition_of_row(key_values: Sequence, key_types: Sequence[Type], nparts: int) -> int:
+    """The reference's partition function for one row of key values (None = NULL)."""
+    n = len(key_values)
+    bits = (ctypes.c_int64 * n)()
+    nulls = (ctypes.c_uint8 * n)()
+    kinds = (ctypes.c_int32 * n)()
+    for i, (v, t) in enumerate(zip(key_values, key_types)):
+        if t.kind not in PART_KIND:
+            raise ValueError("hash partitioning on %s keys is not supported" % t)
+        kinds[i] = PART_KIND[t.kind]
+        if v is None:
+            nulls[i] = 1
+        elif t.kind == 4:
+            bits[i] = int(np.array([v], dtype=np.float64).view(np.int64)[0])
+        else:
+            bits[i] = int(v)
+    return N.lib().pgpu_partition_of(bits, nulls, kinds, n, nparts)
+
+
+def partition_pages_host(pages: Sequence[Page], nkeys: int, nparts: int) -> List[List[Page]]:
+    """Host restatement of PartitionedOutputOperator.partitionPage for small pages: one page list per partition."""
+    buckets: List[List[list]] = [[] for _ in range(nparts)]
+    types: Optional[List[Type]] = None
+    for p in pages:
+        types = [b.type for b in p.blocks]
+        for row in p.to_rows():
+            buckets[partition_of_row(row[:nkeys], types[:nkeys], nparts)].append(row)
+    out: List[List[Page]] = []
+    for rows in buckets:
+        if not rows or types is None:
+            out.append([])
+            continue
+        cols = list(zip(*rows))
+        out.append([Page(*[block_of(t, list(c)) for t, c in zip(types, cols)], positionCount=len(rows))])
+    return out
+
+
+def exchange_pages_host(per_dest: Sequence[Sequence[Page]], device=None, group=None) -> List[Page]:
+    """All-to-all of small host pages (per_dest[r] goes to rank r); returns what this rank received, in source-rank order."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return [p for pages in per_dest for p in pages]
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    blobs = [_pages_to_blob(list(pages)) for pages in per_dest]
+    gathered: List[Optional[list]] = [None] * world
+    dist.all_gather_object(gathered, blobs, group=group)
+    out: List[Page] = []
+    for src in range(world):
+        out.extend(_blob_to_pages(gathered[src][rank]))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ repartition (device)
+class DeviceRepartition:
+    """PARTIAL pipeline -> hash partition on the device -> NCCL all_to_all_single per column -> FINAL pipeline.
+
+    `partial` must be finishing (finish() called); `final` is a FINAL-step GpuPipelineOperator whose input channels are the
+    partial pipeline's output channels. After run() the final operator holds this rank's partition of the groups."""
+
+    def __init__(self, device: int, world: int, rank: int, group=None):
+        self.device, self.world, self.rank, self.group = device, world, rank, group
+        self.recv_keepalive: list = []
+        self.sent_bytes = 0
+        self.recv_rows = 0
+
+    def run(self, partial, final) -> int:
+        import torch
+        import torch.distributed as dist
+        L = N.lib()
+        dev = torch.device("cuda", self.device)
+        ncap = max(L.pgpu_output_channel_count(partial._h), 1)
+        cols = (N.Column * ncap)()
+        nc = ctypes.c_int32()
+        offs = (ctypes.c_int64 * (self.world + 1))()
+        partial._check(L.pgpu_partition_output_device(partial._h, self.world, cols, ncap, ctypes.byref(nc), offs))
+        types = partial.outputTypes()
+        send_rows = [offs[i + 1] - offs[i] for i in range(self.world)]
+        if self.world > 1:
+            send_t = torch.tensor(send_rows, dtype=torch.int64, device=dev)
+            recv_t = torch.empty(self.world, dtype=torch.int64, device=dev)
+            dist.all_to_all_single(recv_t, send_t, group=self.group)
+            recv_rows = recv_t.cpu().tolist()
+        else:
+            recv_rows = list(send_rows)
+        total_recv = int(sum(recv_rows))
+        total_send = int(offs[self.world])
+        self.recv_rows = total_recv
+        self.recv_keepalive = []
+        fcols = (N.Column * nc.value)()
+        for c in range(nc.value):
+            t = types[c]
+            width = 16 if t.is_long_decimal else {0: 1, 1: 8, 2: 4, 3: 4, 4: 8, 5: 8}.get(t.kind)
+            if width is None:
+                raise RuntimeError("device repartition of %s channels is not supported" % t)
+            bufs = []
+            for ptr, w in ((cols[c].values, width), (cols[c].nulls, 1)):
+                src = device_bytes_tensor(ptr, total_send * w, dev)
+                if self.world > 1:
+                    dst = torch.empty(max(total_recv * w, 16), dtype=torch.uint8, device=dev)
+                    dist.all_to_all_single(dst[:total_recv * w], src, [r * w for r in recv_rows], [r * w for r in send_rows], group=self.group)
+                    self.sent_bytes += (total_send - send_rows[self.rank]) * w
+                else:
+                    dst = src
+                bufs.append(dst)
+            self.recv_keepalive.extend(bufs)
+            fc = fcols[c]
+            fc.encoding = N.ENC_PLAIN
+            fc.type_kind, fc.precision, fc.scale = t.kind, t.precision, t.scale
+            fc.position_count = total_recv
+            fc.values = bufs[0].data_ptr() if total_recv else None
+            fc.nulls = bufs[1].data_ptr() if total_recv else None
+        if self.world > 1:
+            torch.cuda.current_stream(dev).synchronize()  # the FINAL pipeline reads the received buffers on its own stream
+        if total_recv:
+            final.addDeviceInput(fcols, nc.value, total_recv)
+        final.finish()
+        return total_recv
