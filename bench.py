@@ -19,6 +19,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 SF100_ROWS = 600_037_902  # TPC-H lineitem at sf100
+# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the ncu --set full captures under
+# profiles/ (bytes; None = not captured for that workload)
+# stored as measured DRAM bytes / algorithmic bytes of the captured launch (profiles/r01c_q1_staged_ncu_raw.csv)
+TRAFFIC_RATIO = {"q1": 1.0014}
 
 
 def parse_args():
@@ -184,72 +188,116 @@ def final_plan_for(wl, partial_plan):
     if name == "q6":
         return plan_text([BIGINT, DOUBLE], step="final", aggregations=[Aggregation("sum", DOUBLE, 0, DOUBLE)])
     return plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0], aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)],
-                     expectedGroups=10_000_000)
+                     expectedGroups=max(wl.get("rows", 40_000_000) // 4, 1000))
 
 
 # ------------------------------------------------------------------------------------------------ GPU legs
+def drain_output(op, to_host):
+    """Operator.getOutput() until isFinished(), through the raw C ABI (no Python-side page copies). Returns rows."""
+    from presto_b200 import _native as N
+    L = N.lib()
+    n = max(L.pgpu_output_channel_count(op._h), 1)
+    cols = (N.Column * n)()
+    nc, rows = ctypes.c_int32(), ctypes.c_int64()
+    total = 0
+    fn = L.pgpu_get_output if to_host else L.pgpu_get_output_device
+    while not L.pgpu_is_finished(op._h):
+        op._check(fn(op._h, cols, n, ctypes.byref(nc), ctypes.byref(rows)))
+        if rows.value > 0:
+            total += rows.value
+    return total
+
+
 def run_device_steps(args, wl, device, dist):
-    """`value`: inputs resident in HBM before the timed region. Times each step with CUDA events on the pipeline's
-    stream; the barrier + synchronize bracket and the max over ranks follow the bench contract."""
+    """`value`: inputs resident in HBM before the timed region. One step = reset, one pass of the fused pipeline over the
+    rank's shard, and (N > 1) the partial -> final exchange. Timed with CUDA events recorded on an idle device on both
+    sides (barrier + synchronize), max over ranks taken by the caller."""
     import torch
     from presto_b200 import _native as N
+    from presto_b200 import exchange as X
     from presto_b200 import tpch
-    from presto_b200.operators import GpuPipelineOperator
+    from presto_b200.operators import GpuPipelineOperator, toPages
     L = N.lib()
     rows = args.rows
-    first = dist["rank"] * rows
-    total = rows * dist["world"]
+    world, rank = dist["world"], dist["rank"]
+    first = rank * rows
+    total = rows * world
     dp = tpch.DevicePage(device, wl["spec"], rows, first_row=first, total_rows=total)
-    op = GpuPipelineOperator(wl["plan"]("single" if dist["world"] == 1 else "partial"), device)
-    stream = torch.cuda.ExternalStream(L.pgpu_stream(op._h), device=torch.device("cuda", device))
+    single = world == 1
+    op = GpuPipelineOperator(wl["plan"]("single" if single else "partial"), device)
+    final = None if single else GpuPipelineOperator(final_plan_for(wl, None), device)
     ncol = len(wl["spec"])
+    small = wl["name"] in ("q1", "q1dict", "q6")   # result is a handful of rows: host output / gather exchange
+    tdev = torch.device("cuda", device)
+    repart = None if single or small else X.DeviceRepartition(device, world, rank)
+    state = {"result_rows": 0, "exchange_bytes": 0}
 
     def one_step():
         op.reset()
         op.addDeviceInput(dp.cols, ncol, rows)
         op.finish()
-        out = []
-        while not op.isFinished():
-            p = op.getOutput()
-            if p is not None:
-                out.append(p)
-        return out
+        if single:
+            state["result_rows"] = drain_output(op, to_host=small)
+            return
+        final.reset()
+        if small:
+            partial_pages = []
+            while not op.isFinished():
+                p = op.getOutput()
+                if p is not None:
+                    partial_pages.append(p)
+            gathered = X.gather_partial_pages(partial_pages, device=tdev)
+            state["result_rows"] = sum(p.position_count for p in toPages(final, gathered))
+        else:
+            repart.run(op, final)
+            state["result_rows"] = drain_output(final, to_host=False)
+            state["exchange_bytes"] = repart.sent_bytes
 
     def barrier():
-        if dist["world"] > 1:
+        if world > 1:
             import torch.distributed as td
             td.barrier()
         torch.cuda.synchronize(device)
 
-    result = None
+    def launches():
+        n = op.stats().kernel_launches
+        return n + (final.stats().kernel_launches if final is not None else 0)
+
     for _ in range(args.warmup):
-        result = one_step()
+        one_step()
     sampler = ClockSampler(device)
     sampler.start()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
-    e0.record(stream)
-    launches = 0
+    e0.record()
+    nl = 0
     for _ in range(args.steps):
-        result = one_step()
-        launches += op.stats().kernel_launches
-    e1.record(stream)
+        one_step()
+        nl += launches()
     barrier()
+    e1.record()
+    e1.synchronize()
     wall = time.perf_counter() - t0
     dev_ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
     # dominant kernel alone: per-launch CUDA-event durations (pgpu_set_timing brackets every page-kernel launch)
     op.setTiming(True)
     kern_ms, kern_launches = 0.0, 0
-    for _ in range(max(3, min(args.steps, 5))):
-        one_step()
+    ksteps = max(3, min(args.steps, 5))
+    for _ in range(ksteps):
+        op.reset()
+        op.addDeviceInput(dp.cols, ncol, rows)
+        op.sync()
         st = op.stats()
         kern_ms += st.device_ms
         kern_launches += st.kernel_launches
     op.setTiming(False)
-    info = dict(dev_ms=dev_ms, wall_s=wall, launches=launches, clocks=clocks, kern_ms=kern_ms, kern_launches=kern_launches,
-                kern_steps=max(3, min(args.steps, 5)), result=result, table_capacity=op.stats().table_capacity)
+    info = dict(dev_ms=dev_ms, wall_s=wall, launches=nl, clocks=clocks, kern_ms=kern_ms, kern_launches=kern_launches,
+                kern_steps=ksteps, result_rows=state["result_rows"], table_capacity=op.stats().table_capacity,
+                exchange_bytes=state["exchange_bytes"])
+    if final is not None:
+        final.close()
     return info, dp, op
 
 
@@ -312,12 +360,7 @@ def run_e2e_steps(args, wl, device, dp_device, steps, warmup):
         op.reset()
         op._check(L.pgpu_add_page(op._h, cols, len(wl["spec"]), rows, N.PAGE_PINNED))
         op.finish()
-        out = []
-        while not op.isFinished():
-            p = op.getOutput()
-            if p is not None:
-                out.append(p)
-        return out
+        return drain_output(op, to_host=True)
 
     for _ in range(warmup):
         one_step()
@@ -341,6 +384,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     wl = workload_def(args.workload, args.rows)
     wl["name"] = args.workload
+    wl["rows"] = args.rows if args.impl == "ours" else args.cpu_rows_per_core
     cores = os.cpu_count() or 1
     metric = "lineitem_rows_per_second"
     config = {"workload": wl["label"], "rows_per_gpu": args.rows, "scale_factor_equivalent": round(args.rows / 6_001_215, 2),
@@ -388,8 +432,12 @@ def main():
     peak, peak_src = measured_peak()
     kern_rows = args.rows * info["kern_steps"]
     achieved = kern_rows * wl["bytes_per_row"] / (info["kern_ms"] / 1000.0) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": "pgpu_k_page (fused scan+filter+project+hash-aggregate)", "peak_source": peak_src,
+    kname = "pgpu_k_page_staged (cp.async.bulk ring + register-resident groups)" if args.workload in ("q1", "q1dict") else "pgpu_k_page (fused scan+filter+project+aggregate, direct loads)"
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": (TRAFFIC_RATIO[args.workload] * kern_rows * wl["bytes_per_row"] / max(info["kern_launches"], 1)) if args.workload in TRAFFIC_RATIO else None,
+                "bytes_per_launch": kern_rows * wl["bytes_per_row"] / max(info["kern_launches"], 1),
+                "avg_launch_ms": info["kern_ms"] / max(info["kern_launches"], 1),
+                "kernel": kname, "peak_source": peak_src,
                 "launches_timed": info["kern_launches"], "algorithmic_bytes_per_row": wl["bytes_per_row"]}
     e2e = None
     if not args.no_e2e and world == 1:
@@ -409,7 +457,9 @@ def main():
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": config, "gb_per_s": value * wl["bytes_per_row"] / 1e9,
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": info["launches"], "clocks": info["clocks"],
-                "table_capacity_slots": info["table_capacity"]}
+                "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"],
+                "exchange": None if world == 1 else {"shape": "gather (all ranks run FINAL over all partial pages)" if args.workload in ("q1", "q1dict", "q6") else "hash repartition + all_to_all_single + FINAL per rank",
+                                                     "bytes_sent_per_rank_per_step": info["exchange_bytes"]}}
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as td

@@ -1,0 +1,77 @@
+"""Device side of the partial -> final exchange on one GPU: pgpu_partition_output_device places every row in the
+partition the reference's function assigns, and PARTIAL -> partition -> FINAL equals the single-step result."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from presto_b200 import _native as N
+from presto_b200 import exchange as X
+from presto_b200 import tpch
+from presto_b200.operators import Aggregation, GpuPipelineOperator, plan_text
+from presto_b200.spi import BIGINT, DOUBLE
+from util import assert_rows_equal_ignore_order, rows_of, run_gpu, run_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _d2h(ptr, nbytes, dtype):
+    out = np.empty(nbytes // np.dtype(dtype).itemsize, dtype=dtype)
+    if nbytes:
+        assert N.lib().pgpu_memcpy_d2h(0, out.ctypes.data, ptr, nbytes) == 0
+    return out
+
+
+@pytest.mark.parametrize("nparts", [1, 3, 8])
+def test_partition_output_device(nparts):
+    total = 300_000
+    pages = [tpch.highcard_page(0, total, total, shuffled=True)]
+    op = GpuPipelineOperator(tpch.highcard_plan(1000, "partial"), 0)
+    try:
+        for p in pages:
+            op.addInput(p)
+        op.finish()
+        L = N.lib()
+        cols = (N.Column * 8)()
+        nc = ctypes.c_int32()
+        offs = (ctypes.c_int64 * (nparts + 1))()
+        op._check(L.pgpu_partition_output_device(op._h, nparts, cols, 8, ctypes.byref(nc), offs))
+        assert nc.value == 3 and op.isFinished()
+        rows = offs[nparts]
+        keys = _d2h(cols[0].values, rows * 8, np.int64)
+        cnt = _d2h(cols[1].values, rows * 8, np.int64)
+        sums = _d2h(cols[2].values, rows * 8, np.float64)
+    finally:
+        op.close()
+    exp = run_oracle(tpch.highcard_plan(1000, "partial"), pages)
+    assert rows == len(exp) and len(set(keys.tolist())) == rows
+    for part in range(nparts):
+        for k in keys[offs[part]:offs[part + 1]][:2000].tolist():
+            assert X.partition_of_row([k], [BIGINT], nparts) == part
+    assert_rows_equal_ignore_order(list(zip(keys.tolist(), cnt.tolist(), sums.tolist())), exp, nkeys=1)
+
+
+def test_partial_partition_final_equals_single():
+    import torch
+    total = 400_000
+    pages = [tpch.highcard_page(0, total // 2, total), tpch.highcard_page(total // 2, total // 2, total)]
+    single = run_gpu(tpch.highcard_plan(1000), pages)
+    partial = GpuPipelineOperator(tpch.highcard_plan(1000, "partial"), 0)
+    final = GpuPipelineOperator(plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0],
+                                          aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)], expectedGroups=200_000), 0)
+    try:
+        for p in pages:
+            partial.addInput(p)
+        partial.finish()
+        ex = X.DeviceRepartition(0, 1, 0)
+        n = ex.run(partial, final)   # world 1: partition + FINAL merge on the same device, no collective
+        assert n == len(single)
+        out = []
+        while not final.isFinished():
+            p = final.getOutput()
+            if p is not None:
+                out.append(p)
+        assert_rows_equal_ignore_order(rows_of(out), single, nkeys=1)
+    finally:
+        partial.close()
+        final.close()
