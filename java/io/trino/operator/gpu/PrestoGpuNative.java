@@ -1,0 +1,53 @@
+/*
+ * JNI surface of libprestogpu (include/prestogpu.h). NOT COMPILED IN THIS REPOSITORY'S IMAGE (no JDK); this is the
+ * binding a Trino 359 maintainer adds next to io.trino.operator. One long handle = one pgpu_pipeline = one Operator.
+ */
+package io.trino.operator.gpu;
+
+final class PrestoGpuNative
+{
+    static {
+        System.loadLibrary("prestogpu_jni"); // jni/prestogpu_jni.c, links libprestogpu.so
+    }
+
+    private PrestoGpuNative() {}
+
+    /** pgpu_pipeline_create: plan text (DESIGN.md "Plan language"); throws TrinoException(NOT_SUPPORTED | COMPILER_ERROR ...). */
+    static native long create(byte[] plan, int device);
+
+    /** pgpu_pipeline_destroy — Operator.close(). */
+    static native void destroy(long handle);
+
+    /** pgpu_needs_input — Operator.needsInput(). */
+    static native boolean needsInput(long handle);
+
+    /**
+     * pgpu_add_page — Operator.addInput(Page). One entry per channel:
+     * encoding[c] (0 plain, 1 dictionary, 2 RLE), typeKind/precision/scale[c], and the block's backing arrays
+     * (long[] / int[] / byte[] / boolean[]; null when absent). The shim pins each array with
+     * GetPrimitiveArrayCritical, copies it into the pipeline's pinned staging ring and releases it before returning,
+     * so Trino's immutable Blocks are never retained.
+     */
+    static native void addPage(long handle, int positionCount, int[] encoding, int[] typeKind, int[] precision, int[] scale,
+            Object[] values, int[] valuesOffset, boolean[][] valueIsNull, int[][] offsets, int[][] ids, int[] idsOffset,
+            Object[] dictionaryValues, boolean[][] dictionaryIsNull, int[][] dictionaryOffsets, int[] dictionaryPositionCount);
+
+    /** pgpu_finish — Operator.finish(). */
+    static native void finish(long handle);
+
+    /** pgpu_is_finished — Operator.isFinished(). */
+    static native boolean isFinished(long handle);
+
+    /**
+     * pgpu_get_output — Operator.getOutput(). Returns null when there is no page now; otherwise
+     * [positionCount (Integer), then per channel: values array (long[] / int[] / byte[]), boolean[] valueIsNull or null,
+     * int[] offsets or null]. Arrays are fresh Java arrays (the library-owned pinned buffers are copied out).
+     */
+    static native Object[] getOutput(long handle);
+
+    /** pgpu_output_channel_count / pgpu_output_channel_type. */
+    static native int[] outputTypes(long handle); // kind, precision, scale triples
+
+    /** pgpu_last_error. */
+    static native String lastError(long handle);
+}

@@ -1,0 +1,114 @@
+/*
+ * JNI shim between io.trino.operator.gpu.PrestoGpuNative and libprestogpu (include/prestogpu.h).
+ * NOT BUILT by __graft_entry__.build(): this image has no JDK (no jni.h). Build where one exists with
+ *   gcc -shared -fPIC -I$JAVA_HOME/include -I$JAVA_HOME/include/linux -Iinclude jni/prestogpu_jni.c \
+ *       -Lpresto_b200 -lprestogpu -o libprestogpu_jni.so
+ * Only the hot entry point (addPage) and the error mapping are spelled out; the remaining natives are one-line
+ * forwards to the C ABI call named in PrestoGpuNative.java.
+ */
+#include <jni.h>
+#include <string.h>
+
+#include "prestogpu.h"
+
+/* io.trino.spi.StandardErrorCode names, indexed by pgpu_status */
+static const char* const kErrorCode[] = {"OK", "NOT_SUPPORTED", "GENERIC_INTERNAL_ERROR", "NUMERIC_VALUE_OUT_OF_RANGE", "DIVISION_BY_ZERO",
+                                         "GENERIC_INSUFFICIENT_RESOURCES", "COMPILER_ERROR", "GENERIC_INTERNAL_ERROR", "GENERIC_INTERNAL_ERROR",
+                                         "INVALID_CAST_ARGUMENT"};
+
+static void throwTrino(JNIEnv* env, pgpu_status st, const char* msg) {
+    /* new TrinoException(StandardErrorCode.valueOf(name), msg) */
+    jclass codes = (*env)->FindClass(env, "io/trino/spi/StandardErrorCode");
+    jmethodID valueOf = (*env)->GetStaticMethodID(env, codes, "valueOf", "(Ljava/lang/String;)Lio/trino/spi/StandardErrorCode;");
+    jobject code = (*env)->CallStaticObjectMethod(env, codes, valueOf, (*env)->NewStringUTF(env, kErrorCode[st]));
+    jclass ex = (*env)->FindClass(env, "io/trino/spi/TrinoException");
+    jmethodID ctor = (*env)->GetMethodID(env, ex, "<init>", "(Lio/trino/spi/ErrorCodeSupplier;Ljava/lang/String;)V");
+    (*env)->Throw(env, (jthrowable)(*env)->NewObject(env, ex, ctor, code, (*env)->NewStringUTF(env, msg)));
+}
+
+JNIEXPORT jlong JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_create(JNIEnv* env, jclass cls, jbyteArray plan, jint device) {
+    jsize n = (*env)->GetArrayLength(env, plan);
+    jbyte* text = (*env)->GetByteArrayElements(env, plan, NULL);
+    pgpu_pipeline* p = NULL;
+    pgpu_status st = pgpu_pipeline_create((const uint8_t*)text, (size_t)n, device, &p);
+    (*env)->ReleaseByteArrayElements(env, plan, text, JNI_ABORT);
+    if (st != PGPU_OK) {
+        throwTrino(env, st, pgpu_last_global_error());
+        return 0;
+    }
+    return (jlong)(intptr_t)p;
+}
+
+/*
+ * addPage: every Java heap array is pinned with GetPrimitiveArrayCritical only for the duration of pgpu_add_page, which
+ * copies it into the pipeline's pinned staging ring (flags = 0) before returning — Trino's blocks are never retained and no
+ * JNI call is made while arrays are pinned.
+ */
+#define MAX_CH 64
+JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addPage(JNIEnv* env, jclass cls, jlong handle, jint positionCount, jintArray encoding,
+        jintArray typeKind, jintArray precision, jintArray scale, jobjectArray values, jintArray valuesOffset, jobjectArray valueIsNull,
+        jobjectArray offsets, jobjectArray ids, jintArray idsOffset, jobjectArray dictValues, jobjectArray dictIsNull, jobjectArray dictOffsets,
+        jintArray dictPositionCount) {
+    pgpu_pipeline* p = (pgpu_pipeline*)(intptr_t)handle;
+    jsize nc = (*env)->GetArrayLength(env, encoding);
+    pgpu_column cols[MAX_CH], dicts[MAX_CH];
+    jarray pinned[MAX_CH * 8];
+    void* pinnedPtr[MAX_CH * 8];
+    int npinned = 0;
+    jint enc[MAX_CH], kind[MAX_CH], prec[MAX_CH], sc[MAX_CH], voff[MAX_CH], ioff[MAX_CH], dcount[MAX_CH];
+    if (nc > MAX_CH) { throwTrino(env, PGPU_NOT_SUPPORTED, "more than 64 channels"); return; }
+    (*env)->GetIntArrayRegion(env, encoding, 0, nc, enc);
+    (*env)->GetIntArrayRegion(env, typeKind, 0, nc, kind);
+    (*env)->GetIntArrayRegion(env, precision, 0, nc, prec);
+    (*env)->GetIntArrayRegion(env, scale, 0, nc, sc);
+    (*env)->GetIntArrayRegion(env, valuesOffset, 0, nc, voff);
+    (*env)->GetIntArrayRegion(env, idsOffset, 0, nc, ioff);
+    (*env)->GetIntArrayRegion(env, dictPositionCount, 0, nc, dcount);
+    /* collect the array references first (JNI calls are not allowed inside the critical region) */
+    jarray aValues[MAX_CH], aNulls[MAX_CH], aOffsets[MAX_CH], aIds[MAX_CH], aDV[MAX_CH], aDN[MAX_CH], aDO[MAX_CH];
+    for (jsize c = 0; c < nc; c++) {
+        aValues[c] = (jarray)(*env)->GetObjectArrayElement(env, values, c);
+        aNulls[c] = (jarray)(*env)->GetObjectArrayElement(env, valueIsNull, c);
+        aOffsets[c] = (jarray)(*env)->GetObjectArrayElement(env, offsets, c);
+        aIds[c] = (jarray)(*env)->GetObjectArrayElement(env, ids, c);
+        aDV[c] = (jarray)(*env)->GetObjectArrayElement(env, dictValues, c);
+        aDN[c] = (jarray)(*env)->GetObjectArrayElement(env, dictIsNull, c);
+        aDO[c] = (jarray)(*env)->GetObjectArrayElement(env, dictOffsets, c);
+    }
+#define PIN(arr) ((arr) ? (pinned[npinned] = (arr), pinnedPtr[npinned] = (*env)->GetPrimitiveArrayCritical(env, (arr), NULL), pinnedPtr[npinned++]) : NULL)
+    static const int width[] = {1, 8, 4, 4, 8, 8, 1, 1};
+    for (jsize c = 0; c < nc; c++) {
+        pgpu_column* col = &cols[c];
+        memset(col, 0, sizeof *col);
+        col->encoding = enc[c]; col->type_kind = kind[c]; col->precision = prec[c]; col->scale = sc[c];
+        col->position_count = positionCount;
+        int w = (kind[c] == PGPU_DECIMAL && prec[c] > 18) ? 16 : width[kind[c]];
+        if (enc[c] == PGPU_ENC_PLAIN) {
+            char* v = (char*)PIN(aValues[c]);
+            int varWidth = kind[c] == PGPU_VARCHAR || kind[c] == PGPU_VARBINARY;
+            col->values = v ? v + (varWidth ? 0 : (size_t)voff[c] * w) : NULL;      /* boolean[] is 1 byte per element */
+            col->nulls = (const uint8_t*)PIN(aNulls[c]);
+            if (col->nulls) col->nulls += voff[c];
+            col->offsets = (const int32_t*)PIN(aOffsets[c]);
+            if (col->offsets) col->offsets += voff[c];
+        } else {
+            pgpu_column* d = &dicts[c];
+            memset(d, 0, sizeof *d);
+            d->encoding = PGPU_ENC_PLAIN; d->type_kind = kind[c]; d->precision = prec[c]; d->scale = sc[c];
+            d->position_count = dcount[c];
+            d->values = PIN(aDV[c]);
+            d->nulls = (const uint8_t*)PIN(aDN[c]);
+            d->offsets = (const int32_t*)PIN(aDO[c]);
+            col->dictionary = d;
+            if (enc[c] == PGPU_ENC_DICTIONARY) col->ids = (const int32_t*)PIN(aIds[c]) + ioff[c];
+        }
+    }
+    pgpu_status st = pgpu_add_page(p, cols, (int32_t)nc, positionCount, 0);
+    for (int i = npinned - 1; i >= 0; i--) (*env)->ReleasePrimitiveArrayCritical(env, pinned[i], pinnedPtr[i], JNI_ABORT);
+    if (st != PGPU_OK) throwTrino(env, st, pgpu_last_error(p));
+}
+
+JNIEXPORT jboolean JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_needsInput(JNIEnv* env, jclass cls, jlong h) { return pgpu_needs_input((pgpu_pipeline*)(intptr_t)h) != 0; }
+JNIEXPORT jboolean JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_isFinished(JNIEnv* env, jclass cls, jlong h) { return pgpu_is_finished((pgpu_pipeline*)(intptr_t)h) != 0; }
+JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_finish(JNIEnv* env, jclass cls, jlong h) { pgpu_finish((pgpu_pipeline*)(intptr_t)h); }
+JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_destroy(JNIEnv* env, jclass cls, jlong h) { pgpu_pipeline_destroy((pgpu_pipeline*)(intptr_t)h); }

@@ -26,6 +26,7 @@ import numpy as np
 from . import _native as N
 from .spi import Block, Page, Type, block_of
 
+_FRAME = 32 * 1024
 PART_KIND = {1: 0, 2: 1, 3: 1, 4: 2}  # type kind -> pgpu_partition_of kind (BIGINT, INTEGER, DATE, DOUBLE)
 
 
@@ -72,19 +73,28 @@ def gather_partial_pages(pages: Sequence[Page], device=None, group=None) -> List
     world = dist.get_world_size(group)
     dev = device if device is not None else torch.device("cpu")
     blob = np.frombuffer(_pages_to_blob(pages), dtype=np.uint8)
-    size = torch.tensor([blob.size], dtype=torch.int64, device=dev)
-    sizes = torch.empty(world, dtype=torch.int64, device=dev)
-    dist.all_gather_into_tensor(sizes, size, group=group)
-    sizes_h = sizes.cpu().tolist()
-    cap = max(sizes_h)
-    send = torch.zeros(cap, dtype=torch.uint8, device=dev)
-    send[:blob.size] = torch.from_numpy(blob.copy()).to(dev)
-    recv = torch.empty(world * cap, dtype=torch.uint8, device=dev)
-    dist.all_gather_into_tensor(recv, send, group=group)
-    recv_h = recv.cpu().numpy()
+    # one collective in the common case: [8-byte length | payload] in a fixed 32 KB frame; every rank sees every length,
+    # so all ranks agree on whether a second, larger round is needed
+    cap = _FRAME
+    rounds = 0
+    while True:
+        frame = np.zeros(cap, dtype=np.uint8)
+        frame[:8] = np.frombuffer(np.int64(blob.size).tobytes(), dtype=np.uint8)
+        n = min(blob.size, cap - 8)
+        frame[8:8 + n] = blob[:n]
+        send = torch.from_numpy(frame).to(dev)
+        recv = torch.empty(world * cap, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(recv, send, group=group)
+        recv_h = recv.cpu().numpy()
+        sizes = [int(np.frombuffer(recv_h[r * cap:r * cap + 8].tobytes(), dtype=np.int64)[0]) for r in range(world)]
+        rounds += 1
+        if max(sizes) <= cap - 8:
+            break
+        cap = (max(sizes) + 8 + 4095) // 4096 * 4096
+        assert rounds < 3
     out: List[Page] = []
     for r in range(world):
-        out.extend(_blob_to_pages(recv_h[r * cap:r * cap + sizes_h[r]].tobytes()))
+        out.extend(_blob_to_pages(recv_h[r * cap + 8:r * cap + 8 + sizes[r]].tobytes()))
     return out
 
 
@@ -164,6 +174,7 @@ class DeviceRepartition:
         import torch.distributed as dist
         L = N.lib()
         dev = torch.device("cuda", self.device)
+        self.sent_bytes = 0
         ncap = max(L.pgpu_output_channel_count(partial._h), 1)
         cols = (N.Column * ncap)()
         nc = ctypes.c_int32()
