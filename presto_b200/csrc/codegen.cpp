@@ -1117,7 +1117,9 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     const int NH = (int)hotKinds.size(), NHA = std::max(NH, 1);
     const int NW = res.NW, KW = res.KW;
     const int NWA = std::max(NW, 1), KWA = std::max(KW, 1);
-    res.SLOTW = ((1 + KW + NW) + 3) / 4 * 4;
+    // tagless slots: keys of 1-2 words whose last word has a spare top byte carry the "occupied" mark themselves
+    const bool tagless = res.mode == KernelMode::AGG_HASH && KW >= 1 && KW <= 2 && keyLen < KW * 8 && !getenv("PGPU_TUNE_TAGGED");
+    res.SLOTW = (((tagless ? 0 : 1) + KW + NW) + 3) / 4 * 4;
 
     // directory sizing (shared memory): 8 warps x DCAP x NW words + keys + tags
     res.useDir = res.mode == KernelMode::AGG_HASH && plan.expectedGroups <= (1 << 20) && NW > 0;
@@ -1164,6 +1166,8 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     src << "struct P {\n";
     src << "    static constexpr int NC = " << res.NC << ", NO = " << res.NO << ", KW = " << KW << ", NW = " << NW << ", SLOTW = " << res.SLOTW << ";\n";
     src << "    static constexpr int KWA = " << KWA << ", NWA = " << NWA << ", NH = " << NH << ", NHA = " << NHA << ";\n";
+    src << "    static constexpr bool TAGLESS = " << (tagless ? "true" : "false") << ";\n";
+    src << "    static constexpr int KOFF = " << (tagless ? 0 : 1) << ";  // first key word of a slot\n";
     src << "    static constexpr bool USE_DIR = " << (res.useDir ? "true" : "false") << ";\n";
     src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 8;\n";
     // register-resident groups: as many as fit in ~28 64-bit accumulator registers per thread, at most 4

@@ -402,11 +402,65 @@ PGPU_DEV u64 ld_acquire_u64(const u64* p) {
 }
 PGPU_DEV void st_release_u64(u64* p, u64 v) { asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 
+PGPU_DEV u64 ld_relaxed_u64(const u64* p) {
+    u64 v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// single-copy atomic 16-byte load / compare-and-swap (LDG.E.128.STRONG.GPU / ATOMG.E.CAS.128)
+PGPU_DEV void ld_relaxed_u128(const u64* p, u64& lo, u64& hi) {
+    asm volatile("{\n .reg .b128 v;\n ld.relaxed.gpu.global.b128 v, [%2];\n mov.b128 {%0, %1}, v;\n}" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
+}
+PGPU_DEV void cas_u128(u64* p, u64 clo, u64 chi, u64 nlo, u64 nhi, u64& olo, u64& ohi) {
+    asm volatile("{\n .reg .b128 c, n, o;\n mov.b128 c, {%2, %3};\n mov.b128 n, {%4, %5};\n atom.relaxed.gpu.global.cas.b128 o, [%6], c, n;\n mov.b128 {%0, %1}, o;\n}"
+                 : "=l"(olo), "=l"(ohi)
+                 : "l"(clo), "l"(chi), "l"(nlo), "l"(nhi), "l"(p)
+                 : "memory");
+}
+#define KEY_MARK 0x8000000000000000ull  // top bit of the last key word: "slot occupied" (tagless slots)
+
 // Find the slot of `key` or claim an empty one (BigintGroupByHash.putIfAbsent :213-244, linear probing).
-// Returns the slot base pointer, or nullptr when the probe chain is exhausted.
-template <int KW, int SLOTW>
-PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool force) {
+// Returns the slot base pointer, or nullptr when the probe chain is exhausted / the table reached its limit.
+// `nins` counts the slots this thread claimed; callers add it to t.counters[0] in bulk (one atomic per warp and tile
+// instead of one per group).
+//   TAGLESS (keys of at most 2 words with a spare top byte): slot = [key words | cells]; the key itself is published
+//   with ONE 64-/128-bit compare-and-swap, lookups are ONE relaxed load — no lock state, no fences.
+//   otherwise: slot = [tag | key words | cells]; tag 0 empty, 1 locked, else 2 | hash << 8 (acquire / release protocol).
+template <int KW, int SLOTW, bool TAGLESS>
+PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool force, u32& nins) {
     u64 pos = __umul64hi(h, t.capacity);
+    const bool guarded = !force && t.limit != ~0ull;
+    if (TAGLESS) {
+        const u64 k0 = KW == 1 ? (key[0] | KEY_MARK) : key[0];
+        const u64 k1 = KW == 2 ? (key[KW - 1] | KEY_MARK) : 0ull;
+#pragma unroll 1
+        for (u64 probes = 0; probes < t.capacity; probes++) {
+            u64* s = t.slots + pos * SLOTW;
+            if (KW == 1) {
+                u64 cur = ld_relaxed_u64(s);
+                if (cur == k0) return s;
+                if (cur == 0ull) {
+                    if (guarded && ld_volatile_u64(t.counters) >= t.limit) return nullptr;
+                    cur = atomicCAS(s, 0ull, k0);
+                    if (cur == 0ull) { nins++; return s; }
+                    if (cur == k0) return s;
+                }
+            } else {
+                u64 c0, c1;
+                ld_relaxed_u128(s, c0, c1);
+                if (c0 == k0 && c1 == k1) return s;
+                if (c1 == 0ull) {
+                    if (guarded && ld_volatile_u64(t.counters) >= t.limit) return nullptr;
+                    cas_u128(s, 0ull, 0ull, k0, k1, c0, c1);
+                    if (c1 == 0ull) { nins++; return s; }
+                    if (c0 == k0 && c1 == k1) return s;
+                }
+            }
+            pos++;
+            if (pos == t.capacity) pos = 0;
+        }
+        return nullptr;
+    }
     const u64 tagv = TAG_FULL | (h << 8);
 #pragma unroll 1
     for (u64 probes = 0; probes < t.capacity; probes++) {
@@ -414,13 +468,13 @@ PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1]
         for (;;) {
             u64 tag = ld_acquire_u64(s);
             if (tag == TAG_EMPTY) {
-                if (!force && ld_volatile_u64(t.counters) >= t.limit) return nullptr;  // full enough: defer this row
+                if (guarded && ld_volatile_u64(t.counters) >= t.limit) return nullptr;  // full enough: defer this row
                 u64 old = atomicCAS(s, TAG_EMPTY, TAG_LOCKED);
                 if (old == TAG_EMPTY) {
 #pragma unroll
                     for (int i = 0; i < KW; i++) s[1 + i] = key[i];
                     st_release_u64(s, tagv);
-                    atomicAdd(t.counters, 1ull);
+                    nins++;
                     return s;
                 }
                 continue;  // somebody else got it: re-read
@@ -439,6 +493,17 @@ PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1]
     }
     return nullptr;
 }
+// slot occupied? / key words of an occupied slot (marker stripped)
+template <class P>
+PGPU_DEV bool slot_live(const u64* slot) {
+    return P::TAGLESS ? (slot[P::KW - 1] & KEY_MARK) != 0 : (slot[0] & 0xffull) == TAG_FULL;
+}
+template <class P>
+PGPU_DEV void slot_key(const u64* slot, u64 (&key)[P::KW > 0 ? P::KW : 1]) {
+#pragma unroll
+    for (int i = 0; i < P::KW; i++) key[i] = slot[P::KOFF + i];
+    if (P::TAGLESS) key[P::KW - 1] &= ~KEY_MARK;
+}
 
 // Accumulator words come in two layouts. CELLS (P::NW words) is the persistent layout of a table slot / the global
 // state; it never depends on which pages carry null vectors. HOT (P::NH words) is what the scan loop carries: cells
@@ -447,11 +512,16 @@ PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1]
 
 // Update the group of `key` with the hot contributions `hot`. Returns false when the row has to be deferred.
 template <class P>
-PGPU_DEV bool table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::KW : 1], const u64 (&hot)[P::NHA], bool force) {
-    u64* s = table_upsert<P::KW, P::SLOTW>(t, key, hash_key<P::KW>(key), force);
+PGPU_DEV bool table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::KW : 1], const u64 (&hot)[P::NHA], bool force, u32& nins) {
+    u64* s = table_upsert<P::KW, P::SLOTW, P::TAGLESS>(t, key, hash_key<P::KW>(key), force, nins);
     if (!s) return false;
-    P::atomic_cells(s + 1 + P::KW, hot);
+    P::atomic_cells(s + P::KOFF + P::KW, hot);
     return true;
+}
+// add the slots a thread claimed to the table's group counter
+PGPU_DEV void flush_inserts(const TableArgs& t, u32& nins) {
+    if (nins) atomicAdd(t.counters, (u64)nins);
+    nins = 0;
 }
 
 // Defer rows [row, row + nrows): they are re-evaluated by k_replay once the host has grown the table.
@@ -597,6 +667,7 @@ struct HashCtx {
     u64 racc[RG > 0 ? RG : 1][NHA];
     u64 rkey[RG > 0 ? RG : 1][KW > 0 ? KW : 1];  // keys of the register-resident groups this thread has met (rmask bit g)
     u32 rmask;
+    u32 nins;      // table slots claimed since the last flush_inserts
     bool use_dir;  // warp-uniform
     u32 err;
 
@@ -614,6 +685,7 @@ struct HashCtx {
         use_dir = P::USE_DIR;
         err = 0;
         rmask = 0;
+        nins = 0;
 #pragma unroll
         for (int g = 0; g < (RG > 0 ? RG : 1); g++) P::identity(racc[g]);
         if (P::USE_DIR) {  // whole block participates; caller synchronises afterwards
@@ -654,7 +726,7 @@ struct HashCtx {
                     const int e = dir_lookup<P>(dkeys, dtags, dids, dpos, dcount, key[r], dir_hash<KW>(key[r]));
                     if (e < 0) {  // 2. not in the (full) directory: straight to the HBM table
                         nmiss++;
-                        if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
+                        if (!table_update<P>(t, key[r], cw[r], false, nins)) defer_rows(t, base + r, 1, err);
                     } else if (RG > 0 && (e >> 16) < RG) {
                         const int id = e >> 16;
                         reg_accumulate<P>(racc, id, cw[r]);
@@ -690,7 +762,7 @@ struct HashCtx {
 #pragma unroll
                         for (int r = 0; r < R; r++) {
                             if (slot[r] >= 0) {
-                                if (!table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, 1, err);
+                                if (!table_update<P>(t, key[r], cw[r], false, nins)) defer_rows(t, base + r, 1, err);
                                 nmiss++;
                             }
                         }
@@ -738,14 +810,23 @@ struct HashCtx {
             }
 #pragma unroll
             for (int r = 0; r < R; r++)
-                if (sel[r] && !table_update<P>(t, key[r], cw[r], false)) defer_rows(t, base + r, span[r], err);
+                if (sel[r] && !table_update<P>(t, key[r], cw[r], false, nins)) defer_rows(t, base + r, span[r], err);
+        }
+        // group counter: one atomic per warp and call instead of one per claimed slot
+        if (__any_sync(FULLMASK, nins != 0)) {
+            const u32 tot = __reduce_add_sync(FULLMASK, nins);
+            if (lane == 0) atomicAdd(t.counters, (u64)tot);
+            nins = 0;
         }
     }
 
     // End of kernel, whole block: fold register groups -> warp tables -> HBM table. `accwarps` = warps that own a wacc table
     // and hold register accumulators (the compute warps); other warps only take part in the barriers.
     PGPU_DEV void flush(const TableArgs& t, int accwarps) {
-        if (!P::USE_DIR) return;
+        if (!P::USE_DIR) {
+            flush_inserts(t, nins);
+            return;
+        }
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         __syncthreads();
         if (RG > 0) {
@@ -771,8 +852,9 @@ struct HashCtx {
 #pragma unroll
             for (int i = 0; i < KW; i++) key[i] = dkeys[s * KW + i];
             // the host keeps gridDim * DLIMIT slots in reserve below the load-factor limit for this flush
-            if (!table_update<P>(t, key, tot, true)) err |= PGPU_ERR_TABLE_FULL;
+            if (!table_update<P>(t, key, tot, true, nins)) err |= PGPU_ERR_TABLE_FULL;
         }
+        flush_inserts(t, nins);
     }
 };
 
@@ -949,7 +1031,7 @@ PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t,
 // Re-run deferred rows (one row per thread) against the grown table.
 template <class P>
 PGPU_DEV void body_replay(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc, const u64* rows, u64 n) {
-    u32 err = 0;
+    u32 err = 0, nins = 0;
     for (u64 k = (u64)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (u64)gridDim.x * blockDim.x) {
         i64 row = (i64)rows[k];
         i64 base = row & ~3ll;
@@ -959,8 +1041,9 @@ PGPU_DEV void body_replay(const PageArgs<P::NC>& a, const TableArgs& t, const Sc
         u32 ignored = 0;  // arithmetic errors of this tile were already reported by the first pass
         P::eval(a, base, a.rows, sel, key, cw, ignored);
         int r = (int)(row & 3);
-        if (sel[r] && !table_update<P>(t, key[r], cw[r], true)) err |= PGPU_ERR_TABLE_FULL;
+        if (sel[r] && !table_update<P>(t, key[r], cw[r], true, nins)) err |= PGPU_ERR_TABLE_FULL;
     }
+    flush_inserts(t, nins);
     if (err) atomicOr(sc.err, err);
 }
 
@@ -1061,7 +1144,7 @@ PGPU_DEV void body_materialize(const TableArgs& t, const OutArgs<P::NO>& out, co
     for (i64 s0 = first_slot + ((i64)blockIdx.x * blockDim.x + threadIdx.x) - lane; s0 < end; s0 += (i64)gridDim.x * blockDim.x) {
         i64 s = s0 + lane;
         const u64* slot = t.slots + (u64)s * P::SLOTW;
-        bool live = s < end && (slot[0] & 0xffull) == TAG_FULL;
+        bool live = s < end && slot_live<P>(slot);
         u32 m = __ballot_sync(FULLMASK, live);
         if (!m) continue;
         u64 basepos = 0;
@@ -1069,7 +1152,11 @@ PGPU_DEV void body_materialize(const TableArgs& t, const OutArgs<P::NO>& out, co
         basepos = shfl_u64(basepos, 0);
         if (live) {
             i64 pos = (i64)(basepos + __popc(m & ((1u << lane) - 1u)));
-            if (pos < out.capacity) P::emit(slot + 1, slot + 1 + P::KW, out, pos, err);
+            if (pos < out.capacity) {
+                u64 key[P::KW > 0 ? P::KW : 1];
+                slot_key<P>(slot, key);
+                P::emit(key, slot + P::KOFF + P::KW, out, pos, err);
+            }
             else err |= PGPU_ERR_OUTPUT_FULL;
         }
     }
@@ -1078,18 +1165,18 @@ PGPU_DEV void body_materialize(const TableArgs& t, const OutArgs<P::NO>& out, co
 
 template <class P>
 PGPU_DEV void body_rehash(const TableArgs& from, const TableArgs& to, const Scratch& sc) {
-    u32 err = 0;
+    u32 err = 0, nins = 0;
     for (u64 s = (u64)blockIdx.x * blockDim.x + threadIdx.x; s < from.capacity; s += (u64)gridDim.x * blockDim.x) {
         const u64* slot = from.slots + s * P::SLOTW;
-        if ((slot[0] & 0xffull) != TAG_FULL) continue;
+        if (!slot_live<P>(slot)) continue;
         u64 key[P::KW > 0 ? P::KW : 1];
-#pragma unroll
-        for (int i = 0; i < P::KW; i++) key[i] = slot[1 + i];
-        u64* d = table_upsert<P::KW, P::SLOTW>(to, key, hash_key<P::KW>(key), true);
+        slot_key<P>(slot, key);
+        u64* d = table_upsert<P::KW, P::SLOTW, P::TAGLESS>(to, key, hash_key<P::KW>(key), true, nins);
         if (!d) { err |= PGPU_ERR_TABLE_FULL; continue; }
 #pragma unroll
-        for (int w = 0; w < P::NW; w++) d[1 + P::KW + w] = slot[1 + P::KW + w];  // keys are distinct: plain stores
+        for (int w = 0; w < P::NW; w++) d[P::KOFF + P::KW + w] = slot[P::KOFF + P::KW + w];  // keys are distinct: plain stores
     }
+    flush_inserts(to, nins);
     if (err) atomicOr(sc.err, err);
 }
 

@@ -419,7 +419,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
             if (st) return st;
         }
         TableArgs t = tableOf(p);
-        t.limit = limit;
+        t.limit = risky ? limit : ~0ull;  // the load-factor guard is only armed for chunks that could reach the limit
         t.faillog_cap = risky ? (uint64_t)n : 0;
         pgpu_status st;
         // staged variant (bulk-async ring in shared memory) for pages long enough to fill the ring on every SM and whose
