@@ -1405,7 +1405,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, Scratch sc) { body_agg_global<P>(a, sc); }\n";
         src << "extern \"C\" __global__ void pgpu_k_emit(Scratch sc, OutArgs<P::NO> out) { body_emit_global<P>(sc, out); }\n";
     } else {
-        src << "extern \"C\" __global__ void __launch_bounds__(256, " << (getenv("PGPU_TUNE_MINBLOCKS") ? atoi(getenv("PGPU_TUNE_MINBLOCKS")) : 2) << ") pgpu_k_page(PageArgs<P::NC> a, TableArgs t, Scratch sc) { body_agg_hash<P>(a, t, sc); }\n";
+        src << "extern \"C\" __global__ void __launch_bounds__(256, " << (getenv("PGPU_TUNE_MINBLOCKS") ? atoi(getenv("PGPU_TUNE_MINBLOCKS")) : (res.useDir ? 2 : 3)) << ") pgpu_k_page(PageArgs<P::NC> a, TableArgs t, Scratch sc) { body_agg_hash<P>(a, t, sc); }\n";
         if (res.staged)
             src << "extern \"C\" __global__ void __launch_bounds__(512, 1) pgpu_k_page_staged(PageArgs<P::NC> a, TableArgs t, Scratch sc, int nstages) { body_agg_hash_staged<P>(a, t, sc, nstages); }\n";
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots) { body_materialize<P>(t, out, sc, first_slot, nslots); }\n";

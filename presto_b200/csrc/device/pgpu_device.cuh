@@ -426,36 +426,51 @@ PGPU_DEV void cas_u128(u64* p, u64 clo, u64 chi, u64 nlo, u64 nhi, u64& olo, u64
 //   TAGLESS (keys of at most 2 words with a spare top byte): slot = [key words | cells]; the key itself is published
 //   with ONE 64-/128-bit compare-and-swap, lookups are ONE relaxed load — no lock state, no fences.
 //   otherwise: slot = [tag | key words | cells]; tag 0 empty, 1 locked, else 2 | hash << 8 (acquire / release protocol).
+// `allow` = new slots may be claimed (false: the table reached its load-factor limit, rows needing a new slot are deferred).
+// `pre` (tagless only): the home slot's key words were already loaded by probe_prefetch — a thread issues the loads of all
+// its rows before it waits for the first one.
+struct ProbePre {
+    u64 c0, c1;
+};
+template <int KW, int SLOTW>
+PGPU_DEV ProbePre probe_prefetch(const TableArgs& t, u64 h) {
+    ProbePre p;
+    const u64* s = t.slots + __umul64hi(h, t.capacity) * SLOTW;
+    if (KW == 1) { p.c0 = ld_relaxed_u64(s); p.c1 = 0; }
+    else ld_relaxed_u128(s, p.c0, p.c1);
+    return p;
+}
 template <int KW, int SLOTW, bool TAGLESS>
-PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool force, u32& nins) {
+PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool allow, u32& nins, const ProbePre* pre = nullptr) {
     u64 pos = __umul64hi(h, t.capacity);
-    const bool guarded = !force && t.limit != ~0ull;
     if (TAGLESS) {
         const u64 k0 = KW == 1 ? (key[0] | KEY_MARK) : key[0];
         const u64 k1 = KW == 2 ? (key[KW - 1] | KEY_MARK) : 0ull;
+        bool have = pre != nullptr;
+        u64 c0 = have ? pre->c0 : 0ull, c1 = have ? pre->c1 : 0ull;
 #pragma unroll 1
         for (u64 probes = 0; probes < t.capacity; probes++) {
             u64* s = t.slots + pos * SLOTW;
             if (KW == 1) {
-                u64 cur = ld_relaxed_u64(s);
-                if (cur == k0) return s;
-                if (cur == 0ull) {
-                    if (guarded && ld_volatile_u64(t.counters) >= t.limit) return nullptr;
-                    cur = atomicCAS(s, 0ull, k0);
-                    if (cur == 0ull) { nins++; return s; }
-                    if (cur == k0) return s;
+                if (!have) c0 = ld_relaxed_u64(s);
+                if (c0 == k0) return s;
+                if (c0 == 0ull) {
+                    if (!allow) return nullptr;
+                    c0 = atomicCAS(s, 0ull, k0);
+                    if (c0 == 0ull) { nins++; return s; }
+                    if (c0 == k0) return s;
                 }
             } else {
-                u64 c0, c1;
-                ld_relaxed_u128(s, c0, c1);
+                if (!have) ld_relaxed_u128(s, c0, c1);
                 if (c0 == k0 && c1 == k1) return s;
                 if (c1 == 0ull) {
-                    if (guarded && ld_volatile_u64(t.counters) >= t.limit) return nullptr;
+                    if (!allow) return nullptr;
                     cas_u128(s, 0ull, 0ull, k0, k1, c0, c1);
                     if (c1 == 0ull) { nins++; return s; }
                     if (c0 == k0 && c1 == k1) return s;
                 }
             }
+            have = false;
             pos++;
             if (pos == t.capacity) pos = 0;
         }
@@ -468,7 +483,7 @@ PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1]
         for (;;) {
             u64 tag = ld_acquire_u64(s);
             if (tag == TAG_EMPTY) {
-                if (guarded && ld_volatile_u64(t.counters) >= t.limit) return nullptr;  // full enough: defer this row
+                if (!allow) return nullptr;  // full enough: defer this row
                 u64 old = atomicCAS(s, TAG_EMPTY, TAG_LOCKED);
                 if (old == TAG_EMPTY) {
 #pragma unroll
@@ -511,9 +526,12 @@ PGPU_DEV void slot_key(const u64* slot, u64 (&key)[P::KW > 0 ? P::KW : 1]) {
 // expanded back to cells only when a partial result is merged into a slot (P::atomic_cells / P::merge_cells).
 
 // Update the group of `key` with the hot contributions `hot`. Returns false when the row has to be deferred.
+PGPU_DEV bool table_may_insert(const TableArgs& t) {  // load-factor guard; armed by the host only for chunks that could reach the limit
+    return t.limit == ~0ull || ld_volatile_u64(t.counters) < t.limit;
+}
 template <class P>
 PGPU_DEV bool table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::KW : 1], const u64 (&hot)[P::NHA], bool force, u32& nins) {
-    u64* s = table_upsert<P::KW, P::SLOTW, P::TAGLESS>(t, key, hash_key<P::KW>(key), force, nins);
+    u64* s = table_upsert<P::KW, P::SLOTW, P::TAGLESS>(t, key, hash_key<P::KW>(key), force || table_may_insert(t), nins);
     if (!s) return false;
     P::atomic_cells(s + P::KOFF + P::KW, hot);
     return true;
@@ -808,9 +826,32 @@ struct HashCtx {
                     sel[r] = false;
                 }
             }
+            if (P::TAGLESS) {
+                // issue the home-slot loads of all rows, then resolve them one by one: R independent HBM accesses in flight
+                // per thread instead of one; the load-factor guard is read once per call
+                const bool allow = table_may_insert(t);
+                u64 h[R];
+                ProbePre pre[R];
 #pragma unroll
-            for (int r = 0; r < R; r++)
-                if (sel[r] && !table_update<P>(t, key[r], cw[r], false, nins)) defer_rows(t, base + r, span[r], err);
+                for (int r = 0; r < R; r++) {
+                    if (sel[r]) {
+                        h[r] = hash_key<KW>(key[r]);
+                        pre[r] = probe_prefetch<KW, P::SLOTW>(t, h[r]);
+                    }
+                }
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+                    if (sel[r]) {
+                        u64* s = table_upsert<KW, P::SLOTW, true>(t, key[r], h[r], allow, nins, &pre[r]);
+                        if (s) P::atomic_cells(s + P::KOFF + KW, cw[r]);
+                        else defer_rows(t, base + r, span[r], err);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; r++)
+                    if (sel[r] && !table_update<P>(t, key[r], cw[r], false, nins)) defer_rows(t, base + r, span[r], err);
+            }
         }
         // group counter: one atomic per warp and call instead of one per claimed slot
         if (__any_sync(FULLMASK, nins != 0)) {
