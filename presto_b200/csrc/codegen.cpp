@@ -698,6 +698,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     bool stagedPossible = true;
     int stageBytes = 0, tailGuard = 0;
     std::ostringstream issueLoad, issueVar, issueCopies;  // stage_issue(): global loads before the stage is free; stores into the stage; bulk copies of lane 0
+    std::ostringstream preFields, preLoads, limFields, limLoads;  // StagePre / StageLim of the producer
     unsigned fixedTx = 0;
     {
         auto region = [&](int bytes) {
@@ -727,11 +728,20 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
                 so.vbytes = region(so.vcap + 32);
                 so.vbase = region(16);
                 // byte range of the tile: 16-byte aligned body by bulk copy, the < 16 trailing bytes by the producer lanes
-                issueLoad << "        const i32 vb0_" << C << " = a.c[" << C << "].offsets[row0], vb1_" << C << " = a.c[" << C << "].offsets[row0 + " << kTile << "];\n";
-                issueLoad << "        i32 s0_" << C << " = vb0_" << C << " & ~15, e1_" << C << " = vb1_" << C << " & ~15;\n";
+                // StagePre: the two bounding offsets, loaded by the producer two tiles ahead; StageLim: end of the readable bytes
+                preFields << "        i32 vb0_" << C << ", vb1_" << C << ";\n";
+                preLoads << "        p.vb0_" << C << " = a.c[" << C << "].offsets[row0]; p.vb1_" << C << " = a.c[" << C << "].offsets[row0 + " << kTile << "];\n";
+                limFields << "        i32 vend_" << C << ";\n";
+                limLoads << "        l.vend_" << C << " = a.c[" << C << "].offsets[a.rows + " << 3 << "];\n";
+                // the copy end is rounded UP to 16 bytes when the over-read stays inside the byte array (always, except in
+                // the last tiles of a page); otherwise rounded down and the < 16 trailing bytes are moved by hand
+                issueLoad << "        const i32 vb0_" << C << " = p.vb0_" << C << ", vb1_" << C << " = p.vb1_" << C << ";\n";
+                issueLoad << "        i32 s0_" << C << " = vb0_" << C << " & ~15, e1_" << C << " = (vb1_" << C << " + 15) & ~15;\n";
+                issueLoad << "        const bool up_" << C << " = e1_" << C << " <= l.vend_" << C << ";\n";
+                issueLoad << "        if (!up_" << C << ") e1_" << C << " = vb1_" << C << " & ~15;\n";
                 issueLoad << "        if (e1_" << C << " < s0_" << C << ") e1_" << C << " = s0_" << C << ";\n";
-                issueLoad << "        if (e1_" << C << " - s0_" << C << " > " << so.vcap << ") { err |= PGPU_ERR_VARCHAR_LEN; e1_" << C << " = s0_" << C << " + " << so.vcap << "; }\n";
-                issueLoad << "        const i32 tq_" << C << " = e1_" << C << " + lane; const bool tl_" << C << " = lane < 16 && tq_" << C << " < vb1_" << C << " && tq_" << C << " - s0_" << C << " < " << (so.vcap + 16) << ";\n";
+                issueLoad << "        if (e1_" << C << " - s0_" << C << " > " << (so.vcap + 16) << ") { err |= PGPU_ERR_VARCHAR_LEN; e1_" << C << " = s0_" << C << " + " << so.vcap << "; }\n";
+                issueLoad << "        const i32 tq_" << C << " = e1_" << C << " + lane; const bool tl_" << C << " = !up_" << C << " && lane < 16 && tq_" << C << " < vb1_" << C << " && tq_" << C << " - s0_" << C << " < " << (so.vcap + 16) << ";\n";
                 issueLoad << "        u8 tb_" << C << " = 0; if (tl_" << C << ") tb_" << C << " = ((const u8*)a.c[" << C << "].values)[tq_" << C << "];\n";
                 issueVar << "        if (tl_" << C << ") st[" << so.vbytes << " + (tq_" << C << " - s0_" << C << ")] = tb_" << C << ";\n";
                 issueVar << "        if (lane == 0) *reinterpret_cast<i32*>(st + " << so.vbase << ") = s0_" << C << ";\n";
@@ -1229,7 +1239,11 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         src << "        }\n";
         src << "    }\n";
         // producer warp: arm the stage's full barrier with the byte count, then hand the copies to the TMA engine
-        src << "    PGPU_DEV static void stage_issue(const PageArgs<NC>& a, i64 row0, unsigned char* st, u64* bar, int lane, u32& err, u64* empty_bar, bool wait_empty, u32 empty_parity) {\n";
+        src << "    struct StagePre {\n        int unused;\n" << preFields.str() << "    };\n";
+        src << "    struct StageLim {\n        int unused;\n" << limFields.str() << "    };\n";
+        src << "    PGPU_DEV static void stage_prefetch(const PageArgs<NC>& a, i64 row0, StagePre& p) {\n        p.unused = 0;\n" << preLoads.str() << "    }\n";
+        src << "    PGPU_DEV static void stage_limits(const PageArgs<NC>& a, StageLim& l) {\n        l.unused = 0;\n" << limLoads.str() << "    }\n";
+        src << "    PGPU_DEV static void stage_issue(const PageArgs<NC>& a, i64 row0, unsigned char* st, u64* bar, int lane, u32& err, u64* empty_bar, bool wait_empty, u32 empty_parity, const StagePre& p, const StageLim& l) {\n";
         src << "        u32 tx = " << fixedTx << "u;\n";
         src << issueLoad.str();
         src << "        if (wait_empty) mbar_wait(empty_bar, empty_parity);\n";

@@ -1040,11 +1040,20 @@ PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t,
         // ---- producer
         int s = 0;
         u32 use = 0;  // how many times the ring has wrapped
+        // what a tile's copies need from global memory (bounding offsets of var-width columns) is loaded two tiles ahead,
+        // so the producer never sits on a load round trip between two stages
+        typename P::StageLim lim;
+        P::stage_limits(a, lim);
+        typename P::StagePre q0, q1;
+        if (mine > 0) P::stage_prefetch(a, (i64)blockIdx.x * TILE, q0);
+        if (mine > 1) P::stage_prefetch(a, ((i64)blockIdx.x + gridDim.x) * TILE, q1);
         for (i64 it = 0; it < mine; it++) {
             const i64 row0 = (blockIdx.x + it * gridDim.x) * TILE;
-            // stage_issue first loads what it needs from global memory (var-width byte ranges), then waits for the stage
-            // to be free, then arms the barrier and issues the copies
-            P::stage_issue(a, row0, stages + (size_t)s * P::STAGE_BYTES, full + s, lane, cx.err, empty + s, use > 0, (use - 1) & 1u);
+            const typename P::StagePre cur = q0;
+            q0 = q1;
+            if (it + 2 < mine) P::stage_prefetch(a, (blockIdx.x + (it + 2) * gridDim.x) * TILE, q1);
+            // stage_issue waits for the stage to be free, then arms the barrier and issues the copies
+            P::stage_issue(a, row0, stages + (size_t)s * P::STAGE_BYTES, full + s, lane, cx.err, empty + s, use > 0, (use - 1) & 1u, cur, lim);
             if (++s == nstages) { s = 0; use++; }
         }
     } else {

@@ -369,6 +369,7 @@ uint64_t flushReserve(pgpu_pipeline* p, const Variant* v) {
 struct DevPage {
     std::vector<ColArg> cols;
     int64_t rows = 0;
+    int64_t slack = 0;  // rows of the same arrays that follow this slice (offsets past the end stay readable)
 };
 
 pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
@@ -434,7 +435,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         if (staged) {
             // whole tiles through the staged kernel, the ragged tail (and the 3 offsets a var-width tile reads past its end)
             // through the direct kernel: same table, same stream
-            const int64_t nst = (n - 3) / g.stagedTile * g.stagedTile;
+            const int64_t nst = (n - (pg.slack >= 3 ? 0 : 3)) / g.stagedTile * g.stagedTile;
             std::vector<unsigned char> ps = pa;
             memcpy(ps.data() + sizeof(ColArg) * g.NC, &nst, 8);
             int nstages = v->stagedStages;
@@ -442,22 +443,24 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
             st = launch(p, v->kPageStaged, p->numSMs, g.stagedThreads, v->stagedSmem, args);
             if (st) return st;
             const int64_t nt = n - nst;
-            std::vector<ColArg> tc = pg.cols;
-            for (int c : g.usedChannels) {
-                ColArg& ca = tc[c];
-                const Type& ty = p->plan->input[c];
-                if (ca.ids) ca.ids += nst;
-                if (ca.offsets) ca.offsets += nst;                                   // var-width: values stay (offsets are absolute)
-                else if (ca.values) ca.values = (const char*)ca.values + (size_t)nst * ty.width();
-                if (ca.nulls) ca.nulls += nst;
+            if (nt > 0) {
+                std::vector<ColArg> tc = pg.cols;
+                for (int c : g.usedChannels) {
+                    ColArg& ca = tc[c];
+                    const Type& ty = p->plan->input[c];
+                    if (ca.ids) ca.ids += nst;
+                    if (ca.offsets) ca.offsets += nst;                                   // var-width: values stay (offsets are absolute)
+                    else if (ca.values) ca.values = (const char*)ca.values + (size_t)nst * ty.width();
+                    if (ca.nulls) ca.nulls += nst;
+                }
+                memcpy(ps.data(), tc.data(), sizeof(ColArg) * g.NC);
+                memcpy(ps.data() + sizeof(ColArg) * g.NC, &nt, 8);
+                TableArgs tt = t;
+                tt.row_bias = (uint64_t)nst;  // deferred rows are logged with chunk-relative numbers (the replay runs on the chunk)
+                int tgrid = (int)std::min<int64_t>((nt + kTileRows - 1) / kTileRows, (int64_t)p->numSMs * v->blocksPerSM);
+                void* targs[] = {ps.data(), &tt, &sc};
+                st = launch(p, v->kPage, tgrid, kThreads, (size_t)g.smemBytes, targs);
             }
-            memcpy(ps.data(), tc.data(), sizeof(ColArg) * g.NC);
-            memcpy(ps.data() + sizeof(ColArg) * g.NC, &nt, 8);
-            TableArgs tt = t;
-            tt.row_bias = (uint64_t)nst;  // deferred rows are logged with chunk-relative numbers (the replay runs on the chunk)
-            int tgrid = (int)std::min<int64_t>((nt + kTileRows - 1) / kTileRows, (int64_t)p->numSMs * v->blocksPerSM);
-            void* targs[] = {ps.data(), &tt, &sc};
-            st = launch(p, v->kPage, tgrid, kThreads, (size_t)g.smemBytes, targs);
         } else {
             void* args[] = {pa.data(), &t, &sc};
             st = launch(p, v->kPage, grid, kThreads, (size_t)g.smemBytes, args);
@@ -577,10 +580,12 @@ pgpu_status processDevicePage(pgpu_pipeline* p, Variant* v, const pgpu_column* c
         return runCompact(p, v, pg);
     }
     int64_t chunk = g.mode == KernelMode::AGG_HASH ? kHashChunkRows : rows;
+    if (v->kPageStaged) chunk = chunk / g.stagedTile * g.stagedTile;  // inner chunks are whole tiles: only the page's end is ragged
     for (int64_t r0 = 0; r0 < rows; r0 += chunk) {
         int64_t n = std::min(chunk, rows - r0);
         DevPage pg;
         pg.rows = n;
+        pg.slack = rows - (r0 + n);
         colArgsFor(r0, pg.cols);
         pgpu_status st = launchPageKernel(p, v, pg);
         if (st) return st;
