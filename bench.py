@@ -241,13 +241,11 @@ def run_device_steps(args, wl, device, dist):
             return
         final.reset()
         if small:
-            partial_pages = []
-            while not op.isFinished():
-                p = op.getOutput()
-                if p is not None:
-                    partial_pages.append(p)
-            gathered = X.gather_partial_pages(partial_pages, device=tdev)
-            state["result_rows"] = sum(p.position_count for p in toPages(final, gathered))
+            frames = X.all_gather_frames(X.pack_output(op), device=tdev)   # one NCCL all-gather of a 32 KB frame per rank
+            for f in frames:
+                X.add_packed(final, f)                                      # FINAL step: addIntermediate over every rank's partial page
+            final.finish()
+            state["result_rows"] = drain_output(final, to_host=True)
         else:
             repart.run(op, final)
             state["result_rows"] = drain_output(final, to_host=False)

@@ -694,7 +694,17 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     // ---------------------------------------------------------------- eval prologue shared by all modes
     // ---- stage layout of the staged variant: one region per used array, 128-byte aligned
     constexpr int kStagedWarps = 15;               // consumer warps (+ 1 producer warp = 512 threads, 128 registers each)
-    const int kTile = kStagedWarps * 32 * g.SR;    // rows per stage: every consumer thread owns SR consecutive rows
+    // sub-tiles per stage: wide rows (>= 40 bytes of staged arrays per row, Q1) run fastest with two 960-row sub-tiles per
+    // stage and a 2-deep ring (measured: 5.6 -> 4.1 ms per sf100 pass), narrow rows with one sub-tile and a 4-deep ring
+    int rowBytes = 0;
+    for (int c : res.usedChannels) {
+        const Type& t = plan.input[c];
+        if (sig[c].encoding == PGPU_ENC_RLE) continue;
+        rowBytes += sig[c].encoding == PGPU_ENC_DICTIONARY ? 4 : t.isVarWidth() ? 4 + std::max(t.precision, 1) : t.width();
+        if (sig[c].encoding == PGPU_ENC_PLAIN && sig[c].nullable) rowBytes += 1;
+    }
+    const int kSub = getenv("PGPU_TUNE_SUB") ? std::max(1, atoi(getenv("PGPU_TUNE_SUB"))) : (rowBytes >= 40 && rowBytes <= 100 ? 2 : 1);
+    const int kTile = kStagedWarps * 32 * g.SR * kSub;  // rows per stage: every consumer thread owns SR consecutive rows of each sub-tile
     bool stagedPossible = true;
     int stageBytes = 0, tailGuard = 0;
     std::ostringstream issueLoad, issueVar, issueCopies;  // stage_issue(): global loads before the stage is free; stores into the stage; bulk copies of lane 0
@@ -1228,7 +1238,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     }
     (void)projRaises;
     if (res.staged) {
-        src << "    static constexpr int SR = " << g.SR << ", CWARPS = " << kStagedWarps << ", TILE = " << kTile << ", STAGE_BYTES = " << stageBytes << ", TAIL_GUARD = " << tailGuard << ";\n";
+        src << "    static constexpr int SR = " << g.SR << ", CWARPS = " << kStagedWarps << ", SUB = " << kSub << ", TILE = " << kTile << ", STAGE_BYTES = " << stageBytes << ", TAIL_GUARD = " << tailGuard << ";\n";
         src << "    PGPU_DEV static void eval_staged(const PageArgs<NC>& a, const unsigned char* st, int trow, bool (&sel)[SR], u64 (&key)[SR][KWA], u64 (&cw)[SR][NHA], u32& err) {\n";
         src << evalFilterStaged.str();
         src << "        #pragma unroll\n";

@@ -1063,14 +1063,20 @@ PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t,
         u32 phase = 0;
         for (i64 it = 0; it < mine; it++) {
             mbar_wait(full + s, phase);
-            const i64 base = (blockIdx.x + it * gridDim.x) * TILE + trow;
-            bool sel[SR];
-            u64 key[SR][KW];
-            u64 cw[SR][NHA];
-            P::eval_staged(a, stages + (size_t)s * P::STAGE_BYTES, trow, sel, key, cw, cx.err);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(empty + s);  // this warp is done reading the stage
-            cx.template consume<SR>(t, base, sel, key, cw);
+#pragma unroll 1
+            for (int sub = 0; sub < P::SUB; sub++) {
+                const int srow = sub * (TILE / P::SUB) + trow;
+                const i64 base = (blockIdx.x + it * gridDim.x) * TILE + srow;
+                bool sel[SR];
+                u64 key[SR][KW];
+                u64 cw[SR][NHA];
+                P::eval_staged(a, stages + (size_t)s * P::STAGE_BYTES, srow, sel, key, cw, cx.err);
+                if (sub == P::SUB - 1) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(empty + s);  // this warp is done reading the stage
+                }
+                cx.template consume<SR>(t, base, sel, key, cw);
+            }
             if (++s == nstages) { s = 0; phase ^= 1u; }
         }
     }

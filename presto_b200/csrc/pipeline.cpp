@@ -425,7 +425,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         pgpu_status st;
         // staged variant (bulk-async ring in shared memory) for pages long enough to fill the ring on every SM and whose
         // arrays are 16-byte aligned (cp.async.bulk); short or unaligned pages take the direct-load kernel
-        bool staged = v->kPageStaged && n >= (int64_t)g.stagedTile * p->numSMs * 2;
+        bool staged = v->kPageStaged && n >= (int64_t)g.stagedTile * p->numSMs;
         if (staged) {
             for (int c : g.usedChannels) {
                 const ColArg& ca = pg.cols[c];

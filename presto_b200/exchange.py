@@ -98,6 +98,105 @@ def gather_partial_pages(pages: Sequence[Page], device=None, group=None) -> List
     return out
 
 
+# Raw (no Python pages) variant of the gather shape: output blocks are packed straight from the library-owned host
+# buffers into one frame and handed to the FINAL pipeline as host columns pointing into the received frame.
+_WIDTH = {0: 1, 1: 8, 2: 4, 3: 4, 4: 8, 5: 8}
+
+
+def _col_width(col) -> int:
+    return 16 if (col.type_kind == 5 and col.precision > 18) else _WIDTH[col.type_kind]
+
+
+def pack_output(op) -> bytes:
+    """Drain a finishing operator through pgpu_get_output and pack its pages:
+    [npages:i64] then per page [ncols:i64][rows:i64] and per column [kind, precision, scale, flags(1 nulls | 2 offsets), nbytes]
+    (5 x i64) followed by values, nulls, offsets — each padded to 16 bytes."""
+    L = N.lib()
+    n = max(L.pgpu_output_channel_count(op._h), 1)
+    cols = (N.Column * n)()
+    nc, rows = ctypes.c_int32(), ctypes.c_int64()
+    parts: List[bytes] = []
+    npages = 0
+
+    def pad(b: bytes) -> bytes:
+        return b + b"\0" * (-len(b) % 16)
+
+    while not L.pgpu_is_finished(op._h):
+        op._check(L.pgpu_get_output(op._h, cols, n, ctypes.byref(nc), ctypes.byref(rows)))
+        r = rows.value
+        if r <= 0:
+            continue
+        npages += 1
+        parts.append(np.array([nc.value, r], dtype=np.int64).tobytes())
+        for c in range(nc.value):
+            col = cols[c]
+            var = col.type_kind in (6, 7)
+            offs = ctypes.string_at(col.offsets, (r + 1) * 4) if var else b""
+            nbytes = int(np.frombuffer(offs[-4:], dtype=np.int32)[0]) if var else r * _col_width(col)
+            flags = (1 if col.nulls else 0) | (2 if var else 0)
+            parts.append(np.array([col.type_kind, col.precision, col.scale, flags, nbytes], dtype=np.int64).tobytes())
+            parts.append(pad(ctypes.string_at(col.values, nbytes) if nbytes else b""))
+            if col.nulls:
+                parts.append(pad(ctypes.string_at(col.nulls, r)))
+            if var:
+                parts.append(pad(offs))
+    return np.array([npages], dtype=np.int64).tobytes() + b"".join(parts)
+
+
+def add_packed(final_op, frame: np.ndarray) -> int:
+    """Feed the pages of one packed frame (uint8 array, kept alive by the caller) to `final_op` as host pages."""
+    L = N.lib()
+    base = frame.ctypes.data
+    hdr = frame[:8].view(np.int64)
+    pos, total = 8, 0
+    for _ in range(int(hdr[0])):
+        ncols, rows = (int(x) for x in frame[pos:pos + 16].view(np.int64))
+        pos += 16
+        cols = (N.Column * ncols)()
+        for c in range(ncols):
+            kind, prec, scale, flags, nbytes = (int(x) for x in frame[pos:pos + 40].view(np.int64))
+            pos += 40
+            col = cols[c]
+            col.encoding, col.type_kind, col.precision, col.scale, col.position_count = N.ENC_PLAIN, kind, prec, scale, rows
+            col.values = base + pos
+            pos += nbytes + (-nbytes % 16)
+            if flags & 1:
+                col.nulls = base + pos
+                pos += rows + (-rows % 16)
+            if flags & 2:
+                col.offsets = base + pos
+                pos += (rows + 1) * 4 + (-((rows + 1) * 4) % 16)
+        final_op._check(L.pgpu_add_page(final_op._h, cols, ncols, rows, 0))
+        total += rows
+    return total
+
+
+def all_gather_frames(frame: bytes, device=None, group=None):
+    """One padded all-gather of every rank's frame; returns a list of uint8 arrays (one per rank, rank order)."""
+    import torch
+    import torch.distributed as dist
+    blob = np.frombuffer(frame, dtype=np.uint8)
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return [blob.copy()]
+    world = dist.get_world_size(group)
+    dev = device if device is not None else torch.device("cpu")
+    cap, rounds = _FRAME, 0
+    while True:
+        buf = np.zeros(cap, dtype=np.uint8)
+        buf[:8] = np.frombuffer(np.int64(blob.size).tobytes(), dtype=np.uint8)
+        n = min(blob.size, cap - 16)
+        buf[16:16 + n] = blob[:n]
+        recv = torch.empty(world * cap, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(recv, torch.from_numpy(buf).to(dev), group=group)
+        recv_h = recv.cpu().numpy()
+        sizes = [int(recv_h[r * cap:r * cap + 8].view(np.int64)[0]) for r in range(world)]
+        rounds += 1
+        if max(sizes) <= cap - 16:
+            return [recv_h[r * cap + 16:r * cap + 16 + sizes[r]] for r in range(world)]
+        cap = (max(sizes) + 16 + 4095) // 4096 * 4096
+        assert rounds < 3
+
+
 def final_over_pages(final_operator, pages: Sequence[Page]) -> List[Page]:
     from .operators import toPages
     return toPages(final_operator, [p for p in pages if p.position_count])

@@ -108,3 +108,37 @@ def test_two_rank_exchange_over_gloo():
         assert_rows_equal_ignore_order(q1, single_q1, nkeys=2, rtol=sequential_bound(total))  # every rank holds the final Q1 answer
         hc_all += hc
     assert_rows_equal_ignore_order(hc_all, single_hc, nkeys=1, rtol=1e-12)  # the union of the partitions is the answer
+
+
+def _frame_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import numpy as np
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ok = True
+        for size in (0, 100, 40_000 + rank * 70_000):   # empty, one frame, ragged frames larger than the fixed frame
+            mine = (np.arange(size, dtype=np.int64) * (rank + 3) % 251).astype(np.uint8).tobytes()
+            frames = X.all_gather_frames(mine)
+            for r, f in enumerate(frames):
+                n = size if size < 40_000 else 40_000 + r * 70_000
+                exp = (np.arange(n, dtype=np.int64) * (r + 3) % 251).astype(np.uint8)
+                ok = ok and f.size == n and bool((f == exp).all())
+        q.put((rank, ok))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_all_gather_frames_over_gloo():
+    import torch.multiprocessing as mp
+    world, port = 2, 31000 + os.getpid() % 2000
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_frame_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok in results)

@@ -10,7 +10,7 @@ from presto_b200 import exchange as X
 from presto_b200 import tpch
 from presto_b200.operators import Aggregation, GpuPipelineOperator, plan_text
 from presto_b200.spi import BIGINT, DOUBLE
-from util import assert_rows_equal_ignore_order, rows_of, run_gpu, run_oracle
+from util import assert_rows_equal_ignore_order, rows_of, run_gpu, run_oracle, sequential_bound
 
 pytestmark = pytest.mark.gpu
 
@@ -74,4 +74,34 @@ def test_partial_partition_final_equals_single():
         assert_rows_equal_ignore_order(rows_of(out), single, nkeys=1)
     finally:
         partial.close()
+        final.close()
+
+
+def test_packed_partial_frames_feed_final():
+    """gather shape without Python pages: PARTIAL output packed from the library's buffers, FINAL fed from the frames"""
+    import numpy as np
+    from presto_b200 import _native as N
+    from test_oracle_protocol import q1_final_plan
+    total = 300_000
+    single = run_gpu(tpch.q1_plan(), [tpch.q1_page(0, total, total)])
+    frames = []
+    for part in range(2):
+        op = GpuPipelineOperator(tpch.q1_plan("partial"), 0)
+        try:
+            op.addInput(tpch.q1_page(part * (total // 2), total // 2, total))
+            op.finish()
+            frames.append(np.frombuffer(X.pack_output(op), dtype=np.uint8).copy())
+        finally:
+            op.close()
+    final = GpuPipelineOperator(q1_final_plan(), 0)
+    try:
+        assert sum(X.add_packed(final, f) for f in frames) == 8   # 4 groups per partial page
+        final.finish()
+        out = []
+        while not final.isFinished():
+            p = final.getOutput()
+            if p is not None:
+                out.append(p)
+        assert_rows_equal_ignore_order(rows_of(out), single, nkeys=2, rtol=sequential_bound(total))
+    finally:
         final.close()
