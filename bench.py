@@ -21,7 +21,7 @@ sys.path.insert(0, ROOT)
 SF100_ROWS = 600_037_902  # TPC-H lineitem at sf100
 # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the ncu --set full captures under
 # profiles/ (bytes; None = not captured for that workload)
-# stored as measured DRAM bytes / algorithmic bytes of the captured launch (profiles/r01c_q1_staged_ncu_raw.csv)
+# stored as measured DRAM bytes / algorithmic bytes of the captured launch (profiles/r01d_q1_staged_ncu_raw.txt)
 TRAFFIC_RATIO = {"q1": 1.0014}
 
 
@@ -35,6 +35,8 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=SF100_ROWS, help="lineitem rows per GPU")
     ap.add_argument("--e2e-rows", type=int, default=0, help="rows of the end-to-end (host pages) leg; 0 = same as --rows if RAM allows")
     ap.add_argument("--cpu-rows-per-core", type=int, default=4_000_000)
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1, large group counts: FINAL reads the peers' partitions over NVLink (peer) or NCCL all-to-all first (nccl)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -229,7 +231,7 @@ def run_device_steps(args, wl, device, dist):
     ncol = len(wl["spec"])
     small = wl["name"] in ("q1", "q1dict", "q6")   # result is a handful of rows: host output / gather exchange
     tdev = torch.device("cuda", device)
-    repart = None if single or small else X.DeviceRepartition(device, world, rank)
+    repart = None if single or small else X.DeviceRepartition(device, world, rank, transport=args.exchange)
     state = {"result_rows": 0, "exchange_bytes": 0}
 
     def one_step():
@@ -294,6 +296,8 @@ def run_device_steps(args, wl, device, dist):
     info = dict(dev_ms=dev_ms, wall_s=wall, launches=nl, clocks=clocks, kern_ms=kern_ms, kern_launches=kern_launches,
                 kern_steps=ksteps, result_rows=state["result_rows"], table_capacity=op.stats().table_capacity,
                 exchange_bytes=state["exchange_bytes"])
+    if repart is not None:
+        repart.close()
     if final is not None:
         final.close()
     return info, dp, op
@@ -456,7 +460,7 @@ def main():
                 "data": "synthetic", "config": config, "gb_per_s": value * wl["bytes_per_row"] / 1e9,
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": info["launches"], "clocks": info["clocks"],
                 "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"],
-                "exchange": None if world == 1 else {"shape": "gather (all ranks run FINAL over all partial pages)" if args.workload in ("q1", "q1dict", "q6") else "hash repartition + all_to_all_single + FINAL per rank",
+                "exchange": None if world == 1 else {"shape": "gather (all ranks run FINAL over all partial pages)" if args.workload in ("q1", "q1dict", "q6") else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),
                                                      "bytes_sent_per_rank_per_step": info["exchange_bytes"]}}
         print(json.dumps(line))
     if world > 1:

@@ -166,16 +166,30 @@ void* pgpu_stream(const pgpu_pipeline* p);
  * (presto_b200/exchange.py; DESIGN.md "Multi-GPU"). */
 /* Hash-partition the complete output of a finishing PARTIAL-step pipeline into `nparts` (<= 64) contiguous
  * row ranges, device resident. After the call out_cols describe ONE device page sorted by partition and
- * part_row_offsets[nparts+1] (host) gives the row ranges; the pipeline is finished afterwards.
+ * partition i occupies rows [part_row_offsets[i], part_row_offsets[i] + part_row_counts[i]) of every column (host arrays of
+ * nparts+1 / nparts entries). Offsets are multiples of 16 rows, so each partition of each column is a 16-byte aligned
+ * device block that pgpu_add_device_page accepts; part_row_offsets[nparts] is the padded end. All columns live in ONE
+ * device allocation (see pgpu_ipc_export). The pipeline is finished afterwards.
  * The partition function is the reference's: (rawHash & 0x7fff_ffff_ffff_ffff) % nparts with
  * rawHash = 31 * previous + hash(key channel) (main/operator/HashGenerator.java:24-35,
  * InterpretedHashGenerator.java:66-74, spi/type/AbstractLongType.java:126-130). Key types: BIGINT, INTEGER,
  * DATE, DOUBLE; other key types are rejected with PGPU_NOT_SUPPORTED (VARCHAR keys hash with airlift's
  * XxHash64, which is not in the reference tree). */
 pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_column* out_cols, int32_t max_cols,
-                                         int32_t* ncols, int64_t* part_row_offsets);
+                                         int32_t* ncols, int64_t* part_row_offsets, int64_t* part_row_counts);
 /* The same partition function for ONE row on the host (kinds: 0 = int64, 1 = int32, 2 = double bits). */
 int32_t pgpu_partition_of(const int64_t* key_bits, const uint8_t* is_null, const int32_t* kinds, int32_t nkeys, int32_t nparts);
+
+/* Peer access over NVLink / NVSwitch for one-process-per-GPU deployments (cudaIpc*). The owner exports the allocation
+ * that contains dev_ptr (`handle`, PGPU_IPC_HANDLE_BYTES bytes, plus dev_ptr's byte offset inside it); a peer process maps it
+ * and may hand `mapped_base + offset (+ rows * width)` to pgpu_add_device_page of its own pipeline: the kernel then reads the
+ * rows straight out of the owner's HBM, no staging copy (this is the exchange between PARTIAL and FINAL, standing in for
+ * PartitionedOutputOperator -> ExchangeClient, main/operator/PartitionedOutputOperator.java:56-133). The owner must keep
+ * the buffer unchanged until the peers are done (a barrier in the caller); a handle must not be opened by its exporter. */
+#define PGPU_IPC_HANDLE_BYTES 64
+pgpu_status pgpu_ipc_export(int32_t device, const void* dev_ptr, uint8_t* handle, int64_t* offset);
+pgpu_status pgpu_ipc_open(int32_t device, const uint8_t* handle, void** mapped_base);
+pgpu_status pgpu_ipc_close(int32_t device, void* mapped_base);
 
 /* Pinned host memory helpers (what the JNI shim stages heap arrays into). */
 void* pgpu_host_alloc(size_t bytes);

@@ -64,7 +64,10 @@ SYMBOLS = [
     ("pgpu_get_stats", ctypes.c_int32, [_P, ctypes.POINTER(Stats)]),
     ("pgpu_set_timing", ctypes.c_int32, [_P, ctypes.c_int32]),
     ("pgpu_stream", ctypes.c_void_p, [_P]),
-    ("pgpu_partition_output_device", ctypes.c_int32, [_P, ctypes.c_int32, _COLS, ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int64)]),
+    ("pgpu_partition_output_device", ctypes.c_int32, [_P, ctypes.c_int32, _COLS, ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]),
+    ("pgpu_ipc_export", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64)]),
+    ("pgpu_ipc_open", ctypes.c_int32, [ctypes.c_int32, ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]),
+    ("pgpu_ipc_close", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p]),
     ("pgpu_partition_of", ctypes.c_int32, [ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_uint8), ctypes.POINTER(ctypes.c_int32), ctypes.c_int32, ctypes.c_int32]),
     ("pgpu_host_alloc", ctypes.c_void_p, [ctypes.c_size_t]),
     ("pgpu_host_free", None, [ctypes.c_void_p]),

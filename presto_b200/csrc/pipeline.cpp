@@ -140,7 +140,11 @@ struct pgpu_pipeline {
     std::vector<HostOut> outHost, outHostNulls, outHostAux;  // aux: offsets for var-width
     int64_t outCapacityRows = 0;
     // partitioned output (exchange)
-    std::vector<DeviceBuf> partDev, partDevNulls;
+    // one allocation for every partitioned column (a peer maps it with a single IPC handle); arenas replaced by a
+    // larger one stay allocated until destroy because a peer may still have them mapped
+    DeviceBuf partArena;
+    std::vector<void*> partRetired;
+    std::vector<void*> partDev, partDevNulls;  // per output column: pointers into partArena
     DeviceBuf partPid, partDst, partCounts;
     unsigned long long* hostPart = nullptr;  // pinned: counts[64] + cursors[64]
 };
@@ -957,9 +961,8 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
             if (b.ptr) cudaFree(b.ptr);
         for (auto& b : p->outDevNulls)
             if (b.ptr) cudaFree(b.ptr);
-        for (auto* vec : {&p->partDev, &p->partDevNulls})
-            for (auto& b : *vec)
-                if (b.ptr) cudaFree(b.ptr);
+        if (p->partArena.ptr) cudaFree(p->partArena.ptr);
+        for (void* q : p->partRetired) cudaFree(q);
         for (auto* b : {&p->partPid, &p->partDst, &p->partCounts})
             if (b->ptr) cudaFree(b->ptr);
         if (p->hostPart) cudaFreeHost(p->hostPart);
@@ -1222,8 +1225,9 @@ pgpu_status pgpu_memcpy_d2h(int32_t device, void* host_dst, const void* dev_src,
     return cudaMemcpy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
 }
 
-pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* part_row_offsets) {
-    if (!p || !ncols || !part_row_offsets) return PGPU_INVALID_ARGUMENT;
+pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols,
+                                         int64_t* part_row_offsets, int64_t* part_row_counts) {
+    if (!p || !ncols || !part_row_offsets || !part_row_counts) return PGPU_INVALID_ARGUMENT;
     if (p->device < 0) return fail(p, PGPU_INVALID_STATE, "pipeline was created compile-only (device < 0)");
     const Plan& plan = *p->plan;
     const GenResult& g = p->layout;
@@ -1247,6 +1251,7 @@ pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_
         if (g.out[c].varWidth && g.out[c].lenPrefixed) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: device-resident var-width output");
     CU(cudaSetDevice(p->device));
     for (int i = 0; i <= nparts; i++) part_row_offsets[i] = 0;
+    for (int i = 0; i < nparts; i++) part_row_counts[i] = 0;
     *ncols = g.NO;
     int64_t rows = 0;
     if (!p->finished && (p->outputReady || p->sawInput)) {
@@ -1257,19 +1262,37 @@ pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_
         rows = p->outRowsTotal - p->outRowsServed;
     }
     const int64_t r0 = p->outRowsServed;
-    if ((int)p->partDev.size() != g.NO) {
-        p->partDev.resize(g.NO);
-        p->partDevNulls.resize(g.NO);
-    }
     if (!p->hostPart) CU(cudaMallocHost((void**)&p->hostPart, 2 * kMaxParts * sizeof(unsigned long long)));
     const int64_t rr = std::max<int64_t>(rows, 1);
     pgpu_status st;
     if ((st = ensureDev(p, p->partPid, (size_t)rr))) return st;
     if ((st = ensureDev(p, p->partDst, (size_t)rr * 8))) return st;
     if ((st = ensureDev(p, p->partCounts, 2 * kMaxParts * sizeof(unsigned long long)))) return st;
+    // every partition starts at a multiple of 16 rows: each partition of each column is a 16-byte aligned device block
+    // that a FINAL pipeline (local or a peer's, over NVLink) accepts as it is. Sized by the output capacity so that the
+    // allocation (and a peer's mapping of it) is stable from step to step.
+    const int64_t capRows = (std::max(rr, p->outCapacityRows) + 15) / 16 * 16 + 16 * (int64_t)kMaxParts;
+    size_t need = 0;
+    std::vector<size_t> offV(g.NO), offN(g.NO);
     for (int c = 0; c < g.NO; c++) {
-        if ((st = ensureDev(p, p->partDev[c], (size_t)rr * std::max(g.out[c].stride, 1)))) return st;
-        if ((st = ensureDev(p, p->partDevNulls[c], (size_t)rr))) return st;
+        offV[c] = need;
+        need += align256((size_t)capRows * std::max(g.out[c].stride, 1));
+        offN[c] = need;
+        need += align256((size_t)capRows);
+    }
+    if (p->partArena.cap < need) {
+        CU(cudaStreamSynchronize(p->stream));
+        if (p->partArena.ptr) p->partRetired.push_back(p->partArena.ptr);
+        p->partArena = DeviceBuf{};
+        const size_t want = (need + (2u << 20) - 1) / (2u << 20) * (2u << 20);
+        CU(cudaMalloc(&p->partArena.ptr, want));
+        p->partArena.cap = want;
+    }
+    p->partDev.assign(g.NO, nullptr);
+    p->partDevNulls.assign(g.NO, nullptr);
+    for (int c = 0; c < g.NO; c++) {
+        p->partDev[c] = (char*)p->partArena.ptr + offV[c];
+        p->partDevNulls[c] = (char*)p->partArena.ptr + offN[c];
     }
     if (rows > 0) {
         for (int k = 0; k < nkeys; k++) {
@@ -1282,20 +1305,22 @@ pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_
         CU(partitionCount(p->stream, p->numSMs, keys, rows, (uint8_t*)p->partPid.ptr, dCounts));
         CU(cudaMemcpyAsync(p->hostPart, dCounts, kMaxParts * sizeof(unsigned long long), cudaMemcpyDeviceToHost, p->stream));
         CU(cudaStreamSynchronize(p->stream));
-        unsigned long long acc = 0;
+        unsigned long long acc = 0, real = 0;
         for (int i = 0; i < nparts; i++) {
             p->hostPart[kMaxParts + i] = acc;
             part_row_offsets[i] = (int64_t)acc;
-            acc += p->hostPart[i];
+            part_row_counts[i] = (int64_t)p->hostPart[i];
+            real += p->hostPart[i];
+            acc = (acc + p->hostPart[i] + 15) / 16 * 16;
         }
         part_row_offsets[nparts] = (int64_t)acc;
-        if ((int64_t)acc != rows) return fail(p, PGPU_CUDA_ERROR, "internal: partition counts do not add up");
+        if ((int64_t)real != rows) return fail(p, PGPU_CUDA_ERROR, "internal: partition counts do not add up");
         CU(cudaMemcpyAsync(dCursors, p->hostPart + kMaxParts, kMaxParts * sizeof(unsigned long long), cudaMemcpyHostToDevice, p->stream));
         CU(partitionAssign(p->stream, p->numSMs, nparts, rows, (const uint8_t*)p->partPid.ptr, dCursors, (int64_t*)p->partDst.ptr));
         for (int c = 0; c < g.NO; c++) {
             const int stride = g.out[c].stride;
-            CU(partitionScatter(p->stream, p->numSMs, rows, (const int64_t*)p->partDst.ptr, (const char*)p->outDev[c].ptr + (size_t)r0 * stride, p->partDev[c].ptr, stride));
-            CU(partitionScatter(p->stream, p->numSMs, rows, (const int64_t*)p->partDst.ptr, (const uint8_t*)p->outDevNulls[c].ptr + r0, p->partDevNulls[c].ptr, 1));
+            CU(partitionScatter(p->stream, p->numSMs, rows, (const int64_t*)p->partDst.ptr, (const char*)p->outDev[c].ptr + (size_t)r0 * stride, p->partDev[c], stride));
+            CU(partitionScatter(p->stream, p->numSMs, rows, (const int64_t*)p->partDst.ptr, (const uint8_t*)p->outDevNulls[c].ptr + r0, p->partDevNulls[c], 1));
         }
         p->stats.kernel_launches += 2 + 2 * g.NO;
         CU(cudaStreamSynchronize(p->stream));
@@ -1307,13 +1332,66 @@ pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_
         oc.type_kind = (int32_t)g.out[c].type.kind;
         oc.precision = g.out[c].type.precision;
         oc.scale = g.out[c].type.scale;
-        oc.position_count = rows;
-        oc.values = p->partDev[c].ptr;
-        oc.nulls = (const uint8_t*)p->partDevNulls[c].ptr;
+        oc.position_count = part_row_offsets[nparts];
+        oc.values = p->partDev[c];
+        oc.nulls = (const uint8_t*)p->partDevNulls[c];
     }
     p->outRowsServed = p->outRowsTotal;
     p->outputReady = false;
     p->finished = true;
+    return PGPU_OK;
+}
+
+// ---- peer access over NVLink / NVSwitch (one process per GPU) ------------------------------------------------------------
+namespace {
+typedef int (*AddressRangeFn)(unsigned long long* base, size_t* size, unsigned long long ptr);
+AddressRangeFn addressRangeFn() {
+    static AddressRangeFn fn = []() -> AddressRangeFn {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &f, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) return nullptr;
+        return (AddressRangeFn)f;
+    }();
+    return fn;
+}
+}  // namespace
+
+pgpu_status pgpu_ipc_export(int32_t device, const void* dev_ptr, uint8_t* handle, int64_t* offset) {
+    if (!dev_ptr || !handle || !offset) return PGPU_INVALID_ARGUMENT;
+    static_assert(sizeof(cudaIpcMemHandle_t) == PGPU_IPC_HANDLE_BYTES, "handle size");
+    if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
+    AddressRangeFn range = addressRangeFn();
+    unsigned long long base = 0;
+    size_t size = 0;
+    if (!range || range(&base, &size, (unsigned long long)(uintptr_t)dev_ptr) != 0) return PGPU_CUDA_ERROR;
+    cudaIpcMemHandle_t h;
+    if (cudaIpcGetMemHandle(&h, (void*)(uintptr_t)base) != cudaSuccess) {
+        cudaGetLastError();
+        return PGPU_CUDA_ERROR;
+    }
+    memcpy(handle, &h, sizeof h);
+    *offset = (int64_t)((unsigned long long)(uintptr_t)dev_ptr - base);
+    return PGPU_OK;
+}
+
+pgpu_status pgpu_ipc_open(int32_t device, const uint8_t* handle, void** mapped_base) {
+    if (!handle || !mapped_base) return PGPU_INVALID_ARGUMENT;
+    if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    if (cudaIpcOpenMemHandle(mapped_base, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        cudaGetLastError();
+        return PGPU_CUDA_ERROR;
+    }
+    return PGPU_OK;
+}
+
+pgpu_status pgpu_ipc_close(int32_t device, void* mapped_base) {
+    if (!mapped_base) return PGPU_INVALID_ARGUMENT;
+    if (cudaSetDevice(device) != cudaSuccess || cudaIpcCloseMemHandle(mapped_base) != cudaSuccess) {
+        cudaGetLastError();
+        return PGPU_CUDA_ERROR;
+    }
     return PGPU_OK;
 }
 

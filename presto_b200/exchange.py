@@ -257,67 +257,173 @@ def exchange_pages_host(per_dest: Sequence[Sequence[Page]], device=None, group=N
 
 # ------------------------------------------------------------------------------------------------ repartition (device)
 class DeviceRepartition:
-    """PARTIAL pipeline -> hash partition on the device -> NCCL all_to_all_single per column -> FINAL pipeline.
+    """PARTIAL pipeline -> hash partition on the device -> FINAL pipeline of the owning rank.
 
     `partial` must be finishing (finish() called); `final` is a FINAL-step GpuPipelineOperator whose input channels are the
-    partial pipeline's output channels. After run() the final operator holds this rank's partition of the groups."""
+    partial pipeline's output channels. After run() the final operator holds this rank's partition of the groups.
 
-    def __init__(self, device: int, world: int, rank: int, group=None):
+    transport "peer" (default for world > 1 on one node): every rank maps the peers' partition buffers (one CUDA IPC
+    handle per rank, cached while the allocation is stable) and its FINAL page kernel reads its partition of each peer's
+    rows straight out of that peer's HBM over NVLink / NVSwitch — the merge is fused with the transfer, there is no staging
+    copy and one small all-gather (row ranges + handles) plus one barrier per exchange.
+    transport "nccl": one all_to_all_single per column into receive buffers, then the FINAL pipeline over those (baseline)."""
+
+    def __init__(self, device: int, world: int, rank: int, group=None, transport: str = "peer"):
         self.device, self.world, self.rank, self.group = device, world, rank, group
+        self.transport = transport if world > 1 else "local"
         self.recv_keepalive: list = []
-        self.sent_bytes = 0
+        self.sent_bytes = 0       # bytes this rank's partitions put on the wire (nccl) / peers read from it is symmetric (peer)
         self.recv_rows = 0
+        self._mapped = {}         # (peer rank, handle bytes) -> mapped base address
+
+    def close(self):
+        L = N.lib()
+        for base in self._mapped.values():
+            L.pgpu_ipc_close(self.device, base)
+        self._mapped = {}
+
+    @staticmethod
+    def _width(t) -> int:
+        w = 16 if t.is_long_decimal else {0: 1, 1: 8, 2: 4, 3: 4, 4: 8, 5: 8}.get(t.kind)
+        if w is None:
+            raise RuntimeError("device repartition of %s channels is not supported" % t)
+        return w
+
+    def _feed(self, final, types, bases, start, count):
+        """add one partition (rows [start, start+count) of buffers `bases` = [(values, nulls)] per channel) to FINAL"""
+        nc = len(types)
+        fcols = (N.Column * nc)()
+        for c, t in enumerate(types):
+            fc = fcols[c]
+            fc.encoding = N.ENC_PLAIN
+            fc.type_kind, fc.precision, fc.scale = t.kind, t.precision, t.scale
+            fc.position_count = count
+            fc.values = bases[c][0] + start * self._width(t)
+            fc.nulls = bases[c][1] + start
+        final.addDeviceInput(fcols, nc, count)
 
     def run(self, partial, final) -> int:
-        import torch
-        import torch.distributed as dist
         L = N.lib()
-        dev = torch.device("cuda", self.device)
         self.sent_bytes = 0
         ncap = max(L.pgpu_output_channel_count(partial._h), 1)
         cols = (N.Column * ncap)()
         nc = ctypes.c_int32()
         offs = (ctypes.c_int64 * (self.world + 1))()
-        partial._check(L.pgpu_partition_output_device(partial._h, self.world, cols, ncap, ctypes.byref(nc), offs))
-        types = partial.outputTypes()
-        send_rows = [offs[i + 1] - offs[i] for i in range(self.world)]
-        if self.world > 1:
-            send_t = torch.tensor(send_rows, dtype=torch.int64, device=dev)
-            recv_t = torch.empty(self.world, dtype=torch.int64, device=dev)
-            dist.all_to_all_single(recv_t, send_t, group=self.group)
-            recv_rows = recv_t.cpu().tolist()
+        cnts = (ctypes.c_int64 * self.world)()
+        partial._check(L.pgpu_partition_output_device(partial._h, self.world, cols, ncap, ctypes.byref(nc), offs, cnts))
+        types = partial.outputTypes()[:nc.value]
+        own = [(cols[c].values or 0, cols[c].nulls or 0) for c in range(nc.value)]
+        if self.transport == "local":
+            total = 0
+            for part in range(self.world):
+                if cnts[part]:
+                    self._feed(final, types, own, offs[part], cnts[part])
+                    total += cnts[part]
+        elif self.transport == "peer":
+            total = self._run_peer(final, types, own, offs, cnts)
         else:
-            recv_rows = list(send_rows)
-        total_recv = int(sum(recv_rows))
-        total_send = int(offs[self.world])
-        self.recv_rows = total_recv
-        self.recv_keepalive = []
-        fcols = (N.Column * nc.value)()
-        for c in range(nc.value):
-            t = types[c]
-            width = 16 if t.is_long_decimal else {0: 1, 1: 8, 2: 4, 3: 4, 4: 8, 5: 8}.get(t.kind)
-            if width is None:
-                raise RuntimeError("device repartition of %s channels is not supported" % t)
-            bufs = []
-            for ptr, w in ((cols[c].values, width), (cols[c].nulls, 1)):
-                src = device_bytes_tensor(ptr, total_send * w, dev)
-                if self.world > 1:
-                    dst = torch.empty(max(total_recv * w, 16), dtype=torch.uint8, device=dev)
-                    dist.all_to_all_single(dst[:total_recv * w], src, [r * w for r in recv_rows], [r * w for r in send_rows], group=self.group)
-                    self.sent_bytes += (total_send - send_rows[self.rank]) * w
-                else:
-                    dst = src
-                bufs.append(dst)
-            self.recv_keepalive.extend(bufs)
-            fc = fcols[c]
-            fc.encoding = N.ENC_PLAIN
-            fc.type_kind, fc.precision, fc.scale = t.kind, t.precision, t.scale
-            fc.position_count = total_recv
-            fc.values = bufs[0].data_ptr() if total_recv else None
-            fc.nulls = bufs[1].data_ptr() if total_recv else None
-        if self.world > 1:
-            torch.cuda.current_stream(dev).synchronize()  # the FINAL pipeline reads the received buffers on its own stream
-        if total_recv:
-            final.addDeviceInput(fcols, nc.value, total_recv)
+            total = self._run_nccl(final, types, own, offs, cnts)
+        self.recv_rows = total
         final.finish()
-        return total_recv
+        return total
+
+    # -- peer transport ------------------------------------------------------------------------------------------------
+    def _run_peer(self, final, types, own, offs, cnts) -> int:
+        import torch
+        import torch.distributed as dist
+        L = N.lib()
+        dev = torch.device("cuda", self.device)
+        nbuf = 2 * len(types)
+        # frame (int64): [starts(world) | counts(world) | offset per buffer (nbuf) | handle index per buffer (nbuf) |
+        #                 nhandles | handles (8 words each, at most nbuf)]
+        frame = np.zeros(2 * self.world + 2 * nbuf + 1 + 8 * nbuf, dtype=np.int64)
+        frame[:self.world] = offs[:self.world]
+        frame[self.world:2 * self.world] = cnts[:self.world]
+        handles: List[bytes] = []
+        pos = 2 * self.world
+        if any(cnts[i] for i in range(self.world)):
+            for b, ptr in enumerate(q for pair in own for q in pair):
+                h = ctypes.create_string_buffer(64)
+                off = ctypes.c_int64()
+                if L.pgpu_ipc_export(self.device, ptr, h, ctypes.byref(off)) != 0:
+                    raise RuntimeError("pgpu_ipc_export failed (CUDA IPC unavailable in this process environment)")
+                if h.raw not in handles:
+                    handles.append(h.raw)
+                frame[pos + b] = off.value
+                frame[pos + nbuf + b] = handles.index(h.raw)
+        frame[pos + 2 * nbuf] = len(handles)
+        hw = frame[pos + 2 * nbuf + 1:].view(np.uint8)
+        for i, h in enumerate(handles):
+            hw[64 * i:64 * i + 64] = np.frombuffer(h, dtype=np.uint8)
+        if dist.get_backend(self.group) != "nccl":
+            dev = torch.device("cpu")                        # control messages over gloo (tests: two processes, one GPU)
+        recv = torch.empty(self.world * frame.size, dtype=torch.int64, device=dev)
+        # the partition kernels have completed (pgpu_partition_output_device synchronises its stream), so a peer that has
+        # this rank's frame may read this rank's buffers
+        dist.all_gather_into_tensor(recv, torch.from_numpy(frame).to(dev), group=self.group)
+        frames = recv.cpu().numpy().reshape(self.world, frame.size)
+        total = 0
+        live = set()
+        for step in range(self.world):                       # own partition first, then the peers round-robin: at any
+            src = (self.rank + step) % self.world            # moment every rank reads from a different peer
+            f = frames[src]
+            start, count = int(f[self.rank]), int(f[self.world + self.rank])
+            if count == 0:
+                continue
+            if src == self.rank:
+                bases = own
+            else:
+                fh = f[pos + 2 * nbuf + 1:].view(np.uint8)
+                mapped = []
+                for i in range(int(f[pos + 2 * nbuf])):
+                    key = (src, fh[64 * i:64 * i + 64].tobytes())
+                    if key not in self._mapped:
+                        base = ctypes.c_void_p()
+                        if L.pgpu_ipc_open(self.device, key[1], ctypes.byref(base)) != 0:
+                            raise RuntimeError("pgpu_ipc_open failed for rank %d's partition buffers" % src)
+                        self._mapped[key] = base.value
+                    live.add(key)
+                    mapped.append(self._mapped[key])
+                flat = [mapped[int(f[pos + nbuf + b])] + int(f[pos + b]) for b in range(nbuf)]
+                bases = [(flat[2 * c], flat[2 * c + 1]) for c in range(len(types))]
+                self.sent_bytes += count * sum(self._width(t) + 1 for t in types)
+            self._feed(final, types, bases, start, count)
+            total += count
+        final.sync()                                         # this rank's reads of peer memory are complete ...
+        dist.barrier(group=self.group)                       # ... and so are everybody's: partition buffers may be reused
+        for key in [k for k in self._mapped if k not in live and any(k[0] == l[0] for l in live)]:
+            L.pgpu_ipc_close(self.device, self._mapped.pop(key))   # the peer moved to a larger allocation
+        return total
+
+    # -- NCCL transport (baseline) -----------------------------------------------------------------------------------------
+    def _run_nccl(self, final, types, own, offs, cnts) -> int:
+        import torch
+        import torch.distributed as dist
+        dev = torch.device("cuda", self.device)
+        pad_send = [offs[i + 1] - offs[i] for i in range(self.world)]           # padded partitions, multiples of 16 rows
+        send_t = torch.tensor([v for i in range(self.world) for v in (pad_send[i], cnts[i])], dtype=torch.int64, device=dev)
+        recv_t = torch.empty(2 * self.world, dtype=torch.int64, device=dev)
+        dist.all_to_all_single(recv_t, send_t, group=self.group)
+        rt = recv_t.cpu().tolist()
+        pad_recv, real_recv = rt[0::2], rt[1::2]
+        tot_send, tot_recv = int(offs[self.world]), int(sum(pad_recv))
+        self.recv_keepalive = []
+        bases = []
+        for c, t in enumerate(types):
+            pair = []
+            for ptr, w in ((own[c][0], self._width(t)), (own[c][1], 1)):
+                src = device_bytes_tensor(ptr, tot_send * w, dev)
+                dst = torch.empty(max(tot_recv * w, 16), dtype=torch.uint8, device=dev)
+                dist.all_to_all_single(dst[:tot_recv * w], src, [r * w for r in pad_recv], [r * w for r in pad_send], group=self.group)
+                self.sent_bytes += (tot_send - pad_send[self.rank]) * w
+                self.recv_keepalive.append(dst)
+                pair.append(dst.data_ptr())
+            bases.append(tuple(pair))
+        torch.cuda.current_stream(dev).synchronize()  # the FINAL pipeline reads the received buffers on its own stream
+        total, start = 0, 0
+        for src in range(self.world):
+            if real_recv[src]:
+                self._feed(final, types, bases, start, real_recv[src])
+                total += real_recv[src]
+            start += pad_recv[src]
+        return total

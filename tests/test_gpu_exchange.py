@@ -35,18 +35,24 @@ def test_partition_output_device(nparts):
         cols = (N.Column * 8)()
         nc = ctypes.c_int32()
         offs = (ctypes.c_int64 * (nparts + 1))()
-        op._check(L.pgpu_partition_output_device(op._h, nparts, cols, 8, ctypes.byref(nc), offs))
+        cnts = (ctypes.c_int64 * nparts)()
+        op._check(L.pgpu_partition_output_device(op._h, nparts, cols, 8, ctypes.byref(nc), offs, cnts))
         assert nc.value == 3 and op.isFinished()
-        rows = offs[nparts]
-        keys = _d2h(cols[0].values, rows * 8, np.int64)
-        cnt = _d2h(cols[1].values, rows * 8, np.int64)
-        sums = _d2h(cols[2].values, rows * 8, np.float64)
+        padded = offs[nparts]
+        assert all(offs[i] % 16 == 0 and offs[i] + cnts[i] <= offs[i + 1] for i in range(nparts))   # aligned, disjoint
+        assert all(cols[c].values % 16 == 0 and cols[c].nulls % 16 == 0 for c in range(3))
+        live = np.concatenate([np.arange(offs[i], offs[i] + cnts[i]) for i in range(nparts)])
+        keys_p = _d2h(cols[0].values, padded * 8, np.int64)
+        keys = keys_p[live]
+        cnt = _d2h(cols[1].values, padded * 8, np.int64)[live]
+        sums = _d2h(cols[2].values, padded * 8, np.float64)[live]
     finally:
         op.close()
     exp = run_oracle(tpch.highcard_plan(1000, "partial"), pages)
+    rows = sum(cnts)
     assert rows == len(exp) and len(set(keys.tolist())) == rows
     for part in range(nparts):
-        for k in keys[offs[part]:offs[part + 1]][:2000].tolist():
+        for k in keys_p[offs[part]:offs[part] + cnts[part]][:2000].tolist():
             assert X.partition_of_row([k], [BIGINT], nparts) == part
     assert_rows_equal_ignore_order(list(zip(keys.tolist(), cnt.tolist(), sums.tolist())), exp, nkeys=1)
 
@@ -105,3 +111,60 @@ def test_packed_partial_frames_feed_final():
         assert_rows_equal_ignore_order(rows_of(out), single, nkeys=2, rtol=sequential_bound(total))
     finally:
         final.close()
+
+
+def _peer_worker(rank, world, port, total, q):
+    import os
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    partial = final = ex = None
+    try:
+        per = total // world
+        partial = GpuPipelineOperator(tpch.highcard_plan(1000, "partial"), 0)
+        final = GpuPipelineOperator(plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0],
+                                              aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)], expectedGroups=200_000), 0)
+        ex = X.DeviceRepartition(0, world, rank, transport="peer")
+        out = []
+        for step in range(2):                                  # the second exchange reuses the cached mappings
+            partial.reset()
+            final.reset()
+            partial.addInput(tpch.highcard_page(rank * per, per, total, shuffled=True))
+            partial.finish()
+            ex.run(partial, final)
+            out = []
+            while not final.isFinished():
+                p = final.getOutput()
+                if p is not None:
+                    out.append(p)
+        rows = rows_of(out)
+        assert all(X.partition_of_row([r[0]], [BIGINT], world) == rank for r in rows[:5000])
+        q.put((rank, rows, ex.sent_bytes))
+    finally:
+        if ex is not None:
+            ex.close()
+        for op in (partial, final):
+            if op is not None:
+                op.close()
+        dist.destroy_process_group()
+
+
+def test_peer_memory_exchange_two_processes():
+    """two processes (ranks) on this GPU: each FINAL kernel reads the other process's partition buffers through CUDA IPC"""
+    import os
+    import torch.multiprocessing as mp
+    world, total, port = 2, 200_000, 33000 + os.getpid() % 2000
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_peer_worker, args=(r, world, port, total, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    per = total // world
+    single = run_gpu(tpch.highcard_plan(1000), [tpch.highcard_page(r * per, per, total, shuffled=True) for r in range(world)])
+    got = [row for _, rows, _ in results for row in rows]
+    assert all(sent > 0 for _, _, sent in results)
+    assert_rows_equal_ignore_order(got, single, nkeys=1, rtol=1e-12)
