@@ -210,6 +210,22 @@ def drain_output(op, to_host):
     return total
 
 
+def exchange_and_final(op, final, small, repart, tdev, state):
+    """N > 1: the partial -> final exchange of one step (op has finished its shard); leaves the result drained."""
+    from presto_b200 import exchange as X
+    final.reset()
+    if small:
+        frames = X.all_gather_frames(X.pack_output(op), device=tdev)   # one NCCL all-gather of a 32 KB frame per rank
+        for f in frames:
+            X.add_packed(final, f)                                      # FINAL step: addIntermediate over every rank's partial page
+        final.finish()
+        state["result_rows"] = drain_output(final, to_host=True)
+    else:
+        repart.run(op, final)
+        state["result_rows"] = drain_output(final, to_host=False)
+        state["exchange_bytes"] = repart.sent_bytes
+
+
 def run_device_steps(args, wl, device, dist):
     """`value`: inputs resident in HBM before the timed region. One step = reset, one pass of the fused pipeline over the
     rank's shard, and (N > 1) the partial -> final exchange. Timed with CUDA events recorded on an idle device on both
@@ -241,17 +257,7 @@ def run_device_steps(args, wl, device, dist):
         if single:
             state["result_rows"] = drain_output(op, to_host=small)
             return
-        final.reset()
-        if small:
-            frames = X.all_gather_frames(X.pack_output(op), device=tdev)   # one NCCL all-gather of a 32 KB frame per rank
-            for f in frames:
-                X.add_packed(final, f)                                      # FINAL step: addIntermediate over every rank's partial page
-            final.finish()
-            state["result_rows"] = drain_output(final, to_host=True)
-        else:
-            repart.run(op, final)
-            state["result_rows"] = drain_output(final, to_host=False)
-            state["exchange_bytes"] = repart.sent_bytes
+        exchange_and_final(op, final, small, repart, tdev, state)
 
     def barrier():
         if world > 1:
@@ -303,14 +309,18 @@ def run_device_steps(args, wl, device, dist):
     return info, dp, op
 
 
-def run_e2e_steps(args, wl, device, dp_device, steps, warmup):
-    """`e2e`: the same pass through pgpu_add_page with HOST pages in pinned memory; H2D copies and the D2H read of the
-    result are inside the timed region (wall clock around the public API call sequence)."""
+def run_e2e_steps(args, wl, device, dp_device, steps, warmup, dist):
+    """`e2e`: the same pass through pgpu_add_page with HOST pages in pinned memory; H2D copies, the exchange (N > 1) and the
+    D2H read of the result are inside the timed region (wall clock around the public API call sequence, bracketed by
+    barriers; the caller takes the max over ranks)."""
     import numpy as np
+    import torch
     from presto_b200 import _native as N
+    from presto_b200 import exchange as X
     from presto_b200 import tpch
     from presto_b200.operators import GpuPipelineOperator
     L = N.lib()
+    world, rank = dist["world"], dist["rank"]
     rows = args.e2e_rows or args.rows
     # bound by available host memory (pinned): keep below 40 % of MemAvailable
     need = rows * wl["bytes_per_row"] * 1.05
@@ -318,9 +328,14 @@ def run_e2e_steps(args, wl, device, dp_device, steps, warmup):
         avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
     except Exception:
         avail = 64 << 30
-    if need > 0.4 * avail:
-        rows = int(0.4 * avail / (wl["bytes_per_row"] * 1.05))
+    if need * world > 0.4 * avail:           # all ranks pin host memory of the same box
+        rows = int(0.4 * avail / world / (wl["bytes_per_row"] * 1.05))
     rows = min(rows, dp_device.rows)
+    if world > 1:                            # every rank runs the same number of rows
+        import torch.distributed as td
+        t = torch.tensor([rows], device="cuda", dtype=torch.int64)
+        td.all_reduce(t, op=td.ReduceOp.MIN)
+        rows = int(t.item())
     # host pages = the device columns copied back into pinned host buffers (identical bytes, no slow host generation)
     cols = (N.Column * len(wl["spec"]))()
     hostbufs = []
@@ -356,24 +371,47 @@ def run_e2e_steps(args, wl, device, dp_device, steps, warmup):
             s[3]._fill(d, keep)
             dict_cols.append((d, keep))
             dst.dictionary = ctypes.pointer(d)
-    op = GpuPipelineOperator(wl["plan"]("single"), device)
+    single = world == 1
+    op = GpuPipelineOperator(wl["plan"]("single" if single else "partial"), device)
+    final = None if single else GpuPipelineOperator(final_plan_for(wl, None), device)
+    small = wl["name"] in ("q1", "q1dict", "q6")
+    tdev = torch.device("cuda", device)
+    repart = None if single or small else X.DeviceRepartition(device, world, rank, transport=args.exchange)
+    state = {"result_rows": 0, "exchange_bytes": 0}
 
     def one_step():
         op.reset()
         op._check(L.pgpu_add_page(op._h, cols, len(wl["spec"]), rows, N.PAGE_PINNED))
         op.finish()
-        return drain_output(op, to_host=True)
+        if single:
+            return drain_output(op, to_host=True)
+        exchange_and_final(op, final, small, repart, tdev, state)
+        if not small:                         # the device-resident result is read back: that is the step's D2H
+            final.sync()
+        return state["result_rows"]
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as td
+            td.barrier()
+        torch.cuda.synchronize(device)
 
     for _ in range(warmup):
         one_step()
+    barrier()
     t0 = time.perf_counter()
     d2h = 0
     for _ in range(steps):
         one_step()
-        d2h = op.stats().d2h_bytes
+        d2h = op.stats().d2h_bytes + (final.stats().d2h_bytes if final is not None else 0)
+    barrier()
     dt = time.perf_counter() - t0
     st = op.stats()
     op.close()
+    if repart is not None:
+        repart.close()
+    if final is not None:
+        final.close()
     for hp in hostbufs:
         L.pgpu_host_free(hp)
     return dict(rows=rows, seconds=dt, steps=steps, h2d_bytes_per_step=int(st.h2d_bytes), d2h_bytes_per_step=int(d2h))
@@ -442,11 +480,15 @@ def main():
                 "kernel": kname, "peak_source": peak_src,
                 "launches_timed": info["kern_launches"], "algorithmic_bytes_per_row": wl["bytes_per_row"]}
     e2e = None
-    if not args.no_e2e and world == 1:
-        e = run_e2e_steps(args, wl, device, dp, steps=max(2, min(args.steps, 5)), warmup=1)
-        e2e = {"value": e["rows"] * e["steps"] / e["seconds"], "unit": "rows/s", "h2d_bytes_per_step": e["h2d_bytes_per_step"],
-               "d2h_bytes_per_step": e["d2h_bytes_per_step"], "rows_per_step": e["rows"], "steps": e["steps"],
-               "gb_per_s": e["h2d_bytes_per_step"] * e["steps"] / e["seconds"] / 1e9}
+    if not args.no_e2e:
+        e = run_e2e_steps(args, wl, device, dp, steps=max(2, min(args.steps, 5)), warmup=1, dist=dist)
+        if world > 1:
+            t = torch.tensor([e["seconds"]], device="cuda", dtype=torch.float64)
+            td.all_reduce(t, op=td.ReduceOp.MAX)
+            e["seconds"] = float(t.item())
+        e2e = {"value": e["rows"] * world * e["steps"] / e["seconds"], "unit": "rows/s", "h2d_bytes_per_step": e["h2d_bytes_per_step"] * world,
+               "d2h_bytes_per_step": e["d2h_bytes_per_step"] * world, "rows_per_step": e["rows"] * world, "steps": e["steps"],
+               "gb_per_s": e["h2d_bytes_per_step"] * world * e["steps"] / e["seconds"] / 1e9}
     op.close()
     dp.free()
     cpu = None

@@ -1187,6 +1187,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     src << "    static constexpr int NC = " << res.NC << ", NO = " << res.NO << ", KW = " << KW << ", NW = " << NW << ", SLOTW = " << res.SLOTW << ";\n";
     src << "    static constexpr int KWA = " << KWA << ", NWA = " << NWA << ", NH = " << NH << ", NHA = " << NHA << ";\n";
     src << "    static constexpr bool TAGLESS = " << (tagless ? "true" : "false") << ";\n";
+    src << "    static constexpr bool LANE_MERGE = " << (getenv("PGPU_TUNE_NOLANEMERGE") ? "false" : "true") << ";\n";
     src << "    static constexpr int KOFF = " << (tagless ? 0 : 1) << ";  // first key word of a slot\n";
     src << "    static constexpr bool USE_DIR = " << (res.useDir ? "true" : "false") << ";\n";
     src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 8;\n";

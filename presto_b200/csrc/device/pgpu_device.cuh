@@ -441,8 +441,9 @@ PGPU_DEV ProbePre probe_prefetch(const TableArgs& t, u64 h) {
     return p;
 }
 template <int KW, int SLOTW, bool TAGLESS>
-PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool allow, u32& nins, const ProbePre* pre = nullptr) {
-    u64 pos = __umul64hi(h, t.capacity);
+PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool allow, u32& nins, const ProbePre* pre = nullptr, u32 skip = 0) {
+    u64 pos = __umul64hi(h, t.capacity) + skip;  // skip: slots of the chain the caller has already examined
+    if (pos >= t.capacity) pos -= t.capacity;
     if (TAGLESS) {
         const u64 k0 = KW == 1 ? (key[0] | KEY_MARK) : key[0];
         const u64 k1 = KW == 2 ? (key[KW - 1] | KEY_MARK) : 0ull;
@@ -826,25 +827,119 @@ struct HashCtx {
                     sel[r] = false;
                 }
             }
-            if (P::TAGLESS) {
-                // issue the home-slot loads of all rows, then resolve them one by one: R independent HBM accesses in flight
-                // per thread instead of one; the load-factor guard is read once per call
-                const bool allow = table_may_insert(t);
-                u64 h[R];
-                ProbePre pre[R];
+            // a run that continues in the next lane (lanes hold consecutive rows): the head run of a lane is handed to the tail
+            // run of the previous lane, so a run costs one table update however it is split over threads. A single-run
+            // lane that is still receiving hands over in a later pass; chains of equal keys settle right to left.
+            if (P::LANE_MERGE) {
+                int tr = -1;  // index of the thread's last run
 #pragma unroll
-                for (int r = 0; r < R; r++) {
-                    if (sel[r]) {
-                        h[r] = hash_key<KW>(key[r]);
-                        pre[r] = probe_prefetch<KW, P::SLOTW>(t, h[r]);
+                for (int r = 0; r < R; r++)
+                    if (sel[r]) tr = r;
+                bool tail_edge = false;  // the last run reaches the thread's last row
+#pragma unroll
+                for (int r = 0; r < R; r++)
+                    if (r == tr) tail_edge = (r + span[r] == R);
+                const i64 pbase = (i64)shfl_u64((u64)base, (lane + 31) & 31);
+                const bool contig = lane > 0 && pbase + R == base;
+#pragma unroll 1
+                for (int pass = 0; pass < 31; pass++) {
+                    u64 tk[KW];
+#pragma unroll
+                    for (int i = 0; i < KW; i++) tk[i] = 0;
+#pragma unroll
+                    for (int r = 0; r < R; r++)
+                        if (r == tr) {
+#pragma unroll
+                            for (int i = 0; i < KW; i++) tk[i] = key[r][i];
+                        }
+                    const bool prev_edge = __shfl_up_sync(FULLMASK, (int)tail_edge, 1) != 0;  // every lane takes part in the shuffle
+                    bool want = contig && sel[0] && prev_edge;
+#pragma unroll
+                    for (int i = 0; i < KW; i++) want &= (shfl_u64(tk[i], (lane + 31) & 31) == key[0][i]);
+                    const bool next_wants = (__shfl_down_sync(FULLMASK, (int)want, 1) != 0) & (lane < 31);
+                    const bool give = want && !(tr == 0 && next_wants);
+                    if (!__any_sync(FULLMASK, give)) break;
+                    const bool recv = (__shfl_down_sync(FULLMASK, (int)give, 1) != 0) & (lane < 31);
+                    u64 in[NHA];
+#pragma unroll
+                    for (int i = 0; i < NHA; i++) in[i] = shfl_u64(cw[0][i], (lane + 1) & 31);
+                    const int in_span = __shfl_down_sync(FULLMASK, span[0], 1);
+                    if (recv) {
+#pragma unroll
+                        for (int r = 0; r < R; r++)
+                            if (r == tr) {
+                                P::combine(cw[r], in);
+                                span[r] += in_span;
+                            }
+                    }
+                    if (give) {
+                        sel[0] = false;
+                        if (tr == 0) { tr = -1; tail_edge = false; }
                     }
                 }
+            }
+            if (P::TAGLESS) {
+                const bool allow = table_may_insert(t);
+                u64 h[R];
+                if (allow) {
+                    // three phases so that a thread never waits for one row's memory access before it has issued the next
+                    // row's: (1) home-slot loads of all rows, (2) a compare-and-swap for every row whose home slot is empty,
+                    // (3) results. Known-at-home and new-at-home groups (the common cases below the load-factor limit) cost
+                    // two round trips per thread however many runs it holds; collisions walk the probe chain from slot + 1.
+                    ProbePre pre[R];
+                    u64 o0[R], o1[R];
+                    int st[R];  // 0 = slot known, 1 = compare-and-swap in flight, 2 = walk the chain
 #pragma unroll
-                for (int r = 0; r < R; r++) {
-                    if (sel[r]) {
-                        u64* s = table_upsert<KW, P::SLOTW, true>(t, key[r], h[r], allow, nins, &pre[r]);
-                        if (s) P::atomic_cells(s + P::KOFF + KW, cw[r]);
-                        else defer_rows(t, base + r, span[r], err);
+                    for (int r = 0; r < R; r++) {
+                        if (sel[r]) {
+                            h[r] = hash_key<KW>(key[r]);
+                            pre[r] = probe_prefetch<KW, P::SLOTW>(t, h[r]);
+                        }
+                    }
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        o0[r] = o1[r] = 0;
+                        st[r] = 0;
+                        if (sel[r]) {
+                            const u64 k0 = KW == 1 ? (key[r][0] | KEY_MARK) : key[r][0];
+                            const u64 k1 = KW == 2 ? (key[r][KW - 1] | KEY_MARK) : 0ull;
+                            const bool found = KW == 1 ? pre[r].c0 == k0 : (pre[r].c0 == k0 && pre[r].c1 == k1);
+                            const bool empty = KW == 1 ? pre[r].c0 == 0ull : pre[r].c1 == 0ull;
+                            st[r] = found ? 0 : empty ? 1 : 2;
+                            if (st[r] == 1) {
+                                u64* s = t.slots + __umul64hi(h[r], t.capacity) * P::SLOTW;
+                                if (KW == 1) o0[r] = atomicCAS(s, 0ull, k0);
+                                else cas_u128(s, 0ull, 0ull, k0, k1, o0[r], o1[r]);
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        if (sel[r]) {
+                            u64* s = t.slots + __umul64hi(h[r], t.capacity) * P::SLOTW;
+                            if (st[r] == 1) {
+                                const u64 k0 = KW == 1 ? (key[r][0] | KEY_MARK) : key[r][0];
+                                const u64 k1 = KW == 2 ? (key[r][KW - 1] | KEY_MARK) : 0ull;
+                                const bool claimed = KW == 1 ? o0[r] == 0ull : o1[r] == 0ull;
+                                const bool found = KW == 1 ? o0[r] == k0 : (o0[r] == k0 && o1[r] == k1);
+                                if (claimed) nins++;
+                                else if (!found) st[r] = 2;
+                            }
+                            if (st[r] == 2) s = table_upsert<KW, P::SLOTW, true>(t, key[r], h[r], true, nins, nullptr, 1);
+                            if (s) P::atomic_cells(s + P::KOFF + KW, cw[r]);
+                            else defer_rows(t, base + r, span[r], err);
+                        }
+                    }
+                } else {
+                    // the table is at its load-factor limit: look up only (rows that need a new slot are deferred)
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        if (sel[r]) {
+                            h[r] = hash_key<KW>(key[r]);
+                            u64* s = table_upsert<KW, P::SLOTW, true>(t, key[r], h[r], false, nins);
+                            if (s) P::atomic_cells(s + P::KOFF + KW, cw[r]);
+                            else defer_rows(t, base + r, span[r], err);
+                        }
                     }
                 }
             } else {
@@ -1193,28 +1288,62 @@ PGPU_DEV void body_compact(const PageArgs<P::NC>& a, const OutArgs<P::NO>& out, 
 // ------------------------------------------------------------------------------------------------ table output / rehash
 template <class P>
 PGPU_DEV void body_materialize(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, i64 first_slot, i64 nslots) {
+    // A block takes blockDim * 4 consecutive slots per iteration, counts its live slots with one block scan and reserves
+    // their output rows with ONE atomic on the output counter (a counter bumped per warp serialises on its L2 slice:
+    // 214 M slots / 32 were 6.7 M same-address atomics, the whole cost of the kernel at 150 M groups).
+    constexpr int SPT = 4;
+    __shared__ u32 s_warp[32];
+    __shared__ u64 s_base;
     u32 err = 0;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
     i64 end = first_slot + nslots;
     if (end > (i64)t.capacity) end = (i64)t.capacity;
-    for (i64 s0 = first_slot + ((i64)blockIdx.x * blockDim.x + threadIdx.x) - lane; s0 < end; s0 += (i64)gridDim.x * blockDim.x) {
-        i64 s = s0 + lane;
-        const u64* slot = t.slots + (u64)s * P::SLOTW;
-        bool live = s < end && slot_live<P>(slot);
-        u32 m = __ballot_sync(FULLMASK, live);
-        if (!m) continue;
-        u64 basepos = 0;
-        if (lane == 0) basepos = atomicAdd(sc.out_count, (u64)__popc(m));
-        basepos = shfl_u64(basepos, 0);
-        if (live) {
-            i64 pos = (i64)(basepos + __popc(m & ((1u << lane) - 1u)));
-            if (pos < out.capacity) {
-                u64 key[P::KW > 0 ? P::KW : 1];
-                slot_key<P>(slot, key);
-                P::emit(key, slot + P::KOFF + P::KW, out, pos, err);
-            }
-            else err |= PGPU_ERR_OUTPUT_FULL;
+    const i64 per_iter = (i64)blockDim.x * SPT;
+    for (i64 b0 = first_slot + (i64)blockIdx.x * per_iter; b0 < end; b0 += (i64)gridDim.x * per_iter) {
+        const i64 s = b0 + (i64)threadIdx.x * SPT;
+        bool live[SPT];
+        u32 cnt = 0;
+#pragma unroll
+        for (int k = 0; k < SPT; k++) {
+            live[k] = s + k < end && slot_live<P>(t.slots + (u64)(s + k) * P::SLOTW);
+            cnt += live[k] ? 1u : 0u;
         }
+        u32 incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const u32 n = __shfl_up_sync(FULLMASK, incl, d);
+            if (lane >= d) incl += n;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const u32 w = lane < nwarps ? s_warp[lane] : 0u;
+            u32 wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const u32 n = __shfl_up_sync(FULLMASK, wi, d);
+                if (lane >= d) wi += n;
+            }
+            s_warp[lane] = wi - w;  // exclusive prefix of the warp totals
+            if (lane == 31) s_base = wi ? atomicAdd(sc.out_count, (u64)wi) : 0ull;
+        }
+        __syncthreads();
+        i64 pos = (i64)(s_base + s_warp[warp] + incl - cnt);
+#pragma unroll
+        for (int k = 0; k < SPT; k++) {
+            if (live[k]) {
+                if (pos < out.capacity) {
+                    const u64* slot = t.slots + (u64)(s + k) * P::SLOTW;
+                    u64 key[P::KW > 0 ? P::KW : 1];
+                    slot_key<P>(slot, key);
+                    P::emit(key, slot + P::KOFF + P::KW, out, pos, err);
+                } else {
+                    err |= PGPU_ERR_OUTPUT_FULL;
+                }
+                pos++;
+            }
+        }
+        __syncthreads();  // s_warp / s_base are rewritten by the next iteration
     }
     if (err) atomicOr(sc.err, err);
 }

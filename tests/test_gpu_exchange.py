@@ -140,6 +140,10 @@ def _peer_worker(rank, world, port, total, q):
         rows = rows_of(out)
         assert all(X.partition_of_row([r[0]], [BIGINT], world) == rank for r in rows[:5000])
         q.put((rank, rows, ex.sent_bytes))
+    except BaseException:
+        import traceback
+        q.put((rank, traceback.format_exc(), -1))   # the parent fails at once instead of waiting for its queue timeout
+        raise
     finally:
         if ex is not None:
             ex.close()
@@ -159,7 +163,10 @@ def test_peer_memory_exchange_two_processes():
     procs = [ctx.Process(target=_peer_worker, args=(r, world, port, total, q)) for r in range(world)]
     for p in procs:
         p.start()
-    results = [q.get(timeout=600) for _ in range(world)]
+    results = []
+    for _ in range(world):
+        results.append(q.get(timeout=300))
+        assert results[-1][2] >= 0, results[-1][1]
     for p in procs:
         p.join(120)
         assert p.exitcode == 0

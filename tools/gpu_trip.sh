@@ -1,4 +1,18 @@
 #!/bin/bash
 mkdir -p gpurun_out
 exec > gpurun_out/trip.log 2>&1
-timeout 900 python -m pytest tests/test_gpu_exchange.py -m gpu -x -q 2>&1 | tail -15
+timeout 600 python -m pytest tests -m gpu -x -q -p no:cacheprovider --timeout 180 > gpurun_out/trip_pytest.log 2>&1; tail -3 gpurun_out/trip_pytest.log
+run() {
+  w=$1; shift
+  env "$@" timeout 150 python bench.py --workload $w --steps 5 --no-cpu --no-e2e 2>gpurun_out/trip_$w.err | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$w $*', d['ms_per_step'], d['roofline']['frac'], d['roofline']['avg_launch_ms'], d['gpu_launches'], d['result_rows'])"
+  tail -3 gpurun_out/trip_$w.err
+}
+run highcard A=1
+run highcard PGPU_TUNE_NOLANEMERGE=1
+run highcard PGPU_TUNE_MINBLOCKS=2
+run highcard PGPU_TUNE_MINBLOCKS=2 PGPU_TUNE_NOLANEMERGE=1
+run highcard_shuffled A=1
+run highcard_shuffled PGPU_TUNE_NOLANEMERGE=1
+run highcard_shuffled PGPU_TUNE_MINBLOCKS=2
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:pgpu_k_page -s 1 -c 1 -f -o gpurun_out/hc_d \
+    python bench.py --workload highcard --steps 1 --warmup 1 --no-e2e --no-cpu --rows 200000000 2>&1 | tail -1 | cut -c1-100

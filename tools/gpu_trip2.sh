@@ -1,9 +1,20 @@
 #!/bin/bash
+# multi-GPU visit: bash tools/gpu_trip2.sh N   (run under gpurun --gpus N)
+N=${1:-2}
 mkdir -p gpurun_out
-exec > gpurun_out/trip2.log 2>&1
+exec > gpurun_out/trip${N}.log 2>&1
 nvidia-smi -L
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
-for w in q1 highcard; do
-  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --workload $w --steps 5 --warmup 3 2>gpurun_out/trip2_$w.err > gpurun_out/trip2_$w.json
-  echo "exit $?"; tail -1 gpurun_out/trip2_$w.json | cut -c1-1800; tail -5 gpurun_out/trip2_$w.err
-done
+nvidia-smi topo -m | head -12
+run() {
+  tag=$1; shift
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N "$@" 2>gpurun_out/scale${N}_$tag.err > gpurun_out/scale${N}_$tag.json
+  echo "$tag exit $?"; tail -1 gpurun_out/scale${N}_$tag.json | python -c "
+import sys,json
+d=json.loads(sys.stdin.read()); print('$tag', 'ms/step', round(d['ms_per_step'],3), 'rows/s %.4g' % d['value'], 'e2e', d['e2e'] and '%.4g' % d['e2e']['value'], 'result_rows', d['result_rows'], d['exchange'])"
+  tail -4 gpurun_out/scale${N}_$tag.err
+}
+run q1 --workload q1 --steps 10 --warmup 3 --no-cpu
+run q6 --workload q6 --steps 10 --warmup 3 --no-cpu --no-e2e
+run hc_peer --workload highcard --steps 5 --warmup 3 --no-cpu --no-e2e --exchange peer
+run hc_nccl --workload highcard --steps 5 --warmup 3 --no-cpu --no-e2e --exchange nccl
+run hcs_peer --workload highcard_shuffled --steps 5 --warmup 3 --no-cpu --no-e2e --exchange peer
