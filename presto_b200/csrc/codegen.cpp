@@ -139,6 +139,16 @@ struct Gen {
     int indent = 2;
     // staged mode: tile loads come from a shared-memory stage `st` (thread's first row = trow) instead of global memory
     bool stagedLoads = false;
+    // staged kernel: dictionaries of at most kDcCap entries are decoded once per block into shared memory (what
+    // DictionaryAwarePageProjection does once per dictionary, project/DictionaryAwarePageProjection.java:125-273):
+    // channel -> cache slot. Layout: [int ok[16]] then per slot kDcCap x 8-byte values + kDcCap null bytes.
+    std::map<int, int> dcSlot;
+    static constexpr int kDcCap = 256, kDcHeader = 64, kDcSlotBytes = kDcCap * 8 + kDcCap, kDcMaxSlots = 8;
+    bool dcEligible(const Type& t) const {
+        if (t.kind == TypeKind::VARCHAR) return t.precision >= 1 && t.precision <= 7;  // one packed word, length in byte 0
+        if (t.kind == TypeKind::BOOLEAN || t.isVarWidth() || t.isLongDecimal()) return false;
+        return true;
+    }
     int SR = 2;  // rows per thread of the staged variant (the direct variants use 4)
     struct StageOff { int values = -1, nulls = -1, offsets = -1, vbytes = -1, vbase = -1, vcap = 0; };
     std::map<int, StageOff> soff;
@@ -228,6 +238,23 @@ struct Gen {
                 if (cs.nullable) line("const bool z" + C + " = n" + C + "[r] != 0;");
             } else {
                 std::string idx = cs.encoding == PGPU_ENC_DICTIONARY ? "id" + C + "[r]" : "0";
+                if (stagedLoads && cs.encoding == PGPU_ENC_DICTIONARY && dcEligible(t) && (dcSlot.count(c) || (int)dcSlot.size() < kDcMaxSlots)) {
+                    if (!dcSlot.count(c)) {
+                        const int k = (int)dcSlot.size();
+                        dcSlot[c] = k;
+                    }
+                    const int k = dcSlot[c];
+                    const std::string dv = "((const u64*)(dc + " + std::to_string(kDcHeader + k * kDcSlotBytes) + "))[" + idx + "]";
+                    const std::string dn = "(dc + " + std::to_string(kDcHeader + k * kDcSlotBytes + kDcCap * 8) + ")[" + idx + "]";
+                    if (t.kind == TypeKind::VARCHAR) {
+                        // length byte 0xff marks an entry longer than the type allows: only rows that use it raise
+                        line("u64 x" + C + " = " + dv + ", y" + C + " = 0; if ((x" + C + " & 0xffull) == 0xffull) { err |= PGPU_ERR_VARCHAR_LEN; x" + C + " = 0; }");
+                    } else {
+                        line("const " + ct + " x" + C + " = " + (t.kind == TypeKind::DOUBLE ? "u2d(" + dv + ")" : "(" + ct + ")" + dv) + ";");
+                    }
+                    if (cs.nullable) line("const bool z" + C + " = " + dn + " != 0;");
+                    continue;
+                }
                 if (t.isVarWidth()) {
                     if (t.kind == TypeKind::VARCHAR) {
                         line("u64 x" + C + ", y" + C + "; { const i32 q0 = a.c[" + C + "].doffsets[" + idx + "], q1 = a.c[" + C + "].doffsets[" + idx + " + 1]; pack_varchar<" +
@@ -1159,7 +1186,10 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         int dirBytes = res.useDir ? kStagedWarps * cap * NHA * 8 + cap * KW * 8 + cap * 12 + 16 : 0;
         res.stagedTile = kTile;
         res.stagedThreads = (kStagedWarps + 1) * 32;
-        res.stagedFixedSmem = (dirBytes + 127) / 128 * 128 + 128;
+        const int dcBytes = g.dcSlot.empty() ? 0 : (Gen::kDcHeader + (int)g.dcSlot.size() * Gen::kDcSlotBytes + 127) / 128 * 128;
+        res.stagedFixedSmem = (dirBytes + 127) / 128 * 128 + 128 + dcBytes;
+        res.dcacheCap = Gen::kDcCap;
+        for (auto& kv : g.dcSlot) res.dcacheChannels.push_back(kv.first);
         res.stageBytes = stageBytes;
         res.staged = stagedPossible && res.useDir && !getenv("PGPU_TUNE_NOSTAGE") && stageBytes > 0 && res.stagedFixedSmem + 2 * stageBytes <= kBudget;
     }
@@ -1240,7 +1270,32 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     (void)projRaises;
     if (res.staged) {
         src << "    static constexpr int SR = " << g.SR << ", CWARPS = " << kStagedWarps << ", SUB = " << kSub << ", TILE = " << kTile << ", STAGE_BYTES = " << stageBytes << ", TAIL_GUARD = " << tailGuard << ";\n";
-        src << "    PGPU_DEV static void eval_staged(const PageArgs<NC>& a, const unsigned char* st, int trow, bool (&sel)[SR], u64 (&key)[SR][KWA], u64 (&cw)[SR][NHA], u32& err) {\n";
+        {
+            const int dcBytes = g.dcSlot.empty() ? 0 : (Gen::kDcHeader + (int)g.dcSlot.size() * Gen::kDcSlotBytes + 127) / 128 * 128;
+            src << "    static constexpr int DCACHE_BYTES = " << dcBytes << ";\n";
+            // executed by the whole block before the ring starts; the caller synchronises afterwards
+            src << "    PGPU_DEV static void dcache_fill(const PageArgs<NC>& a, unsigned char* dc) {\n";
+            // (the host only launches the staged kernel when every cached dictionary has at most kDcCap entries)
+            for (auto& kv : g.dcSlot) {
+                const int c = kv.first, k = kv.second;
+                const Type& t = plan.input[c];
+                const std::string C = std::to_string(c);
+                const int voff = Gen::kDcHeader + k * Gen::kDcSlotBytes, noff = voff + Gen::kDcCap * 8;
+                src << "        for (int i = threadIdx.x; i < a.c[" << C << "].dcount && i < " << Gen::kDcCap << "; i += blockDim.x) {\n";
+                if (t.kind == TypeKind::VARCHAR) {
+                    src << "            u64 x, y; u32 e = 0; const i32 q0 = a.c[" << C << "].doffsets[i], q1 = a.c[" << C << "].doffsets[i + 1];\n";
+                    src << "            pack_varchar<" << t.precision << ">((const u8*)a.c[" << C << "].dvalues, q0, q1 - q0, x, y, e);\n";
+                    src << "            ((u64*)(dc + " << voff << "))[i] = e ? 0xffull : x;\n";
+                } else {
+                    const std::string raw = "((const " + stype(t) + "*)a.c[" + C + "].dvalues)[i]";
+                    src << "            ((u64*)(dc + " << voff << "))[i] = " << (t.kind == TypeKind::DOUBLE ? "d2u(" + raw + ")" : "(u64)(i64)" + raw) << ";\n";
+                }
+                if (sig[c].nullable) src << "            (dc + " << noff << ")[i] = a.c[" << C << "].dnulls[i];\n";
+                src << "        }\n";
+            }
+            src << "    }\n";
+        }
+        src << "    PGPU_DEV static void eval_staged(const PageArgs<NC>& a, const unsigned char* st, const unsigned char* dc, int trow, bool (&sel)[SR], u64 (&key)[SR][KWA], u64 (&cw)[SR][NHA], u32& err) {\n";
         src << evalFilterStaged.str();
         src << "        #pragma unroll\n";
         src << "        for (int r = 0; r < SR; r++) {\n";

@@ -40,6 +40,8 @@ struct GenResult {
     int stagedTile = 1024;     // rows per stage
     int stageBytes = 0;        // bytes of one stage
     int stagedFixedSmem = 0;   // directory + warp tables + mbarriers in front of the stages
+    std::vector<int> dcacheChannels;  // staged kernel: channels whose dictionary is decoded into shared memory
+    int dcacheCap = 0;                // ... which needs dictionaries of at most this many entries
     double keyDomain = 0;      // upper bound of distinct group keys when the key types bound it (0 = unbounded)
     std::vector<int> cellKinds;  // NW entries (CK_*)
     std::vector<OutColDesc> out;

@@ -52,6 +52,8 @@ struct ColArg {
     const void* dvalues;
     const u8* dnulls;
     const i32* doffsets;
+    i32 dcount;  // entries of the dictionary
+    i32 pad;
 };
 
 template <int NC>
@@ -1111,11 +1113,12 @@ template <class P>
 PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc, int nstages) {
     constexpr int KW = P::KW, NHA = P::NHA, CW = P::CWARPS, TILE = P::TILE, SR = P::SR;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    // layout: [directory + warp tables][full[4] empty[4] mbarriers][pad to 128][stages]
+    // layout: [directory + warp tables][full[4] empty[4] mbarriers][pad to 128][decoded dictionaries][stages]
     constexpr int DIRB = (HashCtx<P>::dir_bytes(CW) + 127) / 128 * 128;
     u64* full = reinterpret_cast<u64*>(smem_raw + DIRB);
     u64* empty = full + 4;
-    unsigned char* stages = smem_raw + DIRB + 128;
+    unsigned char* dcache = smem_raw + DIRB + 128;
+    unsigned char* stages = dcache + P::DCACHE_BYTES;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     HashCtx<P> cx;
     cx.init(smem_raw, CW, warp < CW ? warp : 0);
@@ -1126,6 +1129,7 @@ PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t,
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    P::dcache_fill(a, dcache);
     __syncthreads();
     // a.rows is a whole number of tiles (the host runs the ragged tail through the direct kernel); var-width columns read
     // up to 3 offsets past the last tile, which the host keeps in range
@@ -1165,7 +1169,7 @@ PGPU_DEV void body_agg_hash_staged(const PageArgs<P::NC>& a, const TableArgs& t,
                 bool sel[SR];
                 u64 key[SR][KW];
                 u64 cw[SR][NHA];
-                P::eval_staged(a, stages + (size_t)s * P::STAGE_BYTES, srow, sel, key, cw, cx.err);
+                P::eval_staged(a, stages + (size_t)s * P::STAGE_BYTES, dcache, srow, sel, key, cw, cx.err);
                 if (sub == P::SUB - 1) {
                     __syncwarp();
                     if (lane == 0) mbar_arrive(empty + s);  // this warp is done reading the stage

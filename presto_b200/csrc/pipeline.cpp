@@ -36,6 +36,8 @@ struct ColArg {
     const void* dvalues;
     const uint8_t* dnulls;
     const int32_t* doffsets;
+    int32_t dcount;
+    int32_t pad;
 };
 struct TableArgs {
     uint64_t* slots;
@@ -135,7 +137,13 @@ struct pgpu_pipeline {
     // staging + output
     StageSlot slots[3];
     int nextSlot = 0;
-    std::vector<DeviceBuf> outDev;       // per output column: values
+    // output columns live in ONE device allocation (values / nulls of column c at outOffV[c] / outOffN[c]) so that a
+    // small result reaches the host with a single copy instead of two per column
+    DeviceBuf outArena;
+    HostOut outHostArena;
+    std::vector<size_t> outOffV, outOffN;
+    size_t outLayoutBytes = 0;
+    std::vector<DeviceBuf> outDev;       // per output column: values (views into outArena)
     std::vector<DeviceBuf> outDevNulls;
     std::vector<HostOut> outHost, outHostNulls, outHostAux;  // aux: offsets for var-width
     int64_t outCapacityRows = 0;
@@ -164,6 +172,8 @@ pgpu_status fail(pgpu_pipeline* p, pgpu_status st, const std::string& m) {
     p->err = m;
     return st;
 }
+
+size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 
 pgpu_status ensureDev(pgpu_pipeline* p, DeviceBuf& b, size_t bytes) {
     if (b.cap >= bytes && b.ptr) return PGPU_OK;
@@ -435,6 +445,9 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
                 const ColArg& ca = pg.cols[c];
                 if (((uintptr_t)ca.values | (uintptr_t)ca.nulls | (uintptr_t)ca.offsets | (uintptr_t)ca.ids) & 15) staged = false;
             }
+            // the staged kernel decodes small dictionaries into shared memory once per block; larger ones take the direct kernel
+            for (int c : g.dcacheChannels)
+                if (pg.cols[c].dcount > g.dcacheCap) staged = false;
         }
         if (staged) {
             // whole tiles through the staged kernel, the ragged tail (and the 3 offsets a var-width tile reads past its end)
@@ -502,11 +515,24 @@ pgpu_status ensureOutBuffers(pgpu_pipeline* p, int64_t rows) {
         p->outHostAux.resize(g.NO);
     }
     int64_t r = std::max<int64_t>(rows, 1);
+    if (p->outArena.ptr && p->outCapacityRows >= r && (int)p->outOffV.size() == g.NO) return PGPU_OK;  // layout stays
+    p->outOffV.assign(g.NO, 0);
+    p->outOffN.assign(g.NO, 0);
+    size_t need = 0;
     for (int c = 0; c < g.NO; c++) {
-        pgpu_status st = ensureDev(p, p->outDev[c], (size_t)r * std::max(g.out[c].stride, 1));
-        if (st) return st;
-        st = ensureDev(p, p->outDevNulls[c], (size_t)r);
-        if (st) return st;
+        p->outOffV[c] = need;
+        need += align256((size_t)r * std::max(g.out[c].stride, 1));
+        p->outOffN[c] = need;
+        need += align256((size_t)r);
+    }
+    pgpu_status st = ensureDev(p, p->outArena, need);
+    if (st) return st;
+    p->outLayoutBytes = need;
+    for (int c = 0; c < g.NO; c++) {
+        p->outDev[c].ptr = (char*)p->outArena.ptr + p->outOffV[c];
+        p->outDev[c].cap = (size_t)r * std::max(g.out[c].stride, 1);
+        p->outDevNulls[c].ptr = (char*)p->outArena.ptr + p->outOffN[c];
+        p->outDevNulls[c].cap = (size_t)r;
     }
     p->outCapacityRows = r;
     return PGPU_OK;
@@ -573,6 +599,7 @@ pgpu_status processDevicePage(pgpu_pipeline* p, Variant* v, const pgpu_column* c
                 a.dvalues = d->values;
                 a.dnulls = d->nulls;
                 a.doffsets = d->offsets;
+                a.dcount = (int32_t)std::min<int64_t>(d->position_count, INT32_MAX);
             }
             out[c] = a;
         }
@@ -626,7 +653,6 @@ pgpu_status validatePage(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncol
     return PGPU_OK;
 }
 
-size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 
 // Stage rows [r0, r0+n) of a host page into a ring slot and return device-side column descriptors.
 pgpu_status stageChunk(pgpu_pipeline* p, Variant* v, const pgpu_column* cols, int64_t r0, int64_t n, bool pinned, StageSlot& slot, std::vector<ColArg>& out) {
@@ -721,6 +747,7 @@ pgpu_status stageChunk(pgpu_pipeline* p, Variant* v, const pgpu_column* cols, in
         } else {
             if (col.encoding == PGPU_ENC_DICTIONARY) a.ids = (const int32_t*)(dbase + o.ids);
             a.dvalues = dbase + o.dvalues;
+            a.dcount = (int32_t)std::min<int64_t>(col.dictionary->position_count, INT32_MAX);
             if (t.isVarWidth()) a.doffsets = (const int32_t*)(dbase + o.doffsets);
             if (o.hasDnulls) a.dnulls = (const uint8_t*)(dbase + o.dnulls);
         }
@@ -957,10 +984,8 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
             if (s.host) cudaFreeHost(s.host);
             if (s.done) cudaEventDestroy(s.done);
         }
-        for (auto& b : p->outDev)
-            if (b.ptr) cudaFree(b.ptr);
-        for (auto& b : p->outDevNulls)
-            if (b.ptr) cudaFree(b.ptr);
+        if (p->outArena.ptr) cudaFree(p->outArena.ptr);
+        if (p->outHostArena.ptr) cudaFreeHost(p->outHostArena.ptr);
         if (p->partArena.ptr) cudaFree(p->partArena.ptr);
         for (void* q : p->partRetired) cudaFree(q);
         for (auto* b : {&p->partPid, &p->partDst, &p->partCounts})
@@ -1048,6 +1073,14 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
         else resetAggState(p);
         return PGPU_OK;
     }
+    // small results: the whole output arena in one copy (a copy call costs more than these bytes take on the wire)
+    const bool oneCopy = toHost && n > 0 && p->outLayoutBytes <= (256u << 10);
+    if (oneCopy) {
+        pgpu_status st = ensureHost(p, p->outHostArena, p->outLayoutBytes);
+        if (st) return st;
+        CU(cudaMemcpyAsync(p->outHostArena.ptr, p->outArena.ptr, p->outLayoutBytes, cudaMemcpyDeviceToHost, p->stream));
+        p->stats.d2h_bytes += (int64_t)p->outLayoutBytes;
+    }
     for (int c = 0; c < g.NO; c++) {
         const OutColDesc& d = g.out[c];
         pgpu_column& oc = out_cols[c];
@@ -1063,6 +1096,11 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
             if (d.varWidth) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: device-resident var-width output");
             oc.values = dv;
             oc.nulls = dn;
+            continue;
+        }
+        if (oneCopy) {
+            oc.values = (char*)p->outHostArena.ptr + p->outOffV[c] + (size_t)r0 * d.stride;
+            oc.nulls = (const uint8_t*)p->outHostArena.ptr + p->outOffN[c] + r0;
             continue;
         }
         pgpu_status st = ensureHost(p, p->outHost[c], (size_t)std::max<int64_t>(n, 1) * std::max(d.stride, 1));
@@ -1086,8 +1124,8 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
             pgpu_status st = ensureHost(p, p->outHostAux[c], (size_t)(n + 1) * 4);
             if (st) return st;
             int32_t* offs = (int32_t*)p->outHostAux[c].ptr;
-            unsigned char* cells = (unsigned char*)p->outHost[c].ptr;
-            const uint8_t* nulls = (const uint8_t*)p->outHostNulls[c].ptr;
+            unsigned char* cells = (unsigned char*)const_cast<void*>(out_cols[c].values);
+            const uint8_t* nulls = out_cols[c].nulls;
             int32_t w = 0;
             offs[0] = 0;
             for (int64_t i = 0; i < n; i++) {
