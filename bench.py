@@ -213,13 +213,28 @@ def drain_output(op, to_host):
 def exchange_and_final(op, final, small, repart, tdev, state):
     """N > 1: the partial -> final exchange of one step (op has finished its shard); leaves the result drained."""
     from presto_b200 import exchange as X
+    trace = state.get("trace")
+    t0 = time.perf_counter()
     final.reset()
+    t1 = time.perf_counter()
     if small:
-        frames = X.all_gather_frames(X.pack_output(op), device=tdev)   # one NCCL all-gather of a 32 KB frame per rank
+        if trace is not None:
+            op.sync()
+            trace["kernels"] = trace.get("kernels", 0.0) + time.perf_counter() - t1
+            t1 = time.perf_counter()
+        frame = X.pack_output(op)                                       # waits for the shard's kernels, drains the partial page
+        t2 = time.perf_counter()
+        frames = X.all_gather_frames(frame, device=tdev)                # one NCCL all-gather of a 32 KB frame per rank
+        t3 = time.perf_counter()
         for f in frames:
             X.add_packed(final, f)                                      # FINAL step: addIntermediate over every rank's partial page
         final.finish()
+        t4 = time.perf_counter()
         state["result_rows"] = drain_output(final, to_host=True)
+        t5 = time.perf_counter()
+        if trace is not None:
+            for k, v in (("final_reset", t1 - t0), ("pack_output", t2 - t1), ("all_gather", t3 - t2), ("final_add", t4 - t3), ("final_output", t5 - t4)):
+                trace[k] = trace.get(k, 0.0) + v
     else:
         repart.run(op, final)
         state["result_rows"] = drain_output(final, to_host=False)
@@ -249,6 +264,8 @@ def run_device_steps(args, wl, device, dist):
     tdev = torch.device("cuda", device)
     repart = None if single or small else X.DeviceRepartition(device, world, rank, transport=args.exchange)
     state = {"result_rows": 0, "exchange_bytes": 0}
+    if os.environ.get("PGPU_BENCH_TRACE"):
+        state["trace"] = {}
 
     def one_step():
         op.reset()
@@ -271,6 +288,8 @@ def run_device_steps(args, wl, device, dist):
 
     for _ in range(args.warmup):
         one_step()
+    if state.get("trace") is not None:
+        state["trace"].clear()
     sampler = ClockSampler(device)
     sampler.start()
     barrier()
@@ -287,6 +306,8 @@ def run_device_steps(args, wl, device, dist):
     wall = time.perf_counter() - t0
     dev_ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
+    if state.get("trace") and rank == 0:
+        print("exchange trace (ms/step): " + ", ".join("%s %.3f" % (k, v * 1e3 / args.steps) for k, v in state["trace"].items()), file=sys.stderr)
     # dominant kernel alone: per-launch CUDA-event durations (pgpu_set_timing brackets every page-kernel launch)
     op.setTiming(True)
     kern_ms, kern_launches = 0.0, 0

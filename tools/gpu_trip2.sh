@@ -3,16 +3,20 @@
 N=${1:-2}
 mkdir -p gpurun_out
 exec > gpurun_out/trip${N}.log 2>&1
-nvidia-smi -L
-nvidia-smi topo -m | head -12
+nvidia-smi -L | head -8
 run() {
   tag=$1; shift
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N "$@" 2>gpurun_out/scale${N}_$tag.err > gpurun_out/scale${N}_$tag.json
   echo "$tag exit $?"; tail -1 gpurun_out/scale${N}_$tag.json | python -c "
 import sys,json
 d=json.loads(sys.stdin.read()); print('$tag', 'ms/step', round(d['ms_per_step'],3), 'rows/s %.4g' % d['value'], 'e2e', d['e2e'] and '%.4g' % d['e2e']['value'], 'result_rows', d['result_rows'], d['exchange'])"
-  tail -4 gpurun_out/scale${N}_$tag.err
+  grep -v "^\*\*\*\|OMP_NUM\|^$" gpurun_out/scale${N}_$tag.err | tail -4
 }
+if [ "$2" = "trace" ]; then
+  export PGPU_BENCH_TRACE=1
+  run q1 --workload q1 --steps 20 --warmup 3 --no-cpu --no-e2e
+  exit 0
+fi
 run q1 --workload q1 --steps 10 --warmup 3 --no-cpu
 run q6 --workload q6 --steps 10 --warmup 3 --no-cpu --no-e2e
 run hc_peer --workload highcard --steps 5 --warmup 3 --no-cpu --no-e2e --exchange peer
