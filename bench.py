@@ -210,14 +210,37 @@ def drain_output(op, to_host):
     return total
 
 
+def make_exchange(args, device, world, rank, small, leg):
+    from presto_b200 import exchange as X
+    if world == 1:
+        return None
+    if not small:
+        return X.DeviceRepartition(device, world, rank, transport=args.exchange)
+    if args.exchange == "peer":
+        return X.PeerGather(device, world, rank, "pgpu_mail_%s_%s" % (os.environ.get("MASTER_PORT", "0"), leg))
+    return None
+
+
 def exchange_and_final(op, final, small, repart, tdev, state):
-    """N > 1: the partial -> final exchange of one step (op has finished its shard); leaves the result drained."""
+    """N > 1: the partial -> final exchange of one step (op has finished its shard); leaves the result drained.
+    `repart` is the exchange object: PeerGather / None (small results), DeviceRepartition (large group counts)."""
     from presto_b200 import exchange as X
     trace = state.get("trace")
     t0 = time.perf_counter()
     final.reset()
     t1 = time.perf_counter()
-    if small:
+    if small and repart is not None:
+        if trace is not None:
+            op.sync()
+            trace["kernels"] = trace.get("kernels", 0.0) + time.perf_counter() - t1
+            t1 = time.perf_counter()
+        repart.run(op, final)                       # FINAL kernel reads every rank's partial rows over NVLink
+        t2 = time.perf_counter()
+        state["result_rows"] = drain_output(final, to_host=True)
+        if trace is not None:
+            trace["peer_gather+final"] = trace.get("peer_gather+final", 0.0) + t2 - t1
+            trace["final_output"] = trace.get("final_output", 0.0) + time.perf_counter() - t2
+    elif small:
         if trace is not None:
             op.sync()
             trace["kernels"] = trace.get("kernels", 0.0) + time.perf_counter() - t1
@@ -262,7 +285,7 @@ def run_device_steps(args, wl, device, dist):
     ncol = len(wl["spec"])
     small = wl["name"] in ("q1", "q1dict", "q6")   # result is a handful of rows: host output / gather exchange
     tdev = torch.device("cuda", device)
-    repart = None if single or small else X.DeviceRepartition(device, world, rank, transport=args.exchange)
+    repart = make_exchange(args, device, world, rank, small, "value")
     state = {"result_rows": 0, "exchange_bytes": 0}
     if os.environ.get("PGPU_BENCH_TRACE"):
         state["trace"] = {}
@@ -397,7 +420,7 @@ def run_e2e_steps(args, wl, device, dp_device, steps, warmup, dist):
     final = None if single else GpuPipelineOperator(final_plan_for(wl, None), device)
     small = wl["name"] in ("q1", "q1dict", "q6")
     tdev = torch.device("cuda", device)
-    repart = None if single or small else X.DeviceRepartition(device, world, rank, transport=args.exchange)
+    repart = make_exchange(args, device, world, rank, small, "e2e")
     state = {"result_rows": 0, "exchange_bytes": 0}
 
     def one_step():
@@ -523,7 +546,7 @@ def main():
                 "data": "synthetic", "config": config, "gb_per_s": value * wl["bytes_per_row"] / 1e9,
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": info["launches"], "clocks": info["clocks"],
                 "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"],
-                "exchange": None if world == 1 else {"shape": "gather (all ranks run FINAL over all partial pages)" if args.workload in ("q1", "q1dict", "q6") else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),
+                "exchange": None if world == 1 else {"shape": ("gather: every rank's FINAL kernel reads all partial pages over NVLink (CUDA IPC peer memory, shared-memory mailbox)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if args.workload in ("q1", "q1dict", "q6") else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),
                                                      "bytes_sent_per_rank_per_step": info["exchange_bytes"]}}
         print(json.dumps(line))
     if world > 1:

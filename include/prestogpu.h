@@ -47,7 +47,10 @@ typedef enum pgpu_status {
 typedef enum pgpu_encoding {
     PGPU_ENC_PLAIN = 0,       /* LongArrayBlock / IntArrayBlock / ByteArrayBlock / Int128ArrayBlock / VariableWidthBlock */
     PGPU_ENC_DICTIONARY = 1,  /* spi/block/DictionaryBlock.java:40-48 : ids[] into `dictionary`                          */
-    PGPU_ENC_RLE = 2          /* spi/block/RunLengthEncodedBlock.java:45-48 : single-position `dictionary` repeated       */
+    PGPU_ENC_RLE = 2,         /* spi/block/RunLengthEncodedBlock.java:45-48 : single-position `dictionary` repeated       */
+    PGPU_ENC_VARCELL = 3      /* device-resident VARCHAR(<=15) column as fixed 16-byte cells (byte 0 = length, bytes 1..15 =
+                                 data): what pgpu_get_output_device returns for VARCHAR channels and pgpu_add_device_page
+                                 accepts — the device-to-device form of a short VariableWidthBlock (no reference counterpart) */
 } pgpu_encoding;
 
 /* Logical types of the supported subset (spi/type/...). Physical layout in a block:

@@ -11,7 +11,7 @@ INSUFFICIENT_RESOURCES, COMPILER_ERROR, CUDA_ERROR, INVALID_STATE, INVALID_CAST_
 STATUS_NAMES = {0: "OK", 1: "NOT_SUPPORTED", 2: "INVALID_ARGUMENT", 3: "NUMERIC_VALUE_OUT_OF_RANGE", 4: "DIVISION_BY_ZERO",
                 5: "GENERIC_INSUFFICIENT_RESOURCES", 6: "COMPILER_ERROR", 7: "CUDA_ERROR", 8: "INVALID_STATE",
                 9: "INVALID_CAST_ARGUMENT"}
-ENC_PLAIN, ENC_DICTIONARY, ENC_RLE = 0, 1, 2
+ENC_PLAIN, ENC_DICTIONARY, ENC_RLE, ENC_VARCELL = 0, 1, 2, 3
 PAGE_PINNED = 1
 
 # PGPU_LI_* column ids

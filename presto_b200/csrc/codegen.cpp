@@ -191,7 +191,9 @@ struct Gen {
                 line("i32 id" + C + "[4]; load_tile4<i32>(a.c[" + C + "].ids, base, nrows, full, id" + C + ");");
                 continue;
             }
-            if (t.isVarWidth()) {
+            if (cs.encoding == PGPU_ENC_VARCELL) {
+                line("raw128 q" + C + "[4]; for (int q = 0; q < 4; q++) { raw128 e; e.lo = 0; e.hi = 0; if (base + q < nrows) e = ((const raw128*)a.c[" + C + "].values)[base + q]; q" + C + "[q] = e; }");
+            } else if (t.isVarWidth()) {
                 line("i32 o" + C + "[5];");
                 line("if (full) { i32 t4[4]; load_tile4<i32>(a.c[" + C + "].offsets, base, nrows, true, t4); o" + C + "[0] = t4[0]; o" + C + "[1] = t4[1]; o" + C +
                      "[2] = t4[2]; o" + C + "[3] = t4[3]; o" + C + "[4] = a.c[" + C + "].offsets[base + 4]; }");
@@ -218,7 +220,10 @@ struct Gen {
                 if (t.isLongDecimal()) return "dec_from_raw(" + raw + ")";
                 return raw;
             };
-            if (cs.encoding == PGPU_ENC_PLAIN) {
+            if (cs.encoding == PGPU_ENC_VARCELL) {
+                line("const u64 x" + C + " = q" + C + "[r].lo, y" + C + " = q" + C + "[r].hi;");
+                if (cs.nullable) line("const bool z" + C + " = n" + C + "[r] != 0;");
+            } else if (cs.encoding == PGPU_ENC_PLAIN) {
                 if (t.isVarWidth()) {
                     int n = t.kind == TypeKind::VARCHAR ? t.precision : 0;
                     if (t.kind == TypeKind::VARCHAR && n <= 4 && stagedLoads) {
@@ -753,6 +758,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
             std::string C = std::to_string(c);
             Gen::StageOff so;
             if (cs.encoding == PGPU_ENC_RLE) continue;
+            if (cs.encoding == PGPU_ENC_VARCELL) { stagedPossible = false; break; }  // device-to-device pages of partial results: short
             if (cs.encoding == PGPU_ENC_DICTIONARY) {
                 so.values = region(kTile * 4);
                 copy(so.values, "(const char*)a.c[" + C + "].ids + row0 * 4", kTile * 4);

@@ -585,7 +585,10 @@ pgpu_status processDevicePage(pgpu_pipeline* p, Variant* v, const pgpu_column* c
             const pgpu_column& col = cols[c];
             const Type& t = plan.input[c];
             ColArg a{};
-            if (col.encoding == PGPU_ENC_PLAIN) {
+            if (col.encoding == PGPU_ENC_VARCELL) {
+                a.values = (const char*)col.values + (size_t)r0 * 16;
+                a.nulls = col.nulls ? col.nulls + r0 : nullptr;
+            } else if (col.encoding == PGPU_ENC_PLAIN) {
                 if (t.isVarWidth()) {
                     a.values = col.values;
                     a.offsets = col.offsets + r0;
@@ -640,6 +643,10 @@ pgpu_status validatePage(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncol
             sig[c].nullable = col.nulls != nullptr;
             if (rows > 0 && !col.values && !(t.isVarWidth())) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " has no values");
             if (t.isVarWidth() && !col.offsets) return fail(p, PGPU_INVALID_ARGUMENT, "var-width channel " + std::to_string(c) + " has no offsets");
+        } else if (col.encoding == PGPU_ENC_VARCELL) {
+            if (t.kind != TypeKind::VARCHAR || t.precision < 1 || t.precision > 15) return fail(p, PGPU_INVALID_ARGUMENT, "16-byte cell encoding is for VARCHAR(<=15) channels (channel " + std::to_string(c) + ")");
+            if (rows > 0 && !col.values) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " has no values");
+            sig[c].nullable = col.nulls != nullptr;
         } else if (col.encoding == PGPU_ENC_DICTIONARY || col.encoding == PGPU_ENC_RLE) {
             const pgpu_column* d = col.dictionary;
             if (!d || d->encoding != PGPU_ENC_PLAIN) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: nested dictionary/RLE encodings (channel " + std::to_string(c) + ")");
@@ -780,6 +787,8 @@ pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
         }
         return processDevicePage(p, v, cols, rows);
     }
+    for (int c : v->gen.usedChannels)
+        if (cols[c].encoding == PGPU_ENC_VARCELL) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: 16-byte cell columns in host pages (device-to-device encoding)");
     // host page: stage in chunks through the ring, then run as device chunks
     const bool pinned = (flags & PGPU_PAGE_PINNED) != 0;
     const bool compact = v->gen.mode == KernelMode::COMPACT;
@@ -1093,7 +1102,8 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
         const char* dv = (const char*)p->outDev[c].ptr + (size_t)r0 * d.stride;
         const uint8_t* dn = (const uint8_t*)p->outDevNulls[c].ptr + r0;
         if (!toHost) {
-            if (d.varWidth) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: device-resident var-width output");
+            if (d.varWidth && !(d.lenPrefixed && d.stride == 16)) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: device-resident var-width output");
+            if (d.varWidth) oc.encoding = PGPU_ENC_VARCELL;
             oc.values = dv;
             oc.nulls = dn;
             continue;

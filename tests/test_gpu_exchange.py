@@ -175,3 +175,100 @@ def test_peer_memory_exchange_two_processes():
     got = [row for _, rows, _ in results for row in rows]
     assert all(sent > 0 for _, _, sent in results)
     assert_rows_equal_ignore_order(got, single, nkeys=1, rtol=1e-12)
+
+
+def test_device_cells_feed_final():
+    """PARTIAL output stays in HBM (VARCHAR keys as 16-byte cells) and is fed to FINAL as a device page"""
+    from test_oracle_protocol import q1_final_plan
+    total = 300_000
+    single = run_gpu(tpch.q1_plan(), [tpch.q1_page(0, total, total)])
+    L = N.lib()
+    final = GpuPipelineOperator(q1_final_plan(), 0)
+    parts = []
+    try:
+        for part in range(2):
+            op = GpuPipelineOperator(tpch.q1_plan("partial"), 0)
+            parts.append(op)
+            op.addInput(tpch.q1_page(part * (total // 2), total // 2, total))
+            op.finish()
+            n = L.pgpu_output_channel_count(op._h)
+            cols = (N.Column * n)()
+            nc, rows = ctypes.c_int32(), ctypes.c_int64()
+            op._check(L.pgpu_get_output_device(op._h, cols, n, ctypes.byref(nc), ctypes.byref(rows)))
+            assert rows.value == 4 and cols[0].encoding == N.ENC_VARCELL and cols[1].encoding == N.ENC_VARCELL
+            final.addDeviceInput(cols, nc.value, rows.value)
+        final.finish()
+        out = []
+        while not final.isFinished():
+            p = final.getOutput()
+            if p is not None:
+                out.append(p)
+        assert_rows_equal_ignore_order(rows_of(out), single, nkeys=2, rtol=sequential_bound(total))
+    finally:
+        final.close()
+        for op in parts:
+            op.close()
+
+
+def _peer_gather_worker(rank, world, port, total, q):
+    import os
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import torch.distributed as dist
+    from test_oracle_protocol import q1_final_plan
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    partial = final = ex = None
+    try:
+        per = total // world
+        partial = GpuPipelineOperator(tpch.q1_plan("partial"), 0)
+        final = GpuPipelineOperator(q1_final_plan(), 0)
+        ex = X.PeerGather(0, world, rank, "pgpu_test_gather_%d" % port)
+        page = tpch.q1_page(rank * per, per, total)
+        rows = []
+        for step in range(3):                                  # later exchanges reuse the mappings and the mailbox
+            partial.reset()
+            final.reset()
+            partial.addInput(page)
+            partial.finish()
+            assert ex.run(partial, final) == 4 * world
+            out = []
+            while not final.isFinished():
+                p = final.getOutput()
+                if p is not None:
+                    out.append(p)
+            rows = rows_of(out)
+        q.put((rank, rows, 0))
+    except BaseException:
+        import traceback
+        q.put((rank, traceback.format_exc(), -1))
+        raise
+    finally:
+        if ex is not None:
+            ex.close()
+        for op in (partial, final):
+            if op is not None:
+                op.close()
+        dist.destroy_process_group()
+
+
+def test_peer_gather_two_processes():
+    """small group counts: every rank's FINAL reads both ranks' partial pages through CUDA IPC; no data-path collective"""
+    import os
+    import torch.multiprocessing as mp
+    world, total, port = 2, 200_000, 35000 + os.getpid() % 2000
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_peer_gather_worker, args=(r, world, port, total, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = []
+    for _ in range(world):
+        results.append(q.get(timeout=300))
+        assert results[-1][2] >= 0, results[-1][1]
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    single = run_gpu(tpch.q1_plan(), [tpch.q1_page(0, total, total)])
+    for _, rows, _ in results:
+        assert_rows_equal_ignore_order(rows, single, nkeys=2, rtol=sequential_bound(total))

@@ -13,8 +13,16 @@ d=json.loads(sys.stdin.read()); print('$tag', 'ms/step', round(d['ms_per_step'],
   grep -v "^\*\*\*\|OMP_NUM\|^$" gpurun_out/scale${N}_$tag.err | tail -4
 }
 if [ "$2" = "trace" ]; then
-  export PGPU_BENCH_TRACE=1
+  PGPU_BENCH_TRACE=1 run q1t --workload q1 --steps 20 --warmup 3 --no-cpu --no-e2e
   run q1 --workload q1 --steps 20 --warmup 3 --no-cpu --no-e2e
+  run q1_nccl --workload q1 --steps 20 --warmup 3 --no-cpu --no-e2e --exchange nccl
+  run q6 --workload q6 --steps 20 --warmup 3 --no-cpu --no-e2e
+  exit 0
+fi
+if [ "$2" = "small" ]; then
+  run q1 --workload q1 --steps 10 --warmup 3 --no-cpu
+  run q6 --workload q6 --steps 10 --warmup 3 --no-cpu --no-e2e
+  run q1dict --workload q1dict --steps 10 --warmup 3 --no-cpu --no-e2e
   exit 0
 fi
 run q1 --workload q1 --steps 10 --warmup 3 --no-cpu
