@@ -21,7 +21,7 @@ sys.path.insert(0, ROOT)
 SF100_ROWS = 600_037_902  # TPC-H lineitem at sf100
 # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the ncu --set full captures under
 # profiles/ (bytes; None = not captured for that workload)
-# stored as measured DRAM bytes / algorithmic bytes of the captured launch (profiles/r01d_q1_staged_ncu_raw.txt)
+# stored as measured DRAM bytes / algorithmic bytes of the captured launch (profiles/r01e_q1_staged_ncu_raw.txt)
 TRAFFIC_RATIO = {"q1": 1.0014}
 
 

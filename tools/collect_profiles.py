@@ -22,7 +22,9 @@ for w in ("q1", "q6", "highcard", "highcard_shuffled", "q1dict", "ref"):
         rows.append((w, d))
 if os.path.exists(os.path.join(G, "launches_q1.csv")):
     shutil.copy(os.path.join(G, "launches_q1.csv"), os.path.join(P, "%s_q1_launches.csv" % tag))
-for rep, name in (("q1_full", "q1_staged"), ("hc_full", "highcard"), ("q6_full", "q6")):
+if os.path.exists(os.path.join(G, "launches_highcard.csv")):
+    shutil.copy(os.path.join(G, "launches_highcard.csv"), os.path.join(P, "%s_highcard_launches.csv" % tag))
+for rep, name in (("q1_full", "q1_staged"), ("hc_full", "highcard"), ("q6_full", "q6"), ("q1dict_full", "q1dict_staged")):
     f = os.path.join(G, rep + ".ncu-rep")
     if not os.path.exists(f):
         continue

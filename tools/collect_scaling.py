@@ -12,7 +12,7 @@ G, P = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
 tag = sys.argv[1]
 base_tag = sys.argv[2] if len(sys.argv) > 2 else tag
 single = {}
-for w, name in (("q1", "q1"), ("q6", "q6"), ("highcard", "hc_peer"), ("highcard", "hc_nccl"), ("highcard_shuffled", "hcs_peer")):
+for w, name in (("q1", "q1"), ("q1", "q1_nccl"), ("q6", "q6"), ("q1dict", "q1dict"), ("highcard", "hc_peer"), ("highcard", "hc_nccl"), ("highcard_shuffled", "hcs_peer")):
     f = os.path.join(P, "%s_bench_%s.json" % (base_tag, w))
     if os.path.exists(f):
         single[name] = json.loads(open(f).read().strip().splitlines()[-1])
@@ -30,7 +30,7 @@ for f in sorted(glob.glob(os.path.join(G, "scale*_*.json"))):
 with open(os.path.join(P, "%s_scaling.md" % tag), "w") as out:
     out.write("Weak scaling, %s rows per GPU (sf100 shard each), one process per GPU under torchrun; `value` = all ranks' rows / max-over-ranks device time.\n\n" % "600 037 902")
     out.write("| workload / exchange | GPUs | ms/step | rows/s | vs 1 GPU | efficiency | e2e rows/s | exchange bytes sent per rank |\n|---|---|---|---|---|---|---|---|\n")
-    for name in ("q1", "q6", "hc_peer", "hc_nccl", "hcs_peer"):
+    for name in ("q1", "q1_nccl", "q6", "q1dict", "hc_peer", "hc_nccl", "hcs_peer"):
         s = single.get(name)
         if s:
             out.write("| %s | 1 | %.2f | %.3g | 1.00 | 1.00 | %s | |\n" % (name, s["ms_per_step"], s["value"], ("%.3g" % s["e2e"]["value"]) if s.get("e2e") else ""))

@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 exec > gpurun_out/gpu_check.log 2>&1
 set -x
 nvidia-smi -L; nproc; free -g | head -2; which java javac mvn; ls /usr/lib/jvm
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"
+timeout 900 python -m pytest tests -m gpu -x -q --timeout 300 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"
 tail -3 gpurun_out/pytest_gpu.log
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
 timeout 1200 python bench.py > gpurun_out/bench_q1.json 2> gpurun_out/bench_q1.err; echo "bench q1 exit $?"
@@ -24,4 +24,8 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:pgpu
   python bench.py --workload highcard --steps 1 --warmup 1 --no-e2e --no-cpu --rows 200000000 > gpurun_out/ncu_full_hc.log 2>&1; echo "ncu full hc exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:pgpu_k_page -s 1 -c 1 -f -o gpurun_out/q6_full \
   python bench.py --workload q6 --steps 1 --warmup 1 --no-e2e --no-cpu --rows 200000000 > gpurun_out/ncu_full_q6.log 2>&1; echo "ncu full q6 exit $?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:pgpu_k_page_staged -s 2 -c 1 -f -o gpurun_out/q1dict_full \
+  python bench.py --workload q1dict --steps 1 --warmup 1 --no-e2e --no-cpu --rows 200000000 > gpurun_out/ncu_full_q1dict.log 2>&1; echo "ncu full q1dict exit $?"
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_highcard.csv \
+  python bench.py --workload highcard --steps 1 --warmup 1 --no-e2e --no-cpu > /dev/null 2>&1; echo "ncu launches highcard exit $?"
 ls -la gpurun_out

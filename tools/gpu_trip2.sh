@@ -19,14 +19,17 @@ if [ "$2" = "trace" ]; then
   run q6 --workload q6 --steps 20 --warmup 3 --no-cpu --no-e2e
   exit 0
 fi
-if [ "$2" = "small" ]; then
+if [ "$2" = "lean" ]; then
   run q1 --workload q1 --steps 10 --warmup 3 --no-cpu
   run q6 --workload q6 --steps 10 --warmup 3 --no-cpu --no-e2e
   run q1dict --workload q1dict --steps 10 --warmup 3 --no-cpu --no-e2e
+  run hc_peer --workload highcard --steps 5 --warmup 3 --no-cpu --no-e2e --exchange peer
   exit 0
 fi
 run q1 --workload q1 --steps 10 --warmup 3 --no-cpu
+run q1_nccl --workload q1 --steps 10 --warmup 3 --no-cpu --no-e2e --exchange nccl
 run q6 --workload q6 --steps 10 --warmup 3 --no-cpu --no-e2e
+run q1dict --workload q1dict --steps 10 --warmup 3 --no-cpu --no-e2e
 run hc_peer --workload highcard --steps 5 --warmup 3 --no-cpu --no-e2e --exchange peer
 run hc_nccl --workload highcard --steps 5 --warmup 3 --no-cpu --no-e2e --exchange nccl
 run hcs_peer --workload highcard_shuffled --steps 5 --warmup 3 --no-cpu --no-e2e --exchange peer
