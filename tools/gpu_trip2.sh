@@ -24,6 +24,12 @@ if [ "$2" = "lean" ]; then
   run q6 --workload q6 --steps 10 --warmup 3 --no-cpu --no-e2e
   run q1dict --workload q1dict --steps 10 --warmup 3 --no-cpu --no-e2e
   run hc_peer --workload highcard --steps 5 --warmup 3 --no-cpu --no-e2e --exchange peer
+  # config 5: sf1000 (5 999 989 709 rows) split over the N GPUs, device resident
+  R=$((5999989709 / N))
+  if [ $R -le 1600000000 ]; then
+    run q1_sf1000 --workload q1 --rows $R --steps 5 --warmup 3 --no-cpu --no-e2e
+    run hc_sf1000 --workload highcard --rows $R --steps 3 --warmup 3 --no-cpu --no-e2e --exchange peer
+  fi
   exit 0
 fi
 run q1 --workload q1 --steps 10 --warmup 3 --no-cpu
