@@ -40,4 +40,11 @@ with open(os.path.join(P, "%s_scaling.md" % tag), "w") as out:
             sp = d["value"] / s["value"] if s else float("nan")
             out.write("| %s | %d | %.2f | %.3g | %.2f | %.2f | %s | %s |\n" % (name, n, d["ms_per_step"], d["value"], sp, sp / n, ("%.3g" % d["e2e"]["value"]) if d.get("e2e") else "",
                                                                      (d.get("exchange") or {}).get("bytes_sent_per_rank_per_step", "")))
+    big = [(nm, n, d) for nm, n, d in rows if nm.endswith("_sf1000")]
+    if big:
+        out.write("\nConfig 5 — sf1000 (5 999 989 709 lineitem rows in total, device resident, split over the GPUs; 1 and 2 GPUs cannot hold it: "
+                  "276 GB of Q1 columns, and one page of VARCHAR(1) bytes is limited to 2^31 rows by the int32 offsets):\n\n")
+        out.write("| workload | GPUs | rows per GPU | ms/step | rows/s | GB/s (algorithmic) |\n|---|---|---|---|---|---|\n")
+        for nm, n, d in sorted(big, key=lambda r: (r[0], r[1])):
+            out.write("| %s | %d | %d | %.2f | %.3g | %.0f |\n" % (nm, n, d["config"]["rows_per_gpu"], d["ms_per_step"], d["value"], d["gb_per_s"]))
 print(open(os.path.join(P, "%s_scaling.md" % tag)).read())
