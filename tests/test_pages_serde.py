@@ -1,0 +1,96 @@
+"""The page wire format (PagesSerdeUtil + the spi block encodings): the oracle's writer/reader against the reference's
+serialized-size known answers (main/test/execution/buffer/TestPagesSerde.java:64-108) and round trips; the GPU ingest of
+serialized pages (pgpu_add_serialized_page) against the same pages fed block by block."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle"))
+import pages_serde as S  # noqa: E402
+
+from presto_b200 import tpch  # noqa: E402
+from presto_b200.spi import (BIGINT, BOOLEAN, DATE, DOUBLE, INTEGER, VARCHAR, ByteArrayBlock, DictionaryBlock, Int128ArrayBlock, IntArrayBlock,  # noqa: E402
+                             LongArrayBlock, Page, RunLengthEncodedBlock, VariableWidthBlock, block_of, createDecimalType, createVarcharType)
+
+FRAME = 13  # positionCount, markers, uncompressedSize, size (PagesSerdeUtil.writeSerializedPage)
+
+
+def test_bigint_serialized_size_kat():
+    # TestPagesSerde.testBigintSerializedSize: an empty builder builds RLE(null) x 0 -> 52 bytes; values: 35 + 9, then + 8
+    empty = RunLengthEncodedBlock(LongArrayBlock(BIGINT, [0], [1]), 0)
+    assert len(S.write_serialized_page([empty], 0)) == 52
+    assert len(S.write_serialized_page([LongArrayBlock(BIGINT, [123])], 1)) == 35 + 9
+    assert len(S.write_serialized_page([LongArrayBlock(BIGINT, [123, 456])], 2)) == 35 + 9 + 8
+
+
+def test_varchar_serialized_size_kat():
+    # TestPagesSerde.testVarcharSerializedSize: 44 empty, + 4 + 5 for "alice", + 4 + 3 for "bob"
+    assert len(S.write_serialized_page([VariableWidthBlock.from_values(VARCHAR, [])], 0)) == 44
+    assert len(S.write_serialized_page([VariableWidthBlock.from_values(VARCHAR, ["alice"])], 1)) == 44 + 9
+    assert len(S.write_serialized_page([VariableWidthBlock.from_values(VARCHAR, ["alice", "bob"])], 2)) == 44 + 9 + 7
+
+
+def test_null_bits_are_msb_first():
+    # EncoderUtil.encodeNullsAsBits: position 0 -> 0b1000_0000; the ragged tail fills the high bits of the last byte
+    assert S.encode_nulls_as_bits(np.array([1, 0, 0, 0, 0, 0, 0, 1, 0, 1], dtype=np.uint8), 10) == bytes([1, 0b10000001, 0b01000000])
+    assert S.encode_nulls_as_bits(None, 10) == b"\x00"
+
+
+def sample_blocks(n, seed=7):
+    rng = np.random.default_rng(seed)
+    nulls = (rng.random(n) < 0.3).astype(np.uint8)
+    words = ["", "a", "bc", "def", "ghij"]
+    return [
+        LongArrayBlock(BIGINT, rng.integers(-2**62, 2**62, n)),
+        LongArrayBlock(BIGINT, rng.integers(-2**62, 2**62, n), nulls),
+        LongArrayBlock(DOUBLE, rng.random(n) * 100, nulls),
+        IntArrayBlock(DATE, rng.integers(0, 20000, n)),
+        IntArrayBlock(INTEGER, rng.integers(-2**31, 2**31 - 1, n), nulls),
+        ByteArrayBlock(BOOLEAN, rng.integers(0, 2, n), nulls),
+        Int128ArrayBlock(createDecimalType(30, 2), [int(x) * 10**12 for x in rng.integers(-10**9, 10**9, n)], nulls),
+        VariableWidthBlock.from_values(createVarcharType(4), [None if nulls[i] else words[int(x)] for i, x in enumerate(rng.integers(0, 5, n))]),
+        VariableWidthBlock.from_values(createVarcharType(4), [words[int(x)] for x in rng.integers(0, 5, n)]),
+        DictionaryBlock(LongArrayBlock(DOUBLE, [0.0, 0.01, 0.02, 0.03]), rng.integers(0, 4, n)),
+        DictionaryBlock(VariableWidthBlock.from_values(createVarcharType(1), ["A", "N", None]), rng.integers(0, 3, n)),
+        RunLengthEncodedBlock(LongArrayBlock(BIGINT, [42]), n),
+    ]
+
+
+def storage_values(block):
+    """what the wire carries: raw storage words / bytes per position"""
+    if isinstance(block, DictionaryBlock):
+        d = storage_values(block.dictionary)
+        return [d[i] for i in block.ids.tolist()]
+    if isinstance(block, RunLengthEncodedBlock):
+        return storage_values(block.value) * block.position_count
+    n = block.position_count
+    nulls = block.valueIsNull
+    if isinstance(block, VariableWidthBlock):
+        raw = block.data.tobytes()
+        vals = [raw[block.offsets[i]:block.offsets[i + 1]] for i in range(n)]
+    elif isinstance(block, Int128ArrayBlock):
+        vals = [bytes(r) for r in block.values.view(np.uint8).reshape(n, 16)]
+    else:
+        vals = block.values.tolist()
+    return [None if nulls is not None and nulls[i] else vals[i] for i in range(n)]
+
+
+@pytest.mark.parametrize("n", [0, 1, 7, 8, 9, 64, 1000])
+def test_round_trip_every_encoding(n):
+    blocks = sample_blocks(n)
+    data = S.write_raw_page(blocks)
+    back = S.read_raw_page(data)
+    assert len(back) == len(blocks)
+    for b, r in zip(blocks, back):
+        assert r["positionCount"] == n
+        assert S.block_values(r) == storage_values(b)
+
+
+def test_non_null_values_only_are_written():
+    # LongArrayBlockEncoding.writeBlock: a block that may have nulls carries nonNullCount + the non-null values
+    b = LongArrayBlock(BIGINT, [1, 2, 3, 4], [0, 1, 1, 0])
+    data = S.write_block(b)
+    assert len(data) == 4 + 10 + 4 + 1 + 1 + 4 + 2 * 8
+    assert data[-16:] == np.array([1, 4], dtype="<i8").tobytes()
