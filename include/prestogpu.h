@@ -119,6 +119,13 @@ const char* pgpu_last_error(const pgpu_pipeline* p);
 int32_t pgpu_needs_input(const pgpu_pipeline* p);
 /* Operator.addInput(Page): columns are copied (or DMA'd) before the call returns control of unpinned buffers. */
 pgpu_status pgpu_add_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows, uint32_t flags);
+/* Operator.addInput of a Page in the reference's wire format: `data` (host) is the uncompressed payload of a SerializedPage —
+ * what PagesSerdeUtil.writeRawPage produces (main/execution/buffer/PagesSerdeUtil.java:45-62): int32 channel count, then per
+ * block the length-prefixed encoding name and body (LONG_ARRAY / INT_ARRAY / BYTE_ARRAY / INT128_ARRAY / VARIABLE_WIDTH, and
+ * DICTIONARY / RLE over those; spi/block/{Long,Int,...}ArrayBlockEncoding.java etc.). Only the block headers are read on the host: the payload goes
+ * to the device in ONE copy and is decoded there (null bit stream -> flags, non-null-only values -> positions). Compressed or
+ * encrypted pages (PageCodecMarker) must be decoded by the caller first. `data` may be reused when the call returns. */
+pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size_t len, int64_t position_count);
 /* Same, with device-resident blocks (no copy). Buffers must stay valid until pgpu_sync(). */
 pgpu_status pgpu_add_device_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows);
 /* Operator.finish(): no more input; may be called repeatedly (main/operator/Driver.java:368-372). */

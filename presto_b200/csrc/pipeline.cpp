@@ -22,6 +22,7 @@
 #include "exchange.h"
 #include "jit.h"
 #include "plan.h"
+#include "serde.h"
 
 using namespace pgpu;
 
@@ -147,6 +148,8 @@ struct pgpu_pipeline {
     std::vector<DeviceBuf> outDevNulls;
     std::vector<HostOut> outHost, outHostNulls, outHostAux;  // aux: offsets for var-width
     int64_t outCapacityRows = 0;
+    // serialized-page ingest: the payload + the decoded, aligned block arrays of the page being added
+    DeviceBuf serdeArena;
     // partitioned output (exchange)
     // one allocation for every partitioned column (a peer maps it with a single IPC handle); arenas replaced by a
     // larger one stay allocated until destroy because a peer may still have them mapped
@@ -995,6 +998,7 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
         }
         if (p->outArena.ptr) cudaFree(p->outArena.ptr);
         if (p->outHostArena.ptr) cudaFreeHost(p->outHostArena.ptr);
+        if (p->serdeArena.ptr) cudaFree(p->serdeArena.ptr);
         if (p->partArena.ptr) cudaFree(p->partArena.ptr);
         for (void* q : p->partRetired) cudaFree(q);
         for (auto* b : {&p->partPid, &p->partDst, &p->partCounts})
@@ -1028,6 +1032,216 @@ pgpu_status pgpu_add_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
 pgpu_status pgpu_add_device_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows) {
     if (!p) return PGPU_INVALID_ARGUMENT;
     pgpu_status st = addPageCommon(p, cols, ncols, rows, true, 0);
+    return st ? st : updatePartialFill(p);
+}
+
+// ---- pages in the reference's wire format -----------------------------------------------------------------------------------
+namespace {
+
+// One block of a serialized page: where its pieces lie in the payload (byte offsets). Parsed on the host from the few
+// header bytes only; the arrays themselves are never touched by the CPU.
+struct WireBlock {
+    enum Kind { FLAT, VARWIDTH, DICTIONARY, RLE } kind = FLAT;
+    int width = 0;           // FLAT: bytes per value
+    int64_t n = 0;           // positionCount
+    bool hasNulls = false;
+    size_t bitsOff = 0;      // packed null flags, (n + 7) / 8 bytes
+    int64_t nonNull = 0;     // FLAT with nulls: values present
+    size_t valuesOff = 0;    // FLAT: values; VARWIDTH: bytes; DICTIONARY: ids
+    size_t offsetsOff = 0;   // VARWIDTH: n int32 END offsets
+    int64_t dataLen = 0;     // VARWIDTH: total bytes
+    std::unique_ptr<WireBlock> child;  // DICTIONARY: dictionary; RLE: value
+};
+
+struct WireReader {
+    const uint8_t* d;
+    size_t len, pos = 0;
+    bool ok = true;
+    int32_t i32() {
+        if (pos + 4 > len) { ok = false; return 0; }
+        int32_t v;
+        memcpy(&v, d + pos, 4);
+        pos += 4;
+        return v;
+    }
+    size_t skip(size_t n) {
+        size_t at = pos;
+        if (n > len - std::min(pos, len)) { ok = false; return at; }
+        pos += n;
+        return at;
+    }
+};
+
+// main/metadata/InternalBlockEncodingSerde.java:43-53 + spi/block/*BlockEncoding.readBlock
+bool parseWireBlock(WireReader& r, WireBlock& b, int depth, std::string& why) {
+    const int32_t nameLen = r.i32();
+    if (!r.ok || nameLen < 0 || nameLen > 32) { why = "corrupt block encoding name"; return false; }
+    const size_t nameAt = r.skip((size_t)nameLen);
+    if (!r.ok) { why = "truncated page"; return false; }
+    const std::string name((const char*)r.d + nameAt, (size_t)nameLen);
+    b.n = r.i32();
+    if (!r.ok || b.n < 0) { why = "truncated page"; return false; }
+    auto nulls = [&]() {  // spi/block/EncoderUtil.java:33-70
+        const size_t at = r.skip(1);
+        if (!r.ok) return;
+        b.hasNulls = r.d[at] != 0;
+        if (b.hasNulls) b.bitsOff = r.skip((size_t)((b.n + 7) / 8));
+    };
+    int width = name == "LONG_ARRAY" ? 8 : name == "INT_ARRAY" ? 4 : name == "BYTE_ARRAY" ? 1 : name == "INT128_ARRAY" ? 16 : 0;
+    if (width) {
+        b.kind = WireBlock::FLAT;
+        b.width = width;
+        nulls();
+        b.nonNull = b.n;
+        if (r.ok && b.hasNulls) b.nonNull = r.i32();
+        if (!r.ok || b.nonNull < 0 || b.nonNull > b.n) { why = "corrupt " + name + " block"; return false; }
+        b.valuesOff = r.skip((size_t)b.nonNull * (size_t)width);
+    } else if (name == "VARIABLE_WIDTH") {
+        b.kind = WireBlock::VARWIDTH;
+        b.offsetsOff = r.skip((size_t)b.n * 4);
+        nulls();
+        b.dataLen = r.i32();
+        if (!r.ok || b.dataLen < 0) { why = "corrupt VARIABLE_WIDTH block"; return false; }
+        b.valuesOff = r.skip((size_t)b.dataLen);
+    } else if (name == "DICTIONARY" || name == "RLE") {
+        if (depth > 0) { why = "not supported on the GPU path: nested dictionary/RLE encodings"; return false; }
+        b.kind = name == "RLE" ? WireBlock::RLE : WireBlock::DICTIONARY;
+        b.child.reset(new WireBlock());
+        if (!parseWireBlock(r, *b.child, depth + 1, why)) return false;
+        if (b.kind == WireBlock::DICTIONARY) {
+            b.valuesOff = r.skip((size_t)b.n * 4);
+            r.skip(24);  // DictionaryId: most / least significant bits, sequence id
+        } else if (b.child->n != 1) {
+            why = "RLE value block must have exactly one position";
+            return false;
+        }
+    } else {
+        why = "not supported on the GPU path: block encoding " + name;
+        return false;
+    }
+    if (!r.ok) { why = "truncated page"; return false; }
+    return true;
+}
+
+}  // namespace
+
+pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size_t len, int64_t position_count) {
+    if (!p || (!data && len)) return PGPU_INVALID_ARGUMENT;
+    if (p->device < 0) return fail(p, PGPU_INVALID_STATE, "pipeline was created compile-only (device < 0)");
+    if (p->finishing) return fail(p, PGPU_INVALID_STATE, "Operator is already finishing");
+    if (!pgpu_needs_input(p)) return fail(p, PGPU_INVALID_STATE, "Operator does not need input");
+    const Plan& plan = *p->plan;
+    WireReader r{data, len};
+    const int32_t nblocks = r.i32();  // PagesSerdeUtil.readRawPage
+    if (!r.ok || nblocks != (int)plan.input.size())
+        return fail(p, PGPU_INVALID_ARGUMENT, "page has " + std::to_string(nblocks) + " channels, plan expects " + std::to_string(plan.input.size()));
+    std::vector<WireBlock> blocks((size_t)nblocks);
+    for (int c = 0; c < nblocks; c++) {
+        std::string why;
+        if (!parseWireBlock(r, blocks[c], 0, why))
+            return fail(p, why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT, why + " (channel " + std::to_string(c) + ")");
+        if (blocks[c].n != position_count) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " position count differs from the page");
+        const WireBlock& leaf = blocks[c].child ? *blocks[c].child : blocks[c];
+        const Type& t = plan.input[c];
+        const bool match = t.isVarWidth() ? leaf.kind == WireBlock::VARWIDTH : (leaf.kind == WireBlock::FLAT && leaf.width == t.width());
+        if (!match) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " block encoding does not match the plan type (" + t.str() + ")");
+    }
+    if (r.pos != len) return fail(p, PGPU_INVALID_ARGUMENT, "trailing bytes after the last block");
+    CU(cudaSetDevice(p->device));
+    // device arena: [payload][decoded arrays, each 256-byte aligned]
+    size_t need = align256(len);
+    auto reserve = [&](size_t bytes) {
+        size_t at = need;
+        need += align256(std::max<size_t>(bytes, 16));
+        return at;
+    };
+    struct Placed {
+        size_t values = 0, nulls = 0, offsets = 0, compact = 0, scratch = 0;
+    };
+    auto place = [&](const WireBlock& b) {
+        Placed q;
+        if (b.kind == WireBlock::FLAT) {
+            q.values = reserve((size_t)b.n * b.width);
+            if (b.hasNulls) {
+                q.nulls = reserve((size_t)b.n);
+                q.compact = reserve((size_t)b.nonNull * b.width);
+                q.scratch = reserve(serdeScratchWords(b.n) * 4);
+            }
+        } else if (b.kind == WireBlock::VARWIDTH) {
+            q.offsets = reserve(((size_t)b.n + 1) * 4 + 16);
+            q.values = reserve((size_t)b.dataLen + 16);
+            if (b.hasNulls) q.nulls = reserve((size_t)b.n);
+        } else if (b.kind == WireBlock::DICTIONARY) {
+            q.values = reserve((size_t)b.n * 4);
+        }
+        return q;
+    };
+    std::vector<Placed> at((size_t)nblocks), atChild((size_t)nblocks);
+    for (int c = 0; c < nblocks; c++) {
+        at[c] = place(blocks[c]);
+        if (blocks[c].child) atChild[c] = place(*blocks[c].child);
+    }
+    pgpu_status st = ensureDev(p, p->serdeArena, need);
+    if (st) return st;
+    char* base = (char*)p->serdeArena.ptr;
+    if (len) CU(cudaMemcpyAsync(base, data, len, cudaMemcpyHostToDevice, p->stream));  // the whole page in one DMA
+    p->stats.h2d_bytes += (int64_t)len;
+    // decode on the device: aligned copies of the arrays, null flags unpacked, sparse values re-expanded
+    auto d2d = [&](size_t dst, size_t src, size_t bytes) -> cudaError_t {
+        return bytes ? cudaMemcpyAsync(base + dst, base + src, bytes, cudaMemcpyDeviceToDevice, p->stream) : cudaSuccess;
+    };
+    auto decode = [&](const WireBlock& b, const Placed& q, const Type& t, pgpu_column& col) -> cudaError_t {
+        cudaError_t e = cudaSuccess;
+        memset(&col, 0, sizeof col);
+        col.encoding = PGPU_ENC_PLAIN;
+        col.type_kind = (int32_t)t.kind;
+        col.precision = t.precision;
+        col.scale = t.scale;
+        col.position_count = b.n;
+        if (b.kind == WireBlock::FLAT) {
+            col.values = base + q.values;
+            if (!b.hasNulls) return d2d(q.values, b.valuesOff, (size_t)b.n * b.width);
+            col.nulls = (const uint8_t*)(base + q.nulls);
+            if ((e = d2d(q.compact, b.valuesOff, (size_t)b.nonNull * b.width))) return e;
+            p->stats.kernel_launches += 3;
+            return expandNulls(p->stream, (const uint8_t*)(base + b.bitsOff), b.n, base + q.compact, base + q.values, (uint8_t*)(base + q.nulls), b.width, (uint32_t*)(base + q.scratch));
+        }
+        // VARWIDTH: offsets[0] = 0, offsets[1..n] = the END offsets of the wire (VariableWidthBlockEncoding.readBlock)
+        col.offsets = (const int32_t*)(base + q.offsets);
+        col.values = base + q.values;
+        if ((e = cudaMemsetAsync(base + q.offsets, 0, 4, p->stream))) return e;
+        if ((e = d2d(q.offsets + 4, b.offsetsOff, (size_t)b.n * 4))) return e;
+        if ((e = d2d(q.values, b.valuesOff, (size_t)b.dataLen))) return e;
+        if (b.hasNulls) {
+            col.nulls = (const uint8_t*)(base + q.nulls);
+            p->stats.kernel_launches += 1;
+            return unpackNullBits(p->stream, (const uint8_t*)(base + b.bitsOff), b.n, (uint8_t*)(base + q.nulls));
+        }
+        return e;
+    };
+    std::vector<pgpu_column> cols((size_t)nblocks), dicts((size_t)nblocks);
+    for (int c = 0; c < nblocks; c++) {
+        const WireBlock& b = blocks[c];
+        const Type& t = plan.input[c];
+        if (!b.child) {
+            CU(decode(b, at[c], t, cols[c]));
+            continue;
+        }
+        CU(decode(*b.child, atChild[c], t, dicts[c]));
+        pgpu_column& col = cols[c];
+        memset(&col, 0, sizeof col);
+        col.encoding = b.kind == WireBlock::RLE ? PGPU_ENC_RLE : PGPU_ENC_DICTIONARY;
+        col.type_kind = (int32_t)t.kind;
+        col.precision = t.precision;
+        col.scale = t.scale;
+        col.position_count = b.n;
+        col.dictionary = &dicts[c];
+        if (b.kind == WireBlock::DICTIONARY) {
+            CU(d2d(at[c].values, b.valuesOff, (size_t)b.n * 4));
+            col.ids = (const int32_t*)(base + at[c].values);
+        }
+    }
+    st = addPageCommon(p, cols.data(), nblocks, position_count, true, 0);
     return st ? st : updatePartialFill(p);
 }
 

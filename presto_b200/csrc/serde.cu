@@ -1,0 +1,133 @@
+// serde.cu — see serde.h. Ahead-of-time sm_100a kernels.
+#include "serde.h"
+
+namespace pgpu {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr unsigned kFull = 0xffffffffu;
+
+__device__ inline bool isNullBit(const uint8_t* bits, int64_t p) { return (bits[p >> 3] >> (7 - (int)(p & 7))) & 1; }
+
+// the 4 positions of a thread: bit i of the result = position base + i is NOT null (positions >= n count as null)
+__device__ inline unsigned liveMask(const uint8_t* bits, int64_t base, int64_t n) {
+    unsigned m = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (base + i < n && !isNullBit(bits, base + i)) m |= 1u << i;
+    return m;
+}
+
+__global__ void __launch_bounds__(kThreads) k_live_counts(const uint8_t* bits, int64_t n, uint32_t* counts) {
+    __shared__ unsigned s_total;
+    if (threadIdx.x == 0) s_total = 0;
+    __syncthreads();
+    const int64_t base = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
+    unsigned c = __popc(liveMask(bits, base, n));
+    c = __reduce_add_sync(kFull, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_total, c);
+    __syncthreads();
+    if (threadIdx.x == 0) counts[blockIdx.x] = s_total;
+}
+
+// exclusive scan of counts[0 .. m) in place, counts[m] = total; one block
+__global__ void __launch_bounds__(1024) k_scan_counts(uint32_t* counts, int64_t m) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t i0 = 0; i0 < m; i0 += 1024) {
+        const int64_t i = i0 + threadIdx.x;
+        const uint32_t v = i < m ? counts[i] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t w = s_warp[lane];
+            uint32_t wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(kFull, wi, d);
+                if (lane >= d) wi += t;
+            }
+            s_warp[lane] = wi - w;
+        }
+        __syncthreads();
+        const uint32_t carry = s_carry;
+        if (i < m) counts[i] = carry + s_warp[warp] + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = carry + s_warp[warp] + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) counts[m] = s_carry;
+}
+
+template <typename T>
+__device__ inline T zeroOf() { return T(0); }
+template <>
+__device__ inline uint4 zeroOf<uint4>() { return make_uint4(0, 0, 0, 0); }
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_expand(const uint8_t* bits, int64_t n, const T* compact, T* values, uint8_t* nulls, const uint32_t* blockBase) {
+    __shared__ uint32_t s_warp[kThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t base = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
+    const unsigned m = liveMask(bits, base, n);
+    const uint32_t cnt = __popc(m);
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(kFull, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0;
+    for (int w = 0; w < warp; w++) before += s_warp[w];
+    uint64_t src = (uint64_t)blockBase[blockIdx.x] + before + incl - cnt;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if (base + i >= n) break;
+        const bool live = (m >> i) & 1;
+        values[base + i] = live ? compact[src] : zeroOf<T>();
+        nulls[base + i] = live ? 0 : 1;
+        src += live ? 1 : 0;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_unpack_bits(const uint8_t* bits, int64_t n, uint8_t* nulls) {
+    for (int64_t p = (int64_t)blockIdx.x * kThreads + threadIdx.x; p < n; p += (int64_t)gridDim.x * kThreads) nulls[p] = isNullBit(bits, p) ? 1 : 0;
+}
+
+}  // namespace
+
+cudaError_t expandNulls(cudaStream_t stream, const uint8_t* bits, int64_t n, const void* compact, void* values, uint8_t* nulls, int width, uint32_t* scratch) {
+    if (n <= 0) return cudaSuccess;
+    const int64_t nblocks = (n + kSerdeBlockPositions - 1) / kSerdeBlockPositions;
+    k_live_counts<<<(unsigned)nblocks, kThreads, 0, stream>>>(bits, n, scratch);
+    k_scan_counts<<<1, 1024, 0, stream>>>(scratch, nblocks);
+    switch (width) {
+        case 1: k_expand<uint8_t><<<(unsigned)nblocks, kThreads, 0, stream>>>(bits, n, (const uint8_t*)compact, (uint8_t*)values, nulls, scratch); break;
+        case 4: k_expand<uint32_t><<<(unsigned)nblocks, kThreads, 0, stream>>>(bits, n, (const uint32_t*)compact, (uint32_t*)values, nulls, scratch); break;
+        case 8: k_expand<uint64_t><<<(unsigned)nblocks, kThreads, 0, stream>>>(bits, n, (const uint64_t*)compact, (uint64_t*)values, nulls, scratch); break;
+        case 16: k_expand<uint4><<<(unsigned)nblocks, kThreads, 0, stream>>>(bits, n, (const uint4*)compact, (uint4*)values, nulls, scratch); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t unpackNullBits(cudaStream_t stream, const uint8_t* bits, int64_t n, uint8_t* nulls) {
+    if (n <= 0) return cudaSuccess;
+    int64_t g = (n + kThreads - 1) / kThreads;
+    if (g > 148 * 16) g = 148 * 16;
+    k_unpack_bits<<<(unsigned)g, kThreads, 0, stream>>>(bits, n, nulls);
+    return cudaGetLastError();
+}
+
+}  // namespace pgpu

@@ -117,6 +117,11 @@ class GpuPipelineOperator:
         """cols: ctypes array of pgpu_column holding DEVICE pointers."""
         self._check(self._lib.pgpu_add_device_page(self._h, cols, ncols, rows))
 
+    def addSerializedInput(self, payload: bytes, positionCount: int):
+        """addInput of a page in the reference's wire format (the uncompressed payload of a SerializedPage,
+        main/execution/buffer/PagesSerdeUtil.java:45-62); decoded on the device."""
+        self._check(self._lib.pgpu_add_serialized_page(self._h, payload, len(payload), positionCount))
+
     def getOutput(self) -> Optional[Page]:
         n = max(self._lib.pgpu_output_channel_count(self._h), 1)
         cols = (N.Column * n)()

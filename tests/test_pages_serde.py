@@ -94,3 +94,103 @@ def test_non_null_values_only_are_written():
     data = S.write_block(b)
     assert len(data) == 4 + 10 + 4 + 1 + 1 + 4 + 2 * 8
     assert data[-16:] == np.array([1, 4], dtype="<i8").tobytes()
+
+
+# ---------------------------------------------------------------------------------------------------- GPU ingest
+def _drain(op):
+    from util import rows_of
+    out = []
+    while not op.isFinished():
+        p = op.getOutput()
+        if p is not None:
+            out.append(p)
+    return rows_of(out)
+
+
+def _run_both(plan, pages):
+    """the same pages through pgpu_add_page (blocks) and pgpu_add_serialized_page (wire format)"""
+    from presto_b200.operators import GpuPipelineOperator
+    results = []
+    for serialized in (False, True):
+        op = GpuPipelineOperator(plan, 0)
+        try:
+            for pg in pages:
+                if serialized:
+                    op.addSerializedInput(S.write_raw_page(pg.blocks), pg.position_count)
+                else:
+                    op.addInput(pg)
+            op.finish()
+            results.append(_drain(op))
+        finally:
+            op.close()
+    return results
+
+
+@pytest.mark.gpu
+def test_serialized_q1_pages_match_block_pages():
+    from util import assert_rows_equal_ignore_order, run_oracle, sequential_bound
+    total = 300_000
+    pages = [tpch.q1_page(0, 100_000, total), tpch.q1_page(100_000, 200_000, total)]
+    blocks, wire = _run_both(tpch.q1_plan(), pages)
+    assert_rows_equal_ignore_order(wire, blocks, nkeys=2, rtol=1e-12)
+    assert_rows_equal_ignore_order(wire, run_oracle(tpch.q1_plan(), pages), nkeys=2, rtol=sequential_bound(total))
+
+
+@pytest.mark.gpu
+def test_serialized_dictionary_and_rle_pages():
+    from util import assert_rows_equal_ignore_order
+    total = 200_000
+    pages = [tpch.q1_page_encoded(0, total, total)]   # DictionaryBlocks + a RunLengthEncodedBlock
+    blocks, wire = _run_both(tpch.q1_plan(), pages)
+    assert_rows_equal_ignore_order(wire, blocks, nkeys=2, rtol=1e-12)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 7, 8, 9, 1023, 1024, 1025, 70_001])
+def test_serialized_pages_with_nulls(n):
+    """null bit streams and non-null-only value arrays are re-expanded on the device: GROUP BY a nullable VARCHAR key,
+    aggregates over nullable BIGINT / DOUBLE / INTEGER / long DECIMAL channels"""
+    from presto_b200.operators import Aggregation, plan_text
+    from util import assert_rows_equal_ignore_order, run_oracle
+    rng = np.random.default_rng(n)
+    nulls = lambda frac: (rng.random(n) < frac).astype(np.uint8)  # noqa: E731
+    words = ["a", "bc", "def", ""]
+    knull = nulls(0.2)
+    dec = createDecimalType(30, 2)
+    key = VariableWidthBlock.from_values(createVarcharType(4), [None if knull[i] else words[int(x)] for i, x in enumerate(rng.integers(0, 4, n))])
+    page = Page(key,
+                LongArrayBlock(BIGINT, rng.integers(-10**6, 10**6, n), nulls(0.3)),
+                LongArrayBlock(DOUBLE, rng.integers(0, 1000, n).astype(np.float64), nulls(0.5)),
+                IntArrayBlock(INTEGER, rng.integers(-1000, 1000, n), nulls(0.9)),
+                Int128ArrayBlock(dec, [int(x) for x in rng.integers(-10**9, 10**9, n)], nulls(0.1)),
+                ByteArrayBlock(BOOLEAN, rng.integers(0, 2, n), nulls(0.4)))
+    types = [createVarcharType(4), BIGINT, DOUBLE, INTEGER, dec, BOOLEAN]
+    plan = plan_text(types, step="single", groupByChannels=[0], aggregations=[
+        Aggregation("sum", BIGINT, 1, BIGINT), Aggregation("count", BIGINT, 1, BIGINT), Aggregation("sum", DOUBLE, 2, DOUBLE),
+        Aggregation("max", INTEGER, 3, INTEGER), Aggregation("sum", dec, 4, createDecimalType(38, 2)), Aggregation("count", BIGINT, 5, BIGINT),
+        Aggregation("count", BIGINT, None, None)], expectedGroups=16)
+    blocks, wire = _run_both(plan, [page])
+    assert_rows_equal_ignore_order(wire, blocks, nkeys=1)
+    assert_rows_equal_ignore_order(wire, run_oracle(plan, [page]), nkeys=1)
+
+
+@pytest.mark.gpu
+def test_serialized_page_errors():
+    from presto_b200.operators import GpuPipelineOperator, TrinoException
+    op = GpuPipelineOperator(tpch.q6_plan(), 0)
+    try:
+        page = tpch.q6_page(0, 1000, 1000)
+        good = S.write_raw_page(page.blocks)
+        with pytest.raises(TrinoException):
+            op.addSerializedInput(good[:-5], 1000)              # truncated
+        with pytest.raises(TrinoException):
+            op.addSerializedInput(good, 999)                    # position count differs
+        with pytest.raises(TrinoException):
+            op.addSerializedInput(S.write_raw_page(page.blocks[:-1]), 1000)   # channel count differs
+        with pytest.raises(TrinoException):
+            op.addSerializedInput(S.write_raw_page(list(page.blocks[1:]) + [page.blocks[0]]), 1000)  # encodings do not match the types
+        op.addSerializedInput(good, 1000)                       # the operator is still usable
+        op.finish()
+        assert len(_drain(op)) == 1
+    finally:
+        op.close()
