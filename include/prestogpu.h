@@ -233,6 +233,23 @@ pgpu_status pgpu_gen_lineitem_device(int32_t device, int32_t column, uint64_t se
                                      int64_t total_rows, void* dev_out);
 pgpu_status pgpu_gen_lineitem_host(int32_t column, uint64_t seed, int64_t first_row, int64_t rows,
                                    int64_t total_rows, void* host_out);
+
+/* TPC-H lineitem rows exactly as the reference's tpch connector produces them (plugin/trino-tpch/.../TpchRecordSet.java:51-60
+ * calling the un-vendored io.trino.tpch:tpch:1.1 generator = the TPC's dbgen): same rows, same order, at any scale factor.
+ * Rows are addressed by ORDER: orders [first_order, first_order + n_orders) of pgpu_tpch_order_count(sf) = 1 500 000 x sf, each
+ * with 1..7 lineitems; pgpu_tpch_lineitem_rows gives the row count of a range (size the buffers with it). Columns are the
+ * PGPU_LI_* ids above (not IOTA_OFFSETS / ORDERKEY_SHUFFLED). Format NATIVE = the connector's types (TpchMetadata.java:587-600:
+ * DOUBLE quantity / extendedprice / discount / tax, int32 epoch days, one byte per flag); DECIMAL_12_2 = unscaled int64 of the
+ * DECIMAL(12,2) columns the reference's hive_tpch golden answers (q01.result, q06.result) were computed on.
+ * The generator is pinned by those answers and by the reference's table statistics (tests/test_tpch_golden.py). */
+#define PGPU_TPCH_NATIVE 0
+#define PGPU_TPCH_DECIMAL_12_2 1
+int64_t pgpu_tpch_order_count(double sf);
+pgpu_status pgpu_tpch_lineitem_rows(double sf, int64_t first_order, int64_t n_orders, int64_t* rows);
+pgpu_status pgpu_tpch_lineitem_device(int32_t device, double sf, int64_t first_order, int64_t n_orders, int32_t column, int32_t format,
+                                      int64_t capacity_rows, void* dev_out, int64_t* rows);
+pgpu_status pgpu_tpch_lineitem_host(double sf, int64_t first_order, int64_t n_orders, int32_t column, int32_t format,
+                                    int64_t capacity_rows, void* host_out, int64_t* rows);
 /* Write `bytes` of device memory (L2 flush between timed iterations). */
 pgpu_status pgpu_flush_l2(int32_t device, void* dev_scratch, size_t bytes);
 

@@ -16,7 +16,7 @@ from . import _native as N
 from .operators import Aggregation, plan_text
 from .relational import and_, call, compare, constant, field
 from .spi import (BIGINT, DATE, DOUBLE, DictionaryBlock, IntArrayBlock, LongArrayBlock, Page, RunLengthEncodedBlock,
-                  VariableWidthBlock, block_of, createVarcharType)
+                  VariableWidthBlock, block_of, createDecimalType, createVarcharType)
 
 VARCHAR1 = createVarcharType(1)
 SEED = 0x5EED0006
@@ -111,6 +111,94 @@ def q1_page_encoded(first_row: int, rows: int, total_rows: int, seed: int = SEED
 def highcard_page(first_row: int, rows: int, total_rows: int, shuffled: bool = False, seed: int = SEED) -> Page:
     c = lambda n: host_column(n, first_row, rows, total_rows, seed)
     return Page(LongArrayBlock(BIGINT, c("orderkey_shuffled" if shuffled else "orderkey")), LongArrayBlock(DOUBLE, c("quantity")))
+
+
+# ------------------------------------------------------------------------------------------------ real TPC-H rows
+# The rows the reference's tpch connector produces (csrc/tpch_dbgen.cuh), addressed by order. NATIVE = the connector's
+# DOUBLE columns; DECIMAL = the DECIMAL(12,2) schema of the reference's hive_tpch golden answers (q01.result, q06.result).
+DEC12_2 = createDecimalType(12, 2)
+TPCH_NATIVE, TPCH_DECIMAL_12_2 = 0, 1
+_TPCH_NUMERIC = ("quantity", "extendedprice", "discount", "tax")
+
+
+def tpch_order_count(sf: float) -> int:
+    return int(N.lib().pgpu_tpch_order_count(float(sf)))
+
+
+def tpch_rows(sf: float, first_order: int = 0, n_orders: int | None = None) -> int:
+    n_orders = tpch_order_count(sf) - first_order if n_orders is None else n_orders
+    r = ctypes.c_int64()
+    if N.lib().pgpu_tpch_lineitem_rows(float(sf), first_order, n_orders, ctypes.byref(r)):
+        raise ValueError("order range [%d, %d) is outside scale factor %s" % (first_order, first_order + n_orders, sf))
+    return r.value
+
+
+def _tpch_dtype(name: str, decimal: bool):
+    return np.int64 if decimal and name in _TPCH_NUMERIC else _DT[name]
+
+
+def tpch_host_column(name: str, sf: float, first_order: int, n_orders: int, decimal: bool = False, rows: int | None = None) -> np.ndarray:
+    rows = tpch_rows(sf, first_order, n_orders) if rows is None else rows
+    if name == "iota_offsets":
+        return np.arange(rows + 1, dtype=np.int32)
+    out = np.empty(rows, dtype=_tpch_dtype(name, decimal))
+    fmt = TPCH_DECIMAL_12_2 if decimal and name in _TPCH_NUMERIC else TPCH_NATIVE
+    st = N.lib().pgpu_tpch_lineitem_host(float(sf), first_order, n_orders, N.LI[name], fmt, rows, out.ctypes.data, None)
+    assert st == 0, st
+    return out
+
+
+def tpch_q1_page(sf: float, first_order: int, n_orders: int, decimal: bool = False) -> Page:
+    rows = tpch_rows(sf, first_order, n_orders)
+    c = lambda n: tpch_host_column(n, sf, first_order, n_orders, decimal, rows)
+    t = DEC12_2 if decimal else DOUBLE
+    off = c("iota_offsets")
+    return Page(VariableWidthBlock(VARCHAR1, c("returnflag"), off), VariableWidthBlock(VARCHAR1, c("linestatus"), off),
+                LongArrayBlock(t, c("quantity")), LongArrayBlock(t, c("extendedprice")), LongArrayBlock(t, c("discount")),
+                LongArrayBlock(t, c("tax")), IntArrayBlock(DATE, c("shipdate")))
+
+
+def tpch_q6_page(sf: float, first_order: int, n_orders: int, decimal: bool = False) -> Page:
+    rows = tpch_rows(sf, first_order, n_orders)
+    c = lambda n: tpch_host_column(n, sf, first_order, n_orders, decimal, rows)
+    t = DEC12_2 if decimal else DOUBLE
+    return Page(LongArrayBlock(t, c("extendedprice")), LongArrayBlock(t, c("discount")), IntArrayBlock(DATE, c("shipdate")),
+                LongArrayBlock(t, c("quantity")))
+
+
+def tpch_highcard_page(sf: float, first_order: int, n_orders: int) -> Page:
+    rows = tpch_rows(sf, first_order, n_orders)
+    c = lambda n: tpch_host_column(n, sf, first_order, n_orders, False, rows)
+    return Page(LongArrayBlock(BIGINT, c("orderkey")), LongArrayBlock(DOUBLE, c("quantity")))
+
+
+def q1_decimal_plan(step: str = "single", expectedGroups: int = 10000) -> str:
+    """hive_tpch/q01.sql on DECIMAL(12,2) columns, typed as the reference's analyzer types it: the integer literal 1 is
+    coerced to decimal(10,0), so 1 - l_discount and 1 + l_tax are decimal(13,2), the products decimal(25,4) and
+    decimal(38,6) (main/type/DecimalOperators.java:84-85,261-262); sum -> decimal(38,s), avg -> the input type."""
+    d10, d13, d25, d38_6 = createDecimalType(10, 0), createDecimalType(13, 2), createDecimalType(25, 4), createDecimalType(38, 6)
+    one = constant(1, d10)
+    disc_price = call("multiply", d25, field(3, DEC12_2), call("subtract", d13, one, field(4, DEC12_2)))
+    charge = call("multiply", d38_6, disc_price, call("add", d13, one, field(5, DEC12_2)))
+    f = compare("le", field(6, DATE), constant(10471, DATE))
+    proj = [field(0, VARCHAR1), field(1, VARCHAR1), field(2, DEC12_2), field(3, DEC12_2), disc_price, charge, field(4, DEC12_2)]
+    s2, s4 = createDecimalType(38, 2), createDecimalType(38, 4)
+    aggs = [Aggregation("sum", s2, 2, DEC12_2), Aggregation("sum", s2, 3, DEC12_2), Aggregation("sum", s4, 4, d25),
+            Aggregation("sum", d38_6, 5, d38_6), Aggregation("avg", DEC12_2, 2, DEC12_2), Aggregation("avg", DEC12_2, 3, DEC12_2),
+            Aggregation("avg", DEC12_2, 6, DEC12_2), Aggregation("count", BIGINT)]
+    inputs = [VARCHAR1, VARCHAR1, DEC12_2, DEC12_2, DEC12_2, DEC12_2, DATE]
+    return plan_text(inputs, f, proj, step=step, groupByChannels=[0, 1], aggregations=aggs, expectedGroups=expectedGroups)
+
+
+def q6_decimal_plan(step: str = "single") -> str:
+    """hive_tpch/q06.sql on DECIMAL(12,2) columns; literals as the optimizer leaves them after folding and coercion to the
+    column type (0.05, 0.07, 24 as decimal(12,2)); extendedprice * discount is decimal(24,4), its sum decimal(38,4)."""
+    d24 = createDecimalType(24, 4)
+    f = and_(compare("ge", field(2, DATE), constant(8766, DATE)), compare("lt", field(2, DATE), constant(9131, DATE)),
+             compare("ge", field(1, DEC12_2), constant(5, DEC12_2)), compare("le", field(1, DEC12_2), constant(7, DEC12_2)),
+             compare("lt", field(3, DEC12_2), constant(2400, DEC12_2)))
+    proj = [call("multiply", d24, field(0, DEC12_2), field(1, DEC12_2))]
+    return plan_text([DEC12_2, DEC12_2, DATE, DEC12_2], f, proj, step=step, aggregations=[Aggregation("sum", createDecimalType(38, 4), 0, d24)])
 
 
 # -------------------------------------------------------------------------------------------- device-resident pages

@@ -167,8 +167,8 @@ def test_serialized_pages_with_nulls(n):
     types = [createVarcharType(4), BIGINT, DOUBLE, INTEGER, dec, BOOLEAN]
     plan = plan_text(types, step="single", groupByChannels=[0], aggregations=[
         Aggregation("sum", BIGINT, 1, BIGINT), Aggregation("count", BIGINT, 1, BIGINT), Aggregation("sum", DOUBLE, 2, DOUBLE),
-        Aggregation("max", INTEGER, 3, INTEGER), Aggregation("sum", dec, 4, createDecimalType(38, 2)), Aggregation("count", BIGINT, 5, BIGINT),
-        Aggregation("count", BIGINT, None, None)], expectedGroups=16)
+        Aggregation("max", INTEGER, 3, INTEGER), Aggregation("sum", createDecimalType(38, 2), 4, dec), Aggregation("count", BIGINT, 5, BOOLEAN),
+        Aggregation("count", BIGINT)], expectedGroups=16)
     blocks, wire = _run_both(plan, [page])
     assert_rows_equal_ignore_order(wire, blocks, nkeys=1)
     assert_rows_equal_ignore_order(wire, run_oracle(plan, [page]), nkeys=1)
