@@ -33,6 +33,10 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="q1", choices=["q1", "q6", "highcard", "highcard_shuffled", "q1dict"])
     ap.add_argument("--rows", type=int, default=SF100_ROWS, help="lineitem rows per GPU")
+    ap.add_argument("--data", default="synthetic", choices=["synthetic", "dbgen"],
+                    help="synthetic: counter-based columns with the TPC-H value distributions (--rows per GPU); dbgen: the tpch connector's real rows "
+                         "(spec-conformant generator, --sf per GPU; rows per GPU follow from the order range)")
+    ap.add_argument("--sf", type=float, default=100.0, help="--data dbgen: TPC-H scale factor per GPU")
     ap.add_argument("--e2e-rows", type=int, default=0, help="rows of the end-to-end (host pages) leg; 0 = same as --rows if RAM allows")
     ap.add_argument("--cpu-rows-per-core", type=int, default=4_000_000)
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
@@ -42,7 +46,23 @@ def parse_args():
     return ap.parse_args()
 
 
-def workload_def(name, rows):
+def workload_def(name, rows, dbgen_sf=None):
+    wl = _workload_def(name, rows)
+    if dbgen_sf is not None:
+        from presto_b200 import tpch
+        if name == "highcard_shuffled":
+            raise SystemExit("--data dbgen has no shuffled-key variant")
+        if name == "q1dict":
+            raise SystemExit("--data dbgen host pages are plain blocks: use --workload q1 (the device leg of q1dict is available through DevicePage)")
+        make = {"q1": tpch.tpch_q1_page, "q6": tpch.tpch_q6_page, "highcard": tpch.tpch_highcard_page}[name]
+        # CPU legs address pages by row range: map it onto the order range of the same position (4.0008 rows per order)
+        norders = tpch.tpch_order_count(dbgen_sf)
+        wl["page"] = lambda first_row, n, total: make(dbgen_sf, (first_row // 4) % max(norders - max(n // 4, 1), 1), max(n // 4, 1))
+        wl["label"] = wl["label"].replace("synthetic lineitem", "the tpch connector's lineitem rows (dbgen)")
+    return wl
+
+
+def _workload_def(name, rows):
     from presto_b200 import tpch
     from presto_b200.spi import DOUBLE, LongArrayBlock, VariableWidthBlock
     import numpy as np
@@ -144,6 +164,7 @@ def cpu_run(wl, rows_per_core, cores, repeats=1):
             pages.append(wl["page"](r0, n, total))
             r0 += n
         shards.append(pages)
+    total = sum(p.position_count for pages in shards for p in pages)
     partial_plan = wl["plan"]("partial")
     best = None
     result = None
@@ -278,7 +299,8 @@ def run_device_steps(args, wl, device, dist):
     world, rank = dist["world"], dist["rank"]
     first = rank * rows
     total = rows * world
-    dp = tpch.DevicePage(device, wl["spec"], rows, first_row=first, total_rows=total)
+    dp = tpch.DevicePage(device, wl["spec"], rows, first_row=first, total_rows=total, dbgen=getattr(args, "dbgen", None))
+    assert dp.rows == rows
     single = world == 1
     op = GpuPipelineOperator(wl["plan"]("single" if single else "partial"), device)
     final = None if single else GpuPipelineOperator(final_plan_for(wl, None), device)
@@ -466,7 +488,18 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    wl = workload_def(args.workload, args.rows)
+    if args.data == "dbgen":
+        from presto_b200 import tpch
+        per_gpu = int(1_500_000 * args.sf)
+        total_sf = args.sf * world
+        first_order = rank * per_gpu
+        n_orders = min(per_gpu, tpch.tpch_order_count(total_sf) - first_order)
+        if args.impl == "ours":
+            args.dbgen = (total_sf, first_order, n_orders)
+            args.rows = tpch.tpch_rows(*args.dbgen)
+    wl = workload_def(args.workload, args.rows, args.sf * world if args.data == "dbgen" else None)
+    wl["dbgen_sf"] = args.sf * world if args.data == "dbgen" else None
+    data = "synthetic" if args.data == "synthetic" else "synthetic: TPC-H dbgen rows (the tpch connector's generator, restated; sf %g per GPU)%s" % (args.sf, ", generated on the device" if args.impl == "ours" else "")
     wl["name"] = args.workload
     wl["rows"] = args.rows if args.impl == "ours" else args.cpu_rows_per_core
     cores = os.cpu_count() or 1
@@ -491,7 +524,7 @@ def main():
         sample = "%d rows (%d per core x %d cores) of the same synthetic lineitem per step, 1 M-row pages, partial per thread + final merge" % (per_core * cores, per_core, cores)
         line = {"impl": "reference", "metric": metric, "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1000.0 * per_core * cores / value, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "vs_baseline": None, "dtype": "f64", "data": data, "config": config,
                 "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port", "sample": sample},
                 "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "note": "reference Java benchmarks (HandTpchQuery1/6) cannot run: no JVM in this image; this is the C++ oracle port"}
@@ -512,7 +545,12 @@ def main():
         t = torch.tensor([ms_per_step], device="cuda", dtype=torch.float64)
         td.all_reduce(t, op=td.ReduceOp.MAX)
         ms_per_step = float(t.item())
-    value = args.rows * world / (ms_per_step / 1000.0)
+    total_rows = args.rows * world
+    if world > 1 and args.data == "dbgen":        # order-range shards differ by a few rows
+        t = torch.tensor([args.rows], device="cuda", dtype=torch.int64)
+        td.all_reduce(t)
+        total_rows = int(t.item())
+    value = total_rows / (ms_per_step / 1000.0)
     peak, peak_src = measured_peak()
     kern_rows = args.rows * info["kern_steps"]
     achieved = kern_rows * wl["bytes_per_row"] / (info["kern_ms"] / 1000.0) / 1e9
@@ -543,7 +581,7 @@ def main():
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-                "data": "synthetic", "config": config, "gb_per_s": value * wl["bytes_per_row"] / 1e9,
+                "data": data, "config": config, "gb_per_s": value * wl["bytes_per_row"] / 1e9,
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": info["launches"], "clocks": info["clocks"],
                 "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"],
                 "exchange": None if world == 1 else {"shape": ("gather: every rank's FINAL kernel reads all partial pages over NVLink (CUDA IPC peer memory, shared-memory mailbox)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if args.workload in ("q1", "q1dict", "q6") else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),

@@ -126,6 +126,12 @@ pgpu_status pgpu_add_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
  * to the device in ONE copy and is decoded there (null bit stream -> flags, non-null-only values -> positions). Compressed or
  * encrypted pages (PageCodecMarker) must be decoded by the caller first. `data` may be reused when the call returns. */
 pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size_t len, int64_t position_count);
+/* Operator.getOutput() in the same wire format: *data / *len = the payload PagesSerdeUtil.writeRawPage would write for the
+ * output page (library-owned pinned memory, valid until the next call on this pipeline), *rows = its position count, or
+ * -1 when there is no output now. Null flags are bit-packed, nullable fixed-width blocks carry only their non-null values,
+ * var-width blocks their end offsets and bytes; all of it is packed on the device. A PARTIAL step's payload is what the
+ * reference's exchange would carry to the FINAL step (feed it to pgpu_add_serialized_page of a FINAL pipeline). */
+pgpu_status pgpu_get_serialized_output(pgpu_pipeline* p, const uint8_t** data, size_t* len, int64_t* rows);
 /* Same, with device-resident blocks (no copy). Buffers must stay valid until pgpu_sync(). */
 pgpu_status pgpu_add_device_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows);
 /* Operator.finish(): no more input; may be called repeatedly (main/operator/Driver.java:368-372). */

@@ -150,6 +150,9 @@ struct pgpu_pipeline {
     int64_t outCapacityRows = 0;
     // serialized-page ingest: the payload + the decoded, aligned block arrays of the page being added
     DeviceBuf serdeArena;
+    DeviceBuf serdeOutArena;            // getOutput in the wire format: packed pieces of every channel
+    HostOut serdeHost, serdeTotals;     // the payload (pinned) and the per-channel counts the layout depends on
+    size_t serdeLen = 0;
     // partitioned output (exchange)
     // one allocation for every partitioned column (a peer maps it with a single IPC handle); arenas replaced by a
     // larger one stay allocated until destroy because a peer may still have them mapped
@@ -999,6 +1002,9 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
         if (p->outArena.ptr) cudaFree(p->outArena.ptr);
         if (p->outHostArena.ptr) cudaFreeHost(p->outHostArena.ptr);
         if (p->serdeArena.ptr) cudaFree(p->serdeArena.ptr);
+        if (p->serdeOutArena.ptr) cudaFree(p->serdeOutArena.ptr);
+        if (p->serdeHost.ptr) cudaFreeHost(p->serdeHost.ptr);
+        if (p->serdeTotals.ptr) cudaFreeHost(p->serdeTotals.ptr);
         if (p->partArena.ptr) cudaFree(p->partArena.ptr);
         for (void* q : p->partRetired) cudaFree(q);
         for (auto* b : {&p->partPid, &p->partDst, &p->partCounts})
@@ -1253,7 +1259,12 @@ pgpu_status pgpu_finish(pgpu_pipeline* p) {
 
 int32_t pgpu_is_finished(const pgpu_pipeline* p) { return p && p->finished ? 1 : 0; }
 
-static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows, bool toHost) {
+enum class OutputTo { HOST, DEVICE, WIRE };
+
+static pgpu_status serializeOutput(pgpu_pipeline* p, int64_t r0, int64_t n);
+
+static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows, OutputTo to) {
+    const bool toHost = to == OutputTo::HOST;
     if (!p || !ncols || !rows) return PGPU_INVALID_ARGUMENT;
     *rows = -1;
     *ncols = 0;
@@ -1284,7 +1295,7 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
             if (st) return st;
         }
     }
-    if (max_cols < g.NO || !out_cols) return fail(p, PGPU_INVALID_ARGUMENT, "out_cols too small: need " + std::to_string(g.NO));
+    if (to != OutputTo::WIRE && (max_cols < g.NO || !out_cols)) return fail(p, PGPU_INVALID_ARGUMENT, "out_cols too small: need " + std::to_string(g.NO));
     int64_t remaining = p->outRowsTotal - p->outRowsServed;
     int64_t n = remaining;
     if (plan.maxOutputRows > 0) n = std::min<int64_t>(n, plan.maxOutputRows);
@@ -1304,7 +1315,11 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
         CU(cudaMemcpyAsync(p->outHostArena.ptr, p->outArena.ptr, p->outLayoutBytes, cudaMemcpyDeviceToHost, p->stream));
         p->stats.d2h_bytes += (int64_t)p->outLayoutBytes;
     }
-    for (int c = 0; c < g.NO; c++) {
+    if (to == OutputTo::WIRE) {
+        pgpu_status st = serializeOutput(p, r0, n);
+        if (st) return st;
+    }
+    for (int c = 0; c < g.NO && to != OutputTo::WIRE; c++) {
         const OutColDesc& d = g.out[c];
         pgpu_column& oc = out_cols[c];
         memset(&oc, 0, sizeof oc);
@@ -1377,11 +1392,149 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
 }
 
 pgpu_status pgpu_get_output(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows) {
-    return getOutputImpl(p, out_cols, max_cols, ncols, rows, true);
+    return getOutputImpl(p, out_cols, max_cols, ncols, rows, OutputTo::HOST);
 }
 
 pgpu_status pgpu_get_output_device(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows) {
-    return getOutputImpl(p, out_cols, max_cols, ncols, rows, false);
+    return getOutputImpl(p, out_cols, max_cols, ncols, rows, OutputTo::DEVICE);
+}
+
+// Rows [r0, r0 + n) of the output buffers -> the payload PagesSerdeUtil.writeRawPage would produce for the same blocks, in
+// p->serdeHost. The device does the packing (null bits, non-null-only values, end offsets + bytes of var-width cells) into
+// aligned scratch; every piece is then copied straight to its (unaligned) place in the pinned payload, next to the block
+// headers the host writes. Two synchronisations: one to learn the non-null counts / byte totals the layout depends on, one
+// at the end.
+static pgpu_status serializeOutput(pgpu_pipeline* p, int64_t r0, int64_t n) {
+    const GenResult& g = p->layout;
+    const int NO = g.NO;
+    struct Col {
+        const char* values;
+        const uint8_t* nulls;
+        size_t bits = 0, counts = 0, compact = 0, offsets = 0, byteCounts = 0;  // scratch offsets
+        uint32_t total = 0;                                     // non-null positions / data bytes
+    };
+    std::vector<Col> cols((size_t)NO);
+    const size_t nblocks = packScratchWords(n);
+    size_t need = 0;
+    auto reserve = [&](size_t bytes) {
+        size_t at = need;
+        need += align256(std::max<size_t>(bytes, 16));
+        return at;
+    };
+    for (int c = 0; c < NO; c++) {
+        const OutColDesc& d = g.out[c];
+        Col& k = cols[c];
+        k.values = (const char*)p->outDev[c].ptr + (size_t)r0 * d.stride;
+        k.nulls = (const uint8_t*)p->outDevNulls[c].ptr + r0;
+        k.bits = reserve((size_t)(n + 7) / 8);
+        k.counts = reserve(nblocks * 4);
+        k.compact = reserve((size_t)n * std::max(d.stride, 1));
+        if (d.varWidth) {
+            k.offsets = reserve((size_t)n * 4);
+            k.byteCounts = reserve(nblocks * 4);
+        } else if (d.stride != 1 && d.stride != 4 && d.stride != 8 && d.stride != 16)
+            return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: wire format of a " + std::to_string(d.stride) + "-byte fixed-width channel");
+    }
+    pgpu_status st = ensureDev(p, p->serdeOutArena, need);
+    if (st) return st;
+    st = ensureHost(p, p->serdeTotals, (size_t)NO * 2 * 4);
+    if (st) return st;
+    char* base = (char*)p->serdeOutArena.ptr;
+    uint32_t* totals = (uint32_t*)p->serdeTotals.ptr;  // [c]: non-null count, [NO + c]: var-width bytes
+    for (int c = 0; c < NO && n > 0; c++) {
+        const OutColDesc& d = g.out[c];
+        const Col& k = cols[c];
+        uint32_t* counts = (uint32_t*)(base + k.counts);
+        CU(packNullBits(p->stream, k.nulls, n, (uint8_t*)(base + k.bits), counts));
+        CU(cudaMemcpyAsync(&totals[c], counts + (nblocks - 1), 4, cudaMemcpyDeviceToHost, p->stream));
+        p->stats.kernel_launches += 2;
+        if (!d.varWidth) continue;
+        counts = (uint32_t*)(base + k.byteCounts);
+        CU(cellByteCounts(p->stream, (const uint8_t*)k.values, k.nulls, n, d.stride, d.lenPrefixed, counts));
+        CU(cudaMemcpyAsync(&totals[NO + c], counts + (nblocks - 1), 4, cudaMemcpyDeviceToHost, p->stream));
+        p->stats.kernel_launches += 2;
+    }
+    CU(cudaStreamSynchronize(p->stream));
+    // layout of the payload
+    auto encodingName = [](const OutColDesc& d) -> const char* {
+        if (d.varWidth) return "VARIABLE_WIDTH";
+        return d.stride == 8 ? "LONG_ARRAY" : d.stride == 4 ? "INT_ARRAY" : d.stride == 1 ? "BYTE_ARRAY" : "INT128_ARRAY";
+    };
+    size_t len = 4;
+    for (int c = 0; c < NO; c++) {
+        const OutColDesc& d = g.out[c];
+        const uint32_t nonNull = n > 0 ? totals[c] : 0;
+        const bool hasNulls = nonNull != (uint32_t)n;
+        len += 4 + strlen(encodingName(d)) + 4;
+        if (d.varWidth) len += (size_t)n * 4 + 1 + (hasNulls ? (size_t)(n + 7) / 8 : 0) + 4 + (n > 0 ? totals[NO + c] : 0);
+        else len += 1 + (hasNulls ? (size_t)(n + 7) / 8 + 4 : 0) + (size_t)nonNull * d.stride;
+    }
+    st = ensureHost(p, p->serdeHost, len);
+    if (st) return st;
+    uint8_t* out = (uint8_t*)p->serdeHost.ptr;
+    size_t pos = 0;
+    auto putInt = [&](int32_t v) {
+        memcpy(out + pos, &v, 4);
+        pos += 4;
+    };
+    auto d2h = [&](const void* src, size_t bytes) -> cudaError_t {
+        cudaError_t e = bytes ? cudaMemcpyAsync(out + pos, src, bytes, cudaMemcpyDeviceToHost, p->stream) : cudaSuccess;
+        pos += bytes;
+        p->stats.d2h_bytes += (int64_t)bytes;
+        return e;
+    };
+    putInt(NO);  // PagesSerdeUtil.writeRawPage: channel count, then the blocks
+    for (int c = 0; c < NO; c++) {
+        const OutColDesc& d = g.out[c];
+        const Col& k = cols[c];
+        const uint32_t nonNull = n > 0 ? totals[c] : 0;
+        const bool hasNulls = nonNull != (uint32_t)n;
+        const char* name = encodingName(d);
+        putInt((int32_t)strlen(name));
+        memcpy(out + pos, name, strlen(name));
+        pos += strlen(name);
+        putInt((int32_t)n);
+        if (d.varWidth) {  // spi/block/VariableWidthBlockEncoding.java:37-58: end offsets, nulls, total length, bytes
+            const uint32_t bytes = n > 0 ? totals[NO + c] : 0;
+            if (n > 0) {
+                CU(packCells(p->stream, (const uint8_t*)k.values, k.nulls, n, d.stride, d.lenPrefixed, (const uint32_t*)(base + k.byteCounts),
+                             (int32_t*)(base + k.offsets), (uint8_t*)(base + k.compact)));
+                p->stats.kernel_launches += 1;
+            }
+            CU(d2h(base + k.offsets, (size_t)n * 4));
+            out[pos++] = hasNulls ? 1 : 0;
+            if (hasNulls) CU(d2h(base + k.bits, (size_t)(n + 7) / 8));
+            putInt((int32_t)bytes);
+            CU(d2h(base + k.compact, bytes));
+        } else {  // spi/block/LongArrayBlockEncoding.java:39-60 and siblings: nulls, [non-null count], non-null values
+            out[pos++] = hasNulls ? 1 : 0;
+            if (!hasNulls) {
+                CU(d2h(k.values, (size_t)n * d.stride));
+                continue;
+            }
+            CU(d2h(base + k.bits, (size_t)(n + 7) / 8));
+            putInt((int32_t)nonNull);
+            CU(compactNonNull(p->stream, k.nulls, n, k.values, base + k.compact, d.stride, (const uint32_t*)(base + k.counts)));
+            p->stats.kernel_launches += 1;
+            CU(d2h(base + k.compact, (size_t)nonNull * d.stride));
+        }
+    }
+    if (pos != len) return fail(p, PGPU_CUDA_ERROR, "internal: wire layout mismatch");
+    CU(cudaStreamSynchronize(p->stream));
+    p->serdeLen = len;
+    return PGPU_OK;
+}
+
+pgpu_status pgpu_get_serialized_output(pgpu_pipeline* p, const uint8_t** data, size_t* len, int64_t* rows) {
+    if (!p || !data || !len || !rows) return PGPU_INVALID_ARGUMENT;
+    *data = nullptr;
+    *len = 0;
+    int32_t nc = 0;
+    pgpu_status st = getOutputImpl(p, nullptr, 0, &nc, rows, OutputTo::WIRE);
+    if (st || *rows < 0) return st;
+    *data = (const uint8_t*)p->serdeHost.ptr;
+    *len = p->serdeLen;
+    return PGPU_OK;
 }
 
 pgpu_status pgpu_sync(pgpu_pipeline* p) {

@@ -105,7 +105,136 @@ __global__ void __launch_bounds__(kThreads) k_unpack_bits(const uint8_t* bits, i
     for (int64_t p = (int64_t)blockIdx.x * kThreads + threadIdx.x; p < n; p += (int64_t)gridDim.x * kThreads) nulls[p] = isNullBit(bits, p) ? 1 : 0;
 }
 
+// ---- encode ------------------------------------------------------------------------------------------------------------
+constexpr int kPer = 8;  // positions per thread
+
+// block-wide exclusive prefix of `v` (256 threads); s_warp: 8 words
+__device__ inline uint32_t blockExclusive(uint32_t v, uint32_t* s_warp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(kFull, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0;
+    for (int w = 0; w < warp; w++) before += s_warp[w];
+    return before + incl - v;
+}
+
+__device__ inline void blockTotal(uint32_t v, uint32_t* out) {
+    __shared__ unsigned s_total;
+    if (threadIdx.x == 0) s_total = 0;
+    __syncthreads();
+    v = __reduce_add_sync(kFull, v);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_total, v);
+    __syncthreads();
+    if (threadIdx.x == 0) *out = s_total;
+}
+
+__global__ void __launch_bounds__(kThreads) k_pack_nulls(const uint8_t* nulls, int64_t n, uint8_t* bits, uint32_t* counts) {
+    const int64_t base = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * kPer;
+    unsigned byte = 0, live = 0;
+#pragma unroll
+    for (int i = 0; i < kPer; i++)
+        if (base + i < n) {
+            const bool isNull = nulls[base + i] != 0;
+            byte |= (isNull ? 1u : 0u) << (7 - i);
+            live += isNull ? 0u : 1u;
+        }
+    if (base < n) bits[base >> 3] = (uint8_t)byte;
+    blockTotal(live, counts + blockIdx.x);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_compact(const uint8_t* nulls, int64_t n, const T* values, T* compact, const uint32_t* blockBase) {
+    __shared__ uint32_t s_warp[kThreads / 32];
+    const int64_t base = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * kPer;
+    unsigned m = 0;
+#pragma unroll
+    for (int i = 0; i < kPer; i++)
+        if (base + i < n && nulls[base + i] == 0) m |= 1u << i;
+    uint64_t dst = (uint64_t)blockBase[blockIdx.x] + blockExclusive(__popc(m), s_warp);
+#pragma unroll
+    for (int i = 0; i < kPer; i++)
+        if ((m >> i) & 1) compact[dst++] = values[base + i];
+}
+
+__device__ inline uint32_t cellLength(const uint8_t* cells, const uint8_t* nulls, int64_t p, int stride, bool lenPrefixed) {
+    if (nulls[p]) return 0;
+    return lenPrefixed ? cells[(size_t)p * stride] : (uint32_t)stride;
+}
+
+__global__ void __launch_bounds__(kThreads) k_cell_bytes(const uint8_t* cells, const uint8_t* nulls, int64_t n, int stride, bool lenPrefixed, uint32_t* counts) {
+    const int64_t base = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * kPer;
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < kPer; i++)
+        if (base + i < n) sum += cellLength(cells, nulls, base + i, stride, lenPrefixed);
+    blockTotal(sum, counts + blockIdx.x);
+}
+
+__global__ void __launch_bounds__(kThreads) k_pack_cells(const uint8_t* cells, const uint8_t* nulls, int64_t n, int stride, bool lenPrefixed, const uint32_t* blockBase,
+                                                         int32_t* endOffsets, uint8_t* bytes) {
+    __shared__ uint32_t s_warp[kThreads / 32];
+    const int64_t base = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * kPer;
+    uint32_t len[kPer], sum = 0;
+#pragma unroll
+    for (int i = 0; i < kPer; i++) {
+        len[i] = base + i < n ? cellLength(cells, nulls, base + i, stride, lenPrefixed) : 0u;
+        sum += len[i];
+    }
+    uint32_t at = blockBase[blockIdx.x] + blockExclusive(sum, s_warp);
+#pragma unroll
+    for (int i = 0; i < kPer; i++) {
+        if (base + i >= n) break;
+        const uint8_t* src = cells + (size_t)(base + i) * stride + (lenPrefixed ? 1 : 0);
+        for (uint32_t k = 0; k < len[i]; k++) bytes[at + k] = src[k];
+        at += len[i];
+        endOffsets[base + i] = (int32_t)at;
+    }
+}
+
 }  // namespace
+
+cudaError_t packNullBits(cudaStream_t stream, const uint8_t* nulls, int64_t n, uint8_t* bits, uint32_t* counts) {
+    if (n <= 0) return cudaSuccess;
+    const int64_t nblocks = (n + kPackBlockPositions - 1) / kPackBlockPositions;
+    k_pack_nulls<<<(unsigned)nblocks, kThreads, 0, stream>>>(nulls, n, bits, counts);
+    k_scan_counts<<<1, 1024, 0, stream>>>(counts, nblocks);
+    return cudaGetLastError();
+}
+
+cudaError_t compactNonNull(cudaStream_t stream, const uint8_t* nulls, int64_t n, const void* values, void* compact, int width, const uint32_t* counts) {
+    if (n <= 0) return cudaSuccess;
+    const unsigned nblocks = (unsigned)((n + kPackBlockPositions - 1) / kPackBlockPositions);
+    switch (width) {
+        case 1: k_compact<uint8_t><<<nblocks, kThreads, 0, stream>>>(nulls, n, (const uint8_t*)values, (uint8_t*)compact, counts); break;
+        case 4: k_compact<uint32_t><<<nblocks, kThreads, 0, stream>>>(nulls, n, (const uint32_t*)values, (uint32_t*)compact, counts); break;
+        case 8: k_compact<uint64_t><<<nblocks, kThreads, 0, stream>>>(nulls, n, (const uint64_t*)values, (uint64_t*)compact, counts); break;
+        case 16: k_compact<uint4><<<nblocks, kThreads, 0, stream>>>(nulls, n, (const uint4*)values, (uint4*)compact, counts); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t cellByteCounts(cudaStream_t stream, const uint8_t* cells, const uint8_t* nulls, int64_t n, int stride, bool lenPrefixed, uint32_t* counts) {
+    if (n <= 0) return cudaSuccess;
+    const int64_t nblocks = (n + kPackBlockPositions - 1) / kPackBlockPositions;
+    k_cell_bytes<<<(unsigned)nblocks, kThreads, 0, stream>>>(cells, nulls, n, stride, lenPrefixed, counts);
+    k_scan_counts<<<1, 1024, 0, stream>>>(counts, nblocks);
+    return cudaGetLastError();
+}
+
+cudaError_t packCells(cudaStream_t stream, const uint8_t* cells, const uint8_t* nulls, int64_t n, int stride, bool lenPrefixed, const uint32_t* counts,
+                      int32_t* endOffsets, uint8_t* bytes) {
+    if (n <= 0) return cudaSuccess;
+    const unsigned nblocks = (unsigned)((n + kPackBlockPositions - 1) / kPackBlockPositions);
+    k_pack_cells<<<nblocks, kThreads, 0, stream>>>(cells, nulls, n, stride, lenPrefixed, counts, endOffsets, bytes);
+    return cudaGetLastError();
+}
 
 cudaError_t expandNulls(cudaStream_t stream, const uint8_t* bits, int64_t n, const void* compact, void* values, uint8_t* nulls, int width, uint32_t* scratch) {
     if (n <= 0) return cudaSuccess;

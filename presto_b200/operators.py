@@ -122,6 +122,14 @@ class GpuPipelineOperator:
         main/execution/buffer/PagesSerdeUtil.java:45-62); decoded on the device."""
         self._check(self._lib.pgpu_add_serialized_page(self._h, payload, len(payload), positionCount))
 
+    def getSerializedOutput(self):
+        """getOutput() in the reference's wire format: (payload bytes, positionCount) or None."""
+        data, n, rows = ctypes.c_void_p(), ctypes.c_size_t(), ctypes.c_int64()
+        self._check(self._lib.pgpu_get_serialized_output(self._h, ctypes.byref(data), ctypes.byref(n), ctypes.byref(rows)))
+        if rows.value < 0:
+            return None
+        return ctypes.string_at(data.value, n.value), rows.value
+
     def getOutput(self) -> Optional[Page]:
         n = max(self._lib.pgpu_output_channel_count(self._h), 1)
         cols = (N.Column * n)()

@@ -205,13 +205,18 @@ def q6_decimal_plan(step: str = "single") -> str:
 class DevicePage:
     """Columns generated directly in HBM (pgpu_gen_lineitem_device) as a pgpu_column array of device pointers."""
 
-    def __init__(self, device: int, spec, rows: int, first_row: int = 0, total_rows: int | None = None, seed: int = SEED):
+    def __init__(self, device: int, spec, rows: int | None = None, first_row: int = 0, total_rows: int | None = None, seed: int = SEED, dbgen=None):
         """spec: list of (type, encoding, column name(s)) per channel:
              (type, 'plain', name)                fixed-width column
              (VARCHAR1, 'varchar1', name)         byte column + shared iota offsets
-             (type, 'dict', id_name, dict_block)  dictionary ids on device, small dictionary uploaded"""
+             (type, 'dict', id_name, dict_block)  dictionary ids on device, small dictionary uploaded
+           dbgen = (scale factor, first order, orders): the connector's real TPC-H rows of that order range
+           (pgpu_tpch_lineitem_device; `rows` is then derived) instead of the synthetic columns; DECIMAL(12,2)-typed
+           channels get the unscaled int64 form."""
         L = N.lib()
         self.device = device
+        if dbgen is not None:
+            rows = tpch_rows(*dbgen)
         self.rows = rows
         self._allocs = []
         self._keep = []
@@ -220,15 +225,19 @@ class DevicePage:
         self.bytes = 0
         offsets_ptr = None
 
-        def gen(name, extra=0):
+        def gen(name, extra=0, fmt=TPCH_NATIVE):
             nbytes = (rows + extra) * np.dtype(_DT[name]).itemsize
             p = L.pgpu_device_alloc(device, max(nbytes, 16))
             if not p:
                 raise MemoryError("device allocation of %d bytes failed" % nbytes)
             self._allocs.append(p)
-            st = L.pgpu_gen_lineitem_device(device, N.LI[name], seed, first_row, rows, total, p)
+            if dbgen is not None and name != "iota_offsets":
+                sf, first_order, n_orders = dbgen
+                st = L.pgpu_tpch_lineitem_device(device, float(sf), first_order, n_orders, N.LI[name], fmt, rows, p, None)
+            else:
+                st = L.pgpu_gen_lineitem_device(device, N.LI[name], seed, first_row, rows, total, p)
             if st:
-                raise RuntimeError("pgpu_gen_lineitem_device failed: %d" % st)
+                raise RuntimeError("lineitem generation on the device failed: %d" % st)
             self.bytes += nbytes
             return p
 
@@ -239,7 +248,7 @@ class DevicePage:
             col.position_count = rows
             if enc == "plain":
                 col.encoding = N.ENC_PLAIN
-                col.values = gen(s[2])
+                col.values = gen(s[2], fmt=TPCH_DECIMAL_12_2 if t == DEC12_2 else TPCH_NATIVE)
             elif enc == "varchar1":
                 col.encoding = N.ENC_PLAIN
                 col.values = gen(s[2])
@@ -294,6 +303,11 @@ Q6_DEVICE_SPEC = [(DOUBLE, "plain", "extendedprice"), (DOUBLE, "plain", "discoun
 Q1_DEVICE_SPEC = [(VARCHAR1, "varchar1", "returnflag"), (VARCHAR1, "varchar1", "linestatus"), (DOUBLE, "plain", "quantity"),
                   (DOUBLE, "plain", "extendedprice"), (DOUBLE, "plain", "discount"), (DOUBLE, "plain", "tax"),
                   (DATE, "plain", "shipdate")]
+Q6_DECIMAL_DEVICE_SPEC = [(DEC12_2, "plain", "extendedprice"), (DEC12_2, "plain", "discount"), (DATE, "plain", "shipdate"),
+                          (DEC12_2, "plain", "quantity")]
+Q1_DECIMAL_DEVICE_SPEC = [(VARCHAR1, "varchar1", "returnflag"), (VARCHAR1, "varchar1", "linestatus"), (DEC12_2, "plain", "quantity"),
+                          (DEC12_2, "plain", "extendedprice"), (DEC12_2, "plain", "discount"), (DEC12_2, "plain", "tax"),
+                          (DATE, "plain", "shipdate")]
 HC_DEVICE_SPEC = [(BIGINT, "plain", "orderkey"), (DOUBLE, "plain", "quantity")]
 HC_SHUFFLED_DEVICE_SPEC = [(BIGINT, "plain", "orderkey_shuffled"), (DOUBLE, "plain", "quantity")]
 

@@ -194,3 +194,133 @@ def test_serialized_page_errors():
         assert len(_drain(op)) == 1
     finally:
         op.close()
+
+
+# ------------------------------------------------------------------------------------------- GPU output in wire format
+def _decoded_rows(blocks):
+    cols = [S.block_values(b) for b in blocks]
+    return list(zip(*cols)) if cols else []
+
+
+def _drain_serialized(op):
+    out = []
+    while not op.isFinished():
+        r = op.getSerializedOutput()
+        if r is not None:
+            payload, n = r
+            blocks = S.read_raw_page(payload)
+            assert all(b["positionCount"] == n for b in blocks)
+            out.append((payload, n, blocks))
+    return out
+
+
+def _nullable_page(n, seed):
+    rng = np.random.default_rng(seed)
+    nulls = lambda frac: (rng.random(n) < frac).astype(np.uint8)  # noqa: E731
+    words = ["a", "bc", "def", ""]
+    knull = nulls(0.2)
+    dec = createDecimalType(30, 2)
+    key = VariableWidthBlock.from_values(createVarcharType(4), [None if knull[i] else words[int(x)] for i, x in enumerate(rng.integers(0, 4, n))])
+    return Page(key,
+                LongArrayBlock(BIGINT, rng.integers(0, 50, n), nulls(0.1)),
+                LongArrayBlock(DOUBLE, rng.integers(0, 1000, n).astype(np.float64), nulls(0.5)),
+                IntArrayBlock(INTEGER, rng.integers(-1000, 1000, n), nulls(0.97)),
+                Int128ArrayBlock(dec, [int(x) for x in rng.integers(-10**9, 10**9, n)], nulls(0.1)),
+                ByteArrayBlock(BOOLEAN, rng.integers(0, 2, n), nulls(0.4)))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,max_rows", [(1, 0), (9, 0), (5000, 0), (5000, 37), (70_001, 2048)])
+@pytest.mark.parametrize("step", ["single", "partial"])
+def test_serialized_output_equals_block_output(n, max_rows, step):
+    """GROUP BY (nullable varchar, nullable bigint): var-width and fixed-width keys with nulls, nullable aggregate results of every
+    width (1 / 4 / 8 / 16 bytes), PARTIAL states (incl. the decimal VARBINARY state), several output pages"""
+    from presto_b200.operators import Aggregation, GpuPipelineOperator, plan_text
+    dec = createDecimalType(30, 2)
+    types = [createVarcharType(4), BIGINT, DOUBLE, INTEGER, dec, BOOLEAN]
+    plan = plan_text(types, step=step, groupByChannels=[0, 1], aggregations=[
+        Aggregation("sum", DOUBLE, 2, DOUBLE), Aggregation("max", INTEGER, 3, INTEGER), Aggregation("sum", createDecimalType(38, 2), 4, dec),
+        Aggregation("min", BOOLEAN, 5, BOOLEAN), Aggregation("avg", DOUBLE, 2, DOUBLE), Aggregation("count", BIGINT)], expectedGroups=1024, maxOutputRows=max_rows)
+    page = _nullable_page(n, n)
+    want, got = [], []
+    for wire in (False, True):
+        op = GpuPipelineOperator(plan, 0)
+        try:
+            op.addInput(page)
+            op.finish()
+            if wire:
+                pages = _drain_serialized(op)
+                if max_rows:   # at most 5 x 51 = 255 groups: (5000, 37) splits into several pages, (70_001, 2048) stays one
+                    total = sum(k for _, k, _ in pages)
+                    assert all(k <= max_rows for _, k, _ in pages) and len(pages) == -(-total // max_rows)
+                for _, _, blocks in pages:
+                    got += _decoded_rows(blocks)
+            else:
+                while not op.isFinished():
+                    p = op.getOutput()
+                    if p is not None:
+                        want += _decoded_rows(S.read_raw_page(S.write_raw_page(p.blocks)))   # same storage view of the block output
+        finally:
+            op.close()
+    assert len(got) == len(want) > 0
+    assert sorted(map(repr, got)) == sorted(map(repr, want))
+
+
+@pytest.mark.gpu
+def test_partial_output_travels_in_wire_format_to_final():
+    """PARTIAL on the GPU -> serialized pages -> FINAL on the GPU (pgpu_add_serialized_page) == SINGLE step"""
+    from presto_b200.operators import GpuPipelineOperator
+    from test_oracle_protocol import q1_final_plan
+    from util import assert_rows_equal_ignore_order
+    total = 400_000
+    pages = [tpch.q1_page(i * 100_000, 100_000, total) for i in range(4)]
+    final = GpuPipelineOperator(q1_final_plan(), 0)
+    try:
+        for half in (pages[:2], pages[2:]):           # two "workers"
+            partial = GpuPipelineOperator(tpch.q1_plan("partial"), 0)
+            try:
+                for pg in half:
+                    partial.addInput(pg)
+                partial.finish()
+                for payload, n, _ in _drain_serialized(partial):
+                    final.addSerializedInput(payload, n)
+            finally:
+                partial.close()
+        final.finish()
+        rows = _drain(final)
+    finally:
+        final.close()
+    single = GpuPipelineOperator(tpch.q1_plan(), 0)
+    try:
+        for pg in pages:
+            single.addInput(pg)
+        single.finish()
+        assert_rows_equal_ignore_order(rows, _drain(single), nkeys=2, rtol=1e-12)
+    finally:
+        single.close()
+
+
+@pytest.mark.gpu
+def test_serialized_output_of_filter_and_project():
+    """the filter + project-only mode (no aggregation): every input page yields one compacted output page"""
+    from presto_b200.operators import GpuPipelineOperator, plan_text
+    from presto_b200.relational import call, compare, constant, field
+    plan = plan_text([BIGINT, DOUBLE], compare("lt", field(0, BIGINT), constant(500, BIGINT)),
+                     [field(0, BIGINT), call("multiply", DOUBLE, field(1, DOUBLE), constant(2.0, DOUBLE))])
+    rng = np.random.default_rng(5)
+    n = 10_000
+    page = Page(LongArrayBlock(BIGINT, rng.integers(0, 1000, n), (rng.random(n) < 0.2).astype(np.uint8)),
+                LongArrayBlock(DOUBLE, rng.random(n), (rng.random(n) < 0.3).astype(np.uint8)))
+    outs = []
+    for wire in (False, True):
+        op = GpuPipelineOperator(plan, 0)
+        try:
+            op.addInput(page)
+            if wire:
+                payload, k = op.getSerializedOutput()
+                outs.append(_decoded_rows(S.read_raw_page(payload)))
+            else:
+                outs.append(_decoded_rows(S.read_raw_page(S.write_raw_page(op.getOutput().blocks))))
+        finally:
+            op.close()
+    assert outs[0] == outs[1] and 0 < len(outs[0]) < n      # order preserving compaction: same rows in the same order

@@ -18,7 +18,7 @@ import pytest
 import oracle_op
 from presto_b200 import _native as N
 from presto_b200 import tpch
-from util import assert_rows_equal_ignore_order, run_gpu, run_oracle
+from util import assert_rows_equal_ignore_order, exact_q1, run_gpu, run_oracle, sequential_bound
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 STATS = json.load(open(os.path.join(GOLDEN, "tpch_lineitem_stats.json")))
@@ -149,6 +149,71 @@ def test_gpu_q1_q6_sf1_double_schema():
     pages = sf1_pages(tpch.tpch_q1_page, False)
     rows = run_gpu(tpch.q1_plan(), pages)
     check_q1_double(rows)
-    assert_rows_equal_ignore_order(rows, run_oracle(tpch.q1_plan(), pages), nkeys=2, rtol=1e-12)
+    assert_rows_equal_ignore_order(rows, exact_q1(pages), nkeys=2, rtol=1e-12)                       # correctly rounded sums
+    assert_rows_equal_ignore_order(rows, run_oracle(tpch.q1_plan(), pages), nkeys=2, rtol=sequential_bound(6_001_215))  # the oracle adds in row order
     (got,), = run_gpu(tpch.q6_plan(), sf1_pages(tpch.tpch_q6_page, False))
     assert abs(got - 123141078.2283) <= 1e-9 * 123141078.2283
+
+
+# ------------------------------------------------------------------------------------------- device generator
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf,first,n", [(0.01, 0, 15000), (1.0, 1_234_567, 65_537), (100.0, 149_000_000, 300_001), (1000.0, 1_499_990_000, 4097)])
+def test_device_generator_equals_host_generator(sf, first, n):
+    L = N.lib()
+    rows = tpch.tpch_rows(sf, first, n)
+    dev = L.pgpu_device_alloc(0, rows * 8 + 64)
+    try:
+        cases = [(name, False) for name in ("orderkey", "quantity", "extendedprice", "discount", "tax", "shipdate", "returnflag", "linestatus",
+                                            "discount_id", "tax_id", "quantity_id", "returnflag_id", "linestatus_id")]
+        cases += [(name, True) for name in ("quantity", "extendedprice", "discount", "tax")]
+        for name, decimal in cases:
+            want = tpch.tpch_host_column(name, sf, first, n, decimal, rows)
+            got = np.empty_like(want)
+            r = ctypes.c_int64()
+            assert L.pgpu_tpch_lineitem_device(0, sf, first, n, N.LI[name], 1 if decimal else 0, rows, dev, ctypes.byref(r)) == 0
+            assert r.value == rows
+            assert L.pgpu_memcpy_d2h(0, got.ctypes.data, dev, got.nbytes) == 0
+            assert np.array_equal(got, want), (name, decimal)
+        r = ctypes.c_int64()
+        assert L.pgpu_tpch_lineitem_device(0, sf, first, n, N.LI["orderkey"], 0, rows - 1, dev, ctypes.byref(r)) == N.INVALID_ARGUMENT
+        assert r.value == rows
+    finally:
+        L.pgpu_device_free(0, dev)
+
+
+def run_device_page(plan, spec, dbgen):
+    from presto_b200.operators import GpuPipelineOperator
+    from util import rows_of
+    dp = tpch.DevicePage(0, spec, dbgen=dbgen)
+    op = GpuPipelineOperator(plan, 0)
+    try:
+        op.addDeviceInput(dp.cols, len(spec), dp.rows)
+        op.finish()
+        out = []
+        while not op.isFinished():
+            p = op.getOutput()
+            if p is not None:
+                out.append(p)
+        return rows_of(out)
+    finally:
+        op.close()
+        dp.free()
+
+
+@pytest.mark.gpu
+def test_gpu_device_resident_sf1_equals_golden_answers():
+    """the whole sf1 table generated in HBM and aggregated in one pass (the bench's --data dbgen path)"""
+    sf1 = (1.0, 0, tpch.tpch_order_count(1.0))
+    check_q1_decimal(run_device_page(tpch.q1_decimal_plan(), tpch.Q1_DECIMAL_DEVICE_SPEC, sf1))
+    assert run_device_page(tpch.q6_decimal_plan(), tpch.Q6_DECIMAL_DEVICE_SPEC, sf1) == golden_rows("hive_tpch_q06.result", (4,))
+    check_q1_double(run_device_page(tpch.q1_plan(), tpch.Q1_DEVICE_SPEC, sf1))       # the staged Q1 kernel on real rows
+    (got,), = run_device_page(tpch.q6_plan(), tpch.Q6_DEVICE_SPEC, sf1)
+    assert abs(got - 123141078.2283) <= 1e-9 * 123141078.2283
+    groups = run_device_page(tpch.highcard_plan(1_500_000), tpch.HC_DEVICE_SPEC, sf1)   # GROUP BY l_orderkey, sum(l_quantity)
+    assert len(groups) == 1_500_000
+    assert sum(g[1] for g in groups) == 37734107 + 991417 + 74476040 + 37719753 + sum_quantity_after_cutoff()
+
+
+def sum_quantity_after_cutoff():
+    c = oracle_lineitem(1.0)
+    return int(c["quantity"][c["shipdate"] > 10471].sum())
