@@ -23,6 +23,14 @@
 namespace pgpu {
 namespace {
 
+// defaults of the high-cardinality knobs (PGPU_TUNE_RUNS / PGPU_TUNE_LOCB override them: bench sweeps, A/B parity tests)
+constexpr int kDefaultRuns = 0;
+constexpr int kDefaultLocBits = 0;
+int envInt(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+
 [[noreturn]] void unsupported(const std::string& m) { throw PlanError(PGPU_NOT_SUPPORTED, "not supported on the GPU path: " + m); }
 
 struct Val {
@@ -1185,6 +1193,23 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         res.smemBytes = 8 * cap * NHA * 8 + cap * KW * 8 + cap * 12 + 16;
     }
 
+    // high cardinality (no directory): run compaction through warp-private shared memory when the staged rows of 8 warps fit
+    // in the 48 KB every kernel may use; placement keeps 2^locB neighbouring keys of an integer first key field in
+    // consecutive slots
+    const int runsBytes = 8 * ((KW + NHA) * 128 * 8 + 256);
+    const bool highCard = res.mode == KernelMode::AGG_HASH && !res.useDir && tagless;
+    const bool runs = highCard && runsBytes <= 48 * 1024 && envInt("PGPU_TUNE_RUNS", kDefaultRuns) != 0;
+    if (runs) res.smemBytes = runsBytes;
+    int locB = 0, locSh = 0;
+    if (highCard && !fields.empty() && fields[0].byteOffset < 7) {
+        const TypeKind k0 = fields[0].type.kind;
+        if (k0 == TypeKind::BIGINT || k0 == TypeKind::INTEGER || k0 == TypeKind::DATE || (k0 == TypeKind::DECIMAL && fields[0].type.isShortDecimal())) {
+            locB = std::min(std::max(envInt("PGPU_TUNE_LOCB", kDefaultLocBits), 0), 6);
+            locSh = 8 * fields[0].byteOffset;
+        }
+    }
+    res.locBits = locB;
+
     // staged variant: low-cardinality hash aggregation whose stage ring (>= 2 stages) fits beside the directory
     {
         const int kBudget = 220 * 1024;
@@ -1224,6 +1249,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     src << "    static constexpr int KWA = " << KWA << ", NWA = " << NWA << ", NH = " << NH << ", NHA = " << NHA << ";\n";
     src << "    static constexpr bool TAGLESS = " << (tagless ? "true" : "false") << ";\n";
     src << "    static constexpr bool LANE_MERGE = " << (getenv("PGPU_TUNE_NOLANEMERGE") ? "false" : "true") << ";\n";
+    src << "    static constexpr bool RUNS = " << (runs ? "true" : "false") << ";  // run compaction (HashCtx::consume_runs)\n";
     src << "    static constexpr int KOFF = " << (tagless ? 0 : 1) << ";  // first key word of a slot\n";
     src << "    static constexpr bool USE_DIR = " << (res.useDir ? "true" : "false") << ";\n";
     src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 8;\n";
@@ -1499,6 +1525,11 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";
     }
     res.source = src.str();
+    if (locB > 0) {
+        const std::string inc = "#include \"pgpu_device.cuh\"";
+        const size_t at = res.source.find(inc);
+        res.source.insert(at, "#define PGPU_LOCB " + std::to_string(locB) + "\n#define PGPU_LOCSH " + std::to_string(locSh) + "\n");
+    }
     return res;
 }
 

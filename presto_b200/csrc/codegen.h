@@ -34,6 +34,7 @@ struct GenResult {
     bool useDir = false;
     int dirCap = 0;
     int smemBytes = 0;         // dynamic shared memory of the page kernel
+    int locBits = 0;           // table placement keeps 2^locBits neighbouring keys in consecutive slots (PGPU_LOCB)
     // staged variant (pgpu_k_page_staged): bulk-async copies of column tiles into a shared-memory ring
     bool staged = false;
     int stagedThreads = 544;   // 2 x 8 consumer warps + 1 producer warp

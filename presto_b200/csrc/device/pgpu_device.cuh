@@ -340,12 +340,29 @@ PGPU_DEV u64 mix64(u64 x) {  // splitmix64 finaliser; table placement only, neve
     x ^= x >> 31;
     return x;
 }
+// Table placement. PGPU_LOCB > 0 (set by the plan compiler for high-cardinality plans) keeps the 2^LOCB keys that differ only
+// in the low bits of the first key field (bit PGPU_LOCSH of key word 0 upwards) in 2^LOCB CONSECUTIVE home slots: the
+// neighbourhood is hashed, the low bits index inside it. Clustered keys (l_orderkey runs of consecutive rows) then share
+// DRAM sectors and pages instead of taking one random sector each; uniformly random keys are placed as before.
+#ifndef PGPU_LOCB
+#define PGPU_LOCB 0
+#endif
+#ifndef PGPU_LOCSH
+#define PGPU_LOCSH 0
+#endif
 template <int KW>
 PGPU_DEV u64 hash_key(const u64 (&k)[KW > 0 ? KW : 1]) {
     u64 h = 0x9e3779b97f4a7c15ull;
+    constexpr u64 LOCM = (1ull << PGPU_LOCB) - 1ull;
 #pragma unroll
-    for (int i = 0; i < KW; i++) h = mix64(h ^ k[i]);
+    for (int i = 0; i < KW; i++) h = mix64(h ^ (i == 0 ? k[i] & ~(LOCM << PGPU_LOCSH) : k[i]));
+    if (PGPU_LOCB > 0) h = (h & ~LOCM) | (((k[0] >> PGPU_LOCSH) + (h >> 32)) & LOCM);  // rotated inside the neighbourhood block
     return h;
+}
+// home slot of a hash value
+PGPU_DEV u64 home_pos(u64 h, u64 capacity) {
+    if (PGPU_LOCB == 0) return __umul64hi(h, capacity);
+    return (__umul64hi(h, capacity >> PGPU_LOCB) << PGPU_LOCB) | (h & ((1ull << PGPU_LOCB) - 1ull));
 }
 
 // cell-word kinds
@@ -437,14 +454,14 @@ struct ProbePre {
 template <int KW, int SLOTW>
 PGPU_DEV ProbePre probe_prefetch(const TableArgs& t, u64 h) {
     ProbePre p;
-    const u64* s = t.slots + __umul64hi(h, t.capacity) * SLOTW;
+    const u64* s = t.slots + home_pos(h, t.capacity) * SLOTW;
     if (KW == 1) { p.c0 = ld_relaxed_u64(s); p.c1 = 0; }
     else ld_relaxed_u128(s, p.c0, p.c1);
     return p;
 }
 template <int KW, int SLOTW, bool TAGLESS>
 PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool allow, u32& nins, const ProbePre* pre = nullptr, u32 skip = 0) {
-    u64 pos = __umul64hi(h, t.capacity) + skip;  // skip: slots of the chain the caller has already examined
+    u64 pos = home_pos(h, t.capacity) + skip;  // skip: slots of the chain the caller has already examined
     if (pos >= t.capacity) pos -= t.capacity;
     if (TAGLESS) {
         const u64 k0 = KW == 1 ? (key[0] | KEY_MARK) : key[0];
@@ -691,9 +708,12 @@ struct HashCtx {
     u32 nins;      // table slots claimed since the last flush_inserts
     bool use_dir;  // warp-uniform
     u32 err;
+    u64* runsm;    // P::RUNS: warp-private staging of the warp's 128 rows, see consume_runs
 
     // shared-memory layout: wacc[nwarps][DCAP][NHA] u64 | dkeys[DCAP][KW] u64 | dtags | dids | dpos [DCAP] u32 | dcount u32
     static constexpr int dir_bytes(int nwarps) { return P::USE_DIR ? nwarps * DCAP * NHA * 8 + DCAP * KW * 8 + DCAP * 12 + 16 : 0; }
+    // P::RUNS: per warp [KW + NHA][128] u64 (one array per key / hot word) + 128 run starts (1 byte each) + pad
+    static constexpr int RUNS_WARP_BYTES = (KW + NHA) * 128 * 8 + 256;
 
     PGPU_DEV void init(unsigned char* smem, int nwarps, int warp) {
         wacc = reinterpret_cast<u64*>(smem);
@@ -703,6 +723,7 @@ struct HashCtx {
         dpos = dids + (P::USE_DIR ? DCAP : 0);
         dcount = dpos + (P::USE_DIR ? DCAP : 0);
         myacc = wacc + (size_t)warp * DCAP * NHA;
+        runsm = reinterpret_cast<u64*>(smem + (size_t)warp * RUNS_WARP_BYTES);  // P::RUNS implies !USE_DIR: the region starts at 0
         use_dir = P::USE_DIR;
         err = 0;
         rmask = 0;
@@ -909,7 +930,7 @@ struct HashCtx {
                             const bool empty = KW == 1 ? pre[r].c0 == 0ull : pre[r].c1 == 0ull;
                             st[r] = found ? 0 : empty ? 1 : 2;
                             if (st[r] == 1) {
-                                u64* s = t.slots + __umul64hi(h[r], t.capacity) * P::SLOTW;
+                                u64* s = t.slots + home_pos(h[r], t.capacity) * P::SLOTW;
                                 if (KW == 1) o0[r] = atomicCAS(s, 0ull, k0);
                                 else cas_u128(s, 0ull, 0ull, k0, k1, o0[r], o1[r]);
                             }
@@ -918,7 +939,7 @@ struct HashCtx {
 #pragma unroll
                     for (int r = 0; r < R; r++) {
                         if (sel[r]) {
-                            u64* s = t.slots + __umul64hi(h[r], t.capacity) * P::SLOTW;
+                            u64* s = t.slots + home_pos(h[r], t.capacity) * P::SLOTW;
                             if (st[r] == 1) {
                                 const u64 k0 = KW == 1 ? (key[r][0] | KEY_MARK) : key[r][0];
                                 const u64 k1 = KW == 2 ? (key[r][KW - 1] | KEY_MARK) : 0ull;
@@ -956,6 +977,140 @@ struct HashCtx {
             if (lane == 0) atomicAdd(t.counters, (u64)tot);
             nins = 0;
         }
+    }
+
+    // High cardinality with run compaction (P::RUNS; tagless slots, no directory). `consume` leaves the runs where the rows
+    // happen to lie: a lane holds 0..4 of them, so the unrolled probe code runs four times per lane for ~1 run, and runs that
+    // cross lanes need shuffle passes. Here the warp's 128 consecutive rows (lane l holds rows 4l..4l+3 of row `wbase`
+    // onwards) are staged in warp-private shared memory, run starts are found with four ballots, and run j of the warp is
+    // handed to lane j: the lane adds the run's rows up out of shared memory while its home-slot load is in flight and makes
+    // ONE table update. Two runs per lane are in flight when a warp holds more than 32 runs (unordered keys).
+    // Unselected rows form "dead" runs (start byte | 0x80) so that every row belongs to exactly one run.
+    struct Run {
+        int s, e;  // rows [s, e) of the warp tile
+        bool act;
+        u64 k[KW > 0 ? KW : 1];
+        u64 h;
+        ProbePre pre;
+    };
+    PGPU_DEV void run_issue(const TableArgs& t, const u8* starts, int nruns, int j, Run& a) {
+        a.act = j < nruns;
+        a.s = a.e = 0;
+        if (a.act) {
+            const u32 b = starts[j];
+            a.s = (int)(b & 127u);
+            a.e = j + 1 < nruns ? (int)(starts[j + 1] & 127u) : 128;
+            a.act = (b & 128u) == 0u;
+        }
+        if (a.act) {
+#pragma unroll
+            for (int w = 0; w < KW; w++) a.k[w] = runsm[w * 128 + a.s];
+            a.h = hash_key<KW>(a.k);
+            a.pre = probe_prefetch<KW, P::SLOTW>(t, a.h);
+        }
+    }
+    PGPU_DEV void run_resolve(const TableArgs& t, i64 wbase, bool allow, const Run& a) {
+        if (!a.act) return;
+        u64 v[NHA];
+#pragma unroll
+        for (int i = 0; i < NHA; i++) v[i] = runsm[(KW + i) * 128 + a.s];
+#pragma unroll 1
+        for (int row = a.s + 1; row < a.e; row++) {
+            u64 b[NHA];
+#pragma unroll
+            for (int i = 0; i < NHA; i++) b[i] = runsm[(KW + i) * 128 + row];
+            P::combine(v, b);
+        }
+        const u64 k0 = KW == 1 ? (a.k[0] | KEY_MARK) : a.k[0];
+        const u64 k1 = KW == 2 ? (a.k[KW - 1] | KEY_MARK) : 0ull;
+        const bool found = KW == 1 ? a.pre.c0 == k0 : (a.pre.c0 == k0 && a.pre.c1 == k1);
+        const bool empty = KW == 1 ? a.pre.c0 == 0ull : a.pre.c1 == 0ull;
+        u64* s = t.slots + home_pos(a.h, t.capacity) * P::SLOTW;
+        if (!found) {
+            if (!empty) {
+                s = table_upsert<KW, P::SLOTW, true>(t, a.k, a.h, allow, nins, nullptr, 1);  // walk the chain from home + 1
+            } else if (!allow) {
+                s = nullptr;  // not in the table and the table is at its load-factor limit: defer
+            } else {
+                u64 o0 = 0, o1 = 0;
+                if (KW == 1) o0 = atomicCAS(s, 0ull, k0);
+                else cas_u128(s, 0ull, 0ull, k0, k1, o0, o1);
+                const bool claimed = KW == 1 ? o0 == 0ull : o1 == 0ull;
+                const bool same = KW == 1 ? o0 == k0 : (o0 == k0 && o1 == k1);
+                if (claimed) nins++;
+                else if (!same) s = table_upsert<KW, P::SLOTW, true>(t, a.k, a.h, true, nins, nullptr, 1);
+            }
+        }
+        if (s) P::atomic_cells(s + P::KOFF + KW, v);
+        else defer_rows(t, wbase + a.s, a.e - a.s, err);
+    }
+    // Must be called by all 32 lanes; `base` = global row number of the lane's first row, lanes hold consecutive rows.
+    PGPU_DEV void consume_runs(const TableArgs& t, i64 base, bool (&sel)[4], u64 (&key)[4][KW], u64 (&cw)[4][NHA]) {
+        const int lane = threadIdx.x & 31;
+        const i64 wbase = base - 4 * lane;
+        u8* starts = reinterpret_cast<u8*>(runsm + (KW + NHA) * 128);
+        // 1. stage the rows: 4 consecutive 64-bit words per lane and array (two 128-bit stores)
+#pragma unroll
+        for (int w = 0; w < KW; w++) {
+            ulonglong2* d = reinterpret_cast<ulonglong2*>(runsm + w * 128 + 4 * lane);
+            d[0] = make_ulonglong2(key[0][w], key[1][w]);
+            d[1] = make_ulonglong2(key[2][w], key[3][w]);
+        }
+#pragma unroll
+        for (int i = 0; i < NHA; i++) {
+            ulonglong2* d = reinterpret_cast<ulonglong2*>(runsm + (KW + i) * 128 + 4 * lane);
+            d[0] = make_ulonglong2(cw[0][i], cw[1][i]);
+            d[1] = make_ulonglong2(cw[2][i], cw[3][i]);
+        }
+        // 2. run starts: a selected row whose predecessor is unselected or has another key starts a live run, the first
+        //    unselected row after a selected one a dead run; row 0 of the warp always starts one
+        bool psel = __shfl_up_sync(FULLMASK, (int)sel[3], 1) != 0;
+        bool peq = true;
+#pragma unroll
+        for (int w = 0; w < KW; w++) peq &= (shfl_u64(key[3][w], (lane + 31) & 31) == key[0][w]);
+        if (lane == 0) { psel = true; peq = false; }
+        bool st[4];
+        st[0] = sel[0] ? !(psel && peq) : psel;
+#pragma unroll
+        for (int r = 1; r < 4; r++) {
+            bool eq = true;
+#pragma unroll
+            for (int w = 0; w < KW; w++) eq &= (key[r][w] == key[r - 1][w]);
+            st[r] = sel[r] ? !(sel[r - 1] && eq) : sel[r - 1];
+        }
+        const u32 below = (1u << lane) - 1u;
+        int rank = 0, nruns = 0;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const u32 m = __ballot_sync(FULLMASK, st[r]);
+            rank += __popc(m & below);
+            nruns += __popc(m);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            if (st[r]) {
+                starts[rank] = (u8)((4 * lane + r) | (sel[r] ? 0 : 128));
+                rank++;
+            }
+        }
+        __syncwarp();
+        // 3. one run per lane (two in flight when the warp holds more than 32)
+        const bool allow = table_may_insert(t);
+#pragma unroll 1
+        for (int j0 = 0; j0 < nruns; j0 += 64) {
+            Run a, b;
+            run_issue(t, starts, nruns, j0 + lane, a);
+            const bool two = j0 + 32 < nruns;  // warp-uniform
+            if (two) run_issue(t, starts, nruns, j0 + 32 + lane, b);
+            run_resolve(t, wbase, allow, a);
+            if (two) run_resolve(t, wbase, allow, b);
+        }
+        if (__any_sync(FULLMASK, nins != 0)) {
+            const u32 tot = __reduce_add_sync(FULLMASK, nins);
+            if (lane == 0) atomicAdd(t.counters, (u64)tot);
+            nins = 0;
+        }
+        __syncwarp();  // the next tile overwrites the staging area
     }
 
     // End of kernel, whole block: fold register groups -> warp tables -> HBM table. `accwarps` = warps that own a wacc table
@@ -1016,7 +1171,8 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
         if (eager) P::eval_eager(a, base, a.rows, sel, key, cw, cx.err);
         else P::eval(a, base, a.rows, sel, key, cw, cx.err);
         eager = __popc(__ballot_sync(FULLMASK, sel[0] | sel[1] | sel[2] | sel[3])) >= P::EAGER_LANES;
-        cx.template consume<4>(t, base, sel, key, cw);
+        if (P::RUNS) cx.consume_runs(t, base, sel, key, cw);
+        else cx.template consume<4>(t, base, sel, key, cw);
     }
     cx.flush(t, P::NWARP);
     if (cx.err) atomicOr(sc.err, cx.err);
