@@ -346,9 +346,94 @@ struct ExprParser {
             checkValueType(e->type);
             return e;
         }
-        if (h == "switch" || h == "when" || h == "null-if" || h == "dereference" || h == "row-constructor" || h == "bind" || h == "lambda")
+        if (h == "null-if") {
+            // main/sql/gen/NullIfCodeGenerator.java:70-113: first NULL -> NULL without evaluating second; equal(first, second)
+            // true -> NULL; false or NULL -> first. Lowered to IF(IS_NULL(a), NULL, IF(EQ(a, b), NULL, a)); IF evaluates only the
+            // branch a row takes and treats a NULL condition as false, which is exactly that control flow. The casts to a common
+            // type the reference carries as function dependencies are explicit (call cast ...) nodes in this plan language.
+            if (x.kids.size() != 3) bad("(null-if a b)");
+            auto a = parse(x.kids[1]);
+            auto b = parse(x.kids[2]);
+            if (a->type != b->type) bad("null-if operand types differ (wrap one side in (call cast ...)): " + a->type.str() + " vs " + b->type.str());
+            const Type t = a->type;
+            checkValueType(t);
+            checkComparable(t, false);
+            auto inner = makeIf(t, makeEq(std::move(a), std::move(b)), makeNull(t), parse(x.kids[1]));
+            return makeIf(t, makeIsNull(parse(x.kids[1])), makeNull(t), std::move(inner));
+        }
+        if (h == "switch") {
+            // main/sql/gen/SwitchCodeGenerator.java:113-159: value evaluated once, NULL value -> else branch; otherwise the first
+            // WHEN whose equal(operand, value) is true (a NULL comparison counts as false) yields its result; no ELSE -> NULL.
+            // Lowered to IF(IS_NULL(v), else, IF(EQ(o1, v), r1, IF(EQ(o2, v), r2, ... else))). (Expressions are deterministic, so
+            // re-evaluating the value per comparison is unobservable.)
+            if (x.kids.size() < 4) bad("(switch <type> v (when o r)... [else])");
+            const Type t = parseType(x.kids[1]);
+            checkValueType(t);
+            size_t last = x.kids.size();  // one past the last WHEN clause
+            const Sx* elseSx = nullptr;
+            if (x.kids.back().atom || x.kids.back().head() != "when") {
+                elseSx = &x.kids.back();
+                last--;
+            }
+            if (last < 4) bad("switch needs at least one (when operand result) clause");
+            auto elseExpr = [&]() -> std::unique_ptr<Expr> {
+                if (!elseSx) return makeNull(t);
+                auto r = parse(*elseSx);
+                if (r->type != t) bad("switch else type differs from result type");
+                return r;
+            };
+            const Type vt = parse(x.kids[2])->type;
+            checkComparable(vt, false);
+            std::unique_ptr<Expr> chain = elseExpr();
+            for (size_t k = last; k-- > 3;) {
+                const Sx& w = x.kids[k];
+                if (w.atom || w.head() != "when" || w.kids.size() != 3) bad("(when operand result)");
+                auto o = parse(w.kids[1]);
+                auto r = parse(w.kids[2]);
+                if (o->type != vt) bad("when operand type differs from the switch value (wrap it in (call cast ...)): " + o->type.str() + " vs " + vt.str());
+                if (r->type != t) bad("when result type differs from result type");
+                chain = makeIf(t, makeEq(std::move(o), parse(x.kids[2])), std::move(r), std::move(chain));
+            }
+            return makeIf(t, makeIsNull(parse(x.kids[2])), elseExpr(), std::move(chain));
+        }
+        if (h == "when") bad("(when ...) outside (switch ...)");
+        if (h == "dereference" || h == "row-constructor" || h == "bind" || h == "lambda")
             unsupported("special form " + h);
         bad("unknown expression form '" + h + "'");
+    }
+
+    // nodes of the lowered forms (null-if, switch)
+    static std::unique_ptr<Expr> makeNull(const Type& t) {
+        auto e = std::make_unique<Expr>();
+        e->kind = ExprKind::CONST;
+        e->type = t;
+        e->isNull = true;
+        return e;
+    }
+    static std::unique_ptr<Expr> makeIsNull(std::unique_ptr<Expr> a) {
+        auto e = std::make_unique<Expr>();
+        e->kind = ExprKind::IS_NULL;
+        e->type = Type::boolean();
+        e->args.push_back(std::move(a));
+        return e;
+    }
+    static std::unique_ptr<Expr> makeEq(std::unique_ptr<Expr> a, std::unique_ptr<Expr> b) {
+        auto e = std::make_unique<Expr>();
+        e->kind = ExprKind::CALL;
+        e->op = Op::EQ;
+        e->type = Type::boolean();
+        e->args.push_back(std::move(a));
+        e->args.push_back(std::move(b));
+        return e;
+    }
+    static std::unique_ptr<Expr> makeIf(const Type& t, std::unique_ptr<Expr> c, std::unique_ptr<Expr> a, std::unique_ptr<Expr> b) {
+        auto e = std::make_unique<Expr>();
+        e->kind = ExprKind::IF;
+        e->type = t;
+        e->args.push_back(std::move(c));
+        e->args.push_back(std::move(a));
+        e->args.push_back(std::move(b));
+        return e;
     }
 
     static void checkValueType(const Type& t) {

@@ -58,7 +58,8 @@ class CallExpression(RowExpression):
 
 @dataclass
 class SpecialForm(RowExpression):
-    """form: AND OR BETWEEN IN IS_NULL IF COALESCE (SpecialForm.Form, SpecialForm.java:137-152)"""
+    """form: AND OR BETWEEN IN IS_NULL IF COALESCE NULL_IF SWITCH WHEN (SpecialForm.Form, SpecialForm.java:137-152);
+    SWITCH arguments = [value, WHEN(operand, result)..., optional else] as SwitchCodeGenerator.java:48-66 reads them"""
     form: str
     type: Type
     arguments: Sequence[RowExpression]
@@ -80,7 +81,9 @@ class SpecialForm(RowExpression):
             return "(if %s %s)" % (self.type, args)
         if f == "COALESCE":
             return "(coalesce %s %s)" % (self.type, args)
-        # forwarded verbatim so the native side reports NOT_SUPPORTED
+        if f == "SWITCH":
+            return "(switch %s %s)" % (self.type, args)
+        # NULL_IF / WHEN as they are; anything else is forwarded verbatim so the native side reports NOT_SUPPORTED
         return "(%s %s)" % (f.lower().replace("_", "-"), args)
 
 

@@ -8,6 +8,9 @@
   hash aggregation operator/TestHashAggregationOperator.java:161-219 (40 000 groups x 3 pages -> (i, 3, 3i, i, 3, 3)),
                    :222-271 (global default row over empty input), :477-560 (multi-page output)
   page processor   operator/project/TestPageProcessor.java:125-200, TestDictionaryAwarePageFilter.java:49-116
+  NULLIF / CASE    sql/gen/TestExpressionCompiler.java:321-348,440,492 (nullif over the left x right grids, expectation
+                   #nullIf :675-697), :981-1024 (simple CASE over value x first x second grids), :1649-1655;
+                   operator/scalar/TestConditions.java:308-380 (simple CASE literals, NULL operands and NULL value)
 
 Each case = (name, plan text, input pages, expected rows, number of leading key columns or None).
 The same cases run against the CPU oracle (-m "not gpu": pins the oracle) and the CUDA path (-m gpu: parity).
@@ -225,6 +228,109 @@ def filter_project_cases():
     return cases
 
 
+def conditional_cases():
+    """NULL_IF (NullIfCodeGenerator.java:70-113) and SWITCH/WHEN (SwitchCodeGenerator.java:113-159) over the value grids of
+    TestExpressionCompiler (:114-136). Every grid combination is one row; the CASE results 'first' / 'second' / 'else' of the
+    reference test are the BIGINT codes 1 / 2 / 0 here (VARCHAR values are not computed on this path)."""
+    cases = []
+
+    def null_if(left, right):  # TestExpressionCompiler.java:675-697
+        if left is None:
+            return None
+        if right is None:
+            return left
+        return None if left == right else left
+
+    def grid(*axes):
+        rows = [()]
+        for ax in axes:
+            rows = [r + (v,) for r in rows for v in ax]
+        return [list(c) for c in zip(*rows)]
+
+    small_ints = [9, 10, 11, -9, -10, -11, None]
+    int_lefts, int_rights, int_middle = small_ints + [101510, 2 ** 31 - 1], [3, -3, 101510823, None], [9, -3, 88, None]
+    long_lefts, long_rights = [9, 10, 11, -9, -10, -11, None], [3, -3, 10151082135029369, None]
+    dbl_lefts = [9.0, 10.0, 11.0, -9.0, -10.0, -11.0, 9.1, 10.1, 11.1, -9.1, -10.1, -11.1, 5e-324, 1.7976931348623157e308, 2.2250738585072014e-308, None]
+    dbl_rights, dbl_middle = [3.0, -3.0, 3.1, -3.1, None], [9.0, -3.1, 88.0, None]
+    D31 = createDecimalType(3, 1)
+    dec_lefts, dec_rights = [90, 100, 110, -90, -100, -110, 91, 101, 111, -91, -101, -111, None], [30, -30, 31, -31, None]  # unscaled
+
+    # nullif(left, right) for every pair of a grid, and against the left column itself (always NULL or left IS NULL)
+    for name, t, lefts, rights in (("integer", INTEGER, int_lefts, int_rights + [9, -11]), ("bigint", BIGINT, long_lefts, long_rights + [10, -9]),
+                                   ("double", DOUBLE, dbl_lefts, dbl_rights + [9.1, -0.0, 5e-324]), ("decimal", D31, dec_lefts, dec_rights + [91, -110])):
+        lcol, rcol = grid(lefts, rights)
+        L, R = field(0, t), field(1, t)
+        plan = plan_text([t, t], None, [SpecialForm("NULL_IF", t, [L, R]), SpecialForm("NULL_IF", t, [L, L]),
+                                        SpecialForm("NULL_IF", t, [L, constant(None, t)]), SpecialForm("NULL_IF", t, [constant(None, t), R])])
+        exp = [(null_if(x, y), None, x, None) for x, y in zip(lcol, rcol)]
+        cases.append(("nullif_grid_" + name, plan, [Page(block_of(t, lcol), block_of(t, rcol))], exp, "ordered"))
+
+    # case value when first then 1 when second then 2 else 0 end (doubles); without ELSE (integers, decimals)
+    def simple_case(value, first, second, otherwise):
+        if value is None:
+            return otherwise
+        if first is not None and value == first:
+            return 1
+        if second is not None and value == second:
+            return 2
+        return otherwise
+
+    for name, t, lefts, middle, rights, with_else in (("double_else", DOUBLE, dbl_lefts, dbl_middle + [11.1], dbl_rights + [-9.0], True),
+                                                      ("integer_no_else", INTEGER, int_lefts, int_middle, int_rights + [9], False),
+                                                      ("decimal_no_else", D31, dec_lefts, [90, -31, 880, None], dec_rights + [90], False)):
+        v, f, s2 = grid(lefts, middle, rights)
+        args = [field(0, t), SpecialForm("WHEN", BIGINT, [field(1, t), constant(1, BIGINT)]), SpecialForm("WHEN", BIGINT, [field(2, t), constant(2, BIGINT)])]
+        if with_else:
+            args.append(constant(0, BIGINT))
+        plan = plan_text([t, t, t], None, [SpecialForm("SWITCH", BIGINT, args)])
+        exp = [(simple_case(a, b, c, 0 if with_else else None),) for a, b, c in zip(v, f, s2)]
+        assert {r[0] for r in exp} >= {1, 2}
+        cases.append(("simple_case_grid_" + name, plan, [Page(block_of(t, v), block_of(t, f), block_of(t, s2))], exp, "ordered"))
+
+    # TestConditions.testSimpleCase literals on a BOOLEAN value (one row each, the value comes from the page)
+    T, F, N = constant(True, BOOLEAN), constant(False, BOOLEAN), constant(None, BOOLEAN)
+    V = field(0, BOOLEAN)
+
+    def when(o, r):
+        return SpecialForm("WHEN", BIGINT, [o, r])
+
+    c33, c1, cnull = constant(33, BIGINT), constant(1, BIGINT), constant(None, BIGINT)
+    proj = [SpecialForm("SWITCH", BIGINT, [V, when(T, c33)]),                                  # :318  -> 33
+            SpecialForm("SWITCH", BIGINT, [V, when(F, c1), c33]),                              # :332  -> 33
+            SpecialForm("SWITCH", BIGINT, [V, when(F, c1), when(F, c1), when(T, c33), c1]),    # :346  -> 33
+            SpecialForm("SWITCH", BIGINT, [V, when(F, c1)]),                                   # :355  -> NULL
+            SpecialForm("SWITCH", BIGINT, [V, when(T, cnull), c1]),                            # :361  -> NULL (a NULL result is a result)
+            SpecialForm("SWITCH", BIGINT, [V, when(N, c1), when(T, c33)]),                     # :369  -> 33 (NULL operand never matches)
+            SpecialForm("SWITCH", BIGINT, [constant(None, BOOLEAN), when(T, c1), c33]),        # :383  -> 33 (NULL value takes ELSE)
+            SpecialForm("SWITCH", BIGINT, [V, when(V, c33), c1])]                              # value = operand, NULL = NULL does not match
+    plan = plan_text([BOOLEAN], None, proj)
+    exp = [(33, 33, 33, None, None, 33, 33, 33), (None, 1, 1, 1, 1, None, 33, 33), (None, 33, 1, None, 1, None, 33, 1)]
+    cases.append(("simple_case_literals", plan, [Page(block_of(BOOLEAN, [True, False, None]))], exp, "ordered"))
+
+    # CASE and NULLIF feeding a filter and an aggregation: sum(nullif(x, 0)), count(case k when 1 then x when 2 then -x end) by k
+    n = 4000
+    k = [None if i % 17 == 0 else i % 4 for i in range(n)]
+    x = [None if i % 19 == 0 else (i * 7) % 11 - 5 for i in range(n)]
+    K, X = field(0, BIGINT), field(1, BIGINT)
+    sw = SpecialForm("SWITCH", BIGINT, [K, SpecialForm("WHEN", BIGINT, [constant(1, BIGINT), X]), SpecialForm("WHEN", BIGINT, [constant(2, BIGINT), call("negate", BIGINT, X)])])
+    f = compare("ne", SpecialForm("COALESCE", BIGINT, [SpecialForm("NULL_IF", BIGINT, [X, constant(3, BIGINT)]), constant(0, BIGINT)]), constant(-4, BIGINT))
+    plan = plan_text([BIGINT, BIGINT], f, [K, SpecialForm("NULL_IF", BIGINT, [X, constant(0, BIGINT)]), sw], step="single", groupByChannels=[0],
+                     aggregations=[Aggregation("sum", BIGINT, 1, BIGINT), Aggregation("count", BIGINT, 2, BIGINT), Aggregation("sum", BIGINT, 2, BIGINT)], expectedGroups=16)
+    groups = {}
+    for a, b in zip(k, x):
+        if (0 if (b is None or b == 3) else b) == -4:
+            continue
+        g = groups.setdefault(a, [[], []])
+        if b is not None and b != 0:
+            g[0].append(b)
+        c = None if a is None else (b if a == 1 else (None if b is None else -b) if a == 2 else None)
+        if c is not None:
+            g[1].append(c)
+    exp = [(a, sum(g[0]) if g[0] else None, len(g[1]), sum(g[1]) if g[1] else None) for a, g in groups.items()]
+    cases.append(("case_nullif_into_aggregation", plan, [Page(block_of(BIGINT, k), block_of(BIGINT, x))], exp, 1))
+    return cases
+
+
 def dictionary_rle_cases():
     """TestDictionaryAwarePageFilter (:49-116) / TestDictionaryAwarePageProjection (:80-143): dictionary, RLE and plain
     inputs holding the same values must give the same result."""
@@ -263,4 +369,4 @@ def dictionary_rle_cases():
 
 
 def all_cases():
-    return global_aggregate_cases() + hash_aggregation_cases() + filter_project_cases() + dictionary_rle_cases()
+    return global_aggregate_cases() + hash_aggregation_cases() + filter_project_cases() + conditional_cases() + dictionary_rle_cases()

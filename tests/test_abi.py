@@ -63,6 +63,18 @@ def test_canonical_plans_compile_for_every_page_signature():
         op.close()
 
 
+def test_conditional_forms_compile_for_sm_100a():
+    """NULL_IF / SWITCH plans of the known-answer suite: generated CUDA compiles (NVRTC, sm_100a) for plain and all-nullable pages"""
+    import kat_cases
+    for name, plan, pages, _, _ in kat_cases.conditional_cases():
+        op = GpuPipelineOperator(plan, device=-1)
+        n = len(pages[0].blocks)
+        op.compileSignature([0] * n, [b.mayHaveNull() for b in pages[0].blocks])
+        op.compileSignature([1] * n, [True] * n)
+        assert "null-if" in plan or "switch" in plan, name
+        op.close()
+
+
 def test_output_schema():
     op = GpuPipelineOperator(tpch.q1_plan(), device=-1)
     kinds = [t.kind for t in op.outputTypes()]
@@ -82,7 +94,13 @@ def test_output_schema():
 REJECTED = [
     ("unbounded varchar key", lambda: plan_text([VARCHAR, BIGINT], step="single", groupByChannels=[0], aggregations=[Aggregation("count", BIGINT)])),
     ("varchar(64) key", lambda: plan_text([createVarcharType(64), BIGINT], step="single", groupByChannels=[0], aggregations=[Aggregation("count", BIGINT)])),
-    ("unknown special form", lambda: plan_text([BIGINT], SpecialForm("NULL_IF", BOOLEAN, [field(0, BIGINT), constant(1, BIGINT)]), [field(0, BIGINT)])),
+    ("unsupported special form", lambda: plan_text([BIGINT], None, [SpecialForm("DEREFERENCE", BIGINT, [field(0, BIGINT), constant(1, BIGINT)])])),
+    ("when outside switch", lambda: plan_text([BIGINT], None, [SpecialForm("WHEN", BIGINT, [field(0, BIGINT), constant(1, BIGINT)])])),
+    ("null-if of differing types", lambda: plan_text([BIGINT, DOUBLE], None, [SpecialForm("NULL_IF", BIGINT, [field(0, BIGINT), field(1, DOUBLE)])])),
+    ("switch without when", lambda: plan_text([BIGINT], None, [SpecialForm("SWITCH", BIGINT, [field(0, BIGINT), constant(1, BIGINT)])])),
+    ("switch operand of another type", lambda: plan_text([BIGINT, DOUBLE], None, [SpecialForm("SWITCH", BIGINT, [field(0, BIGINT), SpecialForm("WHEN", BIGINT, [field(1, DOUBLE), constant(1, BIGINT)])])])),
+    ("switch result of another type", lambda: plan_text([BIGINT], None, [SpecialForm("SWITCH", BIGINT, [field(0, BIGINT), SpecialForm("WHEN", DOUBLE, [field(0, BIGINT), constant(1.0, DOUBLE)])])])),
+    ("switch computing varchar", lambda: plan_text([BIGINT, createVarcharType(3)], None, [SpecialForm("SWITCH", createVarcharType(3), [field(0, BIGINT), SpecialForm("WHEN", createVarcharType(3), [constant(1, BIGINT), field(1, createVarcharType(3))])])])),
     ("unknown function", lambda: plan_text([DOUBLE], None, [CallExpression("sqrt", DOUBLE, [field(0, DOUBLE)])])),
     ("unknown aggregate", lambda: plan_text([DOUBLE], step="single", aggregations=[Aggregation("approx_distinct", BIGINT, 0, DOUBLE)])),
     ("decimal division", lambda: plan_text([createDecimalType(10, 2)], None, [call("divide", createDecimalType(10, 2), field(0, createDecimalType(10, 2)), field(0, createDecimalType(10, 2)))])),
