@@ -132,6 +132,36 @@ pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size
  * var-width blocks their end offsets and bytes; all of it is packed on the device. A PARTIAL step's payload is what the
  * reference's exchange would carry to the FINAL step (feed it to pgpu_add_serialized_page of a FINAL pipeline). */
 pgpu_status pgpu_get_serialized_output(pgpu_pipeline* p, const uint8_t** data, size_t* len, int64_t* rows);
+/* One column chunk of a Parquet row group, as it lies in the file: from the first page header of the chunk (dictionary page if
+ * there is one) to its end — ColumnChunkMetaData.getStartingPos() / getTotalSize() as ParquetReader.readColumnChunk slices it
+ * (lib/trino-parquet/src/main/java/io/trino/parquet/reader/ParquetReader.java:244-268). Pages must be UNCOMPRESSED (the caller
+ * undoes the codec, as PageReader.readPage does, .../reader/PageReader.java:63-99). */
+typedef struct pgpu_parquet_chunk {
+    const uint8_t* data;          /* host pointer                                                            */
+    size_t len;
+    int32_t physical_type;        /* parquet.thrift Type: 0 BOOLEAN, 1 INT32, 2 INT64, 5 DOUBLE, 6 BYTE_ARRAY */
+    int32_t max_definition_level; /* 0 = required, 1 = optional flat column (nested columns are rejected)     */
+    int64_t num_values;           /* ColumnMetaData.num_values = rows of the row group for a flat column     */
+} pgpu_parquet_chunk;
+/* Operator.addInput of the Page that ParquetReader.nextPage / readBlock -> PrimitiveColumnReader.readPrimitive would build from
+ * one row group (.../reader/ParquetReader.java:211-268, PrimitiveColumnReader.java:148-317): chunk c feeds input channel c
+ * (INT32 -> INTEGER/DATE, INT64 -> BIGINT/short DECIMAL, DOUBLE, BOOLEAN, BYTE_ARRAY -> VARCHAR/VARBINARY with the bounded-VARCHAR
+ * truncation of BinaryColumnReader.java:44-58). Only page headers and the run headers of the RLE / bit-packed hybrid streams are
+ * read on the host; each chunk goes to the device in ONE copy and definition levels, dictionary ids and booleans are expanded
+ * there. A chunk whose data pages are all dictionary encoded is consumed as a DictionaryBlock (ids + dictionary page), never
+ * materialised. Data pages v1 and v2; PLAIN, PLAIN_DICTIONARY, RLE_DICTIONARY, RLE (levels, booleans). Rejected with
+ * PGPU_NOT_SUPPORTED: compressed pages, nested columns, DELTA_* / BYTE_STREAM_SPLIT encodings, INT96 / FLOAT / FIXED_LEN_BYTE_ARRAY,
+ * var-width chunks that are not dictionary encoded throughout. */
+pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chunk* chunks, int32_t nchunks, int64_t rows);
+/* What pgpu_add_parquet_row_group reads on the host, without a GPU: info[0] data pages, [1] dictionary entries (-1: none), [2] every
+ * data page dictionary encoded, [3] non-null values, [4] definition-level runs kept (0: no NULLs), [5] value runs, [6] some page
+ * dictionary encoded, [7] rows. Same status / message as the ingest would give for a chunk it rejects. */
+pgpu_status pgpu_parquet_inspect_chunk(const pgpu_parquet_chunk* chunk, int64_t* info, char* err, size_t err_len);
+/* The run tables the ingest hands to its device kernels, for checking them without a GPU: which = 0 definition levels, 1 values
+ * (dictionary ids / booleans), 2 data pages {start = first non-null value, src = byte offset of the values, count = non-null
+ * values, width = 1 if dictionary encoded}. Entry = {int64 start; uint64 src (bit offset of a bit-packed run | value of an RLE
+ * run); uint32 count; uint32 bit width | packed << 31}. *n = entries available, at most `cap` are written to `out`. */
+pgpu_status pgpu_parquet_chunk_runs(const pgpu_parquet_chunk* chunk, int32_t which, void* out, int64_t cap, int64_t* n);
 /* Same, with device-resident blocks (no copy). Buffers must stay valid until pgpu_sync(). */
 pgpu_status pgpu_add_device_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows);
 /* Operator.finish(): no more input; may be called repeatedly (main/operator/Driver.java:368-372). */

@@ -31,6 +31,12 @@ Column._fields_ = [
 ]
 
 
+class ParquetChunk(ctypes.Structure):
+    """pgpu_parquet_chunk"""
+    _fields_ = [("data", ctypes.c_char_p), ("len", ctypes.c_size_t), ("physical_type", ctypes.c_int32), ("max_definition_level", ctypes.c_int32),
+                ("num_values", ctypes.c_int64)]
+
+
 class Stats(ctypes.Structure):
     _fields_ = [("kernel_launches", ctypes.c_int64), ("h2d_bytes", ctypes.c_int64), ("d2h_bytes", ctypes.c_int64),
                 ("input_rows", ctypes.c_int64), ("input_pages", ctypes.c_int64), ("jit_compiles", ctypes.c_int64),
@@ -67,6 +73,9 @@ SYMBOLS = [
     ("pgpu_partition_output_device", ctypes.c_int32, [_P, ctypes.c_int32, _COLS, ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_add_serialized_page", ctypes.c_int32, [_P, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int64]),
     ("pgpu_get_serialized_output", ctypes.c_int32, [_P, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_int64)]),
+    ("pgpu_add_parquet_row_group", ctypes.c_int32, [_P, ctypes.POINTER(ParquetChunk), ctypes.c_int32, ctypes.c_int64]),
+    ("pgpu_parquet_inspect_chunk", ctypes.c_int32, [ctypes.POINTER(ParquetChunk), ctypes.POINTER(ctypes.c_int64), ctypes.c_char_p, ctypes.c_size_t]),
+    ("pgpu_parquet_chunk_runs", ctypes.c_int32, [ctypes.POINTER(ParquetChunk), ctypes.c_int32, ctypes.c_void_p, ctypes.c_int64, ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_tpch_order_count", ctypes.c_int64, [ctypes.c_double]),
     ("pgpu_tpch_lineitem_rows", ctypes.c_int32, [ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_tpch_lineitem_device", ctypes.c_int32, [ctypes.c_int32, ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]),

@@ -1,0 +1,109 @@
+// parquet.cu — see parquet.h. Ahead-of-time sm_100a kernels.
+#include "parquet.h"
+
+namespace pgpu {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr uint32_t kPacked = 0x80000000u;
+
+// index of the run that holds value `idx` (runs sorted by start, gap-free from runs[0].start)
+__device__ inline int64_t findRun(const PqRun* runs, int64_t nruns, int64_t idx) {
+    int64_t lo = 0, hi = nruns;  // first run with start > idx
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (runs[mid].start <= idx) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo - 1;
+}
+
+__device__ inline uint32_t codeAt(const uint8_t* chunk, size_t chunkLen, const PqRun& r, int64_t idx) {
+    const uint32_t width = r.widthPacked & 0xffu;
+    if (!(r.widthPacked & kPacked)) return (uint32_t)r.src;
+    if (width == 0) return 0;
+    const uint64_t bit = r.src + (uint64_t)(idx - r.start) * width;
+    const uint64_t byte = bit >> 3;
+    const uint32_t shift = (uint32_t)(bit & 7);
+    uint64_t w = 0;
+    const int need = (int)((shift + width + 7) >> 3);  // <= 5
+    for (int b = 0; b < need; b++)
+        if (byte + b < chunkLen) w |= (uint64_t)chunk[byte + b] << (8 * b);
+    return (uint32_t)((w >> shift) & (width == 32 ? 0xffffffffull : ((1ull << width) - 1)));
+}
+
+__global__ void __launch_bounds__(kThreads) k_pq_null_bits(const uint8_t* chunk, size_t chunkLen, const PqRun* runs, int64_t nruns, int64_t n, uint8_t* bits) {
+    const int64_t nbytes = (n + 7) >> 3;
+    for (int64_t j = (int64_t)blockIdx.x * kThreads + threadIdx.x; j < nbytes; j += (int64_t)gridDim.x * kThreads) {
+        int64_t pos = j << 3;
+        int64_t ri = findRun(runs, nruns, pos);
+        PqRun r = runs[ri < 0 ? 0 : ri];
+        uint32_t out = 0;
+        for (int k = 0; k < 8 && pos < n; k++, pos++) {
+            while (pos >= r.start + (int64_t)r.count && ri + 1 < nruns) r = runs[++ri];
+            const uint32_t level = codeAt(chunk, chunkLen, r, pos);
+            if (level == 0) out |= 0x80u >> k;
+        }
+        bits[j] = (uint8_t)out;
+    }
+}
+
+template <typename OUT, bool GATHER>
+__global__ void __launch_bounds__(kThreads) k_pq_expand(const uint8_t* chunk, size_t chunkLen, const PqRun* runs, int64_t nruns, int64_t first, int64_t count,
+                                                        const OUT* dict, uint32_t limit, OUT* out, uint32_t* err) {
+    bool bad = false;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < count; i += (int64_t)gridDim.x * kThreads) {
+        const int64_t idx = first + i;
+        const int64_t ri = findRun(runs, nruns, idx);
+        uint32_t code = codeAt(chunk, chunkLen, runs[ri < 0 ? 0 : ri], idx);
+        if (code >= limit) {
+            bad = true;
+            code = 0;
+        }
+        if (GATHER) out[i] = limit ? dict[code] : OUT(0);
+        else out[i] = (OUT)code;
+    }
+    if (bad) atomicOr(err, kPqErrBadId);
+}
+
+__global__ void __launch_bounds__(kThreads) k_pq_null_ids(int32_t* ids, const uint8_t* nulls, int64_t n, int32_t nullId) {
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
+        if (nulls[i]) ids[i] = nullId;
+}
+
+inline int gridFor(int64_t items) {
+    const int64_t blocks = (items + kThreads - 1) / kThreads;
+    return (int)(blocks < 1 ? 1 : blocks > 148 * 16 ? 148 * 16 : blocks);  // grid-stride loops: at most 16 blocks per SM
+}
+
+}  // namespace
+
+cudaError_t pqLevelsToNullBits(cudaStream_t stream, const uint8_t* chunk, size_t chunkLen, const PqRun* runs, int64_t nruns, int64_t n, uint8_t* bits) {
+    if (n <= 0) return cudaSuccess;
+    k_pq_null_bits<<<gridFor((n + 7) / 8), kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, n, bits);
+    return cudaGetLastError();
+}
+
+cudaError_t pqExpandRuns(cudaStream_t stream, const uint8_t* chunk, size_t chunkLen, const PqRun* runs, int64_t nruns, int64_t first, int64_t count, int outWidth,
+                         const void* dict, uint32_t limit, void* out, uint32_t* err) {
+    if (count <= 0) return cudaSuccess;
+    const int g = gridFor(count);
+    if (dict) {
+        if (outWidth == 8) k_pq_expand<uint64_t, true><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, (const uint64_t*)dict, limit, (uint64_t*)out, err);
+        else if (outWidth == 4) k_pq_expand<uint32_t, true><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, (const uint32_t*)dict, limit, (uint32_t*)out, err);
+        else return cudaErrorInvalidValue;
+    } else {
+        if (outWidth == 4) k_pq_expand<uint32_t, false><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, nullptr, limit, (uint32_t*)out, err);
+        else if (outWidth == 1) k_pq_expand<uint8_t, false><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, nullptr, limit, (uint8_t*)out, err);
+        else return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t pqNullIds(cudaStream_t stream, int32_t* ids, const uint8_t* nulls, int64_t n, int32_t nullId) {
+    if (n <= 0) return cudaSuccess;
+    k_pq_null_ids<<<gridFor(n), kThreads, 0, stream>>>(ids, nulls, n, nullId);
+    return cudaGetLastError();
+}
+
+}  // namespace pgpu

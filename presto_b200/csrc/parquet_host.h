@@ -1,0 +1,432 @@
+// parquet_host.h — host side of ingesting Parquet column chunks: reads the page HEADERS and the RUN HEADERS of the hybrid
+// streams of a column chunk (a few bytes per page / per run) and describes where every piece lies. Values are never decoded
+// on the CPU: the chunk goes to the device in one DMA and the kernels of parquet.cu expand it there.
+//
+// Stands in for (paths under /root/reference/lib/trino-parquet/src/main/java/io/trino/parquet/):
+//   reader/ParquetColumnChunk.java:54-135      readPageHeader / readAllPages / readDictionaryPage / readDataPageV1 / V2
+//   reader/PrimitiveColumnReader.java:268-317  readPageV1 / readPageV2 / initDataReader (levels, then values)
+//   ParquetEncoding.java:58-234                PLAIN, RLE, PLAIN_DICTIONARY, RLE_DICTIONARY value readers
+// The formats themselves (Thrift compact PageHeader, RLE / bit-packed hybrid) are parquet-format's; the reference takes them
+// from the org.apache.parquet classes shaded into io.trino.hive:hive-apache 3.1.2-12 (not in the reference tree).
+//
+// Subset: flat columns (max definition level 0 or 1, no repetition), UNCOMPRESSED pages, data pages v1 and v2, PLAIN /
+// PLAIN_DICTIONARY / RLE_DICTIONARY values (+ RLE booleans), RLE levels. Everything else is rejected ("not supported ...").
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace pgpu {
+namespace pq {
+
+enum PhysicalType { BOOLEAN = 0, INT32 = 1, INT64 = 2, INT96 = 3, FLOAT = 4, DOUBLE = 5, BYTE_ARRAY = 6, FIXED_LEN_BYTE_ARRAY = 7 };  // parquet.thrift Type
+enum Encoding { PLAIN = 0, PLAIN_DICTIONARY = 2, RLE = 3, BIT_PACKED = 4, RLE_DICTIONARY = 8 };                                       // parquet.thrift Encoding
+enum PageType { DATA_PAGE = 0, INDEX_PAGE = 1, DICTIONARY_PAGE = 2, DATA_PAGE_V2 = 3 };                                               // parquet.thrift PageType
+
+// One run of a hybrid stream, in the form the device kernels read (24 bytes). `start` counts in the stream's own numbering,
+// chunk-wide: rows for definition levels, non-null values for ids / booleans.
+struct Run {
+    int64_t start;
+    uint64_t src;      // bit-packed: BIT offset of the run's first value from the start of the chunk; RLE: the repeated value
+    uint32_t count;
+    uint32_t widthPacked;  // bits 0..7: bit width; bit 31: bit-packed
+};
+constexpr uint32_t kPackedFlag = 0x80000000u;
+
+struct DataPage {
+    int64_t firstRow = 0, rows = 0;
+    int64_t firstValue = 0, nonNull = 0;  // position among the chunk's non-null values
+    int encoding = PLAIN;
+    bool dictionaryEncoded = false;
+    size_t valuesOff = 0, valuesEnd = 0;  // PLAIN fixed width: the values; otherwise the value stream (described by valueRuns)
+    size_t runLo = 0, runHi = 0;          // this page's slice of Chunk::valueRuns
+};
+
+struct Chunk {
+    int64_t rows = 0, nonNull = 0;
+    bool hasDictionary = false;
+    int64_t dictionaryCount = 0;
+    size_t dictionaryOff = 0, dictionaryEnd = 0;  // PLAIN values of the dictionary page
+    bool allDictionary = false;                   // every data page is dictionary encoded -> DictionaryBlock
+    bool anyDictionary = false;
+    std::vector<DataPage> pages;
+    std::vector<Run> levelRuns;   // definition levels of the whole chunk (empty when there is no NULL: rows == nonNull)
+    std::vector<Run> valueRuns;   // dictionary ids, BOOLEAN values
+    bool hasNulls() const { return nonNull != rows; }
+};
+
+namespace detail {
+
+struct Reader {
+    const uint8_t* d;
+    size_t len, pos;
+    bool ok = true;
+    uint8_t byte() {
+        if (pos >= len) { ok = false; return 0; }
+        return d[pos++];
+    }
+    uint64_t varint() {
+        uint64_t v = 0;
+        for (int s = 0; s < 70; s += 7) {
+            const uint8_t c = byte();
+            if (!ok) return 0;
+            if (s < 64) v |= (uint64_t)(c & 0x7F) << s;
+            if (!(c & 0x80)) return v;
+        }
+        ok = false;
+        return 0;
+    }
+    int64_t zigzag() {
+        const uint64_t v = varint();
+        return (int64_t)(v >> 1) ^ -(int64_t)(v & 1);
+    }
+    void advance(uint64_t n) {
+        if (n > len - pos) { ok = false; pos = len; return; }
+        pos += (size_t)n;
+    }
+    // Thrift compact protocol: skip one value of wire type t
+    void skip(int t, int depth = 0) {
+        if (!ok || depth > 16) { ok = false; return; }
+        switch (t) {
+            case 1: case 2: return;  // booleans live in the field header
+            case 3: byte(); return;
+            case 4: case 5: case 6: varint(); return;
+            case 7: advance(8); return;
+            case 8: advance(varint()); return;
+            case 9: case 10: {
+                const uint8_t h = byte();
+                uint64_t n = h >> 4;
+                if (n == 15) n = varint();
+                for (uint64_t i = 0; i < n && ok; i++) skipElement(h & 15, depth);
+                return;
+            }
+            case 11: {
+                const uint64_t n = varint();
+                if (!n) return;
+                const uint8_t kv = byte();
+                for (uint64_t i = 0; i < n && ok; i++) {
+                    skipElement(kv >> 4, depth);
+                    skipElement(kv & 15, depth);
+                }
+                return;
+            }
+            case 12: {
+                int16_t last = 0;
+                int fid, ft;
+                while (field(last, fid, ft)) skip(ft, depth + 1);
+                return;
+            }
+            default: ok = false;
+        }
+    }
+    void skipElement(int t, int depth) {
+        if (t == 1 || t == 2) byte();  // booleans inside collections take a byte
+        else skip(t, depth + 1);
+    }
+    // next field header of a struct; false at the stop byte
+    bool field(int16_t& last, int& fid, int& type) {
+        const uint8_t h = byte();
+        if (!ok || h == 0) return false;
+        type = h & 15;
+        const int delta = h >> 4;
+        fid = delta ? last + delta : (int)zigzag();
+        last = (int16_t)fid;
+        return ok;
+    }
+};
+
+struct PageHeader {
+    int type = -1;
+    int64_t uncompressedSize = -1, compressedSize = -1;
+    int64_t numValues = -1, numNulls = -1;
+    int encoding = -1, defEncoding = RLE, repEncoding = RLE;
+    int64_t defBytes = 0, repBytes = 0;
+    bool isCompressed = true;  // DataPageHeaderV2 default
+};
+
+// parquet.thrift PageHeader {1 type, 2 uncompressed_page_size, 3 compressed_page_size, 4 crc, 5 data_page_header,
+// 6 index_page_header, 7 dictionary_page_header, 8 data_page_header_v2}
+inline bool readPageHeader(Reader& r, PageHeader& h) {
+    int16_t last = 0;
+    int fid, t;
+    while (r.field(last, fid, t)) {
+        if (fid == 1 && t == 5) h.type = (int)r.zigzag();
+        else if (fid == 2 && t == 5) h.uncompressedSize = r.zigzag();
+        else if (fid == 3 && t == 5) h.compressedSize = r.zigzag();
+        else if ((fid == 5 || fid == 7 || fid == 8) && t == 12) {
+            int16_t l2 = 0;
+            int f2, t2;
+            while (r.field(l2, f2, t2)) {
+                const bool integer = t2 == 4 || t2 == 5 || t2 == 6;
+                if (f2 == 1 && integer) h.numValues = r.zigzag();
+                else if (fid != 8 && f2 == 2 && integer) h.encoding = (int)r.zigzag();
+                else if (fid == 5 && f2 == 3 && integer) h.defEncoding = (int)r.zigzag();
+                else if (fid == 5 && f2 == 4 && integer) h.repEncoding = (int)r.zigzag();
+                else if (fid == 8 && f2 == 2 && integer) h.numNulls = r.zigzag();
+                else if (fid == 8 && f2 == 4 && integer) h.encoding = (int)r.zigzag();
+                else if (fid == 8 && f2 == 5 && integer) h.defBytes = r.zigzag();
+                else if (fid == 8 && f2 == 6 && integer) h.repBytes = r.zigzag();
+                else if (fid == 8 && f2 == 7 && (t2 == 1 || t2 == 2)) h.isCompressed = t2 == 1;
+                else r.skip(t2);
+            }
+        } else {
+            r.skip(t);
+        }
+    }
+    return r.ok && h.type >= 0 && h.uncompressedSize >= 0 && h.compressedSize >= 0;
+}
+
+inline int64_t popcountBits(const uint8_t* d, uint64_t bits) {
+    int64_t c = 0;
+    uint64_t i = 0;
+    for (; i + 64 <= bits; i += 64) {
+        uint64_t w;
+        memcpy(&w, d + i / 8, 8);
+        c += __builtin_popcountll(w);
+    }
+    for (; i < bits; i++) c += (d[i / 8] >> (i & 7)) & 1;
+    return c;
+}
+
+// Reads the run headers of one hybrid stream d[pos, end) holding `count` values of `width` bits and appends them to `runs`
+// (numbered from `start`); *ones = how many values equal 1 (definition levels of width 1). Adjacent RLE runs of the same value
+// are merged when `merge` (levels of a column without NULLs collapse into one run per chunk).
+inline bool scanHybrid(const uint8_t* d, size_t pos, size_t end, int width, int64_t count, int64_t start, std::vector<Run>& runs, int64_t* ones,
+                       bool merge, std::string& why) {
+    Reader r{d, end, pos};
+    const int valueBytes = (width + 7) / 8;
+    int64_t n = 0;
+    while (n < count) {
+        if (r.pos >= end) { why = "corrupt Parquet page: hybrid stream ends after " + std::to_string(n) + " of " + std::to_string(count) + " values"; return false; }
+        const uint64_t h = r.varint();
+        if (!r.ok) { why = "corrupt Parquet page: truncated run header"; return false; }
+        if (h & 1) {
+            const uint64_t groups = h >> 1;
+            if (groups == 0 || groups > (1ull << 40)) { why = "corrupt Parquet page: bit-packed run of " + std::to_string(groups) + " groups"; return false; }
+            const uint64_t bytes = groups * (uint64_t)width;
+            const int64_t take = (int64_t)std::min<uint64_t>(groups * 8, (uint64_t)(count - n));
+            // the last group of a stream may be cut short by its writer; what we take must be there
+            if (((uint64_t)take * width + 7) / 8 > end - r.pos) { why = "corrupt Parquet page: bit-packed run exceeds the stream"; return false; }
+            if (ones) *ones += width == 1 ? popcountBits(d + r.pos, (uint64_t)take) : 0;
+            int64_t done = 0;
+            while (done < take) {  // Run::count is 32 bits
+                const int64_t c = std::min<int64_t>(take - done, 0x40000000);
+                runs.push_back(Run{start + n + done, (uint64_t)r.pos * 8 + (uint64_t)done * width, (uint32_t)c, (uint32_t)width | kPackedFlag});
+                done += c;
+            }
+            r.pos += (size_t)std::min<uint64_t>(bytes, end - r.pos);
+            n += take;
+        } else {
+            const uint64_t len = h >> 1;
+            if (len == 0) { why = "corrupt Parquet page: empty RLE run"; return false; }
+            if ((size_t)valueBytes > end - r.pos) { why = "corrupt Parquet page: RLE run exceeds the stream"; return false; }
+            uint64_t v = 0;
+            memcpy(&v, d + r.pos, (size_t)valueBytes);
+            r.pos += (size_t)valueBytes;
+            const int64_t take = (int64_t)std::min<uint64_t>(len, (uint64_t)(count - n));
+            if (ones && v == 1) *ones += take;
+            int64_t done = 0;
+            while (done < take) {
+                const int64_t c = std::min<int64_t>(take - done, 0x40000000);
+                Run* prev = runs.empty() ? nullptr : &runs.back();
+                if (merge && prev && !(prev->widthPacked & kPackedFlag) && prev->src == v && prev->start + prev->count == start + n + done && (int64_t)prev->count + c <= 0x40000000)
+                    prev->count += (uint32_t)c;
+                else
+                    runs.push_back(Run{start + n + done, v, (uint32_t)c, (uint32_t)width});
+                done += c;
+            }
+            n += take;
+        }
+    }
+    return true;
+}
+
+inline int32_t le32(const uint8_t* p) {
+    int32_t v;
+    memcpy(&v, p, 4);
+    return v;
+}
+
+}  // namespace detail
+
+inline int valueWidth(int ptype) { return ptype == INT32 ? 4 : ptype == INT64 || ptype == DOUBLE ? 8 : ptype == BOOLEAN ? 1 : 0; }
+
+// Describes one column chunk. `why` starts with "not supported" for rejections of well-formed input.
+inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int64_t numValues, Chunk& out, std::string& why) {
+    using namespace detail;
+    if (maxDef < 0 || maxDef > 1) { why = "not supported on the GPU path: nested Parquet columns (max definition level " + std::to_string(maxDef) + ")"; return false; }
+    if (!(ptype == BOOLEAN || ptype == INT32 || ptype == INT64 || ptype == DOUBLE || ptype == BYTE_ARRAY)) {
+        why = "not supported on the GPU path: Parquet physical type " + std::to_string(ptype);
+        return false;
+    }
+    if (numValues < 0 || (!d && len)) { why = "corrupt Parquet chunk: bad arguments"; return false; }
+    out = Chunk();
+    out.rows = numValues;
+    std::vector<Run> levels;
+    size_t pos = 0;
+    int64_t done = 0, values = 0;
+    bool anyPlain = false;
+    while (done < numValues) {
+        if (pos >= len) { why = "corrupt Parquet chunk: ends after " + std::to_string(done) + " of " + std::to_string(numValues) + " values"; return false; }
+        Reader r{d, len, pos};
+        PageHeader h;
+        if (!readPageHeader(r, h)) { why = "corrupt Parquet chunk: unreadable page header at byte " + std::to_string(pos); return false; }
+        if (h.compressedSize != h.uncompressedSize) { why = "not supported on the GPU path: compressed Parquet pages (decompress before handing the chunk over)"; return false; }
+        const size_t body = r.pos;
+        if ((uint64_t)h.compressedSize > len - body) { why = "corrupt Parquet chunk: page exceeds the chunk"; return false; }
+        const size_t end = body + (size_t)h.compressedSize;
+        pos = end;
+        if (h.type == INDEX_PAGE) continue;
+        if (h.type == DICTIONARY_PAGE) {
+            if (out.hasDictionary || done) { why = "corrupt Parquet chunk: dictionary page must be the first page"; return false; }
+            if (h.encoding != PLAIN && h.encoding != PLAIN_DICTIONARY) { why = "not supported on the GPU path: dictionary page encoding " + std::to_string(h.encoding); return false; }
+            if (ptype == BOOLEAN) { why = "not supported on the GPU path: dictionary-encoded BOOLEAN"; return false; }
+            if (h.numValues < 0 || h.numValues > 0x7fffffff) { why = "corrupt Parquet chunk: dictionary size"; return false; }
+            const int w = valueWidth(ptype);
+            if (w && (uint64_t)h.numValues * w > end - body) { why = "corrupt Parquet chunk: dictionary values exceed the page"; return false; }
+            out.hasDictionary = true;
+            out.dictionaryCount = h.numValues;
+            out.dictionaryOff = body;
+            out.dictionaryEnd = end;
+            continue;
+        }
+        if (h.type != DATA_PAGE && h.type != DATA_PAGE_V2) { why = "not supported on the GPU path: Parquet page type " + std::to_string(h.type); return false; }
+        if (h.numValues < 0 || h.numValues > numValues - done) { why = "corrupt Parquet chunk: pages hold more values than the metadata says"; return false; }
+        DataPage pg;
+        pg.firstRow = done;
+        pg.rows = h.numValues;
+        pg.firstValue = values;
+        pg.encoding = h.encoding;
+        size_t p = body;
+        int64_t ones = 0;
+        bool scanned = false;
+        if (h.type == DATA_PAGE) {
+            // v1: [repetition levels (absent at max level 0)][4-byte length + hybrid definition levels][values]
+            if (maxDef) {
+                if (h.defEncoding != RLE) { why = "not supported on the GPU path: definition level encoding " + std::to_string(h.defEncoding); return false; }
+                if (end - p < 4) { why = "corrupt Parquet page: no room for the level length"; return false; }
+                const int32_t ln = le32(d + p);
+                if (ln < 0 || (uint64_t)ln > end - p - 4) { why = "corrupt Parquet page: definition levels exceed the page"; return false; }
+                if (!scanHybrid(d, p + 4, p + 4 + (size_t)ln, 1, pg.rows, done, levels, &ones, true, why)) return false;
+                scanned = true;
+                p += 4 + (size_t)ln;
+            } else {
+                ones = pg.rows;
+            }
+        } else {
+            if (h.repBytes) { why = "not supported on the GPU path: repetition levels"; return false; }
+            if (h.defBytes < 0 || (uint64_t)h.defBytes > end - p) { why = "corrupt Parquet page: definition levels exceed the page"; return false; }
+            if (maxDef && h.defBytes) {
+                if (!scanHybrid(d, p, p + (size_t)h.defBytes, 1, pg.rows, done, levels, &ones, true, why)) return false;
+                scanned = true;
+            } else {
+                ones = pg.rows;
+            }
+            p += (size_t)h.defBytes;
+        }
+        if (!scanned) {  // no level stream for this page: all present. Keeps the chunk-wide level stream gap-free.
+            Run* prev = levels.empty() ? nullptr : &levels.back();
+            int64_t left = pg.rows, at = done;
+            while (left > 0) {
+                const int64_t c = std::min<int64_t>(left, 0x40000000);
+                if (prev && !(prev->widthPacked & kPackedFlag) && prev->src == 1 && prev->start + prev->count == at && (int64_t)prev->count + c <= 0x40000000) {
+                    prev->count += (uint32_t)c;
+                } else {
+                    levels.push_back(Run{at, 1, (uint32_t)c, 1});
+                    prev = &levels.back();
+                }
+                at += c;
+                left -= c;
+            }
+        }
+        pg.nonNull = ones;
+        if (h.type == DATA_PAGE_V2 && h.numNulls >= 0 && h.numNulls != pg.rows - ones) { why = "corrupt Parquet page: num_nulls disagrees with the definition levels"; return false; }
+        pg.valuesOff = p;
+        pg.valuesEnd = end;
+        pg.runLo = out.valueRuns.size();
+        if (h.encoding == PLAIN_DICTIONARY || h.encoding == RLE_DICTIONARY) {
+            if (!out.hasDictionary) { why = "corrupt Parquet chunk: Dictionary is missing for Page"; return false; }
+            pg.dictionaryEncoded = true;
+            out.anyDictionary = true;
+            if (pg.nonNull) {
+                if (p >= end) { why = "corrupt Parquet page: no dictionary id width"; return false; }
+                const int width = d[p];
+                if (width > 32) { why = "corrupt Parquet page: dictionary id width " + std::to_string(width); return false; }
+                if (!scanHybrid(d, p + 1, end, width, pg.nonNull, values, out.valueRuns, nullptr, false, why)) return false;
+            }
+        } else if (h.encoding == PLAIN) {
+            anyPlain = true;
+            if (ptype == BYTE_ARRAY) { why = "not supported on the GPU path: PLAIN-encoded BYTE_ARRAY data pages (only dictionary-encoded var-width chunks)"; return false; }
+            if (ptype == BOOLEAN) {  // bits, least significant first = one bit-packed run of width 1
+                if (((uint64_t)pg.nonNull + 7) / 8 > end - p) { why = "corrupt Parquet page: PLAIN booleans exceed the page"; return false; }
+                int64_t doneV = 0;
+                while (doneV < pg.nonNull) {
+                    const int64_t c = std::min<int64_t>(pg.nonNull - doneV, 0x40000000);
+                    out.valueRuns.push_back(Run{values + doneV, (uint64_t)p * 8 + (uint64_t)doneV, (uint32_t)c, 1u | kPackedFlag});
+                    doneV += c;
+                }
+            } else if ((uint64_t)pg.nonNull * valueWidth(ptype) > end - p) {
+                why = "corrupt Parquet page: PLAIN values exceed the page";
+                return false;
+            }
+        } else if (h.encoding == RLE && ptype == BOOLEAN) {  // ParquetEncoding.java:106-116, max "level" of BOOLEAN values = 1
+            anyPlain = true;
+            if (end - p < 4) { why = "corrupt Parquet page: no room for the RLE length"; return false; }
+            const int32_t ln = le32(d + p);
+            if (ln < 0 || (uint64_t)ln > end - p - 4) { why = "corrupt Parquet page: RLE booleans exceed the page"; return false; }
+            if (pg.nonNull && !scanHybrid(d, p + 4, p + 4 + (size_t)ln, 1, pg.nonNull, values, out.valueRuns, nullptr, false, why)) return false;
+        } else {
+            why = "not supported on the GPU path: Parquet data page encoding " + std::to_string(h.encoding);
+            return false;
+        }
+        pg.runHi = out.valueRuns.size();
+        out.pages.push_back(pg);
+        done += pg.rows;
+        values += pg.nonNull;
+    }
+    out.nonNull = values;
+    out.allDictionary = out.anyDictionary && !anyPlain;
+    if (ptype == BYTE_ARRAY && !out.allDictionary && out.rows) {
+        why = "not supported on the GPU path: var-width Parquet chunk that is not dictionary encoded throughout";
+        return false;
+    }
+    if (out.hasNulls()) out.levelRuns.swap(levels);
+    return true;
+}
+
+// PLAIN BYTE_ARRAY dictionary page -> offsets[count + 1] + the value bytes (4-byte length prefixes dropped). `maxChars` > 0
+// truncates every value to that many UTF-8 code points, as BinaryColumnReader does for a bounded VARCHAR
+// (reader/BinaryColumnReader.java:44-58, spi/type/Varchars.truncateToLength).
+inline bool binaryDictionary(const uint8_t* d, size_t off, size_t end, int64_t count, int maxChars, std::vector<int32_t>& offsets, std::vector<uint8_t>& bytes, std::string& why) {
+    offsets.assign(1, 0);
+    bytes.clear();
+    size_t p = off;
+    for (int64_t i = 0; i < count; i++) {
+        if (end - p < 4) { why = "corrupt Parquet dictionary page: truncated length"; return false; }
+        const int32_t n = detail::le32(d + p);
+        p += 4;
+        if (n < 0 || (uint64_t)n > end - p) { why = "corrupt Parquet dictionary page: value exceeds the page"; return false; }
+        size_t keep = (size_t)n;
+        if (maxChars > 0) {
+            int chars = 0;
+            size_t k = 0;
+            while (k < (size_t)n) {
+                if ((d[p + k] & 0xC0) != 0x80) {  // a code point starts here
+                    if (chars == maxChars) break;
+                    chars++;
+                }
+                k++;
+            }
+            keep = k;
+        }
+        bytes.insert(bytes.end(), d + p, d + p + keep);
+        if (bytes.size() > 0x7fffffff) { why = "Parquet dictionary page larger than 2 GB"; return false; }
+        offsets.push_back((int32_t)bytes.size());
+        p += (size_t)n;
+    }
+    return true;
+}
+
+}  // namespace pq
+}  // namespace pgpu

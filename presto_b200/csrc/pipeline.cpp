@@ -23,6 +23,8 @@
 #include "jit.h"
 #include "plan.h"
 #include "serde.h"
+#include "parquet.h"
+#include "parquet_host.h"
 
 using namespace pgpu;
 
@@ -153,6 +155,7 @@ struct pgpu_pipeline {
     DeviceBuf serdeOutArena;            // getOutput in the wire format: packed pieces of every channel
     HostOut serdeHost, serdeTotals;     // the payload (pinned) and the per-channel counts the layout depends on
     size_t serdeLen = 0;
+    DeviceBuf parquetArena;             // Parquet ingest: chunk bytes, run tables and the decoded block arrays of the row group being added
     // partitioned output (exchange)
     // one allocation for every partitioned column (a peer maps it with a single IPC handle); arenas replaced by a
     // larger one stay allocated until destroy because a peer may still have them mapped
@@ -326,6 +329,7 @@ pgpu_status checkDeviceErrors(pgpu_pipeline* p) {
     if (e & 1u) return fail(p, PGPU_NUMERIC_VALUE_OUT_OF_RANGE, "numeric value out of range (integer or decimal overflow)");
     if (e & 32u) return fail(p, PGPU_INVALID_CAST_ARGUMENT, "Unable to cast double to bigint");
     if (e & 8u) return fail(p, PGPU_INVALID_ARGUMENT, "varchar(n) value longer than n bytes");
+    if (e & 64u) return fail(p, PGPU_INVALID_ARGUMENT, "corrupt Parquet page: dictionary id out of range");
     if (e & 4u) return fail(p, PGPU_INSUFFICIENT_RESOURCES, "internal: hash table full");
     return fail(p, PGPU_CUDA_ERROR, "internal: output buffer overflow");
 }
@@ -1003,6 +1007,7 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
         if (p->outHostArena.ptr) cudaFreeHost(p->outHostArena.ptr);
         if (p->serdeArena.ptr) cudaFree(p->serdeArena.ptr);
         if (p->serdeOutArena.ptr) cudaFree(p->serdeOutArena.ptr);
+        if (p->parquetArena.ptr) cudaFree(p->parquetArena.ptr);
         if (p->serdeHost.ptr) cudaFreeHost(p->serdeHost.ptr);
         if (p->serdeTotals.ptr) cudaFreeHost(p->serdeTotals.ptr);
         if (p->partArena.ptr) cudaFree(p->partArena.ptr);
@@ -1249,6 +1254,227 @@ pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size
     }
     st = addPageCommon(p, cols.data(), nblocks, position_count, true, 0);
     return st ? st : updatePartialFill(p);
+}
+
+// ---- Parquet column chunks ------------------------------------------------------------------------------------------------
+// Stands in for ParquetReader.nextPage / readBlock -> PrimitiveColumnReader.readPrimitive
+// (lib/trino-parquet/src/main/java/io/trino/parquet/reader/ParquetReader.java:211-268, PrimitiveColumnReader.java:148-175):
+// one row group's column chunks become the Blocks of one input Page. The host reads page and run headers only
+// (parquet_host.h); the chunk bytes go to the device in one DMA per column and are expanded there (parquet.cu, serde.cu).
+// A chunk whose data pages are all dictionary encoded becomes a DictionaryBlock (ids + the dictionary page's values, a NULL
+// entry appended when the column has NULLs) — what the staged Q1 kernel consumes without materialising the values.
+pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chunk* chunks, int32_t nchunks, int64_t rows) {
+    if (!p || (!chunks && nchunks)) return PGPU_INVALID_ARGUMENT;
+    if (p->device < 0) return fail(p, PGPU_INVALID_STATE, "pipeline was created compile-only (device < 0)");
+    if (p->finishing) return fail(p, PGPU_INVALID_STATE, "Operator is already finishing");
+    if (!pgpu_needs_input(p)) return fail(p, PGPU_INVALID_STATE, "Operator does not need input");
+    const Plan& plan = *p->plan;
+    if (nchunks != (int)plan.input.size())
+        return fail(p, PGPU_INVALID_ARGUMENT, "row group has " + std::to_string(nchunks) + " column chunks, plan expects " + std::to_string(plan.input.size()));
+    if (rows < 0 || rows > 0x7fffffff) return fail(p, PGPU_INVALID_ARGUMENT, "row group row count out of range");
+    std::vector<pq::Chunk> ck((size_t)nchunks);
+    std::vector<std::vector<int32_t>> dictOffsets((size_t)nchunks);
+    std::vector<std::vector<uint8_t>> dictBytes((size_t)nchunks);
+    for (int c = 0; c < nchunks; c++) {
+        const pgpu_parquet_chunk& in = chunks[c];
+        const Type& t = plan.input[c];
+        const int pt = in.physical_type;
+        const bool match = (pt == pq::BOOLEAN && t.kind == TypeKind::BOOLEAN) || (pt == pq::INT32 && t.isInt32()) || (pt == pq::INT64 && t.isInt64Like()) ||
+                           (pt == pq::DOUBLE && t.kind == TypeKind::DOUBLE) || (pt == pq::BYTE_ARRAY && t.isVarWidth());
+        if (!match)
+            return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: Parquet physical type " + std::to_string(pt) + " for a " + t.str() + " channel (channel " + std::to_string(c) + ")");
+        if (in.num_values != rows) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " holds " + std::to_string(in.num_values) + " values, the row group " + std::to_string(rows) + " rows");
+        std::string why;
+        if (!pq::parseChunk(in.data, in.len, pt, in.max_definition_level, in.num_values, ck[c], why))
+            return fail(p, why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT, why + " (channel " + std::to_string(c) + ")");
+        if (pt == pq::BYTE_ARRAY && ck[c].hasDictionary) {
+            const int maxChars = t.kind == TypeKind::VARCHAR ? t.precision : 0;
+            if (!pq::binaryDictionary(in.data, ck[c].dictionaryOff, ck[c].dictionaryEnd, ck[c].dictionaryCount, maxChars, dictOffsets[c], dictBytes[c], why))
+                return fail(p, PGPU_INVALID_ARGUMENT, why + " (channel " + std::to_string(c) + ")");
+        }
+    }
+    if (rows == 0) return PGPU_OK;  // an empty row group adds nothing
+    CU(cudaSetDevice(p->device));
+    // arena layout, every piece 256-byte aligned
+    size_t need = 0;
+    auto reserve = [&](size_t bytes) {
+        const size_t at = need;
+        need += align256(bytes + 16);
+        return at;
+    };
+    struct Placed {
+        size_t chunk = 0, levelRuns = 0, valueRuns = 0, bits = 0, nulls = 0, scratch = 0, compact = 0, values = 0, dict = 0, dictNulls = 0, dictOffsets = 0;
+    };
+    std::vector<Placed> at((size_t)nchunks);
+    for (int c = 0; c < nchunks; c++) {
+        const pq::Chunk& k = ck[c];
+        Placed& q = at[c];
+        const int W = pq::valueWidth(chunks[c].physical_type);  // 0 for BYTE_ARRAY
+        q.chunk = reserve(chunks[c].len);
+        q.valueRuns = reserve(k.valueRuns.size() * sizeof(pq::Run));
+        if (k.hasNulls()) {
+            q.levelRuns = reserve(k.levelRuns.size() * sizeof(pq::Run));
+            q.bits = reserve((size_t)(rows + 7) / 8);
+            q.nulls = reserve((size_t)rows);
+            q.scratch = reserve(serdeScratchWords(rows) * 4);
+        }
+        if (k.allDictionary) {
+            if (k.hasNulls()) q.compact = reserve((size_t)k.nonNull * 4);
+            q.values = reserve((size_t)rows * 4);  // ids
+            const size_t entries = (size_t)k.dictionaryCount + 1;
+            if (W) {
+                q.dict = reserve(entries * W);
+            } else {
+                q.dictOffsets = reserve((entries + 1) * 4);
+                q.dict = reserve(dictBytes[c].size());
+            }
+            q.dictNulls = reserve(entries);
+        } else {
+            if (k.hasNulls()) q.compact = reserve((size_t)k.nonNull * W);
+            q.values = reserve((size_t)rows * W);
+            if (k.anyDictionary) q.dict = reserve((size_t)k.dictionaryCount * W);
+        }
+    }
+    pgpu_status st = ensureDev(p, p->parquetArena, need);
+    if (st) return st;
+    char* base = (char*)p->parquetArena.ptr;
+    std::vector<pgpu_column> cols((size_t)nchunks), dicts((size_t)nchunks);
+    for (int c = 0; c < nchunks; c++) {
+        const pq::Chunk& k = ck[c];
+        const Placed& q = at[c];
+        const Type& t = plan.input[c];
+        const int pt = chunks[c].physical_type;
+        const int W = pq::valueWidth(pt);
+        const size_t len = chunks[c].len;
+        const uint8_t* dchunk = (const uint8_t*)(base + q.chunk);
+        if (len) CU(cudaMemcpyAsync(base + q.chunk, chunks[c].data, len, cudaMemcpyHostToDevice, p->stream));  // the whole chunk in one DMA
+        p->stats.h2d_bytes += (int64_t)len;
+        if (!k.valueRuns.empty()) CU(cudaMemcpyAsync(base + q.valueRuns, k.valueRuns.data(), k.valueRuns.size() * sizeof(pq::Run), cudaMemcpyHostToDevice, p->stream));
+        const PqRun* vruns = (const PqRun*)(base + q.valueRuns);
+        const bool nul = k.hasNulls();
+        if (nul) {
+            CU(cudaMemcpyAsync(base + q.levelRuns, k.levelRuns.data(), k.levelRuns.size() * sizeof(pq::Run), cudaMemcpyHostToDevice, p->stream));
+            CU(pqLevelsToNullBits(p->stream, dchunk, len, (const PqRun*)(base + q.levelRuns), (int64_t)k.levelRuns.size(), rows, (uint8_t*)(base + q.bits)));
+            p->stats.kernel_launches += 1;
+        }
+        // where the non-null values are written: straight into the block when there is no NULL, else into `compact`
+        char* dense = base + (nul ? q.compact : q.values);
+        pgpu_column& col = cols[c];
+        memset(&col, 0, sizeof col);
+        col.type_kind = (int32_t)t.kind;
+        col.precision = t.precision;
+        col.scale = t.scale;
+        col.position_count = rows;
+        if (k.allDictionary) {
+            // ids of the whole chunk in one launch
+            CU(pqExpandRuns(p->stream, dchunk, len, vruns, (int64_t)k.valueRuns.size(), 0, k.nonNull, 4, nullptr, (uint32_t)k.dictionaryCount, dense, p->dErr));
+            p->stats.kernel_launches += 1;
+            if (nul) {
+                CU(expandNulls(p->stream, (const uint8_t*)(base + q.bits), rows, base + q.compact, base + q.values, (uint8_t*)(base + q.nulls), 4, (uint32_t*)(base + q.scratch)));
+                CU(pqNullIds(p->stream, (int32_t*)(base + q.values), (const uint8_t*)(base + q.nulls), rows, (int32_t)k.dictionaryCount));
+                p->stats.kernel_launches += 4;
+            }
+            // the dictionary block: the dictionary page's PLAIN values + one NULL entry
+            pgpu_column& d = dicts[c];
+            memset(&d, 0, sizeof d);
+            d.encoding = PGPU_ENC_PLAIN;
+            d.type_kind = col.type_kind;
+            d.precision = t.precision;
+            d.scale = t.scale;
+            const size_t entries = (size_t)k.dictionaryCount + 1;
+            d.position_count = (int64_t)entries;
+            CU(cudaMemsetAsync(base + q.dictNulls, 0, entries, p->stream));
+            CU(cudaMemsetAsync(base + q.dictNulls + k.dictionaryCount, 1, 1, p->stream));
+            if (nul) d.nulls = (const uint8_t*)(base + q.dictNulls);
+            else d.position_count = k.dictionaryCount ? k.dictionaryCount : 1;
+            if (W) {
+                CU(cudaMemsetAsync(base + q.dict, 0, entries * W, p->stream));
+                if (k.dictionaryCount) CU(cudaMemcpyAsync(base + q.dict, base + q.chunk + k.dictionaryOff, (size_t)k.dictionaryCount * W, cudaMemcpyDeviceToDevice, p->stream));
+                d.values = base + q.dict;
+            } else {
+                std::vector<int32_t>& off = dictOffsets[c];
+                off.push_back(off.back());  // the NULL entry is empty
+                CU(cudaMemcpyAsync(base + q.dictOffsets, off.data(), off.size() * 4, cudaMemcpyHostToDevice, p->stream));
+                if (!dictBytes[c].empty()) CU(cudaMemcpyAsync(base + q.dict, dictBytes[c].data(), dictBytes[c].size(), cudaMemcpyHostToDevice, p->stream));
+                d.offsets = (const int32_t*)(base + q.dictOffsets);
+                d.values = base + q.dict;
+            }
+            col.encoding = PGPU_ENC_DICTIONARY;
+            col.ids = (const int32_t*)(base + q.values);
+            col.dictionary = &d;
+            continue;
+        }
+        col.encoding = PGPU_ENC_PLAIN;
+        col.values = base + q.values;
+        if (pt == pq::BOOLEAN) {
+            CU(pqExpandRuns(p->stream, dchunk, len, vruns, (int64_t)k.valueRuns.size(), 0, k.nonNull, 1, nullptr, 2u, dense, p->dErr));
+            p->stats.kernel_launches += 1;
+        } else {
+            if (k.anyDictionary && k.dictionaryCount)
+                CU(cudaMemcpyAsync(base + q.dict, base + q.chunk + k.dictionaryOff, (size_t)k.dictionaryCount * W, cudaMemcpyDeviceToDevice, p->stream));
+            for (const pq::DataPage& pg : k.pages) {
+                if (!pg.nonNull) continue;
+                char* dst = dense + (size_t)pg.firstValue * W;
+                if (pg.dictionaryEncoded) {  // a chunk that fell back to PLAIN part-way: materialise the dictionary-encoded pages
+                    CU(pqExpandRuns(p->stream, dchunk, len, vruns + pg.runLo, (int64_t)(pg.runHi - pg.runLo), pg.firstValue, pg.nonNull, W, base + q.dict,
+                                    (uint32_t)k.dictionaryCount, dst, p->dErr));
+                    p->stats.kernel_launches += 1;
+                } else {
+                    CU(cudaMemcpyAsync(dst, base + q.chunk + pg.valuesOff, (size_t)pg.nonNull * W, cudaMemcpyDeviceToDevice, p->stream));
+                }
+            }
+        }
+        if (nul) {
+            col.nulls = (const uint8_t*)(base + q.nulls);
+            CU(expandNulls(p->stream, (const uint8_t*)(base + q.bits), rows, base + q.compact, base + q.values, (uint8_t*)(base + q.nulls), W, (uint32_t*)(base + q.scratch)));
+            p->stats.kernel_launches += 3;
+        }
+    }
+    st = addPageCommon(p, cols.data(), nchunks, rows, true, 0);
+    return st ? st : updatePartialFill(p);
+}
+
+// Host-only view of what pgpu_add_parquet_row_group reads from a chunk (no GPU needed): info[0] data pages, [1] dictionary
+// entries (-1: no dictionary page), [2] 1 if every data page is dictionary encoded, [3] non-null values, [4] definition level
+// runs kept (0 when the chunk has no NULL), [5] value runs (ids / booleans), [6] 1 if some page is dictionary encoded, [7] rows.
+pgpu_status pgpu_parquet_inspect_chunk(const pgpu_parquet_chunk* chunk, int64_t* info, char* err, size_t err_len) {
+    if (!chunk || !info) return PGPU_INVALID_ARGUMENT;
+    pq::Chunk k;
+    std::string why;
+    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why)) {
+        if (err && err_len) {
+            strncpy(err, why.c_str(), err_len - 1);
+            err[err_len - 1] = 0;
+        }
+        return why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT;
+    }
+    info[0] = (int64_t)k.pages.size();
+    info[1] = k.hasDictionary ? k.dictionaryCount : -1;
+    info[2] = k.allDictionary ? 1 : 0;
+    info[3] = k.nonNull;
+    info[4] = (int64_t)k.levelRuns.size();
+    info[5] = (int64_t)k.valueRuns.size();
+    info[6] = k.anyDictionary ? 1 : 0;
+    info[7] = k.rows;
+    return PGPU_OK;
+}
+
+// The run tables pgpu_add_parquet_row_group hands to the device kernels (no GPU needed; used by the CPU test-suite to check them
+// against the oracle): which = 0 definition levels, 1 values (dictionary ids / booleans), 2 data pages as
+// {start = firstValue, src = byte offset of the values, count = non-null values, widthPacked = dictionary encoded ? 1 : 0}.
+// Each entry = {int64 start, uint64 src, uint32 count, uint32 width | packed << 31}. *n = entries available.
+pgpu_status pgpu_parquet_chunk_runs(const pgpu_parquet_chunk* chunk, int32_t which, void* out, int64_t cap, int64_t* n) {
+    if (!chunk || !n) return PGPU_INVALID_ARGUMENT;
+    pq::Chunk k;
+    std::string why;
+    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why))
+        return why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT;
+    std::vector<pq::Run> pages;
+    for (const pq::DataPage& pg : k.pages) pages.push_back(pq::Run{pg.firstValue, (uint64_t)pg.valuesOff, (uint32_t)pg.nonNull, pg.dictionaryEncoded ? 1u : 0u});
+    const std::vector<pq::Run>& v = which == 0 ? k.levelRuns : which == 1 ? k.valueRuns : pages;
+    *n = (int64_t)v.size();
+    if (out && cap > 0) memcpy(out, v.data(), (size_t)std::min<int64_t>(cap, *n) * sizeof(pq::Run));
+    return PGPU_OK;
 }
 
 pgpu_status pgpu_finish(pgpu_pipeline* p) {

@@ -122,6 +122,19 @@ class GpuPipelineOperator:
         main/execution/buffer/PagesSerdeUtil.java:45-62); decoded on the device."""
         self._check(self._lib.pgpu_add_serialized_page(self._h, payload, len(payload), positionCount))
 
+    def addParquetRowGroup(self, chunks, rows: int):
+        """addInput of the Page the reference's ParquetReader.nextPage would build from one row group
+        (lib/trino-parquet/.../reader/ParquetReader.java:211-268): chunks[c] = (column chunk bytes as they lie in the file,
+        uncompressed; parquet physical type; max definition level; num_values) feeds input channel c. Page and run headers are
+        read on the host, everything else is decoded on the device (pgpu_add_parquet_row_group)."""
+        arr = (N.ParquetChunk * len(chunks))()
+        keep = []
+        for i, (data, ptype, max_def, num_values) in enumerate(chunks):
+            data = bytes(data)
+            keep.append(data)
+            arr[i].data, arr[i].len, arr[i].physical_type, arr[i].max_definition_level, arr[i].num_values = data, len(data), ptype, max_def, num_values
+        self._check(self._lib.pgpu_add_parquet_row_group(self._h, arr, len(chunks), rows))
+
     def getSerializedOutput(self):
         """getOutput() in the reference's wire format: (payload bytes, positionCount) or None."""
         data, n, rows = ctypes.c_void_p(), ctypes.c_size_t(), ctypes.c_int64()

@@ -1,0 +1,205 @@
+"""Host side of the Parquet ingest (csrc/parquet_host.h, through pgpu_parquet_inspect_chunk: no GPU): page headers, dictionary
+pages, non-null counts from the definition-level runs and the dictionary / plain classification must agree with the oracle
+(oracle/parquet_pages.py, itself pinned against pyarrow) on the golden files and on live pyarrow output; malformed chunks are
+rejected, never crash."""
+import ctypes
+import io
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+import parquet_pages as PP  # noqa: E402
+from parquet_util import GOLDEN, chunks_of  # noqa: E402
+from presto_b200 import _native as N  # noqa: E402
+
+
+def inspect(buf, ptype, max_def, num_values):
+    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values)
+    info = (ctypes.c_int64 * 8)()
+    err = ctypes.create_string_buffer(512)
+    st = N.lib().pgpu_parquet_inspect_chunk(ctypes.byref(c), info, err, 512)
+    return st, list(info), err.value.decode()
+
+
+RUN = np.dtype([("start", "<i8"), ("src", "<u8"), ("count", "<u4"), ("width", "<u4")])
+
+
+def runs_of(buf, ptype, max_def, num_values, which):
+    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values)
+    n = ctypes.c_int64()
+    assert N.lib().pgpu_parquet_chunk_runs(ctypes.byref(c), which, None, 0, ctypes.byref(n)) == N.OK
+    out = np.zeros(n.value, RUN)
+    if n.value:
+        assert N.lib().pgpu_parquet_chunk_runs(ctypes.byref(c), which, out.ctypes.data, n.value, ctypes.byref(n)) == N.OK
+    return out
+
+
+def expand(buf, runs, first, count):
+    """numpy statement of the device kernel (parquet.cu k_pq_expand / codeAt): value index -> run by binary search -> code"""
+    raw = np.frombuffer(bytes(buf) + b"\0" * 8, np.uint8)
+    idx = first + np.arange(count, dtype=np.int64)
+    ri = np.searchsorted(runs["start"], idx, side="right") - 1
+    assert (ri >= 0).all()
+    r = runs[ri]
+    assert (idx < r["start"] + r["count"].astype(np.int64)).all(), "run table has gaps"
+    width = (r["width"] & 0xFF).astype(np.uint64)
+    packed = (r["width"] >> 31) != 0
+    bit = r["src"] + (idx - r["start"]).astype(np.uint64) * width
+    byte = np.minimum((bit >> np.uint64(3)).astype(np.int64), len(raw) - 8)
+    w = np.zeros(count, np.uint64)
+    for b in range(5):
+        w |= raw[byte + b].astype(np.uint64) << np.uint64(8 * b)
+    mask = (np.uint64(1) << width) - np.uint64(1)
+    code = (w >> (bit & np.uint64(7))) & mask
+    return np.where(packed, code, r["src"]).astype(np.uint32)
+
+
+def check_runs(name, buf, ptype, max_def, nvals, nulls, o):
+    levels = runs_of(buf, ptype, max_def, nvals, 0)
+    if nulls.any():
+        assert np.array_equal(expand(buf, levels, 0, nvals) == 0, nulls.astype(bool)), name
+    else:
+        assert len(levels) == 0
+    nn = int((nulls == 0).sum())
+    values = runs_of(buf, ptype, max_def, nvals, 1)
+    pages = runs_of(buf, ptype, max_def, nvals, 2)
+    assert int(pages["count"].sum()) == nn
+    if o["all_dictionary"]:
+        assert np.array_equal(expand(buf, values, 0, nn).astype(np.int32), o["ids"][nulls == 0]), name
+    elif ptype == PP.BOOLEAN:
+        got = expand(buf, values, 0, nn)
+        want, _, _ = PP.decode_chunk(buf, ptype, max_def, nvals)
+        assert np.array_equal(got, np.asarray(want)[nulls == 0]), name
+    else:  # plain / mixed fixed-width chunk: page by page, as the ingest copies or gathers them
+        want, _, _ = PP.decode_chunk(buf, ptype, max_def, nvals)
+        dense = np.asarray(want)[nulls == 0]
+        dt = dense.dtype
+        for pg in pages:
+            a, c = int(pg["start"]), int(pg["count"])
+            if pg["width"] & 1:
+                page_runs = values[(values["start"] >= a) & (values["start"] < a + c)]
+                got = np.asarray(o["dictionary"])[expand(buf, page_runs, a, c)]
+            else:
+                got = np.frombuffer(bytes(buf), dt, c, int(pg["src"]))
+            assert np.array_equal(got.view(np.uint8), dense[a:a + c].view(np.uint8)), name
+
+
+def check_against_oracle(path_or_bytes):
+    n = 0
+    for rows, cols in chunks_of(path_or_bytes):
+        for name, (buf, ptype, max_def, nvals) in cols.items():
+            st, info, err = inspect(buf, ptype, max_def, nvals)
+            try:
+                _, nulls, o = PP.decode_chunk(buf, ptype, max_def, nvals)
+            except PP.Unsupported:
+                assert st == N.NOT_SUPPORTED, (name, err)
+                continue
+            if ptype == PP.BYTE_ARRAY and not o["all_dictionary"]:
+                assert st == N.NOT_SUPPORTED and "dictionary" in err or "BYTE_ARRAY" in err, (name, err)
+                continue
+            assert st == N.OK, (name, err)
+            data_pages = [p for p in o["pages"] if p[0] != "dictionary"]
+            assert info[0] == len(data_pages), name
+            assert info[1] == (len(o["dictionary"]) if o["dictionary"] is not None else -1), name
+            assert info[2] == int(o["all_dictionary"]), name
+            assert info[3] == int((nulls == 0).sum()), name
+            assert (info[4] == 0) == (int(nulls.sum()) == 0), name
+            assert info[7] == rows
+            check_runs(name, buf, ptype, max_def, nvals, nulls, o)
+            n += 1
+    return n
+
+
+def test_golden_files():
+    assert check_against_oracle(os.path.join(GOLDEN, "lineitem_v1.parquet")) == 16
+    assert check_against_oracle(os.path.join(GOLDEN, "nullable_v2.parquet")) == 7
+
+
+@pytest.mark.parametrize("version,page_size,dict_cols", [("1.0", 64, True), ("2.0", 1 << 20, True), ("1.0", 300, False), ("2.0", 97, ["flag", "runs"])])
+def test_live_pyarrow_files(version, page_size, dict_cols):
+    pytest.importorskip("pyarrow")
+    import pyarrow.parquet as pq
+    sys.path.insert(0, GOLDEN)
+    import make_parquet_fixtures as M
+    for table in (M.nullable_table(777, seed=21), M.lineitem_table(1501, seed=22)):
+        buf = io.BytesIO()
+        pq.write_table(table, buf, compression="NONE", data_page_version=version, data_page_size=page_size, use_dictionary=dict_cols,
+                       write_statistics=True, row_group_size=500, write_batch_size=37)
+        assert check_against_oracle(buf.getvalue()) > 0
+
+
+def test_compressed_pages_are_rejected():
+    pytest.importorskip("pyarrow")
+    import pyarrow.parquet as pq
+    sys.path.insert(0, GOLDEN)
+    import make_parquet_fixtures as M
+    buf = io.BytesIO()
+    pq.write_table(M.lineitem_table(3000, seed=3), buf, compression="SNAPPY")
+    rows, cols = chunks_of(buf.getvalue())[0]
+    b, pt, md, n = cols["extendedprice"]
+    st, _, err = inspect(b, pt, md, n)
+    assert st == N.NOT_SUPPORTED and "compressed" in err
+
+
+def test_rejections_and_corruption():
+    rows, cols = chunks_of(os.path.join(GOLDEN, "nullable_v2.parquet"))[0]
+    b, pt, md, n = cols["runs"]
+    assert inspect(b, pt, md, n)[0] == N.OK
+    st, _, err = inspect(b, pt, 3, n)
+    assert st == N.NOT_SUPPORTED and "nested" in err
+    st, _, err = inspect(b, 3, md, n)          # INT96
+    assert st == N.NOT_SUPPORTED and "physical type" in err
+    st, _, err = inspect(b, pt, md, n + 1)
+    assert st == N.INVALID_ARGUMENT and "ends after" in err
+    st, _, err = inspect(b[:len(b) * 2 // 3], pt, md, n)
+    assert st == N.INVALID_ARGUMENT
+    st, _, err = inspect(b"", pt, md, 5)
+    assert st == N.INVALID_ARGUMENT
+    assert inspect(b"", pt, md, 0)[0] == N.OK
+    # a data page before the dictionary page's ids can be resolved: drop the dictionary page
+    h, body = PP.read_page_header(bytes(b), 0)
+    assert h["type"] == PP.PAGE_DICTIONARY
+    st, _, err = inspect(b[body + h["compressed_size"]:], pt, md, n)
+    assert st == N.INVALID_ARGUMENT and "Dictionary is missing" in err
+
+
+def test_fuzzed_chunks_never_crash():
+    rng = np.random.default_rng(99)
+    for fname in ("nullable_v2.parquet", "lineitem_v1.parquet"):
+        for rows, cols in chunks_of(os.path.join(GOLDEN, fname)):
+            for name, (b, pt, md, n) in cols.items():
+                raw = np.frombuffer(b, np.uint8)
+                for trial in range(60):
+                    x = raw.copy()
+                    k = int(rng.integers(1, 4))
+                    x[rng.integers(0, min(len(x), 64 if trial % 2 else len(x)), k)] = rng.integers(0, 256, k)
+                    cut = len(x) if trial % 3 else int(rng.integers(0, len(x)))
+                    st, info, err = inspect(x[:cut].tobytes(), pt, md, n)
+                    assert st in (N.OK, N.NOT_SUPPORTED, N.INVALID_ARGUMENT)
+                    if st == N.OK:
+                        assert 0 <= info[3] <= n and info[7] == n
+
+
+def test_dictionary_fallback_to_plain_mid_chunk():
+    """a writer whose dictionary page outgrows its limit continues the chunk with PLAIN pages: both kinds in one chunk"""
+    pa = pytest.importorskip("pyarrow")
+    import pyarrow.parquet as pq
+    rng = np.random.default_rng(4)
+    n = 5000
+    keys = np.concatenate([rng.integers(0, 20, n // 2), rng.integers(0, 1 << 40, n - n // 2)]).astype(np.int64)
+    t = pa.table({"k": pa.array(keys, mask=rng.random(n) < 0.1), "d": pa.array(keys.astype(np.float64) * 0.5)})
+    buf = io.BytesIO()
+    pq.write_table(t, buf, compression="NONE", use_dictionary=True, dictionary_pagesize_limit=2048, data_page_size=1024, write_batch_size=100,
+                   data_page_version="1.0")
+    kinds = set()
+    for rows, cols in chunks_of(buf.getvalue()):
+        for name, (b, pt, md, nv) in cols.items():
+            _, _, info = PP.decode_chunk(b, pt, md, nv)
+            kinds |= {(p[0], p[2]) for p in info["pages"] if p[0] != "dictionary"}
+    assert ("data", PP.ENC_PLAIN) in kinds and (("data", PP.ENC_RLE_DICTIONARY) in kinds or ("data", PP.ENC_PLAIN_DICTIONARY) in kinds)
+    sys.path.insert(0, GOLDEN)
+    import make_parquet_fixtures as M
+    assert check_against_oracle(buf.getvalue()) > 0

@@ -88,3 +88,25 @@ def test_rejections():
         PP.decode_chunk(buf[:len(buf) // 2], ptype, max_def, n)
     with pytest.raises(PP.Corrupt):
         PP.decode_chunk(buf, ptype, max_def, n + 5)
+
+
+def test_dictionary_fallback_to_plain_mid_chunk():
+    """a writer whose dictionary page outgrows its limit continues the chunk with PLAIN pages: both kinds in one chunk"""
+    pa = pytest.importorskip("pyarrow")
+    import pyarrow.parquet as pq
+    rng = np.random.default_rng(4)
+    n = 5000
+    keys = np.concatenate([rng.integers(0, 20, n // 2), rng.integers(0, 1 << 40, n - n // 2)]).astype(np.int64)
+    t = pa.table({"k": pa.array(keys, mask=rng.random(n) < 0.1), "d": pa.array(keys.astype(np.float64) * 0.5)})
+    buf = io.BytesIO()
+    pq.write_table(t, buf, compression="NONE", use_dictionary=True, dictionary_pagesize_limit=2048, data_page_size=1024, write_batch_size=100,
+                   data_page_version="1.0")
+    kinds = set()
+    for rows, cols in chunks_of(buf.getvalue()):
+        for name, (b, pt, md, nv) in cols.items():
+            _, _, info = PP.decode_chunk(b, pt, md, nv)
+            kinds |= {(p[0], p[2]) for p in info["pages"] if p[0] != "dictionary"}
+    assert ("data", PP.ENC_PLAIN) in kinds and (("data", PP.ENC_RLE_DICTIONARY) in kinds or ("data", PP.ENC_PLAIN_DICTIONARY) in kinds)
+    sys.path.insert(0, GOLDEN)
+    import make_parquet_fixtures as M
+    check_file(buf.getvalue(), M.expected(pq.read_table(io.BytesIO(buf.getvalue()))))
