@@ -32,3 +32,43 @@ def chunks_of(path):
 def expected_of(name):
     z = np.load(os.path.join(GOLDEN, name + ".expected.npz"), allow_pickle=False)
     return {k: z[k] for k in z.files}
+
+
+# ---- hand-built chunks (Thrift compact page headers written field by field) ---------------------------------------------------
+def _varint(v):
+    out = bytearray()
+    while True:
+        if v < 0x80:
+            out.append(v)
+            return bytes(out)
+        out.append((v & 0x7F) | 0x80)
+        v >>= 7
+
+
+def _zz(v):
+    return _varint((v << 1) ^ (v >> 63))
+
+
+def page_header(page_type, size, num_values, encoding):
+    """parquet.thrift PageHeader for a dictionary page (type 2) or a v1 data page (type 0; RLE levels)"""
+    h = b"\x15" + _zz(page_type) + b"\x15" + _zz(size) + b"\x15" + _zz(size)
+    if page_type == 2:
+        return h + b"\x4c" + b"\x15" + _zz(num_values) + b"\x15" + _zz(encoding) + b"\x00" + b"\x00"
+    return h + b"\x2c" + b"\x15" + _zz(num_values) + b"\x15" + _zz(encoding) + b"\x15" + _zz(3) + b"\x15" + _zz(3) + b"\x00" + b"\x00"
+
+
+def bit_packed(values, width):
+    """one bit-packed hybrid run (header + groups of 8, least significant bit first)"""
+    groups = (len(values) + 7) // 8
+    bits = np.zeros(groups * 8 * width, np.uint8)
+    for i, v in enumerate(values):
+        for b in range(width):
+            bits[i * width + b] = (v >> b) & 1
+    return _varint((groups << 1) | 1) + np.packbits(bits, bitorder="little").tobytes()
+
+
+def dictionary_chunk(dictionary, ids, width):
+    """required INT64 column: PLAIN dictionary page + one RLE_DICTIONARY v1 data page whose ids are one bit-packed run"""
+    d = np.asarray(dictionary, "<i8").tobytes()
+    body = bytes([width]) + bit_packed(ids, width)
+    return page_header(2, len(d), len(dictionary), 0) + d + page_header(0, len(body), len(ids), 8) + body

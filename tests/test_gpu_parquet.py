@@ -1,0 +1,180 @@
+"""Parquet column chunks through pgpu_add_parquet_row_group on the GPU against (a) what pyarrow's reader returns for the same
+files (tests/golden/*.expected.npz), (b) the CPU oracle operator fed with plain pages of those values, and (c) the GPU path
+itself fed with the same plain pages. Bit-exact: identity projections return the file's values; aggregates over exact data."""
+import io
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from parquet_util import GOLDEN, chunks_of, dictionary_chunk, expected_of
+from presto_b200 import tpch
+from presto_b200.operators import Aggregation, GpuPipelineOperator, TrinoException, plan_text
+from presto_b200.relational import compare, constant, field
+from presto_b200.spi import (BIGINT, BOOLEAN, DATE, DOUBLE, INTEGER, ByteArrayBlock, IntArrayBlock, LongArrayBlock, Page, VariableWidthBlock,
+                             createVarcharType)
+from util import assert_rows_equal_ignore_order, assert_rows_equal_ordered, rows_of, run_gpu, run_oracle, sequential_bound
+
+pytestmark = pytest.mark.gpu
+V1, V3 = createVarcharType(1), createVarcharType(3)
+NULLABLE = [("k", BIGINT), ("runs", INTEGER), ("x", DOUBLE), ("flag", V3), ("b", BOOLEAN), ("allnull", BIGINT), ("big", BIGINT)]
+
+
+def run_parquet(plan, groups, columns, device=0):
+    """groups = chunks_of(file); columns = parquet column names in plan channel order"""
+    op = GpuPipelineOperator(plan, device)
+    out = []
+    try:
+        for rows, cols in groups:
+            assert op.needsInput()
+            op.addParquetRowGroup([cols[c] for c in columns], rows)
+            p = op.getOutput()
+            if p is not None and p.position_count:
+                out.append(p)
+        op.finish()
+        while not op.isFinished():
+            p = op.getOutput()
+            if p is not None and p.position_count:
+                out.append(p)
+        return rows_of(out), op.stats()
+    finally:
+        op.close()
+
+
+def plain_block(t, values, nulls):
+    nn = nulls.astype(np.uint8) if nulls.any() else None
+    if t.is_var_width:
+        return VariableWidthBlock.from_values(t, [None if z else str(v) for v, z in zip(values, nulls)])
+    if t.kind == 0:
+        return ByteArrayBlock(t, values.astype(np.int8), nn)
+    if t.kind in (2, 3):
+        return IntArrayBlock(t, values.astype(np.int32), nn)
+    if t.kind == 4:
+        return LongArrayBlock(t, values.astype(np.float64), nn)
+    return LongArrayBlock(t, values.astype(np.int64), nn)
+
+
+def plain_pages(exp, schema, row_counts):
+    pages, at = [], 0
+    for n in row_counts:
+        pages.append(Page(*[plain_block(t, exp[c + ".values"][at:at + n], exp[c + ".nulls"][at:at + n]) for c, t in schema]))
+        at += n
+    return pages
+
+
+def test_identity_projection_returns_the_files_values():
+    """every decode path at once: required / optional columns, dictionary ids with a NULL entry, RLE + bit-packed runs, PLAIN
+    doubles with NULLs, RLE booleans, an all-NULL column, data page v2"""
+    groups = chunks_of(os.path.join(GOLDEN, "nullable_v2.parquet"))
+    exp = expected_of("nullable_v2")
+    types = [t for _, t in NULLABLE]
+    plan = plan_text(types, None, [field(i, t) for i, t in enumerate(types)])
+    got, st = run_parquet(plan, groups, [c for c, _ in NULLABLE])
+    want = rows_of(plain_pages(exp, NULLABLE, [g[0] for g in groups]))
+    assert len(want) == 1000
+    assert_rows_equal_ordered(got, want)
+    assert st.kernel_launches > len(NULLABLE)
+
+
+def test_aggregation_over_nullable_chunks_equals_oracle():
+    groups = chunks_of(os.path.join(GOLDEN, "nullable_v2.parquet"))
+    exp = expected_of("nullable_v2")
+    types = [t for _, t in NULLABLE]
+    plan = plan_text(types, compare("ge", field(0, BIGINT), constant(-400, BIGINT)), [field(3, V3), field(1, INTEGER), field(2, DOUBLE), field(6, BIGINT), field(4, BOOLEAN)],
+                     step="single", groupByChannels=[0, 1],
+                     aggregations=[Aggregation("count", BIGINT), Aggregation("count", BIGINT, 2, DOUBLE), Aggregation("min", DOUBLE, 2, DOUBLE),
+                                   Aggregation("max", BIGINT, 3, BIGINT), Aggregation("min", BOOLEAN, 4, BOOLEAN)], expectedGroups=64)
+    got, _ = run_parquet(plan, groups, [c for c, _ in NULLABLE])
+    pages = plain_pages(exp, NULLABLE, [g[0] for g in groups])
+    assert_rows_equal_ignore_order(got, run_oracle(plan, pages), nkeys=2)
+    assert_rows_equal_ignore_order(got, run_gpu(plan, pages), nkeys=2)
+
+
+LINEITEM = {"returnflag": V1, "linestatus": V1, "quantity": DOUBLE, "extendedprice": DOUBLE, "discount": DOUBLE, "tax": DOUBLE, "shipdate": DATE,
+            "orderkey": BIGINT}
+
+
+@pytest.mark.parametrize("plan,columns,nkeys", [
+    (tpch.q1_plan(), ["returnflag", "linestatus", "quantity", "extendedprice", "discount", "tax", "shipdate"], 2),
+    (tpch.q6_plan(), ["extendedprice", "discount", "shipdate", "quantity"], None),
+    (tpch.highcard_plan(1000), ["orderkey", "quantity"], 1)], ids=["q1", "q6", "highcard"])
+def test_tpch_plans_over_lineitem_row_groups(plan, columns, nkeys):
+    """Q1 / Q6 / GROUP BY orderkey straight off Parquet row groups (dictionary-encoded flag, discount, tax, quantity chunks reach
+    the kernels as DictionaryBlocks) = the same plans over plain pages of the values pyarrow reads"""
+    groups = chunks_of(os.path.join(GOLDEN, "lineitem_v1.parquet"))
+    exp = expected_of("lineitem_v1")
+    got, _ = run_parquet(plan, groups, columns)
+    pages = plain_pages(exp, [(c, LINEITEM[c]) for c in columns], [g[0] for g in groups])
+    rtol = sequential_bound(600)
+    assert_rows_equal_ignore_order(got, run_oracle(plan, pages), nkeys=nkeys, rtol=rtol)
+    assert_rows_equal_ignore_order(got, run_gpu(plan, pages), nkeys=nkeys, rtol=rtol)
+
+
+def test_large_row_group_size_independent_properties():
+    """1.2 M rows written by pyarrow (dictionary chunk that falls back to PLAIN, many pages): count, exact integer sums and the
+    number of groups are known in closed form"""
+    pa = pytest.importorskip("pyarrow")
+    import pyarrow.parquet as pq
+    n = 1_200_000
+    k = (np.arange(n, dtype=np.int64) * 7919) % 100_003
+    v = (np.arange(n, dtype=np.int64) % 1000).astype(np.float64)
+    t = pa.table({"k": pa.array(k, mask=(np.arange(n) % 97 == 0)), "v": pa.array(v)})
+    buf = io.BytesIO()
+    pq.write_table(t, buf, compression="NONE", use_dictionary=["k"], dictionary_pagesize_limit=1 << 16, row_group_size=500_000, data_page_version="2.0")
+    groups = chunks_of(buf.getvalue())
+    plan = plan_text([BIGINT, DOUBLE], step="single", groupByChannels=[0], aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE), Aggregation("count", BIGINT)],
+                     expectedGroups=200_000)
+    got, _ = run_parquet(plan, groups, ["k", "v"])
+    mask = np.arange(n) % 97 == 0
+    assert len(got) == len(np.unique(k[~mask])) + 1
+    assert sum(r[2] for r in got) == n
+    assert sum(r[1] for r in got) == float(v.sum())
+    null_row = [r for r in got if r[0] is None]
+    assert len(null_row) == 1 and null_row[0][2] == int(mask.sum()) and null_row[0][1] == float(v[mask].sum())
+
+
+def test_rejected_and_corrupt_chunks_raise():
+    groups = chunks_of(os.path.join(GOLDEN, "lineitem_v1.parquet"))
+    rows, cols = groups[0]
+    op = GpuPipelineOperator(tpch.q6_plan(), 0)
+    try:
+        with pytest.raises(TrinoException) as e:   # a DOUBLE channel fed with the INT64 chunk
+            op.addParquetRowGroup([cols["orderkey"], cols["discount"], cols["shipdate"], cols["quantity"]], rows)
+        assert e.value.code == "NOT_SUPPORTED"
+        b, pt, md, n = cols["extendedprice"]
+        with pytest.raises(TrinoException) as e:
+            op.addParquetRowGroup([(b[:len(b) // 2], pt, md, n), cols["discount"], cols["shipdate"], cols["quantity"]], rows)
+        assert e.value.code != "NOT_SUPPORTED"
+    finally:
+        op.close()
+
+
+def test_dictionary_id_out_of_range_is_caught_on_the_device():
+    """a page that points past its dictionary (PrimitiveColumnReader would throw from Dictionary.decodeToLong): the kernel flags it,
+    the operator reports it where device faults surface"""
+    plan = plan_text([BIGINT], step="single", aggregations=[Aggregation("sum", BIGINT, 0, BIGINT), Aggregation("count", BIGINT)])
+    good = dictionary_chunk([10, 20, 30], [0, 1, 2, 2, 1, 0, 0, 2, 1, 1, 2], 2)
+    op = GpuPipelineOperator(plan, 0)
+    try:
+        op.addParquetRowGroup([(good, 2, 0, 11)], 11)
+        op.finish()
+        out = []
+        while not op.isFinished():
+            p = op.getOutput()
+            if p is not None:
+                out.append(p)
+        assert rows_of(out) == [(10 * 3 + 20 * 4 + 30 * 4, 11)]
+    finally:
+        op.close()
+    bad = dictionary_chunk([10, 20, 30], [0, 1, 2, 3, 1, 0, 0, 2, 1, 1, 2], 2)   # id 3 of a 3-entry dictionary
+    op = GpuPipelineOperator(plan, 0)
+    try:
+        with pytest.raises(TrinoException) as e:
+            op.addParquetRowGroup([(bad, 2, 0, 11)], 11)
+            op.finish()
+            while not op.isFinished():
+                op.getOutput()
+        assert "dictionary id" in str(e.value)
+    finally:
+        op.close()

@@ -12,7 +12,7 @@ import pytest
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
 import parquet_pages as PP  # noqa: E402
-from parquet_util import GOLDEN, chunks_of  # noqa: E402
+from parquet_util import GOLDEN, chunks_of, dictionary_chunk  # noqa: E402
 from presto_b200 import _native as N  # noqa: E402
 
 
@@ -203,3 +203,11 @@ def test_dictionary_fallback_to_plain_mid_chunk():
     sys.path.insert(0, GOLDEN)
     import make_parquet_fixtures as M
     assert check_against_oracle(buf.getvalue()) > 0
+
+
+def test_hand_built_dictionary_chunk():
+    ids = [0, 1, 2, 2, 1, 0, 0, 2, 1, 1, 2]
+    buf = dictionary_chunk([10, 20, 30], ids, 2)
+    st, info, err = inspect(buf, PP.INT64, 0, len(ids))
+    assert st == N.OK and info[:4] == [1, 3, 1, 11] and info[4] == 0 and info[5] == 1, (info, err)
+    assert expand(buf, runs_of(buf, PP.INT64, 0, len(ids), 1), 0, len(ids)).tolist() == ids

@@ -10,7 +10,7 @@ import pytest
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
 import parquet_pages as PP  # noqa: E402
-from parquet_util import GOLDEN, chunks_of, expected_of  # noqa: E402
+from parquet_util import GOLDEN, chunks_of, dictionary_chunk, expected_of  # noqa: E402
 
 
 def check_file(path_or_bytes, exp):
@@ -110,3 +110,13 @@ def test_dictionary_fallback_to_plain_mid_chunk():
     sys.path.insert(0, GOLDEN)
     import make_parquet_fixtures as M
     check_file(buf.getvalue(), M.expected(pq.read_table(io.BytesIO(buf.getvalue()))))
+
+
+def test_hand_built_dictionary_chunk():
+    """a chunk assembled byte by byte from the format description (parquet_util.dictionary_chunk): what the oracle must read"""
+    ids = [0, 1, 2, 2, 1, 0, 0, 2, 1, 1, 2]
+    buf = dictionary_chunk([10, 20, 30], ids, 2)
+    values, nulls, info = PP.decode_chunk(buf, PP.INT64, 0, len(ids))
+    assert values.tolist() == [[10, 20, 30][i] for i in ids] and not nulls.any() and info["all_dictionary"]
+    with pytest.raises(PP.Corrupt):
+        PP.decode_chunk(dictionary_chunk([10, 20, 30], [0, 3, 1], 2), PP.INT64, 0, 3)

@@ -56,6 +56,7 @@ def patch():
     cls.addInput = add_input
     cls.addDeviceInput = add_device_input
     cls.addSerializedInput = lambda self, payload, n: None
+    cls.addParquetRowGroup = lambda self, chunks, rows: None
     cls.getOutput = lambda self: None
     cls.getSerializedOutput = lambda self: None
     cls.needsInput = lambda self: not self._done
