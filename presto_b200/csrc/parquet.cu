@@ -48,20 +48,33 @@ __global__ void __launch_bounds__(kThreads) k_pq_null_bits(const uint8_t* chunk,
     }
 }
 
+// Each thread expands kPer consecutive values: one binary search for the first, then a walk along the run table (a run holds
+// >= 8 values unless it is a short RLE run), so the search cost is shared and a warp writes kPer * 32 consecutive outputs.
+constexpr int kPer = 4;
+
 template <typename OUT, bool GATHER>
 __global__ void __launch_bounds__(kThreads) k_pq_expand(const uint8_t* chunk, size_t chunkLen, const PqRun* runs, int64_t nruns, int64_t first, int64_t count,
                                                         const OUT* dict, uint32_t limit, OUT* out, uint32_t* err) {
     bool bad = false;
-    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < count; i += (int64_t)gridDim.x * kThreads) {
-        const int64_t idx = first + i;
-        const int64_t ri = findRun(runs, nruns, idx);
-        uint32_t code = codeAt(chunk, chunkLen, runs[ri < 0 ? 0 : ri], idx);
-        if (code >= limit) {
-            bad = true;
-            code = 0;
+    const int64_t tiles = (count + kPer - 1) / kPer;
+    for (int64_t t = (int64_t)blockIdx.x * kThreads + threadIdx.x; t < tiles; t += (int64_t)gridDim.x * kThreads) {
+        int64_t i = t * kPer;
+        int64_t ri = findRun(runs, nruns, first + i);
+        if (ri < 0) ri = 0;
+        PqRun r = runs[ri];
+#pragma unroll
+        for (int k = 0; k < kPer; k++, i++) {
+            if (i >= count) break;
+            const int64_t idx = first + i;
+            while (idx >= r.start + (int64_t)r.count && ri + 1 < nruns) r = runs[++ri];
+            uint32_t code = codeAt(chunk, chunkLen, r, idx);
+            if (code >= limit) {
+                bad = true;
+                code = 0;
+            }
+            if (GATHER) out[i] = limit ? dict[code] : OUT(0);
+            else out[i] = (OUT)code;
         }
-        if (GATHER) out[i] = limit ? dict[code] : OUT(0);
-        else out[i] = (OUT)code;
     }
     if (bad) atomicOr(err, kPqErrBadId);
 }
@@ -87,7 +100,7 @@ cudaError_t pqLevelsToNullBits(cudaStream_t stream, const uint8_t* chunk, size_t
 cudaError_t pqExpandRuns(cudaStream_t stream, const uint8_t* chunk, size_t chunkLen, const PqRun* runs, int64_t nruns, int64_t first, int64_t count, int outWidth,
                          const void* dict, uint32_t limit, void* out, uint32_t* err) {
     if (count <= 0) return cudaSuccess;
-    const int g = gridFor(count);
+    const int g = gridFor((count + kPer - 1) / kPer);
     if (dict) {
         if (outWidth == 8) k_pq_expand<uint64_t, true><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, (const uint64_t*)dict, limit, (uint64_t*)out, err);
         else if (outWidth == 4) k_pq_expand<uint32_t, true><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, (const uint32_t*)dict, limit, (uint32_t*)out, err);

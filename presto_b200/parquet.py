@@ -1,0 +1,39 @@
+"""Row groups of a Parquet file as the column chunks pgpu_add_parquet_row_group takes.
+
+The footer (FileMetaData: schema, row groups, chunk offsets) is read with pyarrow — the reference reads it with
+MetadataReader.readFooter (lib/trino-parquet/src/main/java/io/trino/parquet/reader/MetadataReader.java:95-140) and a Trino
+integration would hand the same numbers over from its own ParquetMetadata. The column chunk itself is sliced out of the file
+untouched, [starting position, + total size), exactly as ParquetReader.readColumnChunk does (.../reader/ParquetReader.java:
+244-268); nothing in it is decoded here."""
+import io
+from typing import Dict, Iterator, List, Tuple, Union
+
+PHYSICAL = {"BOOLEAN": 0, "INT32": 1, "INT64": 2, "INT96": 3, "FLOAT": 4, "DOUBLE": 5, "BYTE_ARRAY": 6, "FIXED_LEN_BYTE_ARRAY": 7}  # parquet.thrift Type
+Chunk = Tuple[bytes, int, int, int]   # (chunk bytes, physical type, max definition level, num_values)
+
+
+def row_groups(source: Union[str, bytes]) -> Iterator[Tuple[int, Dict[str, Chunk]]]:
+    """-> (row count, {column path: chunk}) per row group of the file (a path or the file's bytes)"""
+    import pyarrow.parquet as pq
+    data = open(source, "rb").read() if isinstance(source, str) else bytes(source)
+    md = pq.ParquetFile(io.BytesIO(data)).metadata
+    for g in range(md.num_row_groups):
+        rg = md.row_group(g)
+        cols: Dict[str, Chunk] = {}
+        for j in range(rg.num_columns):
+            c = rg.column(j)
+            start = c.data_page_offset
+            if c.has_dictionary_page and c.dictionary_page_offset:
+                start = min(start, c.dictionary_page_offset)
+            cols[c.path_in_schema] = (data[start:start + c.total_compressed_size], PHYSICAL[c.physical_type], md.schema.column(j).max_definition_level, c.num_values)
+        yield rg.num_rows, cols
+
+
+def add_file(operator, source: Union[str, bytes], columns: List[str]) -> int:
+    """addInput of every row group of a file (columns = column paths in the plan's channel order); -> rows added.
+    The caller drains getOutput() between calls if the plan can fill up (partial aggregation limits)."""
+    total = 0
+    for rows, cols in row_groups(source):
+        operator.addParquetRowGroup([cols[c] for c in columns], rows)
+        total += rows
+    return total
