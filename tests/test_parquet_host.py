@@ -211,3 +211,37 @@ def test_hand_built_dictionary_chunk():
     st, info, err = inspect(buf, PP.INT64, 0, len(ids))
     assert st == N.OK and info[:4] == [1, 3, 1, 11] and info[4] == 0 and info[5] == 1, (info, err)
     assert expand(buf, runs_of(buf, PP.INT64, 0, len(ids), 1), 0, len(ids)).tolist() == ids
+
+
+def test_plans_of_the_gpu_suite_compile_for_the_signatures_the_ingest_produces():
+    """the page signatures pgpu_add_parquet_row_group hands to the kernels (dictionary / plain, with or without a NULL vector)
+    for the golden files, compiled for sm_100a without a GPU (also warms the in-tree kernel cache for the GPU box)"""
+    from presto_b200 import tpch
+    from presto_b200.operators import GpuPipelineOperator
+    import test_gpu_parquet as G
+
+    def signature(cols, names):
+        enc, nullable = [], []
+        for c in names:
+            st, info, err = inspect(*cols[c])
+            assert st == N.OK, err
+            enc.append(1 if info[2] else 0)
+            nullable.append(info[4] > 0)
+        return enc, nullable
+
+    from presto_b200.operators import plan_text
+    from presto_b200.relational import field
+    types = [t for _, t in G.NULLABLE]
+    jobs = [(plan_text(types, None, [field(i, t) for i, t in enumerate(types)]), "nullable_v2.parquet", [c for c, _ in G.NULLABLE]),
+            (tpch.q1_plan(), "lineitem_v1.parquet", ["returnflag", "linestatus", "quantity", "extendedprice", "discount", "tax", "shipdate"]),
+            (tpch.q6_plan(), "lineitem_v1.parquet", ["extendedprice", "discount", "shipdate", "quantity"]),
+            (tpch.highcard_plan(1000), "lineitem_v1.parquet", ["orderkey", "quantity"])]
+    for plan, fname, names in jobs:
+        op = GpuPipelineOperator(plan, device=-1)
+        try:
+            for rows, cols in chunks_of(os.path.join(GOLDEN, fname)):
+                enc, nullable = signature(cols, names)
+                op.compileSignature(enc, nullable)
+            assert op.stats().jit_compiles + op.stats().jit_cache_hits >= 2
+        finally:
+            op.close()

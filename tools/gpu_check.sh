@@ -26,6 +26,8 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:pgpu
   python bench.py --workload q6 --steps 1 --warmup 1 --no-e2e --no-cpu --rows 200000000 > gpurun_out/ncu_full_q6.log 2>&1; echo "ncu full q6 exit $?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:pgpu_k_page_staged -s 2 -c 1 -f -o gpurun_out/q1dict_full \
   python bench.py --workload q1dict --steps 1 --warmup 1 --no-e2e --no-cpu --rows 200000000 > gpurun_out/ncu_full_q1dict.log 2>&1; echo "ncu full q1dict exit $?"
+timeout 300 python tools/parquet_ingest_bench.py > gpurun_out/parquet_ingest.json 2> gpurun_out/parquet_ingest.err; echo "parquet ingest exit $?"
+cat gpurun_out/parquet_ingest.json; tail -3 gpurun_out/parquet_ingest.err
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_highcard.csv \
   python bench.py --workload highcard --steps 1 --warmup 1 --no-e2e --no-cpu > /dev/null 2>&1; echo "ncu launches highcard exit $?"
 ls -la gpurun_out
