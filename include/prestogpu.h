@@ -139,18 +139,23 @@ pgpu_status pgpu_get_serialized_output(pgpu_pipeline* p, const uint8_t** data, s
 typedef struct pgpu_parquet_chunk {
     const uint8_t* data;          /* host pointer                                                            */
     size_t len;
-    int32_t physical_type;        /* parquet.thrift Type: 0 BOOLEAN, 1 INT32, 2 INT64, 5 DOUBLE, 6 BYTE_ARRAY */
+    int32_t physical_type;        /* parquet.thrift Type: 0 BOOLEAN, 1 INT32, 2 INT64, 5 DOUBLE, 6 BYTE_ARRAY, 7 FIXED_LEN_BYTE_ARRAY */
     int32_t max_definition_level; /* 0 = required, 1 = optional flat column (nested columns are rejected)     */
     int64_t num_values;           /* ColumnMetaData.num_values = rows of the row group for a flat column     */
+    int32_t type_length;          /* FIXED_LEN_BYTE_ARRAY: bytes per value (1..16, a DECIMAL's unscaled value); else 0 */
+    int32_t reserved;
 } pgpu_parquet_chunk;
 /* Operator.addInput of the Page that ParquetReader.nextPage / readBlock -> PrimitiveColumnReader.readPrimitive would build from
  * one row group (.../reader/ParquetReader.java:211-268, PrimitiveColumnReader.java:148-317): chunk c feeds input channel c
- * (INT32 -> INTEGER/DATE, INT64 -> BIGINT/short DECIMAL, DOUBLE, BOOLEAN, BYTE_ARRAY -> VARCHAR/VARBINARY with the bounded-VARCHAR
- * truncation of BinaryColumnReader.java:44-58). Only page headers and the run headers of the RLE / bit-packed hybrid streams are
+ * (INT32 -> INTEGER/DATE, or widened to BIGINT/short DECIMAL as IntColumnReader / ShortDecimalColumnReader.java:52-62 do; INT64 ->
+ * BIGINT/short DECIMAL; DOUBLE; BOOLEAN; BYTE_ARRAY -> VARCHAR/VARBINARY with the bounded-VARCHAR truncation of
+ * BinaryColumnReader.java:44-58; FIXED_LEN_BYTE_ARRAY(<= 8) -> short DECIMAL, (9..16) -> long DECIMAL: big-endian two's complement
+ * unscaled value, ParquetTypeUtils.getShortDecimalValue :226-240, LongDecimalColumnReader.java:58. The file's decimal must have the
+ * channel's scale: the rescaling casts of those readers are not built). Only page headers and the run headers of the RLE / bit-packed hybrid streams are
  * read on the host; each chunk goes to the device in ONE copy and definition levels, dictionary ids and booleans are expanded
  * there. A chunk whose data pages are all dictionary encoded is consumed as a DictionaryBlock (ids + dictionary page), never
  * materialised. Data pages v1 and v2; PLAIN, PLAIN_DICTIONARY, RLE_DICTIONARY, RLE (levels, booleans). Rejected with
- * PGPU_NOT_SUPPORTED: compressed pages, nested columns, DELTA_* / BYTE_STREAM_SPLIT encodings, INT96 / FLOAT / FIXED_LEN_BYTE_ARRAY,
+ * PGPU_NOT_SUPPORTED: compressed pages, nested columns, DELTA_* / BYTE_STREAM_SPLIT encodings, INT96 / FLOAT,
  * var-width chunks that are not dictionary encoded throughout. */
 pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chunk* chunks, int32_t nchunks, int64_t rows);
 /* What pgpu_add_parquet_row_group reads on the host, without a GPU: info[0] data pages, [1] dictionary entries (-1: none), [2] every

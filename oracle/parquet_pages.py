@@ -21,7 +21,8 @@ implementation, pyarrow's C++ reader, on files pyarrow's writer produced (tests/
 
 Subset (everything else raises Unsupported, as the product rejects it): flat columns (max repetition level 0, max definition
 level <= 1), UNCOMPRESSED codec, data pages v1 and v2, encodings PLAIN, PLAIN_DICTIONARY, RLE_DICTIONARY (+ RLE for levels and BOOLEAN values),
-physical types BOOLEAN, INT32, INT64, DOUBLE, BYTE_ARRAY.
+physical types BOOLEAN, INT32, INT64, DOUBLE, BYTE_ARRAY (dictionary-encoded chunks), FIXED_LEN_BYTE_ARRAY of 1..16 bytes
+as a DECIMAL's unscaled value.
 """
 import struct
 
@@ -194,8 +195,19 @@ def hybrid_decode(buf, pos, end, width, count):
 _FIXED = {INT32: ("<i4", 4), INT64: ("<i8", 8), DOUBLE: ("<f8", 8)}
 
 
-def plain_values(buf, pos, end, ptype, count):
-    """PLAIN-encoded values -> numpy array (fixed width), or list of bytes (BYTE_ARRAY)"""
+def plain_values(buf, pos, end, ptype, count, type_length=0):
+    """PLAIN-encoded values -> numpy array (fixed width), list of bytes (BYTE_ARRAY), or numpy object array of Python ints
+    (FIXED_LEN_BYTE_ARRAY read as a DECIMAL's unscaled value: big-endian two's complement, ParquetTypeUtils.getShortDecimalValue
+    :226-240 / new BigInteger(bytes) in LongDecimalColumnReader.java:58)"""
+    if ptype == FIXED_LEN_BYTE_ARRAY:
+        if not 1 <= type_length <= 16:
+            raise Unsupported("FIXED_LEN_BYTE_ARRAY(%d) (only DECIMALs of up to 16 bytes)" % type_length)
+        if pos + count * type_length > end:
+            raise Corrupt("PLAIN values exceed the page")
+        out = np.empty(count, object)
+        for i in range(count):
+            out[i] = int.from_bytes(buf[pos + i * type_length:pos + (i + 1) * type_length], "big", signed=True)
+        return out
     if ptype in _FIXED:
         dt, w = _FIXED[ptype]
         if pos + count * w > end:
@@ -220,7 +232,7 @@ def plain_values(buf, pos, end, ptype, count):
     raise Unsupported("parquet physical type %d" % ptype)
 
 
-def decode_chunk(buf, ptype, max_def, num_values):
+def decode_chunk(buf, ptype, max_def, num_values, type_length=0):
     """One column chunk (bytes from its first page header to its end) -> (values, nulls uint8[num_values], info).
     values: numpy array with 0 at NULL positions (fixed width) / list with None (BYTE_ARRAY).
     info: {"pages": [...], "all_dictionary": bool, "dictionary": array/list or None, "ids": int32[n] with -1 at NULLs (when
@@ -231,7 +243,10 @@ def decode_chunk(buf, ptype, max_def, num_values):
     pos, done = 0, 0
     dictionary = None
     nulls = np.zeros(num_values, np.uint8)
-    values = [None] * num_values if ptype == BYTE_ARRAY else np.zeros(num_values, {BOOLEAN: np.uint8, INT32: np.int32, INT64: np.int64, DOUBLE: np.float64}.get(ptype, np.int64))
+    if ptype == FIXED_LEN_BYTE_ARRAY:
+        values = np.zeros(num_values, object)
+    else:
+        values = [None] * num_values if ptype == BYTE_ARRAY else np.zeros(num_values, {BOOLEAN: np.uint8, INT32: np.int32, INT64: np.int64, DOUBLE: np.float64}.get(ptype, np.int64))
     ids_all = np.full(num_values, -1, np.int32)
     pages, all_dict = [], True
     while done < num_values:
@@ -249,7 +264,7 @@ def decode_chunk(buf, ptype, max_def, num_values):
                 raise Corrupt("dictionary page must be the first page of the chunk")
             if h["encoding"] not in (ENC_PLAIN, ENC_PLAIN_DICTIONARY):
                 raise Unsupported("dictionary page encoding %d" % h["encoding"])
-            dictionary = plain_values(buf, body, end, ptype, h["num_values"])
+            dictionary = plain_values(buf, body, end, ptype, h["num_values"], type_length)
             pages.append(("dictionary", h["num_values"]))
             continue
         if h["type"] == PAGE_INDEX:
@@ -300,7 +315,7 @@ def decode_chunk(buf, ptype, max_def, num_values):
                 values[where] = np.asarray(dictionary)[ids]
         elif enc == ENC_PLAIN:
             all_dict = False
-            v = plain_values(buf, p, end, ptype, nn)
+            v = plain_values(buf, p, end, ptype, nn, type_length)
             if ptype == BYTE_ARRAY:
                 for w, x in zip(where, v):
                     values[w] = x

@@ -48,6 +48,15 @@ __global__ void __launch_bounds__(kThreads) k_pq_null_bits(const uint8_t* chunk,
     }
 }
 
+template <typename T>
+__device__ inline T zeroOf() { return T(0); }
+template <>
+__device__ inline ulonglong2 zeroOf<ulonglong2>() { return make_ulonglong2(0, 0); }
+template <typename T>
+__device__ inline T fromCode(uint32_t c) { return (T)c; }
+template <>
+__device__ inline ulonglong2 fromCode<ulonglong2>(uint32_t c) { return make_ulonglong2(c, 0); }
+
 // Each thread expands kPer consecutive values: one binary search for the first, then a walk along the run table (a run holds
 // >= 8 values unless it is a short RLE run), so the search cost is shared and a warp writes kPer * 32 consecutive outputs.
 constexpr int kPer = 4;
@@ -72,11 +81,35 @@ __global__ void __launch_bounds__(kThreads) k_pq_expand(const uint8_t* chunk, si
                 bad = true;
                 code = 0;
             }
-            if (GATHER) out[i] = limit ? dict[code] : OUT(0);
-            else out[i] = (OUT)code;
+            if (GATHER) out[i] = limit ? dict[code] : zeroOf<OUT>();
+            else out[i] = fromCode<OUT>(code);
         }
     }
     if (bad) atomicOr(err, kPqErrBadId);
+}
+
+template <int KIND, int OUTW>
+__global__ void __launch_bounds__(kThreads) k_pq_convert(const uint8_t* src, int inWidth, int64_t count, void* out) {
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < count; i += (int64_t)gridDim.x * kThreads) {
+        const uint8_t* s = src + i * inWidth;
+        if (KIND == 0) {
+            const uint32_t v = (uint32_t)s[0] | (uint32_t)s[1] << 8 | (uint32_t)s[2] << 16 | (uint32_t)s[3] << 24;
+            ((int64_t*)out)[i] = (int64_t)(int32_t)v;
+        } else {
+            // big-endian two's complement, sign-extended to 128 bits
+            const bool neg = (s[0] & 0x80) != 0;
+            unsigned __int128 v = neg ? ~(unsigned __int128)0 : 0;
+            for (int b = 0; b < inWidth; b++) v = (v << 8) | s[b];
+            if (OUTW == 8) {
+                ((int64_t*)out)[i] = (int64_t)(uint64_t)v;
+            } else {
+                const unsigned __int128 mag = neg ? (unsigned __int128)0 - v : v;
+                uint64_t lo = (uint64_t)mag, hi = (uint64_t)(mag >> 64);
+                if (neg) hi |= 0x8000000000000000ull;
+                ((ulonglong2*)out)[i] = make_ulonglong2(lo, hi);
+            }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(kThreads) k_pq_null_ids(int32_t* ids, const uint8_t* nulls, int64_t n, int32_t nullId) {
@@ -102,7 +135,8 @@ cudaError_t pqExpandRuns(cudaStream_t stream, const uint8_t* chunk, size_t chunk
     if (count <= 0) return cudaSuccess;
     const int g = gridFor((count + kPer - 1) / kPer);
     if (dict) {
-        if (outWidth == 8) k_pq_expand<uint64_t, true><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, (const uint64_t*)dict, limit, (uint64_t*)out, err);
+        if (outWidth == 16) k_pq_expand<ulonglong2, true><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, (const ulonglong2*)dict, limit, (ulonglong2*)out, err);
+        else if (outWidth == 8) k_pq_expand<uint64_t, true><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, (const uint64_t*)dict, limit, (uint64_t*)out, err);
         else if (outWidth == 4) k_pq_expand<uint32_t, true><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, (const uint32_t*)dict, limit, (uint32_t*)out, err);
         else return cudaErrorInvalidValue;
     } else {
@@ -110,6 +144,16 @@ cudaError_t pqExpandRuns(cudaStream_t stream, const uint8_t* chunk, size_t chunk
         else if (outWidth == 1) k_pq_expand<uint8_t, false><<<g, kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, first, count, nullptr, limit, (uint8_t*)out, err);
         else return cudaErrorInvalidValue;
     }
+    return cudaGetLastError();
+}
+
+cudaError_t pqConvertPlain(cudaStream_t stream, const uint8_t* src, int inWidth, int kind, int64_t count, void* out, int outWidth) {
+    if (count <= 0) return cudaSuccess;
+    const int g = gridFor(count);
+    if (kind == 0 && inWidth == 4 && outWidth == 8) k_pq_convert<0, 8><<<g, kThreads, 0, stream>>>(src, inWidth, count, out);
+    else if (kind == 1 && inWidth >= 1 && inWidth <= 8 && outWidth == 8) k_pq_convert<1, 8><<<g, kThreads, 0, stream>>>(src, inWidth, count, out);
+    else if (kind == 1 && inWidth >= 1 && inWidth <= 16 && outWidth == 16) k_pq_convert<1, 16><<<g, kThreads, 0, stream>>>(src, inWidth, count, out);
+    else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
 

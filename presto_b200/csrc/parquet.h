@@ -25,9 +25,15 @@ cudaError_t pqLevelsToNullBits(cudaStream_t stream, const uint8_t* chunk, size_t
 
 // values [first, first + count) of a hybrid stream -> out[0 .. count). outWidth 4 with dict == nullptr: the codes themselves
 // (dictionary ids; a code >= limit raises kPqErrBadId in *err and is stored as 0). dict != nullptr: out = dict[code], outWidth 4
-// or 8 bytes per value. outWidth 1: the codes as bytes (BOOLEAN).
+// 8 or 16 bytes per value. outWidth 1: the codes as bytes (BOOLEAN).
 cudaError_t pqExpandRuns(cudaStream_t stream, const uint8_t* chunk, size_t chunkLen, const PqRun* runs, int64_t nruns, int64_t first, int64_t count,
                          int outWidth, const void* dict, uint32_t limit, void* out, uint32_t* err);
+
+// PLAIN values as they lie in the chunk (any alignment) -> block values. kind 0: little-endian int32 -> int64 (IntColumnReader /
+// ShortDecimalColumnReader on an INT32 column). kind 1: big-endian two's complement of inWidth (1..16) bytes -> int64 (outWidth 8,
+// inWidth <= 8: ParquetTypeUtils.getShortDecimalValue) or -> the 128-bit sign-magnitude form of Int128ArrayBlock, low word first,
+// sign in the top bit of the high word (outWidth 16: Decimals.encodeUnscaledValue(new BigInteger(bytes))).
+cudaError_t pqConvertPlain(cudaStream_t stream, const uint8_t* src, int inWidth, int kind, int64_t count, void* out, int outWidth);
 
 // ids[i] = nullId where nulls[i] (the NULL entry appended to the dictionary)
 cudaError_t pqNullIds(cudaStream_t stream, int32_t* ids, const uint8_t* nulls, int64_t n, int32_t nullId);

@@ -10,7 +10,8 @@
 // from the org.apache.parquet classes shaded into io.trino.hive:hive-apache 3.1.2-12 (not in the reference tree).
 //
 // Subset: flat columns (max definition level 0 or 1, no repetition), UNCOMPRESSED pages, data pages v1 and v2, PLAIN /
-// PLAIN_DICTIONARY / RLE_DICTIONARY values (+ RLE booleans), RLE levels. Everything else is rejected ("not supported ...").
+// PLAIN_DICTIONARY / RLE_DICTIONARY values (+ RLE booleans), RLE levels; BOOLEAN, INT32, INT64, DOUBLE, FIXED_LEN_BYTE_ARRAY(<= 16)
+// and dictionary-encoded BYTE_ARRAY. Everything else is rejected ("not supported ...").
 #pragma once
 #include <cstdint>
 #include <cstring>
@@ -250,14 +251,21 @@ inline int32_t le32(const uint8_t* p) {
 
 }  // namespace detail
 
-inline int valueWidth(int ptype) { return ptype == INT32 ? 4 : ptype == INT64 || ptype == DOUBLE ? 8 : ptype == BOOLEAN ? 1 : 0; }
+// bytes per PLAIN value in the file (0 = var-width)
+inline int valueWidth(int ptype, int typeLength = 0) {
+    return ptype == INT32 ? 4 : ptype == INT64 || ptype == DOUBLE ? 8 : ptype == BOOLEAN ? 1 : ptype == FIXED_LEN_BYTE_ARRAY ? typeLength : 0;
+}
 
 // Describes one column chunk. `why` starts with "not supported" for rejections of well-formed input.
-inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int64_t numValues, Chunk& out, std::string& why) {
+inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int64_t numValues, Chunk& out, std::string& why, int typeLength = 0) {
     using namespace detail;
     if (maxDef < 0 || maxDef > 1) { why = "not supported on the GPU path: nested Parquet columns (max definition level " + std::to_string(maxDef) + ")"; return false; }
-    if (!(ptype == BOOLEAN || ptype == INT32 || ptype == INT64 || ptype == DOUBLE || ptype == BYTE_ARRAY)) {
+    if (!(ptype == BOOLEAN || ptype == INT32 || ptype == INT64 || ptype == DOUBLE || ptype == BYTE_ARRAY || ptype == FIXED_LEN_BYTE_ARRAY)) {
         why = "not supported on the GPU path: Parquet physical type " + std::to_string(ptype);
+        return false;
+    }
+    if (ptype == FIXED_LEN_BYTE_ARRAY && (typeLength < 1 || typeLength > 16)) {
+        why = "not supported on the GPU path: FIXED_LEN_BYTE_ARRAY(" + std::to_string(typeLength) + ") (only DECIMALs of up to 16 bytes)";
         return false;
     }
     if (numValues < 0 || (!d && len)) { why = "corrupt Parquet chunk: bad arguments"; return false; }
@@ -283,7 +291,7 @@ inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int6
             if (h.encoding != PLAIN && h.encoding != PLAIN_DICTIONARY) { why = "not supported on the GPU path: dictionary page encoding " + std::to_string(h.encoding); return false; }
             if (ptype == BOOLEAN) { why = "not supported on the GPU path: dictionary-encoded BOOLEAN"; return false; }
             if (h.numValues < 0 || h.numValues > 0x7fffffff) { why = "corrupt Parquet chunk: dictionary size"; return false; }
-            const int w = valueWidth(ptype);
+            const int w = valueWidth(ptype, typeLength);
             if (w && (uint64_t)h.numValues * w > end - body) { why = "corrupt Parquet chunk: dictionary values exceed the page"; return false; }
             out.hasDictionary = true;
             out.dictionaryCount = h.numValues;
@@ -366,7 +374,7 @@ inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int6
                     out.valueRuns.push_back(Run{values + doneV, (uint64_t)p * 8 + (uint64_t)doneV, (uint32_t)c, 1u | kPackedFlag});
                     doneV += c;
                 }
-            } else if ((uint64_t)pg.nonNull * valueWidth(ptype) > end - p) {
+            } else if ((uint64_t)pg.nonNull * valueWidth(ptype, typeLength) > end - p) {
                 why = "corrupt Parquet page: PLAIN values exceed the page";
                 return false;
             }

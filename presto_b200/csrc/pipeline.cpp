@@ -1279,13 +1279,15 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
         const pgpu_parquet_chunk& in = chunks[c];
         const Type& t = plan.input[c];
         const int pt = in.physical_type;
-        const bool match = (pt == pq::BOOLEAN && t.kind == TypeKind::BOOLEAN) || (pt == pq::INT32 && t.isInt32()) || (pt == pq::INT64 && t.isInt64Like()) ||
-                           (pt == pq::DOUBLE && t.kind == TypeKind::DOUBLE) || (pt == pq::BYTE_ARRAY && t.isVarWidth());
+        const int tl = in.type_length;
+        const bool match = (pt == pq::BOOLEAN && t.kind == TypeKind::BOOLEAN) || (pt == pq::INT32 && (t.isInt32() || t.isInt64Like())) || (pt == pq::INT64 && t.isInt64Like()) ||
+                           (pt == pq::DOUBLE && t.kind == TypeKind::DOUBLE) || (pt == pq::BYTE_ARRAY && t.isVarWidth()) ||
+                           (pt == pq::FIXED_LEN_BYTE_ARRAY && ((tl >= 1 && tl <= 8 && t.isShortDecimal()) || (tl >= 9 && tl <= 16 && t.isLongDecimal())));
         if (!match)
             return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: Parquet physical type " + std::to_string(pt) + " for a " + t.str() + " channel (channel " + std::to_string(c) + ")");
         if (in.num_values != rows) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " holds " + std::to_string(in.num_values) + " values, the row group " + std::to_string(rows) + " rows");
         std::string why;
-        if (!pq::parseChunk(in.data, in.len, pt, in.max_definition_level, in.num_values, ck[c], why))
+        if (!pq::parseChunk(in.data, in.len, pt, in.max_definition_level, in.num_values, ck[c], why, tl))
             return fail(p, why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT, why + " (channel " + std::to_string(c) + ")");
         if (pt == pq::BYTE_ARRAY && ck[c].hasDictionary) {
             const int maxChars = t.kind == TypeKind::VARCHAR ? t.precision : 0;
@@ -1309,7 +1311,7 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
     for (int c = 0; c < nchunks; c++) {
         const pq::Chunk& k = ck[c];
         Placed& q = at[c];
-        const int W = pq::valueWidth(chunks[c].physical_type);  // 0 for BYTE_ARRAY
+        const int W = plan.input[c].width();  // bytes per position of the block; 0 for var-width
         q.chunk = reserve(chunks[c].len);
         q.valueRuns = reserve(k.valueRuns.size() * sizeof(pq::Run));
         if (k.hasNulls()) {
@@ -1344,7 +1346,16 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
         const Placed& q = at[c];
         const Type& t = plan.input[c];
         const int pt = chunks[c].physical_type;
-        const int W = pq::valueWidth(pt);
+        const int W = t.width();                                    // bytes per position of the block
+        const int Win = pq::valueWidth(pt, chunks[c].type_length);  // bytes per PLAIN value in the file
+        // PLAIN values that are not the block's representation: INT32 widened to 64 bits (kind 0), big-endian decimals (kind 1)
+        const int conv = pt == pq::FIXED_LEN_BYTE_ARRAY ? 1 : (pt == pq::INT32 && W == 8) ? 0 : -1;
+        auto plainValues = [&](size_t srcOff, int64_t count, char* dst) -> cudaError_t {
+            if (count <= 0) return cudaSuccess;
+            if (conv < 0) return cudaMemcpyAsync(dst, base + q.chunk + srcOff, (size_t)count * W, cudaMemcpyDeviceToDevice, p->stream);
+            p->stats.kernel_launches += 1;
+            return pqConvertPlain(p->stream, (const uint8_t*)(base + q.chunk + srcOff), Win, conv, count, dst, W);
+        };
         const size_t len = chunks[c].len;
         const uint8_t* dchunk = (const uint8_t*)(base + q.chunk);
         if (len) CU(cudaMemcpyAsync(base + q.chunk, chunks[c].data, len, cudaMemcpyHostToDevice, p->stream));  // the whole chunk in one DMA
@@ -1389,7 +1400,7 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
             else d.position_count = k.dictionaryCount ? k.dictionaryCount : 1;
             if (W) {
                 CU(cudaMemsetAsync(base + q.dict, 0, entries * W, p->stream));
-                if (k.dictionaryCount) CU(cudaMemcpyAsync(base + q.dict, base + q.chunk + k.dictionaryOff, (size_t)k.dictionaryCount * W, cudaMemcpyDeviceToDevice, p->stream));
+                CU(plainValues(k.dictionaryOff, k.dictionaryCount, base + q.dict));
                 d.values = base + q.dict;
             } else {
                 std::vector<int32_t>& off = dictOffsets[c];
@@ -1410,8 +1421,7 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
             CU(pqExpandRuns(p->stream, dchunk, len, vruns, (int64_t)k.valueRuns.size(), 0, k.nonNull, 1, nullptr, 2u, dense, p->dErr));
             p->stats.kernel_launches += 1;
         } else {
-            if (k.anyDictionary && k.dictionaryCount)
-                CU(cudaMemcpyAsync(base + q.dict, base + q.chunk + k.dictionaryOff, (size_t)k.dictionaryCount * W, cudaMemcpyDeviceToDevice, p->stream));
+            if (k.anyDictionary) CU(plainValues(k.dictionaryOff, k.dictionaryCount, base + q.dict));
             for (const pq::DataPage& pg : k.pages) {
                 if (!pg.nonNull) continue;
                 char* dst = dense + (size_t)pg.firstValue * W;
@@ -1420,7 +1430,7 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
                                     (uint32_t)k.dictionaryCount, dst, p->dErr));
                     p->stats.kernel_launches += 1;
                 } else {
-                    CU(cudaMemcpyAsync(dst, base + q.chunk + pg.valuesOff, (size_t)pg.nonNull * W, cudaMemcpyDeviceToDevice, p->stream));
+                    CU(plainValues(pg.valuesOff, pg.nonNull, dst));
                 }
             }
         }
@@ -1441,7 +1451,7 @@ pgpu_status pgpu_parquet_inspect_chunk(const pgpu_parquet_chunk* chunk, int64_t*
     if (!chunk || !info) return PGPU_INVALID_ARGUMENT;
     pq::Chunk k;
     std::string why;
-    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why)) {
+    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length)) {
         if (err && err_len) {
             strncpy(err, why.c_str(), err_len - 1);
             err[err_len - 1] = 0;
@@ -1467,7 +1477,7 @@ pgpu_status pgpu_parquet_chunk_runs(const pgpu_parquet_chunk* chunk, int32_t whi
     if (!chunk || !n) return PGPU_INVALID_ARGUMENT;
     pq::Chunk k;
     std::string why;
-    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why))
+    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length))
         return why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT;
     std::vector<pq::Run> pages;
     for (const pq::DataPage& pg : k.pages) pages.push_back(pq::Run{pg.firstValue, (uint64_t)pg.valuesOff, (uint32_t)pg.nonNull, pg.dictionaryEncoded ? 1u : 0u});

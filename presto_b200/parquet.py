@@ -9,7 +9,7 @@ import io
 from typing import Dict, Iterator, List, Tuple, Union
 
 PHYSICAL = {"BOOLEAN": 0, "INT32": 1, "INT64": 2, "INT96": 3, "FLOAT": 4, "DOUBLE": 5, "BYTE_ARRAY": 6, "FIXED_LEN_BYTE_ARRAY": 7}  # parquet.thrift Type
-Chunk = Tuple[bytes, int, int, int]   # (chunk bytes, physical type, max definition level, num_values)
+Chunk = Tuple[bytes, int, int, int, int]   # (chunk bytes, physical type, max definition level, num_values, type_length of FIXED_LEN_BYTE_ARRAY)
 
 
 def row_groups(source: Union[str, bytes]) -> Iterator[Tuple[int, Dict[str, Chunk]]]:
@@ -25,7 +25,8 @@ def row_groups(source: Union[str, bytes]) -> Iterator[Tuple[int, Dict[str, Chunk
             start = c.data_page_offset
             if c.has_dictionary_page and c.dictionary_page_offset:
                 start = min(start, c.dictionary_page_offset)
-            cols[c.path_in_schema] = (data[start:start + c.total_compressed_size], PHYSICAL[c.physical_type], md.schema.column(j).max_definition_level, c.num_values)
+            cols[c.path_in_schema] = (data[start:start + c.total_compressed_size], PHYSICAL[c.physical_type], md.schema.column(j).max_definition_level, c.num_values,
+                                       md.schema.column(j).length if c.physical_type == "FIXED_LEN_BYTE_ARRAY" else 0)
         yield rg.num_rows, cols
 
 

@@ -57,3 +57,39 @@ def dictionary_chunk(dictionary, ids, width):
     d = np.asarray(dictionary, "<i8").tobytes()
     body = bytes([width]) + bit_packed(ids, width)
     return page_header(2, len(d), len(dictionary), 0) + d + page_header(0, len(body), len(ids), 8) + body
+
+
+# ---- the tpch connector's lineitem rows as a Parquet file (pyarrow's writer) ------------------------------------------------
+def decimal_array(unscaled, precision, scale):
+    """int64 unscaled values -> pyarrow decimal128(precision, scale) without a Python object per value"""
+    import pyarrow as pa
+    v = np.ascontiguousarray(unscaled, np.int64)
+    words = np.empty((len(v), 2), np.int64)
+    words[:, 0] = v
+    words[:, 1] = v >> 63          # sign extension of the little-endian 128-bit value
+    return pa.Array.from_buffers(pa.decimal128(precision, scale), len(v), [None, pa.py_buffer(words.tobytes())])
+
+
+def tpch_lineitem_parquet(sf, row_group_rows, as_integer=False, first_order=0, n_orders=None):
+    """Q1's columns of TPC-H lineitem (product-side host generator, pinned by the sf1 golden answers in test_tpch_golden.py) with
+    DECIMAL(12,2) numerics, dictionary-encoded flags, DATE ship dates -> the bytes of an uncompressed Parquet file"""
+    import io
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    from presto_b200 import tpch
+    if n_orders is None:
+        n_orders = tpch.tpch_order_count(sf) - first_order
+    c = lambda name, dec=False: tpch.tpch_host_column(name, sf, first_order, n_orders, dec)
+    t = pa.table({
+        "returnflag": pa.DictionaryArray.from_arrays(pa.array(c("returnflag_id").astype(np.int32)), pa.array(["A", "N", "R"])),
+        "linestatus": pa.DictionaryArray.from_arrays(pa.array(c("linestatus_id").astype(np.int32)), pa.array(["F", "O"])),
+        "quantity": decimal_array(c("quantity", True), 12, 2), "extendedprice": decimal_array(c("extendedprice", True), 12, 2),
+        "discount": decimal_array(c("discount", True), 12, 2), "tax": decimal_array(c("tax", True), 12, 2),
+        "shipdate": pa.array(c("shipdate").astype(np.int32), pa.date32())})
+    buf = io.BytesIO()
+    pq.write_table(t, buf, compression="NONE", use_dictionary=["returnflag", "linestatus", "quantity", "discount", "tax"], row_group_size=row_group_rows,
+                   write_statistics=False, store_decimal_as_integer=as_integer)
+    return buf.getvalue()
+
+
+Q1_COLUMNS = ["returnflag", "linestatus", "quantity", "extendedprice", "discount", "tax", "shipdate"]

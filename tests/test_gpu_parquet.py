@@ -142,7 +142,7 @@ def test_rejected_and_corrupt_chunks_raise():
         with pytest.raises(TrinoException) as e:   # a DOUBLE channel fed with the INT64 chunk
             op.addParquetRowGroup([cols["orderkey"], cols["discount"], cols["shipdate"], cols["quantity"]], rows)
         assert e.value.code == "NOT_SUPPORTED"
-        b, pt, md, n = cols["extendedprice"]
+        b, pt, md, n, tl = cols["extendedprice"]
         with pytest.raises(TrinoException) as e:
             op.addParquetRowGroup([(b[:len(b) // 2], pt, md, n), cols["discount"], cols["shipdate"], cols["quantity"]], rows)
         assert e.value.code != "NOT_SUPPORTED"
@@ -178,3 +178,37 @@ def test_dictionary_id_out_of_range_is_caught_on_the_device():
         assert "dictionary id" in str(e.value)
     finally:
         op.close()
+
+
+@pytest.mark.parametrize("as_integer", [False, True], ids=["flba", "integers"])
+def test_decimal_columns_identity(as_integer):
+    """DECIMALs stored as FIXED_LEN_BYTE_ARRAY (short: 6 and 4 bytes -> int64; long: 11 bytes -> sign-magnitude int128) or as INT64 /
+    INT32 (widened): the blocks must hold the unscaled values pyarrow's reader returns, dictionary-encoded and plain, with NULLs"""
+    pytest.importorskip("pyarrow")
+    import pyarrow.parquet as pq
+    import test_parquet_oracle as O
+    from presto_b200.spi import createDecimalType
+    t = O.decimal_table()
+    buf = io.BytesIO()
+    pq.write_table(t, buf, compression="NONE", use_dictionary=["discount"], data_page_size=2048, write_batch_size=64, store_decimal_as_integer=as_integer)
+    back = pq.read_table(io.BytesIO(buf.getvalue()))
+    names = ["price", "discount", "wide", "small"]
+    types = [createDecimalType(12, 2), createDecimalType(12, 2), createDecimalType(25, 4), createDecimalType(7, 2)]
+    plan = plan_text(types, None, [field(i, ty) for i, ty in enumerate(types)])
+    got, _ = run_parquet(plan, chunks_of(buf.getvalue()), names)
+    want = list(zip(*[O.unscaled(back.column(n)) for n in names]))
+    assert_rows_equal_ordered(got, want)
+
+
+def test_sf1_lineitem_parquet_file_equals_golden_answers():
+    """the reference's own golden TPC-H answers (hive_tpch q01 / q06, computed on DECIMAL(12,2) columns) straight off a Parquet
+    file of the sf1 table: FIXED_LEN_BYTE_ARRAY(6) decimals, dictionary-encoded flags / quantity / discount / tax, 1 M-row groups"""
+    pytest.importorskip("pyarrow")
+    import test_tpch_golden as G
+    from parquet_util import Q1_COLUMNS, tpch_lineitem_parquet
+    groups = chunks_of(tpch_lineitem_parquet(1.0, 1_000_000))
+    assert sum(g[0] for g in groups) == 6_001_215
+    got, st = run_parquet(tpch.q1_decimal_plan(), groups, Q1_COLUMNS)
+    G.check_q1_decimal(got)
+    got, _ = run_parquet(tpch.q6_decimal_plan(), groups, ["extendedprice", "discount", "shipdate", "quantity"])
+    assert got == G.golden_rows("hive_tpch_q06.result", (4,))

@@ -16,8 +16,8 @@ from parquet_util import GOLDEN, chunks_of, dictionary_chunk  # noqa: E402
 from presto_b200 import _native as N  # noqa: E402
 
 
-def inspect(buf, ptype, max_def, num_values):
-    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values)
+def inspect(buf, ptype, max_def, num_values, tl=0):
+    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values, tl, 0)
     info = (ctypes.c_int64 * 8)()
     err = ctypes.create_string_buffer(512)
     st = N.lib().pgpu_parquet_inspect_chunk(ctypes.byref(c), info, err, 512)
@@ -27,8 +27,8 @@ def inspect(buf, ptype, max_def, num_values):
 RUN = np.dtype([("start", "<i8"), ("src", "<u8"), ("count", "<u4"), ("width", "<u4")])
 
 
-def runs_of(buf, ptype, max_def, num_values, which):
-    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values)
+def runs_of(buf, ptype, max_def, num_values, which, tl=0):
+    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values, tl, 0)
     n = ctypes.c_int64()
     assert N.lib().pgpu_parquet_chunk_runs(ctypes.byref(c), which, None, 0, ctypes.byref(n)) == N.OK
     out = np.zeros(n.value, RUN)
@@ -57,24 +57,24 @@ def expand(buf, runs, first, count):
     return np.where(packed, code, r["src"]).astype(np.uint32)
 
 
-def check_runs(name, buf, ptype, max_def, nvals, nulls, o):
-    levels = runs_of(buf, ptype, max_def, nvals, 0)
+def check_runs(name, buf, ptype, max_def, nvals, nulls, o, tl):
+    levels = runs_of(buf, ptype, max_def, nvals, 0, tl)
     if nulls.any():
         assert np.array_equal(expand(buf, levels, 0, nvals) == 0, nulls.astype(bool)), name
     else:
         assert len(levels) == 0
     nn = int((nulls == 0).sum())
-    values = runs_of(buf, ptype, max_def, nvals, 1)
-    pages = runs_of(buf, ptype, max_def, nvals, 2)
+    values = runs_of(buf, ptype, max_def, nvals, 1, tl)
+    pages = runs_of(buf, ptype, max_def, nvals, 2, tl)
     assert int(pages["count"].sum()) == nn
     if o["all_dictionary"]:
         assert np.array_equal(expand(buf, values, 0, nn).astype(np.int32), o["ids"][nulls == 0]), name
     elif ptype == PP.BOOLEAN:
         got = expand(buf, values, 0, nn)
-        want, _, _ = PP.decode_chunk(buf, ptype, max_def, nvals)
+        want, _, _ = PP.decode_chunk(buf, ptype, max_def, nvals, tl)
         assert np.array_equal(got, np.asarray(want)[nulls == 0]), name
     else:  # plain / mixed fixed-width chunk: page by page, as the ingest copies or gathers them
-        want, _, _ = PP.decode_chunk(buf, ptype, max_def, nvals)
+        want, _, _ = PP.decode_chunk(buf, ptype, max_def, nvals, tl)
         dense = np.asarray(want)[nulls == 0]
         dt = dense.dtype
         for pg in pages:
@@ -90,10 +90,10 @@ def check_runs(name, buf, ptype, max_def, nvals, nulls, o):
 def check_against_oracle(path_or_bytes):
     n = 0
     for rows, cols in chunks_of(path_or_bytes):
-        for name, (buf, ptype, max_def, nvals) in cols.items():
-            st, info, err = inspect(buf, ptype, max_def, nvals)
+        for name, (buf, ptype, max_def, nvals, tl) in cols.items():
+            st, info, err = inspect(buf, ptype, max_def, nvals, tl)
             try:
-                _, nulls, o = PP.decode_chunk(buf, ptype, max_def, nvals)
+                _, nulls, o = PP.decode_chunk(buf, ptype, max_def, nvals, tl)
             except PP.Unsupported:
                 assert st == N.NOT_SUPPORTED, (name, err)
                 continue
@@ -108,7 +108,7 @@ def check_against_oracle(path_or_bytes):
             assert info[3] == int((nulls == 0).sum()), name
             assert (info[4] == 0) == (int(nulls.sum()) == 0), name
             assert info[7] == rows
-            check_runs(name, buf, ptype, max_def, nvals, nulls, o)
+            check_runs(name, buf, ptype, max_def, nvals, nulls, o, tl)
             n += 1
     return n
 
@@ -139,14 +139,14 @@ def test_compressed_pages_are_rejected():
     buf = io.BytesIO()
     pq.write_table(M.lineitem_table(3000, seed=3), buf, compression="SNAPPY")
     rows, cols = chunks_of(buf.getvalue())[0]
-    b, pt, md, n = cols["extendedprice"]
+    b, pt, md, n, tl = cols["extendedprice"]
     st, _, err = inspect(b, pt, md, n)
     assert st == N.NOT_SUPPORTED and "compressed" in err
 
 
 def test_rejections_and_corruption():
     rows, cols = chunks_of(os.path.join(GOLDEN, "nullable_v2.parquet"))[0]
-    b, pt, md, n = cols["runs"]
+    b, pt, md, n, tl = cols["runs"]
     assert inspect(b, pt, md, n)[0] == N.OK
     st, _, err = inspect(b, pt, 3, n)
     assert st == N.NOT_SUPPORTED and "nested" in err
@@ -170,7 +170,7 @@ def test_fuzzed_chunks_never_crash():
     rng = np.random.default_rng(99)
     for fname in ("nullable_v2.parquet", "lineitem_v1.parquet"):
         for rows, cols in chunks_of(os.path.join(GOLDEN, fname)):
-            for name, (b, pt, md, n) in cols.items():
+            for name, (b, pt, md, n, tl) in cols.items():
                 raw = np.frombuffer(b, np.uint8)
                 for trial in range(60):
                     x = raw.copy()
@@ -196,8 +196,8 @@ def test_dictionary_fallback_to_plain_mid_chunk():
                    data_page_version="1.0")
     kinds = set()
     for rows, cols in chunks_of(buf.getvalue()):
-        for name, (b, pt, md, nv) in cols.items():
-            _, _, info = PP.decode_chunk(b, pt, md, nv)
+        for name, (b, pt, md, nv, tl) in cols.items():
+            _, _, info = PP.decode_chunk(b, pt, md, nv, tl)
             kinds |= {(p[0], p[2]) for p in info["pages"] if p[0] != "dictionary"}
     assert ("data", PP.ENC_PLAIN) in kinds and (("data", PP.ENC_RLE_DICTIONARY) in kinds or ("data", PP.ENC_PLAIN_DICTIONARY) in kinds)
     sys.path.insert(0, GOLDEN)
@@ -245,3 +245,48 @@ def test_plans_of_the_gpu_suite_compile_for_the_signatures_the_ingest_produces()
             assert op.stats().jit_compiles + op.stats().jit_cache_hits >= 2
         finally:
             op.close()
+
+
+@pytest.mark.parametrize("as_integer", [False, True])
+def test_tpch_decimal_lineitem_file(as_integer):
+    """sf0.01 lineitem with DECIMAL(12,2) columns (FIXED_LEN_BYTE_ARRAY(6), or INT64 when stored as integers): the oracle reads the
+    generator's rows back, and the product's page / run tables reproduce them"""
+    pytest.importorskip("pyarrow")
+    from parquet_util import Q1_COLUMNS, tpch_lineitem_parquet
+    from presto_b200 import tpch
+    data = tpch_lineitem_parquet(0.01, 25_000, as_integer)
+    groups = chunks_of(data)
+    assert sum(g[0] for g in groups) == 60_175 and len(groups) == 3
+    at = 0
+    for rows, cols in groups:
+        for name in Q1_COLUMNS:
+            b, pt, md, nv, tl = cols[name]
+            values, nulls, o = PP.decode_chunk(b, pt, md, nv, tl)
+            assert not nulls.any()
+            if name in ("quantity", "extendedprice", "discount", "tax"):
+                assert pt == (PP.INT64 if as_integer else PP.FIXED_LEN_BYTE_ARRAY) and (as_integer or tl == 6)
+                want = tpch.tpch_host_column(name, 0.01, 0, tpch.tpch_order_count(0.01), True)[at:at + rows]
+                assert np.array_equal(np.asarray(values).astype(np.int64), want), name
+                assert o["all_dictionary"] == (name != "extendedprice")
+            st, info, err = inspect(b, pt, md, nv, tl)
+            assert st == N.OK and info[3] == rows, (name, err)
+            if pt != PP.FIXED_LEN_BYTE_ARRAY:
+                check_runs(name, b, pt, md, nv, nulls, o, tl)
+            else:
+                pages = runs_of(b, pt, md, nv, 2, tl)
+                assert int(pages["count"].sum()) == rows
+                if o["all_dictionary"]:
+                    assert np.array_equal(expand(b, runs_of(b, pt, md, nv, 1, tl), 0, rows).astype(np.int32), o["ids"])
+                else:  # PLAIN pages: big-endian values at the byte offsets the ingest converts from
+                    got = np.concatenate([[int.from_bytes(b[int(pg["src"]) + i * tl:int(pg["src"]) + (i + 1) * tl], "big", signed=True) for i in range(int(pg["count"]))]
+                                          for pg in pages])
+                    assert np.array_equal(got.astype(np.int64), np.asarray(values).astype(np.int64))
+        at += rows
+
+
+def test_fixed_len_byte_array_limits():
+    b = b"\x00" * 40
+    st, _, err = inspect(b, PP.FIXED_LEN_BYTE_ARRAY, 0, 1, 0)
+    assert st == N.NOT_SUPPORTED and "FIXED_LEN_BYTE_ARRAY" in err
+    st, _, err = inspect(b, PP.FIXED_LEN_BYTE_ARRAY, 0, 1, 17)
+    assert st == N.NOT_SUPPORTED

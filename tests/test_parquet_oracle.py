@@ -17,9 +17,9 @@ def check_file(path_or_bytes, exp):
     row0 = 0
     seen = set()
     for rows, cols in chunks_of(path_or_bytes):
-        for name, (buf, ptype, max_def, nvals) in cols.items():
+        for name, (buf, ptype, max_def, nvals, tl) in cols.items():
             assert nvals == rows
-            values, nulls, info = PP.decode_chunk(buf, ptype, max_def, nvals)
+            values, nulls, info = PP.decode_chunk(buf, ptype, max_def, nvals, tl)
             e_nulls = exp[name + ".nulls"][row0:row0 + rows]
             e_vals = exp[name + ".values"][row0:row0 + rows]
             assert np.array_equal(nulls, e_nulls), name
@@ -81,7 +81,7 @@ def test_hybrid_decoder_vectors():
 
 def test_rejections():
     rows, cols = chunks_of(os.path.join(GOLDEN, "lineitem_v1.parquet"))[0]
-    buf, ptype, max_def, n = cols["quantity"]
+    buf, ptype, max_def, n, tl = cols["quantity"]
     with pytest.raises(PP.Unsupported):
         PP.decode_chunk(buf, ptype, 2, n)
     with pytest.raises(PP.Corrupt):
@@ -103,8 +103,8 @@ def test_dictionary_fallback_to_plain_mid_chunk():
                    data_page_version="1.0")
     kinds = set()
     for rows, cols in chunks_of(buf.getvalue()):
-        for name, (b, pt, md, nv) in cols.items():
-            _, _, info = PP.decode_chunk(b, pt, md, nv)
+        for name, (b, pt, md, nv, tl) in cols.items():
+            _, _, info = PP.decode_chunk(b, pt, md, nv, tl)
             kinds |= {(p[0], p[2]) for p in info["pages"] if p[0] != "dictionary"}
     assert ("data", PP.ENC_PLAIN) in kinds and (("data", PP.ENC_RLE_DICTIONARY) in kinds or ("data", PP.ENC_PLAIN_DICTIONARY) in kinds)
     sys.path.insert(0, GOLDEN)
@@ -120,3 +120,43 @@ def test_hand_built_dictionary_chunk():
     assert values.tolist() == [[10, 20, 30][i] for i in ids] and not nulls.any() and info["all_dictionary"]
     with pytest.raises(PP.Corrupt):
         PP.decode_chunk(dictionary_chunk([10, 20, 30], [0, 3, 1], 2), PP.INT64, 0, 3)
+
+
+def decimal_table(n=900, seed=31):
+    import decimal
+    pa = pytest.importorskip("pyarrow")
+    rng = np.random.default_rng(seed)
+    D = decimal.Decimal
+    short = [None if rng.random() < 0.1 else D(int(rng.integers(-10 ** 11, 10 ** 11))).scaleb(-2) for _ in range(n)]
+    few = [D(int(rng.integers(0, 11))).scaleb(-2) for _ in range(n)]
+    longs = [None if rng.random() < 0.1 else D(int(rng.integers(-2 ** 62, 2 ** 62)) * int(rng.integers(1, 2 ** 20)) + int(rng.integers(-5, 5))).scaleb(-4) for _ in range(n)]
+    small = [D(int(rng.integers(-99999, 99999))).scaleb(-2) for _ in range(n)]
+    return pa.table({"price": pa.array(short, pa.decimal128(12, 2)), "discount": pa.array(few, pa.decimal128(12, 2)),
+                     "wide": pa.array(longs, pa.decimal128(25, 4)), "small": pa.array(small, pa.decimal128(7, 2))})
+
+
+def unscaled(col):
+    return [None if v is None else int(v.scaleb(-v.as_tuple().exponent)) for v in col.to_pylist()]
+
+
+@pytest.mark.parametrize("as_integer", [False, True])
+def test_decimal_columns(as_integer):
+    """DECIMALs as FIXED_LEN_BYTE_ARRAY (big-endian two's complement) and as INT32 / INT64 (parquet-format Logical types): the
+    unscaled values must be what pyarrow's reader returns"""
+    pytest.importorskip("pyarrow")
+    import pyarrow.parquet as pq
+    t = decimal_table()
+    buf = io.BytesIO()
+    pq.write_table(t, buf, compression="NONE", use_dictionary=["discount"], data_page_size=2048, write_batch_size=64, store_decimal_as_integer=as_integer)
+    back = pq.read_table(io.BytesIO(buf.getvalue()))
+    kinds = set()
+    for rows, cols in chunks_of(buf.getvalue()):
+        for name, (b, pt, md, nv, tl) in cols.items():
+            values, nulls, info = PP.decode_chunk(b, pt, md, nv, tl)
+            want = unscaled(back.column(name))
+            assert [None if z else int(v) for v, z in zip(values, nulls)] == want, name
+            kinds.add((name, pt))
+    if as_integer:
+        assert ("small", PP.INT32) in kinds and ("price", PP.INT64) in kinds and ("wide", PP.FIXED_LEN_BYTE_ARRAY) in kinds
+    else:
+        assert {pt for _, pt in kinds} == {PP.FIXED_LEN_BYTE_ARRAY}
