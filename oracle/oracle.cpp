@@ -342,7 +342,10 @@ static Vec evalArith(const Expr& e, const Vec& a, const Vec& b) {
                     break;
                 case Op::DIVIDE:
                     if (y == 0) throw OracleError(PGPU_DIVISION_BY_ZERO, "Division by zero");
-                    z = y == -1 ? (int32_t)(0u - (uint32_t)x) : x / y;  // Java int division: MIN / -1 wraps
+                    // IntegerOperators.java:79-89 divides Java longs: MIN / -1 = 2^31 leaves the INTEGER domain and fails when written
+                    // to a block (spi/type/AbstractIntType.java:85-95); reported here, at the division
+                    if (x == INT32_MIN && y == -1) throw OracleError(PGPU_NUMERIC_VALUE_OUT_OF_RANGE, "integer division overflow: value 2147483648 exceeds MAX_INT");
+                    z = x / y;
                     break;
                 default:
                     if (y == 0) throw OracleError(PGPU_DIVISION_BY_ZERO, "Division by zero");

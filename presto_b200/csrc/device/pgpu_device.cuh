@@ -243,9 +243,15 @@ PGPU_DEV i32 narrow_i32_checked(i64 v, u32& err) {  // Math.toIntExact / Integer
     if (v != (i64)(i32)v) err |= PGPU_ERR_OVERFLOW;
     return (i32)v;
 }
-PGPU_DEV i32 div_i32_checked(i32 a, i32 b, u32& err) {  // IntegerOperators.divide: Java int division, MIN / -1 wraps
+// IntegerOperators.divide (main/type/IntegerOperators.java:79-89) divides Java longs: MIN / -1 is 2^31, which leaves the INTEGER
+// domain and fails when it is written to a block (AbstractIntType.writeLong: "Value 2147483648 exceeds MAX_INT"). Here it fails
+// at the division, as an out-of-range value; it never wraps silently.
+PGPU_DEV i32 div_i32_checked(i32 a, i32 b, u32& err) {
     if (b == 0) { err |= PGPU_ERR_DIVZERO; return 0; }
-    if (b == -1) return (i32)(0u - (u32)a);
+    if (b == -1) {
+        if (a == (i32)0x80000000u) err |= PGPU_ERR_OVERFLOW;
+        return (i32)(0u - (u32)a);
+    }
     return a / b;
 }
 PGPU_DEV i32 mod_i32_checked(i32 a, i32 b, u32& err) {
