@@ -32,6 +32,22 @@ final class PrestoGpuNative
             Object[] values, int[] valuesOffset, boolean[][] valueIsNull, int[][] offsets, int[][] ids, int[] idsOffset,
             Object[] dictionaryValues, boolean[][] dictionaryIsNull, int[][] dictionaryOffsets, int[] dictionaryPositionCount);
 
+    /**
+     * pgpu_add_serialized_page — Operator.addInput of a Page in the wire format of PagesSerdeUtil.writeRawPage: address / length of
+     * the (uncompressed) payload Slice, off-heap or pinned by the shim for the duration of the call.
+     */
+    static native void addSerializedPage(long handle, long address, int length, int positionCount);
+
+    /**
+     * pgpu_add_parquet_row_group — Operator.addInput of the Page ParquetReader.nextPage would build from one row group. Per channel:
+     * the column chunk's bytes as they lie in the file (ColumnChunkMetaData.getStartingPos() .. + getTotalSize(), decompressed page
+     * by page if the codec is not UNCOMPRESSED) as address / length of a direct buffer, the parquet physical type ordinal
+     * (PrimitiveTypeName: BOOLEAN 0, INT32 1, INT64 2, DOUBLE 5, BINARY 6, FIXED_LEN_BYTE_ARRAY 7), the column's max definition
+     * level (0 or 1), its value count and, for FIXED_LEN_BYTE_ARRAY, the type length.
+     */
+    static native void addParquetRowGroup(long handle, long rows, long[] address, long[] length, int[] physicalType, int[] maxDefinitionLevel,
+            long[] valueCount, int[] typeLength);
+
     /** pgpu_finish — Operator.finish(). */
     static native void finish(long handle);
 

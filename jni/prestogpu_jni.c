@@ -108,6 +108,44 @@ JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addPage(JNIEnv
     if (st != PGPU_OK) throwTrino(env, st, pgpu_last_error(p));
 }
 
+JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addSerializedPage(JNIEnv* env, jclass cls, jlong h, jlong address, jint length, jint positionCount) {
+    pgpu_pipeline* p = (pgpu_pipeline*)(intptr_t)h;
+    pgpu_status st = pgpu_add_serialized_page(p, (const uint8_t*)(intptr_t)address, (size_t)length, positionCount);
+    if (st != PGPU_OK) throwTrino(env, st, pgpu_last_error(p));
+}
+
+/* addParquetRowGroup: the chunks are direct (off-heap) buffers, so nothing is pinned; the small per-channel arrays are copied. */
+JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addParquetRowGroup(JNIEnv* env, jclass cls, jlong h, jlong rows, jlongArray address,
+                                                                                   jlongArray length, jintArray physicalType, jintArray maxDefinitionLevel,
+                                                                                   jlongArray valueCount, jintArray typeLength) {
+    pgpu_pipeline* p = (pgpu_pipeline*)(intptr_t)h;
+    jsize n = (*env)->GetArrayLength(env, address);
+    if (n > MAX_CH) {
+        throwTrino(env, PGPU_NOT_SUPPORTED, "more than 64 channels");
+        return;
+    }
+    jlong addr[MAX_CH], len[MAX_CH], count[MAX_CH];
+    jint type[MAX_CH], def[MAX_CH], tl[MAX_CH];
+    (*env)->GetLongArrayRegion(env, address, 0, n, addr);
+    (*env)->GetLongArrayRegion(env, length, 0, n, len);
+    (*env)->GetLongArrayRegion(env, valueCount, 0, n, count);
+    (*env)->GetIntArrayRegion(env, physicalType, 0, n, type);
+    (*env)->GetIntArrayRegion(env, maxDefinitionLevel, 0, n, def);
+    (*env)->GetIntArrayRegion(env, typeLength, 0, n, tl);
+    pgpu_parquet_chunk chunks[MAX_CH];
+    for (jsize c = 0; c < n; c++) {
+        chunks[c].data = (const uint8_t*)(intptr_t)addr[c];
+        chunks[c].len = (size_t)len[c];
+        chunks[c].physical_type = type[c];
+        chunks[c].max_definition_level = def[c];
+        chunks[c].num_values = count[c];
+        chunks[c].type_length = tl[c];
+        chunks[c].reserved = 0;
+    }
+    pgpu_status st = pgpu_add_parquet_row_group(p, chunks, (int32_t)n, rows);
+    if (st != PGPU_OK) throwTrino(env, st, pgpu_last_error(p));
+}
+
 JNIEXPORT jboolean JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_needsInput(JNIEnv* env, jclass cls, jlong h) { return pgpu_needs_input((pgpu_pipeline*)(intptr_t)h) != 0; }
 JNIEXPORT jboolean JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_isFinished(JNIEnv* env, jclass cls, jlong h) { return pgpu_is_finished((pgpu_pipeline*)(intptr_t)h) != 0; }
 JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_finish(JNIEnv* env, jclass cls, jlong h) { pgpu_finish((pgpu_pipeline*)(intptr_t)h); }
