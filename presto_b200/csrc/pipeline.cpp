@@ -15,6 +15,7 @@
 #include <map>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/prestogpu.h"
@@ -1286,15 +1287,33 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
         if (!match)
             return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: Parquet physical type " + std::to_string(pt) + " for a " + t.str() + " channel (channel " + std::to_string(c) + ")");
         if (in.num_values != rows) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " holds " + std::to_string(in.num_values) + " values, the row group " + std::to_string(rows) + " rows");
-        std::string why;
-        if (!pq::parseChunk(in.data, in.len, pt, in.max_definition_level, in.num_values, ck[c], why, tl))
-            return fail(p, why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT, why + " (channel " + std::to_string(c) + ")");
-        if (pt == pq::BYTE_ARRAY && ck[c].hasDictionary) {
-            const int maxChars = t.kind == TypeKind::VARCHAR ? t.precision : 0;
-            if (!pq::binaryDictionary(in.data, ck[c].dictionaryOff, ck[c].dictionaryEnd, ck[c].dictionaryCount, maxChars, dictOffsets[c], dictBytes[c], why))
-                return fail(p, PGPU_INVALID_ARGUMENT, why + " (channel " + std::to_string(c) + ")");
-        }
     }
+    // the header walk of a chunk is sequential, the chunks are independent: one host thread per column chunk
+    std::vector<std::string> whys((size_t)nchunks);
+    auto parseOne = [&](int c) {
+        const pgpu_parquet_chunk& in = chunks[c];
+        const Type& t = plan.input[c];
+        if (!pq::parseChunk(in.data, in.len, in.physical_type, in.max_definition_level, in.num_values, ck[c], whys[c], in.type_length)) {
+            if (whys[c].empty()) whys[c] = "corrupt Parquet chunk";
+            return;
+        }
+        if (in.physical_type == pq::BYTE_ARRAY && ck[c].hasDictionary) {
+            const int maxChars = t.kind == TypeKind::VARCHAR ? t.precision : 0;
+            if (!pq::binaryDictionary(in.data, ck[c].dictionaryOff, ck[c].dictionaryEnd, ck[c].dictionaryCount, maxChars, dictOffsets[c], dictBytes[c], whys[c]) && whys[c].empty())
+                whys[c] = "corrupt Parquet dictionary page";
+        }
+    };
+    if (nchunks > 1 && rows >= 65536) {
+        std::vector<std::thread> workers;
+        for (int c = 1; c < nchunks; c++) workers.emplace_back(parseOne, c);
+        parseOne(0);
+        for (auto& w : workers) w.join();
+    } else {
+        for (int c = 0; c < nchunks; c++) parseOne(c);
+    }
+    for (int c = 0; c < nchunks; c++)
+        if (!whys[c].empty())
+            return fail(p, whys[c].rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT, whys[c] + " (channel " + std::to_string(c) + ")");
     if (rows == 0) return PGPU_OK;  // an empty row group adds nothing
     CU(cudaSetDevice(p->device));
     // arena layout, every piece 256-byte aligned
