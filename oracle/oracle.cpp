@@ -953,7 +953,7 @@ struct Oracle {
             for (size_t k = 0; k < m; k++) gid[k] = hash.putIfAbsent(keyRow, k);
             for (auto& a : accs) a.ensure(hash.groupCount);
         }
-        const bool fin = plan->step == Step::FINAL;
+        const bool fin = inputIsIntermediate(plan->step);
         for (auto& a : accs) {
             if (fin) {
                 size_t ni = Plan::intermediateTypes(a.spec).size();
@@ -988,7 +988,7 @@ struct Oracle {
         result.assign(ot.size(), Vec());
         for (size_t c = 0; c < ot.size(); c++) result[c].type = ot[c];
         int64_t groups = hasGroups() ? hash.groupCount : 1;
-        const bool partial = plan->step == Step::PARTIAL;
+        const bool partial = outputIsIntermediate(plan->step);
         for (int64_t g = 0; g < groups; g++) {
             size_t oc = 0;
             for (size_t c = 0; c < plan->groupChannels.size(); c++) appendValue(result[oc++], hash.keys[c], (size_t)g);
@@ -1058,7 +1058,7 @@ struct Oracle {
     }
 
     bool partialFlushDue() const {
-        return plan->hasAgg && plan->step == Step::PARTIAL && plan->maxPartialGroups > 0 && hasGroups() && hash.groupCount >= plan->maxPartialGroups;
+        return plan->hasAgg && outputIsIntermediate(plan->step) && plan->maxPartialGroups > 0 && hasGroups() && hash.groupCount >= plan->maxPartialGroups;
     }
 
     bool needsInput() const {  // HashAggregationOperator.needsInput :367-378

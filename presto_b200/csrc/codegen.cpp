@@ -694,7 +694,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     res.NC = (int)plan.input.size();
     Gen g(plan, sig);
     std::vector<Type> proj = plan.projectedTypes();
-    const bool finalStep = plan.hasAgg && plan.step == Step::FINAL;
+    const bool finalStep = plan.hasAgg && inputIsIntermediate(plan.step);  // FINAL / INTERMEDIATE: inputs are partial states
 
     // which projected channels does the consumer need?
     std::set<int> neededProj;
@@ -1425,7 +1425,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
                 else if (t.isInt32()) L("((i32*)out.c[" + O(k) + "].values)[pos] = (i32)" + kx + ";");
                 else L("((i64*)out.c[" + O(k) + "].values)[pos] = " + kx + ";");
             };
-            const bool partial = plan.step == Step::PARTIAL;
+            const bool partial = outputIsIntermediate(plan.step);  // PARTIAL / INTERMEDIATE: states go out
             switch (a.fn) {
                 case AggFn::COUNT:
                     L("((i64*)out.c[" + O(0) + "].values)[pos] = (i64)" + cnt + ";");

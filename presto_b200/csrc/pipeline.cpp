@@ -832,7 +832,7 @@ pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
 // PARTIAL step: once the row-count upper bound crosses the flush threshold, learn the real group count
 pgpu_status updatePartialFill(pgpu_pipeline* p) {
     const Plan& plan = *p->plan;
-    if (plan.hasAgg && plan.step == Step::PARTIAL && plan.maxPartialGroups > 0 && !plan.groupChannels.empty() && p->dSlots &&
+    if (plan.hasAgg && outputIsIntermediate(plan.step) && plan.maxPartialGroups > 0 && !plan.groupChannels.empty() && p->dSlots &&
         p->groupsKnown + p->rowsSinceKnown >= plan.maxPartialGroups)
         return refreshGroupCount(p);
     return PGPU_OK;
@@ -901,7 +901,7 @@ void resetAggState(pgpu_pipeline* p) {
 }
 
 bool isPartialFlushDue(const pgpu_pipeline* p) {
-    return p->plan->hasAgg && p->plan->step == Step::PARTIAL && p->plan->maxPartialGroups > 0 && !p->plan->groupChannels.empty() &&
+    return p->plan->hasAgg && outputIsIntermediate(p->plan->step) && p->plan->maxPartialGroups > 0 && !p->plan->groupChannels.empty() &&
            (p->groupsKnown + p->rowsSinceKnown) >= p->plan->maxPartialGroups;
 }
 

@@ -625,7 +625,7 @@ std::vector<Type> Plan::outputTypes() const {
     std::vector<Type> out;
     for (int g : groupChannels) out.push_back(proj[g]);
     for (auto& a : aggs) {
-        if (step == Step::PARTIAL) {
+        if (outputIsIntermediate(step)) {
             for (auto& t : intermediateTypes(a)) out.push_back(t);
         } else {
             out.push_back(a.outType);
@@ -690,7 +690,7 @@ std::unique_ptr<Plan> parsePlan(const std::string& text) {
                 if (t == "single") plan->step = Step::SINGLE;
                 else if (t == "partial") plan->step = Step::PARTIAL;
                 else if (t == "final") plan->step = Step::FINAL;
-                else if (t == "intermediate") unsupported("aggregation step INTERMEDIATE");
+                else if (t == "intermediate") plan->step = Step::INTERMEDIATE;
                 else bad("unknown step '" + t + "'");
             } else if (h == "group") {
                 for (size_t j = 1; j < s.kids.size(); j++) {
@@ -734,7 +734,7 @@ std::unique_ptr<Plan> parsePlan(const std::string& text) {
         if (plan->aggs.size() > 32) unsupported("more than 32 aggregates");
         // channel checks
         for (auto& a : plan->aggs) {
-            if (plan->step == Step::FINAL) {
+            if (inputIsIntermediate(plan->step)) {
                 if (a.mask >= 0) bad("mask on FINAL step");
                 std::vector<Type> it = Plan::intermediateTypes(a);
                 int first = a.hasArg ? a.arg : -1;
@@ -766,7 +766,7 @@ std::unique_ptr<Plan> parsePlan(const std::string& text) {
             if (!proj[c].isVarWidth()) continue;
             bool isKey = std::find(plan->groupChannels.begin(), plan->groupChannels.end(), (int)c) != plan->groupChannels.end();
             bool isState = false;
-            if (plan->step == Step::FINAL)
+            if (inputIsIntermediate(plan->step))
                 for (auto& a : plan->aggs) isState |= (a.arg == (int)c && proj[c].kind == TypeKind::VARBINARY);
             (void)isKey; (void)isState;  // unused var-width channels are simply ignored by the aggregation
         }

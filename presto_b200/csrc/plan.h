@@ -60,7 +60,10 @@ struct Expr {
 };
 
 enum class AggFn { SUM, COUNT, AVG, MIN, MAX };
-enum class Step { SINGLE, PARTIAL, FINAL };  // main/sql/planner/plan/AggregationNode.java Step (INTERMEDIATE unsupported)
+enum class Step { SINGLE, PARTIAL, FINAL, INTERMEDIATE };  // main/sql/planner/plan/AggregationNode.java:348-380 Step
+// Step.isInputRaw() / isOutputPartial() of the reference, negated / as is
+inline bool inputIsIntermediate(Step s) { return s == Step::FINAL || s == Step::INTERMEDIATE; }
+inline bool outputIsIntermediate(Step s) { return s == Step::PARTIAL || s == Step::INTERMEDIATE; }
 
 struct AggSpec {
     AggFn fn = AggFn::COUNT;

@@ -75,6 +75,14 @@ def test_conditional_forms_compile_for_sm_100a():
         op.close()
 
 
+def test_intermediate_step_compiles_and_keeps_the_state_schema():
+    from test_oracle_protocol import q1_stage_plan
+    op = GpuPipelineOperator(q1_stage_plan("intermediate"), device=-1)
+    assert [t.kind for t in op.outputTypes()] == [6, 6] + [1, 4] * 4 + [4, 1] * 3 + [1]     # same as the PARTIAL step's output
+    op.compileSignature([0] * 17, [True] * 17)
+    op.close()
+
+
 def test_output_schema():
     op = GpuPipelineOperator(tpch.q1_plan(), device=-1)
     kinds = [t.kind for t in op.outputTypes()]
@@ -104,7 +112,8 @@ REJECTED = [
     ("unknown function", lambda: plan_text([DOUBLE], None, [CallExpression("sqrt", DOUBLE, [field(0, DOUBLE)])])),
     ("unknown aggregate", lambda: plan_text([DOUBLE], step="single", aggregations=[Aggregation("approx_distinct", BIGINT, 0, DOUBLE)])),
     ("decimal division", lambda: plan_text([createDecimalType(10, 2)], None, [call("divide", createDecimalType(10, 2), field(0, createDecimalType(10, 2)), field(0, createDecimalType(10, 2)))])),
-    ("intermediate step", lambda: plan_text([BIGINT], step="intermediate", aggregations=[Aggregation("count", BIGINT)])),
+    ("unknown step", lambda: plan_text([BIGINT], step="streaming", aggregations=[Aggregation("count", BIGINT)])),
+    ("intermediate step over raw input", lambda: plan_text([DOUBLE], step="intermediate", aggregations=[Aggregation("sum", DOUBLE, 0, DOUBLE)])),
 ]
 
 

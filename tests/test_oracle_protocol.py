@@ -38,6 +38,43 @@ def test_partial_then_final_equals_single():
     assert sorted(r[-1] for r in final) == sorted(r[-1] for r in single)
 
 
+def q1_stage_plan(step):
+    return q1_final_plan().replace("(step final)", "(step %s)" % step)
+
+
+def intermediate_chain(make_operator):
+    """PARTIAL per shard -> INTERMEDIATE over pairs of partial outputs -> FINAL (AggregationNode.Step: INTERMEDIATE takes and
+    emits partial states, main/sql/planner/plan/AggregationNode.java:348-380; HashAggregationOperator treats it as
+    step.isOutputPartial() / !step.isInputRaw())"""
+    total = 90_000
+    cuts = [0, 20_000, 45_000, 70_000, total]
+    shards = [[tpch.q1_page(a, b - a, total)] for a, b in zip(cuts, cuts[1:])]
+    partial = []
+    for s in shards:
+        op = make_operator(tpch.q1_plan("partial"))
+        partial.append(toPages(op, s))
+        op.close()
+    inter = []
+    for pair in (partial[0] + partial[1], partial[2] + partial[3]):
+        op = make_operator(q1_stage_plan("intermediate"))
+        inter += toPages(op, pair)
+        op.close()
+    op = make_operator(q1_stage_plan("final"))
+    final = toPages(op, inter)
+    op.close()
+    return total, [pg for s in shards for pg in s], inter, final
+
+
+def test_partial_intermediate_final_equals_single():
+    from util import rows_of
+    total, pages, inter, final = intermediate_chain(OracleOperator)
+    single = run_oracle(tpch.q1_plan(), pages)
+    assert "(step intermediate)" in q1_stage_plan("intermediate")
+    assert all(len(pg.blocks) == 17 for pg in inter)           # keys + the 15 state channels: still partial states
+    assert_rows_equal_ignore_order(rows_of(final), single, nkeys=2, rtol=sequential_bound(total))
+    assert sorted(r[-1] for r in rows_of(final)) == sorted(r[-1] for r in single)
+
+
 def test_partial_flushes_when_full_and_multi_page_output():
     # HashAggregationOperator.needsInput (:367-378) turns false once the partial table is full; getOutput then
     # flushes it in pages of <= maxOutputRows rows and the operator accepts input again.
