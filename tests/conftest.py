@@ -23,7 +23,7 @@ def _native_built():
 
 # GPU cases added since the last visit to a B200 (profiles/r01g_pytest_gpu.log) run after everything that has already
 # passed there, so that under `-x` a surprise in a new case cannot hide the state of the proven ones.
-NEWEST_GPU_CASES = ("nullif_grid_", "simple_case_", "case_nullif_into_aggregation", "test_gpu_parquet", "test_gpu_operators", "test_gpu_intermediate")
+NEWEST_GPU_CASES = ("nullif_grid_", "simple_case_", "case_nullif_into_aggregation", "optest_", "test_gpu_parquet", "test_gpu_operators", "test_gpu_intermediate")
 
 
 def pytest_collection_modifyitems(config, items):

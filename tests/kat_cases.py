@@ -331,6 +331,30 @@ def conditional_cases():
     return cases
 
 
+def operator_test_cases():
+    """TestAggregationOperator.java:91-118 (mask with dirty nulls), :120-156 (global aggregation over sequence pages, the functions of
+    the supported subset), TestFilterAndProjectOperator.java:80-124 (filter bigint <= 9, project the varchar and bigint + 5)."""
+    from presto_b200.spi import ByteArrayBlock, VARCHAR
+    cases = []
+    # count(channel 0) masked by a BOOLEAN channel whose NULL positions hold garbage and whose TRUE is any non-zero byte
+    mask = ByteArrayBlock(BOOLEAN, np.array([0, 27, 0, 75], dtype=np.int8), np.array([1, 1, 0, 0], dtype=np.uint8))
+    plan = plan_text([BIGINT, BOOLEAN], step="single", aggregations=[Aggregation("count", BIGINT, 0, BIGINT, maskChannel=1)])
+    cases.append(("optest_mask_with_dirty_nulls", plan, [Page(block_of(BIGINT, [1, 2, 3, 4]), mask)], [(1,)], None))
+    # addSequencePage(100, 0, 0, 300, 500, 400, 500, 500): channel i holds start_i .. start_i + 99 (varchar: the decimal string)
+    v10 = createVarcharType(10)
+    seq = lambda start: list(range(start, start + 100))
+    page = Page(block_of(v10, [str(x) for x in seq(0)]), block_of(BIGINT, seq(0)), block_of(BIGINT, seq(500)), block_of(DOUBLE, [float(x) for x in seq(500)]))
+    plan = plan_text([v10, BIGINT, BIGINT, DOUBLE], step="single",
+                     aggregations=[Aggregation("count", BIGINT, 0, v10), Aggregation("sum", BIGINT, 1, BIGINT), Aggregation("avg", DOUBLE, 1, BIGINT),
+                                   Aggregation("count", BIGINT, 0, v10), Aggregation("sum", BIGINT, 2, BIGINT), Aggregation("sum", DOUBLE, 3, DOUBLE)])
+    cases.append(("optest_global_aggregation", plan, [page], [(100, 4950, 49.5, 100, 54950, 54950.0)], None))
+    # FilterAndProjectOperator
+    page = Page(block_of(v10, [str(x) for x in seq(0)]), block_of(BIGINT, seq(0)))
+    plan = plan_text([v10, BIGINT], compare("le", field(1, BIGINT), constant(9, BIGINT)), [field(0, v10), call("add", BIGINT, field(1, BIGINT), constant(5, BIGINT))])
+    cases.append(("optest_filter_and_project", plan, [page], [(str(i), i + 5) for i in range(10)], "ordered"))
+    return cases
+
+
 def dictionary_rle_cases():
     """TestDictionaryAwarePageFilter (:49-116) / TestDictionaryAwarePageProjection (:80-143): dictionary, RLE and plain
     inputs holding the same values must give the same result."""
@@ -369,4 +393,4 @@ def dictionary_rle_cases():
 
 
 def all_cases():
-    return global_aggregate_cases() + hash_aggregation_cases() + filter_project_cases() + conditional_cases() + dictionary_rle_cases()
+    return global_aggregate_cases() + hash_aggregation_cases() + filter_project_cases() + conditional_cases() + operator_test_cases() + dictionary_rle_cases()
