@@ -15,7 +15,9 @@
 #pragma once
 #include <cstdint>
 #include <cstring>
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace pgpu {
@@ -256,8 +258,118 @@ inline int valueWidth(int ptype, int typeLength = 0) {
     return ptype == INT32 ? 4 : ptype == INT64 || ptype == DOUBLE ? 8 : ptype == BOOLEAN ? 1 : ptype == FIXED_LEN_BYTE_ARRAY ? typeLength : 0;
 }
 
-// Describes one column chunk. `why` starts with "not supported" for rejections of well-formed input.
-inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int64_t numValues, Chunk& out, std::string& why, int typeLength = 0) {
+namespace detail {
+
+struct PageDesc {
+    PageHeader h;
+    size_t body = 0, end = 0;
+    int64_t firstRow = 0;
+};
+
+// What one data page contributes, computed independently of every other page (so pages can be walked in parallel): definition
+// level runs numbered by ROW (absolute), value runs numbered from 0 within the page (shifted by the page's first value when the
+// chunk is assembled), the non-null count.
+struct PageResult {
+    bool ok = true;
+    std::string why;
+    std::vector<Run> levels, values;
+    bool scanned = false;  // the page has a definition level stream
+    bool plain = false;    // not dictionary encoded
+    DataPage pg;
+};
+
+inline void appendLevelRun(std::vector<Run>& levels, int64_t at, uint64_t value, int64_t count) {
+    while (count > 0) {
+        const int64_t c = std::min<int64_t>(count, 0x40000000);
+        Run* prev = levels.empty() ? nullptr : &levels.back();
+        if (prev && !(prev->widthPacked & kPackedFlag) && prev->src == value && prev->start + prev->count == at && (int64_t)prev->count + c <= 0x40000000)
+            prev->count += (uint32_t)c;
+        else
+            levels.push_back(Run{at, value, (uint32_t)c, 1});
+        at += c;
+        count -= c;
+    }
+}
+
+inline void parsePage(const uint8_t* d, const PageDesc& pd, int ptype, int maxDef, int typeLength, bool hasDictionary, PageResult& r) {
+    const PageHeader& h = pd.h;
+    const size_t end = pd.end;
+    auto failed = [&](const std::string& m) { r.ok = false; r.why = m; };
+    DataPage& pg = r.pg;
+    pg.firstRow = pd.firstRow;
+    pg.rows = h.numValues;
+    pg.encoding = h.encoding;
+    size_t p = pd.body;
+    int64_t ones = 0;
+    if (h.type == DATA_PAGE) {
+        // v1: [repetition levels (absent at max level 0)][4-byte length + hybrid definition levels][values]
+        if (maxDef) {
+            if (h.defEncoding != RLE) return failed("not supported on the GPU path: definition level encoding " + std::to_string(h.defEncoding));
+            if (end - p < 4) return failed("corrupt Parquet page: no room for the level length");
+            const int32_t ln = le32(d + p);
+            if (ln < 0 || (uint64_t)ln > end - p - 4) return failed("corrupt Parquet page: definition levels exceed the page");
+            if (!scanHybrid(d, p + 4, p + 4 + (size_t)ln, 1, pg.rows, pd.firstRow, r.levels, &ones, true, r.why)) { r.ok = false; return; }
+            r.scanned = true;
+            p += 4 + (size_t)ln;
+        } else {
+            ones = pg.rows;
+        }
+    } else {
+        if (h.repBytes) return failed("not supported on the GPU path: repetition levels");
+        if (h.defBytes < 0 || (uint64_t)h.defBytes > end - p) return failed("corrupt Parquet page: definition levels exceed the page");
+        if (maxDef && h.defBytes) {
+            if (!scanHybrid(d, p, p + (size_t)h.defBytes, 1, pg.rows, pd.firstRow, r.levels, &ones, true, r.why)) { r.ok = false; return; }
+            r.scanned = true;
+        } else {
+            ones = pg.rows;
+        }
+        p += (size_t)h.defBytes;
+    }
+    pg.nonNull = ones;
+    if (h.type == DATA_PAGE_V2 && h.numNulls >= 0 && h.numNulls != pg.rows - ones) return failed("corrupt Parquet page: num_nulls disagrees with the definition levels");
+    pg.valuesOff = p;
+    pg.valuesEnd = end;
+    if (h.encoding == PLAIN_DICTIONARY || h.encoding == RLE_DICTIONARY) {
+        if (!hasDictionary) return failed("corrupt Parquet chunk: Dictionary is missing for Page");
+        pg.dictionaryEncoded = true;
+        if (pg.nonNull) {
+            if (p >= end) return failed("corrupt Parquet page: no dictionary id width");
+            const int width = d[p];
+            if (width > 32) return failed("corrupt Parquet page: dictionary id width " + std::to_string(width));
+            if (!scanHybrid(d, p + 1, end, width, pg.nonNull, 0, r.values, nullptr, false, r.why)) { r.ok = false; return; }
+        }
+    } else if (h.encoding == PLAIN) {
+        r.plain = true;
+        if (ptype == BYTE_ARRAY) return failed("not supported on the GPU path: PLAIN-encoded BYTE_ARRAY data pages (only dictionary-encoded var-width chunks)");
+        if (ptype == BOOLEAN) {  // bits, least significant first = one bit-packed run of width 1
+            if (((uint64_t)pg.nonNull + 7) / 8 > end - p) return failed("corrupt Parquet page: PLAIN booleans exceed the page");
+            int64_t doneV = 0;
+            while (doneV < pg.nonNull) {
+                const int64_t c = std::min<int64_t>(pg.nonNull - doneV, 0x40000000);
+                r.values.push_back(Run{doneV, (uint64_t)p * 8 + (uint64_t)doneV, (uint32_t)c, 1u | kPackedFlag});
+                doneV += c;
+            }
+        } else if ((uint64_t)pg.nonNull * valueWidth(ptype, typeLength) > end - p) {
+            return failed("corrupt Parquet page: PLAIN values exceed the page");
+        }
+    } else if (h.encoding == RLE && ptype == BOOLEAN) {  // ParquetEncoding.java:106-116, max "level" of BOOLEAN values = 1
+        r.plain = true;
+        if (end - p < 4) return failed("corrupt Parquet page: no room for the RLE length");
+        const int32_t ln = le32(d + p);
+        if (ln < 0 || (uint64_t)ln > end - p - 4) return failed("corrupt Parquet page: RLE booleans exceed the page");
+        if (pg.nonNull && !scanHybrid(d, p + 4, p + 4 + (size_t)ln, 1, pg.nonNull, 0, r.values, nullptr, false, r.why)) { r.ok = false; return; }
+    } else {
+        return failed("not supported on the GPU path: Parquet data page encoding " + std::to_string(h.encoding));
+    }
+}
+
+}  // namespace detail
+
+// Describes one column chunk. `why` starts with "not supported" for rejections of well-formed input. Three steps: the page
+// headers in file order (each says where the next one lies), the run headers of every data page (pages are independent:
+// `threads` > 1 walks them in parallel), then the pages' pieces put together in order (non-null prefix sums fix where each
+// page's values land).
+inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int64_t numValues, Chunk& out, std::string& why, int typeLength = 0, int threads = 1) {
     using namespace detail;
     if (maxDef < 0 || maxDef > 1) { why = "not supported on the GPU path: nested Parquet columns (max definition level " + std::to_string(maxDef) + ")"; return false; }
     if (!(ptype == BOOLEAN || ptype == INT32 || ptype == INT64 || ptype == DOUBLE || ptype == BYTE_ARRAY || ptype == FIXED_LEN_BYTE_ARRAY)) {
@@ -271,20 +383,21 @@ inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int6
     if (numValues < 0 || (!d && len)) { why = "corrupt Parquet chunk: bad arguments"; return false; }
     out = Chunk();
     out.rows = numValues;
-    std::vector<Run> levels;
+    // 1. page headers
+    std::vector<PageDesc> descs;
     size_t pos = 0;
-    int64_t done = 0, values = 0;
-    bool anyPlain = false;
+    int64_t done = 0;
     while (done < numValues) {
         if (pos >= len) { why = "corrupt Parquet chunk: ends after " + std::to_string(done) + " of " + std::to_string(numValues) + " values"; return false; }
         Reader r{d, len, pos};
-        PageHeader h;
+        PageDesc pd;
+        PageHeader& h = pd.h;
         if (!readPageHeader(r, h)) { why = "corrupt Parquet chunk: unreadable page header at byte " + std::to_string(pos); return false; }
         if (h.compressedSize != h.uncompressedSize) { why = "not supported on the GPU path: compressed Parquet pages (decompress before handing the chunk over)"; return false; }
-        const size_t body = r.pos;
-        if ((uint64_t)h.compressedSize > len - body) { why = "corrupt Parquet chunk: page exceeds the chunk"; return false; }
-        const size_t end = body + (size_t)h.compressedSize;
-        pos = end;
+        pd.body = r.pos;
+        if ((uint64_t)h.compressedSize > len - pd.body) { why = "corrupt Parquet chunk: page exceeds the chunk"; return false; }
+        pd.end = pd.body + (size_t)h.compressedSize;
+        pos = pd.end;
         if (h.type == INDEX_PAGE) continue;
         if (h.type == DICTIONARY_PAGE) {
             if (out.hasDictionary || done) { why = "corrupt Parquet chunk: dictionary page must be the first page"; return false; }
@@ -292,106 +405,61 @@ inline bool parseChunk(const uint8_t* d, size_t len, int ptype, int maxDef, int6
             if (ptype == BOOLEAN) { why = "not supported on the GPU path: dictionary-encoded BOOLEAN"; return false; }
             if (h.numValues < 0 || h.numValues > 0x7fffffff) { why = "corrupt Parquet chunk: dictionary size"; return false; }
             const int w = valueWidth(ptype, typeLength);
-            if (w && (uint64_t)h.numValues * w > end - body) { why = "corrupt Parquet chunk: dictionary values exceed the page"; return false; }
+            if (w && (uint64_t)h.numValues * w > pd.end - pd.body) { why = "corrupt Parquet chunk: dictionary values exceed the page"; return false; }
             out.hasDictionary = true;
             out.dictionaryCount = h.numValues;
-            out.dictionaryOff = body;
-            out.dictionaryEnd = end;
+            out.dictionaryOff = pd.body;
+            out.dictionaryEnd = pd.end;
             continue;
         }
         if (h.type != DATA_PAGE && h.type != DATA_PAGE_V2) { why = "not supported on the GPU path: Parquet page type " + std::to_string(h.type); return false; }
         if (h.numValues < 0 || h.numValues > numValues - done) { why = "corrupt Parquet chunk: pages hold more values than the metadata says"; return false; }
-        DataPage pg;
-        pg.firstRow = done;
-        pg.rows = h.numValues;
+        pd.firstRow = done;
+        done += h.numValues;
+        descs.push_back(pd);
+    }
+    // 2. run headers, page by page
+    std::vector<PageResult> res(descs.size());
+    auto walk = [&](size_t lo, size_t hi) {
+        for (size_t k = lo; k < hi; k++) parsePage(d, descs[k], ptype, maxDef, typeLength, out.hasDictionary, res[k]);
+    };
+    const size_t np = descs.size();
+    const size_t nt = std::min<size_t>((size_t)std::max(threads, 1), np / 32);  // at least 32 pages (~ 0.3 ms of walking) per thread: below that a thread costs more than it saves
+    if (nt > 1) {
+        std::vector<std::thread> workers;
+        for (size_t t = 1; t < nt; t++) workers.emplace_back(walk, np * t / nt, np * (t + 1) / nt);
+        walk(0, np / nt);
+        for (auto& w : workers) w.join();
+    } else {
+        walk(0, np);
+    }
+    // 3. assemble in page order
+    std::vector<Run> levels;
+    int64_t values = 0;
+    bool anyPlain = false;
+    for (size_t k = 0; k < np; k++) {
+        PageResult& r = res[k];
+        if (!r.ok) { why = r.why.empty() ? "corrupt Parquet page" : r.why; return false; }
+        DataPage& pg = r.pg;
+        if (r.scanned) {
+            for (const Run& run : r.levels) {
+                if (run.widthPacked & kPackedFlag) levels.push_back(run);
+                else appendLevelRun(levels, run.start, run.src, run.count);
+            }
+        } else {
+            appendLevelRun(levels, pg.firstRow, 1, pg.rows);  // no level stream: all present; keeps the chunk-wide stream gap-free
+        }
         pg.firstValue = values;
-        pg.encoding = h.encoding;
-        size_t p = body;
-        int64_t ones = 0;
-        bool scanned = false;
-        if (h.type == DATA_PAGE) {
-            // v1: [repetition levels (absent at max level 0)][4-byte length + hybrid definition levels][values]
-            if (maxDef) {
-                if (h.defEncoding != RLE) { why = "not supported on the GPU path: definition level encoding " + std::to_string(h.defEncoding); return false; }
-                if (end - p < 4) { why = "corrupt Parquet page: no room for the level length"; return false; }
-                const int32_t ln = le32(d + p);
-                if (ln < 0 || (uint64_t)ln > end - p - 4) { why = "corrupt Parquet page: definition levels exceed the page"; return false; }
-                if (!scanHybrid(d, p + 4, p + 4 + (size_t)ln, 1, pg.rows, done, levels, &ones, true, why)) return false;
-                scanned = true;
-                p += 4 + (size_t)ln;
-            } else {
-                ones = pg.rows;
-            }
-        } else {
-            if (h.repBytes) { why = "not supported on the GPU path: repetition levels"; return false; }
-            if (h.defBytes < 0 || (uint64_t)h.defBytes > end - p) { why = "corrupt Parquet page: definition levels exceed the page"; return false; }
-            if (maxDef && h.defBytes) {
-                if (!scanHybrid(d, p, p + (size_t)h.defBytes, 1, pg.rows, done, levels, &ones, true, why)) return false;
-                scanned = true;
-            } else {
-                ones = pg.rows;
-            }
-            p += (size_t)h.defBytes;
-        }
-        if (!scanned) {  // no level stream for this page: all present. Keeps the chunk-wide level stream gap-free.
-            Run* prev = levels.empty() ? nullptr : &levels.back();
-            int64_t left = pg.rows, at = done;
-            while (left > 0) {
-                const int64_t c = std::min<int64_t>(left, 0x40000000);
-                if (prev && !(prev->widthPacked & kPackedFlag) && prev->src == 1 && prev->start + prev->count == at && (int64_t)prev->count + c <= 0x40000000) {
-                    prev->count += (uint32_t)c;
-                } else {
-                    levels.push_back(Run{at, 1, (uint32_t)c, 1});
-                    prev = &levels.back();
-                }
-                at += c;
-                left -= c;
-            }
-        }
-        pg.nonNull = ones;
-        if (h.type == DATA_PAGE_V2 && h.numNulls >= 0 && h.numNulls != pg.rows - ones) { why = "corrupt Parquet page: num_nulls disagrees with the definition levels"; return false; }
-        pg.valuesOff = p;
-        pg.valuesEnd = end;
         pg.runLo = out.valueRuns.size();
-        if (h.encoding == PLAIN_DICTIONARY || h.encoding == RLE_DICTIONARY) {
-            if (!out.hasDictionary) { why = "corrupt Parquet chunk: Dictionary is missing for Page"; return false; }
-            pg.dictionaryEncoded = true;
-            out.anyDictionary = true;
-            if (pg.nonNull) {
-                if (p >= end) { why = "corrupt Parquet page: no dictionary id width"; return false; }
-                const int width = d[p];
-                if (width > 32) { why = "corrupt Parquet page: dictionary id width " + std::to_string(width); return false; }
-                if (!scanHybrid(d, p + 1, end, width, pg.nonNull, values, out.valueRuns, nullptr, false, why)) return false;
-            }
-        } else if (h.encoding == PLAIN) {
-            anyPlain = true;
-            if (ptype == BYTE_ARRAY) { why = "not supported on the GPU path: PLAIN-encoded BYTE_ARRAY data pages (only dictionary-encoded var-width chunks)"; return false; }
-            if (ptype == BOOLEAN) {  // bits, least significant first = one bit-packed run of width 1
-                if (((uint64_t)pg.nonNull + 7) / 8 > end - p) { why = "corrupt Parquet page: PLAIN booleans exceed the page"; return false; }
-                int64_t doneV = 0;
-                while (doneV < pg.nonNull) {
-                    const int64_t c = std::min<int64_t>(pg.nonNull - doneV, 0x40000000);
-                    out.valueRuns.push_back(Run{values + doneV, (uint64_t)p * 8 + (uint64_t)doneV, (uint32_t)c, 1u | kPackedFlag});
-                    doneV += c;
-                }
-            } else if ((uint64_t)pg.nonNull * valueWidth(ptype, typeLength) > end - p) {
-                why = "corrupt Parquet page: PLAIN values exceed the page";
-                return false;
-            }
-        } else if (h.encoding == RLE && ptype == BOOLEAN) {  // ParquetEncoding.java:106-116, max "level" of BOOLEAN values = 1
-            anyPlain = true;
-            if (end - p < 4) { why = "corrupt Parquet page: no room for the RLE length"; return false; }
-            const int32_t ln = le32(d + p);
-            if (ln < 0 || (uint64_t)ln > end - p - 4) { why = "corrupt Parquet page: RLE booleans exceed the page"; return false; }
-            if (pg.nonNull && !scanHybrid(d, p + 4, p + 4 + (size_t)ln, 1, pg.nonNull, values, out.valueRuns, nullptr, false, why)) return false;
-        } else {
-            why = "not supported on the GPU path: Parquet data page encoding " + std::to_string(h.encoding);
-            return false;
+        for (Run run : r.values) {
+            run.start += values;
+            out.valueRuns.push_back(run);
         }
         pg.runHi = out.valueRuns.size();
-        out.pages.push_back(pg);
-        done += pg.rows;
+        out.anyDictionary |= pg.dictionaryEncoded;
+        anyPlain |= r.plain;
         values += pg.nonNull;
+        out.pages.push_back(pg);
     }
     out.nonNull = values;
     out.allDictionary = out.anyDictionary && !anyPlain;

@@ -1257,6 +1257,13 @@ pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size
     return st ? st : updatePartialFill(p);
 }
 
+// host threads per chunk for the run-header walk: PGPU_PARQUET_THREADS, else the cores shared by the chunks walked at the same time
+static int parquetHostThreads(int concurrentChunks) {
+    if (const char* e = getenv("PGPU_PARQUET_THREADS")) return std::max(1, atoi(e));
+    const unsigned hw = std::thread::hardware_concurrency();
+    return (int)std::max(1u, std::min(16u, (hw ? hw : 1u) / (unsigned)std::max(concurrentChunks, 1)));
+}
+
 // ---- Parquet column chunks ------------------------------------------------------------------------------------------------
 // Stands in for ParquetReader.nextPage / readBlock -> PrimitiveColumnReader.readPrimitive
 // (lib/trino-parquet/src/main/java/io/trino/parquet/reader/ParquetReader.java:211-268, PrimitiveColumnReader.java:148-175):
@@ -1288,12 +1295,14 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
             return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: Parquet physical type " + std::to_string(pt) + " for a " + t.str() + " channel (channel " + std::to_string(c) + ")");
         if (in.num_values != rows) return fail(p, PGPU_INVALID_ARGUMENT, "channel " + std::to_string(c) + " holds " + std::to_string(in.num_values) + " values, the row group " + std::to_string(rows) + " rows");
     }
-    // the header walk of a chunk is sequential, the chunks are independent: one host thread per column chunk
+    // the chunks are independent and so are the pages of a chunk once their headers are known: one host thread per column chunk,
+    // each sharing the remaining cores over its pages
+    const int pageThreads = parquetHostThreads(nchunks);
     std::vector<std::string> whys((size_t)nchunks);
     auto parseOne = [&](int c) {
         const pgpu_parquet_chunk& in = chunks[c];
         const Type& t = plan.input[c];
-        if (!pq::parseChunk(in.data, in.len, in.physical_type, in.max_definition_level, in.num_values, ck[c], whys[c], in.type_length)) {
+        if (!pq::parseChunk(in.data, in.len, in.physical_type, in.max_definition_level, in.num_values, ck[c], whys[c], in.type_length, pageThreads)) {
             if (whys[c].empty()) whys[c] = "corrupt Parquet chunk";
             return;
         }
@@ -1470,7 +1479,7 @@ pgpu_status pgpu_parquet_inspect_chunk(const pgpu_parquet_chunk* chunk, int64_t*
     if (!chunk || !info) return PGPU_INVALID_ARGUMENT;
     pq::Chunk k;
     std::string why;
-    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length)) {
+    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length, parquetHostThreads(1))) {
         if (err && err_len) {
             strncpy(err, why.c_str(), err_len - 1);
             err[err_len - 1] = 0;
@@ -1496,7 +1505,7 @@ pgpu_status pgpu_parquet_chunk_runs(const pgpu_parquet_chunk* chunk, int32_t whi
     if (!chunk || !n) return PGPU_INVALID_ARGUMENT;
     pq::Chunk k;
     std::string why;
-    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length))
+    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length, parquetHostThreads(1)))
         return why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT;
     std::vector<pq::Run> pages;
     for (const pq::DataPage& pg : k.pages) pages.push_back(pq::Run{pg.firstValue, (uint64_t)pg.valuesOff, (uint32_t)pg.nonNull, pg.dictionaryEncoded ? 1u : 0u});

@@ -290,3 +290,27 @@ def test_fixed_len_byte_array_limits():
     assert st == N.NOT_SUPPORTED and "FIXED_LEN_BYTE_ARRAY" in err
     st, _, err = inspect(b, PP.FIXED_LEN_BYTE_ARRAY, 0, 1, 17)
     assert st == N.NOT_SUPPORTED
+
+
+def test_page_parallel_walk_gives_the_same_tables(monkeypatch):
+    """a chunk of 200 small pages walked by 1 and by 6 host threads (PGPU_PARQUET_THREADS): identical run and page tables"""
+    pytest.importorskip("pyarrow")
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    rng = np.random.default_rng(12)
+    n = 40_000
+    t = pa.table({"k": pa.array(rng.integers(0, 9, n).astype(np.int32), mask=rng.random(n) < 0.2), "b": pa.array(rng.random(n) < 0.3, mask=rng.random(n) < 0.1)})
+    buf = io.BytesIO()
+    pq.write_table(t, buf, compression="NONE", use_dictionary=["k"], data_page_size=128, write_batch_size=200, row_group_size=n)
+    (rows, cols), = chunks_of(buf.getvalue())
+    for name, (b, pt, md, nv, tl) in cols.items():
+        tables = []
+        for threads in ("1", "6"):
+            monkeypatch.setenv("PGPU_PARQUET_THREADS", threads)
+            st, info, err = inspect(b, pt, md, nv, tl)
+            assert st == N.OK and info[0] >= (64 if name == "k" else 30), (name, info, err)   # >= 64 pages: really walked by 2+ threads
+            tables.append([runs_of(b, pt, md, nv, which, tl) for which in (0, 1, 2)])
+        for a, c in zip(*tables):
+            assert np.array_equal(a, c), name
+        _, nulls, o = PP.decode_chunk(b, pt, md, nv, tl)
+        check_runs(name, b, pt, md, nv, nulls, o, tl)
