@@ -124,6 +124,7 @@ inline int gridFor(int64_t items) {
 
 }  // namespace
 
+#ifndef PGPU_HOST_EMULATION  // tests/emu/parquet_kernels_emu.cpp includes this file to run the kernels above thread by thread on the CPU
 cudaError_t pqLevelsToNullBits(cudaStream_t stream, const uint8_t* chunk, size_t chunkLen, const PqRun* runs, int64_t nruns, int64_t n, uint8_t* bits) {
     if (n <= 0) return cudaSuccess;
     k_pq_null_bits<<<gridFor((n + 7) / 8), kThreads, 0, stream>>>(chunk, chunkLen, runs, nruns, n, bits);
@@ -162,5 +163,6 @@ cudaError_t pqNullIds(cudaStream_t stream, int32_t* ids, const uint8_t* nulls, i
     k_pq_null_ids<<<gridFor(n), kThreads, 0, stream>>>(ids, nulls, n, nullId);
     return cudaGetLastError();
 }
+#endif  // PGPU_HOST_EMULATION
 
 }  // namespace pgpu
