@@ -314,3 +314,32 @@ def test_page_parallel_walk_gives_the_same_tables(monkeypatch):
             assert np.array_equal(a, c), name
         _, nulls, o = PP.decode_chunk(b, pt, md, nv, tl)
         check_runs(name, b, pt, md, nv, nulls, o, tl)
+
+
+def test_host_parser_under_sanitizers(tmp_path):
+    """csrc/parquet_host.h compiled with AddressSanitizer + UBSan (tests/emu/parquet_host_fuzz.cpp): 150 mutations / truncations of
+    every golden chunk, parsed with 1 and 4 page threads from an exactly sized heap copy — no out-of-bounds access, and every
+    accepted chunk's run / page tables stay inside the chunk (what the device kernels will read)"""
+    import shutil
+    import subprocess
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    here = os.path.dirname(os.path.abspath(__file__))
+    exe = str(tmp_path / "parquet_host_fuzz")
+    r = subprocess.run(["g++", "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", "-fno-sanitize-recover=all", "-pthread", "-o", exe,
+                        os.path.join(here, "emu", "parquet_host_fuzz.cpp")], capture_output=True, text=True)
+    if r.returncode != 0 and "asan" in r.stderr.lower():
+        pytest.skip("sanitizer runtime not installed")
+    assert r.returncode == 0, r.stderr
+    accepted = rejected = 0
+    for fname in ("nullable_v2.parquet", "lineitem_v1.parquet"):
+        for rows, cols in chunks_of(os.path.join(GOLDEN, fname)):
+            for name, (b, pt, md, nv, tl) in cols.items():
+                path = tmp_path / "chunk.bin"
+                path.write_bytes(b)
+                r = subprocess.run([exe, str(path), str(pt), str(md), str(nv), str(tl), "150", "11"], capture_output=True, text=True)
+                assert r.returncode == 0, (fname, name, r.returncode, r.stderr[-2000:])
+                a, j = map(int, r.stdout.split())
+                accepted += a
+                rejected += j
+    assert accepted > 1000 and rejected > 1000
