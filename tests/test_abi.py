@@ -155,3 +155,31 @@ def test_null_arguments_do_not_crash():
     assert L.pgpu_finish(None) == N.INVALID_ARGUMENT
     L.pgpu_pipeline_destroy(None)
     assert L.pgpu_output_channel_count(None) == 0
+
+
+def test_plan_parser_under_sanitizers(tmp_path):
+    """csrc/plan.cpp compiled with AddressSanitizer + UBSan (tests/emu/plan_fuzz.cpp): 400 random edits of each benchmark / known-answer
+    plan are accepted or rejected with a PlanError — no crash, no out-of-bounds access, no undefined behaviour"""
+    import shutil
+    import subprocess
+    import kat_cases
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "plan_fuzz")
+    r = subprocess.run(["g++", "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", "-fno-sanitize-recover=all", "-I" + os.path.join(root, "include"), "-o", exe,
+                        os.path.join(root, "tests", "emu", "plan_fuzz.cpp"), os.path.join(root, "presto_b200", "csrc", "plan.cpp")], capture_output=True, text=True)
+    if r.returncode != 0 and "asan" in r.stderr.lower():
+        pytest.skip("sanitizer runtime not installed")
+    assert r.returncode == 0, r.stderr
+    plans = [tpch.q1_plan(), tpch.q1_plan("partial"), tpch.q6_plan(), tpch.q1_decimal_plan(), tpch.highcard_plan(1000)] + [c[1] for c in kat_cases.conditional_cases()]
+    accepted = rejected = 0
+    for i, plan in enumerate(plans):
+        path = tmp_path / "plan.txt"
+        path.write_text(plan)
+        r = subprocess.run([exe, str(path), "400", str(i)], capture_output=True, text=True)
+        assert r.returncode == 0, (i, r.returncode, r.stderr[-2000:])
+        a, j = map(int, r.stdout.split())
+        accepted += a
+        rejected += j
+    assert accepted >= len(plans) and rejected > 1000
