@@ -183,3 +183,33 @@ def test_plan_parser_under_sanitizers(tmp_path):
         accepted += a
         rejected += j
     assert accepted >= len(plans) and rejected > 1000
+
+
+def test_code_generator_under_sanitizers(tmp_path):
+    """csrc/plan.cpp + codegen.cpp compiled with AddressSanitizer + UBSan (tests/emu/codegen_asan.cpp): the kernel source of every
+    benchmark / known-answer / operator plan is generated for every sampled combination of block encodings and null vectors"""
+    import shutil
+    import subprocess
+    import kat_cases
+    import operator_cases
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "codegen_asan")
+    csrc = os.path.join(root, "presto_b200", "csrc")
+    r = subprocess.run(["g++", "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", "-fno-sanitize-recover=all", "-o", exe,
+                        os.path.join(root, "tests", "emu", "codegen_asan.cpp"), os.path.join(csrc, "plan.cpp"), os.path.join(csrc, "codegen.cpp")], capture_output=True, text=True)
+    if r.returncode != 0 and "asan" in r.stderr.lower():
+        pytest.skip("sanitizer runtime not installed")
+    assert r.returncode == 0, r.stderr
+    plans = [tpch.q1_plan(), tpch.q1_plan("partial"), tpch.q6_plan(), tpch.q1_decimal_plan(), tpch.highcard_plan(1000), tpch.highcard_plan(1 << 22)]
+    plans += [c[1] for c in kat_cases.all_cases()] + [c[1] for c in operator_cases.value_cases()]
+    paths = []
+    for i, plan in enumerate(plans):
+        path = tmp_path / ("plan%d.txt" % i)
+        path.write_text(plan)
+        paths.append(str(path))
+    r = subprocess.run([exe] + paths, capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stderr[-3000:])
+    generated, rejected, size = map(int, r.stdout.split())
+    assert generated > 10 * len(plans) and size > 1 << 20
