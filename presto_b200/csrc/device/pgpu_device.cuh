@@ -95,6 +95,13 @@ struct OutArgs {
 };
 
 // ------------------------------------------------------------------------------------------------ loads
+#ifdef PGPU_HOST_EMULATION
+// tests/emu/expr_emu.py compiles this header's scalar part and a plan's generated P::eval_project as plain C++ to run the
+// expression code on the CPU against the known answers; the kernels below the scalar section are not part of that build.
+PGPU_DEV int4 ld_stream16(const void* p) { int4 r; memcpy(&r, p, 16); return r; }
+PGPU_DEV u32 ld_stream4(const void* p) { u32 r; memcpy(&r, p, 4); return r; }
+PGPU_DEV u64 ld_stream8(const void* p) { u64 r; memcpy(&r, p, 8); return r; }
+#else
 PGPU_DEV int4 ld_stream16(const void* p) {
     int4 r;
     asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
@@ -110,6 +117,7 @@ PGPU_DEV u64 ld_stream8(const void* p) {
     asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(r) : "l"(p));
     return r;
 }
+#endif  // PGPU_HOST_EMULATION
 
 // Load the R (=4) consecutive elements [base, base+4) of a flat column. `full` = the whole tile is in range and the
 // column pointer is 16-byte aligned (host guarantees alignment; base is a multiple of 4).
@@ -339,6 +347,7 @@ PGPU_DEV void window_varchar(u64 wlo, u64 whi, i32 rel, i32 len, u64& x, u32& er
     x = (u64)(u32)len | (d << 8);
 }
 
+#ifndef PGPU_HOST_EMULATION  // everything below needs a GPU: warp operations, atomics, shared memory, the kernels
 // ------------------------------------------------------------------------------------------------ hashing / warp ops
 PGPU_DEV u64 mix64(u64 x) {  // splitmix64 finaliser; table placement only, never observable
     x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
@@ -1542,3 +1551,4 @@ PGPU_DEV void body_emit_global(const Scratch& sc, const OutArgs<P::NO>& out) {
         if (err) atomicOr(sc.err, err);
     }
 }
+#endif  // PGPU_HOST_EMULATION
