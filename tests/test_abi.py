@@ -213,3 +213,24 @@ def test_code_generator_under_sanitizers(tmp_path):
     assert r.returncode == 0, (r.returncode, r.stderr[-3000:])
     generated, rejected, size = map(int, r.stdout.split())
     assert generated > 10 * len(plans) and size > 1 << 20
+
+
+def test_intermediate_step_differs_from_final_only_in_the_output_section():
+    """the kernel source generated for an INTERMEDIATE step is the FINAL step's except for the output section (which writes the
+    accumulator cells out as states, like PARTIAL, instead of finalising them): the input side — state channels into cells — is the
+    code that has run on the GPU as the FINAL step since round 1"""
+    import difflib
+    from test_oracle_protocol import q1_stage_plan
+
+    def source(plan, n):
+        op = GpuPipelineOperator(plan, device=-1)
+        op.compileSignature([0] * n, [False] * n)
+        s = [line.strip() for line in op.generatedSource().splitlines() if not line.startswith("//")]
+        op.close()
+        return s
+    final, inter = source(q1_stage_plan("final"), 17), source(q1_stage_plan("intermediate"), 17)
+    diff = [d for d in difflib.unified_diff(final, inter, lineterm="", n=0) if d[:1] in "+-" and d[:3] not in ("+++", "---")]
+    assert len(diff) > 20
+    assert all("out.c[" in d or d[1:].strip() in ("{", "}") or "NO =" in d for d in diff), [d for d in diff if "out.c[" not in d][:5]
+    states = [d for d in diff if d.startswith("+") and "cells[" in d]
+    assert len(states) == 8 and all("/" not in d for d in states)     # 8 aggregates, none divided (avg stays sum + count)
