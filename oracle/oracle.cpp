@@ -519,8 +519,34 @@ static Vec evalExpr(const Expr& e, const EvalCtx& cx, const std::vector<int32_t>
             return r;
         }
         case ExprKind::CALL: {
+            // BytecodeUtils.generateFullInvocation (main/sql/gen/BytecodeUtils.java:244-310): arguments are evaluated left to right and
+            // the call is left as soon as one is NULL — a later argument is not evaluated (and cannot raise) at that position
             std::vector<Vec> a;
-            for (auto& x : e.args) a.push_back(evalExpr(*x, cx, pos));
+            std::vector<char> dead(n, 0);
+            bool anyDead = false;
+            for (auto& x : e.args) {
+                if (!anyDead) {
+                    a.push_back(evalExpr(*x, cx, pos));
+                } else {
+                    std::vector<int32_t> live;
+                    std::vector<size_t> at;
+                    for (size_t k = 0; k < n; k++)
+                        if (!dead[k]) { live.push_back(pos[k]); at.push_back(k); }
+                    Vec full = scatterNew(x->type, n);
+                    full.null.assign(n, 1);
+                    if (!live.empty()) {
+                        Vec part = evalExpr(*x, cx, live);
+                        for (size_t j = 0; j < at.size(); j++) {
+                            if (part.isNull(j)) continue;
+                            full.null[at[j]] = 0;
+                            copyAt(full, at[j], part, j);
+                        }
+                    }
+                    a.push_back(std::move(full));
+                }
+                for (size_t k = 0; k < n; k++)
+                    if (a.back().isNull(k)) { dead[k] = 1; anyDead = true; }
+            }
             switch (e.op) {
                 case Op::EQ: case Op::NE: case Op::LT: case Op::LE: case Op::GT: case Op::GE: return compareOp(e.op, a[0], a[1]);
                 case Op::NOT: {

@@ -13,6 +13,7 @@
 #include "codegen.h"
 
 #include <algorithm>
+#include <cctype>
 #include <cstdlib>
 #include <map>
 #include <set>
@@ -538,9 +539,50 @@ struct Gen {
         return r;
     }
 
+    // Faults of code that the reference would not have run. BytecodeUtils.generateFullInvocation (main/sql/gen/BytecodeUtils.java:
+    // 244-310) evaluates a call's arguments left to right and jumps past the rest of the call as soon as one is NULL
+    // (ifWasNullPopAndGoto after every NEVER_NULL argument): a later argument is not evaluated, the operator is not invoked, so
+    // neither can raise. The straight-line code here evaluates everything (values under NULL positions are arbitrary), so the
+    // error bits of the code emitted since `mark` go to a private word that only counts when `nullExpr` is false.
+    void guardFaults(size_t mark, const std::string& nullExpr) {
+        if (nullExpr.empty()) return;
+        std::string all = out.str();
+        std::string tail = all.substr(mark);
+        std::string renamed;
+        const std::string name = tmp("e");
+        bool any = false;
+        for (size_t i = 0; i < tail.size();) {
+            const bool startsWord = i == 0 || !(isalnum((unsigned char)tail[i - 1]) || tail[i - 1] == '_');
+            if (startsWord && tail.compare(i, 3, "err") == 0 && (i + 3 >= tail.size() || !(isalnum((unsigned char)tail[i + 3]) || tail[i + 3] == '_'))) {
+                renamed += name;
+                i += 3;
+                any = true;
+            } else {
+                renamed += tail[i++];
+            }
+        }
+        if (!any) return;
+        const std::string pad(indent * 4, ' ');
+        out.str(all.substr(0, mark) + pad + "u32 " + name + " = 0;\n" + renamed + pad + "if (!(" + nullExpr + ")) err |= " + name + ";\n");
+        out.seekp(0, std::ios::end);
+    }
+
     Val genCall(const Expr& e) {
         std::vector<Val> a;
-        for (auto& x : e.args) a.push_back(gen(*x));
+        std::string earlierNull;  // some earlier argument of this call is NULL
+        for (auto& x : e.args) {
+            const size_t mark = (size_t)out.tellp();
+            a.push_back(gen(*x));
+            guardFaults(mark, earlierNull);
+            earlierNull = nullOr(earlierNull, a.back().n);
+        }
+        const size_t mark = (size_t)out.tellp();
+        Val r = genCallOp(e, a);
+        guardFaults(mark, earlierNull);
+        return r;
+    }
+
+    Val genCallOp(const Expr& e, std::vector<Val>& a) {
         Val r;
         r.type = e.type;
         for (auto& x : a) r.n = nullOr(r.n, x.n);
