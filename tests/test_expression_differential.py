@@ -162,3 +162,37 @@ def test_a_null_argument_stops_the_evaluation_of_the_later_ones():
     page = [Page(dirty, block_of(BIGINT, [1, 1]), block_of(BIGINT, [1, 1]))]
     got, err = execute(plan, page)
     assert err == 0 and got == run_oracle(plan, page) == [(None, None), (6, 4)]
+
+
+def test_casts_at_the_boundaries():
+    """every cast the plan language accepts between BIGINT / INTEGER / DOUBLE / BOOLEAN / DECIMAL(p,s), over boundary values one row at
+    a time: same value (rounding included) or matching fault on both sides"""
+    d5_2, d12_2, d18_0, d20_4, d38_10 = (createDecimalType(*x) for x in ((5, 2), (12, 2), (18, 0), (20, 4), (38, 10)))
+    types = [BIGINT, INTEGER, DOUBLE, BOOLEAN, d5_2, d12_2, d18_0, d20_4, d38_10]
+
+    def samples(t):
+        if t is BIGINT:
+            return [I64_MIN, I64_MIN + 1, -10 ** 18, I32_MIN - 1, I32_MIN, -100000, -1, 0, 1, 99999, I32_MAX, I32_MAX + 1, 10 ** 18, I64_MAX, None]
+        if t is INTEGER:
+            return [I32_MIN, -100000, -1, 0, 1, 999, 99999, I32_MAX, None]
+        if t is DOUBLE:
+            return [0.0, -0.0, 0.5, -0.5, 1.5, 2.5, 0.005, 0.015, 999.995, 999.994999, -999.995, 1e10, -1e10, 1e19, 1e38, 1e39, float("nan"), float("inf"), 123456.789, None]
+        if t is BOOLEAN:
+            return [True, False, None]
+        top = 10 ** t.precision - 1
+        half = 5 * 10 ** max(t.scale - 1, 0)
+        return [-top, -top + 1, -half, -half + 1, -1, 0, 1, half - 1, half, half + 1, 10 ** t.scale, 15 * 10 ** max(t.scale - 1, 0), top - 1, top, None]
+    supported, outcomes = 0, set()
+    for f in types:
+        for to in types:
+            if f == to:
+                continue
+            plan = plan_text([f, f], None, [call("cast", to, field(0, f))])
+            try:
+                GpuPipelineOperator(plan, device=-1).close()
+            except TrinoException as e:
+                assert e.code == "NOT_SUPPORTED", (f, to, e)
+                continue
+            supported += 1
+            outcomes |= check_row_by_row(plan, f, [(v, v) for v in samples(f)])
+    assert supported >= 20 and {None, "NUMERIC_VALUE_OUT_OF_RANGE", "INVALID_CAST_ARGUMENT"} <= outcomes
