@@ -196,3 +196,26 @@ def test_casts_at_the_boundaries():
             supported += 1
             outcomes |= check_row_by_row(plan, f, [(v, v) for v in samples(f)])
     assert supported >= 20 and {None, "NUMERIC_VALUE_OUT_OF_RANGE", "INVALID_CAST_ARGUMENT"} <= outcomes
+
+
+def test_short_circuit_forms_do_not_raise_in_untaken_branches():
+    """AND / OR (AndCodeGenerator / OrCodeGenerator stop at the first FALSE / TRUE), IF and COALESCE evaluate only what they need: a
+    division by zero in an operand that is not reached is not raised; where it is reached, it is — identically in the oracle and in
+    the generated code"""
+    X, Y = field(0, BIGINT), field(1, BIGINT)
+    one, zero = constant(1, BIGINT), constant(0, BIGINT)
+    faulty = compare("eq", call("divide", BIGINT, one, Y), one)             # 1 / y = 1
+    from presto_b200.relational import and_, or_
+    plans = {"and": plan_text([BIGINT, BIGINT], None, [and_(compare("lt", X, zero), faulty)]),
+             "or": plan_text([BIGINT, BIGINT], None, [or_(compare("ge", X, zero), faulty)]),
+             "if": plan_text([BIGINT, BIGINT], None, [SpecialForm("IF", BIGINT, [compare("lt", X, zero), call("divide", BIGINT, one, Y), X])]),
+             "coalesce": plan_text([BIGINT, BIGINT], None, [SpecialForm("COALESCE", BIGINT, [X, call("divide", BIGINT, one, Y)])]),
+             "filter": plan_text([BIGINT, BIGINT], and_(compare("lt", X, zero), faulty), [X])}
+    pairs = [(5, 0), (-5, 0), (5, 1), (-5, 1), (None, 0), (None, 1), (0, None), (-1, None)]
+    for name, plan in plans.items():
+        seen = check_row_by_row(plan, BIGINT, pairs)
+        assert seen == {None, "DIVISION_BY_ZERO"}, (name, seen)
+    # and the unreached operand really is unreached: x >= 0 with y = 0 gives FALSE / TRUE / x / x without a fault
+    for name, want in (("and", [(False,)]), ("or", [(True,)]), ("if", [(5,)]), ("coalesce", [(5,)]), ("filter", [])):
+        got, err = execute(plans[name], [Page(block_of(BIGINT, [5]), block_of(BIGINT, [0]))])
+        assert err == 0 and got == want, name
