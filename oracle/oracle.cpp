@@ -443,9 +443,35 @@ static Vec evalExpr(const Expr& e, const EvalCtx& cx, const std::vector<int32_t>
         case ExprKind::CONST: return constantVec(e, n);
         case ExprKind::AND:
         case ExprKind::OR: return evalLogic(e, cx, pos);
-        case ExprKind::BETWEEN: {  // BetweenCodeGenerator: value >= min AND value <= max
-            Vec v = evalExpr(*e.args[0], cx, pos), lo = evalExpr(*e.args[1], cx, pos), hi = evalExpr(*e.args[2], cx, pos);
-            return logic2(true, compareOp(Op::GE, v, lo), compareOp(Op::LE, v, hi));
+        case ExprKind::BETWEEN: {
+            // BetweenCodeGenerator: value >= min AND value <= max, the value evaluated once. min is an argument of the first comparison
+            // (skipped where the value is NULL); max of the second, which AND evaluates only where the first is not FALSE.
+            auto evalWhere = [&](const Expr& x, const std::vector<char>& live) {
+                std::vector<int32_t> sub;
+                std::vector<size_t> at;
+                for (size_t k = 0; k < n; k++)
+                    if (live[k]) { sub.push_back(pos[k]); at.push_back(k); }
+                if (at.size() == n) return evalExpr(x, cx, pos);
+                Vec full = scatterNew(x.type, n);
+                full.null.assign(n, 1);
+                if (!sub.empty()) {
+                    Vec part = evalExpr(x, cx, sub);
+                    for (size_t j = 0; j < at.size(); j++) {
+                        if (part.isNull(j)) continue;
+                        full.null[at[j]] = 0;
+                        copyAt(full, at[j], part, j);
+                    }
+                }
+                return full;
+            };
+            Vec v = evalExpr(*e.args[0], cx, pos);
+            std::vector<char> live(n, 1);
+            for (size_t k = 0; k < n; k++) live[k] = !v.isNull(k);
+            Vec lo = evalWhere(*e.args[1], live);
+            Vec ge = compareOp(Op::GE, v, lo);
+            for (size_t k = 0; k < n; k++) live[k] = !v.isNull(k) && !(!ge.isNull(k) && !ge.i[k]);
+            Vec hi = evalWhere(*e.args[2], live);
+            return logic2(true, ge, compareOp(Op::LE, v, hi));
         }
         case ExprKind::IN: {  // InCodeGenerator: NULL value -> NULL; no match and a NULL member -> NULL
             Vec v = evalExpr(*e.args[0], cx, pos);

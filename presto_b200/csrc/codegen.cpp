@@ -674,8 +674,18 @@ struct Gen {
             case ExprKind::AND:
             case ExprKind::OR: return genLogic(e);
             case ExprKind::BETWEEN: {
-                Val v = gen(*e.args[0]), lo = gen(*e.args[1]), hi = gen(*e.args[2]);
-                Val ge = compare(Op::GE, v, lo), le = compare(Op::LE, v, hi);
+                // BetweenCodeGenerator: value >= min AND value <= max, the value evaluated once. min is the second argument of the first
+                // comparison (not evaluated when the value is NULL); max belongs to the second comparison, which AND reaches only when
+                // the first is not FALSE: faults of the bounds count under those conditions only.
+                Val v = gen(*e.args[0]);
+                const size_t m1 = (size_t)out.tellp();
+                Val lo = gen(*e.args[1]);
+                guardFaults(m1, v.n);
+                Val ge = compare(Op::GE, v, lo);
+                const size_t m2 = (size_t)out.tellp();
+                Val hi = gen(*e.args[2]);
+                guardFaults(m2, nullOr(v.n, ge.nullable() ? "(!" + ge.n + " && !" + ge.v + ")" : "(!" + ge.v + ")"));
+                Val le = compare(Op::LE, v, hi);
                 return logic(true, {ge, le});
             }
             case ExprKind::IN: return genIn(e);

@@ -219,3 +219,25 @@ def test_short_circuit_forms_do_not_raise_in_untaken_branches():
     for name, want in (("and", [(False,)]), ("or", [(True,)]), ("if", [(5,)]), ("coalesce", [(5,)]), ("filter", [])):
         got, err = execute(plans[name], [Page(block_of(BIGINT, [5]), block_of(BIGINT, [0]))])
         assert err == 0 and got == want, name
+
+
+def test_between_evaluates_its_bounds_like_the_reference():
+    """BetweenCodeGenerator: value >= min AND value <= max. A faulting upper bound is not reached where value < min, neither bound where
+    the value is NULL; where they are reached the fault is raised — oracle and generated code alike"""
+    V, Y = field(0, BIGINT), field(1, BIGINT)
+    ten = constant(10, BIGINT)
+    hundred_over_y = call("divide", BIGINT, constant(100, BIGINT), Y)
+    upper = plan_text([BIGINT, BIGINT], None, [SpecialForm("BETWEEN", BOOLEAN, [V, ten, hundred_over_y])])
+    lower = plan_text([BIGINT, BIGINT], None, [SpecialForm("BETWEEN", BOOLEAN, [V, hundred_over_y, ten])])
+    pairs = [(5, 0), (15, 0), (15, 2), (60, 2), (None, 0), (None, 2), (15, None), (5, None), (10, 10), (10, 0)]
+    for plan in (upper, lower):
+        assert check_row_by_row(plan, BIGINT, pairs) == {None, "DIVISION_BY_ZERO"}
+    for plan, row, want in ((upper, (5, 0), [(False,)]), (upper, (None, 0), [(None,)]), (lower, (None, 0), [(None,)]), (upper, (15, None), [(None,)]), (upper, (5, None), [(False,)])):
+        page = [Page(block_of(BIGINT, [row[0]]), block_of(BIGINT, [row[1]]))]
+        got, err = execute(plan, page)
+        assert err == 0 and got == want == run_oracle(plan, page), (row, got)
+    for plan, row in ((upper, (15, 0)), (lower, (15, 0))):
+        page = [Page(block_of(BIGINT, [row[0]]), block_of(BIGINT, [row[1]]))]
+        with pytest.raises(TrinoException):
+            run_oracle(plan, page)
+        assert execute(plan, page)[1] & ERR_BITS["DIVISION_BY_ZERO"]
