@@ -1,15 +1,21 @@
 #!/usr/bin/env python
-"""bench.py — TPC-H Q1 (BASELINE.json configs[1]) lineitem rows/s on N B200s, with the kernel roofline and a CPU
-baseline. One "step" = one full pass of the fused scan->filter->project->hash-aggregate pipeline over the
-synthetic lineitem table (device-resident for `value`, pinned host pages for `e2e`).
+"""bench.py — TPC-H Q1 (BASELINE.json configs[1]) lineitem rows/s on N B200s, with the kernel roofline, a CPU baseline, an
+end-to-end leg at the reference's page shape and the other north_star configs as sub-records.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload q1|q6|highcard|q1dict]
-                  [--rows R]
+One "step" = one full pass of the fused scan->filter->project->hash-aggregate pipeline over the rank's lineitem shard
+(device-resident for `value`; 1 M-row host pages in ordinary pageable memory through pgpu_add_page for `e2e`).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                  [--workload q1|q6|highcard|highcard_shuffled|q1dict] [--rows R]
+
+Without --workload the line is the Q1 headline plus `configs` = {q6, highcard, highcard_shuffled, q1dict} sub-records
+(N > 1: {highcard}), every record checked against the CPU oracle on a prefix of the very rows it timed.
 """
 import argparse
 import ctypes
 import json
 import os
+import struct
 import subprocess
 import sys
 import threading
@@ -19,10 +25,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 SF100_ROWS = 600_037_902  # TPC-H lineitem at sf100
-# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the ncu --set full captures under
-# profiles/ (bytes; None = not captured for that workload)
-# stored as measured DRAM bytes / algorithmic bytes of the captured launch (profiles/r01e_q1_staged_ncu_raw.txt)
-TRAFFIC_RATIO = {"q1": 1.0014}
+SUB_CONFIGS = ("q6", "highcard", "highcard_shuffled", "q1dict")
 
 
 def parse_args():
@@ -31,23 +34,29 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="q1", choices=["q1", "q6", "highcard", "highcard_shuffled", "q1dict"])
+    ap.add_argument("--workload", default=None, choices=["q1", "q6", "highcard", "highcard_shuffled", "q1dict"],
+                    help="one workload only (default: the Q1 headline + the other configs as sub-records)")
     ap.add_argument("--rows", type=int, default=SF100_ROWS, help="lineitem rows per GPU")
     ap.add_argument("--data", default="synthetic", choices=["synthetic", "dbgen"],
                     help="synthetic: counter-based columns with the TPC-H value distributions (--rows per GPU); dbgen: the tpch connector's real rows "
                          "(spec-conformant generator, --sf per GPU; rows per GPU follow from the order range)")
     ap.add_argument("--sf", type=float, default=100.0, help="--data dbgen: TPC-H scale factor per GPU")
     ap.add_argument("--e2e-rows", type=int, default=0, help="rows of the end-to-end (host pages) leg; 0 = same as --rows if RAM allows")
-    ap.add_argument("--cpu-rows-per-core", type=int, default=4_000_000)
+    ap.add_argument("--page-rows", type=int, default=1_000_000, help="rows per host page of the end-to-end leg")
+    ap.add_argument("--verify-rows", type=int, default=64_000_000, help="prefix of the timed rows checked against the CPU oracle (0 = skip)")
+    ap.add_argument("--cpu-rows-per-core", type=int, default=4_000_000, help="--impl reference: rows per host thread and step")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N > 1, large group counts: FINAL reads the peers' partitions over NVLink (peer) or NCCL all-to-all first (nccl)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="headline only")
     return ap.parse_args()
 
 
 def workload_def(name, rows, dbgen_sf=None):
     wl = _workload_def(name, rows)
+    wl["name"] = name
+    wl["rows"] = rows
     if dbgen_sf is not None:
         from presto_b200 import tpch
         if name == "highcard_shuffled":
@@ -134,7 +143,6 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -143,78 +151,156 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s; MEASURED_PEAKS.json absent)"
 
 
-# ------------------------------------------------------------------------------------------------ CPU baseline
-def cpu_run(wl, rows_per_core, cores, repeats=1):
-    """The CPU oracle (oracle/, the C++ restatement of the reference's loops — the reference itself is Java and there
-    is no JVM on this box) on all host cores: one PARTIAL pipeline per thread over its own row range, page-at-a-time
-    (1 M-row pages), then one FINAL pipeline over the partial outputs (the analogue of task_concurrency drivers +
-    the partial->final exchange). Data generation is outside the timed region. Returns rows/s."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from oracle_op import OracleOperator
-    from presto_b200.operators import toPages
-    from presto_b200.spi import Page
-    total = rows_per_core * cores
-    page_rows = 1_000_000
-    shards = []
-    for t in range(cores):
-        pages, r0 = [], t * rows_per_core
-        end = r0 + rows_per_core
-        while r0 < end:
-            n = min(page_rows, end - r0)
-            pages.append(wl["page"](r0, n, total))
-            r0 += n
-        shards.append(pages)
-    total = sum(p.position_count for pages in shards for p in pages)
-    partial_plan = wl["plan"]("partial")
-    best = None
-    result = None
-    for _ in range(repeats):
-        outs = [None] * cores
-
-        def work(t):
-            op = OracleOperator(partial_plan)
-            outs[t] = toPages(op, shards[t])
-            op.close()
-
-        t0 = time.perf_counter()
-        th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
-        for x in th:
-            x.start()
-        for x in th:
-            x.join()
-        # FINAL step over the partial pages
-        from presto_b200.tpch import plan_text  # noqa: F401
-        final_plan = final_plan_for(wl, partial_plan)
-        fop = OracleOperator(final_plan)
-        pages = [p for o in outs for p in o]
-        result = toPages(fop, pages)
-        fop.close()
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
-    return total / best, total, result
+def measured_traffic(name):
+    """DRAM bytes per row of the workload's dominant kernel from the last `ncu --set full` capture (profiles/traffic.json,
+    written by tools/collect_profiles.py from dram__bytes_read.sum + dram__bytes_write.sum), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        return json.load(f).get(name)
 
 
-def final_plan_for(wl, partial_plan):
-    """FINAL-step plan whose input channels are the PARTIAL plan's output channels."""
-    from presto_b200.operators import Aggregation, GpuPipelineOperator, plan_text
-    import re
-    from presto_b200 import tpch
-    from presto_b200.spi import BIGINT, DOUBLE
-    name = wl["name"]
-    if name in ("q1", "q1dict"):
-        # partial output: returnflag, linestatus, then per aggregate its intermediate channels
-        inp = [tpch.VARCHAR1, tpch.VARCHAR1] + [BIGINT, DOUBLE] * 4 + [DOUBLE, BIGINT] * 3 + [BIGINT]
-        aggs = [Aggregation("sum", DOUBLE, 2, DOUBLE), Aggregation("sum", DOUBLE, 4, DOUBLE), Aggregation("sum", DOUBLE, 6, DOUBLE),
-                Aggregation("sum", DOUBLE, 8, DOUBLE), Aggregation("avg", DOUBLE, 10, DOUBLE), Aggregation("avg", DOUBLE, 12, DOUBLE),
-                Aggregation("avg", DOUBLE, 14, DOUBLE), Aggregation("count", BIGINT, 16, BIGINT)]
-        return plan_text(inp, step="final", groupByChannels=[0, 1], aggregations=aggs)
-    if name == "q6":
-        return plan_text([BIGINT, DOUBLE], step="final", aggregations=[Aggregation("sum", DOUBLE, 0, DOUBLE)])
-    return plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0], aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)],
-                     expectedGroups=max(wl.get("rows", 40_000_000) // 4, 1000))
+# ------------------------------------------------------------------------------------------------ host pages
+def h2d_ceiling(device, mb=512, reps=6):
+    """Plain pinned host -> device copy bandwidth of this process's GPU (GB/s): what the link gives when nothing else is in the way."""
+    import torch
+    n = mb << 20
+    h = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    d = torch.empty(n, dtype=torch.uint8, device="cuda:%d" % device)
+    d.copy_(h, non_blocking=True)
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        d.copy_(h, non_blocking=True)
+    e1.record()
+    e1.synchronize()
+    return reps * n / (e0.elapsed_time(e1) / 1e3) / 1e9
 
 
-# ------------------------------------------------------------------------------------------------ GPU legs
+class HostTable:
+    """The rank's shard as a Trino worker holds it: one ordinary (pageable) numpy array per block array, cut into pages of
+    page_rows positions. The bytes are the device columns copied back, so host pages and device page hold identical rows."""
+    WIDTH = {0: 1, 1: 8, 2: 4, 3: 4, 4: 8}
+
+    def __init__(self, device, wl, dp, rows):
+        import numpy as np
+        from presto_b200 import _native as N
+        self.N, self.np = N, np
+        L = N.lib()
+        self.rows = rows
+        self.spec = wl["spec"]
+        self.ncol = len(self.spec)
+        self.arrays = []       # per channel: dict(values=, offsets=, ids=)
+        self.base = (N.Column * self.ncol)()
+        self._keep = []
+        self.bytes_per_row = 0
+
+        def back(dev_ptr, count, dtype):
+            a = np.empty(count, dtype=dtype)
+            if L.pgpu_memcpy_d2h(device, a.ctypes.data, dev_ptr, a.nbytes):
+                raise RuntimeError("d2h copy failed")
+            return a
+
+        for i, s in enumerate(self.spec):
+            src = dp.cols[i]
+            ctypes.memmove(ctypes.byref(self.base[i]), ctypes.byref(src), ctypes.sizeof(N.Column))
+            self.base[i].values = None
+            self.base[i].offsets = None
+            self.base[i].ids = None
+            self.base[i].nulls = None
+            self.base[i].dictionary = None
+            t, enc = s[0], s[1]
+            a = {}
+            if enc == "plain":
+                w = self.WIDTH[t.kind]
+                a["values"] = back(src.values, rows, {1: np.uint8, 4: np.int32, 8: np.int64}[w])
+                self.bytes_per_row += w
+            elif enc == "varchar1":
+                a["values"] = back(src.values, rows, np.uint8)
+                a["offsets"] = back(src.offsets, rows + 1, np.int32)
+                self.bytes_per_row += 5
+            else:  # dict: ids from the device, the dictionary block straight from the host block
+                a["ids"] = back(src.ids, rows, np.int32)
+                d = N.Column()
+                keep = []
+                s[3]._fill(d, keep)
+                self._keep.append((d, keep))
+                a["dictionary"] = d
+                a["dict_block"] = s[3]
+                self.bytes_per_row += 4
+            self.arrays.append(a)
+
+    def pages(self, page_rows, rows=None):
+        """[(pgpu_column array of HOST pointers, positions)] — built up front, like Block objects a caller already holds"""
+        N = self.N
+        rows = self.rows if rows is None else min(rows, self.rows)
+        out = []
+        for r0 in range(0, rows, page_rows):
+            n = min(page_rows, rows - r0)
+            cols = (N.Column * self.ncol)()
+            ctypes.memmove(cols, self.base, ctypes.sizeof(cols))
+            for i, a in enumerate(self.arrays):
+                c = cols[i]
+                c.position_count = n
+                if "ids" in a:
+                    c.ids = a["ids"].ctypes.data + 4 * r0
+                    c.dictionary = ctypes.pointer(a["dictionary"])
+                elif "offsets" in a:   # a slice of a VariableWidthBlock: absolute offsets into the block's bytes (arrayOffset != 0)
+                    c.values = a["values"].ctypes.data
+                    c.offsets = a["offsets"].ctypes.data + 4 * r0
+                else:
+                    c.values = a["values"].ctypes.data + a["values"].itemsize * r0
+            out.append((cols, n))
+        return out
+
+    def serialized_pages(self, page_rows, rows=None):
+        """[(payload bytes, positions)]: PagesSerdeUtil.writeRawPage of the same pages (main/execution/buffer/PagesSerdeUtil.java:45-62;
+        blocks without nulls: spi/block/LongArrayBlockEncoding.java:39-60, VariableWidthBlockEncoding.java:37-58,
+        DictionaryBlockEncoding.java:36-58) — what an upstream worker's output buffer would deliver."""
+        np = self.np
+        rows = self.rows if rows is None else min(rows, self.rows)
+
+        def name(b):
+            return struct.pack("<i", len(b)) + b
+
+        def flat(arr, n):
+            return [name({1: b"BYTE_ARRAY", 4: b"INT_ARRAY", 8: b"LONG_ARRAY"}[arr.itemsize]), struct.pack("<i", n), b"\x00", arr.tobytes()]
+
+        def varwidth(data, offs, n):
+            ends = (offs[1:n + 1].astype(np.int64) - int(offs[0])).astype("<i4")
+            total = int(ends[-1]) if n else 0
+            return [name(b"VARIABLE_WIDTH"), struct.pack("<i", n), ends.tobytes(), b"\x00", struct.pack("<i", total),
+                    data[int(offs[0]):int(offs[0]) + total].tobytes()]
+
+        out = []
+        for r0 in range(0, rows, page_rows):
+            n = min(page_rows, rows - r0)
+            parts = [struct.pack("<i", self.ncol)]
+            for a in self.arrays:
+                if "ids" in a:
+                    d = a["dict_block"]
+                    parts += [name(b"DICTIONARY"), struct.pack("<i", n)]
+                    parts += varwidth(d.data, d.offsets, d.position_count) if hasattr(d, "offsets") else flat(d.values, d.position_count)
+                    parts += [a["ids"][r0:r0 + n].tobytes(), struct.pack("<qqq", 0x1234, 0x5678, 1)]
+                elif "offsets" in a:
+                    parts += varwidth(a["values"], a["offsets"][r0:r0 + n + 1], n)
+                else:
+                    parts += flat(a["values"][r0:r0 + n], n)
+            out.append((b"".join(parts), n))
+        return out
+
+    def exact_view(self, name, rows):
+        """numpy view of a plain column's first `rows` values (float64 for DOUBLE channels)"""
+        np = self.np
+        for s, a in zip(self.spec, self.arrays):
+            if s[2] == name:
+                v = a["values"][:rows]
+                return v.view(np.float64) if s[0].kind == 4 else v
+        raise KeyError(name)
+
+
 def drain_output(op, to_host):
     """Operator.getOutput() until isFinished(), through the raw C ABI (no Python-side page copies). Returns rows."""
     from presto_b200 import _native as N
@@ -231,6 +317,256 @@ def drain_output(op, to_host):
     return total
 
 
+def time_host_pages(op, pages, steps, to_host=True, warmup=1, flags=0):
+    """One step = Operator protocol over the page stream: needsInput / addInput(page) per page, finish, getOutput until finished.
+    Wall clock from the first addInput to the last output page on the host."""
+    from presto_b200 import _native as N
+    L = N.lib()
+    h = op._h
+    ncol = len(pages[0][0])
+    add, need = L.pgpu_add_page, L.pgpu_needs_input
+    total = sum(n for _, n in pages)
+    t0 = 0.0
+    for it in range(warmup + steps):
+        if it == warmup:
+            t0 = time.perf_counter()
+        op.reset()
+        for cols, n in pages:
+            if not need(h):
+                raise RuntimeError("operator refused input")
+            st = add(h, cols, ncol, n, flags)
+            if st:
+                op._check(st)
+        op.finish()
+        out_rows = drain_output(op, to_host=to_host)
+        if not to_host:
+            op.sync()
+    dt = time.perf_counter() - t0
+    st = op.stats()
+    return dict(rows_per_s=total * steps / dt, seconds_per_step=dt / steps, rows=total, pages=len(pages), steps=steps,
+                h2d_bytes_per_step=int(st.h2d_bytes), d2h_bytes_per_step=int(st.d2h_bytes), super_pages_per_step=int(st.super_pages),
+                launches_per_step=int(st.kernel_launches), result_rows=out_rows)
+
+
+def time_serialized_pages(op, payloads, steps, to_host=True, warmup=1):
+    from presto_b200 import _native as N
+    L = N.lib()
+    h = op._h
+    add = L.pgpu_add_serialized_page
+    total = sum(n for _, n in payloads)
+    t0 = 0.0
+    for it in range(warmup + steps):
+        if it == warmup:
+            t0 = time.perf_counter()
+        op.reset()
+        for data, n in payloads:
+            st = add(h, data, len(data), n)
+            if st:
+                op._check(st)
+        op.finish()
+        out_rows = drain_output(op, to_host=to_host)
+    dt = time.perf_counter() - t0
+    st = op.stats()
+    return dict(rows_per_s=total * steps / dt, seconds_per_step=dt / steps, rows=total, pages=len(payloads), steps=steps,
+                h2d_bytes_per_step=int(st.h2d_bytes), d2h_bytes_per_step=int(st.d2h_bytes), super_pages_per_step=int(st.super_pages),
+                launches_per_step=int(st.kernel_launches), result_rows=out_rows)
+
+
+# ------------------------------------------------------------------------------------------------ CPU oracle legs
+def oracle_run(wl, pages, cores):
+    """The CPU oracle (oracle/, the C++ restatement of the reference's loops — the reference itself is Java and there is no JVM
+    on this box) over `pages` = [(pgpu_column array, positions)] on `cores` threads: one PARTIAL pipeline per thread over its
+    share of the pages, then one FINAL pipeline over the partial outputs (the analogue of task_concurrency drivers + the
+    partial -> final exchange). Returns (seconds, result pages)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle_op import OracleOperator
+    from presto_b200.operators import toPages
+    partial_plan = wl["plan"]("partial")
+    ncol = len(pages[0][0])
+    shards = [pages[t::cores] for t in range(cores)]
+    outs = [None] * cores
+
+    def work(t):
+        op = OracleOperator(partial_plan)
+        res = []
+        for cols, n in shards[t]:
+            op.addRaw(cols, ncol, n)
+            p = op.getOutput()
+            if p is not None and p.position_count:
+                res.append(p)
+        op.finish()
+        while not op.isFinished():
+            p = op.getOutput()
+            if p is not None and p.position_count:
+                res.append(p)
+        op.close()
+        outs[t] = res
+
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    fop = OracleOperator(final_plan_for(wl, partial_plan))
+    result = toPages(fop, [p for o in outs for p in o])
+    fop.close()
+    return time.perf_counter() - t0, result
+
+
+def cpu_run(wl, rows_per_core, cores, repeats=1):
+    """--impl reference: the oracle over freshly generated host pages (1 M-row pages, rows_per_core per thread)."""
+    total = rows_per_core * cores
+    page_rows = 1_000_000
+    from presto_b200.operators import GpuPipelineOperator
+    pages = []
+    keep = []
+    for t in range(cores):
+        r0, end = t * rows_per_core, (t + 1) * rows_per_core
+        while r0 < end:
+            n = min(page_rows, end - r0)
+            pg = wl["page"](r0, n, total)
+            cols, k = GpuPipelineOperator._marshal(pg.blocks)
+            keep.append((pg, k))
+            pages.append((cols, pg.position_count))
+            r0 += n
+    total = sum(n for _, n in pages)
+    best, result = None, None
+    for _ in range(repeats):
+        dt, result = oracle_run(wl, pages, cores)
+        best = dt if best is None else min(best, dt)
+    return total / best, total, result
+
+
+def final_plan_for(wl, partial_plan):
+    """FINAL-step plan whose input channels are the PARTIAL plan's output channels."""
+    from presto_b200.operators import Aggregation, plan_text
+    from presto_b200 import tpch
+    from presto_b200.spi import BIGINT, DOUBLE
+    name = wl["name"]
+    if name in ("q1", "q1dict"):
+        # partial output: returnflag, linestatus, then per aggregate its intermediate channels
+        inp = [tpch.VARCHAR1, tpch.VARCHAR1] + [BIGINT, DOUBLE] * 4 + [DOUBLE, BIGINT] * 3 + [BIGINT]
+        aggs = [Aggregation("sum", DOUBLE, 2, DOUBLE), Aggregation("sum", DOUBLE, 4, DOUBLE), Aggregation("sum", DOUBLE, 6, DOUBLE),
+                Aggregation("sum", DOUBLE, 8, DOUBLE), Aggregation("avg", DOUBLE, 10, DOUBLE), Aggregation("avg", DOUBLE, 12, DOUBLE),
+                Aggregation("avg", DOUBLE, 14, DOUBLE), Aggregation("count", BIGINT, 16, BIGINT)]
+        return plan_text(inp, step="final", groupByChannels=[0, 1], aggregations=aggs)
+    if name == "q6":
+        return plan_text([BIGINT, DOUBLE], step="final", aggregations=[Aggregation("sum", DOUBLE, 0, DOUBLE)])
+    return plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0], aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)],
+                     expectedGroups=max(wl.get("rows", 40_000_000) // 4, 1000))
+
+
+# ------------------------------------------------------------------------------------------------ correctness of the timed data
+def _channels(pages):
+    """result pages -> per channel (values ndarray, nulls ndarray | None), rows concatenated"""
+    import numpy as np
+    if not pages:
+        return []
+    out = []
+    for c in range(len(pages[0].blocks)):
+        bl = [p.blocks[c] for p in pages]
+        if hasattr(bl[0], "offsets"):
+            vals = np.array([v if v is not None else "" for b in bl for v in b.to_pylist()])
+        else:
+            vals = np.concatenate([b.values.view(np.float64) if b.type.kind == 4 else b.values for b in bl])
+        nulls = None
+        if any(b.valueIsNull is not None for b in bl):
+            nulls = np.concatenate([b.valueIsNull if b.valueIsNull is not None else np.zeros(b.position_count, np.uint8) for b in bl])
+        out.append((vals, nulls))
+    return out
+
+
+def _close(a, b, rtol):
+    import numpy as np
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return bool(np.all(np.abs(a - b) <= rtol * np.maximum(np.abs(a), np.abs(b))))
+
+
+def gpu_result_pages(op, dp, ncol, rows):
+    """SINGLE-step result of the device page's first `rows` rows, as host pages"""
+    from presto_b200 import _native as N
+    cols = (N.Column * ncol)()
+    ctypes.memmove(cols, dp.cols, ctypes.sizeof(cols))
+    for i in range(ncol):
+        cols[i].position_count = rows
+    op.reset()
+    op.addDeviceInput(cols, ncol, rows)
+    op.finish()
+    out = []
+    while not op.isFinished():
+        p = op.getOutput()
+        if p is not None and p.position_count:
+            out.append(p)
+    return out
+
+
+def verify_prefix(wl, op, dp, host, rows, cores):
+    """Check the pipeline on the rows it was timed on: the first `rows` rows of the device page through the GPU, the same rows
+    (the host copy of the same bytes) through the CPU oracle on `cores` threads, and — Q1 / Q6 — through numpy with 80-bit
+    accumulation as the correctly rounded reference. Keys and counts bit-exact; DOUBLE sums within 1e-12 relative of the exact
+    sum (GPU) and within the sequential-summation bound n * 2^-53 (oracle). Returns (record, oracle seconds)."""
+    import numpy as np
+    name = wl["name"]
+    ncol = len(wl["spec"])
+    gpu = _channels(gpu_result_pages(op, dp, ncol, rows))
+    secs, ora_pages = oracle_run(wl, host.pages(1_000_000, rows), cores)
+    ora = _channels(ora_pages)
+    rec = {"verified": False, "verified_rows": rows, "oracle_seconds": secs, "tolerance": "keys / counts bit-exact; DOUBLE sums 1e-12 relative"}
+    seq = max(1e-12, rows * 2.0 ** -53)
+    ok = len(gpu) == len(ora) and len(gpu) > 0 and len(gpu[0][0]) == len(ora[0][0])
+    if not ok:
+        rec["why"] = "result shapes differ"
+        return rec, secs
+    if name in ("q1", "q1dict", "q6"):
+        ld = np.longdouble
+        if name == "q6":
+            e, d, q, ship = (host.exact_view(k, rows) for k in ("extendedprice", "discount", "quantity", "shipdate"))
+            sel = (ship >= 8766) & (ship < 9131) & (d >= 0.05) & (d <= 0.07) & (q < 24.0)
+            exact = float(np.sum((e * d)[sel], dtype=ld))
+            ok = _close(gpu[0][0], [exact], 1e-12) and _close(ora[0][0], [exact], seq)
+            rec["groups"] = 1
+        else:
+            if name == "q1":
+                rf, ls = host.arrays[0]["values"][:rows], host.arrays[1]["values"][:rows]
+                q, e, d, t, ship = (host.exact_view(k, rows) for k in ("quantity", "extendedprice", "discount", "tax", "shipdate"))
+            else:
+                rf = np.frombuffer(b"ANR", dtype=np.uint8)[host.arrays[0]["ids"][:rows]]
+                ls = np.frombuffer(b"FO", dtype=np.uint8)[host.arrays[1]["ids"][:rows]]
+                q = np.arange(1, 51, dtype=np.float64)[host.arrays[2]["ids"][:rows]]
+                d = (np.arange(0, 11, dtype=np.float64) / 100.0)[host.arrays[4]["ids"][:rows]]
+                t = (np.arange(0, 9, dtype=np.float64) / 100.0)[host.arrays[5]["ids"][:rows]]
+                e, ship = host.exact_view("extendedprice", rows), host.exact_view("shipdate", rows)
+            dp_ = e * (1.0 - d)
+            ch = dp_ * (1.0 + t)
+            sel = ship <= 10471
+            code = rf.astype(np.int32) * 256 + ls
+            exact = {}
+            for k in np.unique(code[sel]):
+                m = sel & (code == k)
+                n = int(m.sum())
+                s = [float(np.sum(v[m], dtype=ld)) for v in (q, e, dp_, ch, d)]
+                exact[(chr(k >> 8), chr(k & 255))] = s[:4] + [s[0] / n, s[1] / n, s[4] / n, n]
+
+            def rows_of(ch_):
+                return {(str(ch_[0][0][i]), str(ch_[1][0][i])): [ch_[c][0][i] for c in range(2, 10)] for i in range(len(ch_[0][0]))}
+            g, o = rows_of(gpu), rows_of(ora)
+            ok = set(g) == set(o) == set(exact)
+            for k in exact if ok else ():
+                ok &= int(g[k][7]) == int(o[k][7]) == exact[k][7]                       # count(*): bit-exact
+                ok &= _close(g[k][:7], exact[k][:7], 1e-12) and _close(o[k][:7], exact[k][:7], seq)
+            rec["groups"] = len(exact)
+    else:
+        gk, ok_ = np.argsort(gpu[0][0], kind="stable"), np.argsort(ora[0][0], kind="stable")
+        ok = bool(np.array_equal(gpu[0][0][gk], ora[0][0][ok_])) and _close(gpu[1][0][gk], ora[1][0][ok_], 1e-12)
+        q = host.exact_view("quantity", rows)
+        ok &= _close([float(np.sum(gpu[1][0], dtype=np.longdouble))], [float(np.sum(q, dtype=np.longdouble))], 1e-12)  # sum of sums
+        rec["groups"] = int(len(gk))
+    rec["verified"] = bool(ok)
+    return rec, secs
+
+
+# ------------------------------------------------------------------------------------------------ GPU legs
 def make_exchange(args, device, world, rank, small, leg):
     from presto_b200 import exchange as X
     if world == 1:
@@ -246,60 +582,35 @@ def exchange_and_final(op, final, small, repart, tdev, state):
     """N > 1: the partial -> final exchange of one step (op has finished its shard); leaves the result drained.
     `repart` is the exchange object: PeerGather / None (small results), DeviceRepartition (large group counts)."""
     from presto_b200 import exchange as X
-    trace = state.get("trace")
-    t0 = time.perf_counter()
     final.reset()
-    t1 = time.perf_counter()
     if small and repart is not None:
-        if trace is not None:
-            op.sync()
-            trace["kernels"] = trace.get("kernels", 0.0) + time.perf_counter() - t1
-            t1 = time.perf_counter()
         repart.run(op, final)                       # FINAL kernel reads every rank's partial rows over NVLink
-        t2 = time.perf_counter()
         state["result_rows"] = drain_output(final, to_host=True)
-        if trace is not None:
-            trace["peer_gather+final"] = trace.get("peer_gather+final", 0.0) + t2 - t1
-            trace["final_output"] = trace.get("final_output", 0.0) + time.perf_counter() - t2
     elif small:
-        if trace is not None:
-            op.sync()
-            trace["kernels"] = trace.get("kernels", 0.0) + time.perf_counter() - t1
-            t1 = time.perf_counter()
         frame = X.pack_output(op)                                       # waits for the shard's kernels, drains the partial page
-        t2 = time.perf_counter()
         frames = X.all_gather_frames(frame, device=tdev)                # one NCCL all-gather of a 32 KB frame per rank
-        t3 = time.perf_counter()
         for f in frames:
             X.add_packed(final, f)                                      # FINAL step: addIntermediate over every rank's partial page
         final.finish()
-        t4 = time.perf_counter()
         state["result_rows"] = drain_output(final, to_host=True)
-        t5 = time.perf_counter()
-        if trace is not None:
-            for k, v in (("final_reset", t1 - t0), ("pack_output", t2 - t1), ("all_gather", t3 - t2), ("final_add", t4 - t3), ("final_output", t5 - t4)):
-                trace[k] = trace.get(k, 0.0) + v
     else:
         repart.run(op, final)
         state["result_rows"] = drain_output(final, to_host=False)
         state["exchange_bytes"] = repart.sent_bytes
 
 
-def run_device_steps(args, wl, device, dist):
+def run_device_steps(args, wl, device, dist, steps, warmup):
     """`value`: inputs resident in HBM before the timed region. One step = reset, one pass of the fused pipeline over the
     rank's shard, and (N > 1) the partial -> final exchange. Timed with CUDA events recorded on an idle device on both
     sides (barrier + synchronize), max over ranks taken by the caller."""
     import torch
-    from presto_b200 import _native as N
-    from presto_b200 import exchange as X
     from presto_b200 import tpch
-    from presto_b200.operators import GpuPipelineOperator, toPages
-    L = N.lib()
-    rows = args.rows
+    from presto_b200.operators import GpuPipelineOperator
+    rows = wl["rows"]
     world, rank = dist["world"], dist["rank"]
     first = rank * rows
     total = rows * world
-    dp = tpch.DevicePage(device, wl["spec"], rows, first_row=first, total_rows=total, dbgen=getattr(args, "dbgen", None))
+    dp = tpch.DevicePage(device, wl["spec"], rows, first_row=first, total_rows=total, dbgen=wl.get("dbgen"))
     assert dp.rows == rows
     single = world == 1
     op = GpuPipelineOperator(wl["plan"]("single" if single else "partial"), device)
@@ -307,10 +618,8 @@ def run_device_steps(args, wl, device, dist):
     ncol = len(wl["spec"])
     small = wl["name"] in ("q1", "q1dict", "q6")   # result is a handful of rows: host output / gather exchange
     tdev = torch.device("cuda", device)
-    repart = make_exchange(args, device, world, rank, small, "value")
+    repart = make_exchange(args, device, world, rank, small, "value_" + wl["name"])
     state = {"result_rows": 0, "exchange_bytes": 0}
-    if os.environ.get("PGPU_BENCH_TRACE"):
-        state["trace"] = {}
 
     def one_step():
         op.reset()
@@ -331,10 +640,8 @@ def run_device_steps(args, wl, device, dist):
         n = op.stats().kernel_launches
         return n + (final.stats().kernel_launches if final is not None else 0)
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         one_step()
-    if state.get("trace") is not None:
-        state["trace"].clear()
     sampler = ClockSampler(device)
     sampler.start()
     barrier()
@@ -342,7 +649,7 @@ def run_device_steps(args, wl, device, dist):
     t0 = time.perf_counter()
     e0.record()
     nl = 0
-    for _ in range(args.steps):
+    for _ in range(steps):
         one_step()
         nl += launches()
     barrier()
@@ -351,12 +658,10 @@ def run_device_steps(args, wl, device, dist):
     wall = time.perf_counter() - t0
     dev_ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
-    if state.get("trace") and rank == 0:
-        print("exchange trace (ms/step): " + ", ".join("%s %.3f" % (k, v * 1e3 / args.steps) for k, v in state["trace"].items()), file=sys.stderr)
-    # dominant kernel alone: per-launch CUDA-event durations (pgpu_set_timing brackets every page-kernel launch)
+    # dominant kernel alone: per-launch CUDA-event durations on the pipeline's stream (pgpu_set_timing brackets every page-kernel launch)
     op.setTiming(True)
     kern_ms, kern_launches = 0.0, 0
-    ksteps = max(3, min(args.steps, 5))
+    ksteps = max(3, min(steps, 5))
     for _ in range(ksteps):
         op.reset()
         op.addDeviceInput(dp.cols, ncol, rows)
@@ -375,112 +680,217 @@ def run_device_steps(args, wl, device, dist):
     return info, dp, op
 
 
-def run_e2e_steps(args, wl, device, dp_device, steps, warmup, dist):
-    """`e2e`: the same pass through pgpu_add_page with HOST pages in pinned memory; H2D copies, the exchange (N > 1) and the
-    D2H read of the result are inside the timed region (wall clock around the public API call sequence, bracketed by
-    barriers; the caller takes the max over ranks)."""
-    import numpy as np
-    import torch
-    from presto_b200 import _native as N
-    from presto_b200 import exchange as X
-    from presto_b200 import tpch
-    from presto_b200.operators import GpuPipelineOperator
-    L = N.lib()
-    world, rank = dist["world"], dist["rank"]
-    rows = args.e2e_rows or args.rows
-    # bound by available host memory (pinned): keep below 40 % of MemAvailable
-    need = rows * wl["bytes_per_row"] * 1.05
+def e2e_rows_for(args, wl, world, want):
+    """rows of the host-page leg: bounded by host memory (every rank of the box keeps its shard in pageable memory)"""
+    rows = want
     try:
         avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
     except Exception:
         avail = 64 << 30
-    if need * world > 0.4 * avail:           # all ranks pin host memory of the same box
-        rows = int(0.4 * avail / world / (wl["bytes_per_row"] * 1.05))
-    rows = min(rows, dp_device.rows)
+    need = rows * wl["bytes_per_row"] * 1.1
+    if need * world > 0.5 * avail:
+        rows = int(0.5 * avail / world / (wl["bytes_per_row"] * 1.1))
+    return rows
+
+
+def run_e2e(args, wl, device, dp, dist, steps, full):
+    """`e2e`: the same pass fed the way a Trino driver feeds an operator: pages of --page-rows positions in ordinary pageable
+    memory (Java heap arrays cannot be pinned by the caller) through pgpu_add_page(flags = 0); the library coalesces them into
+    super-pages, stages them through its pinned ring with worker threads and overlaps that with the DMA and the kernels. The
+    H2D copy of every input byte, the exchange (N > 1) and the D2H read of the result are inside the timed region (wall clock
+    around the public API call sequence, bracketed by barriers; the caller takes the max over ranks).
+    `full`: also time 64 K-row pages, the wire format and the caller-pinned single-page ceiling."""
+    import torch
+    from presto_b200 import _native as N
+    from presto_b200.operators import GpuPipelineOperator
+    L = N.lib()
+    world, rank = dist["world"], dist["rank"]
+    rows = min(e2e_rows_for(args, wl, world, args.e2e_rows or wl["rows"]), dp.rows)
     if world > 1:                            # every rank runs the same number of rows
         import torch.distributed as td
         t = torch.tensor([rows], device="cuda", dtype=torch.int64)
         td.all_reduce(t, op=td.ReduceOp.MIN)
         rows = int(t.item())
-    # host pages = the device columns copied back into pinned host buffers (identical bytes, no slow host generation)
-    cols = (N.Column * len(wl["spec"]))()
-    hostbufs = []
-    h2d = 0
-
-    def pinned_copy(dev_ptr, nbytes):
-        nonlocal h2d
-        hp = L.pgpu_host_alloc(max(nbytes, 16))
-        if not hp:
-            raise MemoryError("pinned allocation of %d bytes failed" % nbytes)
-        hostbufs.append(hp)
-        if L.pgpu_memcpy_d2h(device, hp, dev_ptr, nbytes):
-            raise RuntimeError("d2h copy failed")
-        h2d += nbytes
-        return hp
-
-    width = {0: 1, 1: 8, 2: 4, 3: 4, 4: 8}
-    dict_cols = []
-    for i, s in enumerate(wl["spec"]):
-        src, dst = dp_device.cols[i], cols[i]
-        ctypes.memmove(ctypes.byref(dst), ctypes.byref(src), ctypes.sizeof(N.Column))
-        dst.position_count = rows
-        t = s[0]
-        if s[1] == "plain":
-            dst.values = pinned_copy(src.values, rows * width[t.kind])
-        elif s[1] == "varchar1":
-            dst.values = pinned_copy(src.values, rows)
-            dst.offsets = pinned_copy(src.offsets, (rows + 1) * 4)
-        else:  # dict: ids from device, dictionary block straight from the host block
-            dst.ids = pinned_copy(src.ids, rows * 4)
-            d = N.Column()
-            keep = []
-            s[3]._fill(d, keep)
-            dict_cols.append((d, keep))
-            dst.dictionary = ctypes.pointer(d)
+    host = HostTable(device, wl, dp, rows)
     single = world == 1
-    op = GpuPipelineOperator(wl["plan"]("single" if single else "partial"), device)
-    final = None if single else GpuPipelineOperator(final_plan_for(wl, None), device)
     small = wl["name"] in ("q1", "q1dict", "q6")
+    ceiling = h2d_ceiling(device)
+    if world > 1:
+        import torch.distributed as td
+        td.barrier()
+    rec = {"unit": "rows/s", "config": {"page_rows": args.page_rows, "pinned": False, "host_memory": "pageable numpy arrays, one per block array; pages are consecutive slices",
+                                        "entry_point": "pgpu_add_page(flags=0)", "copy_threads": int(os.environ.get("PGPU_COPY_THREADS", "0")) or "library default",
+                                        "rows_per_gpu": rows},
+           "h2d_ceiling_gbs": ceiling}
+    if single:
+        op = GpuPipelineOperator(wl["plan"]("single"), device)
+        r = time_host_pages(op, host.pages(args.page_rows), steps, to_host=True)
+        rec.update(value=r["rows_per_s"], h2d_bytes_per_step=r["h2d_bytes_per_step"], d2h_bytes_per_step=r["d2h_bytes_per_step"],
+                   rows_per_step=r["rows"], steps=steps, seconds_per_step=r["seconds_per_step"], super_pages_per_step=r["super_pages_per_step"],
+                   launches_per_step=r["launches_per_step"], gb_per_s=r["rows_per_s"] * host.bytes_per_row / 1e9)
+        rec["frac_of_h2d_ceiling"] = rec["gb_per_s"] / ceiling
+        if full:
+            variants = {}
+            r = time_host_pages(op, host.pages(65536), max(1, steps - 1), to_host=True)
+            variants["page_rows_65536"] = {"value": r["rows_per_s"], "gb_per_s": r["rows_per_s"] * host.bytes_per_row / 1e9, "pages_per_step": r["pages"],
+                                           "super_pages_per_step": r["super_pages_per_step"]}
+            srows = min(rows, 96_000_000)
+            payloads = host.serialized_pages(args.page_rows, srows)
+            r = time_serialized_pages(op, payloads, max(1, steps - 1), to_host=True)
+            variants["serialized_pages"] = {"value": r["rows_per_s"], "gb_per_s": r["rows_per_s"] * host.bytes_per_row / 1e9, "rows_per_step": srows,
+                                            "page_rows": args.page_rows, "entry_point": "pgpu_add_serialized_page", "super_pages_per_step": r["super_pages_per_step"]}
+            del payloads
+            rec["variants"] = variants
+            # ceiling of the path: ONE caller-pinned page (a shape no Trino caller produces): DMA straight from the caller's buffers
+            prow = min(rows, 128_000_000)
+            pinned, bufs = (N.Column * host.ncol)(), []
+            ctypes.memmove(pinned, host.pages(prow, prow)[0][0], ctypes.sizeof(pinned))
+            for i, a in enumerate(host.arrays):
+                for field, key, cnt in (("values", "values", prow), ("offsets", "offsets", prow + 1), ("ids", "ids", prow)):
+                    if key in a:
+                        src = a[key][:cnt]
+                        hp = L.pgpu_host_alloc(max(src.nbytes, 16))
+                        if not hp:
+                            raise MemoryError("pinned allocation failed")
+                        ctypes.memmove(hp, src.ctypes.data, src.nbytes)
+                        bufs.append(hp)
+                        setattr(pinned[i], field, hp)
+            r = time_host_pages(op, [(pinned, prow)], max(1, steps - 1), to_host=True, flags=N.PAGE_PINNED)
+            rec["ceiling_pinned_single_page"] = {"value": r["rows_per_s"], "gb_per_s": r["rows_per_s"] * host.bytes_per_row / 1e9, "rows_per_step": prow}
+            op.sync()
+            for hp in bufs:
+                L.pgpu_host_free(hp)
+        op.close()
+        return rec, host
+    # N > 1: PARTIAL over the host pages, then the exchange and FINAL
+    op = GpuPipelineOperator(wl["plan"]("partial"), device)
+    final = GpuPipelineOperator(final_plan_for(wl, None), device)
     tdev = torch.device("cuda", device)
-    repart = make_exchange(args, device, world, rank, small, "e2e")
+    repart = make_exchange(args, device, world, rank, small, "e2e_" + wl["name"])
     state = {"result_rows": 0, "exchange_bytes": 0}
+    pages = host.pages(args.page_rows)
+    ncol = host.ncol
+
+    def barrier():
+        import torch.distributed as td
+        td.barrier()
+        torch.cuda.synchronize(device)
 
     def one_step():
         op.reset()
-        op._check(L.pgpu_add_page(op._h, cols, len(wl["spec"]), rows, N.PAGE_PINNED))
+        for cols, n in pages:
+            op._check(L.pgpu_add_page(op._h, cols, ncol, n, 0))
         op.finish()
-        if single:
-            return drain_output(op, to_host=True)
         exchange_and_final(op, final, small, repart, tdev, state)
         if not small:                         # the device-resident result is read back: that is the step's D2H
             final.sync()
-        return state["result_rows"]
 
-    def barrier():
-        if world > 1:
-            import torch.distributed as td
-            td.barrier()
-        torch.cuda.synchronize(device)
-
-    for _ in range(warmup):
-        one_step()
+    one_step()
     barrier()
     t0 = time.perf_counter()
-    d2h = 0
     for _ in range(steps):
         one_step()
-        d2h = op.stats().d2h_bytes + (final.stats().d2h_bytes if final is not None else 0)
     barrier()
     dt = time.perf_counter() - t0
+    t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+    import torch.distributed as td
+    td.all_reduce(t, op=td.ReduceOp.MAX)
+    dt = float(t.item())
+    t = torch.tensor([ceiling], device="cuda", dtype=torch.float64)
+    td.all_reduce(t, op=td.ReduceOp.SUM)
     st = op.stats()
+    d2h = st.d2h_bytes + final.stats().d2h_bytes
+    rec.update(value=rows * world * steps / dt, h2d_bytes_per_step=int(st.h2d_bytes) * world, d2h_bytes_per_step=int(d2h) * world,
+               rows_per_step=rows * world, steps=steps, seconds_per_step=dt / steps, gb_per_s=rows * world * steps * host.bytes_per_row / dt / 1e9,
+               h2d_ceiling_gbs=float(t.item()))
+    rec["frac_of_h2d_ceiling"] = rec["gb_per_s"] / rec["h2d_ceiling_gbs"]
     op.close()
-    if repart is not None:
-        repart.close()
-    if final is not None:
-        final.close()
-    for hp in hostbufs:
-        L.pgpu_host_free(hp)
-    return dict(rows=rows, seconds=dt, steps=steps, h2d_bytes_per_step=int(st.h2d_bytes), d2h_bytes_per_step=int(d2h))
+    repart.close() if repart is not None else None
+    final.close()
+    return rec, host
+
+
+def run_workload(args, name, device, dist, headline):
+    """One record: device-resident value + roofline, e2e over host pages, verification against the CPU oracle."""
+    import torch
+    world, rank = dist["world"], dist["rank"]
+    rows = args.rows
+    wl = workload_def(name, rows, args.sf * world if args.data == "dbgen" else None)
+    if args.data == "dbgen":
+        wl["dbgen"] = args.dbgen
+    steps = args.steps if headline else max(3, min(args.steps, 5))
+    warmup = args.warmup if headline else 3
+    info, dp, op = run_device_steps(args, wl, device, dist, steps, warmup)
+    ms_per_step = info["dev_ms"] / steps
+    total_rows = rows * world
+    if world > 1:
+        import torch.distributed as td
+        t = torch.tensor([ms_per_step], device="cuda", dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        ms_per_step = float(t.item())
+        if args.data == "dbgen":        # order-range shards differ by a few rows
+            t = torch.tensor([rows], device="cuda", dtype=torch.int64)
+            td.all_reduce(t)
+            total_rows = int(t.item())
+    value = total_rows / (ms_per_step / 1000.0)
+    peak, peak_src = measured_peak()
+    kern_ms_step = info["kern_ms"] / info["kern_steps"]
+    launches_step = info["kern_launches"] / info["kern_steps"]
+    alg_bytes_step = rows * wl["bytes_per_row"]
+    achieved = alg_bytes_step / (kern_ms_step / 1e3) / 1e9
+    kname = "pgpu_k_page_staged (cp.async.bulk ring + register-resident groups)" if name in ("q1", "q1dict") else "pgpu_k_page (fused scan+filter+project+aggregate, direct loads)"
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "bytes_per_launch": alg_bytes_step / max(launches_step, 1), "avg_launch_ms": kern_ms_step / max(launches_step, 1),
+                "kernel_ms_per_step": kern_ms_step, "launches_per_step": launches_step, "kernel": kname, "peak_source": peak_src,
+                "algorithmic_bytes_per_row": wl["bytes_per_row"]}
+    tr = measured_traffic(name)
+    if tr:
+        dram_step = tr["dram_bytes_per_row"] * rows
+        roofline["traffic"] = dram_step / max(launches_step, 1)
+        roofline["traffic_source"] = tr.get("source")
+        roofline["achieved_dram"] = dram_step / (kern_ms_step / 1e3) / 1e9
+        roofline["frac_dram"] = roofline["achieved_dram"] / peak
+        if name == "q6":   # the kernel skips extendedprice sectors of unselected rows: its roofline position is the DRAM bytes it really moves
+            roofline["frac_algorithmic"] = roofline["frac"]
+            roofline["frac"] = roofline["frac_dram"]
+    config = {"workload": wl["label"], "rows_per_gpu": rows, "scale_factor_equivalent": round(rows / 6_001_215, 2),
+              "bytes_per_row": wl["bytes_per_row"], "partitioning": "row-range shard per GPU, partial -> final aggregation",
+              "l2_policy": "inputs (%.1f GB per GPU) are far larger than the 126 MB L2: no flush needed" % (rows * wl["bytes_per_row"] / 1e9)}
+    rec = {"metric": "lineitem_rows_per_second", "value": value, "unit": "rows/s", "ms_per_step": ms_per_step, "steps": steps, "warmup": warmup,
+           "gb_per_s": value * wl["bytes_per_row"] / 1e9, "roofline": roofline, "config": config, "gpu_launches": info["launches"],
+           "clocks": info["clocks"], "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"]}
+    if world > 1:
+        small = name in ("q1", "q1dict", "q6")
+        rec["exchange"] = {"shape": ("gather: every rank's FINAL kernel reads all partial pages over NVLink (CUDA IPC peer memory, shared-memory mailbox)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if small else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),
+                           "bytes_sent_per_rank_per_step": info["exchange_bytes"]}
+    host = None
+    if not args.no_e2e:
+        if not headline and not args.e2e_rows:
+            args_e2e_rows, args.e2e_rows = args.e2e_rows, min(rows, 64_000_000)   # sub-records: a 64 M-row sample of the shard
+            rec["e2e"], host = run_e2e(args, wl, device, dp, dist, steps=2, full=False)
+            args.e2e_rows = args_e2e_rows
+        else:
+            rec["e2e"], host = run_e2e(args, wl, device, dp, dist, steps=max(2, min(steps, 3)), full=headline)
+    # correctness of the timed rows + the CPU baseline (rank 0, N = 1)
+    if rank == 0 and world == 1 and not args.no_cpu and args.verify_rows > 0:
+        vrows = min(args.verify_rows if headline else min(args.verify_rows, 16_000_000), rows)
+        if host is None or host.rows < vrows:
+            host = HostTable(device, wl, dp, vrows)
+        cores = os.cpu_count() or 1
+        v, secs = verify_prefix(wl, op, dp, host, vrows, cores)
+        rec.update(verified=v["verified"], verified_rows=v["verified_rows"], verification=v)
+        cpu = {"value": vrows / secs, "unit": "rows/s", "cores": cores, "kind": "port",
+               "sample": "the first %d rows of the timed shard (host copy of the same bytes), 1 M-row pages, one PARTIAL pipeline per thread + FINAL merge" % vrows}
+        if headline:
+            srows = min(vrows, 4_000_000)
+            s1, _ = oracle_run(wl, host.pages(1_000_000, srows), 1)
+            cpu["single_thread_value"] = srows / s1
+            cpu["single_thread_sample"] = "%d rows, one thread (the harness's one split / one driver)" % srows
+        rec["cpu_baseline"] = cpu
+    op.close()
+    dp.free()
+    del host
+    return rec
 
 
 def main():
@@ -488,6 +898,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    cores = os.cpu_count() or 1
+    if "PGPU_COPY_THREADS" not in os.environ:   # staging-copy workers of this process: the box's cores shared by its ranks
+        os.environ["PGPU_COPY_THREADS"] = str(max(2, min(16, cores // max(world, 1))))
     if args.data == "dbgen":
         from presto_b200 import tpch
         per_gpu = int(1_500_000 * args.sf)
@@ -497,16 +910,8 @@ def main():
         if args.impl == "ours":
             args.dbgen = (total_sf, first_order, n_orders)
             args.rows = tpch.tpch_rows(*args.dbgen)
-    wl = workload_def(args.workload, args.rows, args.sf * world if args.data == "dbgen" else None)
-    wl["dbgen_sf"] = args.sf * world if args.data == "dbgen" else None
     data = "synthetic" if args.data == "synthetic" else "synthetic: TPC-H dbgen rows (the tpch connector's generator, restated; sf %g per GPU)%s" % (args.sf, ", generated on the device" if args.impl == "ours" else "")
-    wl["name"] = args.workload
-    wl["rows"] = args.rows if args.impl == "ours" else args.cpu_rows_per_core
-    cores = os.cpu_count() or 1
-    metric = "lineitem_rows_per_second"
-    config = {"workload": wl["label"], "rows_per_gpu": args.rows, "scale_factor_equivalent": round(args.rows / 6_001_215, 2),
-              "bytes_per_row": wl["bytes_per_row"], "partitioning": "row-range shard per GPU, partial -> final aggregation",
-              "l2_policy": "inputs (%.1f GB per GPU) are far larger than the 126 MB L2: no flush needed" % (args.rows * wl["bytes_per_row"] / 1e9)}
+    headline_name = args.workload or "q1"
 
     if args.impl == "reference":
         # the reference's CPU implementation of the path: Java, no JVM here -> the oracle port on all host cores
@@ -514,6 +919,7 @@ def main():
             return
         from __graft_entry__ import build
         build()
+        wl = workload_def(headline_name, args.cpu_rows_per_core, args.sf * world if args.data == "dbgen" else None)
         per_core = args.cpu_rows_per_core
         vals = []
         for i in range(args.warmup + args.steps):
@@ -522,7 +928,9 @@ def main():
                 vals.append(v)
         value = sum(vals) / len(vals)
         sample = "%d rows (%d per core x %d cores) of the same synthetic lineitem per step, 1 M-row pages, partial per thread + final merge" % (per_core * cores, per_core, cores)
-        line = {"impl": "reference", "metric": metric, "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps,
+        config = {"workload": wl["label"], "rows_per_gpu": args.rows, "rows_per_step_timed": per_core * cores, "bytes_per_row": wl["bytes_per_row"],
+                  "partitioning": "row-range shard per host thread, partial -> final aggregation"}
+        line = {"impl": "reference", "metric": "lineitem_rows_per_second", "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1000.0 * per_core * cores / value, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f64", "data": data, "config": config,
                 "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port", "sample": sample},
@@ -538,54 +946,25 @@ def main():
     if world > 1:
         import torch.distributed as td
         td.init_process_group("nccl", device_id=torch.device("cuda", device))
-    info, dp, op = run_device_steps(args, wl, device, dist)
-    ms_per_step = info["dev_ms"] / args.steps
-    if world > 1:
-        import torch.distributed as td
-        t = torch.tensor([ms_per_step], device="cuda", dtype=torch.float64)
-        td.all_reduce(t, op=td.ReduceOp.MAX)
-        ms_per_step = float(t.item())
-    total_rows = args.rows * world
-    if world > 1 and args.data == "dbgen":        # order-range shards differ by a few rows
-        t = torch.tensor([args.rows], device="cuda", dtype=torch.int64)
-        td.all_reduce(t)
-        total_rows = int(t.item())
-    value = total_rows / (ms_per_step / 1000.0)
-    peak, peak_src = measured_peak()
-    kern_rows = args.rows * info["kern_steps"]
-    achieved = kern_rows * wl["bytes_per_row"] / (info["kern_ms"] / 1000.0) / 1e9
-    kname = "pgpu_k_page_staged (cp.async.bulk ring + register-resident groups)" if args.workload in ("q1", "q1dict") else "pgpu_k_page (fused scan+filter+project+aggregate, direct loads)"
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": (TRAFFIC_RATIO[args.workload] * kern_rows * wl["bytes_per_row"] / max(info["kern_launches"], 1)) if args.workload in TRAFFIC_RATIO else None,
-                "bytes_per_launch": kern_rows * wl["bytes_per_row"] / max(info["kern_launches"], 1),
-                "avg_launch_ms": info["kern_ms"] / max(info["kern_launches"], 1),
-                "kernel": kname, "peak_source": peak_src,
-                "launches_timed": info["kern_launches"], "algorithmic_bytes_per_row": wl["bytes_per_row"]}
-    e2e = None
-    if not args.no_e2e:
-        e = run_e2e_steps(args, wl, device, dp, steps=max(2, min(args.steps, 5)), warmup=1, dist=dist)
-        if world > 1:
-            t = torch.tensor([e["seconds"]], device="cuda", dtype=torch.float64)
-            td.all_reduce(t, op=td.ReduceOp.MAX)
-            e["seconds"] = float(t.item())
-        e2e = {"value": e["rows"] * world * e["steps"] / e["seconds"], "unit": "rows/s", "h2d_bytes_per_step": e["h2d_bytes_per_step"] * world,
-               "d2h_bytes_per_step": e["d2h_bytes_per_step"] * world, "rows_per_step": e["rows"] * world, "steps": e["steps"],
-               "gb_per_s": e["h2d_bytes_per_step"] * world * e["steps"] / e["seconds"] / 1e9}
-    op.close()
-    dp.free()
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        v, total, _ = cpu_run(wl, args.cpu_rows_per_core, cores)
-        cpu = {"value": v, "unit": "rows/s", "cores": cores, "kind": "port",
-               "sample": "%d rows (%d per core) of the same synthetic lineitem, 1 M-row pages, partial per thread + final merge" % (total, args.cpu_rows_per_core)}
+    rec = run_workload(args, headline_name, device, dist, headline=True)
+    configs = {}
+    if args.workload is None and not args.no_configs and args.data == "synthetic":
+        for name in (SUB_CONFIGS if world == 1 else ("highcard",)):
+            try:
+                configs[name] = run_workload(args, name, device, dist, headline=False)
+            except Exception as e:  # a failing sub-record must not take the headline with it
+                configs[name] = {"error": "%s: %s" % (type(e).__name__, e)}
+                if world > 1:
+                    raise
     if rank == 0:
-        line = {"metric": metric, "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-                "data": data, "config": config, "gb_per_s": value * wl["bytes_per_row"] / 1e9,
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": info["launches"], "clocks": info["clocks"],
-                "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"],
-                "exchange": None if world == 1 else {"shape": ("gather: every rank's FINAL kernel reads all partial pages over NVLink (CUDA IPC peer memory, shared-memory mailbox)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if args.workload in ("q1", "q1dict", "q6") else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),
-                                                     "bytes_sent_per_rank_per_step": info["exchange_bytes"]}}
+        line = {"metric": rec["metric"], "value": rec["value"], "unit": "rows/s", "n_gpus": world, "steps": rec["steps"], "warmup": rec["warmup"],
+                "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": data}
+        for k in ("config", "gb_per_s", "roofline", "cpu_baseline", "e2e", "gpu_launches", "clocks", "table_capacity_slots", "result_rows",
+                  "verified", "verified_rows", "verification", "exchange"):
+            line[k] = rec.get(k)
+        if configs:
+            line["configs"] = configs
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as td
@@ -594,6 +973,3 @@ def main():
 
 if __name__ == "__main__":
     main()
-
-
-

@@ -204,6 +204,7 @@ typedef struct pgpu_stats {
     double  device_ms;      /* sum over timed page kernels */
     int64_t table_capacity; /* slots of the HBM hash table (0 = none) */
     int64_t table_rehashes;
+    int64_t super_pages;    /* launches over coalesced host pages (pgpu_add_page / pgpu_add_serialized_page appends) */
 } pgpu_stats;
 pgpu_status pgpu_get_stats(const pgpu_pipeline* p, pgpu_stats* out);
 pgpu_status pgpu_set_timing(pgpu_pipeline* p, int32_t enabled);

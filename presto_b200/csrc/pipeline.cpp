@@ -21,6 +21,7 @@
 #include "../../include/prestogpu.h"
 #include "codegen.h"
 #include "exchange.h"
+#include "hostcopy.h"
 #include "jit.h"
 #include "plan.h"
 #include "serde.h"
@@ -95,6 +96,51 @@ struct StageSlot {
     bool inFlight = false;
 };
 
+// Where the arrays of one input channel lie inside a staging slot (same byte offsets in the pinned host half and the device
+// half). A slot holds ONE super-page: the rows of as many consecutive small input pages as fit, appended array by array.
+struct StageCol {
+    size_t values = 0, nulls = 0, offsets = 0, ids = 0, dvalues = 0, dnulls = 0, doffsets = 0;
+    size_t valuesCap = 0;  // var-width: payload bytes the region holds
+    int width = 0;         // fixed width: bytes per position
+    int encoding = PGPU_ENC_PLAIN;
+    bool nullable = false; // the block (PLAIN) / its dictionary carries a null vector
+};
+struct StageLayout {
+    int64_t capRows = 0;
+    size_t bytes = 0;
+    std::vector<StageCol> cols;  // per input channel (used channels only)
+};
+// The super-page under construction in slots[nextSlot].
+struct PendingPage {
+    Variant* v = nullptr;
+    std::string key;                 // page signature of the rows gathered so far
+    const StageLayout* lay = nullptr;
+    int64_t rows = 0;
+    std::vector<int64_t> vbytes;     // per channel: var-width payload bytes so far
+    std::vector<int32_t> dcount;     // per channel: entries of the dictionary / RLE value block held in the slot
+    std::vector<size_t> dbytes;      // per channel: bytes of its values
+};
+
+// One channel of a host page as the appender reads it: pgpu_column arrays or the pieces of a serialized block (which may be
+// unaligned and carry END offsets without the leading 0, spi/block/VariableWidthBlockEncoding.java:37-58).
+struct HostCol {
+    int encoding = PGPU_ENC_PLAIN;
+    const void* values = nullptr;
+    const uint8_t* nulls = nullptr;
+    const char* offsets = nullptr;   // int32 entries
+    bool endOffsets = false;
+    const char* ids = nullptr;       // int32 entries
+    // dictionary / RLE value block
+    const void* dvalues = nullptr;
+    const uint8_t* dnulls = nullptr;
+    const char* doffsets = nullptr;
+    bool dEndOffsets = false;
+    int64_t dcount = 0;
+};
+
+constexpr size_t kDictStageBytes = 64u << 10;  // a coalesced super-page carries one dictionary per channel, up to this size
+constexpr int kOffsetsSlack = 8;               // offsets entries kept valid past the end of a super-page (the staged kernel reads 4)
+
 struct HostOut {
     void* ptr = nullptr;
     size_t cap = 0;
@@ -142,6 +188,9 @@ struct pgpu_pipeline {
     // staging + output
     StageSlot slots[3];
     int nextSlot = 0;
+    PendingPage pend;
+    std::map<std::string, StageLayout> stageLayouts;
+    size_t stageTargetBytes = 64u << 20;  // PGPU_STAGE_MB
     // output columns live in ONE device allocation (values / nulls of column c at outOffV[c] / outOffN[c]) so that a
     // small result reaches the host with a single copy instead of two per column
     DeviceBuf outArena;
@@ -673,7 +722,41 @@ pgpu_status validatePage(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncol
 }
 
 
-// Stage rows [r0, r0+n) of a host page into a ring slot and return device-side column descriptors.
+// Both halves of a staging slot hold at least `bytes` (the pinned half only when the library does the staging copy).
+pgpu_status ensureSlot(pgpu_pipeline* p, StageSlot& slot, size_t bytes, bool needHost) {
+    pgpu_status st = ensureDev(p, slot.dev, bytes);
+    if (st) return st;
+    if (needHost && slot.hostCap < bytes) {
+        if (slot.host) CU(cudaFreeHost(slot.host));
+        slot.host = nullptr;
+        slot.hostCap = 0;
+        CU(cudaMallocHost(&slot.host, bytes));
+        slot.hostCap = bytes;
+    }
+    return PGPU_OK;
+}
+
+// The slot the next super-page / chunk goes into: waits until the kernel that read its previous contents has finished.
+pgpu_status acquireSlot(pgpu_pipeline* p, StageSlot** out) {
+    StageSlot& slot = p->slots[p->nextSlot];
+    if (slot.inFlight) {
+        CU(cudaEventSynchronize(slot.done));
+        slot.inFlight = false;
+    }
+    *out = &slot;
+    return PGPU_OK;
+}
+
+pgpu_status releaseSlot(pgpu_pipeline* p, StageSlot& slot) {
+    if (!slot.done) CU(cudaEventCreateWithFlags(&slot.done, cudaEventDisableTiming));
+    CU(cudaEventRecord(slot.done, p->stream));
+    slot.inFlight = true;
+    p->nextSlot = (p->nextSlot + 1) % 3;
+    return PGPU_OK;
+}
+
+// Stage rows [r0, r0+n) of a host page into a ring slot and return device-side column descriptors (pages the coalescing
+// appender below does not take: caller-pinned pages, filter + project pages, very large dictionaries).
 pgpu_status stageChunk(pgpu_pipeline* p, Variant* v, const pgpu_column* cols, int64_t r0, int64_t n, bool pinned, StageSlot& slot, std::vector<ColArg>& out) {
     const GenResult& g = v->gen;
     const Plan& plan = *p->plan;
@@ -731,21 +814,17 @@ pgpu_status stageChunk(pgpu_pipeline* p, Variant* v, const pgpu_column* cols, in
             }
         }
     }
-    pgpu_status st = ensureDev(p, slot.dev, total);
+    pgpu_status st = ensureSlot(p, slot, total, !pinned);
     if (st) return st;
     char* dbase = (char*)slot.dev.ptr;
     if (pinned) {
         for (auto& pc : pieces)
             if (pc.bytes) CU(cudaMemcpyAsync(dbase + pc.off, pc.src, pc.bytes, cudaMemcpyHostToDevice, p->stream));
     } else {
-        if (slot.hostCap < total) {
-            if (slot.host) CU(cudaFreeHost(slot.host));
-            slot.host = nullptr;
-            CU(cudaMallocHost(&slot.host, total));
-            slot.hostCap = total;
-        }
+        std::vector<CopyTask> tasks;
         for (auto& pc : pieces)
-            if (pc.bytes) memcpy((char*)slot.host + pc.off, pc.src, pc.bytes);
+            if (pc.bytes) tasks.push_back(CopyTask{CopyTask::BYTES, (char*)slot.host + pc.off, pc.src, pc.bytes, 0});
+        hostCopy(tasks);
         CU(cudaMemcpyAsync(dbase, slot.host, total, cudaMemcpyHostToDevice, p->stream));
     }
     for (auto& pc : pieces) p->stats.h2d_bytes += (int64_t)pc.bytes;
@@ -775,6 +854,334 @@ pgpu_status stageChunk(pgpu_pipeline* p, Variant* v, const pgpu_column* cols, in
     return PGPU_OK;
 }
 
+// ---- coalescing appender --------------------------------------------------------------------------------------------------
+// The reference hands operators pages of <= 4096 rows out of RecordPageSource (spi/connector/RecordPageSource.java:84-131) and
+// <= 8192-row / ~1 MB batches out of PageProcessor (main/operator/project/PageProcessor.java:56-57). One launch per such page
+// would be all launch latency, so host pages are appended, array by array, to a super-page in the current pinned slot
+// ("one launch per input page or per coalesced super-page") and the slot is sent — one DMA per array, one
+// kernel launch — when it is full, when the page signature changes, or when the operator has to produce output.
+inline int32_t rdI32(const char* q) {
+    int32_t v;
+    memcpy(&v, q, 4);
+    return v;
+}
+
+int varBytesPerRow(const Type& t) {
+    if (t.kind == TypeKind::VARCHAR) return t.precision > 0 ? std::min(t.precision, 64) : 32;
+    return 40;  // VARBINARY: intermediate decimal states, 24 / 32 bytes (LongDecimalWithOverflow[AndLong]StateSerializer)
+}
+
+const StageLayout& stageLayoutFor(pgpu_pipeline* p, Variant* v, const std::string& key, const std::vector<ColSig>& sig) {
+    auto it = p->stageLayouts.find(key);
+    if (it != p->stageLayouts.end()) return it->second;
+    const GenResult& g = v->gen;
+    const Plan& plan = *p->plan;
+    size_t rowBytes = 0;
+    for (int c : g.usedChannels) {
+        const Type& t = plan.input[c];
+        if (sig[c].encoding == PGPU_ENC_RLE) continue;
+        if (sig[c].encoding == PGPU_ENC_DICTIONARY) rowBytes += 4;
+        else rowBytes += t.isVarWidth() ? 4 + (size_t)varBytesPerRow(t) : (size_t)t.width();
+        if (sig[c].encoding == PGPU_ENC_PLAIN && sig[c].nullable) rowBytes += 1;
+    }
+    StageLayout lay;
+    // whole tiles of the staged kernel (so that only the last super-page of a stream has a ragged tail), else of the direct one
+    const int64_t unit = v->kPageStaged ? g.stagedTile : kTileRows;
+    int64_t cap = (int64_t)(p->stageTargetBytes / std::max<size_t>(rowBytes, 1));
+    cap = std::max<int64_t>(cap / unit * unit, unit * std::max(p->numSMs, 1));
+    lay.capRows = cap;
+    lay.cols.assign(g.NC, StageCol{});
+    size_t at = 0;
+    auto reserve = [&](size_t bytes) {
+        const size_t off = at;
+        at += align256(std::max<size_t>(bytes, 16));
+        return off;
+    };
+    for (int c : g.usedChannels) {
+        const Type& t = plan.input[c];
+        StageCol& sc = lay.cols[c];
+        sc.encoding = sig[c].encoding;
+        sc.nullable = sig[c].nullable;
+        if (sig[c].encoding == PGPU_ENC_PLAIN) {
+            if (t.isVarWidth()) {
+                sc.offsets = reserve((size_t)(cap + 1 + kOffsetsSlack) * 4);
+                sc.valuesCap = (size_t)cap * varBytesPerRow(t);
+                sc.values = reserve(sc.valuesCap + 32);
+            } else {
+                sc.width = t.width();
+                sc.values = reserve((size_t)cap * t.width());
+            }
+            if (sig[c].nullable) sc.nulls = reserve((size_t)cap);
+        } else {
+            if (sig[c].encoding == PGPU_ENC_DICTIONARY) sc.ids = reserve((size_t)cap * 4);
+            sc.dvalues = reserve(kDictStageBytes + 32);
+            if (t.isVarWidth()) sc.doffsets = reserve(kDictStageBytes + 64);
+            else sc.width = t.width();
+            if (sig[c].nullable) sc.dnulls = reserve(kDictStageBytes);
+        }
+    }
+    lay.bytes = at;
+    return p->stageLayouts.emplace(key, std::move(lay)).first->second;
+}
+
+// bytes of the dictionary / RLE value block of a channel, or -1 when it is too large to ride in a super-page
+int64_t dictValueBytes(const Type& t, const HostCol& hc) {
+    const int64_t dn = hc.dcount;
+    if (dn < 0 || (size_t)dn + 1 > kDictStageBytes / 4) return -1;
+    if (!t.isVarWidth()) return dn * t.width() <= (int64_t)kDictStageBytes ? dn * t.width() : -1;
+    if (dn == 0) return 0;
+    const int64_t total = hc.dEndOffsets ? rdI32(hc.doffsets + 4 * (dn - 1)) : (int64_t)rdI32(hc.doffsets + 4 * dn) - rdI32(hc.doffsets);
+    return total >= 0 && total <= (int64_t)kDictStageBytes ? total : -1;
+}
+
+// start of the dictionary's payload bytes inside dvalues
+int64_t dictByteBase(const HostCol& hc) { return hc.dEndOffsets || hc.dcount == 0 ? 0 : rdI32(hc.doffsets); }
+
+bool hostPageCoalescible(pgpu_pipeline* p, Variant* v, const std::vector<ColSig>& sig, const std::vector<HostCol>& hc) {
+    const GenResult& g = v->gen;
+    if (g.mode == KernelMode::COMPACT) return false;  // filter + project: one output page per input page
+    for (int c : g.usedChannels) {
+        if (sig[c].encoding == PGPU_ENC_VARCELL) return false;
+        if (sig[c].encoding != PGPU_ENC_PLAIN && dictValueBytes(p->plan->input[c], hc[c]) < 0) return false;
+    }
+    return true;
+}
+
+pgpu_status flushPending(pgpu_pipeline* p);
+
+// the dictionaries of `hc` are the ones the pending super-page already carries
+bool sameDictionaries(pgpu_pipeline* p, const std::vector<ColSig>& sig, const std::vector<HostCol>& hc) {
+    const PendingPage& pd = p->pend;
+    const StageSlot& slot = p->slots[p->nextSlot];
+    for (int c : pd.v->gen.usedChannels) {
+        if (sig[c].encoding == PGPU_ENC_PLAIN) continue;
+        const Type& t = p->plan->input[c];
+        const StageCol& sc = pd.lay->cols[c];
+        const int64_t bytes = dictValueBytes(t, hc[c]);
+        if (hc[c].dcount != pd.dcount[c] || bytes != (int64_t)pd.dbytes[c]) return false;
+        if (bytes && memcmp((const char*)hc[c].dvalues + dictByteBase(hc[c]), (const char*)slot.host + sc.dvalues, (size_t)bytes)) return false;
+        if (hc[c].dnulls && memcmp(hc[c].dnulls, (const char*)slot.host + sc.dnulls, (size_t)hc[c].dcount)) return false;
+        if (t.isVarWidth()) {  // same bytes, same boundaries
+            const int32_t* have = (const int32_t*)((const char*)slot.host + sc.doffsets);
+            const int64_t base = dictByteBase(hc[c]);
+            for (int64_t i = 0; i < hc[c].dcount; i++) {
+                const int64_t endv = hc[c].dEndOffsets ? rdI32(hc[c].doffsets + 4 * i) : rdI32(hc[c].doffsets + 4 * (i + 1)) - base;
+                if (have[i + 1] != (int32_t)endv) return false;
+            }
+        }
+    }
+    return true;
+}
+
+pgpu_status beginPending(pgpu_pipeline* p, Variant* v, const std::string& key, const std::vector<ColSig>& sig, const std::vector<HostCol>& hc) {
+    PendingPage& pd = p->pend;
+    const StageLayout& lay = stageLayoutFor(p, v, key, sig);
+    StageSlot* slot = nullptr;
+    pgpu_status st = acquireSlot(p, &slot);
+    if (st) return st;
+    st = ensureSlot(p, *slot, lay.bytes, true);
+    if (st) return st;
+    pd.v = v;
+    pd.key = key;
+    pd.lay = &lay;
+    pd.rows = 0;
+    pd.vbytes.assign(v->gen.NC, 0);
+    pd.dcount.assign(v->gen.NC, 0);
+    pd.dbytes.assign(v->gen.NC, 0);
+    // the super-page's dictionaries: copied once, by its first page
+    std::vector<CopyTask> tasks;
+    char* hbase = (char*)slot->host;
+    for (int c : v->gen.usedChannels) {
+        if (sig[c].encoding == PGPU_ENC_PLAIN) continue;
+        const Type& t = p->plan->input[c];
+        const StageCol& sc = lay.cols[c];
+        const int64_t bytes = dictValueBytes(t, hc[c]);
+        pd.dcount[c] = (int32_t)hc[c].dcount;
+        pd.dbytes[c] = (size_t)bytes;
+        if (bytes) tasks.push_back(CopyTask{CopyTask::BYTES, hbase + sc.dvalues, (const char*)hc[c].dvalues + dictByteBase(hc[c]), (size_t)bytes, 0});
+        if (hc[c].dnulls && hc[c].dcount) tasks.push_back(CopyTask{CopyTask::BYTES, hbase + sc.dnulls, hc[c].dnulls, (size_t)hc[c].dcount, 0});
+        if (t.isVarWidth()) {
+            int32_t* dst = (int32_t*)(hbase + sc.doffsets);
+            dst[0] = 0;
+            const int32_t base = (int32_t)dictByteBase(hc[c]);
+            if (hc[c].dcount)
+                tasks.push_back(CopyTask{CopyTask::OFFSETS32, dst + 1, hc[c].doffsets + (hc[c].dEndOffsets ? 0 : 4), (size_t)hc[c].dcount * 4, -base});
+        }
+    }
+    hostCopy(tasks);
+    return PGPU_OK;
+}
+
+// Append rows [r0, r0 + n) of a host page to the pending super-page (the caller has made sure they fit).
+void appendRows(pgpu_pipeline* p, const std::vector<ColSig>& sig, const std::vector<HostCol>& hc, int64_t r0, int64_t n) {
+    PendingPage& pd = p->pend;
+    const StageLayout& lay = *pd.lay;
+    char* hbase = (char*)p->slots[p->nextSlot].host;
+    std::vector<CopyTask> tasks;
+    for (int c : pd.v->gen.usedChannels) {
+        const Type& t = p->plan->input[c];
+        const StageCol& sc = lay.cols[c];
+        const HostCol& h = hc[c];
+        if (sig[c].encoding == PGPU_ENC_PLAIN) {
+            if (t.isVarWidth()) {
+                const int32_t b0 = h.endOffsets ? (r0 ? rdI32(h.offsets + 4 * (r0 - 1)) : 0) : rdI32(h.offsets + 4 * r0);
+                const char* ends = h.offsets + 4 * (r0 + (h.endOffsets ? 0 : 1));
+                const int32_t b1 = rdI32(ends + 4 * (n - 1));
+                int32_t* dst = (int32_t*)(hbase + sc.offsets) + pd.rows;
+                dst[0] = (int32_t)pd.vbytes[c];
+                tasks.push_back(CopyTask{CopyTask::OFFSETS32, dst + 1, ends, (size_t)n * 4, (int32_t)pd.vbytes[c] - b0});
+                if (b1 > b0) tasks.push_back(CopyTask{CopyTask::BYTES, hbase + sc.values + pd.vbytes[c], (const char*)h.values + b0, (size_t)(b1 - b0), 0});
+                pd.vbytes[c] += b1 - b0;
+                p->stats.h2d_bytes += (int64_t)n * 4 + (b1 - b0);
+            } else {
+                tasks.push_back(CopyTask{CopyTask::BYTES, hbase + sc.values + (size_t)pd.rows * sc.width, (const char*)h.values + (size_t)r0 * sc.width, (size_t)n * sc.width, 0});
+                p->stats.h2d_bytes += n * sc.width;
+            }
+            if (sig[c].nullable) {
+                tasks.push_back(CopyTask{CopyTask::BYTES, hbase + sc.nulls + pd.rows, h.nulls + r0, (size_t)n, 0});
+                p->stats.h2d_bytes += n;
+            }
+        } else if (sig[c].encoding == PGPU_ENC_DICTIONARY) {
+            tasks.push_back(CopyTask{CopyTask::BYTES, hbase + sc.ids + (size_t)pd.rows * 4, h.ids + (size_t)r0 * 4, (size_t)n * 4, 0});
+            p->stats.h2d_bytes += n * 4;
+        }
+    }
+    hostCopy(tasks);
+    pd.rows += n;
+}
+
+// Send the pending super-page: one DMA per array, one launch of the page kernel.
+pgpu_status flushPending(pgpu_pipeline* p) {
+    PendingPage& pd = p->pend;
+    if (pd.rows == 0) return PGPU_OK;
+    CU(cudaSetDevice(p->device));
+    Variant* v = pd.v;
+    const GenResult& g = v->gen;
+    const StageLayout& lay = *pd.lay;
+    StageSlot& slot = p->slots[p->nextSlot];
+    char* hbase = (char*)slot.host;
+    char* dbase = (char*)slot.dev.ptr;
+    const int64_t n = pd.rows;
+    auto h2d = [&](size_t off, size_t bytes) -> cudaError_t {
+        return bytes ? cudaMemcpyAsync(dbase + off, hbase + off, bytes, cudaMemcpyHostToDevice, p->stream) : cudaSuccess;
+    };
+    DevPage pg;
+    pg.rows = n;
+    pg.slack = kOffsetsSlack;
+    pg.cols.assign(g.NC, ColArg{});
+    for (int c : g.usedChannels) {
+        const Type& t = p->plan->input[c];
+        const StageCol& sc = lay.cols[c];
+        ColArg a{};
+        if (sc.encoding == PGPU_ENC_PLAIN) {
+            if (t.isVarWidth()) {
+                int32_t* offs = (int32_t*)(hbase + sc.offsets);
+                for (int k = 1; k <= kOffsetsSlack; k++) offs[n + k] = offs[n];  // the staged kernel reads a few offsets past the end
+                CU(h2d(sc.offsets, (size_t)(n + 1 + kOffsetsSlack) * 4));
+                CU(h2d(sc.values, (size_t)pd.vbytes[c]));
+                a.offsets = (const int32_t*)(dbase + sc.offsets);
+                a.values = dbase + sc.values;
+            } else {
+                CU(h2d(sc.values, (size_t)n * sc.width));
+                a.values = dbase + sc.values;
+            }
+            if (sc.nullable) {
+                CU(h2d(sc.nulls, (size_t)n));
+                a.nulls = (const uint8_t*)(dbase + sc.nulls);
+            }
+        } else {
+            if (sc.encoding == PGPU_ENC_DICTIONARY) {
+                CU(h2d(sc.ids, (size_t)n * 4));
+                a.ids = (const int32_t*)(dbase + sc.ids);
+            }
+            CU(h2d(sc.dvalues, pd.dbytes[c]));
+            a.dvalues = dbase + sc.dvalues;
+            a.dcount = pd.dcount[c];
+            if (t.isVarWidth()) {
+                CU(h2d(sc.doffsets, (size_t)(pd.dcount[c] + 1) * 4));
+                a.doffsets = (const int32_t*)(dbase + sc.doffsets);
+            }
+            if (sc.nullable) {
+                CU(h2d(sc.dnulls, (size_t)pd.dcount[c]));
+                a.dnulls = (const uint8_t*)(dbase + sc.dnulls);
+            }
+        }
+        pg.cols[c] = a;
+    }
+    pd.rows = 0;
+    p->stats.super_pages++;
+    pgpu_status st = launchPageKernel(p, v, pg);
+    if (st) return st;
+    return releaseSlot(p, slot);
+}
+
+// rows of [r0, rows) that still fit into the pending super-page (row capacity and the payload capacity of var-width channels)
+int64_t rowsThatFit(pgpu_pipeline* p, const std::vector<ColSig>& sig, const std::vector<HostCol>& hc, int64_t r0, int64_t rows) {
+    const PendingPage& pd = p->pend;
+    int64_t n = std::min(rows - r0, pd.lay->capRows - pd.rows);
+    for (int c : pd.v->gen.usedChannels) {
+        if (n <= 0) break;
+        const Type& t = p->plan->input[c];
+        if (sig[c].encoding != PGPU_ENC_PLAIN || !t.isVarWidth()) continue;
+        const HostCol& h = hc[c];
+        const int64_t b0 = h.endOffsets ? (r0 ? rdI32(h.offsets + 4 * (r0 - 1)) : 0) : rdI32(h.offsets + 4 * r0);
+        const char* ends = h.offsets + 4 * (r0 + (h.endOffsets ? 0 : 1));
+        const int64_t room = (int64_t)pd.lay->cols[c].valuesCap - pd.vbytes[c];
+        if ((int64_t)rdI32(ends + 4 * (n - 1)) - b0 <= room) continue;
+        int64_t lo = 0, hi = n;  // largest k with bytes(r0, r0 + k) <= room
+        while (lo < hi) {
+            const int64_t mid = (lo + hi + 1) / 2;
+            if ((int64_t)rdI32(ends + 4 * (mid - 1)) - b0 <= room) lo = mid;
+            else hi = mid - 1;
+        }
+        n = lo;
+    }
+    return std::max<int64_t>(n, 0);
+}
+
+pgpu_status appendHostPage(pgpu_pipeline* p, Variant* v, const std::vector<ColSig>& sig, const std::vector<HostCol>& hc, int64_t rows) {
+    PendingPage& pd = p->pend;
+    const std::string key = sigKey(sig);
+    pgpu_status st;
+    if (pd.rows > 0 && (pd.key != key || !sameDictionaries(p, sig, hc))) {
+        if ((st = flushPending(p))) return st;
+    }
+    int64_t r0 = 0;
+    while (r0 < rows) {
+        if (pd.rows == 0 && (st = beginPending(p, v, key, sig, hc))) return st;
+        const int64_t n = rowsThatFit(p, sig, hc, r0, rows);
+        if (n == 0) {
+            if (pd.rows == 0) return fail(p, PGPU_INSUFFICIENT_RESOURCES, "a single var-width value does not fit into a staging slot");
+            if ((st = flushPending(p))) return st;
+            continue;
+        }
+        appendRows(p, sig, hc, r0, n);
+        r0 += n;
+        if (pd.rows >= pd.lay->capRows && (st = flushPending(p))) return st;
+    }
+    return PGPU_OK;
+}
+
+void hostColsOf(const Plan& plan, const pgpu_column* cols, int ncols, std::vector<HostCol>& hc) {
+    hc.assign((size_t)ncols, HostCol{});
+    for (int c = 0; c < ncols; c++) {
+        const pgpu_column& col = cols[c];
+        HostCol& h = hc[c];
+        h.encoding = col.encoding;
+        if (col.encoding == PGPU_ENC_PLAIN) {
+            h.values = col.values;
+            h.nulls = col.nulls;
+            h.offsets = (const char*)col.offsets;
+        } else if (col.dictionary) {
+            h.ids = (const char*)col.ids;
+            h.dvalues = col.dictionary->values;
+            h.dnulls = col.dictionary->nulls;
+            h.doffsets = (const char*)col.dictionary->offsets;
+            h.dcount = col.dictionary->position_count;
+        }
+    }
+}
+
 pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows, bool onDevice, uint32_t flags) {
     if (p->device < 0) return fail(p, PGPU_INVALID_STATE, "pipeline was created compile-only (device < 0)");
     if (p->finishing) return fail(p, PGPU_INVALID_STATE, "Operator is already finishing");
@@ -797,22 +1204,28 @@ pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
             if (mis(col.values, 16) || mis(col.ids, 16) || mis(col.offsets, 16) || mis(col.nulls, 4))
                 return fail(p, PGPU_INVALID_ARGUMENT, "device blocks must be 16-byte aligned (nulls: 4-byte)");
         }
+        if ((st = flushPending(p))) return st;
         return processDevicePage(p, v, cols, rows);
     }
     for (int c : v->gen.usedChannels)
         if (cols[c].encoding == PGPU_ENC_VARCELL) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: 16-byte cell columns in host pages (device-to-device encoding)");
-    // host page: stage in chunks through the ring, then run as device chunks
     const bool pinned = (flags & PGPU_PAGE_PINNED) != 0;
+    if (!pinned) {
+        // ordinary (pageable) memory: append to the super-page in the pinned ring
+        std::vector<HostCol> hc;
+        hostColsOf(*p->plan, cols, ncols, hc);
+        if (hostPageCoalescible(p, v, sig, hc)) return appendHostPage(p, v, sig, hc, rows);
+    }
+    if ((st = flushPending(p))) return st;
+    // caller-pinned pages (DMA straight from the caller's buffers), filter + project pages, oversized dictionaries: staged in
+    // chunks through the ring, one launch per chunk
     const bool compact = v->gen.mode == KernelMode::COMPACT;
     int64_t chunk = compact ? rows : kHostChunkRows;
     for (int64_t r0 = 0; r0 < rows; r0 += chunk) {
         int64_t n = std::min(chunk, rows - r0);
-        StageSlot& slot = p->slots[p->nextSlot];
-        p->nextSlot = (p->nextSlot + 1) % 3;
-        if (slot.inFlight) {
-            CU(cudaEventSynchronize(slot.done));
-            slot.inFlight = false;
-        }
+        StageSlot* slotp = nullptr;
+        if ((st = acquireSlot(p, &slotp))) return st;
+        StageSlot& slot = *slotp;
         DevPage pg;
         pg.rows = n;
         st = stageChunk(p, v, cols, r0, n, pinned, slot, pg.cols);
@@ -823,9 +1236,7 @@ pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
             st = launchPageKernel(p, v, pg);
         }
         if (st) return st;
-        if (!slot.done) CU(cudaEventCreateWithFlags(&slot.done, cudaEventDisableTiming));
-        CU(cudaEventRecord(slot.done, p->stream));
-        slot.inFlight = true;
+        if ((st = releaseSlot(p, slot))) return st;
     }
     return PGPU_OK;
 }
@@ -833,9 +1244,12 @@ pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
 // PARTIAL step: once the row-count upper bound crosses the flush threshold, learn the real group count
 pgpu_status updatePartialFill(pgpu_pipeline* p) {
     const Plan& plan = *p->plan;
-    if (plan.hasAgg && outputIsIntermediate(plan.step) && plan.maxPartialGroups > 0 && !plan.groupChannels.empty() && p->dSlots &&
-        p->groupsKnown + p->rowsSinceKnown >= plan.maxPartialGroups)
-        return refreshGroupCount(p);
+    if (plan.hasAgg && outputIsIntermediate(plan.step) && plan.maxPartialGroups > 0 && !plan.groupChannels.empty() &&
+        p->groupsKnown + p->rowsSinceKnown + p->pend.rows >= plan.maxPartialGroups) {
+        pgpu_status st = flushPending(p);  // rows still waiting in the staging slot count: aggregate them, then look
+        if (st) return st;
+        if (p->dSlots) return refreshGroupCount(p);
+    }
     return PGPU_OK;
 }
 
@@ -843,6 +1257,10 @@ pgpu_status updatePartialFill(pgpu_pipeline* p) {
 pgpu_status buildAggOutput(pgpu_pipeline* p) {
     const GenResult& g = p->layout;
     CU(cudaSetDevice(p->device));
+    {
+        pgpu_status st = flushPending(p);
+        if (st) return st;
+    }
     // any compiled variant has the emit kernels (layout is signature independent)
     Variant* v = nullptr;
     if (p->variants.empty()) {
@@ -903,7 +1321,7 @@ void resetAggState(pgpu_pipeline* p) {
 
 bool isPartialFlushDue(const pgpu_pipeline* p) {
     return p->plan->hasAgg && outputIsIntermediate(p->plan->step) && p->plan->maxPartialGroups > 0 && !p->plan->groupChannels.empty() &&
-           (p->groupsKnown + p->rowsSinceKnown) >= p->plan->maxPartialGroups;
+           (p->groupsKnown + p->rowsSinceKnown + p->pend.rows) >= p->plan->maxPartialGroups;
 }
 
 }  // namespace
@@ -938,6 +1356,7 @@ pgpu_status pgpu_pipeline_create(const uint8_t* plan, size_t plan_len, int32_t d
         return (pgpu_status)e.status;
     }
     p->device = device;
+    if (const char* e = getenv("PGPU_STAGE_MB")) p->stageTargetBytes = (size_t)std::max(1, atoi(e)) << 20;
     pgpu_pipeline* pp = p.get();
     auto cuFail = [&](cudaError_t e, const char* what) {
         g_lastGlobalError = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
@@ -1161,6 +1580,54 @@ pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size
     }
     if (r.pos != len) return fail(p, PGPU_INVALID_ARGUMENT, "trailing bytes after the last block");
     CU(cudaSetDevice(p->device));
+    // Blocks without null flags carry their arrays as they are (LongArrayBlockEncoding.java:39-60: values of every position;
+    // VariableWidthBlockEncoding.java:37-58: end offsets + bytes): such a page is appended to the current super-page straight
+    // out of the payload, like a page of host blocks — no per-page DMA, no per-page decode launches.
+    bool plainArrays = true;
+    for (int c = 0; c < nblocks; c++) plainArrays &= !blocks[c].hasNulls && !(blocks[c].child && blocks[c].child->hasNulls);
+    if (plainArrays) {
+        std::vector<ColSig> sig((size_t)nblocks);
+        std::vector<HostCol> hc((size_t)nblocks);
+        const char* base = (const char*)data;
+        bool sane = true;
+        for (int c = 0; c < nblocks; c++) {
+            const WireBlock& b = blocks[c];
+            HostCol& h = hc[c];
+            sig[c].encoding = b.kind == WireBlock::DICTIONARY ? PGPU_ENC_DICTIONARY : b.kind == WireBlock::RLE ? PGPU_ENC_RLE : PGPU_ENC_PLAIN;
+            sig[c].nullable = false;
+            h.encoding = sig[c].encoding;
+            auto lastEnd = [&](const WireBlock& w) { return w.n ? rdI32(base + w.offsetsOff + 4 * (size_t)(w.n - 1)) : 0; };
+            if (!b.child) {
+                h.values = base + b.valuesOff;
+                if (b.kind == WireBlock::VARWIDTH) {
+                    h.offsets = base + b.offsetsOff;
+                    h.endOffsets = true;
+                    sane &= lastEnd(b) <= b.dataLen;
+                }
+            } else {
+                const WireBlock& d = *b.child;
+                h.ids = base + b.valuesOff;
+                h.dvalues = base + d.valuesOff;
+                h.dcount = d.n;
+                if (d.kind == WireBlock::VARWIDTH) {
+                    h.doffsets = base + d.offsetsOff;
+                    h.dEndOffsets = true;
+                    sane &= lastEnd(d) <= d.dataLen;
+                }
+            }
+        }
+        if (!sane) return fail(p, PGPU_INVALID_ARGUMENT, "corrupt VARIABLE_WIDTH block: offsets exceed the data length");
+        Variant* v = nullptr;
+        pgpu_status st = getVariant(p, sig, &v);
+        if (st) return st;
+        if (position_count > 0 && hostPageCoalescible(p, v, sig, hc)) {
+            p->sawInput = true;
+            p->stats.input_pages++;
+            p->stats.input_rows += position_count;
+            st = appendHostPage(p, v, sig, hc, position_count);
+            return st ? st : updatePartialFill(p);
+        }
+    }
     // device arena: [payload][decoded arrays, each 256-byte aligned]
     size_t need = align256(len);
     auto reserve = [&](size_t bytes) {
@@ -1336,7 +1803,7 @@ pgpu_status pgpu_parquet_chunk_runs(const pgpu_parquet_chunk* chunk, int32_t whi
 pgpu_status pgpu_finish(pgpu_pipeline* p) {
     if (!p) return PGPU_INVALID_ARGUMENT;
     p->finishing = true;
-    return PGPU_OK;
+    return p->device >= 0 ? flushPending(p) : PGPU_OK;  // the last (partly filled) super-page starts now, not at getOutput
 }
 
 int32_t pgpu_is_finished(const pgpu_pipeline* p) { return p && p->finished ? 1 : 0; }
@@ -1623,6 +2090,10 @@ pgpu_status pgpu_sync(pgpu_pipeline* p) {
     if (!p) return PGPU_INVALID_ARGUMENT;
     if (p->device < 0) return PGPU_OK;
     CU(cudaSetDevice(p->device));
+    {
+        pgpu_status st = flushPending(p);
+        if (st) return st;
+    }
     CU(cudaStreamSynchronize(p->stream));
     for (auto& s : p->slots) s.inFlight = false;
     return checkDeviceErrors(p);
@@ -1630,10 +2101,12 @@ pgpu_status pgpu_sync(pgpu_pipeline* p) {
 
 pgpu_status pgpu_reset(pgpu_pipeline* p) {
     if (!p) return PGPU_INVALID_ARGUMENT;
+    p->pend.rows = 0;  // rows waiting in the staging slot are dropped with the rest of the state
     if (p->device >= 0) {
         CU(cudaSetDevice(p->device));
         resetAggState(p);
         CU(cudaStreamSynchronize(p->stream));
+        for (auto& s : p->slots) s.inFlight = false;
     }
     p->finishing = p->finished = p->sawInput = p->outputReady = false;
     p->outRowsTotal = p->outRowsServed = 0;
