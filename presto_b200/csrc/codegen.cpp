@@ -740,7 +740,7 @@ std::string maskOf(int nbytes) {
 
 }  // namespace
 
-GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
+GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOptions& opt) {
     if (sig.size() != plan.input.size()) throw PlanError(PGPU_INVALID_ARGUMENT, "page has " + std::to_string(sig.size()) + " channels, plan expects " + std::to_string(plan.input.size()));
     GenResult res;
     res.NC = (int)plan.input.size();
@@ -1257,8 +1257,26 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     const bool highCard = res.mode == KernelMode::AGG_HASH && !res.useDir && tagless;
     const bool runs = highCard && runsBytes <= 48 * 1024 && envInt("PGPU_TUNE_RUNS", plan.step == Step::SINGLE ? kDefaultRunsSingleStep : kDefaultRunsOtherSteps) != 0;
     if (runs) res.smemBytes = runsBytes;
+    // bucketed table: one integer key (so that "the 3 low bits" means neighbouring keys), two spare bytes in the last key word
+    // (presence byte + occupied mark), run compaction available (the bucket path is built on it, whatever the step)
+    bool bucketsOk = highCard && fields.size() == 1 && runsBytes <= 48 * 1024 && NW > 0 && keyLen <= KW * 8 - 2 && fields[0].byteOffset < 7;
+    if (bucketsOk) {
+        const TypeKind k0 = fields[0].type.kind;
+        bucketsOk = k0 == TypeKind::BIGINT || k0 == TypeKind::INTEGER || k0 == TypeKind::DATE || (k0 == TypeKind::DECIMAL && fields[0].type.isShortDecimal());
+    }
+    res.bucketsPossible = bucketsOk;
+    res.buckets = bucketsOk && opt.buckets;
+    if (bucketsOk) {
+        const Expr& ke = *plan.projections[fields[0].projChannel];
+        if (ke.kind == ExprKind::INPUT) res.bucketKeyChannel = ke.channel;
+    }
+    const int bslotw = (KW + 8 * NW + 3) / 4 * 4;
+    if (res.buckets) {
+        res.SLOTW = bslotw;
+        res.smemBytes = runsBytes;
+    }
     int locB = 0, locSh = 0;
-    if (highCard && !fields.empty() && fields[0].byteOffset < 7) {
+    if (highCard && !res.buckets && !fields.empty() && fields[0].byteOffset < 7) {
         const TypeKind k0 = fields[0].type.kind;
         if (k0 == TypeKind::BIGINT || k0 == TypeKind::INTEGER || k0 == TypeKind::DATE || (k0 == TypeKind::DECIMAL && fields[0].type.isShortDecimal())) {
             locB = std::min(std::max(envInt("PGPU_TUNE_LOCB", kDefaultLocBits), 0), 6);
@@ -1307,6 +1325,9 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
     src << "    static constexpr bool TAGLESS = " << (tagless ? "true" : "false") << ";\n";
     src << "    static constexpr bool LANE_MERGE = " << (getenv("PGPU_TUNE_NOLANEMERGE") ? "false" : "true") << ";\n";
     src << "    static constexpr bool RUNS = " << (runs ? "true" : "false") << ";  // run compaction (HashCtx::consume_runs)\n";
+    src << "    static constexpr bool BUCKETS = " << (res.buckets ? "true" : "false") << ";  // bucketed table: SLOTW words per bucket of 8 keys\n";
+    src << "    static constexpr int BSLOTW = " << bslotw << ", BSH = " << (fields.empty() ? 0 : 8 * fields[0].byteOffset) << ", BPRES = 48;\n";
+    src << "    static constexpr u64 BPMASK = 0xffull << BPRES;\n";
     src << "    static constexpr int KOFF = " << (tagless ? 0 : 1) << ";  // first key word of a slot\n";
     src << "    static constexpr bool USE_DIR = " << (res.useDir ? "true" : "false") << ";\n";
     src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 8;\n";
@@ -1577,8 +1598,14 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig) {
         src << "extern \"C\" __global__ void __launch_bounds__(256, " << (getenv("PGPU_TUNE_MINBLOCKS") ? atoi(getenv("PGPU_TUNE_MINBLOCKS")) : (res.useDir ? 2 : 3)) << ") pgpu_k_page(PageArgs<P::NC> a, TableArgs t, Scratch sc) { body_agg_hash<P>(a, t, sc); }\n";
         if (res.staged)
             src << "extern \"C\" __global__ void __launch_bounds__(512, 1) pgpu_k_page_staged(PageArgs<P::NC> a, TableArgs t, Scratch sc, int nstages) { body_agg_hash_staged<P>(a, t, sc, nstages); }\n";
-        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots) { body_materialize<P>(t, out, sc, first_slot, nslots); }\n";
-        src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_rehash(TableArgs from, TableArgs to, Scratch sc) { body_rehash<P>(from, to, sc); }\n";
+        if (res.buckets) {
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots) { body_materialize_b<P>(t, out, sc, first_slot, nslots); }\n";
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_rehash(TableArgs from, TableArgs to, Scratch sc) { body_rehash_b<P>(from, to, sc); }\n";
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_count(TableArgs t, Scratch sc) { body_count_groups<P>(t, sc); }\n";
+        } else {
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots) { body_materialize<P>(t, out, sc, first_slot, nslots); }\n";
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_rehash(TableArgs from, TableArgs to, Scratch sc) { body_rehash<P>(from, to, sc); }\n";
+        }
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";
     }
     res.source = src.str();

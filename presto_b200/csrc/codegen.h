@@ -47,9 +47,17 @@ struct GenResult {
     std::vector<int> cellKinds;  // NW entries (CK_*)
     std::vector<OutColDesc> out;
     std::vector<int> usedChannels;  // input channels the kernels dereference
+    // bucketed table (8 neighbouring keys of one integer key field per slot; device/pgpu_device.cuh "bucketed slots")
+    bool bucketsPossible = false;  // the plan qualifies: high cardinality, one integer key, run compaction fits
+    bool buckets = false;          // this source was generated for the bucketed table: SLOTW = words per BUCKET
+    int bucketKeyChannel = -1;     // input channel the key is read from as it is (-1: the key is computed), for the clustering probe
+};
+
+struct GenOptions {
+    bool buckets = false;  // generate the bucketed-table kernels (ignored unless GenResult::bucketsPossible)
 };
 
 // throws PlanError(PGPU_NOT_SUPPORTED) for expression forms that parse but have no GPU implementation
-GenResult generate(const Plan& plan, const std::vector<ColSig>& sig);
+GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOptions& opt = GenOptions());
 
 }  // namespace pgpu

@@ -474,7 +474,8 @@ PGPU_DEV ProbePre probe_prefetch(const TableArgs& t, u64 h) {
     else ld_relaxed_u128(s, p.c0, p.c1);
     return p;
 }
-template <int KW, int SLOTW, bool TAGLESS>
+// PMASK (tagless only): bits of the last key word that take no part in the comparison — the presence byte of a bucket header.
+template <int KW, int SLOTW, bool TAGLESS, u64 PMASK = 0ull>
 PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1], u64 h, bool allow, u32& nins, const ProbePre* pre = nullptr, u32 skip = 0) {
     u64 pos = home_pos(h, t.capacity) + skip;  // skip: slots of the chain the caller has already examined
     if (pos >= t.capacity) pos -= t.capacity;
@@ -488,21 +489,21 @@ PGPU_DEV u64* table_upsert(const TableArgs& t, const u64 (&key)[KW > 0 ? KW : 1]
             u64* s = t.slots + pos * SLOTW;
             if (KW == 1) {
                 if (!have) c0 = ld_relaxed_u64(s);
-                if (c0 == k0) return s;
+                if ((c0 & ~PMASK) == k0) return s;
                 if (c0 == 0ull) {
                     if (!allow) return nullptr;
                     c0 = atomicCAS(s, 0ull, k0);
                     if (c0 == 0ull) { nins++; return s; }
-                    if (c0 == k0) return s;
+                    if ((c0 & ~PMASK) == k0) return s;
                 }
             } else {
                 if (!have) ld_relaxed_u128(s, c0, c1);
-                if (c0 == k0 && c1 == k1) return s;
+                if (c0 == k0 && (c1 & ~PMASK) == k1) return s;
                 if (c1 == 0ull) {
                     if (!allow) return nullptr;
                     cas_u128(s, 0ull, 0ull, k0, k1, c0, c1);
                     if (c1 == 0ull) { nins++; return s; }
-                    if (c0 == k0 && c1 == k1) return s;
+                    if (c0 == k0 && (c1 & ~PMASK) == k1) return s;
                 }
             }
             have = false;
@@ -555,6 +556,36 @@ PGPU_DEV void slot_key(const u64* slot, u64 (&key)[P::KW > 0 ? P::KW : 1]) {
     if (P::TAGLESS) key[P::KW - 1] &= ~KEY_MARK;
 }
 
+// ---- bucketed slots (P::BUCKETS): high-cardinality tables over ONE integer key whose values come in clusters (l_orderkey:
+// 8 used keys of every 32, rows of an order adjacent). A slot holds the 8 keys that differ only in the 3 low bits of the
+// key field: slot = [bucket key words | 8 x NW cells] (P::BSLOTW words). The bucket key is the packed key with those 3 bits
+// cleared, published with the same single compare-and-swap as a tagless key; the last key word also carries a presence
+// byte (bit P::BPRES + j: key j of the bucket exists), set with a fire-and-forget RED.OR and ignored by comparisons.
+// One 160-byte fetch and write-back per 8 groups instead of eight 64 + 32-byte ones; groups are counted when the table is
+// read out (body_count_groups), t.counters[0] counts claimed buckets.
+template <class P>
+PGPU_DEV void bucket_split(const u64 (&key)[P::KWA], u64 (&bk)[P::KWA], u32& sub) {
+#pragma unroll
+    for (int i = 0; i < P::KWA; i++) bk[i] = key[i];
+    sub = (u32)(key[0] >> P::BSH) & 7u;
+    bk[0] &= ~(7ull << P::BSH);
+}
+template <class P>
+PGPU_DEV void bucket_join(const u64* slot, u32 sub, u64 (&key)[P::KWA]) {
+#pragma unroll
+    for (int i = 0; i < P::KW; i++) key[i] = slot[i];
+    key[P::KWA - 1] &= ~(KEY_MARK | P::BPMASK);
+    key[0] |= (u64)sub << P::BSH;
+}
+template <class P>
+PGPU_DEV u32 bucket_presence(const u64* slot) {
+    const u64 w = slot[P::KWA - 1];
+    return (w & KEY_MARK) ? (u32)(w >> P::BPRES) & 0xffu : 0u;
+}
+// update key `key` (force: claim a bucket even beyond the load-factor limit); false = deferred
+template <class P>
+PGPU_DEV bool bucket_update(const TableArgs& t, const u64 (&key)[P::KWA], const u64 (&hot)[P::NHA], bool force, u32& nins);
+
 // Accumulator words come in two layouts. CELLS (P::NW words) is the persistent layout of a table slot / the global
 // state; it never depends on which pages carry null vectors. HOT (P::NH words) is what the scan loop carries: cells
 // whose per-row contribution is the same expression (e.g. every count when no input is NULL) share one hot word and are
@@ -569,6 +600,17 @@ PGPU_DEV bool table_update(const TableArgs& t, const u64 (&key)[P::KW > 0 ? P::K
     u64* s = table_upsert<P::KW, P::SLOTW, P::TAGLESS>(t, key, hash_key<P::KW>(key), force || table_may_insert(t), nins);
     if (!s) return false;
     P::atomic_cells(s + P::KOFF + P::KW, hot);
+    return true;
+}
+template <class P>
+PGPU_DEV bool bucket_update(const TableArgs& t, const u64 (&key)[P::KWA], const u64 (&hot)[P::NHA], bool force, u32& nins) {
+    u64 bk[P::KWA];
+    u32 sub;
+    bucket_split<P>(key, bk, sub);
+    u64* s = table_upsert<P::KW, P::BSLOTW, true, P::BPMASK>(t, bk, hash_key<P::KW>(bk), force || table_may_insert(t), nins);
+    if (!s) return false;
+    P::atomic_cells(s + P::KW + sub * P::NW, hot);
+    atomicOr(s + P::KW - 1, 1ull << (P::BPRES + sub));
     return true;
 }
 // add the slots a thread claimed to the table's group counter
@@ -1059,10 +1101,10 @@ struct HashCtx {
         if (s) P::atomic_cells(s + P::KOFF + KW, v);
         else defer_rows(t, wbase + a.s, a.e - a.s, err);
     }
-    // Must be called by all 32 lanes; `base` = global row number of the lane's first row, lanes hold consecutive rows.
-    PGPU_DEV void consume_runs(const TableArgs& t, i64 base, bool (&sel)[4], u64 (&key)[4][KW], u64 (&cw)[4][NHA]) {
+    // Stage the warp's 128 rows (lane l holds rows 4l .. 4l+3) in warp-private shared memory and list the run starts; returns the
+    // number of runs. Must be called by all 32 lanes.
+    PGPU_DEV int stage_runs(bool (&sel)[4], u64 (&key)[4][KW], u64 (&cw)[4][NHA]) {
         const int lane = threadIdx.x & 31;
-        const i64 wbase = base - 4 * lane;
         u8* starts = reinterpret_cast<u8*>(runsm + (KW + NHA) * 128);
         // 1. stage the rows: 4 consecutive 64-bit words per lane and array (two 128-bit stores)
 #pragma unroll
@@ -1109,6 +1151,14 @@ struct HashCtx {
             }
         }
         __syncwarp();
+        return nruns;
+    }
+    // Must be called by all 32 lanes; `base` = global row number of the lane's first row, lanes hold consecutive rows.
+    PGPU_DEV void consume_runs(const TableArgs& t, i64 base, bool (&sel)[4], u64 (&key)[4][KW], u64 (&cw)[4][NHA]) {
+        const int lane = threadIdx.x & 31;
+        const i64 wbase = base - 4 * lane;
+        const int nruns = stage_runs(sel, key, cw);
+        const u8* starts = reinterpret_cast<const u8*>(runsm + (KW + NHA) * 128);
         // 3. one run per lane (two in flight when the warp holds more than 32)
         const bool allow = table_may_insert(t);
 #pragma unroll 1
@@ -1127,6 +1177,123 @@ struct HashCtx {
         }
         __syncwarp();  // the next tile overwrites the staging area
     }
+
+    // ---- run compaction over a bucketed table (P::BUCKETS). As consume_runs, but the runs of one bucket — adjacent lanes,
+    // because the keys arrive clustered — share ONE probe: the first lane of the bucket (the leader) finds or claims the
+    // slot, its followers take the slot pointer by shuffle, every lane then adds its run to its own cells of the slot.
+    struct RunB {
+        int s, e;
+        bool act;
+        u64 bk[KW > 0 ? KW : 1];
+        u32 sub;
+        u64 h;
+        ProbePre pre;
+    };
+    PGPU_DEV void run_issue_b(const TableArgs& t, const u8* starts, int nruns, int j, RunB& a) {
+        a.act = j < nruns;
+        a.s = a.e = 0;
+        a.sub = 0;
+        a.h = 0;
+#pragma unroll
+        for (int w = 0; w < KW; w++) a.bk[w] = 0;
+        if (a.act) {
+            const u32 b = starts[j];
+            a.s = (int)(b & 127u);
+            a.e = j + 1 < nruns ? (int)(starts[j + 1] & 127u) : 128;
+            a.act = (b & 128u) == 0u;
+        }
+        if (a.act) {
+            u64 k[KW > 0 ? KW : 1];
+#pragma unroll
+            for (int w = 0; w < KW; w++) k[w] = runsm[w * 128 + a.s];
+            bucket_split<P>(k, a.bk, a.sub);
+            a.h = hash_key<KW>(a.bk);
+            a.pre = probe_prefetch<KW, P::BSLOTW>(t, a.h);
+        }
+    }
+    PGPU_DEV void run_resolve_b(const TableArgs& t, i64 wbase, bool allow, const RunB& a) {  // all 32 lanes
+        const int lane = threadIdx.x & 31;
+        u64 v[NHA];
+        P::identity(v);
+        if (a.act) {
+#pragma unroll
+            for (int i = 0; i < NHA; i++) v[i] = runsm[(KW + i) * 128 + a.s];
+#pragma unroll 1
+            for (int row = a.s + 1; row < a.e; row++) {
+                u64 b[NHA];
+#pragma unroll
+                for (int i = 0; i < NHA; i++) b[i] = runsm[(KW + i) * 128 + row];
+                P::combine(v, b);
+            }
+        }
+        // leaders: the first lane of each stretch of lanes that hold runs of the same bucket
+        bool same = a.act && lane > 0 && (__shfl_up_sync(FULLMASK, (int)a.act, 1) != 0);
+#pragma unroll
+        for (int w = 0; w < KW; w++) same &= (shfl_u64(a.bk[w], (lane + 31) & 31) == a.bk[w]);
+        const bool head = a.act && !same;
+        const u32 heads = __ballot_sync(FULLMASK, head);
+        const int leader = a.act ? 31 - __clz(heads & ((2u << lane) - 1u)) : lane;
+        u64* s = nullptr;
+        if (head) {
+            const u64 k0 = KW == 1 ? (a.bk[0] | KEY_MARK) : a.bk[0];
+            const u64 k1 = KW == 2 ? (a.bk[KW - 1] | KEY_MARK) : 0ull;
+            const bool found = KW == 1 ? (a.pre.c0 & ~P::BPMASK) == k0 : (a.pre.c0 == k0 && (a.pre.c1 & ~P::BPMASK) == k1);
+            const bool empty = KW == 1 ? a.pre.c0 == 0ull : a.pre.c1 == 0ull;
+            s = t.slots + home_pos(a.h, t.capacity) * P::BSLOTW;
+            if (!found) {
+                if (!empty) {
+                    s = table_upsert<KW, P::BSLOTW, true, P::BPMASK>(t, a.bk, a.h, allow, nins, nullptr, 1);  // walk the chain from home + 1
+                } else if (!allow) {
+                    s = nullptr;  // a new bucket while the table is at its load-factor limit: defer
+                } else {
+                    u64 o0 = 0, o1 = 0;
+                    if (KW == 1) o0 = atomicCAS(s, 0ull, k0);
+                    else cas_u128(s, 0ull, 0ull, k0, k1, o0, o1);
+                    const bool claimed = KW == 1 ? o0 == 0ull : o1 == 0ull;
+                    const bool mine = KW == 1 ? (o0 & ~P::BPMASK) == k0 : (o0 == k0 && (o1 & ~P::BPMASK) == k1);
+                    if (claimed) nins++;
+                    else if (!mine) s = table_upsert<KW, P::BSLOTW, true, P::BPMASK>(t, a.bk, a.h, true, nins, nullptr, 1);
+                }
+            }
+        }
+        s = reinterpret_cast<u64*>(shfl_u64((u64)(size_t)s, leader));
+        u32 bit = 0;
+        if (a.act) {
+            if (s) {
+                P::atomic_cells(s + KW + a.sub * P::NW, v);
+                bit = 1u << a.sub;
+            } else {
+                defer_rows(t, wbase + a.s, a.e - a.s, err);
+            }
+        }
+        // one RED.OR per bucket: the leader sets the presence bits of all its followers
+        const u32 peers = __match_any_sync(FULLMASK, a.act ? leader : 32 + lane);
+        const u32 bits = __reduce_or_sync(peers, bit);
+        if (head && s && bits) atomicOr(s + KW - 1, (u64)bits << P::BPRES);
+    }
+    PGPU_DEV void consume_runs_b(const TableArgs& t, i64 base, bool (&sel)[4], u64 (&key)[4][KW], u64 (&cw)[4][NHA]) {
+        const int lane = threadIdx.x & 31;
+        const i64 wbase = base - 4 * lane;
+        const int nruns = stage_runs(sel, key, cw);
+        const u8* starts = reinterpret_cast<const u8*>(runsm + (KW + NHA) * 128);
+        const bool allow = table_may_insert(t);
+#pragma unroll 1
+        for (int j0 = 0; j0 < nruns; j0 += 64) {
+            RunB a, b;
+            run_issue_b(t, starts, nruns, j0 + lane, a);
+            const bool two = j0 + 32 < nruns;  // warp-uniform
+            if (two) run_issue_b(t, starts, nruns, j0 + 32 + lane, b);
+            run_resolve_b(t, wbase, allow, a);
+            if (two) run_resolve_b(t, wbase, allow, b);
+        }
+        if (__any_sync(FULLMASK, nins != 0)) {
+            const u32 tot = __reduce_add_sync(FULLMASK, nins);
+            if (lane == 0) atomicAdd(t.counters, (u64)tot);
+            nins = 0;
+        }
+        __syncwarp();  // the next tile overwrites the staging area
+    }
+
 
     // End of kernel, whole block: fold register groups -> warp tables -> HBM table. `accwarps` = warps that own a wacc table
     // and hold register accumulators (the compute warps); other warps only take part in the barriers.
@@ -1186,7 +1353,8 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
         if (eager) P::eval_eager(a, base, a.rows, sel, key, cw, cx.err);
         else P::eval(a, base, a.rows, sel, key, cw, cx.err);
         eager = __popc(__ballot_sync(FULLMASK, sel[0] | sel[1] | sel[2] | sel[3])) >= P::EAGER_LANES;
-        if (P::RUNS) cx.consume_runs(t, base, sel, key, cw);
+        if constexpr (P::BUCKETS) cx.consume_runs_b(t, base, sel, key, cw);
+        else if (P::RUNS) cx.consume_runs(t, base, sel, key, cw);
         else cx.template consume<4>(t, base, sel, key, cw);
     }
     cx.flush(t, P::NWARP);
@@ -1367,7 +1535,12 @@ PGPU_DEV void body_replay(const PageArgs<P::NC>& a, const TableArgs& t, const Sc
         u32 ignored = 0;  // arithmetic errors of this tile were already reported by the first pass
         P::eval(a, base, a.rows, sel, key, cw, ignored);
         int r = (int)(row & 3);
-        if (sel[r] && !table_update<P>(t, key[r], cw[r], true, nins)) err |= PGPU_ERR_TABLE_FULL;
+        if (sel[r]) {
+            bool done;
+            if constexpr (P::BUCKETS) done = bucket_update<P>(t, key[r], cw[r], true, nins);
+            else done = table_update<P>(t, key[r], cw[r], true, nins);
+            if (!done) err |= PGPU_ERR_TABLE_FULL;
+        }
     }
     flush_inserts(t, nins);
     if (err) atomicOr(sc.err, err);
@@ -1538,6 +1711,90 @@ PGPU_DEV void body_rehash(const TableArgs& from, const TableArgs& to, const Scra
     }
     flush_inserts(to, nins);
     if (err) atomicOr(sc.err, err);
+}
+
+// ---- bucketed table: output, growth, group count -------------------------------------------------------------------------
+// One thread per bucket: its live keys (presence bits) become consecutive output rows.
+template <class P>
+PGPU_DEV void body_materialize_b(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, i64 first_slot, i64 nslots) {
+    __shared__ u32 s_warp[32];
+    __shared__ u64 s_base;
+    u32 err = 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    i64 end = first_slot + nslots;
+    if (end > (i64)t.capacity) end = (i64)t.capacity;
+    for (i64 b0 = first_slot + (i64)blockIdx.x * blockDim.x; b0 < end; b0 += (i64)gridDim.x * blockDim.x) {
+        const i64 s = b0 + threadIdx.x;
+        const u64* slot = t.slots + (u64)s * P::BSLOTW;
+        const u32 pres = s < end ? bucket_presence<P>(slot) : 0u;
+        const u32 cnt = (u32)__popc(pres);
+        u32 incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const u32 n = __shfl_up_sync(FULLMASK, incl, d);
+            if (lane >= d) incl += n;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const u32 w = lane < nwarps ? s_warp[lane] : 0u;
+            u32 wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const u32 n = __shfl_up_sync(FULLMASK, wi, d);
+                if (lane >= d) wi += n;
+            }
+            s_warp[lane] = wi - w;
+            if (lane == 31) s_base = wi ? atomicAdd(sc.out_count, (u64)wi) : 0ull;
+        }
+        __syncthreads();
+        i64 pos = (i64)(s_base + s_warp[warp] + incl - cnt);
+#pragma unroll 1
+        for (u32 j = 0; j < 8; j++) {
+            if (!((pres >> j) & 1u)) continue;
+            if (pos < out.capacity) {
+                u64 key[P::KWA];
+                bucket_join<P>(slot, j, key);
+                P::emit(key, slot + P::KW + j * P::NW, out, pos, err);
+            } else {
+                err |= PGPU_ERR_OUTPUT_FULL;
+            }
+            pos++;
+        }
+        __syncthreads();
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
+template <class P>
+PGPU_DEV void body_rehash_b(const TableArgs& from, const TableArgs& to, const Scratch& sc) {
+    u32 err = 0, nins = 0;
+    for (u64 s = (u64)blockIdx.x * blockDim.x + threadIdx.x; s < from.capacity; s += (u64)gridDim.x * blockDim.x) {
+        const u64* slot = from.slots + s * P::BSLOTW;
+        const u64 last = slot[P::KWA - 1];
+        if (!(last & KEY_MARK)) continue;
+        u64 bk[P::KWA];
+#pragma unroll
+        for (int i = 0; i < P::KW; i++) bk[i] = slot[i];
+        bk[P::KWA - 1] &= ~(KEY_MARK | P::BPMASK);
+        u64* d = table_upsert<P::KW, P::BSLOTW, true, P::BPMASK>(to, bk, hash_key<P::KW>(bk), true, nins);
+        if (!d) { err |= PGPU_ERR_TABLE_FULL; continue; }
+        d[P::KWA - 1] = last;  // buckets are distinct: plain stores (the presence byte travels with the header)
+#pragma unroll 1
+        for (int w = 0; w < 8 * P::NW; w++) d[P::KW + w] = slot[P::KW + w];
+    }
+    flush_inserts(to, nins);
+    if (err) atomicOr(sc.err, err);
+}
+
+// groups in the table = presence bits set; added to *sc.out_count
+template <class P>
+PGPU_DEV void body_count_groups(const TableArgs& t, const Scratch& sc) {
+    u32 n = 0;
+    for (u64 s = (u64)blockIdx.x * blockDim.x + threadIdx.x; s < t.capacity; s += (u64)gridDim.x * blockDim.x)
+        n += (u32)__popc(bucket_presence<P>(t.slots + s * P::BSLOTW));
+    n = __reduce_add_sync(FULLMASK, n);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(sc.out_count, (u64)n);
 }
 
 // Single-slot output of a global aggregation (AggregationOperator.getOutput, operator/AggregationOperator.java:164-186).

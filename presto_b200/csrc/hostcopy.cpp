@@ -19,8 +19,9 @@
 namespace pgpu {
 namespace {
 
-constexpr size_t kSegmentBytes = 256u << 10;  // unit of work sharing
-constexpr size_t kInlineBytes = 192u << 10;   // batches below this are copied by the caller alone
+constexpr size_t kSegmentBytes = 256u << 10;  // largest unit of work sharing
+constexpr size_t kMinSegmentBytes = 16u << 10;
+constexpr size_t kInlineBytes = 48u << 10;    // batches below this are copied by the caller alone
 
 inline void cpuRelax() {
 #if PGPU_HAVE_SSE2
@@ -195,11 +196,14 @@ void hostCopy(const std::vector<CopyTask>& tasks) {
     size_t total = 0;
     for (const CopyTask& t : tasks) total += t.bytes;
     if (total == 0) return;
+    // a 4096-row page (RecordPageSource's shape) is ~190 KB: cut small batches finer so that every worker gets a share
+    size_t seg = total / (size_t)(2 * hostCopyThreads());
+    seg = std::min(kSegmentBytes, std::max(kMinSegmentBytes, (seg + 4095) / 4096 * 4096));
     std::vector<Segment> segs;
-    segs.reserve(tasks.size() + total / kSegmentBytes + 1);
+    segs.reserve(tasks.size() + total / seg + 1);
     for (const CopyTask& t : tasks) {
-        for (size_t at = 0; at < t.bytes; at += kSegmentBytes) {
-            const size_t n = std::min(kSegmentBytes, t.bytes - at);
+        for (size_t at = 0; at < t.bytes; at += seg) {
+            const size_t n = std::min(seg, t.bytes - at);
             segs.push_back(Segment{(int32_t)t.kind, t.delta, (char*)t.dst + at, (const char*)t.src + at, n});
         }
     }

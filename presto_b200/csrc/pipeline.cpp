@@ -25,6 +25,7 @@
 #include "jit.h"
 #include "plan.h"
 #include "serde.h"
+#include "tableutil.h"
 #include "parquet.h"
 #include "parquet_host.h"
 #include "parquet_ingest.h"
@@ -77,7 +78,7 @@ thread_local std::string g_lastGlobalError;
 struct Variant {
     GenResult gen;
     cudaLibrary_t lib = nullptr;
-    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr;
+    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr;
     int blocksPerSM = 1;
     int stagedStages = 0;      // stages of the shared-memory ring (0 = staged variant unavailable)
     size_t stagedSmem = 0;
@@ -183,7 +184,11 @@ struct pgpu_pipeline {
     // table
     uint64_t* dSlots = nullptr;
     uint64_t capacity = 0;
-    int64_t groupsKnown = 0, rowsSinceKnown = 0;
+    // slotsKnown: table slots claimed at the last look (what the load factor is about); groupsKnown: groups in the table (what the
+    // output is sized by). The same number for one-key-per-slot tables; a bucketed table claims one slot per 8 neighbouring keys.
+    int64_t slotsKnown = 0, groupsKnown = 0, rowsSinceKnown = 0;
+    enum { TABLE_UNDECIDED = 0, TABLE_PER_KEY = 1, TABLE_BUCKETS = 2 };
+    int tableMode = TABLE_UNDECIDED;  // decided by the first page (key clustering probe) or PGPU_TUNE_BUCKETS; survives pgpu_reset
 
     // staging + output
     StageSlot slots[3];
@@ -273,7 +278,8 @@ std::string sigKey(const std::vector<ColSig>& s) {
 }
 
 pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant** out) {
-    std::string key = sigKey(sig);
+    const bool buckets = p->tableMode == pgpu_pipeline::TABLE_BUCKETS;
+    std::string key = sigKey(sig) + (buckets ? "B" : "");
     auto it = p->variants.find(key);
     if (it != p->variants.end()) {
         *out = &it->second;
@@ -281,7 +287,9 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
     }
     Variant v;
     try {
-        v.gen = generate(*p->plan, sig);
+        GenOptions opt;
+        opt.buckets = buckets;
+        v.gen = generate(*p->plan, sig, opt);
         JitResult jr = jitCompile(v.gen.source);
         if (jr.cacheHit) p->stats.jit_cache_hits++;
         else p->stats.jit_compiles++;
@@ -301,6 +309,7 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
             if (v.gen.mode == KernelMode::AGG_HASH) {
                 CU(cudaLibraryGetKernel(&v.kRehash, v.lib, "pgpu_k_rehash"));
                 CU(cudaLibraryGetKernel(&v.kReplay, v.lib, "pgpu_k_replay"));
+                if (v.gen.buckets) CU(cudaLibraryGetKernel(&v.kCount, v.lib, "pgpu_k_count"));
             }
             if (v.gen.staged) {
                 // ring depth from the opt-in shared memory of the device (227 KB on sm_100), at most 4 stages
@@ -399,10 +408,25 @@ pgpu_status allocTable(pgpu_pipeline* p, uint64_t cap, uint64_t** slotsOut) {
     return PGPU_OK;
 }
 
-pgpu_status refreshGroupCount(pgpu_pipeline* p) {
+// Look at the table's counters (synchronises): slots claimed, rows deferred. `exactGroups`: also learn the number of groups,
+// which a bucketed table only knows by counting presence bits (one pass over the bucket headers).
+pgpu_status refreshGroupCount(pgpu_pipeline* p, Variant* v = nullptr, bool exactGroups = false) {
+    const bool buckets = p->tableMode == pgpu_pipeline::TABLE_BUCKETS;
+    if (buckets && exactGroups && p->dSlots) {
+        if (!v || !v->kCount) return fail(p, PGPU_CUDA_ERROR, "internal: group count without a bucket variant");
+        CU(cudaMemsetAsync(p->dOutCount, 0, 8, p->stream));
+        TableArgs t = tableOf(p);
+        Scratch sc = scratchOf(p);
+        void* args[] = {&t, &sc};
+        int grid = (int)std::min<uint64_t>((p->capacity + kThreads - 1) / kThreads, (uint64_t)p->numSMs * 8);
+        pgpu_status st = launch(p, v->kCount, grid, kThreads, 0, args);
+        if (st) return st;
+        CU(cudaMemcpyAsync(&p->hostScalars[0], p->dOutCount, 8, cudaMemcpyDeviceToHost, p->stream));
+    }
     CU(cudaMemcpyAsync(&p->hostScalars[1], p->dCounters, 16, cudaMemcpyDeviceToHost, p->stream));
     CU(cudaStreamSynchronize(p->stream));
-    p->groupsKnown = (int64_t)p->hostScalars[1];
+    p->slotsKnown = (int64_t)p->hostScalars[1];
+    p->groupsKnown = !buckets ? p->slotsKnown : exactGroups ? (int64_t)p->hostScalars[0] : p->slotsKnown * 8;  // upper bound
     p->rowsSinceKnown = 0;
     return PGPU_OK;
 }
@@ -412,7 +436,7 @@ pgpu_status growTable(pgpu_pipeline* p, Variant* v, uint64_t newCap) {
     pgpu_status st = allocTable(p, newCap, &fresh);
     if (st) return st;
     if (p->dSlots) CU(cudaMemsetAsync(p->dCounters, 0, 16, p->stream));  // groups are re-counted, deferred rows cleared
-    if (p->dSlots && p->groupsKnown > 0) {
+    if (p->dSlots && p->slotsKnown > 0) {
         TableArgs from = tableOf(p);
         TableArgs to = from;
         to.slots = fresh;
@@ -447,6 +471,49 @@ struct DevPage {
     int64_t slack = 0;  // rows of the same arrays that follow this slice (offsets past the end stay readable)
 };
 
+pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant** out);
+
+// First page of a high-cardinality plan that qualifies for the bucketed table: look at how its keys arrive. When most key
+// changes stay inside a bucket of 8 neighbouring keys (l_orderkey: 7 of 8), 8 groups share one slot and one DRAM round trip;
+// keys that jump around (shuffled keys, hash-partitioned partial results) keep the one-key-per-slot table.
+// PGPU_TUNE_BUCKETS = 0 / 1 overrides the probe. *swapped = the bucket variant of the same page signature, if chosen.
+pgpu_status decideTableMode(pgpu_pipeline* p, Variant* v, const DevPage& pg, Variant** swapped) {
+    *swapped = nullptr;
+    const GenResult& g = v->gen;
+    bool buckets = false;
+    const char* force = getenv("PGPU_TUNE_BUCKETS");
+    if (!g.bucketsPossible) {
+        buckets = false;
+    } else if (force && *force) {
+        buckets = atoi(force) != 0;
+    } else if (g.bucketKeyChannel >= 0 && pg.rows >= 1024) {
+        const ColArg& ca = pg.cols[g.bucketKeyChannel];
+        const Type& t = p->plan->input[g.bucketKeyChannel];
+        if (ca.values && !ca.ids && !ca.dvalues && !t.isVarWidth() && (t.width() == 4 || t.width() == 8)) {
+            unsigned long long* dOut = (unsigned long long*)p->dState;  // 64 words of scratch the hash path does not use
+            CU(cudaMemsetAsync(dOut, 0, 16, p->stream));
+            CU(keyClustering(p->stream, ca.values, t.width(), std::min<int64_t>(pg.rows, 1 << 16), dOut));
+            CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 16, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaStreamSynchronize(p->stream));
+            CU(cudaMemsetAsync(dOut, 0, 16, p->stream));
+            p->stats.kernel_launches++;
+            const uint64_t changes = p->hostScalars[4], near = p->hostScalars[5];
+            buckets = changes > 0 && near * 2 >= changes;
+        }
+    }
+    p->tableMode = buckets ? pgpu_pipeline::TABLE_BUCKETS : pgpu_pipeline::TABLE_PER_KEY;
+    p->stats.table_bucketed = buckets ? 1 : 0;
+    if (!buckets) return PGPU_OK;
+    // same page signature, bucketed kernels; the slot layout changes with it (no table exists yet)
+    p->haveLayout = false;
+    std::vector<ColSig> sig;
+    for (auto& kv : p->variants)
+        if (&kv.second == v) {
+            for (size_t i = 0; i + 1 < kv.first.size(); i += 2) sig.push_back(ColSig{kv.first[i] - '0', kv.first[i + 1] == 'n'});
+        }
+    return getVariant(p, sig, swapped);
+}
+
 pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
     const GenResult& g = v->gen;
     // kernel parameter block: PageArgs<NC> = ColArg[NC] + rows
@@ -472,6 +539,12 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         void* args[] = {pa.data(), &sc};
         return launch(p, v->kPage, grid, kThreads, 0, args);
     }
+    if (g.mode == KernelMode::AGG_HASH && !p->dSlots && p->tableMode == pgpu_pipeline::TABLE_UNDECIDED) {
+        Variant* swapped = nullptr;
+        pgpu_status st = decideTableMode(p, v, pg, &swapped);
+        if (st) return st;
+        if (swapped) return launchPageKernel(p, swapped, pg);
+    }
     if (g.mode == KernelMode::AGG_HASH) {
         // Table sizing follows BigintGroupByHash (expectedSize / fill ratio, operator/BigintGroupByHash.java:78-101) and
         // grows on demand (:262-313). A chunk whose rows could push the table past its load-factor limit runs with a
@@ -480,6 +553,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         const uint64_t reserve = flushReserve(p, v);
         if (!p->dSlots) {
             uint64_t cap = (uint64_t)((double)p->plan->expectedGroups / 0.6) + 1024;
+            if (g.buckets) cap = (uint64_t)((double)p->plan->expectedGroups / 8.0 / 0.5) + 1024;  // 8 keys per slot when the clusters are dense
             cap = std::max<uint64_t>(cap, reserve * 4 + 4096);
             // key types that bound the number of groups (<= 1 M): size the table for the whole domain, once
             if (g.keyDomain > 0 && g.keyDomain <= (double)(1 << 20)) cap = std::max<uint64_t>(cap, (uint64_t)(g.keyDomain / 0.7) + reserve * 2 + 4096);
@@ -489,7 +563,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         const int64_t n = pg.rows;
         const uint64_t limit = (uint64_t)(0.75 * (double)p->capacity) - reserve;
         const bool bounded = g.keyDomain > 0 && (uint64_t)g.keyDomain <= limit;  // the table can hold every possible key
-        const bool risky = !bounded && (uint64_t)(p->groupsKnown + p->rowsSinceKnown + n) > limit;
+        const bool risky = !bounded && (uint64_t)(p->slotsKnown + p->rowsSinceKnown + n) > limit;
         if (risky) {
             pgpu_status st = ensureDev(p, p->failLog, (size_t)n * 8);
             if (st) return st;
@@ -546,12 +620,12 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         if (st) return st;
         p->rowsSinceKnown += n;
         if (!risky) return PGPU_OK;
-        st = refreshGroupCount(p);  // synchronises; hostScalars[2] = deferred rows
+        st = refreshGroupCount(p, v);  // synchronises; hostScalars[2] = deferred rows
         if (st) return st;
         uint64_t deferred = p->hostScalars[2];
         if (deferred == 0) return PGPU_OK;
         if (deferred > (uint64_t)n) return fail(p, PGPU_CUDA_ERROR, "internal: deferred-row log overflow");
-        uint64_t cap = std::max<uint64_t>(p->capacity * 2, (uint64_t)((double)(p->groupsKnown + (int64_t)deferred) / 0.6) + reserve * 4 + 4096);
+        uint64_t cap = std::max<uint64_t>(p->capacity * 2, (uint64_t)((double)(p->slotsKnown + (int64_t)deferred) / 0.6) + reserve * 4 + 4096);
         st = growTable(p, v, cap);  // rehash re-counts the groups and clears the deferred counter
         if (st) return st;
         TableArgs t2 = tableOf(p);  // limit = none: the grown table holds every deferred row even if all are new groups
@@ -935,7 +1009,7 @@ int64_t dictValueBytes(const Type& t, const HostCol& hc) {
 }
 
 // start of the dictionary's payload bytes inside dvalues
-int64_t dictByteBase(const HostCol& hc) { return hc.dEndOffsets || hc.dcount == 0 ? 0 : rdI32(hc.doffsets); }
+int64_t dictByteBase(const HostCol& hc) { return hc.dEndOffsets || hc.dcount == 0 || !hc.doffsets ? 0 : rdI32(hc.doffsets); }
 
 bool hostPageCoalescible(pgpu_pipeline* p, Variant* v, const std::vector<ColSig>& sig, const std::vector<HostCol>& hc) {
     const GenResult& g = v->gen;
@@ -1241,6 +1315,14 @@ pgpu_status addPageCommon(pgpu_pipeline* p, const pgpu_column* cols, int32_t nco
     return PGPU_OK;
 }
 
+// any compiled variant whose kernels match the table's slot format (emit / rehash / count kernels do not depend on the page signature)
+Variant* tableVariant(pgpu_pipeline* p) {
+    const bool buckets = p->tableMode == pgpu_pipeline::TABLE_BUCKETS;
+    for (auto& kv : p->variants)
+        if (kv.second.gen.buckets == buckets) return &kv.second;
+    return nullptr;
+}
+
 // PARTIAL step: once the row-count upper bound crosses the flush threshold, learn the real group count
 pgpu_status updatePartialFill(pgpu_pipeline* p) {
     const Plan& plan = *p->plan;
@@ -1248,7 +1330,7 @@ pgpu_status updatePartialFill(pgpu_pipeline* p) {
         p->groupsKnown + p->rowsSinceKnown + p->pend.rows >= plan.maxPartialGroups) {
         pgpu_status st = flushPending(p);  // rows still waiting in the staging slot count: aggregate them, then look
         if (st) return st;
-        if (p->dSlots) return refreshGroupCount(p);
+        if (p->dSlots) return refreshGroupCount(p, tableVariant(p), true);
     }
     return PGPU_OK;
 }
@@ -1262,13 +1344,11 @@ pgpu_status buildAggOutput(pgpu_pipeline* p) {
         if (st) return st;
     }
     // any compiled variant has the emit kernels (layout is signature independent)
-    Variant* v = nullptr;
-    if (p->variants.empty()) {
+    Variant* v = tableVariant(p);
+    if (!v) {
         std::vector<ColSig> sig(p->plan->input.size());
         pgpu_status st = getVariant(p, sig, &v);
         if (st) return st;
-    } else {
-        v = &p->variants.begin()->second;
     }
     CU(cudaMemsetAsync(p->dOutCount, 0, 8, p->stream));
     if (g.mode == KernelMode::AGG_GLOBAL) {
@@ -1284,8 +1364,9 @@ pgpu_status buildAggOutput(pgpu_pipeline* p) {
         if (!p->dSlots) {
             p->outRowsTotal = 0;
         } else {
-            pgpu_status st = refreshGroupCount(p);
+            pgpu_status st = refreshGroupCount(p, v, true);
             if (st) return st;
+            CU(cudaMemsetAsync(p->dOutCount, 0, 8, p->stream));  // the group count of a bucketed table went through it
             st = ensureOutBuffers(p, p->groupsKnown);
             if (st) return st;
             std::vector<unsigned char> oa = outArgsBlock(p);
@@ -1316,6 +1397,7 @@ void resetAggState(pgpu_pipeline* p) {
     if (p->dErr) cudaMemsetAsync(p->dErr, 0, 4, p->stream);
     if (p->dTicket) cudaMemsetAsync(p->dTicket, 0, 4, p->stream);
     p->groupsKnown = 0;
+    p->slotsKnown = 0;
     p->rowsSinceKnown = 0;
 }
 
@@ -1396,6 +1478,23 @@ pgpu_status pgpu_pipeline_create(const uint8_t* plan, size_t plan_len, int32_t d
         g_lastGlobalError = p->err;
         pgpu_pipeline_destroy(p.release());
         return st;
+    }
+    if (!v->gen.bucketsPossible) {
+        p->tableMode = pgpu_pipeline::TABLE_PER_KEY;
+    } else if (const char* force = getenv("PGPU_TUNE_BUCKETS")) {
+        if (*force && atoi(force) != 0) {  // bucketed table from the start (also what build() uses to warm the kernel cache)
+            p->tableMode = pgpu_pipeline::TABLE_BUCKETS;
+            p->stats.table_bucketed = 1;
+            p->haveLayout = false;
+            st = getVariant(pp, sig, &v);
+            if (st) {
+                g_lastGlobalError = p->err;
+                pgpu_pipeline_destroy(p.release());
+                return st;
+            }
+        } else if (*force) {
+            p->tableMode = pgpu_pipeline::TABLE_PER_KEY;
+        }
     }
     if (p->layout.NW > 60) {
         g_lastGlobalError = "not supported on the GPU path: more than 60 accumulator words";
@@ -2110,9 +2209,10 @@ pgpu_status pgpu_reset(pgpu_pipeline* p) {
     }
     p->finishing = p->finished = p->sawInput = p->outputReady = false;
     p->outRowsTotal = p->outRowsServed = 0;
-    int64_t cap = p->stats.table_capacity;
+    int64_t cap = p->stats.table_capacity, bucketed = p->stats.table_bucketed;
     p->stats = pgpu_stats{};
     p->stats.table_capacity = cap;
+    p->stats.table_bucketed = bucketed;
     p->err.clear();
     return PGPU_OK;
 }

@@ -1,0 +1,13 @@
+// tableutil.h — small ahead-of-time kernels around the HBM hash table that do not depend on the plan.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace pgpu {
+
+// Clustering probe for the bucketed table (device/pgpu_device.cuh "bucketed slots"): over the first n (<= 65536) keys of an
+// integer key column, out[0] = positions whose key differs from its predecessor's, out[1] = those of them whose predecessor
+// lies in the same bucket of 8 (key >> 3 equal). `width` = 4 or 8 bytes per key. out must be zeroed by the caller.
+cudaError_t keyClustering(cudaStream_t stream, const void* keys, int width, int64_t n, unsigned long long* out);
+
+}  // namespace pgpu

@@ -16,14 +16,16 @@ from presto_b200.relational import compare, constant, field
 from presto_b200.spi import BIGINT, DOUBLE, INTEGER, IntArrayBlock, LongArrayBlock, Page
 from util import assert_rows_equal_ignore_order, rows_of, run_oracle
 
-VARIANTS = [(0, 0), (1, 0), (0, 4), (1, 4), (1, 6)]       # (PGPU_TUNE_RUNS, PGPU_TUNE_LOCB)
+VARIANTS = [(0, 0), (1, 0), (0, 4), (1, 4), (1, 6)]       # (PGPU_TUNE_RUNS, PGPU_TUNE_LOCB), one key per slot (PGPU_TUNE_BUCKETS=0)
+BUCKETS = "B"                                              # in place of the LOCB value: the bucketed table (PGPU_TUNE_BUCKETS=1)
 NO_DIRECTORY = (1 << 20) + 1                               # expectedGroups above 2^20: no shared-memory directory, HBM table only
 
 
 @contextlib.contextmanager
 def variant(runs, locb):
-    old = {k: os.environ.get(k) for k in ("PGPU_TUNE_RUNS", "PGPU_TUNE_LOCB")}
-    os.environ["PGPU_TUNE_RUNS"], os.environ["PGPU_TUNE_LOCB"] = str(runs), str(locb)
+    old = {k: os.environ.get(k) for k in ("PGPU_TUNE_RUNS", "PGPU_TUNE_LOCB", "PGPU_TUNE_BUCKETS")}
+    os.environ["PGPU_TUNE_RUNS"], os.environ["PGPU_TUNE_LOCB"] = str(runs), "0" if locb == BUCKETS else str(locb)
+    os.environ["PGPU_TUNE_BUCKETS"] = "1" if locb == BUCKETS else "0"
     try:
         yield
     finally:
@@ -49,8 +51,12 @@ def run_variant(plan, pages, runs, locb, device=0):
             op.close()
 
 
-def check_source(src, runs, locb):
+def check_source(src, runs, locb, bucketable=True):
     assert ("RUNS = true" in src) == bool(runs)
+    if locb == BUCKETS:
+        assert ("BUCKETS = true" in src) == bucketable
+        return
+    assert "BUCKETS = false" in src
     assert ("#define PGPU_LOCB %d\n" % locb in src) == (locb > 0)
 
 
@@ -97,14 +103,91 @@ def expected_of(name):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("runs,locb", VARIANTS)
+@pytest.mark.parametrize("runs,locb", VARIANTS + [(1, BUCKETS), (0, BUCKETS)])
 @pytest.mark.parametrize("name", list(CASES))
 def test_variant_equals_oracle(name, runs, locb):
     plan, pages, nkeys, exp = expected_of(name)
-    act, _, src = run_variant(plan, pages, runs, locb)
-    check_source(src, runs, locb)
+    act, st, src = run_variant(plan, pages, runs, locb)
+    check_source(src, runs, locb, bucketable=name != "filtered_two_keys")   # two key fields: no bucket of neighbouring keys
+    assert st.table_bucketed == (1 if locb == BUCKETS and name != "filtered_two_keys" else 0)
     assert len(exp) > 40_000
     assert_rows_equal_ignore_order(act, exp, nkeys=nkeys, rtol=0.0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,bucketed", [("clustered", 1), ("shuffled", 0), ("filtered_int_key", 0)])
+def test_table_format_follows_the_key_clustering(name, bucketed):
+    """no knob set: the first page's keys decide (l_orderkey runs -> buckets of 8 neighbouring keys; random keys -> one key per slot)"""
+    plan, pages, nkeys, exp = expected_of(name)
+    old = os.environ.pop("PGPU_TUNE_BUCKETS", None)
+    try:
+        op = GpuPipelineOperator(plan, 0)
+        try:
+            act = rows_of(toPages(op, pages))
+            assert op.stats().table_bucketed == bucketed
+            op.reset()                                            # the choice survives a reset; so does the result
+            again = rows_of(toPages(op, pages))
+            assert op.stats().table_bucketed == bucketed
+        finally:
+            op.close()
+    finally:
+        if old is not None:
+            os.environ["PGPU_TUNE_BUCKETS"] = old
+    assert_rows_equal_ignore_order(act, exp, nkeys=nkeys, rtol=0.0)
+    assert_rows_equal_ignore_order(again, exp, nkeys=nkeys, rtol=0.0)
+
+
+def bucket_edge_pages():
+    """keys around the bucket boundaries of a signed BIGINT key: negative keys, INT64 extremes, NULL keys, all 8 keys of a
+    bucket, runs that cross pages; integer-valued quantities with NULLs (a group whose quantities are all NULL still exists)"""
+    rng = np.random.default_rng(21)
+    base = np.array([-(1 << 63), -(1 << 63) + 7, -17, -16, -9, -8, -1, 0, 1, 7, 8, 9, 15, 16, (1 << 63) - 8, (1 << 63) - 1, 1 << 40, (1 << 40) + 3], dtype=np.int64)
+    pages = []
+    for n in (5000, 1, 2777, 4096):
+        k = np.repeat(base[rng.integers(0, len(base), n)], rng.integers(1, 5, n))[:n]
+        dense = (np.arange(n, dtype=np.int64) // 3) - 700          # clustered part: every key of many buckets, runs of 3
+        k = np.where(rng.random(n) < 0.5, k, dense)
+        knull = (rng.random(n) < 0.03).astype(np.uint8)
+        q = rng.integers(1, 51, n).astype(np.float64)
+        qnull = (rng.random(n) < 0.3).astype(np.uint8)
+        pages.append(Page(LongArrayBlock(BIGINT, k, knull), LongArrayBlock(DOUBLE, q, qnull)))
+    return pages
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("step", ["single", "partial_final"])
+def test_bucketed_table_edges(step):
+    pages = bucket_edge_pages()
+    aggs = [Aggregation("sum", DOUBLE, 1, DOUBLE), Aggregation("count", BIGINT), Aggregation("max", DOUBLE, 1, DOUBLE)]
+    single = plan_text([BIGINT, DOUBLE], step="single", groupByChannels=[0], aggregations=aggs, expectedGroups=NO_DIRECTORY)
+    exp = run_oracle(single, pages)
+    with variant(1, BUCKETS):
+        if step == "single":
+            op = GpuPipelineOperator(single, 0)
+            try:
+                act = rows_of(toPages(op, pages))
+                assert op.stats().table_bucketed == 1
+            finally:
+                op.close()
+        else:
+            partial = plan_text([BIGINT, DOUBLE], step="partial", groupByChannels=[0], aggregations=aggs, expectedGroups=NO_DIRECTORY,
+                                maxPartialGroups=3000)
+            pop = GpuPipelineOperator(partial, 0)
+            try:
+                mid = toPages(pop, pages)
+                assert pop.stats().table_bucketed == 1 and len(mid) >= 2
+            finally:
+                pop.close()
+            final = plan_text([BIGINT, BIGINT, DOUBLE, BIGINT, DOUBLE], step="final", groupByChannels=[0],
+                              aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE), Aggregation("count", BIGINT, 3, BIGINT), Aggregation("max", DOUBLE, 4, DOUBLE)],
+                              expectedGroups=NO_DIRECTORY)
+            fop = GpuPipelineOperator(final, 0)
+            try:
+                act = rows_of(toPages(fop, mid))
+                assert fop.stats().table_bucketed == 1
+            finally:
+                fop.close()
+    assert_rows_equal_ignore_order(act, exp, nkeys=1, rtol=0.0)
 
 
 def growth_pages():
@@ -117,7 +200,7 @@ def growth_pages():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("runs,locb", [(0, 0), (1, 0), (1, 4), (0, 4)])
+@pytest.mark.parametrize("runs,locb", [(0, 0), (1, 0), (1, 4), (0, 4), (1, BUCKETS)])
 def test_variant_table_growth(runs, locb):
     """1.7 M distinct keys into a table sized for 1.05 M: rows that need a slot past the load-factor limit are deferred,
     the table is grown and the rows are replayed (whole runs in the run-compaction variant)"""
@@ -150,9 +233,9 @@ def prewarm():
         run_variant(tpch.highcard_plan(NO_DIRECTORY), pages, runs, locb, device=-1)
 
 
-@pytest.mark.parametrize("runs,locb", VARIANTS)
+@pytest.mark.parametrize("runs,locb", VARIANTS + [(1, BUCKETS), (0, BUCKETS)])
 def test_variants_compile_without_gpu(runs, locb):
     for name in ("clustered", "filtered_int_key", "filtered_two_keys"):
         plan, pages, _ = CASES[name]()
         _, _, src = run_variant(plan, pages[:1], runs, locb, device=-1)
-        check_source(src, runs, locb)
+        check_source(src, runs, locb, bucketable=name != "filtered_two_keys")

@@ -84,14 +84,14 @@ def test_q6_small_pages():
 
 
 def test_pages_larger_than_a_staging_slot(monkeypatch):
-    monkeypatch.setenv("PGPU_STAGE_MB", "1")        # slots of ~22 k Q1 rows: every page below spans several
-    total = 400_003
-    pages = cut(tpch.q1_page, total, [150_000, 1, 99_999, 150_003])
+    monkeypatch.setenv("PGPU_STAGE_MB", "1")        # the smallest slots: one staged tile per SM (284 160 Q1 rows)
+    total = 700_003
+    pages = cut(tpch.q1_page, total, [350_000, 1, 99_999, 250_003])
     plan = tpch.q1_plan()
     act, st = run_gpu_stats(plan, pages)
     assert_rows_equal_ignore_order(act, exact_q1(pages), nkeys=2)
     assert st.super_pages >= 3
-    hc = cut(tpch.highcard_page, total, [150_000, 1, 99_999, 150_003])
+    hc = cut(tpch.highcard_page, total, [350_000, 1, 99_999, 250_003])
     hplan = tpch.highcard_plan(expectedGroups=1000)  # grows while super-pages are in flight
     assert_rows_equal_ignore_order(run_gpu_stats(hplan, hc)[0], run_oracle(hplan, hc), nkeys=1)
 

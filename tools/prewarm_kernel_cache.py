@@ -69,7 +69,8 @@ def patch():
 def bench_plans():
     rows = 600_037_902
     ops = [O.GpuPipelineOperator(p, -1) for p in (tpch.q1_plan(), tpch.q1_plan("partial"), tpch.q6_plan(), tpch.q6_plan("partial"),
-                                                  tpch.highcard_plan(rows // 4), tpch.highcard_plan(rows // 4, "partial"))]
+                                                  tpch.highcard_plan(rows // 4), tpch.highcard_plan(rows // 4, "partial"),
+                                                  tpch.highcard_plan(16_000_000 // 4), tpch.highcard_plan(64_000_000 // 4))]
     ops[0].compileSignature([1, 1, 1, 0, 1, 1, 0], [False] * 7)
     ops[1].compileSignature([1, 1, 1, 0, 1, 1, 0], [False] * 7)
     for op in ops:
@@ -78,7 +79,7 @@ def bench_plans():
 
 if __name__ == "__main__":
     before = len(os.listdir(os.path.join(ROOT, "presto_b200", "_kernel_cache"))) if os.path.isdir(os.path.join(ROOT, "presto_b200", "_kernel_cache")) else 0
-    for spec in [""] + sys.argv[1:]:
+    for spec in ["", "PGPU_TUNE_BUCKETS=1"] + sys.argv[1:]:
         env = dict(kv.split("=") for kv in spec.split(",") if kv)
         os.environ.update(env)
         bench_plans()
@@ -86,7 +87,9 @@ if __name__ == "__main__":
             os.environ.pop(k)
     import pytest
     patch()
-    pytest.main([os.path.join(ROOT, "tests"), "-m", "gpu", "-q", "--timeout", "120", "-p", "no:cacheprovider", "--no-header", "-x" if False else "-q",
-                 "--tb=no"])
+    # the patch has to reach xdist workers too: they import this module's patch() through conftest's PGPU_PREWARM hook
+    os.environ["PGPU_PREWARM"] = "1"
+    pytest.main([os.path.join(ROOT, "tests"), "-m", "gpu", "-q", "--timeout", "300", "-p", "no:cacheprovider", "--no-header", "--tb=no",
+                 "-n", str(min(8, os.cpu_count() or 1))])
     after = len(os.listdir(os.path.join(ROOT, "presto_b200", "_kernel_cache")))
     print("kernel cache: %d -> %d files" % (before, after))
