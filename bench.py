@@ -567,25 +567,42 @@ def verify_prefix(wl, op, dp, host, rows, cores):
 
 
 # ------------------------------------------------------------------------------------------------ GPU legs
-def make_exchange(args, device, world, rank, small, leg):
+_COMM = {}
+
+
+def get_comm(device, world, rank):
+    """the rank's pgpu_comm (one per process; every pipeline pair of the run exchanges through it)"""
     from presto_b200 import exchange as X
     if world == 1:
         return None
-    if not small:
-        return X.DeviceRepartition(device, world, rank, transport=args.exchange)
+    if "c" not in _COMM:
+        import torch.distributed as td
+        token = [("%s_%d_%d" % (os.environ.get("MASTER_PORT", "0"), os.getpid(), time.time_ns())) if rank == 0 else None]
+        td.broadcast_object_list(token, src=0)      # a segment name no earlier (crashed) job can have left behind
+        _COMM["c"] = X.Comm(world, rank, device, "pgpu_bench_" + token[0])
+    return _COMM["c"]
+
+
+def make_exchange(args, device, world, rank, small, leg):
+    """--exchange peer (default): the native exchange (pgpu_exchange_partial); nccl: the Python NCCL baselines"""
+    from presto_b200 import exchange as X
+    if world == 1:
+        return None
     if args.exchange == "peer":
-        return X.PeerGather(device, world, rank, "pgpu_mail_%s_%s" % (os.environ.get("MASTER_PORT", "0"), leg))
-    return None
+        return get_comm(device, world, rank)
+    return None if small else X.DeviceRepartition(device, world, rank, transport="nccl")
 
 
 def exchange_and_final(op, final, small, repart, tdev, state):
     """N > 1: the partial -> final exchange of one step (op has finished its shard); leaves the result drained.
-    `repart` is the exchange object: PeerGather / None (small results), DeviceRepartition (large group counts)."""
+    `repart` is the exchange object: Comm (native: gather or repartition, chosen by the library from the plan), None (NCCL
+    all-gather baseline, small results) or DeviceRepartition (NCCL all-to-all baseline)."""
     from presto_b200 import exchange as X
     final.reset()
-    if small and repart is not None:
-        repart.run(op, final)                       # FINAL kernel reads every rank's partial rows over NVLink
-        state["result_rows"] = drain_output(final, to_host=True)
+    if isinstance(repart, X.Comm):
+        repart.exchange(op, final)                  # device-side exchange; FINAL is left finishing
+        state["result_rows"] = drain_output(final, to_host=small)
+        state["exchange_bytes"] = repart.sent_bytes
     elif small:
         frame = X.pack_output(op)                                       # waits for the shard's kernels, drains the partial page
         frames = X.all_gather_frames(frame, device=tdev)                # one NCCL all-gather of a 32 KB frame per rank
@@ -673,7 +690,7 @@ def run_device_steps(args, wl, device, dist, steps, warmup):
     info = dict(dev_ms=dev_ms, wall_s=wall, launches=nl, clocks=clocks, kern_ms=kern_ms, kern_launches=kern_launches,
                 kern_steps=ksteps, result_rows=state["result_rows"], table_capacity=op.stats().table_capacity,
                 exchange_bytes=state["exchange_bytes"])
-    if repart is not None:
+    if repart is not None and not hasattr(repart, "exchange"):
         repart.close()
     if final is not None:
         final.close()
@@ -805,7 +822,8 @@ def run_e2e(args, wl, device, dp, dist, steps, full):
                h2d_ceiling_gbs=float(t.item()))
     rec["frac_of_h2d_ceiling"] = rec["gb_per_s"] / rec["h2d_ceiling_gbs"]
     op.close()
-    repart.close() if repart is not None else None
+    if repart is not None and not hasattr(repart, "exchange"):
+        repart.close()
     final.close()
     return rec, host
 
@@ -861,7 +879,7 @@ def run_workload(args, name, device, dist, headline):
            "clocks": info["clocks"], "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"]}
     if world > 1:
         small = name in ("q1", "q1dict", "q6")
-        rec["exchange"] = {"shape": ("gather: every rank's FINAL kernel reads all partial pages over NVLink (CUDA IPC peer memory, shared-memory mailbox)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if small else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),
+        rec["exchange"] = {"shape": ("gather: push kernel stores the partial rows into every rank's inbox over NVLink, FINAL gather kernel merges them; no host round trip (pgpu_exchange_partial)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if small else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory, pgpu_exchange_partial)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),
                            "bytes_sent_per_rank_per_step": info["exchange_bytes"]}
     host = None
     if not args.no_e2e:
@@ -966,6 +984,8 @@ def main():
         if configs:
             line["configs"] = configs
         print(json.dumps(line))
+    if "c" in _COMM:
+        _COMM.pop("c").close()
     if world > 1:
         import torch.distributed as td
         td.destroy_process_group()

@@ -214,9 +214,8 @@ void* pgpu_stream(const pgpu_pipeline* p);
 
 /* Partial -> final exchange (multi-GPU) -----------------------------------------------------------
  * Mirrors PartitionedOutputOperator (main/operator/PartitionedOutputOperator.java:56-133) between a
- * Step.PARTIAL and a Step.FINAL HashAggregationOperator. The collectives themselves (NCCL all-gather /
- * all-to-all) are issued by the host runtime on the device buffers these calls expose
- * (presto_b200/exchange.py; DESIGN.md "Multi-GPU"). */
+ * Step.PARTIAL and a Step.FINAL HashAggregationOperator: pgpu_comm_init / pgpu_exchange_partial below run the whole exchange
+ * (DESIGN.md "Multi-GPU"); the building blocks they use are exported too. */
 /* Hash-partition the complete output of a finishing PARTIAL-step pipeline into `nparts` (<= 64) contiguous
  * row ranges, device resident. After the call out_cols describe ONE device page sorted by partition and
  * partition i occupies rows [part_row_offsets[i], part_row_offsets[i] + part_row_counts[i]) of every column (host arrays of
@@ -232,6 +231,32 @@ pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_
                                          int32_t* ncols, int64_t* part_row_offsets, int64_t* part_row_counts);
 /* The same partition function for ONE row on the host (kinds: 0 = int64, 1 = int32, 2 = double bits). */
 int32_t pgpu_partition_of(const int64_t* key_bits, const uint8_t* is_null, const int32_t* kinds, int32_t nkeys, int32_t nparts);
+
+/* The exchange itself, for one-process-per-GPU deployments on one box. A communicator is the rank's membership of a job:
+ * ranks rendezvous through the POSIX shared-memory segment `name` (unique per job; created by rank 0, unlinked once everybody
+ * has joined) and map each other's HBM through CUDA IPC over NVLink / NVSwitch. No collective library is involved.
+ * pgpu_comm_init blocks until all `nranks` ranks have called it. device < 0 joins the rendezvous only (CPU tests). */
+typedef struct pgpu_comm pgpu_comm;
+pgpu_status pgpu_comm_init(int32_t nranks, int32_t rank, int32_t device, const char* name, pgpu_comm** out);
+void pgpu_comm_destroy(pgpu_comm* c);
+const char* pgpu_comm_last_error(const pgpu_comm* c);
+/* All ranks have arrived (host-side, through the segment). */
+pgpu_status pgpu_comm_barrier(pgpu_comm* c);
+/* PartitionedOutputOperator -> exchange -> HashAggregationOperator(Step.FINAL).addInput for one step, called by every rank:
+ * `partial` is a PARTIAL (or INTERMEDIATE) step pipeline that has received pgpu_finish; `final_pipeline` is a FINAL-step
+ * pipeline in its just-created / reset state whose input channels are the partial plan's output channels. On return the
+ * partial pipeline is finished and the FINAL pipeline is finishing: drain it with pgpu_get_output*.
+ * The shape is chosen from the partial plan alone (so that every rank takes the same one):
+ *   gather — global aggregations and plans whose group count fits an inbox slot (<= 4096 rows; Q1, Q6): every rank's partial
+ *            rows are pushed into every rank's inbox by a kernel and merged by the FINAL plan's gather kernel, with no host
+ *            round trip; every rank ends with the complete result. More groups than a slot holds fail with
+ *            PGPU_INSUFFICIENT_RESOURCES at pgpu_get_output (raise expected-groups to get the repartition shape).
+ *   repartition — the partial rows are hash-partitioned with the reference's partition function (see
+ *            pgpu_partition_output_device); each rank's FINAL page kernel reads its partition of every peer's rows straight
+ *            out of that peer's HBM. The result stays partitioned by key.
+ * *rows_received = rows this rank's FINAL step consumed (-1: known on the device only, gather shape); *bytes_sent = bytes that
+ * crossed NVLink on this rank's behalf. Either may be NULL. */
+pgpu_status pgpu_exchange_partial(pgpu_comm* c, pgpu_pipeline* partial, pgpu_pipeline* final_pipeline, int64_t* rows_received, int64_t* bytes_sent);
 
 /* Peer access over NVLink / NVSwitch for one-process-per-GPU deployments (cudaIpc*). The owner exports the allocation
  * that contains dev_ptr (`handle`, PGPU_IPC_HANDLE_BYTES bytes, plus dev_ptr's byte offset inside it); a peer process maps it

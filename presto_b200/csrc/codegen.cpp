@@ -1259,7 +1259,9 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     if (runs) res.smemBytes = runsBytes;
     // bucketed table: one integer key (so that "the 3 low bits" means neighbouring keys), two spare bytes in the last key word
     // (presence byte + occupied mark), run compaction available (the bucket path is built on it, whatever the step)
-    bool bucketsOk = highCard && fields.size() == 1 && runsBytes <= 48 * 1024 && NW > 0 && keyLen <= KW * 8 - 2 && fields[0].byteOffset < 7;
+    // (the staging bound uses NW, not this signature's NH: whether a plan is bucketed must not depend on which pages carry nulls)
+    const int runsBytesAnySig = 8 * ((KW + NWA) * 128 * 8 + 256);
+    bool bucketsOk = highCard && fields.size() == 1 && runsBytesAnySig <= 64 * 1024 && NW > 0 && keyLen <= KW * 8 - 2 && fields[0].byteOffset < 7;
     if (bucketsOk) {
         const TypeKind k0 = fields[0].type.kind;
         bucketsOk = k0 == TypeKind::BIGINT || k0 == TypeKind::INTEGER || k0 == TypeKind::DATE || (k0 == TypeKind::DECIMAL && fields[0].type.isShortDecimal());
@@ -1594,8 +1596,12 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     if (res.mode == KernelMode::AGG_GLOBAL) {
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, Scratch sc) { body_agg_global<P>(a, sc); }\n";
         src << "extern \"C\" __global__ void pgpu_k_emit(Scratch sc, OutArgs<P::NO> out) { body_emit_global<P>(sc, out); }\n";
+        if (finalStep)  // gather exchange: FINAL over the partial pages in this GPU's inbox
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_gather(const PageArgs<P::NC>* pages, GatherArgs g, Scratch sc) { body_gather_global<P>(pages, g, sc); }\n";
     } else {
         src << "extern \"C\" __global__ void __launch_bounds__(256, " << (getenv("PGPU_TUNE_MINBLOCKS") ? atoi(getenv("PGPU_TUNE_MINBLOCKS")) : (res.useDir ? 2 : 3)) << ") pgpu_k_page(PageArgs<P::NC> a, TableArgs t, Scratch sc) { body_agg_hash<P>(a, t, sc); }\n";
+        if (finalStep)
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_gather(const PageArgs<P::NC>* pages, GatherArgs g, TableArgs t, Scratch sc) { body_gather_hash<P>(pages, g, t, sc); }\n";
         if (res.staged)
             src << "extern \"C\" __global__ void __launch_bounds__(512, 1) pgpu_k_page_staged(PageArgs<P::NC> a, TableArgs t, Scratch sc, int nstages) { body_agg_hash_staged<P>(a, t, sc, nstages); }\n";
         if (res.buckets) {

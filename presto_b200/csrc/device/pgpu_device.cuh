@@ -1227,7 +1227,8 @@ struct HashCtx {
             }
         }
         // leaders: the first lane of each stretch of lanes that hold runs of the same bucket
-        bool same = a.act && lane > 0 && (__shfl_up_sync(FULLMASK, (int)a.act, 1) != 0);
+        const bool pact = __shfl_up_sync(FULLMASK, (int)a.act, 1) != 0;  // every lane takes part in the shuffles
+        bool same = a.act && lane > 0 && pact;
 #pragma unroll
         for (int w = 0; w < KW; w++) same &= (shfl_u64(a.bk[w], (lane + 31) & 31) == a.bk[w]);
         const bool head = a.act && !same;
@@ -1795,6 +1796,80 @@ PGPU_DEV void body_count_groups(const TableArgs& t, const Scratch& sc) {
         n += (u32)__popc(bucket_presence<P>(t.slots + s * P::BSLOTW));
     n = __reduce_add_sync(FULLMASK, n);
     if ((threadIdx.x & 31) == 0 && n) atomicAdd(sc.out_count, (u64)n);
+}
+
+// ---- gather exchange (small results): FINAL over the partial pages the peers pushed into this GPU's inbox ------------------------
+// Stands in for ExchangeOperator -> HashAggregationOperator(Step.FINAL).addInput over every upstream task's partial page
+// (main/operator/HashAggregationOperator.java:380-412 with Step.FINAL: addIntermediate = deserialize + combine). The host is out
+// of the loop: every rank's push kernel (csrc/exchange.cu) stores its partial rows and then a header {sequence, rows, error bits}
+// into the inbox slot it owns on every GPU (peer memory over NVLink, st.release.sys); this kernel — one block — waits for the
+// header of each slot in turn and runs the plan's page kernel body over the slot's rows, which lie in LOCAL HBM.
+PGPU_DEV u64 ld_acquire_sys_u64(const u64* p) {
+    u64 v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+PGPU_DEV u64 globaltimer_ns() {
+    u64 t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define PGPU_ERR_PEER_TIMEOUT 128u  // a peer's partial page did not arrive (the peer failed)
+struct GatherArgs {
+    const u64* hdr;        // header of slot 0: word 0 sequence, word 1 rows, word 2 sender's error bits
+    int npages;
+    int hdr_stride_words;  // 64-bit words from one slot's header to the next
+    u64 seq;
+    u64 timeout_ns;
+};
+// thread 0 waits for slot i's header; returns the slot's row count to every thread
+PGPU_DEV i64 gather_wait(const GatherArgs& g, int i, const Scratch& sc) {
+    __shared__ i64 s_rows;
+    if (threadIdx.x == 0) {
+        const u64* h = g.hdr + (size_t)i * (size_t)g.hdr_stride_words;
+        const u64 t0 = globaltimer_ns();
+        i64 rows = 0;
+        u32 err = 0;
+        for (;;) {
+            if (ld_acquire_sys_u64(h) == g.seq) {
+                rows = (i64)h[1];
+                err = (u32)h[2];
+                break;
+            }
+            if (globaltimer_ns() - t0 > g.timeout_ns) { err = PGPU_ERR_PEER_TIMEOUT; break; }
+            __nanosleep(200);
+        }
+        if (err) atomicOr(sc.err, err);
+        s_rows = err ? 0 : rows;
+    }
+    __syncthreads();
+    const i64 r = s_rows;
+    __syncthreads();
+    return r;
+}
+template <class P>
+PGPU_DEV void body_gather_hash(const PageArgs<P::NC>* pages, const GatherArgs& g, const TableArgs& t, const Scratch& sc) {
+    for (int i = 0; i < g.npages; i++) {
+        const i64 rows = gather_wait(g, i, sc);
+        if (rows > 0) {
+            PageArgs<P::NC> a = pages[i];
+            a.rows = rows;
+            body_agg_hash<P>(a, t, sc);
+        }
+        __syncthreads();
+    }
+}
+template <class P>
+PGPU_DEV void body_gather_global(const PageArgs<P::NC>* pages, const GatherArgs& g, const Scratch& sc) {
+    for (int i = 0; i < g.npages; i++) {
+        const i64 rows = gather_wait(g, i, sc);
+        if (rows > 0) {
+            PageArgs<P::NC> a = pages[i];
+            a.rows = rows;
+            body_agg_global<P>(a, sc);
+        }
+        __syncthreads();
+    }
 }
 
 // Single-slot output of a global aggregation (AggregationOperator.getOutput, operator/AggregationOperator.java:164-186).

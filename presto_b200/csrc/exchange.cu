@@ -81,6 +81,36 @@ struct B32 {
     uint64_t a, b, c, d;
 };
 
+__global__ void __launch_bounds__(256) k_push_partial(PushArgs a) {
+    char* slot = a.slot[blockIdx.x];
+    unsigned long long n = *a.count;
+    unsigned int err = *a.err;
+    if (n > (unsigned long long)a.capRows) {  // more groups than a slot holds: not a "small result" (the caller repartitions instead)
+        err |= 16u;                           // PGPU_ERR_OUTPUT_FULL
+        n = 0;
+    }
+    for (int c = 0; c < a.ncols; c++) {
+        const PushCol& pc = a.c[c];
+        // arrays are 256-byte aligned at both ends and padded: whole 16-byte words
+        const size_t vw = ((size_t)n * pc.stride + 15) / 16, nw = ((size_t)n + 15) / 16;
+        const uint4* sv = (const uint4*)pc.values;
+        uint4* dv = (uint4*)(slot + pc.dstV);
+        for (size_t i = threadIdx.x; i < vw; i += blockDim.x) dv[i] = sv[i];
+        const uint4* sn = (const uint4*)pc.nulls;
+        uint4* dn = (uint4*)(slot + pc.dstN);
+        for (size_t i = threadIdx.x; i < nw; i += blockDim.x) dn[i] = sn[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long* h = (unsigned long long*)slot;
+        h[1] = n;
+        h[2] = err;
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(h), "l"(a.seq) : "memory");
+    }
+}
+
 int gridFor(int numSMs, int64_t rows) {
     int64_t g = (rows + 255) / 256;
     if (g < 1) g = 1;
@@ -111,6 +141,11 @@ cudaError_t partitionScatter(cudaStream_t stream, int numSMs, int64_t rows, cons
         case 32: k_partition_scatter<B32><<<g, 256, 0, stream>>>(rows, dst, (const B32*)in, (B32*)out); break;
         default: return cudaErrorInvalidValue;
     }
+    return cudaGetLastError();
+}
+
+cudaError_t pushPartial(cudaStream_t stream, const PushArgs& args) {
+    k_push_partial<<<args.nranks, 256, 0, stream>>>(args);
     return cudaGetLastError();
 }
 

@@ -34,6 +34,30 @@ cudaError_t partitionAssign(cudaStream_t stream, int numSMs, int nparts, int64_t
 // pass 3 (per column): out[dst[row]] = in[row], element width 1/4/8/16/24/32 bytes
 cudaError_t partitionScatter(cudaStream_t stream, int numSMs, int64_t rows, const int64_t* dst, const void* in, void* out, int width);
 
+// ---- gather exchange (small results): push this rank's partial page into its inbox slot on every GPU -----------------------
+// Stands in for PartitionedOutputOperator -> OutputBuffer -> ExchangeClient for a partial aggregation whose result is a handful
+// of rows (Q1: 4 rows, Q6: 1): no host round trip, no collective. One block per destination copies the first *count rows of
+// every output column into the slot (peer memory over NVLink) and then publishes {seq, rows, error bits} with st.release.sys;
+// the destination's FINAL kernel (pgpu_k_gather, device/pgpu_device.cuh) waits on that header.
+constexpr int kMaxPushCols = 64;
+constexpr int kMaxRanks = 64;
+struct PushCol {
+    const void* values;
+    const uint8_t* nulls;
+    uint32_t stride;   // bytes per position
+    uint32_t pad;
+    uint64_t dstV, dstN;  // byte offsets of the column's arrays inside a slot
+};
+struct PushArgs {
+    PushCol c[kMaxPushCols];
+    char* slot[kMaxRanks];       // destination r: this rank's slot in r's inbox (header at +0)
+    const unsigned long long* count;  // rows in the output buffers (device)
+    const uint32_t* err;              // the partial pipeline's sticky error word (device)
+    unsigned long long seq;
+    int32_t ncols, nranks, capRows, pad;
+};
+cudaError_t pushPartial(cudaStream_t stream, const PushArgs& args);
+
 // host restatement of the same partition function (tests, multi-rank host logic)
 int32_t partitionOfHost(const int64_t* keyBits, const uint8_t* isNull, const int32_t* kinds, int nkeys, int nparts);
 

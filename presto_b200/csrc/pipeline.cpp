@@ -67,6 +67,13 @@ struct OutCol {
     void* values;
     uint8_t* nulls;
 };
+struct GatherArgs {
+    const uint64_t* hdr;
+    int32_t npages;
+    int32_t hdr_stride_words;
+    uint64_t seq;
+    uint64_t timeout_ns;
+};
 
 constexpr int kThreads = 256;
 constexpr int64_t kTileRows = kThreads * 4;
@@ -78,7 +85,7 @@ thread_local std::string g_lastGlobalError;
 struct Variant {
     GenResult gen;
     cudaLibrary_t lib = nullptr;
-    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr;
+    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr, kGather = nullptr;
     int blocksPerSM = 1;
     int stagedStages = 0;      // stages of the shared-memory ring (0 = staged variant unavailable)
     size_t stagedSmem = 0;
@@ -311,6 +318,9 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
                 CU(cudaLibraryGetKernel(&v.kReplay, v.lib, "pgpu_k_replay"));
                 if (v.gen.buckets) CU(cudaLibraryGetKernel(&v.kCount, v.lib, "pgpu_k_count"));
             }
+            if (v.gen.mode != KernelMode::COMPACT && p->plan->hasAgg && inputIsIntermediate(p->plan->step))
+                CU(cudaLibraryGetKernel(&v.kGather, v.lib, "pgpu_k_gather"));
+            if (v.gen.smemBytes > 48 * 1024) CU(cudaFuncSetAttribute((const void*)v.kPage, cudaFuncAttributeMaxDynamicSharedMemorySize, v.gen.smemBytes));
             if (v.gen.staged) {
                 // ring depth from the opt-in shared memory of the device (227 KB on sm_100), at most 4 stages
                 int optin = 0;
@@ -390,8 +400,9 @@ pgpu_status checkDeviceErrors(pgpu_pipeline* p) {
     if (e & 32u) return fail(p, PGPU_INVALID_CAST_ARGUMENT, "Unable to cast double to bigint");
     if (e & 8u) return fail(p, PGPU_INVALID_ARGUMENT, "varchar(n) value longer than n bytes");
     if (e & 64u) return fail(p, PGPU_INVALID_ARGUMENT, "corrupt Parquet page: dictionary id out of range");
+    if (e & 128u) return fail(p, PGPU_INVALID_STATE, "exchange: a peer's partial page did not arrive");
     if (e & 4u) return fail(p, PGPU_INSUFFICIENT_RESOURCES, "internal: hash table full");
-    return fail(p, PGPU_CUDA_ERROR, "internal: output buffer overflow");
+    return fail(p, PGPU_INSUFFICIENT_RESOURCES, "output buffer overflow (gather exchange: more groups than an inbox slot holds)");
 }
 
 // ------------------------------------------------------------------------------------------- table management
@@ -2471,3 +2482,5 @@ int32_t pgpu_partition_of(const int64_t* key_bits, const uint8_t* is_null, const
 }
 
 }  // extern "C"
+
+#include "comm.inc"

@@ -5,15 +5,16 @@ PartitionedOutputOperator -> exchange -> final operator (core/trino-main/src/mai
 PartitionedOutputOperator.java:56-133, HashAggregationOperator.java:367-518 with Step.FINAL, whose addIntermediate is
 deserialize + combine, operator/aggregation/AccumulatorCompiler.java:674-767).
 
-Two shapes:
-  * gather  — small group count (Q1, Q6): every rank's partial page is a few rows; they are all-gathered (one padded
-              NCCL all_gather_into_tensor after a size exchange) and every rank runs the FINAL step over all of them,
-              so every rank ends with the final result (the all-reduce shape, without assuming keys line up by slot).
+The exchange itself lives behind the C ABI (pgpu_comm_init / pgpu_exchange_partial, csrc/comm.inc): `Comm` below is a thin
+caller. Two shapes, chosen by the library from the partial plan:
+  * gather  — small group count (Q1, Q6): every rank's push kernel stores its partial rows into every rank's inbox over
+              NVLink and every rank's FINAL gather kernel merges them: no host round trip, no collective; every rank ends
+              with the final result (the all-reduce shape, without assuming keys line up by slot).
   * repartition — large group count: rows of the partial output are hash-partitioned on the device by the reference's
-              own partition function (pgpu_partition_output_device), exchanged column by column with
-              all_to_all_single over NVLink, and merged by a FINAL pipeline on the receiving GPU; the result stays
-              partitioned by key, as the output of Trino's final stage does.
-The host logic is backend agnostic (NCCL on GPUs, gloo in the CPU test-suite).
+              own partition function and each rank's FINAL page kernel reads its partition of every peer's rows straight
+              out of that peer's HBM (CUDA IPC); the result stays partitioned by key, as the output of Trino's final stage.
+What remains in Python: the NCCL baselines the bench can switch to (`--exchange nccl`: packed all-gather / all_to_all_single
+per column) and the host-side restatements the CPU test-suite drives over gloo.
 """
 from __future__ import annotations
 
@@ -28,6 +29,76 @@ from .spi import Block, Page, Type, block_of
 
 _FRAME = 32 * 1024
 PART_KIND = {1: 0, 2: 1, 3: 1, 4: 2}  # type kind -> pgpu_partition_of kind (BIGINT, INTEGER, DATE, DOUBLE)
+
+
+# ------------------------------------------------------------------------------------------------ the native exchange
+class Comm:
+    """One rank's membership of a job on one box (pgpu_comm): rendezvous through the shared-memory segment `name`, peers'
+    HBM mapped through CUDA IPC. exchange(partial, final) = PartitionedOutputOperator -> exchange -> FINAL.addInput for one
+    step; afterwards `final` is finishing and is drained with getOutput()."""
+
+    def __init__(self, world: int, rank: int, device: int, name: str):
+        self._lib = N.lib()
+        h = ctypes.c_void_p()
+        st = self._lib.pgpu_comm_init(world, rank, device, name.encode(), ctypes.byref(h))
+        if st != N.OK:
+            from .operators import TrinoException
+            raise TrinoException(st, self._lib.pgpu_last_global_error().decode())
+        self._h = h
+        self.world, self.rank, self.device = world, rank, device
+        self.recv_rows = 0
+        self.sent_bytes = 0
+
+    def _check(self, st: int):
+        if st != N.OK:
+            from .operators import TrinoException
+            raise TrinoException(st, self._lib.pgpu_comm_last_error(self._h).decode())
+
+    def exchange(self, partial, final) -> int:
+        rows, sent = ctypes.c_int64(), ctypes.c_int64()
+        self._check(self._lib.pgpu_exchange_partial(self._h, partial._h, final._h, ctypes.byref(rows), ctypes.byref(sent)))
+        self.recv_rows, self.sent_bytes = rows.value, sent.value
+        return rows.value
+
+    run = exchange   # the name the older Python transports used
+
+    def barrier(self):
+        self._check(self._lib.pgpu_comm_barrier(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.pgpu_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def gather_signature(final_plan: str):
+    """(encodings, nullable) of the pages the gather shape feeds a FINAL plan: every channel carries a null vector, VARCHAR
+    channels arrive as 16-byte cells. For pre-compiling the variant (GpuPipelineOperator.compileSignature) at plan time."""
+    at = final_plan.index("(input ") + len("(input ")
+    depth, tok, types = 0, "", []
+    for ch in final_plan[at:]:
+        if ch == "(":
+            depth += 1
+        if ch == ")":
+            if depth == 0:
+                break
+            depth -= 1
+        if ch.isspace() and depth == 0:
+            if tok:
+                types.append(tok)
+            tok = ""
+        else:
+            tok += ch
+    if tok:
+        types.append(tok)
+    enc = [N.ENC_VARCELL if t.startswith("(varchar") or t == "varchar" else N.ENC_PLAIN for t in types]
+    return enc, [True] * len(enc)
 
 
 # ------------------------------------------------------------------------------------------------ helpers
@@ -262,25 +333,18 @@ class DeviceRepartition:
     `partial` must be finishing (finish() called); `final` is a FINAL-step GpuPipelineOperator whose input channels are the
     partial pipeline's output channels. After run() the final operator holds this rank's partition of the groups.
 
-    transport "peer" (default for world > 1 on one node): every rank maps the peers' partition buffers (one CUDA IPC
-    handle per rank, cached while the allocation is stable) and its FINAL page kernel reads its partition of each peer's
-    rows straight out of that peer's HBM over NVLink / NVSwitch — the merge is fused with the transfer, there is no staging
-    copy and one small all-gather (row ranges + handles) plus one barrier per exchange.
-    transport "nccl": one all_to_all_single per column into receive buffers, then the FINAL pipeline over those (baseline)."""
+    This is the NCCL BASELINE of the repartition shape (one all_to_all_single per column into receive buffers, then the FINAL
+    pipeline over those); the product path is Comm.exchange (peer memory, no collective, no staging copy)."""
 
-    def __init__(self, device: int, world: int, rank: int, group=None, transport: str = "peer"):
+    def __init__(self, device: int, world: int, rank: int, group=None, transport: str = "nccl"):
         self.device, self.world, self.rank, self.group = device, world, rank, group
         self.transport = transport if world > 1 else "local"
         self.recv_keepalive: list = []
         self.sent_bytes = 0       # bytes this rank's partitions put on the wire (nccl) / peers read from it is symmetric (peer)
         self.recv_rows = 0
-        self._mapped = {}         # (peer rank, handle bytes) -> mapped base address
 
     def close(self):
-        L = N.lib()
-        for base in self._mapped.values():
-            L.pgpu_ipc_close(self.device, base)
-        self._mapped = {}
+        self.recv_keepalive = []
 
     @staticmethod
     def _width(t) -> int:
@@ -319,80 +383,10 @@ class DeviceRepartition:
                 if cnts[part]:
                     self._feed(final, types, own, offs[part], cnts[part])
                     total += cnts[part]
-        elif self.transport == "peer":
-            total = self._run_peer(final, types, own, offs, cnts)
         else:
             total = self._run_nccl(final, types, own, offs, cnts)
         self.recv_rows = total
         final.finish()
-        return total
-
-    # -- peer transport ------------------------------------------------------------------------------------------------
-    def _run_peer(self, final, types, own, offs, cnts) -> int:
-        import torch
-        import torch.distributed as dist
-        L = N.lib()
-        dev = torch.device("cuda", self.device)
-        nbuf = 2 * len(types)
-        # frame (int64): [starts(world) | counts(world) | offset per buffer (nbuf) | handle index per buffer (nbuf) |
-        #                 nhandles | handles (8 words each, at most nbuf)]
-        frame = np.zeros(2 * self.world + 2 * nbuf + 1 + 8 * nbuf, dtype=np.int64)
-        frame[:self.world] = offs[:self.world]
-        frame[self.world:2 * self.world] = cnts[:self.world]
-        handles: List[bytes] = []
-        pos = 2 * self.world
-        if any(cnts[i] for i in range(self.world)):
-            for b, ptr in enumerate(q for pair in own for q in pair):
-                h = ctypes.create_string_buffer(64)
-                off = ctypes.c_int64()
-                if L.pgpu_ipc_export(self.device, ptr, h, ctypes.byref(off)) != 0:
-                    raise RuntimeError("pgpu_ipc_export failed (CUDA IPC unavailable in this process environment)")
-                if h.raw not in handles:
-                    handles.append(h.raw)
-                frame[pos + b] = off.value
-                frame[pos + nbuf + b] = handles.index(h.raw)
-        frame[pos + 2 * nbuf] = len(handles)
-        hw = frame[pos + 2 * nbuf + 1:].view(np.uint8)
-        for i, h in enumerate(handles):
-            hw[64 * i:64 * i + 64] = np.frombuffer(h, dtype=np.uint8)
-        if dist.get_backend(self.group) != "nccl":
-            dev = torch.device("cpu")                        # control messages over gloo (tests: two processes, one GPU)
-        recv = torch.empty(self.world * frame.size, dtype=torch.int64, device=dev)
-        # the partition kernels have completed (pgpu_partition_output_device synchronises its stream), so a peer that has
-        # this rank's frame may read this rank's buffers
-        dist.all_gather_into_tensor(recv, torch.from_numpy(frame).to(dev), group=self.group)
-        frames = recv.cpu().numpy().reshape(self.world, frame.size)
-        total = 0
-        live = set()
-        for step in range(self.world):                       # own partition first, then the peers round-robin: at any
-            src = (self.rank + step) % self.world            # moment every rank reads from a different peer
-            f = frames[src]
-            start, count = int(f[self.rank]), int(f[self.world + self.rank])
-            if count == 0:
-                continue
-            if src == self.rank:
-                bases = own
-            else:
-                fh = f[pos + 2 * nbuf + 1:].view(np.uint8)
-                mapped = []
-                for i in range(int(f[pos + 2 * nbuf])):
-                    key = (src, fh[64 * i:64 * i + 64].tobytes())
-                    if key not in self._mapped:
-                        base = ctypes.c_void_p()
-                        if L.pgpu_ipc_open(self.device, key[1], ctypes.byref(base)) != 0:
-                            raise RuntimeError("pgpu_ipc_open failed for rank %d's partition buffers" % src)
-                        self._mapped[key] = base.value
-                    live.add(key)
-                    mapped.append(self._mapped[key])
-                flat = [mapped[int(f[pos + nbuf + b])] + int(f[pos + b]) for b in range(nbuf)]
-                bases = [(flat[2 * c], flat[2 * c + 1]) for c in range(len(types))]
-                self.sent_bytes += count * sum(self._width(t) + 1 for t in types)
-            self._feed(final, types, bases, start, count)
-            total += count
-        final.sync()                                         # this rank's reads of peer memory are complete ...
-        dist.barrier(group=self.group)                       # ... and so are everybody's: partition buffers may be reused
-        for key in [k for k in self._mapped if k not in live and any(k[0] == l[0] for l in live)]:
-            L.pgpu_ipc_close(self.device, self._mapped.pop(key))   # the peer moved to a larger allocation
         return total
 
     # -- NCCL transport (baseline) -----------------------------------------------------------------------------------------
@@ -427,188 +421,3 @@ class DeviceRepartition:
                 total += real_recv[src]
             start += pad_recv[src]
         return total
-
-
-# ------------------------------------------------------------------------------------------------ gather (device, peer memory)
-class Mailbox:
-    """One cache line per rank in a POSIX shared-memory segment: [seq, rows, done, -] (int64). A rank posts (seq, rows) once
-    its partial output for exchange `seq` is complete in its HBM; peers spin on the line — a host-side flag costs a few
-    hundred nanoseconds where a collective costs tens of microseconds. `done` = last exchange whose peer reads of this
-    rank's buffers this rank has finished (read by the owners before they overwrite their buffers)."""
-
-    WORDS = 8
-
-    def __init__(self, name: str, world: int, rank: int, create: bool):
-        from multiprocessing import shared_memory
-        size = world * world * self.WORDS * 8 + world * self.WORDS * 8
-        if create:
-            try:
-                old = shared_memory.SharedMemory(name=name)
-                old.close()
-                old.unlink()
-            except FileNotFoundError:
-                pass
-            self.shm = shared_memory.SharedMemory(name=name, create=True, size=size)
-            self.shm.buf[:size] = bytes(size)
-        else:
-            self.shm = shared_memory.SharedMemory(name=name)
-            try:   # the segment belongs to its creator: keep this process's resource tracker from unlinking it at exit
-                from multiprocessing import resource_tracker
-                resource_tracker.unregister(self.shm._name, "shared_memory")
-            except Exception:
-                pass
-        self.owner = create
-        self.world, self.rank = world, rank
-        a = np.ndarray((world + world * world, self.WORDS), dtype=np.int64, buffer=self.shm.buf)
-        self.post_lines = a[:world]                                  # [rank] -> seq, rows
-        self.done_lines = a[world:].reshape(world, world, self.WORDS)  # [reader][owner] -> seq the reader has finished with
-
-    def post(self, seq: int, rows: int):
-        line = self.post_lines[self.rank]
-        line[1] = rows
-        line[0] = seq            # published last (x86 stores are not reordered with older stores)
-
-    def wait_post(self, peer: int, seq: int, timeout_s: float = 60.0) -> int:
-        import time
-        line = self.post_lines[peer]
-        t0 = time.perf_counter()
-        while line[0] < seq:
-            if time.perf_counter() - t0 > timeout_s:
-                raise TimeoutError("rank %d did not post exchange %d" % (peer, seq))
-        return int(line[1])
-
-    def mark_done(self, owner: int, seq: int):
-        self.done_lines[self.rank, owner, 0] = seq
-
-    def wait_readers(self, seq: int, timeout_s: float = 60.0):
-        """until every peer has finished reading this rank's buffers of exchange `seq`"""
-        import time
-        t0 = time.perf_counter()
-        for reader in range(self.world):
-            while reader != self.rank and self.done_lines[reader, self.rank, 0] < seq:
-                if time.perf_counter() - t0 > timeout_s:
-                    raise TimeoutError("rank %d is still reading exchange %d" % (reader, seq))
-
-    def close(self):
-        self.post_lines = self.done_lines = None
-        self.shm.close()
-        if self.owner:
-            try:
-                self.shm.unlink()
-            except FileNotFoundError:
-                pass
-
-
-class PeerGather:
-    """Gather shape for small group counts without a data-path collective: every rank leaves its PARTIAL output in its own
-    HBM (pgpu_get_output_device: one allocation, VARCHAR keys as 16-byte cells), posts the row count in a shared-memory
-    mailbox, and every rank's FINAL kernel reads all ranks' partial rows straight out of their HBM over NVLink (CUDA IPC
-    mappings opened once). Per exchange: no NCCL call, no host staging, one D2H copy of the final result.
-
-    Needs one node (POSIX shared memory + CUDA IPC), which is what one-process-per-GPU under torchrun is."""
-
-    def __init__(self, device: int, world: int, rank: int, name: str):
-        import torch.distributed as dist
-        self.device, self.world, self.rank = device, world, rank
-        self.seq = 0
-        self._mapped = {}       # (peer, handle) -> mapped base
-        self._peer_cols = {}    # peer -> (key, [(values, nulls)] mapped pointers per channel)
-        self._export_key = None
-        self._export = None
-        if rank == 0:
-            self.mail = Mailbox(name, world, rank, create=True)
-        dist.barrier()
-        if rank != 0:
-            self.mail = Mailbox(name, world, rank, create=False)
-        dist.barrier()
-
-    def close(self):
-        L = N.lib()
-        for base in self._mapped.values():
-            L.pgpu_ipc_close(self.device, base)
-        self._mapped = {}
-        self.mail.close()
-
-    def run(self, partial, final) -> int:
-        """`partial` has finished its input; `final` is reset. Returns the rows fed to FINAL; final.finish() is called."""
-        import torch.distributed as dist
-        L = N.lib()
-        self.seq += 1
-        seq = self.seq
-        if seq > 1:
-            self.mail.wait_readers(seq - 1)          # peers are done with the buffers the next call overwrites
-        ncap = max(L.pgpu_output_channel_count(partial._h), 1)
-        cols = (N.Column * ncap)()
-        nc, rows = ctypes.c_int32(), ctypes.c_int64()
-        partial._check(L.pgpu_get_output_device(partial._h, cols, ncap, ctypes.byref(nc), ctypes.byref(rows)))
-        n = max(rows.value, 0)
-        ncols = nc.value if n else len(partial.outputTypes())
-        types = partial.outputTypes()[:ncols]
-        own = [(cols[c].values or 0, cols[c].nulls or 0) for c in range(ncols)] if n else None
-        key = tuple(own) if own else self._export_key
-        changed = own is not None and key != self._export_key
-        # a moved allocation is announced with a negative row count; everybody then joins one all-gather of handles
-        self.mail.post(seq, -(n + 1) if changed else n)
-        counts = [self.mail.wait_post(r, seq) for r in range(self.world)]
-        if any(c < 0 for c in counts):
-            self._share_handles(own, changed, counts)
-            if changed:
-                self._export_key = key
-            counts = [(-c - 1) if c < 0 else c for c in counts]
-        total = 0
-        for step in range(self.world):
-            src = (self.rank + step) % self.world
-            cnt = counts[src]
-            if cnt == 0:
-                continue
-            bases = own if src == self.rank else self._peer_cols[src]
-            fcols = (N.Column * ncols)()
-            for c, t in enumerate(types):
-                fc = fcols[c]
-                fc.encoding = N.ENC_VARCELL if t.kind == 6 else N.ENC_PLAIN
-                fc.type_kind, fc.precision, fc.scale = t.kind, t.precision, t.scale
-                fc.position_count = cnt
-                fc.values, fc.nulls = bases[c][0], bases[c][1]
-            final.addDeviceInput(fcols, ncols, cnt)
-            total += cnt
-        final.finish()
-        final.sync()                                 # this rank's reads of peer memory are complete
-        for r in range(self.world):
-            self.mail.mark_done(r, seq)
-        # drain the (finished) partial operator so that it reports isFinished like after a host read
-        while not L.pgpu_is_finished(partial._h):
-            partial._check(L.pgpu_get_output_device(partial._h, cols, ncap, ctypes.byref(nc), ctypes.byref(rows)))
-        return total
-
-    def _share_handles(self, own, changed, counts):
-        import torch
-        import torch.distributed as dist
-        L = N.lib()
-        nbuf = 2 * len(own) if own else 0
-        mine = {"rank": self.rank, "changed": bool(changed), "handles": [], "bufs": []}
-        if changed:
-            for ptr in (q for pair in own for q in pair):
-                h = ctypes.create_string_buffer(64)
-                off = ctypes.c_int64()
-                if L.pgpu_ipc_export(self.device, ptr, h, ctypes.byref(off)) != 0:
-                    raise RuntimeError("pgpu_ipc_export failed (CUDA IPC unavailable in this process environment)")
-                if h.raw not in mine["handles"]:
-                    mine["handles"].append(h.raw)
-                mine["bufs"].append((mine["handles"].index(h.raw), off.value))
-        everyone = [None] * self.world
-        dist.all_gather_object(everyone, mine)
-        for info in everyone:
-            src = info["rank"]
-            if src == self.rank or not info["changed"]:
-                continue
-            mapped = []
-            for h in info["handles"]:
-                k = (src, h)
-                if k not in self._mapped:
-                    base = ctypes.c_void_p()
-                    if L.pgpu_ipc_open(self.device, h, ctypes.byref(base)) != 0:
-                        raise RuntimeError("pgpu_ipc_open failed for rank %d's output buffers" % src)
-                    self._mapped[k] = base.value
-                mapped.append(self._mapped[k])
-            flat = [mapped[i] + off for i, off in info["bufs"]]
-            self._peer_cols[src] = [(flat[2 * c], flat[2 * c + 1]) for c in range(len(flat) // 2)]

@@ -142,56 +142,3 @@ def test_all_gather_frames_over_gloo():
         p.join(60)
         assert p.exitcode == 0
     assert all(ok for _, ok in results)
-
-
-def _mailbox_worker(rank, name, q):
-    import time
-    try:
-        if rank != 0:
-            time.sleep(0.3)   # the creator (rank 0) goes first; PeerGather orders this with a barrier
-        mb = X.Mailbox(name, 2, rank, create=(rank == 0))
-        if rank == 0:
-            time.sleep(0.5)
-        got = []
-        for seq in (1, 2, 3):
-            if seq > 1:
-                mb.wait_readers(seq - 1, timeout_s=20)
-            mb.post(seq, 10 * seq + rank)
-            got.append([mb.wait_post(r, seq, timeout_s=20) for r in range(2)])
-            for r in range(2):
-                mb.mark_done(r, seq)
-        mb.wait_readers(3, timeout_s=20)
-        q.put((rank, got))
-        time.sleep(0.5)
-        mb.close()
-    except BaseException:
-        import traceback
-        q.put((rank, traceback.format_exc()))
-        raise
-
-
-def test_mailbox_two_processes():
-    import torch.multiprocessing as mp
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    name = "pgpu_test_mail_%d" % os.getpid()
-    procs = [ctx.Process(target=_mailbox_worker, args=(r, name, q)) for r in range(2)]
-    for p in procs:
-        p.start()
-    results = [q.get(timeout=120) for _ in range(2)]
-    for p in procs:
-        p.join(60)
-    for rank, got in results:
-        assert got == [[10, 11], [20, 21], [30, 31]], got
-
-
-def test_mailbox_times_out_on_a_missing_peer():
-    name = "pgpu_test_mail_t_%d" % os.getpid()
-    mb = X.Mailbox(name, 2, 0, create=True)
-    try:
-        mb.post(1, 5)
-        assert mb.wait_post(0, 1) == 5
-        with pytest.raises(TimeoutError):
-            mb.wait_post(1, 1, timeout_s=0.2)
-    finally:
-        mb.close()

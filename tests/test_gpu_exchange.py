@@ -57,28 +57,91 @@ def test_partition_output_device(nparts):
     assert_rows_equal_ignore_order(list(zip(keys.tolist(), cnt.tolist(), sums.tolist())), exp, nkeys=1)
 
 
-def test_partial_partition_final_equals_single():
-    import torch
+FINAL_HC = lambda groups: plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0],  # noqa: E731
+                                    aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)], expectedGroups=groups)
+REPARTITION = 200_000   # expected-groups above what an inbox slot holds: pgpu_exchange_partial takes the repartition shape
+
+
+def drain(op):
+    out = []
+    while not op.isFinished():
+        p = op.getOutput()
+        if p is not None and p.position_count:
+            out.append(p)
+    return rows_of(out)
+
+
+def _unique(tag):
+    import os
+    import time
+    return "pgpu_test_%s_%d_%d" % (tag, os.getpid(), time.time_ns() % 1_000_000_000)
+
+
+def test_exchange_one_rank_repartition_equals_single():
     total = 400_000
     pages = [tpch.highcard_page(0, total // 2, total), tpch.highcard_page(total // 2, total // 2, total)]
     single = run_gpu(tpch.highcard_plan(1000), pages)
-    partial = GpuPipelineOperator(tpch.highcard_plan(1000, "partial"), 0)
-    final = GpuPipelineOperator(plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0],
-                                          aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)], expectedGroups=200_000), 0)
+    partial = GpuPipelineOperator(tpch.highcard_plan(REPARTITION, "partial"), 0)
+    final = GpuPipelineOperator(FINAL_HC(REPARTITION), 0)
+    comm = X.Comm(1, 0, 0, _unique("one"))
     try:
-        for p in pages:
-            partial.addInput(p)
-        partial.finish()
-        ex = X.DeviceRepartition(0, 1, 0)
-        n = ex.run(partial, final)   # world 1: partition + FINAL merge on the same device, no collective
-        assert n == len(single)
-        out = []
-        while not final.isFinished():
-            p = final.getOutput()
-            if p is not None:
-                out.append(p)
-        assert_rows_equal_ignore_order(rows_of(out), single, nkeys=1)
+        for step in range(2):
+            partial.reset()
+            final.reset()
+            for p in pages:
+                partial.addInput(p)
+            partial.finish()
+            assert comm.exchange(partial, final) == len(single)   # world 1: partition + FINAL merge on the same device
+            assert partial.isFinished()
+            assert_rows_equal_ignore_order(drain(final), single, nkeys=1)
     finally:
+        comm.close()
+        partial.close()
+        final.close()
+
+
+def test_exchange_one_rank_gather_q1_and_q6():
+    """gather shape with a single rank: the push kernel stores into the rank's own inbox, the gather kernel merges the slot"""
+    from test_oracle_protocol import q1_final_plan
+    total = 300_000
+    comm = X.Comm(1, 0, 0, _unique("g1"))
+    try:
+        for pplan, fplan, page_fn, nkeys in ((tpch.q1_plan("partial"), q1_final_plan(), tpch.q1_page, 2),
+                                             (tpch.q6_plan("partial"), plan_text([BIGINT, DOUBLE], step="final", aggregations=[Aggregation("sum", DOUBLE, 0, DOUBLE)]), tpch.q6_page, None)):
+            pages = [page_fn(0, total, total)]
+            single = run_gpu(pplan.replace("(step partial)", "(step single)"), pages)
+            partial, final = GpuPipelineOperator(pplan, 0), GpuPipelineOperator(fplan, 0)
+            try:
+                for step in range(3):                              # both inbox parities, then the first one again
+                    partial.reset()
+                    final.reset()
+                    partial.addInput(pages[0])
+                    partial.finish()
+                    assert comm.exchange(partial, final) == -1     # row count known on the device only
+                    assert_rows_equal_ignore_order(drain(final), single, nkeys=nkeys, rtol=sequential_bound(total))
+            finally:
+                partial.close()
+                final.close()
+    finally:
+        comm.close()
+
+
+def test_exchange_gather_overflow_is_an_error():
+    """a plan that promises few groups but produces more than an inbox slot holds fails loudly at getOutput"""
+    from presto_b200.operators import TrinoException
+    total = 100_000
+    partial = GpuPipelineOperator(tpch.highcard_plan(1000, "partial"), 0)    # expected-groups 1000: gather shape; 25 000 groups arrive
+    final = GpuPipelineOperator(FINAL_HC(1000), 0)
+    comm = X.Comm(1, 0, 0, _unique("ovf"))
+    try:
+        partial.addInput(tpch.highcard_page(0, total, total))
+        partial.finish()
+        comm.exchange(partial, final)
+        with pytest.raises(TrinoException) as e:
+            drain(final)
+        assert "inbox slot" in str(e.value)
+    finally:
+        comm.close()
         partial.close()
         final.close()
 
@@ -113,54 +176,40 @@ def test_packed_partial_frames_feed_final():
         final.close()
 
 
-def _peer_worker(rank, world, port, total, q):
-    import os
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
-    import torch.distributed as dist
-    dist.init_process_group("gloo", rank=rank, world_size=world)
-    partial = final = ex = None
+def _repartition_worker(rank, world, name, total, q):
+    partial = final = comm = None
     try:
         per = total // world
-        partial = GpuPipelineOperator(tpch.highcard_plan(1000, "partial"), 0)
-        final = GpuPipelineOperator(plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0],
-                                              aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)], expectedGroups=200_000), 0)
-        ex = X.DeviceRepartition(0, world, rank, transport="peer")
-        out = []
-        for step in range(2):                                  # the second exchange reuses the cached mappings
+        partial = GpuPipelineOperator(tpch.highcard_plan(REPARTITION, "partial"), 0)
+        final = GpuPipelineOperator(FINAL_HC(REPARTITION), 0)
+        comm = X.Comm(world, rank, 0, name)
+        rows = []
+        for step in range(3):                                  # later exchanges reuse the mapped arenas
             partial.reset()
             final.reset()
             partial.addInput(tpch.highcard_page(rank * per, per, total, shuffled=True))
             partial.finish()
-            ex.run(partial, final)
-            out = []
-            while not final.isFinished():
-                p = final.getOutput()
-                if p is not None:
-                    out.append(p)
-        rows = rows_of(out)
+            comm.exchange(partial, final)
+            rows = drain(final)
         assert all(X.partition_of_row([r[0]], [BIGINT], world) == rank for r in rows[:5000])
-        q.put((rank, rows, ex.sent_bytes))
+        q.put((rank, rows, comm.sent_bytes))
     except BaseException:
         import traceback
         q.put((rank, traceback.format_exc(), -1))   # the parent fails at once instead of waiting for its queue timeout
         raise
     finally:
-        if ex is not None:
-            ex.close()
+        if comm is not None:
+            comm.close()
         for op in (partial, final):
             if op is not None:
                 op.close()
-        dist.destroy_process_group()
 
 
-def test_peer_memory_exchange_two_processes():
-    """two processes (ranks) on this GPU: each FINAL kernel reads the other process's partition buffers through CUDA IPC"""
-    import os
+def _spawn(worker, world, name, total):
     import torch.multiprocessing as mp
-    world, total, port = 2, 200_000, 33000 + os.getpid() % 2000
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_peer_worker, args=(r, world, port, total, q)) for r in range(world)]
+    procs = [ctx.Process(target=worker, args=(r, world, name, total, q)) for r in range(world)]
     for p in procs:
         p.start()
     results = []
@@ -170,6 +219,13 @@ def test_peer_memory_exchange_two_processes():
     for p in procs:
         p.join(120)
         assert p.exitcode == 0
+    return results
+
+
+def test_exchange_repartition_two_processes():
+    """two processes (ranks) on this GPU: each FINAL kernel reads the other process's partition arena through CUDA IPC"""
+    world, total = 2, 200_000
+    results = _spawn(_repartition_worker, world, _unique("rp"), total)
     per = total // world
     single = run_gpu(tpch.highcard_plan(1000), [tpch.highcard_page(r * per, per, total, shuffled=True) for r in range(world)])
     got = [row for _, rows, _ in results for row in rows]
@@ -210,65 +266,44 @@ def test_device_cells_feed_final():
             op.close()
 
 
-def _peer_gather_worker(rank, world, port, total, q):
+def _gather_worker(rank, world, name, total, q):
     import os
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     import sys
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
-    import torch.distributed as dist
     from test_oracle_protocol import q1_final_plan
-    dist.init_process_group("gloo", rank=rank, world_size=world)
-    partial = final = ex = None
+    partial = final = comm = None
     try:
         per = total // world
         partial = GpuPipelineOperator(tpch.q1_plan("partial"), 0)
         final = GpuPipelineOperator(q1_final_plan(), 0)
-        ex = X.PeerGather(0, world, rank, "pgpu_test_gather_%d" % port)
+        comm = X.Comm(world, rank, 0, name)
         page = tpch.q1_page(rank * per, per, total)
         rows = []
-        for step in range(3):                                  # later exchanges reuse the mappings and the mailbox
+        for step in range(4):                                  # both inbox parities twice
             partial.reset()
             final.reset()
             partial.addInput(page)
             partial.finish()
-            assert ex.run(partial, final) == 4 * world
-            out = []
-            while not final.isFinished():
-                p = final.getOutput()
-                if p is not None:
-                    out.append(p)
-            rows = rows_of(out)
+            comm.exchange(partial, final)
+            rows = drain(final)
         q.put((rank, rows, 0))
     except BaseException:
         import traceback
         q.put((rank, traceback.format_exc(), -1))
         raise
     finally:
-        if ex is not None:
-            ex.close()
+        if comm is not None:
+            comm.close()
         for op in (partial, final):
             if op is not None:
                 op.close()
-        dist.destroy_process_group()
 
 
-def test_peer_gather_two_processes():
-    """small group counts: every rank's FINAL reads both ranks' partial pages through CUDA IPC; no data-path collective"""
-    import os
-    import torch.multiprocessing as mp
-    world, total, port = 2, 200_000, 35000 + os.getpid() % 2000
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    procs = [ctx.Process(target=_peer_gather_worker, args=(r, world, port, total, q)) for r in range(world)]
-    for p in procs:
-        p.start()
-    results = []
-    for _ in range(world):
-        results.append(q.get(timeout=300))
-        assert results[-1][2] >= 0, results[-1][1]
-    for p in procs:
-        p.join(120)
-        assert p.exitcode == 0
+def test_exchange_gather_two_processes():
+    """small group counts: each rank's push kernel stores its partial rows into both ranks' inboxes (CUDA IPC), each rank's
+    gather kernel merges both slots; no host round trip, no collective"""
+    world, total = 2, 200_000
+    results = _spawn(_gather_worker, world, _unique("ga"), total)
     single = run_gpu(tpch.q1_plan(), [tpch.q1_page(0, total, total)])
     for _, rows, _ in results:
         assert_rows_equal_ignore_order(rows, single, nkeys=2, rtol=sequential_bound(total))

@@ -75,6 +75,23 @@ def bench_plans():
     ops[1].compileSignature([1, 1, 1, 0, 1, 1, 0], [False] * 7)
     for op in ops:
         op.close()
+    gather_variants()
+
+
+def gather_variants():
+    """FINAL plans as the gather exchange feeds them (pgpu_exchange_partial): every channel with a null vector, VARCHAR keys
+    as 16-byte cells; plus the device-page signature of the repartition shape"""
+    import bench as B
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_oracle_protocol import q1_final_plan
+    from test_gpu_exchange import FINAL_HC, REPARTITION
+    plans = [B.final_plan_for({"name": "q1"}, None), B.final_plan_for({"name": "q6"}, None), B.final_plan_for({"name": "highcard", "rows": 600_037_902}, None),
+             q1_final_plan(), FINAL_HC(REPARTITION), FINAL_HC(1000)]
+    for plan in plans:
+        from presto_b200.exchange import gather_signature
+        op = O.GpuPipelineOperator(plan, -1)
+        op.compileSignature(*gather_signature(plan))
+        op.close()
 
 
 if __name__ == "__main__":
