@@ -119,6 +119,19 @@ const char* pgpu_last_error(const pgpu_pipeline* p);
 int32_t pgpu_needs_input(const pgpu_pipeline* p);
 /* Operator.addInput(Page): columns are copied (or DMA'd) before the call returns control of unpinned buffers. */
 pgpu_status pgpu_add_page(pgpu_pipeline* p, const pgpu_column* cols, int32_t ncols, int64_t rows, uint32_t flags);
+/* Everything pgpu_add_page for a page of this signature and size could WAIT for, done ahead of it: the kernel variant of the
+ * signature is compiled, and a staging slot with room for `rows` more positions is ready (the pending super-page is sent and
+ * the next slot's previous kernel awaited when it is not). pgpu_add_page then only copies — which is what a JNI caller holding
+ * GetPrimitiveArrayCritical needs: no compilation and no device wait inside the critical region (pages larger than a whole
+ * staging slot excepted). Optional; pgpu_add_page does the same work itself when it was not called. */
+pgpu_status pgpu_reserve_input(pgpu_pipeline* p, const int32_t* encodings, const uint8_t* nullable, int32_t ncols, int64_t rows);
+/* Operator.isBlocked() (main/operator/Operator.java:24-35): 1 while device work queued by `p` is still running, i.e. while a
+ * pgpu_get_output* / pgpu_sync call would have to wait; never an error. pgpu_on_unblocked registers `fn(user)` to be called
+ * (from a CUDA host-callback thread; it must not call back into the library) once everything queued so far has completed —
+ * the completion of the ListenableFuture the Java operator returns instead of blocking the Driver thread. */
+typedef void (*pgpu_callback)(void* user);
+int32_t pgpu_is_blocked(const pgpu_pipeline* p);
+pgpu_status pgpu_on_unblocked(pgpu_pipeline* p, pgpu_callback fn, void* user);
 /* Operator.addInput of a Page in the reference's wire format: `data` (host) is the uncompressed payload of a SerializedPage —
  * what PagesSerdeUtil.writeRawPage produces (main/execution/buffer/PagesSerdeUtil.java:45-62): int32 channel count, then per
  * block the length-prefixed encoding name and body (LONG_ARRAY / INT_ARRAY / BYTE_ARRAY / INT128_ARRAY / VARIABLE_WIDTH, and
@@ -275,52 +288,6 @@ void pgpu_host_free(void* ptr);
 /* Device memory helpers for callers without torch. */
 void* pgpu_device_alloc(int32_t device, size_t bytes);
 void pgpu_device_free(int32_t device, void* ptr);
-/* Synchronous copies between host and device memory (test / bench plumbing for callers without torch). */
-pgpu_status pgpu_memcpy_h2d(int32_t device, void* dev_dst, const void* host_src, size_t bytes);
-pgpu_status pgpu_memcpy_d2h(int32_t device, void* host_dst, const void* dev_src, size_t bytes);
-
-/* Synthetic TPC-H lineitem columns generated directly in HBM (SURVEY.md §8(d) distributions; the
- * reference's generator io.trino.tpch:tpch:1.1 is not in its tree). Column ids: see PGPU_LI_* below.
- * Row r of a column depends only on (seed, r): pgpu_gen_lineitem_host produces the identical bytes on the CPU. */
-#define PGPU_LI_ORDERKEY 0      /* int64  */
-#define PGPU_LI_QUANTITY 1      /* double */
-#define PGPU_LI_EXTENDEDPRICE 2 /* double */
-#define PGPU_LI_DISCOUNT 3      /* double */
-#define PGPU_LI_TAX 4           /* double */
-#define PGPU_LI_SHIPDATE 5      /* int32 days since epoch */
-#define PGPU_LI_RETURNFLAG 6    /* 1 byte per row (varchar(1) payload) */
-#define PGPU_LI_LINESTATUS 7    /* 1 byte per row */
-#define PGPU_LI_IOTA_OFFSETS 8  /* int32 offsets 0..rows (rows+1 entries) for varchar(1) blocks */
-#define PGPU_LI_DISCOUNT_ID 9   /* int32 dictionary id of discount (0..10) */
-#define PGPU_LI_TAX_ID 10       /* int32 dictionary id of tax (0..8) */
-#define PGPU_LI_QUANTITY_ID 11  /* int32 dictionary id of quantity (0..49) */
-#define PGPU_LI_RETURNFLAG_ID 12/* int32 dictionary id of returnflag (A,N,R) */
-#define PGPU_LI_LINESTATUS_ID 13/* int32 dictionary id of linestatus (F,O) */
-#define PGPU_LI_ORDERKEY_SHUFFLED 14 /* int64, uniform random over the same key domain */
-pgpu_status pgpu_gen_lineitem_device(int32_t device, int32_t column, uint64_t seed, int64_t first_row, int64_t rows,
-                                     int64_t total_rows, void* dev_out);
-pgpu_status pgpu_gen_lineitem_host(int32_t column, uint64_t seed, int64_t first_row, int64_t rows,
-                                   int64_t total_rows, void* host_out);
-
-/* TPC-H lineitem rows exactly as the reference's tpch connector produces them (plugin/trino-tpch/.../TpchRecordSet.java:51-60
- * calling the un-vendored io.trino.tpch:tpch:1.1 generator = the TPC's dbgen): same rows, same order, at any scale factor.
- * Rows are addressed by ORDER: orders [first_order, first_order + n_orders) of pgpu_tpch_order_count(sf) = 1 500 000 x sf, each
- * with 1..7 lineitems; pgpu_tpch_lineitem_rows gives the row count of a range (size the buffers with it). Columns are the
- * PGPU_LI_* ids above (not IOTA_OFFSETS / ORDERKEY_SHUFFLED). Format NATIVE = the connector's types (TpchMetadata.java:587-600:
- * DOUBLE quantity / extendedprice / discount / tax, int32 epoch days, one byte per flag); DECIMAL_12_2 = unscaled int64 of the
- * DECIMAL(12,2) columns the reference's hive_tpch golden answers (q01.result, q06.result) were computed on.
- * The generator is pinned by those answers and by the reference's table statistics (tests/test_tpch_golden.py). */
-#define PGPU_TPCH_NATIVE 0
-#define PGPU_TPCH_DECIMAL_12_2 1
-int64_t pgpu_tpch_order_count(double sf);
-pgpu_status pgpu_tpch_lineitem_rows(double sf, int64_t first_order, int64_t n_orders, int64_t* rows);
-pgpu_status pgpu_tpch_lineitem_device(int32_t device, double sf, int64_t first_order, int64_t n_orders, int32_t column, int32_t format,
-                                      int64_t capacity_rows, void* dev_out, int64_t* rows);
-pgpu_status pgpu_tpch_lineitem_host(double sf, int64_t first_order, int64_t n_orders, int32_t column, int32_t format,
-                                    int64_t capacity_rows, void* host_out, int64_t* rows);
-/* Write `bytes` of device memory (L2 flush between timed iterations). */
-pgpu_status pgpu_flush_l2(int32_t device, void* dev_scratch, size_t bytes);
-
 #ifdef __cplusplus
 }
 #endif

@@ -4,6 +4,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libprestogpu.so")
+BENCH_LIB_PATH = os.path.join(_HERE, "libprestogpu_bench.so")   # include/prestogpu_bench.h: generators, copies, L2 flush (bench / tests)
 
 # pgpu_status
 OK, NOT_SUPPORTED, INVALID_ARGUMENT, NUMERIC_VALUE_OUT_OF_RANGE, DIVISION_BY_ZERO = 0, 1, 2, 3, 4
@@ -57,6 +58,9 @@ SYMBOLS = [
     ("pgpu_last_error", ctypes.c_char_p, [_P]),
     ("pgpu_needs_input", ctypes.c_int32, [_P]),
     ("pgpu_add_page", ctypes.c_int32, [_P, _COLS, ctypes.c_int32, ctypes.c_int64, ctypes.c_uint32]),
+    ("pgpu_reserve_input", ctypes.c_int32, [_P, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_uint8), ctypes.c_int32, ctypes.c_int64]),
+    ("pgpu_is_blocked", ctypes.c_int32, [_P]),
+    ("pgpu_on_unblocked", ctypes.c_int32, [_P, ctypes.c_void_p, ctypes.c_void_p]),
     ("pgpu_add_device_page", ctypes.c_int32, [_P, _COLS, ctypes.c_int32, ctypes.c_int64]),
     ("pgpu_finish", ctypes.c_int32, [_P]),
     ("pgpu_is_finished", ctypes.c_int32, [_P]),
@@ -76,10 +80,6 @@ SYMBOLS = [
     ("pgpu_add_parquet_row_group", ctypes.c_int32, [_P, ctypes.POINTER(ParquetChunk), ctypes.c_int32, ctypes.c_int64]),
     ("pgpu_parquet_inspect_chunk", ctypes.c_int32, [ctypes.POINTER(ParquetChunk), ctypes.POINTER(ctypes.c_int64), ctypes.c_char_p, ctypes.c_size_t]),
     ("pgpu_parquet_chunk_runs", ctypes.c_int32, [ctypes.POINTER(ParquetChunk), ctypes.c_int32, ctypes.c_void_p, ctypes.c_int64, ctypes.POINTER(ctypes.c_int64)]),
-    ("pgpu_tpch_order_count", ctypes.c_int64, [ctypes.c_double]),
-    ("pgpu_tpch_lineitem_rows", ctypes.c_int32, [ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_int64)]),
-    ("pgpu_tpch_lineitem_device", ctypes.c_int32, [ctypes.c_int32, ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]),
-    ("pgpu_tpch_lineitem_host", ctypes.c_int32, [ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_comm_init", ctypes.c_int32, [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_char_p, ctypes.POINTER(_P)]),
     ("pgpu_comm_destroy", None, [_P]),
     ("pgpu_comm_last_error", ctypes.c_char_p, [_P]),
@@ -93,6 +93,14 @@ SYMBOLS = [
     ("pgpu_host_free", None, [ctypes.c_void_p]),
     ("pgpu_device_alloc", ctypes.c_void_p, [ctypes.c_int32, ctypes.c_size_t]),
     ("pgpu_device_free", None, [ctypes.c_int32, ctypes.c_void_p]),
+]
+
+# every symbol include/prestogpu_bench.h declares (libprestogpu_bench.so)
+BENCH_SYMBOLS = [
+    ("pgpu_tpch_order_count", ctypes.c_int64, [ctypes.c_double]),
+    ("pgpu_tpch_lineitem_rows", ctypes.c_int32, [ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_int64)]),
+    ("pgpu_tpch_lineitem_device", ctypes.c_int32, [ctypes.c_int32, ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]),
+    ("pgpu_tpch_lineitem_host", ctypes.c_int32, [ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_memcpy_h2d", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]),
     ("pgpu_memcpy_d2h", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]),
     ("pgpu_gen_lineitem_device", ctypes.c_int32, [ctypes.c_int32, ctypes.c_int32, ctypes.c_uint64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p]),
@@ -101,6 +109,30 @@ SYMBOLS = [
 ]
 
 _lib = None
+
+
+class _Lib:
+    """The product library, with the bench / test plumbing of libprestogpu_bench.so reachable under the same handle (loaded on
+    first use of one of its symbols, so that product code paths never map it)."""
+
+    def __init__(self, handle):
+        self._handle = handle
+        self._bench = None
+
+    def __getattr__(self, name):
+        h = self.__dict__["_handle"]
+        if any(name == b[0] for b in BENCH_SYMBOLS):
+            if self.__dict__["_bench"] is None:
+                if not os.path.exists(BENCH_LIB_PATH):
+                    raise RuntimeError("presto_b200: %s is missing. Build it with `python -m presto_b200.build`." % BENCH_LIB_PATH)
+                b = ctypes.CDLL(BENCH_LIB_PATH)
+                for n, res, args in BENCH_SYMBOLS:
+                    fn = getattr(b, n)
+                    fn.restype = res
+                    fn.argtypes = args
+                self.__dict__["_bench"] = b
+            return getattr(self.__dict__["_bench"], name)
+        return getattr(h, name)
 
 
 def lib():
@@ -116,5 +148,5 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        _lib = handle
+        _lib = _Lib(handle)
     return _lib

@@ -1330,6 +1330,8 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     src << "    static constexpr bool BUCKETS = " << (res.buckets ? "true" : "false") << ";  // bucketed table: SLOTW words per bucket of 8 keys\n";
     src << "    static constexpr int BSLOTW = " << bslotw << ", BSH = " << (fields.empty() ? 0 : 8 * fields[0].byteOffset) << ", BPRES = 48;\n";
     src << "    static constexpr u64 BPMASK = 0xffull << BPRES;\n";
+    src << "    static constexpr bool BCASFIRST = " << (envInt("PGPU_TUNE_BCAS", 1) ? "true" : "false") << ";  // bucket leaders claim with one compare-and-swap, no load first\n";
+    src << "    static constexpr int BKBITS = " << (fields.empty() ? 64 : std::min(64, 8 * fields[0].nbytes)) << ";  // width of the (first) key field\n";
     src << "    static constexpr int KOFF = " << (tagless ? 0 : 1) << ";  // first key word of a slot\n";
     src << "    static constexpr bool USE_DIR = " << (res.useDir ? "true" : "false") << ";\n";
     src << "    static constexpr int DCAP = " << std::max(res.dirCap, 1) << ", DLIMIT = " << std::max(res.dirCap * 3 / 4, 1) << ", NWARP = 8, MAX_WARP_GROUPS = 8;\n";

@@ -71,6 +71,8 @@ struct TableArgs {
     u64* faillog;    // chunk-relative indices of deferred rows; replayed by k_replay after the host grew the table
     u64 faillog_cap;
     u64 row_bias;    // added to the kernel's row numbers when logging (a kernel launched on the tail of a chunk)
+    u64 bucket_off;  // bucketed tables: added to the key before it is cut into (bucket, position), so that clusters that start
+                     // at 8n + 1 (TPC-H order keys: 1..8, 33..40, ...) fill one bucket instead of straddling two
 };
 
 // Per-pipeline device scratch shared by all kernels.
@@ -563,19 +565,35 @@ PGPU_DEV void slot_key(const u64* slot, u64 (&key)[P::KW > 0 ? P::KW : 1]) {
 // byte (bit P::BPRES + j: key j of the bucket exists), set with a fire-and-forget RED.OR and ignored by comparisons.
 // One 160-byte fetch and write-back per 8 groups instead of eight 64 + 32-byte ones; groups are counted when the table is
 // read out (body_count_groups), t.counters[0] counts claimed buckets.
+// the key field (P::BKBITS bits at bit P::BSH of the packed key words) as an integer, and back
 template <class P>
-PGPU_DEV void bucket_split(const u64 (&key)[P::KWA], u64 (&bk)[P::KWA], u32& sub) {
-#pragma unroll
-    for (int i = 0; i < P::KWA; i++) bk[i] = key[i];
-    sub = (u32)(key[0] >> P::BSH) & 7u;
-    bk[0] &= ~(7ull << P::BSH);
+PGPU_DEV u64 bk_extract(const u64* w) {
+    u64 k = w[0] >> P::BSH;
+    if (P::BSH > 0 && P::BSH + P::BKBITS > 64) k |= w[P::KWA - 1] << (64 - P::BSH);
+    if (P::BKBITS < 64) k &= (1ull << (P::BKBITS & 63)) - 1ull;
+    return k;
 }
 template <class P>
-PGPU_DEV void bucket_join(const u64* slot, u32 sub, u64 (&key)[P::KWA]) {
+PGPU_DEV void bk_insert(u64* w, u64 k) {
+    const u64 m = P::BKBITS < 64 ? (1ull << (P::BKBITS & 63)) - 1ull : ~0ull;
+    k &= m;
+    w[0] = (w[0] & ~(m << P::BSH)) | (k << P::BSH);
+    if (P::BSH > 0 && P::BSH + P::BKBITS > 64) w[P::KWA - 1] = (w[P::KWA - 1] & ~(m >> (64 - P::BSH))) | (k >> (64 - P::BSH));
+}
+template <class P>
+PGPU_DEV void bucket_split(const TableArgs& t, const u64 (&key)[P::KWA], u64 (&bk)[P::KWA], u32& sub) {
+#pragma unroll
+    for (int i = 0; i < P::KWA; i++) bk[i] = key[i];
+    const u64 k = bk_extract<P>(key) + t.bucket_off;   // wraps inside the key's width (bk_insert masks)
+    sub = (u32)k & 7u;
+    bk_insert<P>(bk, k & ~7ull);
+}
+template <class P>
+PGPU_DEV void bucket_join(const TableArgs& t, const u64* slot, u32 sub, u64 (&key)[P::KWA]) {
 #pragma unroll
     for (int i = 0; i < P::KW; i++) key[i] = slot[i];
     key[P::KWA - 1] &= ~(KEY_MARK | P::BPMASK);
-    key[0] |= (u64)sub << P::BSH;
+    bk_insert<P>(key, (bk_extract<P>(key) | (u64)sub) - t.bucket_off);
 }
 template <class P>
 PGPU_DEV u32 bucket_presence(const u64* slot) {
@@ -606,7 +624,7 @@ template <class P>
 PGPU_DEV bool bucket_update(const TableArgs& t, const u64 (&key)[P::KWA], const u64 (&hot)[P::NHA], bool force, u32& nins) {
     u64 bk[P::KWA];
     u32 sub;
-    bucket_split<P>(key, bk, sub);
+    bucket_split<P>(t, key, bk, sub);
     u64* s = table_upsert<P::KW, P::BSLOTW, true, P::BPMASK>(t, bk, hash_key<P::KW>(bk), force || table_may_insert(t), nins);
     if (!s) return false;
     P::atomic_cells(s + P::KW + sub * P::NW, hot);
@@ -1183,17 +1201,24 @@ struct HashCtx {
     // slot, its followers take the slot pointer by shuffle, every lane then adds its run to its own cells of the slot.
     struct RunB {
         int s, e;
-        bool act;
+        bool act, head, cased;  // head: first lane of its bucket; cased: the leader's compare-and-swap is in flight (pre = its result)
+        int leader;
         u64 bk[KW > 0 ? KW : 1];
         u32 sub;
         u64 h;
         ProbePre pre;
     };
-    PGPU_DEV void run_issue_b(const TableArgs& t, const u8* starts, int nruns, int j, RunB& a) {
+    // all 32 lanes. Leaders go straight for the slot with ONE compare-and-swap (P::BCASFIRST): its result says claimed / already
+    // this bucket / somebody else's, so the common cases cost one memory round trip instead of a load and then the swap — and only
+    // one lane in (up to) eight issues it. While the table is at its load-factor limit (allow = false) leaders only look.
+    PGPU_DEV void run_issue_b(const TableArgs& t, const u8* starts, int nruns, int j, bool allow, RunB& a) {
+        const int lane = threadIdx.x & 31;
         a.act = j < nruns;
         a.s = a.e = 0;
         a.sub = 0;
         a.h = 0;
+        a.cased = false;
+        a.pre.c0 = a.pre.c1 = 0;
 #pragma unroll
         for (int w = 0; w < KW; w++) a.bk[w] = 0;
         if (a.act) {
@@ -1206,9 +1231,28 @@ struct HashCtx {
             u64 k[KW > 0 ? KW : 1];
 #pragma unroll
             for (int w = 0; w < KW; w++) k[w] = runsm[w * 128 + a.s];
-            bucket_split<P>(k, a.bk, a.sub);
+            bucket_split<P>(t, k, a.bk, a.sub);
             a.h = hash_key<KW>(a.bk);
-            a.pre = probe_prefetch<KW, P::BSLOTW>(t, a.h);
+        }
+        // leaders: the first lane of each stretch of lanes that hold runs of the same bucket
+        const bool pact = __shfl_up_sync(FULLMASK, (int)a.act, 1) != 0;  // every lane takes part in the shuffles
+        bool same = a.act && lane > 0 && pact;
+#pragma unroll
+        for (int w = 0; w < KW; w++) same &= (shfl_u64(a.bk[w], (lane + 31) & 31) == a.bk[w]);
+        a.head = a.act && !same;
+        const u32 heads = __ballot_sync(FULLMASK, a.head);
+        a.leader = a.act ? 31 - __clz(heads & ((2u << lane) - 1u)) : lane;
+        if (a.head) {
+            u64* s = t.slots + home_pos(a.h, t.capacity) * P::BSLOTW;
+            if (P::BCASFIRST && allow) {
+                const u64 k0 = KW == 1 ? (a.bk[0] | KEY_MARK) : a.bk[0];
+                const u64 k1 = KW == 2 ? (a.bk[KW - 1] | KEY_MARK) : 0ull;
+                if (KW == 1) a.pre.c0 = atomicCAS(s, 0ull, k0);
+                else cas_u128(s, 0ull, 0ull, k0, k1, a.pre.c0, a.pre.c1);
+                a.cased = true;
+            } else {
+                a.pre = probe_prefetch<KW, P::BSLOTW>(t, a.h);
+            }
         }
     }
     PGPU_DEV void run_resolve_b(const TableArgs& t, i64 wbase, bool allow, const RunB& a) {  // all 32 lanes
@@ -1226,24 +1270,20 @@ struct HashCtx {
                 P::combine(v, b);
             }
         }
-        // leaders: the first lane of each stretch of lanes that hold runs of the same bucket
-        const bool pact = __shfl_up_sync(FULLMASK, (int)a.act, 1) != 0;  // every lane takes part in the shuffles
-        bool same = a.act && lane > 0 && pact;
-#pragma unroll
-        for (int w = 0; w < KW; w++) same &= (shfl_u64(a.bk[w], (lane + 31) & 31) == a.bk[w]);
-        const bool head = a.act && !same;
-        const u32 heads = __ballot_sync(FULLMASK, head);
-        const int leader = a.act ? 31 - __clz(heads & ((2u << lane) - 1u)) : lane;
         u64* s = nullptr;
-        if (head) {
+        if (a.head) {
             const u64 k0 = KW == 1 ? (a.bk[0] | KEY_MARK) : a.bk[0];
             const u64 k1 = KW == 2 ? (a.bk[KW - 1] | KEY_MARK) : 0ull;
             const bool found = KW == 1 ? (a.pre.c0 & ~P::BPMASK) == k0 : (a.pre.c0 == k0 && (a.pre.c1 & ~P::BPMASK) == k1);
             const bool empty = KW == 1 ? a.pre.c0 == 0ull : a.pre.c1 == 0ull;
             s = t.slots + home_pos(a.h, t.capacity) * P::BSLOTW;
-            if (!found) {
+            if (a.cased) {
+                // pre = what the slot held before the swap: nothing (claimed now), this bucket, or another one
+                if (empty) nins++;
+                else if (!found) s = table_upsert<KW, P::BSLOTW, true, P::BPMASK>(t, a.bk, a.h, true, nins, nullptr, 1);  // walk the chain from home + 1
+            } else if (!found) {
                 if (!empty) {
-                    s = table_upsert<KW, P::BSLOTW, true, P::BPMASK>(t, a.bk, a.h, allow, nins, nullptr, 1);  // walk the chain from home + 1
+                    s = table_upsert<KW, P::BSLOTW, true, P::BPMASK>(t, a.bk, a.h, allow, nins, nullptr, 1);
                 } else if (!allow) {
                     s = nullptr;  // a new bucket while the table is at its load-factor limit: defer
                 } else {
@@ -1257,7 +1297,7 @@ struct HashCtx {
                 }
             }
         }
-        s = reinterpret_cast<u64*>(shfl_u64((u64)(size_t)s, leader));
+        s = reinterpret_cast<u64*>(shfl_u64((u64)(size_t)s, a.leader));
         u32 bit = 0;
         if (a.act) {
             if (s) {
@@ -1268,9 +1308,9 @@ struct HashCtx {
             }
         }
         // one RED.OR per bucket: the leader sets the presence bits of all its followers
-        const u32 peers = __match_any_sync(FULLMASK, a.act ? leader : 32 + lane);
+        const u32 peers = __match_any_sync(FULLMASK, a.act ? a.leader : 32 + lane);
         const u32 bits = __reduce_or_sync(peers, bit);
-        if (head && s && bits) atomicOr(s + KW - 1, (u64)bits << P::BPRES);
+        if (a.head && s && bits) atomicOr(s + KW - 1, (u64)bits << P::BPRES);
     }
     PGPU_DEV void consume_runs_b(const TableArgs& t, i64 base, bool (&sel)[4], u64 (&key)[4][KW], u64 (&cw)[4][NHA]) {
         const int lane = threadIdx.x & 31;
@@ -1281,9 +1321,9 @@ struct HashCtx {
 #pragma unroll 1
         for (int j0 = 0; j0 < nruns; j0 += 64) {
             RunB a, b;
-            run_issue_b(t, starts, nruns, j0 + lane, a);
+            run_issue_b(t, starts, nruns, j0 + lane, allow, a);
             const bool two = j0 + 32 < nruns;  // warp-uniform
-            if (two) run_issue_b(t, starts, nruns, j0 + 32 + lane, b);
+            if (two) run_issue_b(t, starts, nruns, j0 + 32 + lane, allow, b);
             run_resolve_b(t, wbase, allow, a);
             if (two) run_resolve_b(t, wbase, allow, b);
         }
@@ -1755,7 +1795,7 @@ PGPU_DEV void body_materialize_b(const TableArgs& t, const OutArgs<P::NO>& out, 
             if (!((pres >> j) & 1u)) continue;
             if (pos < out.capacity) {
                 u64 key[P::KWA];
-                bucket_join<P>(slot, j, key);
+                bucket_join<P>(t, slot, j, key);
                 P::emit(key, slot + P::KW + j * P::NW, out, pos, err);
             } else {
                 err |= PGPU_ERR_OUTPUT_FULL;

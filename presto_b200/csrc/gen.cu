@@ -5,7 +5,7 @@
 #include <thread>
 #include <vector>
 
-#include "../../include/prestogpu.h"
+#include "../../include/prestogpu_bench.h"
 #include "lineitem_gen.h"
 #include "tpch_dbgen.cuh"
 
@@ -253,6 +253,16 @@ pgpu_status pgpu_gen_lineitem_host(int32_t column, uint64_t seed, int64_t first_
     }
     for (auto& t : th) t.join();
     return PGPU_OK;
+}
+
+pgpu_status pgpu_memcpy_h2d(int32_t device, void* dev_dst, const void* host_src, size_t bytes) {
+    if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
+    return cudaMemcpy(dev_dst, host_src, bytes, cudaMemcpyHostToDevice) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
+}
+
+pgpu_status pgpu_memcpy_d2h(int32_t device, void* host_dst, const void* dev_src, size_t bytes) {
+    if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
+    return cudaMemcpy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
 }
 
 pgpu_status pgpu_flush_l2(int32_t device, void* dev_scratch, size_t bytes) {

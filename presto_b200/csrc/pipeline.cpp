@@ -54,6 +54,7 @@ struct TableArgs {
     uint64_t* faillog;
     uint64_t faillog_cap;
     uint64_t row_bias;
+    uint64_t bucket_off;
 };
 struct Scratch {
     uint32_t* err;
@@ -186,7 +187,7 @@ struct pgpu_pipeline {
     size_t partialsCap = 0;
     DeviceBuf tileStatus;
     DeviceBuf failLog;   // deferred rows of the current hash-aggregation chunk
-    uint64_t* hostScalars = nullptr;  // pinned: [0] out_count, [1..2] counters, [3] err
+    uint64_t* hostScalars = nullptr;  // pinned, 32 words: [0] out_count, [1..2] counters, [3] err, [4..12] key-clustering probe
 
     // table
     uint64_t* dSlots = nullptr;
@@ -195,6 +196,8 @@ struct pgpu_pipeline {
     // output is sized by). The same number for one-key-per-slot tables; a bucketed table claims one slot per 8 neighbouring keys.
     int64_t slotsKnown = 0, groupsKnown = 0, rowsSinceKnown = 0;
     enum { TABLE_UNDECIDED = 0, TABLE_PER_KEY = 1, TABLE_BUCKETS = 2 };
+    uint64_t bucketOff = 0;        // bucketed table: buckets are cut at 8n - bucketOff (chosen by the probe; PGPU_TUNE_BUCKET_OFF)
+    double bucketOccupancy = 8.0;  // keys per bucket the probe expects (table sizing)
     int tableMode = TABLE_UNDECIDED;  // decided by the first page (key clustering probe) or PGPU_TUNE_BUCKETS; survives pgpu_reset
 
     // staging + output
@@ -370,6 +373,7 @@ TableArgs tableOf(pgpu_pipeline* p) {
     t.faillog = (uint64_t*)p->failLog.ptr;
     t.faillog_cap = 0;
     t.row_bias = 0;
+    t.bucket_off = p->bucketOff;
     return t;
 }
 
@@ -502,15 +506,28 @@ pgpu_status decideTableMode(pgpu_pipeline* p, Variant* v, const DevPage& pg, Var
         const Type& t = p->plan->input[g.bucketKeyChannel];
         if (ca.values && !ca.ids && !ca.dvalues && !t.isVarWidth() && (t.width() == 4 || t.width() == 8)) {
             unsigned long long* dOut = (unsigned long long*)p->dState;  // 64 words of scratch the hash path does not use
-            CU(cudaMemsetAsync(dOut, 0, 16, p->stream));
+            CU(cudaMemsetAsync(dOut, 0, 72, p->stream));
             CU(keyClustering(p->stream, ca.values, t.width(), std::min<int64_t>(pg.rows, 1 << 16), dOut));
-            CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 16, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 72, cudaMemcpyDeviceToHost, p->stream));
             CU(cudaStreamSynchronize(p->stream));
-            CU(cudaMemsetAsync(dOut, 0, 16, p->stream));
+            CU(cudaMemsetAsync(dOut, 0, 72, p->stream));
             p->stats.kernel_launches++;
-            const uint64_t changes = p->hostScalars[4], near = p->hostScalars[5];
+            const uint64_t changes = p->hostScalars[4];
+            int best = 0;
+            for (int d = 1; d < 8; d++)
+                if (p->hostScalars[5 + d] > p->hostScalars[5 + best]) best = d;
+            const uint64_t near = p->hostScalars[5 + best];
             buckets = changes > 0 && near * 2 >= changes;
+            if (buckets) {
+                p->bucketOff = (uint64_t)best;
+                // a key change stays inside the bucket with probability near / changes: runs of 1 / (1 - that) keys per bucket
+                p->bucketOccupancy = std::min(8.0, std::max(1.0, (double)changes / (double)std::max<uint64_t>(changes - near, 1)));
+            }
         }
+    }
+    if (buckets && force && *force) {
+        if (const char* off = getenv("PGPU_TUNE_BUCKET_OFF")) p->bucketOff = (uint64_t)(atoi(off) & 7);
+        p->bucketOccupancy = 4.0;
     }
     p->tableMode = buckets ? pgpu_pipeline::TABLE_BUCKETS : pgpu_pipeline::TABLE_PER_KEY;
     p->stats.table_bucketed = buckets ? 1 : 0;
@@ -564,7 +581,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         const uint64_t reserve = flushReserve(p, v);
         if (!p->dSlots) {
             uint64_t cap = (uint64_t)((double)p->plan->expectedGroups / 0.6) + 1024;
-            if (g.buckets) cap = (uint64_t)((double)p->plan->expectedGroups / 8.0 / 0.5) + 1024;  // 8 keys per slot when the clusters are dense
+            if (g.buckets) cap = (uint64_t)((double)p->plan->expectedGroups / p->bucketOccupancy / 0.6) + 1024;  // keys per slot as the probe saw them
             cap = std::max<uint64_t>(cap, reserve * 4 + 4096);
             // key types that bound the number of groups (<= 1 M): size the table for the whole domain, once
             if (g.keyDomain > 0 && g.keyDomain <= (double)(1 << 20)) cap = std::max<uint64_t>(cap, (uint64_t)(g.keyDomain / 0.7) + reserve * 2 + 4096);
@@ -636,7 +653,9 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         uint64_t deferred = p->hostScalars[2];
         if (deferred == 0) return PGPU_OK;
         if (deferred > (uint64_t)n) return fail(p, PGPU_CUDA_ERROR, "internal: deferred-row log overflow");
-        uint64_t cap = std::max<uint64_t>(p->capacity * 2, (uint64_t)((double)(p->slotsKnown + (int64_t)deferred) / 0.6) + reserve * 4 + 4096);
+        // every deferred row of a one-key-per-slot table may be a new group; deferred rows of a bucketed table share slots
+        const double perSlot = g.buckets ? std::max(1.0, p->bucketOccupancy) * 2.0 : 1.0;
+        uint64_t cap = std::max<uint64_t>(p->capacity * 2, (uint64_t)(((double)p->slotsKnown + (double)deferred / perSlot) / 0.6) + reserve * 4 + 4096);
         st = growTable(p, v, cap);  // rehash re-counts the groups and clears the deferred counter
         if (st) return st;
         TableArgs t2 = tableOf(p);  // limit = none: the grown table holds every deferred row even if all are new groups
@@ -1375,7 +1394,10 @@ pgpu_status buildAggOutput(pgpu_pipeline* p) {
         if (!p->dSlots) {
             p->outRowsTotal = 0;
         } else {
-            pgpu_status st = refreshGroupCount(p, v, true);
+            // a bucketed table knows its groups only by counting presence bits. When the probe saw well-filled buckets the
+            // upper bound (8 per claimed bucket) is close enough to size the output with; the emit kernel reports the real count
+            const bool bounded = p->tableMode == pgpu_pipeline::TABLE_BUCKETS && p->bucketOccupancy >= 4.0;
+            pgpu_status st = refreshGroupCount(p, v, !bounded);
             if (st) return st;
             CU(cudaMemsetAsync(p->dOutCount, 0, 8, p->stream));  // the group count of a bucketed table went through it
             st = ensureOutBuffers(p, p->groupsKnown);
@@ -1389,9 +1411,14 @@ pgpu_status buildAggOutput(pgpu_pipeline* p) {
             st = launch(p, v->kEmit, grid, kThreads, 0, args);
             if (st) return st;
             p->outRowsTotal = p->groupsKnown;
+            if (bounded) {
+                CU(cudaMemcpyAsync(&p->hostScalars[0], p->dOutCount, 8, cudaMemcpyDeviceToHost, p->stream));
+                p->outRowsTotal = -1;  // read below
+            }
         }
     }
     CU(cudaStreamSynchronize(p->stream));
+    if (p->outRowsTotal < 0) p->outRowsTotal = p->groupsKnown = (int64_t)p->hostScalars[0];
     pgpu_status st = checkDeviceErrors(p);
     if (st) return st;
     p->outputReady = true;
@@ -1478,8 +1505,8 @@ pgpu_status pgpu_pipeline_create(const uint8_t* plan, size_t plan_len, int32_t d
         p->dOutCount = (uint64_t*)(s + 16);
         p->dCounters = (uint64_t*)(s + 32);
         p->dState = (uint64_t*)(s + 64);
-        if ((e = cudaMallocHost((void**)&p->hostScalars, 64)) != cudaSuccess) return cuFail(e, "cudaMallocHost");
-        memset(p->hostScalars, 0, 64);
+        if ((e = cudaMallocHost((void**)&p->hostScalars, 256)) != cudaSuccess) return cuFail(e, "cudaMallocHost");
+        memset(p->hostScalars, 0, 256);
     }
     // compile the default variant now: plan-time rejection (NOT_SUPPORTED / COMPILER_ERROR) happens here
     std::vector<ColSig> sig(p->plan->input.size());
@@ -1496,6 +1523,8 @@ pgpu_status pgpu_pipeline_create(const uint8_t* plan, size_t plan_len, int32_t d
         if (*force && atoi(force) != 0) {  // bucketed table from the start (also what build() uses to warm the kernel cache)
             p->tableMode = pgpu_pipeline::TABLE_BUCKETS;
             p->stats.table_bucketed = 1;
+            if (const char* off = getenv("PGPU_TUNE_BUCKET_OFF")) p->bucketOff = (uint64_t)(atoi(off) & 7);
+            p->bucketOccupancy = 4.0;  // no probe: a middling guess, the table grows when it is wrong
             p->haveLayout = false;
             st = getVariant(pp, sig, &v);
             if (st) {
@@ -1575,6 +1604,67 @@ pgpu_status pgpu_add_device_page(pgpu_pipeline* p, const pgpu_column* cols, int3
     if (!p) return PGPU_INVALID_ARGUMENT;
     pgpu_status st = addPageCommon(p, cols, ncols, rows, true, 0);
     return st ? st : updatePartialFill(p);
+}
+
+pgpu_status pgpu_reserve_input(pgpu_pipeline* p, const int32_t* encodings, const uint8_t* nullable, int32_t ncols, int64_t rows) {
+    if (!p || !encodings || !nullable) return PGPU_INVALID_ARGUMENT;
+    if (ncols != (int)p->plan->input.size()) return fail(p, PGPU_INVALID_ARGUMENT, "signature length differs from the plan's input channels");
+    std::vector<ColSig> sig(ncols);
+    for (int c = 0; c < ncols; c++) {
+        sig[c].encoding = encodings[c];
+        sig[c].nullable = nullable[c] != 0;
+    }
+    Variant* v = nullptr;
+    pgpu_status st = getVariant(p, sig, &v);  // compiles on first use
+    if (st || p->device < 0) return st;
+    CU(cudaSetDevice(p->device));
+    PendingPage& pd = p->pend;
+    if (pd.rows > 0 && (pd.key != sigKey(sig) || pd.rows + rows > pd.lay->capRows)) {
+        if ((st = flushPending(p))) return st;
+    }
+    if (pd.rows == 0) {  // the next page starts a super-page: its slot must be free
+        StageSlot* slot = nullptr;
+        if ((st = acquireSlot(p, &slot))) return st;
+    }
+    return PGPU_OK;
+}
+
+int32_t pgpu_is_blocked(const pgpu_pipeline* p) {
+    if (!p || p->device < 0 || !p->stream) return 0;
+    if (cudaSetDevice(p->device) != cudaSuccess) return 0;
+    const cudaError_t e = cudaStreamQuery(p->stream);
+    if (e == cudaErrorNotReady) return 1;
+    if (e != cudaSuccess) cudaGetLastError();
+    return 0;
+}
+
+namespace {
+struct UnblockedCall {
+    pgpu_callback fn;
+    void* user;
+};
+void CUDART_CB unblockedTrampoline(void* arg) {
+    UnblockedCall* c = (UnblockedCall*)arg;
+    c->fn(c->user);
+    delete c;
+}
+}  // namespace
+
+pgpu_status pgpu_on_unblocked(pgpu_pipeline* p, pgpu_callback fn, void* user) {
+    if (!p || !fn) return PGPU_INVALID_ARGUMENT;
+    if (p->device < 0) {
+        fn(user);
+        return PGPU_OK;
+    }
+    CU(cudaSetDevice(p->device));
+    UnblockedCall* c = new UnblockedCall{fn, user};
+    cudaError_t e = cudaLaunchHostFunc(p->stream, unblockedTrampoline, c);
+    if (e != cudaSuccess) {
+        delete c;
+        p->err = std::string("CUDA error: ") + cudaGetErrorString(e) + " at cudaLaunchHostFunc";
+        return PGPU_CUDA_ERROR;
+    }
+    return PGPU_OK;
 }
 
 // ---- pages in the reference's wire format -----------------------------------------------------------------------------------
@@ -2041,7 +2131,8 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
     *rows = n;
     p->outRowsServed += n;
     if (g.mode == KernelMode::COMPACT) {
-        p->outputReady = false;
+        // a page that passes more rows than max-output-rows goes out in several calls; needsInput stays false in between
+        if (p->outRowsServed >= p->outRowsTotal) p->outputReady = false;
     } else if (p->outRowsServed >= p->outRowsTotal) {
         p->outputReady = false;
         if (p->finishing) p->finished = true;
@@ -2294,16 +2385,6 @@ void pgpu_device_free(int32_t device, void* ptr) {
     if (!ptr) return;
     cudaSetDevice(device);
     cudaFree(ptr);
-}
-
-pgpu_status pgpu_memcpy_h2d(int32_t device, void* dev_dst, const void* host_src, size_t bytes) {
-    if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
-    return cudaMemcpy(dev_dst, host_src, bytes, cudaMemcpyHostToDevice) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
-}
-
-pgpu_status pgpu_memcpy_d2h(int32_t device, void* host_dst, const void* dev_src, size_t bytes) {
-    if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
-    return cudaMemcpy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
 }
 
 pgpu_status pgpu_partition_output_device(pgpu_pipeline* p, int32_t nparts, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols,

@@ -6,19 +6,23 @@ namespace {
 
 template <typename T>
 __global__ void k_key_clustering(const T* __restrict__ keys, long long n, unsigned long long* out) {
-    unsigned changes = 0, near = 0;
+    unsigned changes = 0, near[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (long long i = 1 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const long long a = (long long)keys[i - 1], b = (long long)keys[i];
         if (a != b) {
             changes++;
-            near += (a >> 3) == (b >> 3) ? 1u : 0u;
+#pragma unroll
+            for (int d = 0; d < 8; d++) near[d] += ((a + d) >> 3) == ((b + d) >> 3) ? 1u : 0u;
         }
     }
     changes = __reduce_add_sync(0xffffffffu, changes);
-    near = __reduce_add_sync(0xffffffffu, near);
+#pragma unroll
+    for (int d = 0; d < 8; d++) near[d] = __reduce_add_sync(0xffffffffu, near[d]);
     if ((threadIdx.x & 31) == 0) {
         if (changes) atomicAdd(out, (unsigned long long)changes);
-        if (near) atomicAdd(out + 1, (unsigned long long)near);
+#pragma unroll
+        for (int d = 0; d < 8; d++)
+            if (near[d]) atomicAdd(out + 1 + d, (unsigned long long)near[d]);
     }
 }
 

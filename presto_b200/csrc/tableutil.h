@@ -6,8 +6,9 @@
 namespace pgpu {
 
 // Clustering probe for the bucketed table (device/pgpu_device.cuh "bucketed slots"): over the first n (<= 65536) keys of an
-// integer key column, out[0] = positions whose key differs from its predecessor's, out[1] = those of them whose predecessor
-// lies in the same bucket of 8 (key >> 3 equal). `width` = 4 or 8 bytes per key. out must be zeroed by the caller.
+// integer key column, out[0] = positions whose key differs from its predecessor's, out[1 + d] (d = 0..7) = those of them whose
+// predecessor lies in the same bucket of 8 when buckets are cut at 8n - d ((key + d) >> 3 equal): clusters of 8 keys need not
+// start at a multiple of 8 (TPC-H order keys start at 8n + 1). `width` = 4 or 8 bytes per key. out[0..8] zeroed by the caller.
 cudaError_t keyClustering(cudaStream_t stream, const void* keys, int width, int64_t n, unsigned long long* out);
 
 }  // namespace pgpu

@@ -28,6 +28,19 @@ def test_library_exports_every_declared_symbol():
     assert declared == bound, "ctypes binding and header disagree: %s" % sorted(declared ^ bound)
 
 
+def test_bench_plumbing_lives_in_its_own_library():
+    """generators, synchronous copies and the L2 flush are not part of the drop-in boundary (include/prestogpu_bench.h,
+    libprestogpu_bench.so): the product library exports none of them"""
+    header = open(os.path.join(ROOT, "include", "prestogpu_bench.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(pgpu_[a-z0-9_]+)\s*\(", header))
+    assert declared == {s[0] for s in N.BENCH_SYMBOLS}
+    product, bench = ctypes.CDLL(N.LIB_PATH), ctypes.CDLL(N.BENCH_LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(bench, name), "libprestogpu_bench.so does not export %s" % name
+        assert not hasattr(product, name), "libprestogpu.so exports bench symbol %s" % name
+
+
 def test_no_device_means_zero_devices_not_an_error():
     L = N.lib()
     assert L.pgpu_device_count() >= 0

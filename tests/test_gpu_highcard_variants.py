@@ -155,8 +155,10 @@ def bucket_edge_pages():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("off", ["0", "7", "3"])
 @pytest.mark.parametrize("step", ["single", "partial_final"])
-def test_bucketed_table_edges(step):
+def test_bucketed_table_edges(step, off, monkeypatch):
+    monkeypatch.setenv("PGPU_TUNE_BUCKET_OFF", off)     # buckets cut at 8n - off: keys wrap around the ends of the BIGINT range
     pages = bucket_edge_pages()
     aggs = [Aggregation("sum", DOUBLE, 1, DOUBLE), Aggregation("count", BIGINT), Aggregation("max", DOUBLE, 1, DOUBLE)]
     single = plan_text([BIGINT, DOUBLE], step="single", groupByChannels=[0], aggregations=aggs, expectedGroups=NO_DIRECTORY)
@@ -171,7 +173,7 @@ def test_bucketed_table_edges(step):
                 op.close()
         else:
             partial = plan_text([BIGINT, DOUBLE], step="partial", groupByChannels=[0], aggregations=aggs, expectedGroups=NO_DIRECTORY,
-                                maxPartialGroups=3000)
+                                maxPartialGroups=400)
             pop = GpuPipelineOperator(partial, 0)
             try:
                 mid = toPages(pop, pages)
