@@ -56,8 +56,9 @@ final class PrestoGpuNative
 
     /**
      * pgpu_get_output — Operator.getOutput(). Returns null when there is no page now; otherwise
-     * [positionCount (Integer), then per channel: values array (long[] / int[] / byte[]), boolean[] valueIsNull or null,
-     * int[] offsets or null]. Arrays are fresh Java arrays (the library-owned pinned buffers are copied out).
+     * [positionCount (Integer), then per channel: values array (long[] / int[] / byte[]; long[2n] for long decimals; the byte[]
+     * payload of a var-width channel), boolean[] valueIsNull or null, int[] offsets (var-width) or null]. Arrays are fresh Java
+     * arrays (the library-owned pinned buffers are copied out).
      */
     static native Object[] getOutput(long handle);
 
@@ -66,4 +67,13 @@ final class PrestoGpuNative
 
     /** pgpu_last_error. */
     static native String lastError(long handle);
+
+    /** pgpu_is_blocked — true while device work queued by this operator is still running (Operator.isBlocked() is not done). */
+    static native boolean isBlocked(long handle);
+
+    /**
+     * pgpu_on_unblocked — runs {@code whenDone} (from a CUDA host-callback thread attached to the JVM for the call) once everything
+     * queued so far has completed: the completion of the ListenableFuture the operator hands to the Driver.
+     */
+    static native void onUnblocked(long handle, Runnable whenDone);
 }

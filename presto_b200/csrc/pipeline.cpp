@@ -441,6 +441,8 @@ pgpu_status refreshGroupCount(pgpu_pipeline* p, Variant* v = nullptr, bool exact
     CU(cudaMemcpyAsync(&p->hostScalars[1], p->dCounters, 16, cudaMemcpyDeviceToHost, p->stream));
     CU(cudaStreamSynchronize(p->stream));
     p->slotsKnown = (int64_t)p->hostScalars[1];
+    p->stats.table_slots_claimed = p->slotsKnown;
+    p->stats.bucket_offset = (int64_t)p->bucketOff;
     p->groupsKnown = !buckets ? p->slotsKnown : exactGroups ? (int64_t)p->hostScalars[0] : p->slotsKnown * 8;  // upper bound
     p->rowsSinceKnown = 0;
     return PGPU_OK;
@@ -488,6 +490,17 @@ struct DevPage {
 
 pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant** out);
 
+// the variant of the same page signature whose kernels work on the bucketed table (callers hold variants that were looked up
+// before the table format was decided: the rest of a chunked page, a pending super-page)
+pgpu_status bucketVariantOf(pgpu_pipeline* p, Variant* v, Variant** out) {
+    std::vector<ColSig> sig;
+    for (auto& kv : p->variants)
+        if (&kv.second == v) {
+            for (size_t i = 0; i + 1 < kv.first.size(); i += 2) sig.push_back(ColSig{kv.first[i] - '0', kv.first[i + 1] == 'n'});
+        }
+    return getVariant(p, sig, out);
+}
+
 // First page of a high-cardinality plan that qualifies for the bucketed table: look at how its keys arrive. When most key
 // changes stay inside a bucket of 8 neighbouring keys (l_orderkey: 7 of 8), 8 groups share one slot and one DRAM round trip;
 // keys that jump around (shuffled keys, hash-partitioned partial results) keep the one-key-per-slot table.
@@ -534,12 +547,7 @@ pgpu_status decideTableMode(pgpu_pipeline* p, Variant* v, const DevPage& pg, Var
     if (!buckets) return PGPU_OK;
     // same page signature, bucketed kernels; the slot layout changes with it (no table exists yet)
     p->haveLayout = false;
-    std::vector<ColSig> sig;
-    for (auto& kv : p->variants)
-        if (&kv.second == v) {
-            for (size_t i = 0; i + 1 < kv.first.size(); i += 2) sig.push_back(ColSig{kv.first[i] - '0', kv.first[i + 1] == 'n'});
-        }
-    return getVariant(p, sig, swapped);
+    return bucketVariantOf(p, v, swapped);
 }
 
 pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
@@ -566,6 +574,13 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         }
         void* args[] = {pa.data(), &sc};
         return launch(p, v->kPage, grid, kThreads, 0, args);
+    }
+    if (g.mode == KernelMode::AGG_HASH && p->tableMode == pgpu_pipeline::TABLE_BUCKETS && !g.buckets) {
+        Variant* swapped = nullptr;
+        pgpu_status st = bucketVariantOf(p, v, &swapped);
+        if (st) return st;
+        if (!swapped->gen.buckets) return fail(p, PGPU_CUDA_ERROR, "internal: no bucketed variant for this page signature");
+        return launchPageKernel(p, swapped, pg);
     }
     if (g.mode == KernelMode::AGG_HASH && !p->dSlots && p->tableMode == pgpu_pipeline::TABLE_UNDECIDED) {
         Variant* swapped = nullptr;
@@ -2315,6 +2330,7 @@ pgpu_status pgpu_reset(pgpu_pipeline* p) {
     p->stats = pgpu_stats{};
     p->stats.table_capacity = cap;
     p->stats.table_bucketed = bucketed;
+    p->stats.bucket_offset = (int64_t)p->bucketOff;
     p->err.clear();
     return PGPU_OK;
 }

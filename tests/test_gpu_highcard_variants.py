@@ -241,3 +241,29 @@ def test_variants_compile_without_gpu(runs, locb):
         plan, pages, _ = CASES[name]()
         _, _, src = run_variant(plan, pages[:1], runs, locb, device=-1)
         check_source(src, runs, locb, bucketable=name != "filtered_two_keys")
+
+
+@pytest.mark.gpu
+def test_table_format_decided_inside_a_chunked_device_page():
+    """a device page longer than one launch chunk (64 M rows): the clustering probe picks the bucketed table while the first chunk
+    is being launched; the remaining chunks must run the bucketed kernels too (size-independent checks: group count, sum of sums)"""
+    rows = 28 * 2_500_000      # 70 M rows, 17.5 M orders
+    old = os.environ.pop("PGPU_TUNE_BUCKETS", None)
+    dp = tpch.DevicePage(0, tpch.HC_DEVICE_SPEC, rows)
+    op = GpuPipelineOperator(tpch.highcard_plan(rows // 4), 0)
+    try:
+        op.addDeviceInput(dp.cols, 2, rows)
+        out = toPages(op, [])
+        st = op.stats()
+    finally:
+        op.close()
+        dp.free()
+        if old is not None:
+            os.environ["PGPU_TUNE_BUCKETS"] = old
+    assert st.table_bucketed == 1 and st.table_rehashes == 0
+    k = np.concatenate([p.blocks[0].values for p in out])
+    s = np.concatenate([p.blocks[1].values.view(np.float64) for p in out])
+    assert len(k) == rows // 4 and len(np.unique(k)) == rows // 4
+    assert st.table_slots_claimed * 8 == rows // 4                      # 8 neighbouring order keys per bucket
+    qty = tpch.host_column("quantity", 0, rows, rows)
+    assert float(s.sum()) == float(qty.sum())                           # integer-valued doubles: exact in any order
