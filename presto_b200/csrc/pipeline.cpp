@@ -510,9 +510,13 @@ pgpu_status decideTableMode(pgpu_pipeline* p, Variant* v, const DevPage& pg, Var
     const GenResult& g = v->gen;
     bool buckets = false;
     const char* force = getenv("PGPU_TUNE_BUCKETS");
-    if (!g.bucketsPossible) {
+    const bool probe = force && !strcmp(force, "auto");
+    if (!g.bucketsPossible || !force || !*force) {
+        // default: one key per slot. Measured on GROUP BY l_orderkey at sf100 (profiles/r02_summary.md): the bucketed table cuts
+        // the DRAM traffic per launch from 3.8x to 1.5x the input, but the kernel is bound by atomic round trips through L2, not
+        // by bytes, and ends up slower (27.0 vs 24.4 ms per pass) — it stays behind PGPU_TUNE_BUCKETS = 1 (always) / auto (probe)
         buckets = false;
-    } else if (force && *force) {
+    } else if (!probe) {
         buckets = atoi(force) != 0;
     } else if (g.bucketKeyChannel >= 0 && pg.rows >= 1024) {
         const ColArg& ca = pg.cols[g.bucketKeyChannel];
@@ -538,7 +542,7 @@ pgpu_status decideTableMode(pgpu_pipeline* p, Variant* v, const DevPage& pg, Var
             }
         }
     }
-    if (buckets && force && *force) {
+    if (buckets && !probe) {
         if (const char* off = getenv("PGPU_TUNE_BUCKET_OFF")) p->bucketOff = (uint64_t)(atoi(off) & 7);
         p->bucketOccupancy = 4.0;
     }
@@ -1535,7 +1539,9 @@ pgpu_status pgpu_pipeline_create(const uint8_t* plan, size_t plan_len, int32_t d
     if (!v->gen.bucketsPossible) {
         p->tableMode = pgpu_pipeline::TABLE_PER_KEY;
     } else if (const char* force = getenv("PGPU_TUNE_BUCKETS")) {
-        if (*force && atoi(force) != 0) {  // bucketed table from the start (also what build() uses to warm the kernel cache)
+        if (!strcmp(force, "auto")) {
+            // decided by the first page's keys
+        } else if (*force && atoi(force) != 0) {  // bucketed table from the start (also what build() uses to warm the kernel cache)
             p->tableMode = pgpu_pipeline::TABLE_BUCKETS;
             p->stats.table_bucketed = 1;
             if (const char* off = getenv("PGPU_TUNE_BUCKET_OFF")) p->bucketOff = (uint64_t)(atoi(off) & 7);

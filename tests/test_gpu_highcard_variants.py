@@ -117,9 +117,17 @@ def test_variant_equals_oracle(name, runs, locb):
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,bucketed", [("clustered", 1), ("shuffled", 0), ("filtered_int_key", 0)])
 def test_table_format_follows_the_key_clustering(name, bucketed):
-    """no knob set: the first page's keys decide (l_orderkey runs -> buckets of 8 neighbouring keys; random keys -> one key per slot)"""
+    """PGPU_TUNE_BUCKETS=auto: the first page's keys decide (l_orderkey runs -> buckets of 8 neighbouring keys; random keys -> one
+    key per slot). Without the knob the table is one key per slot (the measured default)."""
     plan, pages, nkeys, exp = expected_of(name)
     old = os.environ.pop("PGPU_TUNE_BUCKETS", None)
+    op = GpuPipelineOperator(plan, 0)
+    try:
+        assert_rows_equal_ignore_order(rows_of(toPages(op, pages)), exp, nkeys=nkeys, rtol=0.0)
+        assert op.stats().table_bucketed == 0
+    finally:
+        op.close()
+    os.environ["PGPU_TUNE_BUCKETS"] = "auto"
     try:
         op = GpuPipelineOperator(plan, 0)
         try:
@@ -131,6 +139,7 @@ def test_table_format_follows_the_key_clustering(name, bucketed):
         finally:
             op.close()
     finally:
+        os.environ.pop("PGPU_TUNE_BUCKETS", None)
         if old is not None:
             os.environ["PGPU_TUNE_BUCKETS"] = old
     assert_rows_equal_ignore_order(act, exp, nkeys=nkeys, rtol=0.0)
@@ -248,7 +257,8 @@ def test_table_format_decided_inside_a_chunked_device_page():
     """a device page longer than one launch chunk (64 M rows): the clustering probe picks the bucketed table while the first chunk
     is being launched; the remaining chunks must run the bucketed kernels too (size-independent checks: group count, sum of sums)"""
     rows = 28 * 2_500_000      # 70 M rows, 17.5 M orders
-    old = os.environ.pop("PGPU_TUNE_BUCKETS", None)
+    old = os.environ.get("PGPU_TUNE_BUCKETS")
+    os.environ["PGPU_TUNE_BUCKETS"] = "auto"
     dp = tpch.DevicePage(0, tpch.HC_DEVICE_SPEC, rows)
     op = GpuPipelineOperator(tpch.highcard_plan(rows // 4), 0)
     try:
@@ -258,6 +268,7 @@ def test_table_format_decided_inside_a_chunked_device_page():
     finally:
         op.close()
         dp.free()
+        os.environ.pop("PGPU_TUNE_BUCKETS", None)
         if old is not None:
             os.environ["PGPU_TUNE_BUCKETS"] = old
     assert st.table_bucketed == 1 and st.table_rehashes == 0
