@@ -284,6 +284,21 @@ pgpu_status pgpu_ipc_export(int32_t device, const void* dev_ptr, uint8_t* handle
 pgpu_status pgpu_ipc_open(int32_t device, const uint8_t* handle, void** mapped_base);
 pgpu_status pgpu_ipc_close(int32_t device, void* mapped_base);
 
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it). Decodes ONE nullable fixed-width block of the wire format
+ * (what pgpu_add_serialized_page does per such block: spi/block/LongArrayBlockEncoding.java:45-60 + EncoderUtil.java:33-70) with
+ * scratch memory that lives in a file-scope device array of the library instead of an allocation: `null_bits` = the (positions + 7) / 8
+ * bytes of the null bit stream (most significant bit first, 1 = NULL), `compact_values` = the non-null values only, `width` = 1 / 4 /
+ * 8 / 16 bytes per value -> values_out[positions] (zero at NULL positions), nulls_out[positions] (1 = NULL). All four are DEVICE
+ * pointers supplied by the caller (compact_values and values_out aligned to `width`); `stream` is a cudaStream_t (NULL = the default
+ * stream); the three kernels are queued on it and the call returns without waiting. Calls no cudaMalloc / cudaFree / allocating
+ * library routine. Limits: positions <= PGPU_EXPAND_STATIC_MAX_POSITIONS (larger counts are rejected with PGPU_INVALID_ARGUMENT and a
+ * text in pgpu_last_global_error()); every GPU that loads the library holds the 66 560-byte scratch array until exit; ALL calls on a
+ * device share it, so calls that overlap on the GPU (different streams without an ordering between them) race — serialise them. */
+#define PGPU_EXPAND_STATIC_MAX_POSITIONS 16777216 /* 2^24 positions = 16 384 blocks of 1024 */
+pgpu_status pgpu_expand_nulls_static(int32_t device, void* stream, const uint8_t* null_bits, int64_t positions, const void* compact_values,
+                                     int32_t width, void* values_out, uint8_t* nulls_out);
+
 /* Pinned host memory helpers (what the JNI shim stages heap arrays into). */
 void* pgpu_host_alloc(size_t bytes);
 void pgpu_host_free(void* ptr);

@@ -89,6 +89,7 @@ SYMBOLS = [
     ("pgpu_ipc_open", ctypes.c_int32, [ctypes.c_int32, ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]),
     ("pgpu_ipc_close", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p]),
     ("pgpu_partition_of", ctypes.c_int32, [ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_uint8), ctypes.POINTER(ctypes.c_int32), ctypes.c_int32, ctypes.c_int32]),
+    ("pgpu_expand_nulls_static", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]),
     ("pgpu_host_alloc", ctypes.c_void_p, [ctypes.c_size_t]),
     ("pgpu_host_free", None, [ctypes.c_void_p]),
     ("pgpu_device_alloc", ctypes.c_void_p, [ctypes.c_int32, ctypes.c_size_t]),

@@ -1465,6 +1465,11 @@ bool isPartialFlushDue(const pgpu_pipeline* p) {
 
 }  // namespace
 
+// for translation units that have no pipeline handle to hang an error text on (serde.cu: pgpu_expand_nulls_static)
+namespace pgpu {
+void setLastGlobalError(const std::string& m) { g_lastGlobalError = m; }
+}  // namespace pgpu
+
 // ================================================================================================ C ABI
 extern "C" {
 

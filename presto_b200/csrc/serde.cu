@@ -260,3 +260,65 @@ cudaError_t unpackNullBits(cudaStream_t stream, const uint8_t* bits, int64_t n, 
 }
 
 }  // namespace pgpu
+
+// ---- pgpu_expand_nulls_static: expandNulls with its scratch in a file-scope device array (no allocation) --------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it). The three launches are those of expandNulls above;
+// the per-block counts live in g_expandScratch instead of a caller / pipeline allocation. Every GPU that loads the library holds
+// the array (66 560 bytes) until exit. ALL calls on a device share it and it keeps the last call's contents: every word a call
+// reads is written by that same call first (k_live_counts writes counts[0 .. blocks), k_scan_counts writes counts[blocks]), so
+// nothing has to be cleared — but two calls that overlap on the GPU (different streams, no ordering between them) race on it.
+#include <mutex>
+#include <string>
+
+#include "../../include/prestogpu.h"
+
+namespace pgpu {
+void setLastGlobalError(const std::string& m);  // pipeline.cpp: the text pgpu_last_global_error() returns (thread-local)
+}
+
+namespace {
+constexpr int64_t kStaticMaxPositions = PGPU_EXPAND_STATIC_MAX_POSITIONS;
+constexpr int kStaticScratchWords = (int)(kStaticMaxPositions / pgpu::kSerdeBlockPositions) + 256;  // blocks + total, padded to 256-byte multiple
+static_assert((size_t)kStaticScratchWords >= (size_t)(kStaticMaxPositions / pgpu::kSerdeBlockPositions) + 1, "scratch too small for the stated maximum");
+static_assert(kStaticScratchWords * 4 % 256 == 0, "scratch size is a multiple of its alignment");
+
+static __device__ __align__(256) uint32_t g_expandScratch[kStaticScratchWords];
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_scratchMu;
+uint32_t* g_scratchAddr[kStaticMaxDevices];  // device address of g_expandScratch on device d (the symbol itself is a host-side stand-in)
+}  // namespace
+
+extern "C" pgpu_status pgpu_expand_nulls_static(int32_t device, void* stream, const uint8_t* null_bits, int64_t positions, const void* compact_values,
+                                                int32_t width, void* values_out, uint8_t* nulls_out) {
+    auto fail = [](pgpu_status st, const std::string& m) {
+        pgpu::setLastGlobalError("pgpu_expand_nulls_static: " + m);
+        return st;
+    };
+    if (device < 0 || device >= kStaticMaxDevices) return fail(PGPU_INVALID_ARGUMENT, "device index out of range");
+    if (positions < 0) return fail(PGPU_INVALID_ARGUMENT, "negative position count");
+    if (positions > kStaticMaxPositions)
+        return fail(PGPU_INVALID_ARGUMENT, "position count " + std::to_string(positions) + " exceeds the static scratch's maximum of " +
+                                               std::to_string(kStaticMaxPositions) + " (use pgpu_add_serialized_page, which sizes its own scratch)");
+    if (width != 1 && width != 4 && width != 8 && width != 16) return fail(PGPU_INVALID_ARGUMENT, "width must be 1, 4, 8 or 16 bytes");
+    if (positions == 0) return PGPU_OK;
+    if (!null_bits || !compact_values || !values_out || !nulls_out) return fail(PGPU_INVALID_ARGUMENT, "null argument");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(PGPU_CUDA_ERROR, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    uint32_t* scratch = nullptr;
+    {
+        // once per device, with that device current: the device address of the array
+        std::lock_guard<std::mutex> lk(g_scratchMu);
+        if (!g_scratchAddr[device]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_expandScratch);
+            if (e != cudaSuccess || !p) return fail(PGPU_CUDA_ERROR, std::string("cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            g_scratchAddr[device] = (uint32_t*)p;
+        }
+        scratch = g_scratchAddr[device];
+    }
+    e = pgpu::expandNulls((cudaStream_t)stream, null_bits, positions, compact_values, values_out, nulls_out, width, scratch);
+    if (e != cudaSuccess) return fail(PGPU_CUDA_ERROR, std::string("launch failed: ") + cudaGetErrorString(e));
+    return PGPU_OK;
+}

@@ -23,14 +23,3 @@ def _native_built():
     from presto_b200 import build as B
     B.build()
     yield
-
-
-# GPU cases added since the last visit to a B200 (profiles/r01g_pytest_gpu.log) run after everything that has already
-# passed there, so that under `-x` a surprise in a new case cannot hide the state of the proven ones.
-NEWEST_GPU_CASES = ("nullif_grid_", "simple_case_", "case_nullif_into_aggregation", "optest_", "test_gpu_parquet", "test_gpu_operators", "test_gpu_intermediate")
-
-
-def pytest_collection_modifyitems(config, items):
-    def newest(item):
-        return item.get_closest_marker("gpu") is not None and any(k in item.nodeid for k in NEWEST_GPU_CASES)
-    items.sort(key=newest)  # stable: everything else keeps its order
