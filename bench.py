@@ -935,8 +935,10 @@ def main():
         # the reference's CPU implementation of the path: Java, no JVM here -> the oracle port on all host cores
         if rank != 0:
             return
-        from __graft_entry__ import build
-        build()
+        # build what this arm needs without mapping the product library: the oracle, and libprestogpu_bench.so for the input rows
+        from presto_b200 import build as B
+        B.build()
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle")], check=True)
         wl = workload_def(headline_name, args.cpu_rows_per_core, args.sf * world if args.data == "dbgen" else None)
         per_core = args.cpu_rows_per_core
         vals = []

@@ -124,16 +124,28 @@ class _Lib:
         h = self.__dict__["_handle"]
         if any(name == b[0] for b in BENCH_SYMBOLS):
             if self.__dict__["_bench"] is None:
-                if not os.path.exists(BENCH_LIB_PATH):
-                    raise RuntimeError("presto_b200: %s is missing. Build it with `python -m presto_b200.build`." % BENCH_LIB_PATH)
-                b = ctypes.CDLL(BENCH_LIB_PATH)
-                for n, res, args in BENCH_SYMBOLS:
-                    fn = getattr(b, n)
-                    fn.restype = res
-                    fn.argtypes = args
-                self.__dict__["_bench"] = b
+                self.__dict__["_bench"] = bench_lib()
             return getattr(self.__dict__["_bench"], name)
         return getattr(h, name)
+
+
+_bench = None
+
+
+def bench_lib():
+    """libprestogpu_bench.so alone (generators, synchronous copies, L2 flush): what the CPU reference arm of bench.py uses to make
+    its input, so that it never maps the product library."""
+    global _bench
+    if _bench is None:
+        if not os.path.exists(BENCH_LIB_PATH):
+            raise RuntimeError("presto_b200: %s is missing. Build it with `python -m presto_b200.build`." % BENCH_LIB_PATH)
+        b = ctypes.CDLL(BENCH_LIB_PATH)
+        for n, res, args in BENCH_SYMBOLS:
+            fn = getattr(b, n)
+            fn.restype = res
+            fn.argtypes = args
+        _bench = b
+    return _bench
 
 
 def lib():

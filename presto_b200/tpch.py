@@ -75,7 +75,7 @@ def host_column(name: str, first_row: int, rows: int, total_rows: int, seed: int
     counter-based generator the device uses (csrc/lineitem_gen.h)."""
     n = rows + (1 if name == "iota_offsets" else 0)
     out = np.empty(n, dtype=_DT[name])
-    st = N.lib().pgpu_gen_lineitem_host(N.LI[name], seed, first_row, rows, total_rows, out.ctypes.data)
+    st = N.bench_lib().pgpu_gen_lineitem_host(N.LI[name], seed, first_row, rows, total_rows, out.ctypes.data)
     assert st == 0
     return out
 
@@ -122,13 +122,13 @@ _TPCH_NUMERIC = ("quantity", "extendedprice", "discount", "tax")
 
 
 def tpch_order_count(sf: float) -> int:
-    return int(N.lib().pgpu_tpch_order_count(float(sf)))
+    return int(N.bench_lib().pgpu_tpch_order_count(float(sf)))
 
 
 def tpch_rows(sf: float, first_order: int = 0, n_orders: int | None = None) -> int:
     n_orders = tpch_order_count(sf) - first_order if n_orders is None else n_orders
     r = ctypes.c_int64()
-    if N.lib().pgpu_tpch_lineitem_rows(float(sf), first_order, n_orders, ctypes.byref(r)):
+    if N.bench_lib().pgpu_tpch_lineitem_rows(float(sf), first_order, n_orders, ctypes.byref(r)):
         raise ValueError("order range [%d, %d) is outside scale factor %s" % (first_order, first_order + n_orders, sf))
     return r.value
 
@@ -143,7 +143,7 @@ def tpch_host_column(name: str, sf: float, first_order: int, n_orders: int, deci
         return np.arange(rows + 1, dtype=np.int32)
     out = np.empty(rows, dtype=_tpch_dtype(name, decimal))
     fmt = TPCH_DECIMAL_12_2 if decimal and name in _TPCH_NUMERIC else TPCH_NATIVE
-    st = N.lib().pgpu_tpch_lineitem_host(float(sf), first_order, n_orders, N.LI[name], fmt, rows, out.ctypes.data, None)
+    st = N.bench_lib().pgpu_tpch_lineitem_host(float(sf), first_order, n_orders, N.LI[name], fmt, rows, out.ctypes.data, None)
     assert st == 0, st
     return out
 
