@@ -1330,6 +1330,19 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     src << "    static constexpr bool BUCKETS = " << (res.buckets ? "true" : "false") << ";  // bucketed table: SLOTW words per bucket of 8 keys\n";
     src << "    static constexpr int BSLOTW = " << bslotw << ", BSH = " << (fields.empty() ? 0 : 8 * fields[0].byteOffset) << ", BPRES = 48;\n";
     src << "    static constexpr u64 BPMASK = 0xffull << BPRES;\n";
+    {
+        // range-aware exchange split (body_materialize_range): one integer grouping key in tagless one-key-per-slot tables
+        bool rangeOk = res.mode == KernelMode::AGG_HASH && tagless && !res.buckets && fields.size() == 1 && NW > 0 && fields[0].byteOffset < 7;
+        if (rangeOk) {
+            const TypeKind k0 = fields[0].type.kind;
+            rangeOk = k0 == TypeKind::BIGINT || k0 == TypeKind::INTEGER || k0 == TypeKind::DATE || (k0 == TypeKind::DECIMAL && fields[0].type.isShortDecimal());
+        }
+        res.rangeOk = rangeOk;
+        unsigned long long nullMask = 0;
+        if (rangeOk && fields[0].nullable) nullMask = 1ull << fields[0].nullBit;
+        src << "    static constexpr bool RANGE_OK = " << (rangeOk ? "true" : "false") << ";\n";
+        src << "    static constexpr u64 BNULLMASK = " << nullMask << "ull;  // key word 0: the grouping key is NULL\n";
+    }
     src << "    static constexpr bool BCASFIRST = " << (envInt("PGPU_TUNE_BCAS", 1) ? "true" : "false") << ";  // bucket leaders claim with one compare-and-swap, no load first\n";
     src << "    static constexpr int BKBITS = " << (fields.empty() ? 64 : std::min(64, 8 * fields[0].nbytes)) << ";  // width of the (first) key field\n";
     src << "    static constexpr int KOFF = " << (tagless ? 0 : 1) << ";  // first key word of a slot\n";
@@ -1613,6 +1626,10 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
         } else {
             src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots) { body_materialize<P>(t, out, sc, first_slot, nslots); }\n";
             src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_rehash(TableArgs from, TableArgs to, Scratch sc) { body_rehash<P>(from, to, sc); }\n";
+            if (res.rangeOk) {
+                src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit_range(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots, RangeArgs rg) { body_materialize_range<P>(t, out, sc, first_slot, nslots, rg); }\n";
+                src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_keyrange(TableArgs t, i64* out) { body_key_range<P>(t, out); }\n";
+            }
         }
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";
     }

@@ -1675,8 +1675,69 @@ PGPU_DEV void body_compact(const PageArgs<P::NC>& a, const OutArgs<P::NO>& out, 
 }
 
 // ------------------------------------------------------------------------------------------------ table output / rehash
+// ---- range-aware split of a table's groups (multi-GPU exchange, csrc/comm.inc) -----------------------------------------------
+// Ranks own row ranges of the input; when the grouping key is clustered (l_orderkey) a rank's keys lie in a range that overlaps
+// its neighbours' only at the boundaries. A group whose key lies in NO other rank's [lo, hi] exists on this rank alone: it needs no
+// exchange and no second hash build, its final value is its partial state finalised. RangeArgs carries the other ranks' key
+// ranges; mode 1 keeps the private groups, mode 2 the shared ones (NULL keys are always shared). Plans with P::RANGE_OK only
+// (one integer grouping key).
+struct RangeArgs {
+    i64 lo[64], hi[64];  // key ranges of the OTHER ranks (lo > hi: that rank has no keys)
+    int n;
+    int mode;            // 1 = private groups only, 2 = shared groups only
+};
+template <class P>
+PGPU_DEV i64 range_key_value(const u64* key) {  // the key field, sign-extended
+    const u64 k = bk_extract<P>(key);
+    if constexpr (P::BKBITS < 64) return ((i64)(k << (64 - P::BKBITS))) >> (64 - P::BKBITS);
+    else return (i64)k;
+}
+template <class P>
+PGPU_DEV bool range_pass(const u64* key, const RangeArgs& r) {
+    bool shared = (key[0] & P::BNULLMASK) != 0ull;
+    const i64 v = range_key_value<P>(key);
+#pragma unroll 1
+    for (int i = 0; i < r.n; i++) shared |= (v >= r.lo[i]) & (v <= r.hi[i]);
+    return r.mode == 1 ? !shared : shared;
+}
+// min / max of the non-NULL keys in the table -> out[0] (atomicMin, initialised to INT64_MAX), out[1] (atomicMax, INT64_MIN)
+template <class P>
+PGPU_DEV void body_key_range(const TableArgs& t, i64* out) {
+    i64 lo = 0x7fffffffffffffffll, hi = -0x7fffffffffffffffll - 1;
+    for (u64 s = (u64)blockIdx.x * blockDim.x + threadIdx.x; s < t.capacity; s += (u64)gridDim.x * blockDim.x) {
+        const u64* slot = t.slots + s * P::SLOTW;
+        if (!slot_live<P>(slot)) continue;
+        u64 key[P::KW > 0 ? P::KW : 1];
+        slot_key<P>(slot, key);
+        if (key[0] & P::BNULLMASK) continue;
+        const i64 v = range_key_value<P>(key);
+        lo = v < lo ? v : lo;
+        hi = v > hi ? v : hi;
+    }
+#pragma unroll
+    for (int m = 16; m >= 1; m >>= 1) {
+        const i64 ol = (i64)shfl_xor_u64((u64)lo, m), oh = (i64)shfl_xor_u64((u64)hi, m);
+        lo = ol < lo ? ol : lo;
+        hi = oh > hi ? oh : hi;
+    }
+    if ((threadIdx.x & 31) == 0 && lo <= hi) {
+        atomicMin(reinterpret_cast<long long*>(out), (long long)lo);
+        atomicMax(reinterpret_cast<long long*>(out + 1), (long long)hi);
+    }
+}
+
+template <class P, bool RANGE>
+PGPU_DEV void body_materialize_impl(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, i64 first_slot, i64 nslots, const RangeArgs* rg);
 template <class P>
 PGPU_DEV void body_materialize(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, i64 first_slot, i64 nslots) {
+    body_materialize_impl<P, false>(t, out, sc, first_slot, nslots, nullptr);
+}
+template <class P>
+PGPU_DEV void body_materialize_range(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, i64 first_slot, i64 nslots, const RangeArgs& rg) {
+    body_materialize_impl<P, true>(t, out, sc, first_slot, nslots, &rg);
+}
+template <class P, bool RANGE>
+PGPU_DEV void body_materialize_impl(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, i64 first_slot, i64 nslots, const RangeArgs* rg) {
     // A block takes blockDim * 4 consecutive slots per iteration, counts its live slots with one block scan and reserves
     // their output rows with ONE atomic on the output counter (a counter bumped per warp serialises on its L2 slice:
     // 214 M slots / 32 were 6.7 M same-address atomics, the whole cost of the kernel at 150 M groups).
@@ -1695,6 +1756,11 @@ PGPU_DEV void body_materialize(const TableArgs& t, const OutArgs<P::NO>& out, co
 #pragma unroll
         for (int k = 0; k < SPT; k++) {
             live[k] = s + k < end && slot_live<P>(t.slots + (u64)(s + k) * P::SLOTW);
+            if (RANGE && live[k]) {
+                u64 fk[P::KW > 0 ? P::KW : 1];
+                slot_key<P>(t.slots + (u64)(s + k) * P::SLOTW, fk);
+                live[k] = range_pass<P>(fk, *rg);
+            }
             cnt += live[k] ? 1u : 0u;
         }
         u32 incl = cnt;

@@ -68,6 +68,10 @@ struct OutCol {
     void* values;
     uint8_t* nulls;
 };
+struct RangeArgs {
+    int64_t lo[64], hi[64];
+    int32_t n, mode;
+};
 struct GatherArgs {
     const uint64_t* hdr;
     int32_t npages;
@@ -86,7 +90,7 @@ thread_local std::string g_lastGlobalError;
 struct Variant {
     GenResult gen;
     cudaLibrary_t lib = nullptr;
-    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr, kGather = nullptr;
+    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr, kGather = nullptr, kEmitRange = nullptr, kKeyRange = nullptr;
     int blocksPerSM = 1;
     int stagedStages = 0;      // stages of the shared-memory ring (0 = staged variant unavailable)
     size_t stagedSmem = 0;
@@ -204,6 +208,10 @@ struct pgpu_pipeline {
     StageSlot slots[3];
     int nextSlot = 0;
     PendingPage pend;
+    // multi-GPU exchange, range-aware split (comm.inc): the same plan as a SINGLE step — its emit kernel finalises groups of THIS
+    // (PARTIAL-step) pipeline's table that no other rank can hold; rows the exchange appends to a FINAL pipeline's output
+    pgpu_pipeline* singleTwin = nullptr;
+    int64_t extraOutRows = 0;
     std::map<std::string, StageLayout> stageLayouts;
     size_t stageTargetBytes = 64u << 20;  // PGPU_STAGE_MB
     // output columns live in ONE device allocation (values / nulls of column c at outOffV[c] / outOffN[c]) so that a
@@ -320,6 +328,10 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
                 CU(cudaLibraryGetKernel(&v.kRehash, v.lib, "pgpu_k_rehash"));
                 CU(cudaLibraryGetKernel(&v.kReplay, v.lib, "pgpu_k_replay"));
                 if (v.gen.buckets) CU(cudaLibraryGetKernel(&v.kCount, v.lib, "pgpu_k_count"));
+                if (v.gen.rangeOk) {
+                    CU(cudaLibraryGetKernel(&v.kEmitRange, v.lib, "pgpu_k_emit_range"));
+                    CU(cudaLibraryGetKernel(&v.kKeyRange, v.lib, "pgpu_k_keyrange"));
+                }
             }
             if (v.gen.mode != KernelMode::COMPACT && p->plan->hasAgg && inputIsIntermediate(p->plan->step))
                 CU(cudaLibraryGetKernel(&v.kGather, v.lib, "pgpu_k_gather"));
@@ -1419,7 +1431,7 @@ pgpu_status buildAggOutput(pgpu_pipeline* p) {
             pgpu_status st = refreshGroupCount(p, v, !bounded);
             if (st) return st;
             CU(cudaMemsetAsync(p->dOutCount, 0, 8, p->stream));  // the group count of a bucketed table went through it
-            st = ensureOutBuffers(p, p->groupsKnown);
+            st = ensureOutBuffers(p, p->groupsKnown + p->extraOutRows);  // extraOutRows: rows the exchange appends behind the table's groups
             if (st) return st;
             std::vector<unsigned char> oa = outArgsBlock(p);
             Scratch sc = scratchOf(p);
@@ -1573,6 +1585,7 @@ pgpu_status pgpu_pipeline_create(const uint8_t* plan, size_t plan_len, int32_t d
 
 void pgpu_pipeline_destroy(pgpu_pipeline* p) {
     if (!p) return;
+    if (p->singleTwin) pgpu_pipeline_destroy(p->singleTwin);
     if (p->device >= 0) {
         cudaSetDevice(p->device);
         if (p->stream) cudaStreamSynchronize(p->stream);
@@ -2329,6 +2342,7 @@ pgpu_status pgpu_sync(pgpu_pipeline* p) {
 pgpu_status pgpu_reset(pgpu_pipeline* p) {
     if (!p) return PGPU_INVALID_ARGUMENT;
     p->pend.rows = 0;  // rows waiting in the staging slot are dropped with the rest of the state
+    p->extraOutRows = 0;
     if (p->device >= 0) {
         CU(cudaSetDevice(p->device));
         resetAggState(p);

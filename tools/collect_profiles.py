@@ -1,7 +1,8 @@
 #!/usr/bin/env python
-"""Copy the judged summaries of the last tools/gpu_check.sh visit from gpurun_out/ (scratch) into profiles/ (tracked):
-bench JSON lines, the ncu launch list, ncu details pages, raw DRAM-traffic metrics and the SASS hot-spot summary.
-Usage: python tools/collect_profiles.py <tag>   (e.g. r01c)"""
+"""Copy the judged summaries of the last evidence visit (tools/gpu_trip_r2i.sh) from gpurun_out/ (scratch) into profiles/ (tracked):
+bench JSON lines, ncu launch lists, per capture the details page, selected raw metrics and the SASS hot-spot summary, and
+profiles/traffic.json — measured DRAM bytes per row of every workload's dominant kernel, which bench.py reads for `roofline.traffic`.
+Usage: python tools/collect_profiles.py <tag>   (e.g. r02)"""
 import csv
 import json
 import os
@@ -13,41 +14,114 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G, P = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
 tag = sys.argv[1]
 os.makedirs(P, exist_ok=True)
-rows = []
-for w in ("q1", "q6", "highcard", "highcard_shuffled", "q1dict", "ref"):
-    src = os.path.join(G, "bench_%s.json" % w)
+
+# rows of the captured (steady-state, full-chunk) launch: hash-aggregation pages are launched in chunks of kHashChunkRows = 64 Mi rows
+# (csrc/pipeline.cpp), rounded down to whole staged tiles (Q1: 1920 rows, dictionary Q1: 960); a global aggregation is one launch
+CHUNK = 64 << 20
+LAUNCH_ROWS = {"q1": CHUNK // 1920 * 1920, "q1dict": CHUNK // 960 * 960, "q6": 600_037_902, "highcard": CHUNK, "highcard_shuffled": CHUNK,
+               "highcard_buckets": CHUNK}
+ALG_BYTES = {"q1": 46, "q1dict": 32, "q6": 28, "highcard": 16, "highcard_shuffled": 16, "highcard_buckets": 16}
+KEEP = ("Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread",
+        "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic", "smsp__inst_executed.sum",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sector_hit_rate.pct", "lts__t_sectors_srcunit_tex_op_atom.sum", "lts__t_sectors_srcunit_tex_op_red.sum",
+        "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio")
+
+
+def copy(name, dst=None):
+    src = os.path.join(G, name)
     if os.path.exists(src) and os.path.getsize(src):
-        shutil.copy(src, os.path.join(P, "%s_bench_%s.json" % (tag, w)))
-        d = json.loads(open(src).read().strip().splitlines()[-1])
-        rows.append((w, d))
-if os.path.exists(os.path.join(G, "launches_q1.csv")):
-    shutil.copy(os.path.join(G, "launches_q1.csv"), os.path.join(P, "%s_q1_launches.csv" % tag))
-if os.path.exists(os.path.join(G, "launches_highcard.csv")):
-    shutil.copy(os.path.join(G, "launches_highcard.csv"), os.path.join(P, "%s_highcard_launches.csv" % tag))
-for rep, name in (("q1_full", "q1_staged"), ("hc_full", "highcard"), ("q6_full", "q6"), ("q1dict_full", "q1dict_staged")):
-    f = os.path.join(G, rep + ".ncu-rep")
-    if not os.path.exists(f):
+        shutil.copy(src, os.path.join(P, "%s_%s" % (tag, dst or name)))
+        return True
+    return False
+
+
+for f in ("bench_default.json", "bench_ref.json", "bench_highcard_buckets.json", "bench_highcard_buckets_casfirst.json", "randtable.txt",
+          "launches_q1.csv", "launches_highcard.csv", "ingest_serialized.json"):
+    copy(f)
+for t in (16, 8, 4, 2, 1):
+    copy("ingest_t%d.json" % t)
+
+traffic = {}
+peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+lines = []
+for name in ("q1", "q6", "q1dict", "highcard", "highcard_shuffled", "highcard_buckets", "highcard_emit"):
+    rep = os.path.join(G, name + "_full.ncu-rep")
+    if not os.path.exists(rep):
         continue
-    det = subprocess.run(["ncu", "-i", f, "--page", "details"], stdout=subprocess.PIPE, text=True).stdout
+    det = subprocess.run(["ncu", "-i", rep, "--page", "details"], stdout=subprocess.PIPE, text=True).stdout
     open(os.path.join(P, "%s_%s_ncu_details.txt" % (tag, name)), "w").write(det)
-    raw = subprocess.run(["ncu", "-i", f, "--page", "raw", "--csv"], stdout=subprocess.PIPE, text=True).stdout
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=subprocess.PIPE, text=True).stdout
     r = list(csv.reader(raw.splitlines()))
-    keep = ("Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread",
-            "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic", "smsp__inst_executed.sum",
-            "sm__warps_active.avg.pct_of_peak_sustained_active", "dram__throughput.avg.pct_of_peak_sustained_elapsed")
+    vals = {}
     with open(os.path.join(P, "%s_%s_ncu_raw.txt" % (tag, name)), "w") as out:
         for i, h in enumerate(r[0]):
-            if h in keep:
+            if h in KEEP:
                 out.write("%s [%s] = %s\n" % (h, r[1][i], r[2][i]))
-    hot = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_hot.py"), f], stdout=subprocess.PIPE, text=True).stdout
+                vals[h] = (r[1][i], r[2][i])
+    hot = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_hot.py"), rep], stdout=subprocess.PIPE, text=True).stdout
     open(os.path.join(P, "%s_%s_ncu_hot.txt" % (tag, name)), "w").write(hot)
+
+    def to_bytes(key):
+        unit, v = vals.get(key, ("byte", "0"))
+        scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}.get(unit, 1)
+        return float(v.replace(",", "")) * scale
+
+    def to_ms(key):
+        unit, v = vals.get(key, ("ms", "0"))
+        scale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(unit, 1.0)
+        return float(v.replace(",", "")) * scale
+
+    if name in LAUNCH_ROWS:
+        dram = to_bytes("dram__bytes_read.sum") + to_bytes("dram__bytes_write.sum")
+        ms = to_ms("gpu__time_duration.sum")
+        rows = LAUNCH_ROWS[name]
+        traffic[name] = {"dram_bytes_per_row": dram / rows, "dram_bytes_per_launch": dram, "launch_rows": rows, "launch_ms_under_ncu": ms,
+                         "algorithmic_bytes_per_row": ALG_BYTES[name], "ratio_to_algorithmic": dram / rows / ALG_BYTES[name],
+                         "dram_gbs_under_ncu": dram / ms / 1e6 if ms else None,
+                         "source": "profiles/%s_%s_ncu_raw.txt (ncu --set full --clock-control none, one steady-state launch)" % (tag, name)}
+        lines.append("| %s | %.0f M | %.3f | %.2f | %.2f | %.2f | %.0f | %.2f |" % (name, rows / 1e6, ms, dram / 1e9, dram / rows, dram / rows / ALG_BYTES[name],
+                                                                                 dram / ms / 1e6, dram / ms / 1e6 / peak))
+with open(os.path.join(P, "traffic.json"), "w") as f:
+    json.dump(traffic, f, indent=1, sort_keys=True)
+    f.write("\n")
+
 with open(os.path.join(P, "%s_summary.md" % tag), "w") as out:
-    out.write("| workload | ms/step | rows/s | GB/s (algorithmic) | kernel roofline frac | e2e rows/s | launches/step |\n|---|---|---|---|---|---|---|\n")
-    for w, d in rows:
-        if d.get("impl") == "reference":
-            out.write("| CPU oracle port, %d cores (Q1) | %.1f | %.3g | | | | |\n" % (d["cpu_baseline"]["cores"], d["ms_per_step"], d["value"]))
-            continue
+    src = os.path.join(G, "bench_default.json")
+    if os.path.exists(src) and os.path.getsize(src):
+        d = json.loads(open(src).read().strip().splitlines()[-1])
+        out.write("## bench.py default line (1 x B200; every record verified against the CPU oracle on a prefix of the timed rows)\n\n")
+        out.write("| workload | ms/step | rows/s | kernel ms/step | roofline frac | e2e rows/s (1 M-row pageable pages) | e2e / H2D ceiling | verified rows | CPU port rows/s (cores) |\n|---|---|---|---|---|---|---|---|---|\n")
+        recs = [("q1 (headline)", d)] + list((d.get("configs") or {}).items())
+        for name, v in recs:
+            if "error" in v:
+                out.write("| %s | error: %s |\n" % (name, v["error"]))
+                continue
+            e, c = v.get("e2e") or {}, v.get("cpu_baseline") or {}
+            out.write("| %s | %.3f | %.4g | %.3f | %.3f | %s | %s | %s %s | %s |\n" % (
+                name, v["ms_per_step"], v["value"], v["roofline"]["kernel_ms_per_step"], v["roofline"]["frac"],
+                ("%.4g" % e["value"]) if e else "", ("%.2f" % e["frac_of_h2d_ceiling"]) if e.get("frac_of_h2d_ceiling") else "",
+                v.get("verified"), v.get("verified_rows"), ("%.4g (%d)" % (c["value"], c["cores"])) if c else ""))
         e = d.get("e2e") or {}
-        out.write("| %s | %.2f | %.3g | %.0f | %.3f | %s | %d |\n" % (w, d["ms_per_step"], d["value"], d["gb_per_s"], d["roofline"]["frac"],
-                                                                    ("%.3g" % e["value"]) if e else "", d["gpu_launches"] // d["steps"]))
+        out.write("\nQ1 end to end: H2D ceiling %.1f GB/s; 64 K-row pages %.4g rows/s; wire format %.4g rows/s; caller-pinned single page (ceiling of the path) %.4g rows/s; CPU port single thread %.4g rows/s.\n" % (
+            e.get("h2d_ceiling_gbs", 0), e.get("variants", {}).get("page_rows_65536", {}).get("value", 0), e.get("variants", {}).get("serialized_pages", {}).get("value", 0),
+            e.get("ceiling_pinned_single_page", {}).get("value", 0), (d.get("cpu_baseline") or {}).get("single_thread_value", 0)))
+    out.write("\n## ncu, one steady-state launch per workload (DRAM bytes are cold-cache and serialised: ratios matter, not absolute times)\n\n")
+    out.write("| kernel of | launch rows | ms under ncu | DRAM GB | DRAM B/row | x algorithmic | DRAM GB/s | of %.0f GB/s |\n|---|---|---|---|---|---|---|---|\n" % peak)
+    out.write("\n".join(lines) + "\n")
+    for extra, title in (("bench_highcard_buckets.json", "bucketed table, load-then-CAS leaders"), ("bench_highcard_buckets_casfirst.json", "bucketed table, CAS-first leaders")):
+        src = os.path.join(G, extra)
+        if os.path.exists(src) and os.path.getsize(src):
+            v = json.loads(open(src).read().strip().splitlines()[-1])
+            out.write("\nGROUP BY l_orderkey, %s (PGPU_TUNE_BUCKETS=1): %.3f ms/step, kernel %.3f ms/step.\n" % (title, v["ms_per_step"], v["roofline"]["kernel_ms_per_step"]))
+    rt = os.path.join(G, "randtable.txt")
+    if os.path.exists(rt):
+        out.write("\n## random 32-byte slot updates into an 8.6 GB table (tools/microbench/randtable.cu): the floor under shuffled keys\n\n```\n" + open(rt).read() + "```\n")
+    out.write("\n## ingest thread sweep (tools/ingest_bench.py, Q1, 128 M rows, pageable pages through pgpu_add_page)\n\n| copy threads | page rows | rows/s | GB/s | H2D ceiling GB/s |\n|---|---|---|---|---|\n")
+    for t in (16, 8, 4, 2, 1):
+        src = os.path.join(G, "ingest_t%d.json" % t)
+        if os.path.exists(src) and os.path.getsize(src):
+            v = json.loads(open(src).read().strip().splitlines()[-1])
+            for r_ in v.get("add_page", []):
+                out.write("| %d | %d | %.4g | %.1f | %.1f |\n" % (t, r_["page_rows"], r_["rows_per_s"], r_["gb_per_s"], v["h2d_ceiling_gbs"]))
 print(open(os.path.join(P, "%s_summary.md" % tag)).read())
