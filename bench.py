@@ -603,6 +603,7 @@ def exchange_and_final(op, final, small, repart, tdev, state):
         repart.exchange(op, final)                  # device-side exchange; FINAL is left finishing
         state["result_rows"] = drain_output(final, to_host=small)
         state["exchange_bytes"] = repart.sent_bytes
+        state["private_groups"] = repart.private_groups
     elif small:
         frame = X.pack_output(op)                                       # waits for the shard's kernels, drains the partial page
         frames = X.all_gather_frames(frame, device=tdev)                # one NCCL all-gather of a 32 KB frame per rank
@@ -689,7 +690,7 @@ def run_device_steps(args, wl, device, dist, steps, warmup):
     op.setTiming(False)
     info = dict(dev_ms=dev_ms, wall_s=wall, launches=nl, clocks=clocks, kern_ms=kern_ms, kern_launches=kern_launches,
                 kern_steps=ksteps, result_rows=state["result_rows"], table_capacity=op.stats().table_capacity,
-                exchange_bytes=state["exchange_bytes"])
+                exchange_bytes=state["exchange_bytes"], private_groups=state.get("private_groups", 0))
     if repart is not None and not hasattr(repart, "exchange"):
         repart.close()
     if final is not None:
@@ -880,7 +881,8 @@ def run_workload(args, name, device, dist, headline):
     if world > 1:
         small = name in ("q1", "q1dict", "q6")
         rec["exchange"] = {"shape": ("gather: push kernel stores the partial rows into every rank's inbox over NVLink, FINAL gather kernel merges them; no host round trip (pgpu_exchange_partial)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if small else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory, pgpu_exchange_partial)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),
-                           "bytes_sent_per_rank_per_step": info["exchange_bytes"]}
+                           "bytes_sent_per_rank_per_step": info["exchange_bytes"],
+                           "groups_finalised_in_place_per_rank": info.get("private_groups", 0)}
     host = None
     if not args.no_e2e:
         if not headline and not args.e2e_rows:

@@ -272,6 +272,14 @@ pgpu_status pgpu_comm_barrier(pgpu_comm* c);
  * *rows_received = rows this rank's FINAL step consumed (-1: known on the device only, gather shape); *bytes_sent = bytes that
  * crossed NVLink on this rank's behalf. Either may be NULL. */
 pgpu_status pgpu_exchange_partial(pgpu_comm* c, pgpu_pipeline* partial, pgpu_pipeline* final_pipeline, int64_t* rows_received, int64_t* bytes_sent);
+/* Range-aware split of the repartition shape (plans with ONE integer grouping key; PGPU_TUNE_RANGE_SPLIT=0 turns it off): every
+ * rank publishes the [min, max] of its partial keys; a group whose key lies in no other rank's range exists on this rank alone, so it
+ * skips the exchange and the second hash build and is finalised straight out of the partial table (by the same plan compiled as a
+ * SINGLE step), appended behind the FINAL pipeline's own groups. With row-range shards of a table clustered on the key (l_orderkey)
+ * only the boundary groups move; with keys spread over all ranks everything is exchanged as before. Every group still comes out
+ * exactly once across the ranks, but the output is then not partitioned by key hash (no consumer may rely on an order:
+ * InMemoryHashAggregationBuilder.java:309-312 / SURVEY.md 8(b)). Returns the groups the last exchange finalised in place. */
+int64_t pgpu_comm_private_groups(const pgpu_comm* c);
 
 /* Peer access over NVLink / NVSwitch for one-process-per-GPU deployments (cudaIpc*). The owner exports the allocation
  * that contains dev_ptr (`handle`, PGPU_IPC_HANDLE_BYTES bytes, plus dev_ptr's byte offset inside it); a peer process maps it

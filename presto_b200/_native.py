@@ -85,6 +85,7 @@ SYMBOLS = [
     ("pgpu_comm_last_error", ctypes.c_char_p, [_P]),
     ("pgpu_comm_barrier", ctypes.c_int32, [_P]),
     ("pgpu_exchange_partial", ctypes.c_int32, [_P, _P, _P, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]),
+    ("pgpu_comm_private_groups", ctypes.c_int64, [_P]),
     ("pgpu_ipc_export", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_ipc_open", ctypes.c_int32, [ctypes.c_int32, ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]),
     ("pgpu_ipc_close", ctypes.c_int32, [ctypes.c_int32, ctypes.c_void_p]),

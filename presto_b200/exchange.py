@@ -48,6 +48,7 @@ class Comm:
         self.world, self.rank, self.device = world, rank, device
         self.recv_rows = 0
         self.sent_bytes = 0
+        self.private_groups = 0
 
     def _check(self, st: int):
         if st != N.OK:
@@ -58,6 +59,7 @@ class Comm:
         rows, sent = ctypes.c_int64(), ctypes.c_int64()
         self._check(self._lib.pgpu_exchange_partial(self._h, partial._h, final._h, ctypes.byref(rows), ctypes.byref(sent)))
         self.recv_rows, self.sent_bytes = rows.value, sent.value
+        self.private_groups = int(self._lib.pgpu_comm_private_groups(self._h))   # finalised in place by the range-aware split
         return rows.value
 
     run = exchange   # the name the older Python transports used

@@ -77,7 +77,8 @@ def _unique(tag):
     return "pgpu_test_%s_%d_%d" % (tag, os.getpid(), time.time_ns() % 1_000_000_000)
 
 
-def test_exchange_one_rank_repartition_equals_single():
+def test_exchange_one_rank_repartition_equals_single(monkeypatch):
+    monkeypatch.setenv("PGPU_TUNE_RANGE_SPLIT", "0")       # the plain repartition shape (the range-aware split is tested below)
     total = 400_000
     pages = [tpch.highcard_page(0, total // 2, total), tpch.highcard_page(total // 2, total // 2, total)]
     single = run_gpu(tpch.highcard_plan(1000), pages)
@@ -307,3 +308,150 @@ def test_exchange_gather_two_processes():
     single = run_gpu(tpch.q1_plan(), [tpch.q1_page(0, total, total)])
     for _, rows, _ in results:
         assert_rows_equal_ignore_order(rows, single, nkeys=2, rtol=sequential_bound(total))
+
+
+# ---- range-aware split of the repartition shape -----------------------------------------------------------------------------
+def test_range_split_one_rank_finalises_everything_in_place():
+    """world 1: no other rank holds any key, so every group is private: no partition pass, no FINAL hash build"""
+    total = 400_000
+    pages = [tpch.highcard_page(0, total // 2, total), tpch.highcard_page(total // 2, total // 2, total)]
+    single = run_gpu(tpch.highcard_plan(1000), pages)
+    partial = GpuPipelineOperator(tpch.highcard_plan(REPARTITION, "partial"), 0)
+    final = GpuPipelineOperator(FINAL_HC(REPARTITION), 0)
+    comm = X.Comm(1, 0, 0, _unique("rs1"))
+    try:
+        for step in range(2):
+            partial.reset()
+            final.reset()
+            for p in pages:
+                partial.addInput(p)
+            partial.finish()
+            assert comm.exchange(partial, final) == 0               # nothing went through the exchange
+            assert comm.private_groups == len(single)
+            assert final.stats().table_capacity == 0                # FINAL never built a table
+            assert_rows_equal_ignore_order(drain(final), single, nkeys=1)
+    finally:
+        comm.close()
+        partial.close()
+        final.close()
+
+
+def _range_split_worker(rank, world, name, total, q):
+    """arg `total` < 0: shuffled keys (every rank's range covers the others': nearly everything is shared)"""
+    shuffled = total < 0
+    total = abs(total)
+    partial = final = comm = None
+    try:
+        per = total // world
+        partial = GpuPipelineOperator(tpch.highcard_plan(REPARTITION, "partial"), 0)
+        final = GpuPipelineOperator(FINAL_HC(REPARTITION), 0)
+        comm = X.Comm(world, rank, 0, name)
+        rows = []
+        for step in range(3):
+            partial.reset()
+            final.reset()
+            # a cut in the middle of an order: the boundary order's rows lie on both ranks
+            partial.addInput(tpch.highcard_page(rank * per, per, total, shuffled=shuffled))
+            partial.finish()
+            comm.exchange(partial, final)
+            rows = drain(final)
+        q.put((rank, rows, comm.private_groups))
+    except BaseException:
+        import traceback
+        q.put((rank, traceback.format_exc(), -1))
+        raise
+    finally:
+        if comm is not None:
+            comm.close()
+        for op in (partial, final):
+            if op is not None:
+                op.close()
+
+
+@pytest.mark.parametrize("shuffled", [False, True])
+def test_range_split_two_processes(shuffled):
+    """clustered keys: each rank finalises its own orders in place, only the orders around the cut are exchanged;
+    shuffled keys: the ranges overlap, (nearly) everything takes the exchange. Either way every group comes out exactly once."""
+    world, total = 2, 200_002                                      # 100 001 rows per rank: the cut falls inside a 28-row block
+    results = _spawn(_range_split_worker, world, _unique("rs2"), -total if shuffled else total)
+    per = total // world
+    single = run_gpu(tpch.highcard_plan(1000), [tpch.highcard_page(r * per, per, total, shuffled=shuffled) for r in range(world)])
+    got = [row for _, rows, _ in results for row in rows]
+    assert_rows_equal_ignore_order(got, single, nkeys=1, rtol=1e-12)   # exactly once each: a duplicate group would fail the pairing
+    private = [p for _, _, p in results]
+    if shuffled:
+        assert sum(private) < len(single) // 100
+    else:
+        assert all(p > 0 for p in private) and sum(private) >= len(single) - 16
+
+
+def _null_key_worker(rank, world, name, total, q):
+    from presto_b200.spi import INTEGER, IntArrayBlock
+    partial = final = comm = None
+    try:
+        aggs = [Aggregation("sum", DOUBLE, 1, DOUBLE), Aggregation("count", BIGINT), Aggregation("max", DOUBLE, 1, DOUBLE)]
+        pplan = plan_text([INTEGER, DOUBLE], step="partial", groupByChannels=[0], aggregations=aggs, expectedGroups=REPARTITION)
+        fplan = plan_text([INTEGER, BIGINT, DOUBLE, BIGINT, DOUBLE], step="final", groupByChannels=[0],
+                          aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE), Aggregation("count", BIGINT, 3, BIGINT), Aggregation("max", DOUBLE, 4, DOUBLE)],
+                          expectedGroups=REPARTITION)
+        partial, final = GpuPipelineOperator(pplan, 0), GpuPipelineOperator(fplan, 0)
+        comm = X.Comm(world, rank, 0, name)
+        partial.addInput(_null_key_page(rank, total))
+        partial.finish()
+        comm.exchange(partial, final)
+        q.put((rank, drain(final), comm.private_groups))
+    except BaseException:
+        import traceback
+        q.put((rank, traceback.format_exc(), -1))
+        raise
+    finally:
+        if comm is not None:
+            comm.close()
+        for op in (partial, final):
+            if op is not None:
+                op.close()
+
+
+def _null_key_page(rank, n):
+    """nullable INTEGER key (sign-extended 32-bit field behind a null byte): rank 0 holds negative keys up to 10, rank 1 keys from
+    -5 upwards, both hold NULL keys: [-5, 10] and NULL are shared, the rest is private"""
+    from presto_b200.spi import INTEGER, IntArrayBlock, Page, LongArrayBlock
+    rng = np.random.default_rng(40 + rank)
+    k = rng.integers(-3000, 11, n) if rank == 0 else rng.integers(-5, 4000, n)
+    knull = (rng.random(n) < 0.05).astype(np.uint8)
+    v = rng.integers(1, 100, n).astype(np.float64)
+    vnull = (rng.random(n) < 0.2).astype(np.uint8)
+    return Page(IntArrayBlock(INTEGER, k, knull), LongArrayBlock(DOUBLE, v, vnull))
+
+
+def test_range_split_null_and_negative_keys():
+    from presto_b200.spi import INTEGER
+    world, n = 2, 60_000
+    results = _spawn(_null_key_worker, world, _unique("rs3"), n)
+    aggs = [Aggregation("sum", DOUBLE, 1, DOUBLE), Aggregation("count", BIGINT), Aggregation("max", DOUBLE, 1, DOUBLE)]
+    single = plan_text([INTEGER, DOUBLE], step="single", groupByChannels=[0], aggregations=aggs, expectedGroups=REPARTITION)
+    exp = run_oracle(single, [_null_key_page(r, n) for r in range(world)])
+    got = [row for _, rows, _ in results for row in rows]
+    assert_rows_equal_ignore_order(got, exp, nkeys=1, rtol=0.0)       # integer-valued doubles: exact
+    assert sum(1 for r in got if r[0] is None) == 1                    # the NULL group of both ranks was merged, not emitted twice
+    private = dict((rank, p) for rank, _, p in results)
+    assert private[0] > 2000 and private[1] > 3000                     # keys below -5 / above 10
+
+
+def test_range_split_can_be_turned_off(monkeypatch):
+    monkeypatch.setenv("PGPU_TUNE_RANGE_SPLIT", "0")
+    total = 200_000
+    pages = [tpch.highcard_page(0, total, total)]
+    single = run_gpu(tpch.highcard_plan(1000), pages)
+    partial = GpuPipelineOperator(tpch.highcard_plan(REPARTITION, "partial"), 0)
+    final = GpuPipelineOperator(FINAL_HC(REPARTITION), 0)
+    comm = X.Comm(1, 0, 0, _unique("rs0"))
+    try:
+        partial.addInput(pages[0])
+        partial.finish()
+        assert comm.exchange(partial, final) == len(single) and comm.private_groups == 0
+        assert_rows_equal_ignore_order(drain(final), single, nkeys=1)
+    finally:
+        comm.close()
+        partial.close()
+        final.close()
