@@ -1340,6 +1340,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
         res.rangeOk = rangeOk;
         unsigned long long nullMask = 0;
         if (rangeOk && fields[0].nullable) nullMask = 1ull << fields[0].nullBit;
+        res.rangeNullable = nullMask != 0;
         src << "    static constexpr bool RANGE_OK = " << (rangeOk ? "true" : "false") << ";\n";
         src << "    static constexpr u64 BNULLMASK = " << nullMask << "ull;  // key word 0: the grouping key is NULL\n";
     }
@@ -1629,6 +1630,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
             if (res.rangeOk) {
                 src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit_range(TableArgs t, OutArgs<P::NO> out, Scratch sc, i64 first_slot, i64 nslots, RangeArgs rg) { body_materialize_range<P>(t, out, sc, first_slot, nslots, rg); }\n";
                 src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_keyrange(TableArgs t, i64* out) { body_key_range<P>(t, out); }\n";
+                src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit_probe(TableArgs t, OutArgs<P::NO> out, Scratch sc, ProbeArgs pa) { body_emit_probe<P>(t, out, sc, pa); }\n";
             }
         }
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";

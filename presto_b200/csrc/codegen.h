@@ -50,6 +50,7 @@ struct GenResult {
     // bucketed table (8 neighbouring keys of one integer key field per slot; device/pgpu_device.cuh "bucketed slots")
     bool bucketsPossible = false;  // the plan qualifies: high cardinality, one integer key, run compaction fits
     bool buckets = false;          // this source was generated for the bucketed table: SLOTW = words per BUCKET
+    bool rangeNullable = false;    // ... and that key may be NULL (the NULL group is always exchanged)
     bool rangeOk = false;          // one integer grouping key: the exchange may split groups by key range (pgpu_k_emit_range / pgpu_k_keyrange)
     int bucketKeyChannel = -1;     // input channel the key is read from as it is (-1: the key is computed), for the clustering probe
 };

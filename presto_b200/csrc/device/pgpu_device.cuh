@@ -1726,6 +1726,38 @@ PGPU_DEV void body_key_range(const TableArgs& t, i64* out) {
     }
 }
 
+// Shared groups when the overlap with the other ranks' ranges is narrow (row-range shards of a clustered table: the boundary
+// orders): instead of scanning the whole table for them, look every key of the overlap intervals up. `iv` = disjoint intervals,
+// start[i] = candidates before interval i; the NULL-key group is candidate number start[n] when probe_null is set.
+struct ProbeArgs {
+    i64 lo[64], hi[64], start[65];
+    int n;
+    int probe_null;
+};
+template <class P>
+PGPU_DEV void body_emit_probe(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, const ProbeArgs& pa) {
+    u32 err = 0, nins = 0;
+    const i64 total = pa.start[pa.n] + (pa.probe_null ? 1 : 0);
+    for (i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (i64)gridDim.x * blockDim.x) {
+        u64 key[P::KW > 0 ? P::KW : 1];
+#pragma unroll
+        for (int i = 0; i < P::KW; i++) key[i] = 0ull;
+        if (idx == pa.start[pa.n]) {
+            key[0] = P::BNULLMASK;
+        } else {
+            int i = 0;
+            while (i + 1 < pa.n && idx >= pa.start[i + 1]) i++;
+            bk_insert<P>(key, (u64)(pa.lo[i] + (idx - pa.start[i])));
+        }
+        const u64* s = table_upsert<P::KW, P::SLOTW, P::TAGLESS>(t, key, hash_key<P::KW>(key), false, nins);  // look-up only
+        if (!s) continue;
+        const i64 pos = (i64)atomicAdd(sc.out_count, 1ull);
+        if (pos < out.capacity) P::emit(key, s + P::KOFF + P::KW, out, pos, err);
+        else err |= PGPU_ERR_OUTPUT_FULL;
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
 template <class P, bool RANGE>
 PGPU_DEV void body_materialize_impl(const TableArgs& t, const OutArgs<P::NO>& out, const Scratch& sc, i64 first_slot, i64 nslots, const RangeArgs* rg);
 template <class P>

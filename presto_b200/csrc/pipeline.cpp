@@ -72,6 +72,10 @@ struct RangeArgs {
     int64_t lo[64], hi[64];
     int32_t n, mode;
 };
+struct ProbeArgs {
+    int64_t lo[64], hi[64], start[65];
+    int32_t n, probe_null;
+};
 struct GatherArgs {
     const uint64_t* hdr;
     int32_t npages;
@@ -90,7 +94,7 @@ thread_local std::string g_lastGlobalError;
 struct Variant {
     GenResult gen;
     cudaLibrary_t lib = nullptr;
-    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr, kGather = nullptr, kEmitRange = nullptr, kKeyRange = nullptr;
+    cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr, kGather = nullptr, kEmitRange = nullptr, kKeyRange = nullptr, kEmitProbe = nullptr;
     int blocksPerSM = 1;
     int stagedStages = 0;      // stages of the shared-memory ring (0 = staged variant unavailable)
     size_t stagedSmem = 0;
@@ -212,6 +216,7 @@ struct pgpu_pipeline {
     // (PARTIAL-step) pipeline's table that no other rank can hold; rows the exchange appends to a FINAL pipeline's output
     pgpu_pipeline* singleTwin = nullptr;
     int64_t extraOutRows = 0;
+    int64_t tableSizeHint = 0;  // groups to size a not yet allocated table for instead of the plan's expected-groups (FINAL behind a range-split exchange)
     std::map<std::string, StageLayout> stageLayouts;
     size_t stageTargetBytes = 64u << 20;  // PGPU_STAGE_MB
     // output columns live in ONE device allocation (values / nulls of column c at outOffV[c] / outOffN[c]) so that a
@@ -331,6 +336,7 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
                 if (v.gen.rangeOk) {
                     CU(cudaLibraryGetKernel(&v.kEmitRange, v.lib, "pgpu_k_emit_range"));
                     CU(cudaLibraryGetKernel(&v.kKeyRange, v.lib, "pgpu_k_keyrange"));
+                    CU(cudaLibraryGetKernel(&v.kEmitProbe, v.lib, "pgpu_k_emit_probe"));
                 }
             }
             if (v.gen.mode != KernelMode::COMPACT && p->plan->hasAgg && inputIsIntermediate(p->plan->step))
@@ -611,7 +617,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         // grows the table (rehash) and replays exactly those rows. Nothing is dropped, nothing is over-allocated.
         const uint64_t reserve = flushReserve(p, v);
         if (!p->dSlots) {
-            uint64_t cap = (uint64_t)((double)p->plan->expectedGroups / 0.6) + 1024;
+            uint64_t cap = (uint64_t)((double)(p->tableSizeHint > 0 ? p->tableSizeHint : p->plan->expectedGroups) / 0.6) + 1024;
             if (g.buckets) cap = (uint64_t)((double)p->plan->expectedGroups / p->bucketOccupancy / 0.6) + 1024;  // keys per slot as the probe saw them
             cap = std::max<uint64_t>(cap, reserve * 4 + 4096);
             // key types that bound the number of groups (<= 1 M): size the table for the whole domain, once

@@ -11,7 +11,8 @@ rank, world, dev = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(o
 torch.cuda.set_device(dev)
 td.init_process_group("nccl", device_id=torch.device("cuda", dev))
 rows = int(sys.argv[1]) if len(sys.argv) > 1 else 600_037_902
-wl = B.workload_def("q1", rows)
+name = sys.argv[2] if len(sys.argv) > 2 else "q1"     # q1 | q6 | highcard | highcard_shuffled; PGPU_TRACE_EXCHANGE=1 adds the library's phases
+wl = B.workload_def(name, rows)
 dp = tpch.DevicePage(dev, wl["spec"], rows, first_row=rank * rows, total_rows=rows * world)
 op = GpuPipelineOperator(wl["plan"]("partial"), dev)
 fin = GpuPipelineOperator(B.final_plan_for(wl, None), dev)
@@ -29,7 +30,7 @@ for it in range(13):
         op.sync(); t = lap("partial kernels (sync)", t)
     fin.reset(); t = lap("final.reset", t)
     comm.exchange(op, fin); t = lap("exchange (enqueue)", t)
-    n = B.drain_output(fin, True); t = lap("final drain (sync + D2H)", t)
+    n = B.drain_output(fin, name in ("q1", "q6")); t = lap("final drain (sync + output)", t)
 td.barrier()
 if rank == 0:
     print("N=%d rows/rank=%d result rows %d; ms per step:" % (world, rows, n), {k: round(v * 100, 3) for k, v in acc.items()}, "total", round(sum(acc.values()) * 100, 3))
