@@ -8,6 +8,8 @@
  */
 package io.trino.operator.gpu;
 
+import com.google.common.util.concurrent.ListenableFuture;
+import com.google.common.util.concurrent.SettableFuture;
 import io.trino.operator.DriverContext;
 import io.trino.operator.Operator;
 import io.trino.operator.OperatorContext;
@@ -31,12 +33,14 @@ public class GpuPipelineOperator
         private final int operatorId;
         private final PlanNodeId planNodeId;
         private final byte[] plan;          // plan text produced by GpuPlanTranslator from RowExpressions + aggregation spec
+        private final List<Type> inputTypes;
         private final List<Type> outputTypes;
         private final int device;
         private boolean closed;
 
-        public GpuPipelineOperatorFactory(int operatorId, PlanNodeId planNodeId, byte[] plan, List<Type> outputTypes, int device)
+        public GpuPipelineOperatorFactory(int operatorId, PlanNodeId planNodeId, byte[] plan, List<Type> inputTypes, List<Type> outputTypes, int device)
         {
+            this.inputTypes = requireNonNull(inputTypes, "inputTypes is null");
             this.operatorId = operatorId;
             this.planNodeId = requireNonNull(planNodeId, "planNodeId is null");
             this.plan = requireNonNull(plan, "plan is null");
@@ -52,7 +56,7 @@ public class GpuPipelineOperator
         {
             checkState(!closed, "Factory is already closed");
             OperatorContext operatorContext = driverContext.addOperatorContext(operatorId, planNodeId, GpuPipelineOperator.class.getSimpleName());
-            return new GpuPipelineOperator(operatorContext, PrestoGpuNative.create(plan, device), outputTypes);
+            return new GpuPipelineOperator(operatorContext, PrestoGpuNative.create(plan, device), inputTypes, outputTypes);
         }
 
         @Override
@@ -64,19 +68,36 @@ public class GpuPipelineOperator
         @Override
         public OperatorFactory duplicate()
         {
-            return new GpuPipelineOperatorFactory(operatorId, planNodeId, plan, outputTypes, device);
+            return new GpuPipelineOperatorFactory(operatorId, planNodeId, plan, inputTypes, outputTypes, device);
         }
     }
 
     private final OperatorContext operatorContext;
+    private final List<Type> inputTypes;
     private final List<Type> outputTypes;
     private long handle;
 
-    private GpuPipelineOperator(OperatorContext operatorContext, long handle, List<Type> outputTypes)
+    private GpuPipelineOperator(OperatorContext operatorContext, long handle, List<Type> inputTypes, List<Type> outputTypes)
     {
         this.operatorContext = requireNonNull(operatorContext, "operatorContext is null");
         this.handle = handle;
+        this.inputTypes = inputTypes;
         this.outputTypes = outputTypes;
+    }
+
+    /**
+     * Operator.isBlocked() (Operator.java:24-35): while device work queued by this operator is still running, getOutput() would
+     * have to wait for it; instead of blocking the Driver thread the operator hands out a future that a CUDA host callback completes.
+     */
+    @Override
+    public ListenableFuture<Void> isBlocked()
+    {
+        if (handle == 0 || !PrestoGpuNative.isBlocked(handle)) {
+            return NOT_BLOCKED;
+        }
+        SettableFuture<Void> done = SettableFuture.create();
+        PrestoGpuNative.onUnblocked(handle, () -> done.set(null));
+        return done;
     }
 
     @Override
@@ -95,7 +116,7 @@ public class GpuPipelineOperator
     public void addInput(Page page)
     {
         checkState(needsInput(), "Operator does not need input");
-        GpuPageMarshaller.addPage(handle, page);    // getLoadedBlock() per channel, raw arrays -> PrestoGpuNative.addPage
+        GpuPageMarshaller.addPage(handle, page, inputTypes);    // getLoadedBlock() per channel, raw arrays -> PrestoGpuNative.addPage
     }
 
     @Override

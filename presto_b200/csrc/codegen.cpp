@@ -27,9 +27,10 @@ namespace {
 // defaults of the high-cardinality knobs (PGPU_TUNE_RUNS / PGPU_TUNE_LOCB override them: bench sweeps, A/B parity tests).
 // Measured on GROUP BY l_orderkey at sf100 (profiles/r01g_summary.md): run compaction 28.8 -> 24.5 ms per pass, locality-aware
 // placement 28.8 -> 70 ms (sparse keys packed side by side turn linear probing into long chains). Run compaction is the
-// default for the SINGLE step, the one the A/B parity suite covers on the GPU; PARTIAL / FINAL keep the per-thread path
-// until they have the same coverage.
+// default for the steps that read raw rows (SINGLE, PARTIAL: 23.2 -> 19.4 ms for the PARTIAL pass of the 2-GPU run); FINAL /
+// INTERMEDIATE inputs are partial states, one row per key and source, where there are no runs to fold.
 constexpr int kDefaultRunsSingleStep = 1;
+constexpr int kDefaultRunsPartialStep = 1;
 constexpr int kDefaultRunsOtherSteps = 0;
 constexpr int kDefaultLocBits = 0;
 int envInt(const char* name, int dflt) {
@@ -1255,7 +1256,7 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     // consecutive slots
     const int runsBytes = 8 * ((KW + NHA) * 128 * 8 + 256);
     const bool highCard = res.mode == KernelMode::AGG_HASH && !res.useDir && tagless;
-    const bool runs = highCard && runsBytes <= 48 * 1024 && envInt("PGPU_TUNE_RUNS", plan.step == Step::SINGLE ? kDefaultRunsSingleStep : kDefaultRunsOtherSteps) != 0;
+    const bool runs = highCard && runsBytes <= 48 * 1024 && envInt("PGPU_TUNE_RUNS", plan.step == Step::SINGLE ? kDefaultRunsSingleStep : plan.step == Step::PARTIAL ? kDefaultRunsPartialStep : kDefaultRunsOtherSteps) != 0;
     if (runs) res.smemBytes = runsBytes;
     // bucketed table: one integer key (so that "the 3 low bits" means neighbouring keys), two spare bytes in the last key word
     // (presence byte + occupied mark), run compaction available (the bucket path is built on it, whatever the step)

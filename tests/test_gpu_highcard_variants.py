@@ -278,3 +278,33 @@ def test_table_format_decided_inside_a_chunked_device_page():
     assert st.table_slots_claimed * 8 == rows // 4                      # 8 neighbouring order keys per bucket
     qty = tpch.host_column("quantity", 0, rows, rows)
     assert float(s.sum()) == float(qty.sum())                           # integer-valued doubles: exact in any order
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("runs", [0, 1])
+@pytest.mark.parametrize("name", ["clustered", "shuffled", "filtered_int_key"])
+def test_partial_step_variants_feed_final(name, runs):
+    """the PARTIAL step with and without run compaction (its default since round 2), several partial flushes, merged by a FINAL
+    step: equal to the oracle's SINGLE-step answer bit for bit"""
+    plan, pages, nkeys, exp = expected_of(name)
+    partial = plan.replace("(step single)", "(step partial)").rstrip().rstrip(")") + " (options (max-partial-groups 30000)))"
+    with variant(runs, 0):
+        pop = GpuPipelineOperator(partial, 0)
+        try:
+            mid = toPages(pop, pages)
+            assert ("RUNS = true" in pop.generatedSource()) == bool(runs)
+            assert len(mid) >= 2
+        finally:
+            pop.close()
+    if name == "filtered_int_key":      # sum(double) -> (count, sum); count(*) -> count
+        fplan = plan_text([INTEGER, BIGINT, DOUBLE, BIGINT], step="final", groupByChannels=[0],
+                          aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE), Aggregation("count", BIGINT, 3, BIGINT)], expectedGroups=NO_DIRECTORY)
+    else:
+        fplan = plan_text([BIGINT, BIGINT, DOUBLE], step="final", groupByChannels=[0], aggregations=[Aggregation("sum", DOUBLE, 1, DOUBLE)],
+                          expectedGroups=NO_DIRECTORY)
+    fop = GpuPipelineOperator(fplan, 0)
+    try:
+        act = rows_of(toPages(fop, mid))
+    finally:
+        fop.close()
+    assert_rows_equal_ignore_order(act, exp, nkeys=nkeys, rtol=0.0)
