@@ -95,6 +95,10 @@ def gather_variants():
 
 
 if __name__ == "__main__":
+    # start from an empty cache: whatever is in it afterwards is exactly what the current sources compile to (stale cubins of
+    # earlier device-library versions would only travel to the GPU box as dead weight)
+    import shutil
+    shutil.rmtree(os.path.join(ROOT, "presto_b200", "_kernel_cache"), ignore_errors=True)
     before = len(os.listdir(os.path.join(ROOT, "presto_b200", "_kernel_cache"))) if os.path.isdir(os.path.join(ROOT, "presto_b200", "_kernel_cache")) else 0
     for spec in ["", "PGPU_TUNE_BUCKETS=1"] + sys.argv[1:]:
         env = dict(kv.split("=") for kv in spec.split(",") if kv)
