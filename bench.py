@@ -179,6 +179,25 @@ def h2d_ceiling(device, mb=512, reps=6):
     return reps * n / (e0.elapsed_time(e1) / 1e3) / 1e9
 
 
+def host_copy_ceiling(mb=256, seconds=0.4):
+    """pageable -> pinned through the library's own staging copy (worker pool, non-temporal stores), GB/s: what the host memory
+    system gives the ingest path before any byte crosses PCIe"""
+    import numpy as np
+    import torch
+    from presto_b200 import _native as N
+    n = mb << 20
+    src = np.ones(n, dtype=np.uint8)
+    dst = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    L = N.bench_lib()
+    L.pgpu_bench_host_copy(dst.data_ptr(), src.ctypes.data, n)
+    t0 = time.perf_counter()
+    reps = 0
+    while time.perf_counter() - t0 < seconds:
+        L.pgpu_bench_host_copy(dst.data_ptr(), src.ctypes.data, n)
+        reps += 1
+    return reps * n / (time.perf_counter() - t0) / 1e9
+
+
 class HostTable:
     """The rank's shard as a Trino worker holds it: one ordinary (pageable) numpy array per block array, cut into pages of
     page_rows positions. The bytes are the device columns copied back, so host pages and device page hold identical rows."""
@@ -732,14 +751,21 @@ def run_e2e(args, wl, device, dp, dist, steps, full):
     host = HostTable(device, wl, dp, rows)
     single = world == 1
     small = wl["name"] in ("q1", "q1dict", "q6")
+    def sync_ranks():
+        if world > 1:
+            import torch.distributed as td
+            td.barrier()
+
+    sync_ranks()                                  # every rank measures its ceilings while all the others measure theirs
     ceiling = h2d_ceiling(device)
-    if world > 1:
-        import torch.distributed as td
-        td.barrier()
+    sync_ranks()
+    copy_ceiling = host_copy_ceiling()
+    sync_ranks()
     rec = {"unit": "rows/s", "config": {"page_rows": args.page_rows, "pinned": False, "host_memory": "pageable numpy arrays, one per block array; pages are consecutive slices",
                                         "entry_point": "pgpu_add_page(flags=0)", "copy_threads": int(os.environ.get("PGPU_COPY_THREADS", "0")) or "library default",
                                         "rows_per_gpu": rows},
-           "h2d_ceiling_gbs": ceiling}
+           "h2d_ceiling_gbs": ceiling, "host_copy_ceiling_gbs": copy_ceiling,
+           "ceilings": "measured concurrently on all ranks: pinned cudaMemcpy H2D, and the staging copy alone (pageable -> pinned, no GPU); the leg needs both for every byte"}
     if single:
         op = GpuPipelineOperator(wl["plan"]("single"), device)
         r = time_host_pages(op, host.pages(args.page_rows), steps, to_host=True)
@@ -747,6 +773,7 @@ def run_e2e(args, wl, device, dp, dist, steps, full):
                    rows_per_step=r["rows"], steps=steps, seconds_per_step=r["seconds_per_step"], super_pages_per_step=r["super_pages_per_step"],
                    launches_per_step=r["launches_per_step"], gb_per_s=r["rows_per_s"] * host.bytes_per_row / 1e9)
         rec["frac_of_h2d_ceiling"] = rec["gb_per_s"] / ceiling
+        rec["frac_of_host_copy_ceiling"] = rec["gb_per_s"] / copy_ceiling
         if full:
             variants = {}
             r = time_host_pages(op, host.pages(65536), max(1, steps - 1), to_host=True)
@@ -814,14 +841,15 @@ def run_e2e(args, wl, device, dp, dist, steps, full):
     import torch.distributed as td
     td.all_reduce(t, op=td.ReduceOp.MAX)
     dt = float(t.item())
-    t = torch.tensor([ceiling], device="cuda", dtype=torch.float64)
+    t = torch.tensor([ceiling, copy_ceiling], device="cuda", dtype=torch.float64)
     td.all_reduce(t, op=td.ReduceOp.SUM)
     st = op.stats()
     d2h = st.d2h_bytes + final.stats().d2h_bytes
     rec.update(value=rows * world * steps / dt, h2d_bytes_per_step=int(st.h2d_bytes) * world, d2h_bytes_per_step=int(d2h) * world,
                rows_per_step=rows * world, steps=steps, seconds_per_step=dt / steps, gb_per_s=rows * world * steps * host.bytes_per_row / dt / 1e9,
-               h2d_ceiling_gbs=float(t.item()))
+               h2d_ceiling_gbs=float(t[0].item()), host_copy_ceiling_gbs=float(t[1].item()))
     rec["frac_of_h2d_ceiling"] = rec["gb_per_s"] / rec["h2d_ceiling_gbs"]
+    rec["frac_of_host_copy_ceiling"] = rec["gb_per_s"] / rec["host_copy_ceiling_gbs"]
     op.close()
     if repart is not None and not hasattr(repart, "exchange"):
         repart.close()

@@ -55,6 +55,9 @@ pgpu_status pgpu_tpch_lineitem_device(int32_t device, double sf, int64_t first_o
                                       int64_t capacity_rows, void* dev_out, int64_t* rows);
 pgpu_status pgpu_tpch_lineitem_host(double sf, int64_t first_order, int64_t n_orders, int32_t column, int32_t format,
                                     int64_t capacity_rows, void* host_out, int64_t* rows);
+/* The product's staging copy alone (csrc/hostcopy.cpp: worker pool, non-temporal stores) from `src` (pageable) to `dst` (pinned):
+ * lets bench.py measure the host-side ceiling of the ingest path with no GPU involved. */
+pgpu_status pgpu_bench_host_copy(void* dst, const void* src, size_t bytes);
 /* Write `bytes` of device memory (L2 flush between timed iterations). */
 pgpu_status pgpu_flush_l2(int32_t device, void* dev_scratch, size_t bytes);
 

@@ -99,6 +99,7 @@ SYMBOLS = [
 
 # every symbol include/prestogpu_bench.h declares (libprestogpu_bench.so)
 BENCH_SYMBOLS = [
+    ("pgpu_bench_host_copy", ctypes.c_int32, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]),
     ("pgpu_tpch_order_count", ctypes.c_int64, [ctypes.c_double]),
     ("pgpu_tpch_lineitem_rows", ctypes.c_int32, [ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_tpch_lineitem_device", ctypes.c_int32, [ctypes.c_int32, ctypes.c_double, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]),

@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "../../include/prestogpu_bench.h"
+#include "hostcopy.h"
 #include "lineitem_gen.h"
 #include "tpch_dbgen.cuh"
 
@@ -263,6 +264,16 @@ pgpu_status pgpu_memcpy_h2d(int32_t device, void* dev_dst, const void* host_src,
 pgpu_status pgpu_memcpy_d2h(int32_t device, void* host_dst, const void* dev_src, size_t bytes) {
     if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
     return cudaMemcpy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? PGPU_OK : PGPU_CUDA_ERROR;
+}
+
+// the library's staging copy alone (pageable -> pinned, worker pool, non-temporal stores): bench.py measures with it what the host
+// memory system gives the ingest path when no GPU is involved
+pgpu_status pgpu_bench_host_copy(void* dst, const void* src, size_t bytes) {
+    if (!dst || !src) return PGPU_INVALID_ARGUMENT;
+    std::vector<pgpu::CopyTask> t;
+    t.push_back(pgpu::CopyTask{pgpu::CopyTask::BYTES, dst, src, bytes, 0});
+    pgpu::hostCopy(t);
+    return PGPU_OK;
 }
 
 pgpu_status pgpu_flush_l2(int32_t device, void* dev_scratch, size_t bytes) {

@@ -871,7 +871,11 @@ pgpu_status ensureSlot(pgpu_pipeline* p, StageSlot& slot, size_t bytes, bool nee
         if (slot.host) CU(cudaFreeHost(slot.host));
         slot.host = nullptr;
         slot.hostCap = 0;
-        CU(cudaMallocHost(&slot.host, bytes));
+        // PGPU_STAGE_WC=1: write-combined pinned memory (the CPU only writes a slot, with non-temporal stores; the copy engine reads
+        // it without snooping the caches). Experiment knob: the dictionary comparison of the appender reads the slot back.
+        static const bool wc = getenv("PGPU_STAGE_WC") && atoi(getenv("PGPU_STAGE_WC")) != 0;
+        if (wc) CU(cudaHostAlloc(&slot.host, bytes, cudaHostAllocWriteCombined));
+        else CU(cudaMallocHost(&slot.host, bytes));
         slot.hostCap = bytes;
     }
     return PGPU_OK;
