@@ -221,6 +221,8 @@ typedef struct pgpu_stats {
     int64_t table_bucketed; /* 1: the HBM table keeps 8 neighbouring integer keys per slot (clustered keys), 0: one key per slot */
     int64_t table_slots_claimed; /* slots in use at the last look (output time / table growth); buckets for a bucketed table */
     int64_t bucket_offset;  /* bucketed table: buckets are cut at 8n - bucket_offset (chosen by the key-clustering probe) */
+    int64_t pages_merged;   /* filter + project with (merge-min-rows / merge-min-bytes): small output pages appended to the
+                             * buffer instead of going out on their own (MergePages.java:147 appendPage) */
 } pgpu_stats;
 pgpu_status pgpu_get_stats(const pgpu_pipeline* p, pgpu_stats* out);
 pgpu_status pgpu_set_timing(pgpu_pipeline* p, int32_t enabled);

@@ -107,6 +107,23 @@ public final class GpuPlanTranslator
         return plan.append(")").toString().getBytes(StandardCharsets.US_ASCII);
     }
 
+    /**
+     * Filter + project only, with the thresholds FilterAndProjectOperator (main/operator/FilterAndProjectOperator.java:75-83) hands to
+     * MergePages: minOutputPageSize (session property filter_and_project_min_output_page_size) and minOutputPageRowCount.
+     */
+    public static byte[] translateFilterAndProject(
+            List<Type> inputTypes,
+            Optional<RowExpression> filter,
+            List<RowExpression> projections,
+            long minOutputPageSizeInBytes,
+            int minOutputPageRowCount)
+    {
+        String plan = new String(translate(inputTypes, filter, projections, Optional.empty(), List.of(), List.of(), 0), StandardCharsets.US_ASCII);
+        return (plan.substring(0, plan.length() - 1)
+                + " (options (merge-min-rows " + minOutputPageRowCount + ") (merge-min-bytes " + minOutputPageSizeInBytes + ")))")
+                .getBytes(StandardCharsets.US_ASCII);
+    }
+
     /** Type names of the plan language (csrc/plan.cpp parseType). */
     static String type(Type type)
     {

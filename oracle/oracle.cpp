@@ -24,6 +24,7 @@
 #include <limits>
 #include <memory>
 #include <string>
+#include <deque>
 #include <vector>
 
 #include "../include/prestogpu.h"
@@ -928,8 +929,12 @@ struct Oracle {
     GroupByHash hash;
     std::vector<Accumulator> accs;
     bool finishing = false, finished = false, sawInput = false;
-    std::vector<Vec> pending;      // COMPACT: projected rows waiting for getOutput
-    bool pendingReady = false;
+    std::vector<Vec> pending;      // filter + project: projected rows of the page just added
+    bool pendingReady = false;     // ... waiting for the look getOutput takes (the GPU operator learns the row count there)
+    // MergePages (operator/project/MergePages.java:87-164): `builder` is its PageBuilder, `ready` the pages it has let go
+    std::deque<std::vector<Vec>> ready;
+    std::vector<Vec> builder;
+    int64_t frontServed = 0;       // rows of ready.front() already handed out (max-output-rows)
     std::vector<Vec> result;       // aggregation result rows not yet served
     bool resultReady = false;
     int64_t resultServed = 0;
@@ -1109,13 +1114,59 @@ struct Oracle {
         resultServed = 0;
     }
 
+    static int64_t pageRows(const std::vector<Vec>& pg) { return pg.empty() ? 0 : (int64_t)pg[0].size(); }
+
+    // Page.getSizeInBytes = sum of Block.getSizeInBytes: fixed width (width + 1 null byte) per position
+    // (LongArrayBlock.java getSizeInBytes), var width the bytes + (4 offset + 1 null) per position (VariableWidthBlock.java)
+    static int64_t pageBytes(const std::vector<Vec>& pg) {
+        int64_t b = 0;
+        for (auto& v : pg) {
+            int64_t n = (int64_t)v.size();
+            if (v.type.isVarWidth()) {
+                b += n * 5;
+                for (auto& x : v.s) b += (int64_t)x.size();
+            } else {
+                b += n * (v.type.width() + 1);
+            }
+        }
+        return b;
+    }
+
+    void flushBuilder() {
+        ready.push_back(std::move(builder));
+        builder.clear();
+    }
+
+    // MergePages.java:112-151 on the page addPage left in `pending`
+    void mergePagesProcess() {
+        std::vector<Vec> pg;
+        pg.swap(pending);
+        if (pg.empty()) {
+            pg.resize(projTypes.size());
+            for (size_t c = 0; c < pg.size(); c++) pg[c].type = projTypes[c];
+        }
+        const bool merging = plan->mergeMinRows > 0 || plan->mergeMinBytes > 0;
+        if (!merging || pageRows(pg) >= plan->mergeMinRows || pageBytes(pg) >= plan->mergeMinBytes) {
+            if (pageRows(builder) > 0) flushBuilder();  // the buffered rows first, then the page as it is (:135-142)
+            ready.push_back(std::move(pg));
+            return;
+        }
+        if (builder.empty()) {
+            builder.resize(pg.size());
+            for (size_t c = 0; c < pg.size(); c++) builder[c].type = pg[c].type;
+        }
+        for (size_t c = 0; c < pg.size(); c++)          // appendPage (:153-162)
+            for (size_t k = 0; k < pg[c].size(); k++) appendValue(builder[c], pg[c], k);
+        if (pageBytes(builder) >= plan->mergeMaxBytes) flushBuilder();  // PageBuilder.isFull (:147-149)
+    }
+
     bool partialFlushDue() const {
         return plan->hasAgg && outputIsIntermediate(plan->step) && plan->maxPartialGroups > 0 && hasGroups() && hash.groupCount >= plan->maxPartialGroups;
     }
 
     bool needsInput() const {  // HashAggregationOperator.needsInput :367-378
         if (finishing || finished) return false;
-        if (pendingReady || resultReady) return false;
+        if (pendingReady || !ready.empty() || resultReady) return false;
         if (partialFlushDue()) return false;
         return true;
     }
@@ -1124,14 +1175,32 @@ struct Oracle {
     bool getOutput(std::vector<Vec>& page, int64_t& rows) {
         if (finished) return false;
         if (!plan->hasAgg) {
-            if (!pendingReady) {
-                if (finishing) finished = true;
-                return false;
+            if (pendingReady) {
+                pendingReady = false;
+                mergePagesProcess();
             }
-            page.swap(pending);
-            pending.clear();
-            pendingReady = false;
-            rows = page.empty() ? 0 : (int64_t)page[0].size();
+            if (ready.empty()) {
+                if (!finishing) return false;
+                if (pageRows(builder) == 0) {  // MergePages.java:125-129
+                    finished = true;
+                    return false;
+                }
+                flushBuilder();                // MergePages.java:131
+            }
+            const std::vector<Vec>& front = ready.front();
+            int64_t n = pageRows(front) - frontServed;
+            if (plan->maxOutputRows > 0) n = std::min<int64_t>(n, plan->maxOutputRows);
+            page.assign(front.size(), Vec());
+            for (size_t c = 0; c < front.size(); c++) {
+                page[c].type = front[c].type;
+                for (int64_t k = 0; k < n; k++) appendValue(page[c], front[c], (size_t)(frontServed + k));
+            }
+            rows = n;
+            frontServed += n;
+            if (frontServed >= pageRows(front)) {
+                ready.pop_front();
+                frontServed = 0;
+            }
             return true;
         }
         if (!resultReady) {

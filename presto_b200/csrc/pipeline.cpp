@@ -184,6 +184,11 @@ struct pgpu_pipeline {
     bool sawInput = false;
     bool outputReady = false;      // COMPACT: a page result is pending; aggregation: result materialised
     int64_t outRowsTotal = 0, outRowsServed = 0;
+    // COMPACT with merge-min-rows / merge-min-bytes (MergePages): rows [0, mergeRows) of the output arena are buffered small
+    // pages; the next page's kernel writes behind them. compactPending: a page kernel is in flight, its row count unread.
+    // outBoundary: an output page ends here even if more rows follow (the flushed buffer, then the big page that flushed it)
+    bool compactPending = false;
+    int64_t mergeRows = 0, outBoundary = 0, outRowBytes = 0;
 
     // device scratch
     uint32_t* dErr = nullptr;
@@ -707,7 +712,8 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
     return fail(p, PGPU_INVALID_STATE, "internal: launchPageKernel in COMPACT mode");
 }
 
-pgpu_status ensureOutBuffers(pgpu_pipeline* p, int64_t rows) {
+// keepRows > 0: the first keepRows rows of every output column survive a reallocation (buffered small pages)
+pgpu_status ensureOutBuffers(pgpu_pipeline* p, int64_t rows, int64_t keepRows = 0) {
     const GenResult& g = p->layout;
     if ((int)p->outDev.size() != g.NO) {
         p->outDev.resize(g.NO);
@@ -718,6 +724,15 @@ pgpu_status ensureOutBuffers(pgpu_pipeline* p, int64_t rows) {
     }
     int64_t r = std::max<int64_t>(rows, 1);
     if (p->outArena.ptr && p->outCapacityRows >= r && (int)p->outOffV.size() == g.NO) return PGPU_OK;  // layout stays
+    DeviceBuf old;
+    std::vector<size_t> oldOffV, oldOffN;
+    if (keepRows > 0 && p->outArena.ptr) {
+        r = std::max<int64_t>(r, 2 * p->outCapacityRows);
+        old = p->outArena;
+        p->outArena = DeviceBuf();
+        oldOffV = p->outOffV;
+        oldOffN = p->outOffN;
+    }
     p->outOffV.assign(g.NO, 0);
     p->outOffN.assign(g.NO, 0);
     size_t need = 0;
@@ -737,23 +752,34 @@ pgpu_status ensureOutBuffers(pgpu_pipeline* p, int64_t rows) {
         p->outDevNulls[c].cap = (size_t)r;
     }
     p->outCapacityRows = r;
+    if (old.ptr) {
+        for (int c = 0; c < g.NO; c++) {
+            CU(cudaMemcpyAsync(p->outDev[c].ptr, (char*)old.ptr + oldOffV[c], (size_t)keepRows * std::max(g.out[c].stride, 1), cudaMemcpyDeviceToDevice, p->stream));
+            CU(cudaMemcpyAsync(p->outDevNulls[c].ptr, (char*)old.ptr + oldOffN[c], (size_t)keepRows, cudaMemcpyDeviceToDevice, p->stream));
+        }
+        CU(cudaStreamSynchronize(p->stream));
+        CU(cudaFree(old.ptr));
+    }
     return PGPU_OK;
 }
 
-std::vector<unsigned char> outArgsBlock(pgpu_pipeline* p) {
+// baseRows: the kernel's row 0 lands at this row of the output arena
+std::vector<unsigned char> outArgsBlock(pgpu_pipeline* p, int64_t baseRows = 0) {
     const GenResult& g = p->layout;
     std::vector<unsigned char> oa(sizeof(OutCol) * g.NO + 8);
     for (int c = 0; c < g.NO; c++) {
-        OutCol oc{p->outDev[c].ptr, (uint8_t*)p->outDevNulls[c].ptr};
+        OutCol oc{(char*)p->outDev[c].ptr + (size_t)baseRows * std::max(g.out[c].stride, 1), (uint8_t*)p->outDevNulls[c].ptr + baseRows};
         memcpy(oa.data() + sizeof(OutCol) * c, &oc, sizeof oc);
     }
-    memcpy(oa.data() + sizeof(OutCol) * g.NO, &p->outCapacityRows, 8);
+    int64_t cap = p->outCapacityRows - baseRows;
+    memcpy(oa.data() + sizeof(OutCol) * g.NO, &cap, 8);
     return oa;
 }
 
 pgpu_status runCompact(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
     const GenResult& g = v->gen;
-    pgpu_status st = ensureOutBuffers(p, pg.rows);
+    const int64_t base = p->mergeRows;  // buffered small pages stay in front (MergePages)
+    pgpu_status st = ensureOutBuffers(p, base + pg.rows, base);
     if (st) return st;
     int64_t ntiles = (pg.rows + kTileRows - 1) / kTileRows;
     st = ensureDev(p, p->tileStatus, (size_t)ntiles * 8);
@@ -764,7 +790,7 @@ pgpu_status runCompact(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
     std::vector<unsigned char> pa(sizeof(ColArg) * g.NC + 8);
     memcpy(pa.data(), pg.cols.data(), sizeof(ColArg) * g.NC);
     memcpy(pa.data() + sizeof(ColArg) * g.NC, &pg.rows, 8);
-    std::vector<unsigned char> oa = outArgsBlock(p);
+    std::vector<unsigned char> oa = outArgsBlock(p, base);
     Scratch sc = scratchOf(p);
     int grid = (int)std::min<int64_t>(ntiles, (int64_t)p->numSMs * v->blocksPerSM);
     void* args[] = {pa.data(), oa.data(), &sc};
@@ -772,8 +798,7 @@ pgpu_status runCompact(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
     if (st) return st;
     CU(cudaMemcpyAsync(&p->hostScalars[0], p->dOutCount, 8, cudaMemcpyDeviceToHost, p->stream));
     p->outputReady = true;
-    p->outRowsTotal = -1;  // read after sync
-    p->outRowsServed = 0;
+    p->compactPending = true;  // the row count is read after the sync in getOutput
     return PGPU_OK;
 }
 
@@ -2059,6 +2084,34 @@ int32_t pgpu_is_finished(const pgpu_pipeline* p) { return p && p->finished ? 1 :
 
 enum class OutputTo { HOST, DEVICE, WIRE };
 
+// COMPACT: the kernel of one input page has finished and passed `k` rows, written behind the mergeRows buffered ones.
+// MergePages.java:112-151: a page with at least merge-min-rows rows or merge-min-bytes bytes goes out as it is, after the
+// buffer if that holds rows (two output pages); a smaller one joins the buffer, which goes out once it holds merge-max-bytes.
+static void compactPageDone(pgpu_pipeline* p, int64_t k) {
+    const Plan& plan = *p->plan;
+    if (!p->outRowBytes)
+        for (auto& d : p->layout.out) p->outRowBytes += std::max(d.stride, 1) + 1;  // values + the null flag, as Block.getSizeInBytes counts them
+    const bool merging = plan.mergeMinRows > 0 || plan.mergeMinBytes > 0;
+    const bool big = !merging || k >= plan.mergeMinRows || k * p->outRowBytes >= plan.mergeMinBytes;
+    if (big) {
+        p->outBoundary = p->mergeRows;
+        p->outRowsTotal = p->mergeRows + k;
+        p->outRowsServed = 0;
+        p->mergeRows = 0;
+        p->outputReady = true;  // an empty page too: the caller sees a page of 0 rows, as before
+        return;
+    }
+    p->mergeRows += k;
+    p->stats.pages_merged++;
+    if (p->mergeRows * p->outRowBytes >= plan.mergeMaxBytes) {  // PageBuilder.isFull
+        p->outRowsTotal = p->mergeRows;
+        p->outRowsServed = p->outBoundary = p->mergeRows = 0;
+        p->outputReady = true;
+        return;
+    }
+    p->outputReady = false;  // needs more data
+}
+
 static pgpu_status serializeOutput(pgpu_pipeline* p, int64_t r0, int64_t n);
 
 static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_t max_cols, int32_t* ncols, int64_t* rows, OutputTo to) {
@@ -2072,14 +2125,24 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
     const Plan& plan = *p->plan;
     CU(cudaSetDevice(p->device));
     if (g.mode == KernelMode::COMPACT) {
-        if (!p->outputReady) {
-            if (p->finishing) p->finished = true;
-            return PGPU_OK;
+        if (p->compactPending) {
+            CU(cudaStreamSynchronize(p->stream));
+            pgpu_status st = checkDeviceErrors(p);
+            if (st) return st;
+            p->compactPending = false;
+            compactPageDone(p, (int64_t)p->hostScalars[0]);
         }
-        CU(cudaStreamSynchronize(p->stream));
-        pgpu_status st = checkDeviceErrors(p);
-        if (st) return st;
-        p->outRowsTotal = (int64_t)p->hostScalars[0];
+        if (!p->outputReady) {
+            if (!p->finishing) return PGPU_OK;
+            if (p->mergeRows == 0) {
+                p->finished = true;
+                return PGPU_OK;
+            }
+            // MergePages.java:125-131: input finished, flush what the builder holds
+            p->outRowsTotal = p->mergeRows;
+            p->outRowsServed = p->outBoundary = p->mergeRows = 0;
+            p->outputReady = true;
+        }
     } else {
         if (!p->outputReady) {
             const bool flush = isPartialFlushDue(p);
@@ -2098,6 +2161,7 @@ static pgpu_status getOutputImpl(pgpu_pipeline* p, pgpu_column* out_cols, int32_
     int64_t n = remaining;
     if (plan.maxOutputRows > 0) n = std::min<int64_t>(n, plan.maxOutputRows);
     const int64_t r0 = p->outRowsServed;
+    if (g.mode == KernelMode::COMPACT && r0 < p->outBoundary) n = std::min<int64_t>(n, p->outBoundary - r0);
     if (remaining <= 0 && g.mode != KernelMode::COMPACT) {
         // nothing (left) to serve
         p->outputReady = false;
@@ -2359,8 +2423,8 @@ pgpu_status pgpu_reset(pgpu_pipeline* p) {
         CU(cudaStreamSynchronize(p->stream));
         for (auto& s : p->slots) s.inFlight = false;
     }
-    p->finishing = p->finished = p->sawInput = p->outputReady = false;
-    p->outRowsTotal = p->outRowsServed = 0;
+    p->finishing = p->finished = p->sawInput = p->outputReady = p->compactPending = false;
+    p->outRowsTotal = p->outRowsServed = p->mergeRows = p->outBoundary = 0;
     int64_t cap = p->stats.table_capacity, bucketed = p->stats.table_bucketed;
     p->stats = pgpu_stats{};
     p->stats.table_capacity = cap;

@@ -781,9 +781,17 @@ std::unique_ptr<Plan> parsePlan(const std::string& text) {
             if (s.kids.size() != 2) bad("(options (key value)...)");
             if (h == "max-partial-groups") plan->maxPartialGroups = parseInt(s.kids[1], h.c_str());
             else if (h == "max-output-rows") plan->maxOutputRows = parseInt(s.kids[1], h.c_str());
+            else if (h == "merge-min-rows") plan->mergeMinRows = parseInt(s.kids[1], h.c_str());
+            else if (h == "merge-min-bytes") plan->mergeMinBytes = parseInt(s.kids[1], h.c_str());
+            else if (h == "merge-max-bytes") plan->mergeMaxBytes = parseInt(s.kids[1], h.c_str());
             else bad("unknown option '" + h + "'");
         }
     }
+    // MergePages.java:100-105, the same argument checks
+    if (plan->mergeMinRows < 0 || plan->mergeMinBytes < 0) bad("merge-min-rows / merge-min-bytes must be greater or equal than zero");
+    if (plan->mergeMaxBytes <= 0) bad("merge-max-bytes must be greater than zero");
+    if (plan->mergeMaxBytes < plan->mergeMinBytes) bad("merge-max-bytes must be greater or equal than merge-min-bytes");
+    if ((plan->mergeMinRows || plan->mergeMinBytes) && plan->hasAgg) bad("merge-min-rows / merge-min-bytes apply to filter + project plans only");
     return plan;
 }
 

@@ -92,6 +92,11 @@ struct Plan {
     // options
     int64_t maxPartialGroups = 0;   // PARTIAL: flush when the table holds this many groups (0 = never)
     int64_t maxOutputRows = 0;      // rows per output page (0 = one page)
+    // filter + project only: MergePages (operator/project/MergePages.java:60-84). Output pages with fewer than mergeMinRows rows
+    // and fewer than mergeMinBytes bytes are buffered; both 0 = every page goes out as it is (no merging)
+    int64_t mergeMinRows = 0;       // session property filter_and_project_min_output_page_row_count (256 in the reference)
+    int64_t mergeMinBytes = 0;      // filter_and_project_min_output_page_size (500 kB in the reference)
+    int64_t mergeMaxBytes = 1 << 20;  // PageBuilder.DEFAULT_MAX_PAGE_SIZE_IN_BYTES: the buffer is flushed when it holds this much
     std::string text;               // canonical source text
 
     // schema of the page after projection (input to aggregation / output of filter-project)

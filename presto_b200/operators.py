@@ -51,7 +51,10 @@ class Aggregation:
 def plan_text(inputTypes: Sequence[Type], filter: Optional[RowExpression] = None,
               projections: Optional[Sequence[RowExpression]] = None, step: Optional[str] = None,
               groupByChannels: Sequence[int] = (), aggregations: Sequence[Aggregation] = (),
-              expectedGroups: int = 10000, maxPartialGroups: int = 0, maxOutputRows: int = 0) -> str:
+              expectedGroups: int = 10000, maxPartialGroups: int = 0, maxOutputRows: int = 0,
+              mergeMinRows: int = 0, mergeMinBytes: int = 0, mergeMaxBytes: int = 0) -> str:
+    """mergeMinRows / mergeMinBytes: the session properties filter_and_project_min_output_page_row_count / _size
+    (SystemSessionProperties.java) that ScanFilterAndProjectOperator and FilterAndProjectOperator hand to MergePages; 0/0 = off."""
     parts = ["(plan", " (input %s)" % " ".join(str(t) for t in inputTypes)]
     if filter is not None:
         parts.append(" (filter %s)" % filter.sexpr())
@@ -70,6 +73,12 @@ def plan_text(inputTypes: Sequence[Type], filter: Optional[RowExpression] = None
         opts.append("(max-partial-groups %d)" % maxPartialGroups)
     if maxOutputRows:
         opts.append("(max-output-rows %d)" % maxOutputRows)
+    if mergeMinRows:
+        opts.append("(merge-min-rows %d)" % mergeMinRows)
+    if mergeMinBytes:
+        opts.append("(merge-min-bytes %d)" % mergeMinBytes)
+    if mergeMaxBytes:
+        opts.append("(merge-max-bytes %d)" % mergeMaxBytes)
     if opts:
         parts.append(" (options %s)" % " ".join(opts))
     parts.append(")")
