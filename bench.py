@@ -709,7 +709,8 @@ def run_device_steps(args, wl, device, dist, steps, warmup):
     op.setTiming(False)
     info = dict(dev_ms=dev_ms, wall_s=wall, launches=nl, clocks=clocks, kern_ms=kern_ms, kern_launches=kern_launches,
                 kern_steps=ksteps, result_rows=state["result_rows"], table_capacity=op.stats().table_capacity,
-                exchange_bytes=state["exchange_bytes"], private_groups=state.get("private_groups", 0))
+                exchange_bytes=state["exchange_bytes"], private_groups=state.get("private_groups", 0),
+                partition_sweeps=op.stats().partition_sweeps)
     if repart is not None and not hasattr(repart, "exchange"):
         repart.close()
     if final is not None:
@@ -886,6 +887,8 @@ def run_workload(args, name, device, dist, headline):
     alg_bytes_step = rows * wl["bytes_per_row"]
     achieved = alg_bytes_step / (kern_ms_step / 1e3) / 1e9
     kname = "pgpu_k_page_staged (cp.async.bulk ring + register-resident groups)" if name in ("q1", "q1dict") else "pgpu_k_page (fused scan+filter+project+aggregate, direct loads)"
+    if info.get("partition_sweeps"):
+        kname = "pgpu_k_part_count + pgpu_k_part_scatter + pgpu_k_page_sweep (rows reordered by table slice, then the fused kernel with L2-resident table slices; kernel_ms_per_step is the sum of the three)"
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "bytes_per_launch": alg_bytes_step / max(launches_step, 1), "avg_launch_ms": kern_ms_step / max(launches_step, 1),
                 "kernel_ms_per_step": kern_ms_step, "launches_per_step": launches_step, "kernel": kname, "peak_source": peak_src,
@@ -905,7 +908,8 @@ def run_workload(args, name, device, dist, headline):
               "l2_policy": "inputs (%.1f GB per GPU) are far larger than the 126 MB L2: no flush needed" % (rows * wl["bytes_per_row"] / 1e9)}
     rec = {"metric": "lineitem_rows_per_second", "value": value, "unit": "rows/s", "ms_per_step": ms_per_step, "steps": steps, "warmup": warmup,
            "gb_per_s": value * wl["bytes_per_row"] / 1e9, "roofline": roofline, "config": config, "gpu_launches": info["launches"],
-           "clocks": info["clocks"], "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"]}
+           "clocks": info["clocks"], "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"],
+           "partition_sweeps_per_step": info.get("partition_sweeps", 0)}
     if world > 1:
         small = name in ("q1", "q1dict", "q6")
         rec["exchange"] = {"shape": ("gather: push kernel stores the partial rows into every rank's inbox over NVLink, FINAL gather kernel merges them; no host round trip (pgpu_exchange_partial)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if small else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory, pgpu_exchange_partial)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),

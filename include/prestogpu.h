@@ -223,6 +223,8 @@ typedef struct pgpu_stats {
     int64_t bucket_offset;  /* bucketed table: buckets are cut at 8n - bucket_offset (chosen by the key-clustering probe) */
     int64_t pages_merged;   /* filter + project with (merge-min-rows / merge-min-bytes): small output pages appended to the
                              * buffer instead of going out on their own (MergePages.java:147 appendPage) */
+    int64_t partition_sweeps; /* long device-resident pages whose rows were reordered by table slice before the hash-aggregation
+                               * kernel ran (tables far larger than L2; DESIGN.md "partition sweep") */
 } pgpu_stats;
 pgpu_status pgpu_get_stats(const pgpu_pipeline* p, pgpu_stats* out);
 pgpu_status pgpu_set_timing(pgpu_pipeline* p, int32_t enabled);

@@ -28,10 +28,8 @@
 #include <vector>
 
 #include "../include/prestogpu.h"
-#include "../presto_b200/csrc/plan.h"
+#include "oracle_plan.h"  // the oracle's own plan reader: nothing of presto_b200/csrc is compiled into this library
 #include "decimal128.h"
-
-using namespace pgpu;  // Plan / Expr / Type only (the plan parser is shared; nothing else of the product is used)
 
 namespace oracle {
 
@@ -540,6 +538,66 @@ static Vec evalExpr(const Expr& e, const EvalCtx& cx, const std::vector<int32_t>
                 active.swap(np);
                 idx.swap(ni);
             }
+            bool any = false;
+            for (auto x : r.null) any |= x != 0;
+            if (!any) r.null.clear();
+            return r;
+        }
+        case ExprKind::NULL_IF: {
+            // NullIfCodeGenerator.java:70-113: first NULL -> NULL and the second operand is not evaluated there; equal(first, second)
+            // true -> NULL; false or NULL -> first
+            Vec a = evalExpr(*e.args[0], cx, pos);
+            std::vector<int32_t> sub;
+            std::vector<size_t> at;
+            for (size_t k = 0; k < n; k++)
+                if (!a.isNull(k)) { sub.push_back(pos[k]); at.push_back(k); }
+            Vec r = a;
+            if (!sub.empty()) {
+                Vec b = evalExpr(*e.args[1], cx, sub);
+                Vec as = scatterNew(a.type, at.size());
+                for (size_t j = 0; j < at.size(); j++) copyAt(as, j, a, at[j]);
+                Vec eq = compareOp(Op::EQ, as, b);
+                for (size_t j = 0; j < at.size(); j++)
+                    if (!eq.isNull(j) && eq.i[j]) r.setNull(at[j]);
+            }
+            return r;
+        }
+        case ExprKind::SWITCH: {
+            // SwitchCodeGenerator.java:113-159: the value is evaluated once; NULL value -> the else branch; otherwise the first WHEN whose
+            // equal(operand, value) is true (a NULL comparison is not a match) gives its result; no match -> else, no else -> NULL.
+            // Operands and results are evaluated only at the positions that reach / take them.
+            Vec v = evalExpr(*e.args[0], cx, pos);
+            Vec r = scatterNew(e.type, n);
+            r.null.assign(n, 1);
+            std::vector<size_t> open;  // positions (indices into pos) still looking for a match
+            std::vector<size_t> toElse;
+            for (size_t k = 0; k < n; k++) (v.isNull(k) ? toElse : open).push_back(k);
+            auto place = [&](const Expr& x, const std::vector<size_t>& where) {
+                if (where.empty()) return;
+                std::vector<int32_t> sub;
+                for (size_t k : where) sub.push_back(pos[k]);
+                Vec val = evalExpr(x, cx, sub);
+                for (size_t j = 0; j < where.size(); j++) {
+                    if (val.isNull(j)) continue;
+                    r.null[where[j]] = 0;
+                    copyAt(r, where[j], val, j);
+                }
+            };
+            const size_t nwhen = (e.args.size() - 1 - (e.hasElse ? 1 : 0)) / 2;
+            for (size_t w = 0; w < nwhen && !open.empty(); w++) {
+                std::vector<int32_t> sub;
+                for (size_t k : open) sub.push_back(pos[k]);
+                Vec o = evalExpr(*e.args[1 + 2 * w], cx, sub);
+                Vec vs = scatterNew(v.type, open.size());
+                for (size_t j = 0; j < open.size(); j++) copyAt(vs, j, v, open[j]);
+                Vec eq = compareOp(Op::EQ, o, vs);
+                std::vector<size_t> hit, rest;
+                for (size_t j = 0; j < open.size(); j++) ((!eq.isNull(j) && eq.i[j]) ? hit : rest).push_back(open[j]);
+                place(*e.args[2 + 2 * w], hit);
+                open.swap(rest);
+            }
+            toElse.insert(toElse.end(), open.begin(), open.end());
+            if (e.hasElse) place(*e.args.back(), toElse);
             bool any = false;
             for (auto x : r.null) any |= x != 0;
             if (!any) r.null.clear();
@@ -1309,7 +1367,7 @@ int oracle_create(const char* plan, size_t len, void** out, char* err, size_t er
     *out = nullptr;
     try {
         auto o = std::make_unique<Oracle>();
-        o->plan = parsePlan(std::string(plan, len));
+        o->plan = readPlan(std::string(plan, len));
         o->init();
         *out = o.release();
         return PGPU_OK;
@@ -1352,7 +1410,7 @@ int oracle_get_output(void* h, pgpu_column* cols, int max_cols, int* ncols, int6
 int oracle_group_ids(const char* types_plan, size_t len, const pgpu_column* cols, int ncols, int64_t rows, int64_t expected, int64_t* ids_out, int64_t* group_count) {
     try {
         // types_plan: "(plan (input t...))" — only the input types are used
-        auto plan = parsePlan(std::string(types_plan, len));
+        auto plan = readPlan(std::string(types_plan, len));
         GroupByHash gh;
         gh.init(plan->input, expected);
         std::vector<BlockView> views;

@@ -1609,6 +1609,44 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
         src << em.str();
         src << "    }\n";
     }
+    // partition sweep (device header, "partition sweep"): the rows of the used channels can be moved one by one when every
+    // array is fixed width per position: plain values / 16-byte varchar cells / dictionary ids (+ null flags); RLE blocks have
+    // nothing to move
+    bool sweepOk = highCard && !res.buckets && res.mode == KernelMode::AGG_HASH && plan.maxPartialGroups == 0 && envInt("PGPU_TUNE_SWEEP", 1) != 0;
+    int sweepRowBytes = 0;
+    {
+        std::ostringstream cp;
+        for (int c : res.usedChannels) {
+            const Type& t = plan.input[c];
+            const ColSig& cs = sig[c];
+            const std::string C = std::to_string(c);
+            if (cs.encoding == PGPU_ENC_RLE) continue;
+            if (cs.encoding == PGPU_ENC_DICTIONARY) {
+                cp << "        const_cast<i32*>(o.c[" << C << "].ids)[dst] = a.c[" << C << "].ids[src];\n";
+                sweepRowBytes += 4;
+                continue;
+            }
+            int w = cs.encoding == PGPU_ENC_VARCELL ? 16 : t.isVarWidth() ? 0 : t.width();
+            const char* ty = w == 1 ? "u8" : w == 2 ? "unsigned short" : w == 4 ? "u32" : w == 8 || w == 16 ? "u64" : nullptr;
+            if (!ty) { sweepOk = false; break; }
+            if (w == 16) {  // two words: the caller's 16-byte arrays need not be 16-byte aligned
+                cp << "        ((u64*)const_cast<void*>(o.c[" << C << "].values))[2 * dst] = ((const u64*)a.c[" << C << "].values)[2 * src];\n";
+                cp << "        ((u64*)const_cast<void*>(o.c[" << C << "].values))[2 * dst + 1] = ((const u64*)a.c[" << C << "].values)[2 * src + 1];\n";
+            } else {
+                cp << "        ((" << ty << "*)const_cast<void*>(o.c[" << C << "].values))[dst] = ((const " << ty << "*)a.c[" << C << "].values)[src];\n";
+            }
+            sweepRowBytes += w;
+            if (cs.nullable) {
+                cp << "        const_cast<u8*>(o.c[" << C << "].nulls)[dst] = a.c[" << C << "].nulls[src];\n";
+                sweepRowBytes += 1;
+            }
+        }
+        if (sweepOk) {
+            src << "    PGPU_DEV static void copy_row(const PageArgs<NC>& a, i64 src, const PageArgs<NC>& o, i64 dst) {\n" << cp.str() << "    }\n";
+            res.sweepOk = true;
+            res.sweepRowBytes = sweepRowBytes;
+        }
+    }
     src << "};\n\n";
     if (res.mode == KernelMode::AGG_GLOBAL) {
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_page(PageArgs<P::NC> a, Scratch sc) { body_agg_global<P>(a, sc); }\n";
@@ -1633,6 +1671,12 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
                 src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_keyrange(TableArgs t, i64* out) { body_key_range<P>(t, out); }\n";
                 src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit_probe(TableArgs t, OutArgs<P::NO> out, Scratch sc, ProbeArgs pa) { body_emit_probe<P>(t, out, sc, pa); }\n";
             }
+        }
+        if (res.sweepOk) {
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_part_count(PageArgs<P::NC> a, PartArgs pa, Scratch sc) { body_part_count<P>(a, pa, sc); }\n";
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_part_scatter(PageArgs<P::NC> a, PageArgs<P::NC> out, PartArgs pa) { body_part_scatter<P>(a, out, pa); }\n";
+            const int sweepMinBlocks = std::min(std::max(envInt("PGPU_TUNE_SWEEP_MINBLOCKS", 4), 1), 8);
+            src << "extern \"C\" __global__ void __launch_bounds__(256, " << sweepMinBlocks << ") pgpu_k_page_sweep(PageArgs<P::NC> a, TableArgs t, Scratch sc, SweepArgs sw) { body_agg_hash_sweep<P>(a, t, sc, sw); }\n";
         }
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";
     }

@@ -1402,6 +1402,212 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
     if (cx.err) atomicOr(sc.err, cx.err);
 }
 
+// ------------------------------------------------------------------------------------------------ partition sweep
+// A table far larger than L2 takes every update as a random DRAM round trip (10-14 G updates/s, tools/microbench/randtable.cu)
+// where an L2-resident one takes 50 G/s. For long device-resident pages the host therefore reorders the rows first:
+//   pgpu_k_part_count    rows per partition; partition = umulhi(hash, K), i.e. the K equal slices of the table in slot order
+//                        (home_pos is monotone in the hash, whatever the capacity, so the order survives table growth)
+//   (k_partition_scan, tableutil.cu: counts -> first row of every partition)
+//   pgpu_k_part_scatter  copies the rows that pass the filter into partition order: the input arrays of the used channels,
+//                        same encodings, so that the reordered page goes through the ordinary page kernel
+//   pgpu_k_page_sweep    body_agg_hash over the reordered page with (a) tiles handed out by a ticket counter, so that all
+//                        blocks work within a few hundred thousand rows of each other = inside one or two table slices, and
+//                        (b) every tile pulling the table lines that the rows kSweepLookahead further on will touch into L2 with
+//                        sequential full-line prefetches (without them each first touch is a 32-byte random DRAM read).
+// Measured in isolation (tools/microbench/partsweep.cu, 600 M rows, 150 M groups, 8.6 GB table): shuffled keys 56 -> 27 ms.
+struct PartArgs {
+    u32* hist;     // [K] rows per partition (part_count adds, the host zeroes)
+    u64* cursor;   // [K] next free row of every partition in the reordered arrays (part_scatter advances)
+    u32 K;
+    u32 pad;
+};
+struct SweepArgs {
+    const u64* start;  // [K + 1] first row of every partition in the reordered batch
+    u32* ticket;       // tile counter of this launch (zeroed by the host)
+    i64 row0;          // batch row of this launch's row 0 (a batch is launched in chunks)
+    u32 K;
+    u32 pad;
+};
+constexpr int kPartMaxK = 1024;
+constexpr int kPartTile = 4096;     // rows per scatter tile (the copy phase re-reads the tile's rows: they must still be in L1)
+constexpr int kPartThreads = 256;   // => 4 quads per thread
+constexpr i64 kSweepLookahead = 600000;
+
+template <class P>
+PGPU_DEV u32 part_of(const u64 (&key)[P::KW > 0 ? P::KW : 1], u32 K) {
+    return (u32)__umul64hi(hash_key<P::KW>(key), (u64)K);
+}
+
+template <class P>
+PGPU_DEV void body_part_count(const PageArgs<P::NC>& a, const PartArgs& pa, const Scratch& sc) {
+    __shared__ u32 h[kPartMaxK];
+    for (int j = threadIdx.x; j < (int)pa.K; j += blockDim.x) h[j] = 0;
+    __syncthreads();
+    u32 err = 0;
+    const i64 tile_rows = (i64)blockDim.x * 4;
+    const i64 ntiles = (a.rows + tile_rows - 1) / tile_rows;
+    for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const i64 base = tile * tile_rows + (i64)threadIdx.x * 4;
+        bool sel[4];
+        u64 key[4][P::KW > 0 ? P::KW : 1];
+        u64 cw[4][P::NHA];
+        P::eval(a, base, a.rows, sel, key, cw, err);
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+            if (sel[r]) atomicAdd(&h[part_of<P>(key[r], pa.K)], 1u);
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < (int)pa.K; j += blockDim.x)
+        if (h[j]) atomicAdd(&pa.hist[j], h[j]);
+    if (err) atomicOr(sc.err, err);
+}
+
+// dynamic shared memory: u64 gbase[K], u32 lstart[K + 2], u32 fill[K], u16 sidx[kPartTile], u16 spid[kPartTile]
+// = 16 K + 8 + 4 kPartTile bytes (the host computes the same figure)
+template <class P>
+PGPU_DEV void body_part_scatter(const PageArgs<P::NC>& a, const PageArgs<P::NC>& out, const PartArgs& pa) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int K = (int)pa.K;
+    u64* gbase = reinterpret_cast<u64*>(smem_raw);                 // first: keeps the 8-byte alignment
+    u32* lstart = reinterpret_cast<u32*>(gbase + K);               // K + 1 (+ 1 pad)
+    u32* fill = lstart + K + 2;
+    unsigned short* sidx = reinterpret_cast<unsigned short*>(fill + K);
+    unsigned short* spid = sidx + kPartTile;
+    constexpr int Q = kPartTile / (kPartThreads * 4);              // quads per thread
+    const int lane = threadIdx.x & 31;
+    const i64 ntiles = (a.rows + kPartTile - 1) / kPartTile;
+    for (i64 tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const i64 tbase = tile * kPartTile;
+        for (int j = threadIdx.x; j <= K; j += kPartThreads) lstart[j] = 0;
+        __syncthreads();
+        unsigned short pid[Q][4];
+#pragma unroll
+        for (int q = 0; q < Q; q++) {
+            const i64 base = tbase + ((i64)q * kPartThreads + threadIdx.x) * 4;
+            bool sel[4];
+            u64 key[4][P::KW > 0 ? P::KW : 1];
+            u64 cw[4][P::NHA];
+            u32 ignored = 0;  // the count pass has reported arithmetic errors
+#pragma unroll
+            for (int r = 0; r < 4; r++) sel[r] = false;
+            if (base < a.rows) P::eval(a, base, a.rows, sel, key, cw, ignored);
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                pid[q][r] = sel[r] ? (unsigned short)part_of<P>(key[r], pa.K) : (unsigned short)0xffff;
+                if (sel[r]) atomicAdd(&lstart[pid[q][r]], 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {  // exclusive scan of the K counts by one warp
+            u32 carry = 0;
+            for (int j0 = 0; j0 < K; j0 += 32) {
+                const u32 v = j0 + lane < K ? lstart[j0 + lane] : 0u;
+                u32 x = v;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const u32 y = __shfl_up_sync(FULLMASK, x, d);
+                    if (lane >= d) x += y;
+                }
+                if (j0 + lane < K) {
+                    lstart[j0 + lane] = carry + x - v;
+                    fill[j0 + lane] = carry + x - v;
+                }
+                carry += __shfl_sync(FULLMASK, x, 31);
+            }
+            if (lane == 0) lstart[K] = carry;
+        }
+        __syncthreads();
+        for (int j = threadIdx.x; j < K; j += kPartThreads) {
+            const u32 tot = lstart[j + 1] - lstart[j];
+            gbase[j] = tot ? atomicAdd(reinterpret_cast<unsigned long long*>(&pa.cursor[j]), (unsigned long long)tot) : 0ull;
+        }
+        // ranks: consecutive rows of a quad that go to the same partition take consecutive places (runs of equal keys survive)
+#pragma unroll
+        for (int q = 0; q < Q; q++) {
+            u32 pos = 0;
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                if (pid[q][r] == 0xffff) continue;
+                if (r > 0 && pid[q][r] == pid[q][r - 1]) {
+                    pos++;
+                } else {
+                    u32 len = 1;
+#pragma unroll
+                    for (int r2 = r + 1; r2 < 4; r2++) {
+                        if (pid[q][r2] != pid[q][r]) break;
+                        len++;
+                    }
+                    pos = atomicAdd(&fill[pid[q][r]], len);
+                }
+                sidx[pos] = (unsigned short)((q * kPartThreads + threadIdx.x) * 4 + r);
+                spid[pos] = pid[q][r];
+            }
+        }
+        __syncthreads();
+        const u32 total = lstart[K];
+        for (u32 j = threadIdx.x; j < total; j += kPartThreads) {
+            const u32 pp = spid[j];
+            P::copy_row(a, tbase + sidx[j], out, (i64)(gbase[pp] + (j - lstart[pp])));
+        }
+        __syncthreads();
+    }
+}
+
+template <class P>
+PGPU_DEV void body_agg_hash_sweep(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc, const SweepArgs& sw) {
+    constexpr int KW = P::KW, NHA = P::NHA;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashCtx<P> cx;
+    cx.init(smem_raw, P::NWARP, threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    constexpr i64 WT = 1024;  // rows per ticket: tickets go to WARPS (a block-wide hand-out costs two barriers per tile, 30 % of the kernel)
+    const i64 ntick = (a.rows + WT - 1) / WT;
+    const u64 table_bytes = t.capacity * (u64)P::SLOTW * 8ull;
+    const i64 batch_rows = (i64)sw.start[sw.K];
+    for (;;) {
+        i64 tk = 0;
+        u64 pf0 = 0, pf1 = 0;
+        if (lane == 0) {
+            tk = (i64)atomicAdd(sw.ticket, 1u);
+            // table bytes that batch rows [x0, x1) map to: a row at fraction f of partition p sits near slot (p + f) / K * capacity
+            u64 b[2];
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const i64 x = sw.row0 + (tk + e) * WT + kSweepLookahead;
+                if (tk >= ntick || x >= batch_rows) { b[e] = table_bytes; continue; }
+                int lo = 0, hi = (int)sw.K;  // last partition that starts at or before x
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if ((i64)sw.start[mid] <= x) lo = mid; else hi = mid;
+                }
+                const i64 s0 = (i64)sw.start[lo], s1 = (i64)sw.start[lo + 1];
+                const double f = ((double)lo + (double)(x - s0) / (double)(s1 > s0 ? s1 - s0 : 1)) / (double)sw.K;
+                b[e] = (u64)(f * (double)table_bytes);
+            }
+            pf0 = b[0] & ~127ull;
+            pf1 = b[1] > table_bytes ? table_bytes : b[1];
+        }
+        tk = (i64)shfl_u64((u64)tk, 0);
+        if (tk >= ntick) break;
+        pf0 = shfl_u64(pf0, 0);
+        pf1 = shfl_u64(pf1, 0);
+        for (u64 off = pf0 + (u64)lane * 128ull; off < pf1; off += 32ull * 128ull)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(t.slots) + off));
+#pragma unroll 1
+        for (int sub = 0; sub < (int)(WT / 128); sub++) {
+            const i64 base = tk * WT + sub * 128 + lane * 4;
+            bool sel[4];
+            u64 key[4][KW];
+            u64 cw[4][NHA];
+            P::eval_eager(a, base, a.rows, sel, key, cw, cx.err);
+            if (P::RUNS) cx.consume_runs(t, base, sel, key, cw);  // (HashCtx::consume measured no faster here, even for keys in no order)
+            else cx.template consume<4>(t, base, sel, key, cw);
+        }
+    }
+    cx.flush(t, P::NWARP);
+    if (cx.err) atomicOr(sc.err, cx.err);
+}
+
 // ------------------------------------------------------------------------------------------------ staged variant
 // Bulk-async (TMA engine, cp.async.bulk) staging of column tiles into a shared-memory ring, mbarrier full/empty
 // hand-shake, one producer warp + 2 groups of 8 consumer warps per SM. Memory-level parallelism no longer depends on

@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <chrono>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -76,6 +77,19 @@ struct ProbeArgs {
     int64_t lo[64], hi[64], start[65];
     int32_t n, probe_null;
 };
+struct PartArgs {
+    uint32_t* hist;
+    uint64_t* cursor;
+    uint32_t K;
+    uint32_t pad;
+};
+struct SweepArgs {
+    const uint64_t* start;
+    uint32_t* ticket;
+    int64_t row0;
+    uint32_t K;
+    uint32_t pad;
+};
 struct GatherArgs {
     const uint64_t* hdr;
     int32_t npages;
@@ -86,7 +100,13 @@ struct GatherArgs {
 
 constexpr int kThreads = 256;
 constexpr int64_t kTileRows = kThreads * 4;
-constexpr int64_t kHashChunkRows = 64ll << 20;  // rows per launch of the hash-aggregation kernel (bounds the deferred-row log)
+constexpr int64_t kHashChunkRows = 64ll << 20;
+// partition sweep (device header, "partition sweep"): same constants as the kernels
+constexpr int kPartMaxK = 1024, kPartTile = 4096, kPartThreads = 256;
+constexpr size_t partScatterSmem(int K) { return (size_t)16 * K + 8 + (size_t)4 * kPartTile; }
+constexpr int64_t kSweepMinRows = 16ll << 20;          // shorter batches do not pay for a pass over the table
+constexpr size_t kSweepMinTableBytes = 256ull << 20;   // a table that is not much larger than L2 (126 MB) is fast as it is
+constexpr size_t kSweepSliceBytes = 32ull << 20;       // table bytes per partition: what stays L2 resident while a partition is consumed  // rows per launch of the hash-aggregation kernel (bounds the deferred-row log)
 constexpr int64_t kHostChunkRows = 8ll << 20;   // rows per staged H2D chunk
 
 thread_local std::string g_lastGlobalError;
@@ -95,6 +115,8 @@ struct Variant {
     GenResult gen;
     cudaLibrary_t lib = nullptr;
     cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr, kGather = nullptr, kEmitRange = nullptr, kKeyRange = nullptr, kEmitProbe = nullptr;
+    cudaKernel_t kPartCount = nullptr, kPartScatter = nullptr, kPageSweep = nullptr;  // partition sweep (gen.sweepOk)
+    int sweepBlocksPerSM = 1, scatterBlocksPerSM = 1;
     int blocksPerSM = 1;
     int stagedStages = 0;      // stages of the shared-memory ring (0 = staged variant unavailable)
     size_t stagedSmem = 0;
@@ -200,6 +222,8 @@ struct pgpu_pipeline {
     size_t partialsCap = 0;
     DeviceBuf tileStatus;
     DeviceBuf failLog;   // deferred rows of the current hash-aggregation chunk
+    DeviceBuf sweepBuf;  // partition sweep: the reordered arrays of one batch
+    DeviceBuf sweepMeta; // ... [hist u32 x K | ticket u32 x 64 | cursor u64 x K | start u64 x (K + 1)]
     uint64_t* hostScalars = nullptr;  // pinned, 32 words: [0] out_count, [1..2] counters, [3] err, [4..12] key-clustering probe
 
     // table
@@ -346,6 +370,19 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
             }
             if (v.gen.mode != KernelMode::COMPACT && p->plan->hasAgg && inputIsIntermediate(p->plan->step))
                 CU(cudaLibraryGetKernel(&v.kGather, v.lib, "pgpu_k_gather"));
+            if (v.gen.sweepOk) {
+                CU(cudaLibraryGetKernel(&v.kPartCount, v.lib, "pgpu_k_part_count"));
+                CU(cudaLibraryGetKernel(&v.kPartScatter, v.lib, "pgpu_k_part_scatter"));
+                CU(cudaLibraryGetKernel(&v.kPageSweep, v.lib, "pgpu_k_page_sweep"));
+                CU(cudaFuncSetAttribute((const void*)v.kPartScatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)partScatterSmem(kPartMaxK)));
+                if (v.gen.smemBytes > 48 * 1024) CU(cudaFuncSetAttribute((const void*)v.kPageSweep, cudaFuncAttributeMaxDynamicSharedMemorySize, v.gen.smemBytes));
+                int nb = 0;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v.kPageSweep, kThreads, (size_t)v.gen.smemBytes) != cudaSuccess || nb < 1) {
+                    cudaGetLastError();
+                    nb = 2;
+                }
+                v.sweepBlocksPerSM = nb;
+            }
             if (v.gen.smemBytes > 48 * 1024) CU(cudaFuncSetAttribute((const void*)v.kPage, cudaFuncAttributeMaxDynamicSharedMemorySize, v.gen.smemBytes));
             if (v.gen.staged) {
                 // ring depth from the opt-in shared memory of the device (227 KB on sm_100), at most 4 stages
@@ -577,7 +614,20 @@ pgpu_status decideTableMode(pgpu_pipeline* p, Variant* v, const DevPage& pg, Var
     return bucketVariantOf(p, v, swapped);
 }
 
-pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
+// Slots of a table that does not exist yet: BigintGroupByHash sizing (expectedSize / fill ratio, operator/BigintGroupByHash.java:78-101)
+uint64_t initialTableCapacity(pgpu_pipeline* p, Variant* v) {
+    const GenResult& g = v->gen;
+    const uint64_t reserve = flushReserve(p, v);
+    uint64_t cap = (uint64_t)((double)(p->tableSizeHint > 0 ? p->tableSizeHint : p->plan->expectedGroups) / 0.6) + 1024;
+    if (g.buckets) cap = (uint64_t)((double)p->plan->expectedGroups / p->bucketOccupancy / 0.6) + 1024;  // keys per slot as the probe saw them
+    cap = std::max<uint64_t>(cap, reserve * 4 + 4096);
+    // key types that bound the number of groups (<= 1 M): size the table for the whole domain, once
+    if (g.keyDomain > 0 && g.keyDomain <= (double)(1 << 20)) cap = std::max<uint64_t>(cap, (uint64_t)(g.keyDomain / 0.7) + reserve * 2 + 4096);
+    return cap;
+}
+
+// sw: the page is a chunk of a partition-ordered batch (runSweep): the sweep kernel takes it
+pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg, const SweepArgs* sw = nullptr) {
     const GenResult& g = v->gen;
     // kernel parameter block: PageArgs<NC> = ColArg[NC] + rows
     std::vector<unsigned char> pa(sizeof(ColArg) * g.NC + 8);
@@ -622,12 +672,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         // grows the table (rehash) and replays exactly those rows. Nothing is dropped, nothing is over-allocated.
         const uint64_t reserve = flushReserve(p, v);
         if (!p->dSlots) {
-            uint64_t cap = (uint64_t)((double)(p->tableSizeHint > 0 ? p->tableSizeHint : p->plan->expectedGroups) / 0.6) + 1024;
-            if (g.buckets) cap = (uint64_t)((double)p->plan->expectedGroups / p->bucketOccupancy / 0.6) + 1024;  // keys per slot as the probe saw them
-            cap = std::max<uint64_t>(cap, reserve * 4 + 4096);
-            // key types that bound the number of groups (<= 1 M): size the table for the whole domain, once
-            if (g.keyDomain > 0 && g.keyDomain <= (double)(1 << 20)) cap = std::max<uint64_t>(cap, (uint64_t)(g.keyDomain / 0.7) + reserve * 2 + 4096);
-            pgpu_status st = growTable(p, v, cap);
+            pgpu_status st = growTable(p, v, initialTableCapacity(p, v));
             if (st) return st;
         }
         const int64_t n = pg.rows;
@@ -644,7 +689,7 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         pgpu_status st;
         // staged variant (bulk-async ring in shared memory) for pages long enough to fill the ring on every SM and whose
         // arrays are 16-byte aligned (cp.async.bulk); short or unaligned pages take the direct-load kernel
-        bool staged = v->kPageStaged && n >= (int64_t)g.stagedTile * p->numSMs;
+        bool staged = !sw && v->kPageStaged && n >= (int64_t)g.stagedTile * p->numSMs;
         if (staged) {
             for (int c : g.usedChannels) {
                 const ColArg& ca = pg.cols[c];
@@ -683,6 +728,13 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
                 void* targs[] = {ps.data(), &tt, &sc};
                 st = launch(p, v->kPage, tgrid, kThreads, (size_t)g.smemBytes, targs);
             }
+        } else if (sw) {
+            SweepArgs sa = *sw;
+            CU(cudaMemsetAsync(sa.ticket, 0, 4, p->stream));
+            void* args[] = {pa.data(), &t, &sc, &sa};
+            cudaKernel_t k = v->kPageSweep;
+            const int64_t nwarpTickets = (pg.rows + 1023) / 1024;
+            st = launch(p, k, (int)std::min<int64_t>((nwarpTickets + 7) / 8, (int64_t)p->numSMs * v->sweepBlocksPerSM), kThreads, (size_t)g.smemBytes, args);
         } else {
             void* args[] = {pa.data(), &t, &sc};
             st = launch(p, v->kPage, grid, kThreads, (size_t)g.smemBytes, args);
@@ -710,6 +762,182 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg) {
         return PGPU_OK;
     }
     return fail(p, PGPU_INVALID_STATE, "internal: launchPageKernel in COMPACT mode");
+}
+
+// Partition sweep (device header, "partition sweep") over a long device-resident page: count rows per table slice, scatter the
+// used channels' arrays into slice order, run the page kernel's sweep variant over the reordered rows. *swept = false when the
+// page is left to the ordinary path (table not much larger than L2, no memory for the reordered copy, bucketed table).
+pgpu_status runSweep(pgpu_pipeline* p, Variant* v, const DevPage& pg, bool* swept) {
+    *swept = false;
+    const GenResult& g = v->gen;
+    const Plan& plan = *p->plan;
+    if (!v->kPageSweep) return PGPU_OK;
+    if (p->tableMode == pgpu_pipeline::TABLE_BUCKETS) return PGPU_OK;
+    if (p->tableMode == pgpu_pipeline::TABLE_UNDECIDED) {
+        if (p->dSlots) return PGPU_OK;
+        DevPage first = pg;
+        first.rows = std::min<int64_t>(pg.rows, kHashChunkRows);
+        Variant* swapped = nullptr;
+        pgpu_status st = decideTableMode(p, v, first, &swapped);
+        if (st) return st;
+        if (swapped || p->tableMode != pgpu_pipeline::TABLE_PER_KEY) return PGPU_OK;
+    }
+    // test / experiment knobs: PGPU_TUNE_SWEEP_MIN_ROWS, PGPU_TUNE_SWEEP_MIN_TABLE_MB, PGPU_TUNE_SWEEP_BATCH_ROWS, PGPU_TUNE_SWEEP_K
+    auto knob = [](const char* name, int64_t dflt) { const char* e = getenv(name); return e ? (int64_t)atoll(e) : dflt; };
+    const int64_t minRows = knob("PGPU_TUNE_SWEEP_MIN_ROWS", kSweepMinRows);
+    if (pg.rows < minRows) return PGPU_OK;
+    const uint64_t cap = p->dSlots ? p->capacity : initialTableCapacity(p, v);
+    const size_t tableBytes = (size_t)cap * g.SLOTW * 8;
+    if (tableBytes < (size_t)knob("PGPU_TUNE_SWEEP_MIN_TABLE_MB", (int64_t)(kSweepMinTableBytes >> 20)) << 20) return PGPU_OK;
+    // Keys that arrive in runs or in key order are cheap as they are (run compaction makes one table update per run, neighbouring
+    // keys share table lines): measured on sf100 GROUP BY l_orderkey, runs of 4 rows, 19.7 ms on the ordinary path against 25 ms
+    // here; keys in no order 57 ms against 38 ms. The clustering probe of the bucketed table looks at the first 65536 keys.
+    if (!knob("PGPU_TUNE_SWEEP_FORCE", 0) && g.bucketKeyChannel >= 0 && pg.rows >= 1024) {
+        const ColArg& ca = pg.cols[g.bucketKeyChannel];
+        const Type& t = plan.input[g.bucketKeyChannel];
+        if (ca.values && !ca.ids && !ca.dvalues && !t.isVarWidth() && (t.width() == 4 || t.width() == 8)) {
+            unsigned long long* dOut = (unsigned long long*)p->dState;  // 64 words of scratch the hash path does not use
+            const int64_t n = std::min<int64_t>(pg.rows, 1 << 16);
+            CU(cudaMemsetAsync(dOut, 0, 72, p->stream));
+            CU(keyClustering(p->stream, ca.values, t.width(), n, dOut));
+            CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 72, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaStreamSynchronize(p->stream));
+            CU(cudaMemsetAsync(dOut, 0, 72, p->stream));
+            p->stats.kernel_launches++;
+            uint64_t near = 0;
+            for (int d = 0; d < 8; d++) near = std::max<uint64_t>(near, p->hostScalars[5 + d]);
+            const double jumps = (double)p->hostScalars[4] - 0.75 * (double)near;  // key changes that land on another table line
+            if (jumps < 0.45 * (double)n) return PGPU_OK;
+        }
+    }
+    // the reordered copy: one array per moved array of the used channels, each 256-byte aligned
+    struct Moved {
+        int channel;
+        int kind;   // 0 values, 1 nulls, 2 ids
+        int width;
+        size_t off;
+    };
+    std::vector<Moved> moved;
+    size_t perRow = 0;
+    for (int c : g.usedChannels) {
+        const Type& t = plan.input[c];
+        const ColArg& ca = pg.cols[c];
+        if (ca.ids) {
+            moved.push_back({c, 2, 4, 0});
+            perRow += 4;
+        } else if (ca.values) {  // RLE blocks have neither
+            const int w = t.isVarWidth() ? 16 : t.width();
+            moved.push_back({c, 0, w, 0});
+            perRow += w;
+            if (ca.nulls) {
+                moved.push_back({c, 1, 1, 0});
+                perRow += 1;
+            }
+        }
+    }
+    if (perRow == 0) return PGPU_OK;
+    static const bool trace = getenv("PGPU_TRACE_SWEEP") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = trace ? now() : 0;
+    // (cudaMemGetInfo costs 0.2 - 2 ms, now and then 75 ms: only asked when the buffer of an earlier batch does not already fit the page)
+    size_t freeB = 0, totalB = 0;
+    const bool fits = p->dSlots && p->sweepBuf.cap >= (size_t)pg.rows * perRow + moved.size() * 256;
+    if (!fits) CU(cudaMemGetInfo(&freeB, &totalB));
+    const double t1 = trace ? now() : 0;
+    const size_t budget = p->sweepBuf.cap + (size_t)((double)freeB * 0.6);
+    const size_t table0 = p->dSlots ? 0 : tableBytes;  // the table is still to be allocated
+    if (budget < table0 + (size_t)minRows * perRow) return PGPU_OK;
+    int64_t batchRows = std::min<int64_t>(pg.rows, (int64_t)((budget - table0) / perRow));
+    batchRows = std::min<int64_t>(batchRows, knob("PGPU_TUNE_SWEEP_BATCH_ROWS", batchRows));
+    if (batchRows < std::min<int64_t>(minRows, pg.rows)) return PGPU_OK;
+    int K = (int)std::min<size_t>(kPartMaxK, std::max<size_t>(8, (tableBytes + kSweepSliceBytes - 1) / kSweepSliceBytes));
+    K = (int)std::min<int64_t>(kPartMaxK, std::max<int64_t>(1, knob("PGPU_TUNE_SWEEP_K", K)));
+    pgpu_status st;
+    {
+        size_t need = 0;
+        for (auto& m : moved) {
+            m.off = need;
+            need += align256((size_t)batchRows * m.width);
+        }
+        if ((st = ensureDev(p, p->sweepBuf, need))) return st;
+        if ((st = ensureDev(p, p->sweepMeta, (size_t)kPartMaxK * 4 + 256 + (size_t)kPartMaxK * 8 + (size_t)(kPartMaxK + 1) * 8))) return st;
+    }
+    uint32_t* hist = (uint32_t*)p->sweepMeta.ptr;
+    uint32_t* ticket = hist + kPartMaxK;
+    uint64_t* cursor = (uint64_t*)((char*)p->sweepMeta.ptr + (size_t)kPartMaxK * 4 + 256);
+    uint64_t* start = cursor + kPartMaxK;
+    Scratch sc = scratchOf(p);
+    for (int64_t b0 = 0; b0 < pg.rows; b0 += batchRows) {
+        const int64_t bn = std::min(batchRows, pg.rows - b0);
+        // input slice [b0, b0 + bn) and the reordered page over sweepBuf
+        std::vector<ColArg> in = pg.cols, out = pg.cols;
+        for (int c : g.usedChannels) {
+            const Type& t = plan.input[c];
+            ColArg& ca = in[c];
+            if (ca.ids) ca.ids += b0;
+            else if (ca.values) ca.values = (const char*)ca.values + (size_t)b0 * (t.isVarWidth() ? 16 : t.width());
+            if (ca.nulls) ca.nulls += b0;
+        }
+        for (auto& m : moved) {
+            char* base = (char*)p->sweepBuf.ptr + m.off;
+            if (m.kind == 0) out[m.channel].values = base;
+            else if (m.kind == 1) out[m.channel].nulls = (const uint8_t*)base;
+            else out[m.channel].ids = (const int32_t*)base;
+        }
+        std::vector<unsigned char> pin(sizeof(ColArg) * g.NC + 8), pout(sizeof(ColArg) * g.NC + 8);
+        memcpy(pin.data(), in.data(), sizeof(ColArg) * g.NC);
+        memcpy(pin.data() + sizeof(ColArg) * g.NC, &bn, 8);
+        memcpy(pout.data(), out.data(), sizeof(ColArg) * g.NC);
+        memcpy(pout.data() + sizeof(ColArg) * g.NC, &bn, 8);
+        PartArgs pa{hist, cursor, (uint32_t)K, 0};
+        CU(cudaMemsetAsync(hist, 0, (size_t)kPartMaxK * 4, p->stream));
+        {
+            void* args[] = {pin.data(), &pa, &sc};
+            const int64_t ntiles = (bn + kTileRows - 1) / kTileRows;
+            if ((st = launch(p, v->kPartCount, (int)std::min<int64_t>(ntiles, (int64_t)p->numSMs * 8), kThreads, 0, args))) return st;
+        }
+        CU(partitionScan(p->stream, hist, (unsigned long long*)cursor, (unsigned long long*)start, K));
+        {
+            if (v->scatterBlocksPerSM == 1) {
+                int nb = 0;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v->kPartScatter, kPartThreads, partScatterSmem(K)) != cudaSuccess || nb < 1) {
+                    cudaGetLastError();
+                    nb = 1;
+                }
+                v->scatterBlocksPerSM = nb;
+            }
+            void* args[] = {pin.data(), pout.data(), &pa};
+            const int64_t ntiles = (bn + kPartTile - 1) / kPartTile;
+            if ((st = launch(p, v->kPartScatter, (int)std::min<int64_t>(ntiles, (int64_t)p->numSMs * v->scatterBlocksPerSM), kPartThreads, partScatterSmem(K), args))) return st;
+        }
+        const double t2 = trace ? now() : 0;
+        CU(cudaMemcpyAsync(&p->hostScalars[13], start + K, 8, cudaMemcpyDeviceToHost, p->stream));
+        CU(cudaStreamSynchronize(p->stream));
+        const double t3 = trace ? now() : 0;
+        const int64_t passed = (int64_t)p->hostScalars[13];  // rows that pass the filter
+        if (passed < 0 || passed > bn) return fail(p, PGPU_CUDA_ERROR, "internal: partition sweep row count");
+        p->stats.partition_sweeps++;
+        SweepArgs sw{start, ticket, 0, (uint32_t)K, 0};
+        for (int64_t r0 = 0; r0 < passed; r0 += kHashChunkRows) {
+            DevPage chunk;
+            chunk.rows = std::min(kHashChunkRows, passed - r0);
+            chunk.slack = passed - (r0 + chunk.rows);
+            chunk.cols = out;
+            for (auto& m : moved) {
+                ColArg& ca = chunk.cols[m.channel];
+                if (m.kind == 0) ca.values = (const char*)ca.values + (size_t)r0 * m.width;
+                else if (m.kind == 1) ca.nulls += r0;
+                else ca.ids += r0;
+            }
+            sw.row0 = r0;
+            if ((st = launchPageKernel(p, v, chunk, &sw))) return st;
+        }
+        if (trace)
+            fprintf(stderr, "[pgpu sweep] rows %lld passed %lld K %d free %.1f GB: memGetInfo %.2f ms, alloc + count/scatter launches %.2f ms, wait %.2f ms, sweep launches %.2f ms\n",
+                    (long long)bn, (long long)passed, K, freeB / 1e9, t1 - t0, t2 - t1, t3 - t2, now() - t3);
+    }
+    *swept = true;
+    return PGPU_OK;
 }
 
 // keepRows > 0: the first keepRows rows of every output column survive a reallocation (buffered small pages)
@@ -843,6 +1071,16 @@ pgpu_status processDevicePage(pgpu_pipeline* p, Variant* v, const pgpu_column* c
     int64_t chunk = g.mode == KernelMode::AGG_HASH ? kHashChunkRows : rows;
     if (v->kPageStaged) chunk = chunk / g.stagedTile * g.stagedTile;  // inner chunks are whole tiles: only the page's end is ragged
     for (int64_t r0 = 0; r0 < rows; r0 += chunk) {
+        if (v->kPageSweep) {
+            // a long device-resident page and a table far larger than L2: reorder the rest of the page by table slice first
+            DevPage rest;
+            rest.rows = rows - r0;
+            colArgsFor(r0, rest.cols);
+            bool swept = false;
+            pgpu_status st = runSweep(p, v, rest, &swept);
+            if (st) return st;
+            if (swept) return PGPU_OK;
+        }
         int64_t n = std::min(chunk, rows - r0);
         DevPage pg;
         pg.rows = n;
@@ -1630,6 +1868,8 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
         if (p->dPartials) cudaFree(p->dPartials);
         if (p->tileStatus.ptr) cudaFree(p->tileStatus.ptr);
         if (p->failLog.ptr) cudaFree(p->failLog.ptr);
+        if (p->sweepBuf.ptr) cudaFree(p->sweepBuf.ptr);
+        if (p->sweepMeta.ptr) cudaFree(p->sweepMeta.ptr);
         if (p->dSlots) cudaFree(p->dSlots);
         if (p->hostScalars) cudaFreeHost(p->hostScalars);
         for (auto& s : p->slots) {

@@ -26,7 +26,44 @@ __global__ void k_key_clustering(const T* __restrict__ keys, long long n, unsign
     }
 }
 
+// one block of 1024 threads, one partition per thread
+__global__ void k_partition_scan(const unsigned* __restrict__ hist, unsigned long long* cursor, unsigned long long* start, int K) {
+    __shared__ unsigned long long warpSum[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long v = (int)threadIdx.x < K ? hist[threadIdx.x] : 0ull;
+    unsigned long long x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+    }
+    if (lane == 31) warpSum[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long w = warpSum[lane], wx = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long y = __shfl_up_sync(0xffffffffu, wx, d);
+            if (lane >= d) wx += y;
+        }
+        warpSum[lane] = wx - w;  // exclusive
+    }
+    __syncthreads();
+    const unsigned long long excl = warpSum[warp] + x - v;
+    if ((int)threadIdx.x < K) {
+        cursor[threadIdx.x] = excl;
+        start[threadIdx.x] = excl;
+        if ((int)threadIdx.x == K - 1) start[K] = excl + v;
+    }
+}
+
 }  // namespace
+
+cudaError_t partitionScan(cudaStream_t stream, const unsigned* hist, unsigned long long* cursor, unsigned long long* start, int K) {
+    if (K < 1 || K > 1024) return cudaErrorInvalidValue;
+    k_partition_scan<<<1, 1024, 0, stream>>>(hist, cursor, start, K);
+    return cudaGetLastError();
+}
 
 cudaError_t keyClustering(cudaStream_t stream, const void* keys, int width, int64_t n, unsigned long long* out) {
     if (n < 2) return cudaSuccess;

@@ -11,4 +11,8 @@ namespace pgpu {
 // start at a multiple of 8 (TPC-H order keys start at 8n + 1). `width` = 4 or 8 bytes per key. out[0..8] zeroed by the caller.
 cudaError_t keyClustering(cudaStream_t stream, const void* keys, int width, int64_t n, unsigned long long* out);
 
+// Partition sweep (device/pgpu_device.cuh "partition sweep"): rows per partition -> first row of every partition.
+// cursor[k] = start[k] = hist[0] + ... + hist[k - 1]; start[K] = the total. K <= 1024.
+cudaError_t partitionScan(cudaStream_t stream, const unsigned* hist, unsigned long long* cursor, unsigned long long* start, int K);
+
 }  // namespace pgpu

@@ -6,8 +6,8 @@ import numpy as np
 import pytest
 
 from presto_b200.operators import GpuPipelineOperator, plan_text, toPages
-from presto_b200.relational import call, constant, field
-from presto_b200.spi import BIGINT, DOUBLE, INTEGER, BOOLEAN, IntArrayBlock, LongArrayBlock, Page
+from presto_b200.relational import call, compare, constant, field
+from presto_b200.spi import BIGINT, DOUBLE, INTEGER, IntArrayBlock, LongArrayBlock, Page
 
 from oracle_op import OracleOperator
 
@@ -116,7 +116,7 @@ def test_gpu_merge_with_filter_and_growing_buffer():
         pages.append(sequence_page(n, start))
         start += n
     pages.insert(30, sequence_page(40_000, start))
-    filt = call("$operator$EQUAL", BOOLEAN, call("$operator$MODULUS", BIGINT, field(0, BIGINT), constant(97, BIGINT)), constant(3, BIGINT))
+    filt = compare("eq", call("modulus", BIGINT, field(0, BIGINT), constant(97, BIGINT)), constant(3, BIGINT))
     plan = plan_text(TYPES, filt, [field(2, DOUBLE), field(0, BIGINT)], mergeMinRows=256, mergeMinBytes=500_000)
     op = GpuPipelineOperator(plan, 0)
     got = toPages(op, pages)

@@ -82,6 +82,35 @@ for name in ("q1", "q6", "q1dict", "highcard", "highcard_shuffled", "highcard_bu
                          "source": "profiles/%s_%s_ncu_raw.txt (ncu --set full --clock-control none, one steady-state launch)" % (tag, name)}
         lines.append("| %s | %.0f M | %.3f | %.2f | %.2f | %.2f | %.0f | %.2f |" % (name, rows / 1e6, ms, dram / 1e9, dram / rows, dram / rows / ALG_BYTES[name],
                                                                                  dram / ms / 1e6, dram / ms / 1e6 / peak))
+# GROUP BY over keys in no order runs as three kernels (partition sweep): DRAM bytes of one whole step from the launch list
+# (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum over bench.py --workload highcard_shuffled --steps 1)
+ll = os.path.join(G, "launches_highcard_shuffled.csv")
+if os.path.exists(ll):
+    shutil.copy(ll, os.path.join(P, "%s_launches_highcard_shuffled.csv" % tag))
+    rr = [r for r in csv.reader(open(ll)) if len(r) > 10]
+    hdr = rr[0]
+    ik, im, iv, iid = hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Value"), hdr.index("ID")
+    launches = {}
+    for r_ in rr[1:]:
+        launches.setdefault(int(r_[iid]), {"kernel": r_[ik]})[r_[im]] = float(r_[iv].replace(",", ""))
+    ids = sorted(launches)
+    starts = [i for i in ids if launches[i]["kernel"].startswith("pgpu_k_part_count")]
+    if starts:
+        step = []
+        for i in ids[ids.index(starts[-1]):]:
+            if launches[i]["kernel"].startswith("pgpu_k_emit"):
+                break
+            step.append(launches[i])
+        if step and any(x["kernel"].startswith("pgpu_k_page_sweep") for x in step):
+            dram = sum(x.get("dram__bytes_read.sum", 0) + x.get("dram__bytes_write.sum", 0) for x in step)
+            ms = sum(x.get("gpu__time_duration.sum", 0) for x in step) / 1e6
+            rows = LAUNCH_ROWS["q6"]
+            traffic["highcard_shuffled"] = {"dram_bytes_per_row": dram / rows, "dram_bytes_per_launch": dram / len(step), "launch_rows": rows, "launch_ms_under_ncu": ms,
+                                            "algorithmic_bytes_per_row": 16, "ratio_to_algorithmic": dram / rows / 16, "dram_gbs_under_ncu": dram / ms / 1e6,
+                                            "launches": len(step),
+                                            "source": "profiles/%s_launches_highcard_shuffled.csv (ncu launch list of one step: pgpu_k_part_count + k_partition_scan + pgpu_k_part_scatter + %d x pgpu_k_page_sweep)" % (tag, sum(1 for x in step if x["kernel"].startswith("pgpu_k_page_sweep")))}
+            lines = [l for l in lines if not l.startswith("| highcard_shuffled |")]
+            lines.append("| highcard_shuffled (whole step: count + scatter + sweeps) | %.0f M | %.3f | %.2f | %.2f | %.2f | %.0f | %.2f |" % (rows / 1e6, ms, dram / 1e9, dram / rows, dram / rows / 16, dram / ms / 1e6, dram / ms / 1e6 / peak))
 with open(os.path.join(P, "traffic.json"), "w") as f:
     json.dump(traffic, f, indent=1, sort_keys=True)
     f.write("\n")
