@@ -2896,8 +2896,10 @@ pgpu_status pgpu_ipc_open(int32_t device, const uint8_t* handle, void** mapped_b
     if (cudaSetDevice(device) != cudaSuccess) return PGPU_CUDA_ERROR;
     cudaIpcMemHandle_t h;
     memcpy(&h, handle, sizeof h);
-    if (cudaIpcOpenMemHandle(mapped_base, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+    cudaError_t e = cudaIpcOpenMemHandle(mapped_base, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
         cudaGetLastError();
+        pgpu::setLastGlobalError(std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e));
         return PGPU_CUDA_ERROR;
     }
     return PGPU_OK;

@@ -19,8 +19,9 @@ os.makedirs(P, exist_ok=True)
 # (csrc/pipeline.cpp), rounded down to whole staged tiles (Q1: 1920 rows, dictionary Q1: 960); a global aggregation is one launch
 CHUNK = 64 << 20
 LAUNCH_ROWS = {"q1": CHUNK // 1920 * 1920, "q1dict": CHUNK // 960 * 960, "q6": 600_037_902, "highcard": CHUNK, "highcard_shuffled": CHUNK,
-               "highcard_buckets": CHUNK}
-ALG_BYTES = {"q1": 46, "q1dict": 32, "q6": 28, "highcard": 16, "highcard_shuffled": 16, "highcard_buckets": 16}
+               "highcard_buckets": CHUNK, "highcard_shuffled_scatter": 600_037_902, "highcard_shuffled_plain": CHUNK}
+ALG_BYTES = {"q1": 46, "q1dict": 32, "q6": 28, "highcard": 16, "highcard_shuffled": 16, "highcard_buckets": 16, "highcard_shuffled_scatter": 32,
+             "highcard_shuffled_plain": 16}
 KEEP = ("Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread",
         "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic", "smsp__inst_executed.sum",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -37,6 +38,7 @@ def copy(name, dst=None):
 
 
 for f in ("bench_default.json", "bench_ref.json", "bench_highcard_buckets.json", "bench_highcard_buckets_casfirst.json", "randtable.txt",
+          "bench_highcard_shuffled_nosweep.json", "parquet_ingest.json",
           "launches_q1.csv", "launches_highcard.csv", "ingest_serialized.json"):
     copy(f)
 for t in (16, 8, 4, 2, 1):
@@ -45,7 +47,7 @@ for t in (16, 8, 4, 2, 1):
 traffic = {}
 peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
 lines = []
-for name in ("q1", "q6", "q1dict", "highcard", "highcard_shuffled", "highcard_buckets", "highcard_emit"):
+for name in ("q1", "q6", "q1dict", "highcard", "highcard_shuffled", "highcard_shuffled_scatter", "highcard_shuffled_plain", "highcard_buckets", "highcard_emit"):
     rep = os.path.join(G, name + "_full.ncu-rep")
     if not os.path.exists(rep):
         continue
@@ -143,6 +145,13 @@ with open(os.path.join(P, "%s_summary.md" % tag), "w") as out:
         if os.path.exists(src) and os.path.getsize(src):
             v = json.loads(open(src).read().strip().splitlines()[-1])
             out.write("\nGROUP BY l_orderkey, %s (PGPU_TUNE_BUCKETS=1): %.3f ms/step, kernel %.3f ms/step.\n" % (title, v["ms_per_step"], v["roofline"]["kernel_ms_per_step"]))
+    src = os.path.join(G, "bench_highcard_shuffled_nosweep.json")
+    if os.path.exists(src) and os.path.getsize(src):
+        v = json.loads(open(src).read().strip().splitlines()[-1])
+        out.write("\nGROUP BY shuffled l_orderkey without the partition sweep (PGPU_TUNE_SWEEP=0): %.3f ms/step, kernel %.3f ms/step.\n" % (v["ms_per_step"], v["roofline"]["kernel_ms_per_step"]))
+    src = os.path.join(G, "parquet_ingest.json")
+    if os.path.exists(src) and os.path.getsize(src):
+        out.write("\n## Parquet ingest (tools/parquet_ingest_bench.py: Q1 over the same rows as plain blocks and as uncompressed Parquet row groups)\n\n```\n" + open(src).read().strip() + "\n```\n")
     rt = os.path.join(G, "randtable.txt")
     if os.path.exists(rt):
         out.write("\n## random 32-byte slot updates into an 8.6 GB table (tools/microbench/randtable.cu): the floor under shuffled keys\n\n```\n" + open(rt).read() + "```\n")
