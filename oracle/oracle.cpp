@@ -805,6 +805,7 @@ struct AccState {
     bool isNull = true;    // Nullable{Long,Double}State
     int64_t lval = 0;
     double dval = 0.0;
+    Dec128 qval;           // min / max over long DECIMAL (NullableInt128State-like: the value as the block holds it)
 };
 
 struct Accumulator {
@@ -865,8 +866,11 @@ struct Accumulator {
                             take = key(v) < key(s.dval);
                         }
                         if (take) s.dval = v;
-                    } else if (t.isLongDecimal()) {
-                        throw OracleError(PGPU_NOT_SUPPORTED, "min/max(long decimal)");
+                    } else if (t.isLongDecimal()) {  // Int128 state compared with UnscaledDecimal128Arithmetic.compare (decimal128.h)
+                        const Dec128& v = arg->q[k];
+                        if (s.isNull) { s.isNull = false; s.qval = v; break; }
+                        const int c = compare(v, s.qval);
+                        if (isMax ? c > 0 : c < 0) s.qval = v;
                     } else {
                         int64_t v = arg->i[k];
                         if (s.isNull) { s.isNull = false; s.lval = v; break; }
@@ -923,6 +927,7 @@ struct Accumulator {
                     Vec v;
                     v.type = ch[0]->type;
                     if (t.kind == TypeKind::DOUBLE) v.d.push_back(ch[0]->d[k]);
+                    else if (t.isLongDecimal()) v.q.push_back(ch[0]->q[k]);
                     else v.i.push_back(ch[0]->i[k]);
                     addInput(&g, 1, &v, nullptr);
                     break;
@@ -1163,6 +1168,7 @@ struct Oracle {
                     case AggFn::MIN:
                     case AggFn::MAX:
                         if (t.kind == TypeKind::DOUBLE) putD(result[oc++], s.dval, s.isNull);
+                        else if (t.isLongDecimal()) putQ(result[oc++], s.qval, s.isNull);
                         else putI(result[oc++], s.lval, s.isNull);
                         break;
                 }

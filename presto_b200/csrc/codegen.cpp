@@ -1092,6 +1092,18 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     };
     auto sel1 = [](const std::string& cond, const std::string& e, const std::string& zero) { return cond == "true" ? e : "(" + cond + " ? " + e + " : " + zero + ")"; };
 
+    // min / max over long DECIMAL (AbstractMinMaxAggregationFunction.java:274-306 on Int128 values): ONE 128-bit cell = two words
+    // [low, high] of the order-preserving image (two's complement value with the sign bit flipped; complemented for min), updated
+    // with a 16-byte compare-and-swap loop. The pair must be 16-byte aligned inside the 32-byte aligned slot (and in the global
+    // aggregation's state array): a zero word is put in front when the pair would start at an odd word.
+    const bool taglessByKey = res.mode == KernelMode::AGG_HASH && res.KW >= 1 && res.KW <= 2 && keyLen < res.KW * 8 && !getenv("PGPU_TUNE_TAGGED");
+    const int cellBaseWord = res.mode == KernelMode::AGG_HASH ? (taglessByKey ? 0 : 1) + res.KW : 0;
+    auto minMax128Cell = [&](bool isMax, const std::string& ident, const std::string& cond, const std::string& v128) -> int {
+        if ((cellBaseWord + nw) & 1) getCell("pad", "pad" + std::to_string(nw), 1, {"0ull"});
+        const std::string img = "((u128)(" + v128 + ") ^ ((u128)1 << 127))";
+        const std::string enc = isMax ? img : "(~" + img + ")";
+        return getCell(isMax ? "max128" : "min128", ident, 2, {sel1(cond, "(u64)" + enc, "0ull"), sel1(cond, "(u64)(" + enc + " >> 64)", "0ull")});
+    };
     struct AggCells {
         int cnt = -1, sum = -1, ext = -1;
     };
@@ -1142,7 +1154,8 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
                     } else if (t.kind == TypeKind::BOOLEAN) {
                         k = "(i64)(" + x.v + " ? 1 : 0)";
                     } else if (t.isLongDecimal()) {
-                        unsupported(std::string(aggName(a.fn)) + "(" + t.str() + ")");
+                        ac.ext = minMax128Cell(isMax, vid, cond, "(i128)" + x.v);
+                        break;
                     } else {
                         k = "(i64)" + x.v;
                     }
@@ -1197,8 +1210,11 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
                     std::string cond = nn(x), k;
                     if (t.kind == TypeKind::DOUBLE) k = isMax ? "((" + x.v + " != " + x.v + ") ? (i64)0x8000000000000000ull : f64_order_key(" + x.v + "))" : "f64_order_key(" + x.v + ")";
                     else if (t.kind == TypeKind::BOOLEAN) k = "(i64)(" + x.v + " ? 1 : 0)";
-                    else if (t.isLongDecimal()) unsupported(std::string(aggName(a.fn)) + "(" + t.str() + ")");
-                    else k = "(i64)" + x.v;
+                    else if (t.isLongDecimal()) {
+                        ac.cnt = getCell("cnt", "F" + std::to_string(a.arg), 1, {sel1(cond, "1ull", "0ull")});
+                        ac.ext = minMax128Cell(isMax, "F" + std::to_string(a.arg), cond, "(i128)" + x.v);
+                        break;
+                    } else k = "(i64)" + x.v;
                     std::string enc = isMax ? "((u64)" + k + " ^ 0x8000000000000000ull)" : "(~((u64)" + k + " ^ 0x8000000000000000ull))";
                     ac.cnt = getCell("cnt", "F" + std::to_string(a.arg), 1, {sel1(cond, "1ull", "0ull")});
                     ac.ext = getCell(isMax ? "max" : "min", "F" + std::to_string(a.arg), 1, {sel1(cond, enc, "0ull")});
@@ -1210,7 +1226,8 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     }
     res.NW = nw;
     for (auto& c : cells)
-        for (int j = 0; j < c.nwords; j++) res.cellKinds.push_back(c.kind == "sumd" ? 1 : (c.kind == "max" || c.kind == "min") ? 2 : c.kind == "cnt" ? 3 : 0);
+        for (int j = 0; j < c.nwords; j++)
+            res.cellKinds.push_back(c.kind == "sumd" ? 1 : (c.kind == "max" || c.kind == "min") ? 2 : c.kind == "cnt" ? 3 : (c.kind == "max128" || c.kind == "min128") ? 4 + j : 0);
     // hot words: cells with the same kind and the same per-row contribution expression share one word in the scan loop
     std::vector<int> hotOf((size_t)nw, 0), hotKinds;
     {
@@ -1263,6 +1280,8 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     // (the staging bound uses NW, not this signature's NH: whether a plan is bucketed must not depend on which pages carry nulls)
     const int runsBytesAnySig = 8 * ((KW + NWA) * 128 * 8 + 256);
     bool bucketsOk = highCard && fields.size() == 1 && runsBytesAnySig <= 64 * 1024 && NW > 0 && keyLen <= KW * 8 - 2 && fields[0].byteOffset < 7;
+    for (int k : res.cellKinds)
+        if (k >= 4) bucketsOk = false;  // 128-bit cells need their alignment inside the slot: one key per slot only
     if (bucketsOk) {
         const TypeKind k0 = fields[0].type.kind;
         bucketsOk = k0 == TypeKind::BIGINT || k0 == TypeKind::INTEGER || k0 == TypeKind::DATE || (k0 == TypeKind::DECIMAL && fields[0].type.isShortDecimal());
@@ -1362,23 +1381,36 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     src << "    PGPU_DEV static void identity_ptr(u64* a) {\n";
     for (int w = 0; w < NH; w++) src << "        a[" << w << "] = 0ull;\n";
     src << "    }\n";
+    // kinds 4 / 5 = the low / high word of a 128-bit maximum (min / max over long DECIMAL): handled as a pair at the low word
     auto emitCombine = [&](const char* name, const char* sigA, const char* sigB) {
         src << "    PGPU_DEV static void " << name << "(" << sigA << ", " << sigB << ") {\n";
-        for (int w = 0; w < NH; w++) src << "        a[" << w << "] = cell_combine<" << kindName(hotKinds[w]) << ">(a[" << w << "], b[" << w << "]);\n";
+        for (int w = 0; w < NH; w++) {
+            if (hotKinds[w] == 4) src << "        max128_combine(a[" << w << "], a[" << w + 1 << "], b[" << w << "], b[" << w + 1 << "]);\n";
+            else if (hotKinds[w] != 5) src << "        a[" << w << "] = cell_combine<" << kindName(hotKinds[w]) << ">(a[" << w << "], b[" << w << "]);\n";
+        }
         src << "    }\n";
     };
     emitCombine("combine", "u64 (&a)[NHA]", "const u64 (&b)[NHA]");
     emitCombine("combine_ptr", "u64* a", "const u64 (&b)[NHA]");
     emitCombine("combine_ptr_to", "u64 (&a)[NHA]", "const u64* b");
     src << "    PGPU_DEV static void warp_reduce_cells(u64 (&a)[NHA]) {\n";
-    for (int w = 0; w < NH; w++) src << "        a[" << w << "] = warp_reduce<" << kindName(hotKinds[w]) << ">(a[" << w << "]);\n";
+    for (int w = 0; w < NH; w++) {
+        if (hotKinds[w] == 4) src << "        max128_warp_reduce(a[" << w << "], a[" << w + 1 << "]);\n";
+        else if (hotKinds[w] != 5) src << "        a[" << w << "] = warp_reduce<" << kindName(hotKinds[w]) << ">(a[" << w << "]);\n";
+    }
     src << "    }\n";
     // hot -> cells expansion: atomically into a table slot, or plainly into the global-aggregation state
     src << "    PGPU_DEV static void atomic_cells(u64* cells, const u64 (&hot)[NHA]) {\n";
-    for (int w = 0; w < NW; w++) src << "        cell_atomic<" << kindName(res.cellKinds[w]) << ">(cells + " << w << ", hot[" << hotOf[w] << "]);\n";
+    for (int w = 0; w < NW; w++) {
+        if (res.cellKinds[w] == 4) src << "        max128_atomic(cells + " << w << ", hot[" << hotOf[w] << "], hot[" << hotOf[w + 1] << "]);\n";
+        else if (res.cellKinds[w] != 5) src << "        cell_atomic<" << kindName(res.cellKinds[w]) << ">(cells + " << w << ", hot[" << hotOf[w] << "]);\n";
+    }
     src << "    }\n";
     src << "    PGPU_DEV static void merge_cells(u64* cells, const u64 (&hot)[NHA]) {\n";
-    for (int w = 0; w < NW; w++) src << "        cells[" << w << "] = cell_combine<" << kindName(res.cellKinds[w]) << ">(cells[" << w << "], hot[" << hotOf[w] << "]);\n";
+    for (int w = 0; w < NW; w++) {
+        if (res.cellKinds[w] == 4) src << "        max128_combine(cells[" << w << "], cells[" << w + 1 << "], hot[" << hotOf[w] << "], hot[" << hotOf[w + 1] << "]);\n";
+        else if (res.cellKinds[w] != 5) src << "        cells[" << w << "] = cell_combine<" << kindName(res.cellKinds[w]) << ">(cells[" << w << "], hot[" << hotOf[w] << "]);\n";
+    }
     src << "    }\n";
 
     // ---- eval
@@ -1509,6 +1541,11 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
                 return isMax ? "(i64)(" + raw + " ^ 0x8000000000000000ull)" : "(i64)((~" + raw + ") ^ 0x8000000000000000ull)";
             };
             auto storeMinMax = [&](int k, bool isMax) {
+                if (t.isLongDecimal()) {  // the image back to the value, then the block's sign-magnitude words
+                    const std::string img = "(((u128)" + cw(ac.ext, 1) + " << 64) | (u128)" + cw(ac.ext, 0) + ")";
+                    L("{ raw128 q = dec_to_raw((i128)(" + std::string(isMax ? "" : "~") + img + " ^ ((u128)1 << 127))); u64* o = (u64*)out.c[" + O(k) + "].values + 2 * pos; o[0] = q.lo; o[1] = q.hi; }");
+                    return;
+                }
                 std::string kx = extDecode(isMax);
                 if (t.kind == TypeKind::DOUBLE) {
                     if (isMax) L("{ i64 kx = " + kx + "; ((double*)out.c[" + O(k) + "].values)[pos] = (kx == (i64)0x8000000000000000ull) ? u2d(0x7ff8000000000000ull) : f64_from_order_key(kx); }");

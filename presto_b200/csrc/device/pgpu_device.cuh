@@ -421,6 +421,17 @@ PGPU_DEV void cell_atomic(u64* addr, u64 v) {
     else { if (v) atomicMax(addr, v); }
 }
 
+// 128-bit maximum held in two cell words [low, high] (min / max over long DECIMAL; the plan compiler maps values to an
+// order-preserving unsigned image and keeps the pair 16-byte aligned)
+PGPU_DEV void max128_combine(u64& alo, u64& ahi, u64 blo, u64 bhi) {
+    if (bhi > ahi || (bhi == ahi && blo > alo)) {
+        alo = blo;
+        ahi = bhi;
+    }
+}
+PGPU_DEV void max128_warp_reduce(u64& lo, u64& hi);   // after shfl_xor_u64
+PGPU_DEV void max128_atomic(u64* cell, u64 lo, u64 hi);  // after ld_relaxed_u128 / cas_u128
+
 // ------------------------------------------------------------------------------------------------ HBM hash table
 #define TAG_EMPTY 0ull
 #define TAG_LOCKED 1ull
@@ -452,6 +463,23 @@ PGPU_DEV void cas_u128(u64* p, u64 clo, u64 chi, u64 nlo, u64 nhi, u64& olo, u64
                  : "=l"(olo), "=l"(ohi)
                  : "l"(clo), "l"(chi), "l"(nlo), "l"(nhi), "l"(p)
                  : "memory");
+}
+PGPU_DEV void max128_warp_reduce(u64& lo, u64& hi) {
+#pragma unroll
+    for (int m = 16; m >= 1; m >>= 1) max128_combine(lo, hi, shfl_xor_u64(lo, m), shfl_xor_u64(hi, m));
+}
+// compare-and-swap loop: most updates do not raise the maximum and end after the load
+PGPU_DEV void max128_atomic(u64* cell, u64 lo, u64 hi) {
+    if ((lo | hi) == 0ull) return;  // the identity: nothing to contribute
+    u64 clo, chi;
+    ld_relaxed_u128(cell, clo, chi);
+    while (hi > chi || (hi == chi && lo > clo)) {
+        u64 olo, ohi;
+        cas_u128(cell, clo, chi, lo, hi, olo, ohi);
+        if (olo == clo && ohi == chi) return;
+        clo = olo;
+        chi = ohi;
+    }
 }
 #define KEY_MARK 0x8000000000000000ull  // top bit of the last key word: "slot occupied" (tagless slots)
 

@@ -3,7 +3,7 @@
   aggregate KATs   operator/aggregation/AbstractTestAggregationFunction.java:84-143 — every aggregate is run over the
                    sequence blocks start..start+length for (0,0) (0,1) (0,5) (-10,5) (2,4), over 10 NULLs, and over 10
                    values alternating with NULLs; expectations are the closed forms of Test{DoubleSum,LongSum,Count,
-                   CountColumn,DoubleAverage,LongAverage,LongMin,LongMax,DoubleMin,DoubleMax,ShortDecimalSum,LongDecimalSum,
+                   CountColumn,DoubleAverage,LongAverage,LongMin,LongMax,DoubleMin,DoubleMax,LongDecimalMin,LongDecimalMax,ShortDecimalSum,LongDecimalSum,
                    ShortDecimalAverage,LongDecimalAverage}Aggregation.java#getExpectedValue
   hash aggregation operator/TestHashAggregationOperator.java:161-219 (40 000 groups x 3 pages -> (i, 3, 3i, i, 3, 3)),
                    :222-271 (global default row over empty input), :477-560 (multi-page output)
@@ -64,6 +64,13 @@ def aggregate_function_cases():
     add("max_double", DOUBLE, float, [Aggregation("max", DOUBLE, 0, DOUBLE)], lambda v: (max(v) if v else None,))
     add("min_integer", INTEGER, int, [Aggregation("min", INTEGER, 0, INTEGER)], lambda v: (min(v) if v else None,))
     add("max_date", DATE, int, [Aggregation("max", DATE, 0, DATE)], lambda v: (max(v) if v else None,))
+    # TestLongDecimalMinAggregation / TestLongDecimalMaxAggregation: DECIMAL(30, 5), BigDecimal.valueOf(i) = unscaled i * 10^5;
+    # expected start / start + length - 1. Large magnitudes of both signs are in tests/test_gpu_operators.py.
+    big = lambda x: int(x) * 10**5
+    add("min_long_decimal", dec_long, big, [Aggregation("min", dec_long, 0, dec_long)], lambda v: (min(v) if v else None,))
+    add("max_long_decimal", dec_long, big, [Aggregation("max", dec_long, 0, dec_long)], lambda v: (max(v) if v else None,))
+    add("min_short_decimal", dec_short, int, [Aggregation("min", dec_short, 0, dec_short)], lambda v: (min(v) if v else None,))
+    add("max_short_decimal", dec_short, int, [Aggregation("max", dec_short, 0, dec_short)], lambda v: (max(v) if v else None,))
     add("sum_short_decimal", dec_short, int, [Aggregation("sum", dec_sum_out(dec_short), 0, dec_short)], lambda v: (sum(v) if v else None,))
     add("sum_long_decimal", dec_long, int, [Aggregation("sum", dec_sum_out(dec_long), 0, dec_long)], lambda v: (sum(v) if v else None,))
     add("avg_short_decimal", dec_short, int, [Aggregation("avg", dec_short, 0, dec_short)], lambda v: (_avg_decimal(v),))

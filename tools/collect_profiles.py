@@ -97,12 +97,18 @@ if os.path.exists(ll):
         launches.setdefault(int(r_[iid]), {"kernel": r_[ik]})[r_[im]] = float(r_[iv].replace(",", ""))
     ids = sorted(launches)
     starts = [i for i in ids if launches[i]["kernel"].startswith("pgpu_k_part_count")]
-    if starts:
-        step = []
-        for i in ids[ids.index(starts[-1]):]:
+    step = []
+    for st_ in reversed(starts):  # the last COMPLETE step (the capture may end inside one)
+        step, complete = [], False
+        for i in ids[ids.index(st_):]:
             if launches[i]["kernel"].startswith("pgpu_k_emit"):
+                complete = True
                 break
             step.append(launches[i])
+        if complete:
+            break
+        step = []
+    if starts:
         if step and any(x["kernel"].startswith("pgpu_k_page_sweep") for x in step):
             dram = sum(x.get("dram__bytes_read.sum", 0) + x.get("dram__bytes_write.sum", 0) for x in step)
             ms = sum(x.get("gpu__time_duration.sum", 0) for x in step) / 1e6

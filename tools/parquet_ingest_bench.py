@@ -27,7 +27,7 @@ def main():
     files = []
     for pg in pages:
         b = pg.blocks
-        t = pa.table({"returnflag": pa.array([chr(x) for x in b[0].values[:rows_per_group]]), "linestatus": pa.array([chr(x) for x in b[1].values[:rows_per_group]]),
+        t = pa.table({"returnflag": pa.array([chr(x) for x in b[0].data[:rows_per_group]]), "linestatus": pa.array([chr(x) for x in b[1].data[:rows_per_group]]),
                       "quantity": pa.array(b[2].values.view("f8")), "extendedprice": pa.array(b[3].values.view("f8")), "discount": pa.array(b[4].values.view("f8")),
                       "tax": pa.array(b[5].values.view("f8")), "shipdate": pa.array(b[6].values, pa.date32())})
         buf = io.BytesIO()
