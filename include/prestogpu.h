@@ -147,8 +147,7 @@ pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size
 pgpu_status pgpu_get_serialized_output(pgpu_pipeline* p, const uint8_t** data, size_t* len, int64_t* rows);
 /* One column chunk of a Parquet row group, as it lies in the file: from the first page header of the chunk (dictionary page if
  * there is one) to its end — ColumnChunkMetaData.getStartingPos() / getTotalSize() as ParquetReader.readColumnChunk slices it
- * (lib/trino-parquet/src/main/java/io/trino/parquet/reader/ParquetReader.java:244-268). Pages must be UNCOMPRESSED (the caller
- * undoes the codec, as PageReader.readPage does, .../reader/PageReader.java:63-99). */
+ * (lib/trino-parquet/src/main/java/io/trino/parquet/reader/ParquetReader.java:244-268). */
 typedef struct pgpu_parquet_chunk {
     const uint8_t* data;          /* host pointer                                                            */
     size_t len;
@@ -156,7 +155,9 @@ typedef struct pgpu_parquet_chunk {
     int32_t max_definition_level; /* 0 = required, 1 = optional flat column (nested columns are rejected)     */
     int64_t num_values;           /* ColumnMetaData.num_values = rows of the row group for a flat column     */
     int32_t type_length;          /* FIXED_LEN_BYTE_ARRAY: bytes per value (1..16, a DECIMAL's unscaled value); else 0 */
-    int32_t reserved;
+    int32_t codec;                /* parquet.thrift CompressionCodec of the chunk's pages: 0 UNCOMPRESSED, 1 SNAPPY, 7 LZ4_RAW (others:
+                                   * PGPU_NOT_SUPPORTED). Compressed pages are inflated on the host, as the reference does
+                                   * (ParquetCompressionUtils.java:43-70), then take the same path                          */
 } pgpu_parquet_chunk;
 /* Operator.addInput of the Page that ParquetReader.nextPage / readBlock -> PrimitiveColumnReader.readPrimitive would build from
  * one row group (.../reader/ParquetReader.java:211-268, PrimitiveColumnReader.java:148-317): chunk c feeds input channel c
@@ -168,7 +169,7 @@ typedef struct pgpu_parquet_chunk {
  * read on the host; each chunk goes to the device in ONE copy and definition levels, dictionary ids and booleans are expanded
  * there. A chunk whose data pages are all dictionary encoded is consumed as a DictionaryBlock (ids + dictionary page), never
  * materialised. Data pages v1 and v2; PLAIN, PLAIN_DICTIONARY, RLE_DICTIONARY, RLE (levels, booleans). Rejected with
- * PGPU_NOT_SUPPORTED: compressed pages, nested columns, DELTA_* / BYTE_STREAM_SPLIT encodings, INT96 / FLOAT,
+ * PGPU_NOT_SUPPORTED: GZIP / ZSTD / BROTLI / LZO pages, nested columns, DELTA_* / BYTE_STREAM_SPLIT encodings, INT96 / FLOAT,
  * var-width chunks that are not dictionary encoded throughout. */
 pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chunk* chunks, int32_t nchunks, int64_t rows);
 /* What pgpu_add_parquet_row_group reads on the host, without a GPU: info[0] data pages, [1] dictionary entries (-1: none), [2] every

@@ -153,7 +153,7 @@ JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addParquetRowG
         chunks[c].max_definition_level = def[c];
         chunks[c].num_values = count[c];
         chunks[c].type_length = tl[c];
-        chunks[c].reserved = 0;
+        chunks[c].codec = 0;  /* the Java side hands over decompressed chunks (PageReader.readPage has run) */
     }
     pgpu_status st = pgpu_add_parquet_row_group(p, chunks, (int32_t)n, rows);
     if (st != PGPU_OK) throwTrino(env, st, pgpu_last_error(p));

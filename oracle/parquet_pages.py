@@ -232,7 +232,20 @@ def plain_values(buf, pos, end, ptype, count, type_length=0):
     raise Unsupported("parquet physical type %d" % ptype)
 
 
-def decode_chunk(buf, ptype, max_def, num_values, type_length=0):
+CODEC_NAMES = {1: "snappy", 7: "lz4_raw"}   # parquet.thrift CompressionCodec -> pyarrow codec name
+
+
+def _inflate(codec, raw, size):
+    """one compressed page body -> bytes, with pyarrow's codec (Arrow's C++ implementation: independent of the product's decoders)"""
+    import pyarrow as pa
+    if codec not in CODEC_NAMES:
+        raise Unsupported("compression codec %d" % codec)
+    if size == 0:
+        return b""
+    return pa.Codec(CODEC_NAMES[codec]).decompress(bytes(raw), decompressed_size=size).to_pybytes()
+
+
+def decode_chunk(buf, ptype, max_def, num_values, type_length=0, codec=0):
     """One column chunk (bytes from its first page header to its end) -> (values, nulls uint8[num_values], info).
     values: numpy array with 0 at NULL positions (fixed width) / list with None (BYTE_ARRAY).
     info: {"pages": [...], "all_dictionary": bool, "dictionary": array/list or None, "ids": int32[n] with -1 at NULLs (when
@@ -249,16 +262,29 @@ def decode_chunk(buf, ptype, max_def, num_values, type_length=0):
         values = [None] * num_values if ptype == BYTE_ARRAY else np.zeros(num_values, {BOOLEAN: np.uint8, INT32: np.int32, INT64: np.int64, DOUBLE: np.float64}.get(ptype, np.int64))
     ids_all = np.full(num_values, -1, np.int32)
     pages, all_dict = [], True
+    chunk = buf
     while done < num_values:
+        buf = chunk   # (a compressed page is decoded out of its own uncompressed copy, see below)
         if pos >= len(buf):
             raise Corrupt("column chunk ends after %d of %d values" % (done, num_values))
         h, body = read_page_header(buf, pos)
-        if h["compressed_size"] != h["uncompressed_size"]:
-            raise Unsupported("compressed pages")
         end = body + h["compressed_size"]
         if end > len(buf):
             raise Corrupt("page exceeds the column chunk")
         pos = end
+        if codec:
+            # PageReader.readPage (lib/trino-parquet/.../reader/PageReader.java:63-99): v1 and dictionary pages are compressed whole,
+            # v2 pages keep their levels outside the compressed part. The page is decoded out of a private uncompressed copy.
+            lv = (h.get("def_bytes", 0) + h.get("rep_bytes", 0)) if h["type"] == PAGE_DATA_V2 else 0
+            packed = h.get("is_compressed", True) if h["type"] == PAGE_DATA_V2 else True
+            raw = bytes(buf[body:end])
+            page = raw[:lv] + (_inflate(codec, raw[lv:], h["uncompressed_size"] - lv) if packed else raw[lv:])
+            if len(page) != h["uncompressed_size"]:
+                raise Corrupt("page does not decompress to its declared size")
+            h = dict(h, compressed_size=h["uncompressed_size"], is_compressed=False)
+            buf, body, end = page, 0, len(page)
+        elif h["compressed_size"] != h["uncompressed_size"]:
+            raise Unsupported("compressed pages")
         if h["type"] == PAGE_DICTIONARY:
             if dictionary is not None or done:
                 raise Corrupt("dictionary page must be the first page of the chunk")

@@ -35,7 +35,7 @@ Column._fields_ = [
 class ParquetChunk(ctypes.Structure):
     """pgpu_parquet_chunk"""
     _fields_ = [("data", ctypes.c_char_p), ("len", ctypes.c_size_t), ("physical_type", ctypes.c_int32), ("max_definition_level", ctypes.c_int32),
-                ("num_values", ctypes.c_int64), ("type_length", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+                ("num_values", ctypes.c_int64), ("type_length", ctypes.c_int32), ("codec", ctypes.c_int32)]
 
 
 class Stats(ctypes.Structure):

@@ -1650,38 +1650,48 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     // array is fixed width per position: plain values / 16-byte varchar cells / dictionary ids (+ null flags); RLE blocks have
     // nothing to move
     bool sweepOk = highCard && !res.buckets && res.mode == KernelMode::AGG_HASH && plan.maxPartialGroups == 0 && envInt("PGPU_TUNE_SWEEP", 1) != 0;
-    int sweepRowBytes = 0;
+    int sweepRowBytes = 0, sweepStageWidth = 1;
     {
-        std::ostringstream cp;
+        // move_tile: one moved array at a time, the tile's elements are staged in shared memory with coalesced loads (in row order)
+        // and written out in slice order — every global byte is read once and written once, whatever the order of the keys
+        std::ostringstream mv;
+        auto moveArray = [&](const std::string& srcExpr, const std::string& dstExpr, int w) {
+            const char* ty = w == 1 ? "u8" : w == 4 ? "u32" : "u64";
+            const int words = w == 16 ? 2 : 1;  // 16-byte values as two words: the caller's arrays need not be 16-byte aligned
+            mv << "        {\n            " << ty << "* sm = (" << ty << "*)stage;\n";
+            mv << "            const " << ty << "* src = (const " << ty << "*)(" << srcExpr << ") + tbase * " << words << ";\n";
+            mv << "            " << ty << "* dst = (" << ty << "*)const_cast<void*>((const void*)(" << dstExpr << "));\n";
+            mv << "            for (int i = threadIdx.x; i < nt * " << words << "; i += blockDim.x) sm[i] = src[i];\n";
+            mv << "            __syncthreads();\n";
+            mv << "            for (u32 j = threadIdx.x; j < total; j += blockDim.x) {\n";
+            mv << "                const u32 pp = spid[j];\n                const u64 d = gbase[pp] + (j - lstart[pp]);\n                const u32 sr = sidx[j];\n";
+            if (words == 2) mv << "                dst[2 * d] = sm[2 * sr];\n                dst[2 * d + 1] = sm[2 * sr + 1];\n";
+            else mv << "                dst[d] = sm[sr];\n";
+            mv << "            }\n            __syncthreads();\n        }\n";
+            sweepRowBytes += w;
+            sweepStageWidth = std::max(sweepStageWidth, w);
+        };
         for (int c : res.usedChannels) {
             const Type& t = plan.input[c];
             const ColSig& cs = sig[c];
             const std::string C = std::to_string(c);
             if (cs.encoding == PGPU_ENC_RLE) continue;
             if (cs.encoding == PGPU_ENC_DICTIONARY) {
-                cp << "        const_cast<i32*>(o.c[" << C << "].ids)[dst] = a.c[" << C << "].ids[src];\n";
-                sweepRowBytes += 4;
+                moveArray("a.c[" + C + "].ids", "o.c[" + C + "].ids", 4);
                 continue;
             }
-            int w = cs.encoding == PGPU_ENC_VARCELL ? 16 : t.isVarWidth() ? 0 : t.width();
-            const char* ty = w == 1 ? "u8" : w == 2 ? "unsigned short" : w == 4 ? "u32" : w == 8 || w == 16 ? "u64" : nullptr;
-            if (!ty) { sweepOk = false; break; }
-            if (w == 16) {  // two words: the caller's 16-byte arrays need not be 16-byte aligned
-                cp << "        ((u64*)const_cast<void*>(o.c[" << C << "].values))[2 * dst] = ((const u64*)a.c[" << C << "].values)[2 * src];\n";
-                cp << "        ((u64*)const_cast<void*>(o.c[" << C << "].values))[2 * dst + 1] = ((const u64*)a.c[" << C << "].values)[2 * src + 1];\n";
-            } else {
-                cp << "        ((" << ty << "*)const_cast<void*>(o.c[" << C << "].values))[dst] = ((const " << ty << "*)a.c[" << C << "].values)[src];\n";
-            }
-            sweepRowBytes += w;
-            if (cs.nullable) {
-                cp << "        const_cast<u8*>(o.c[" << C << "].nulls)[dst] = a.c[" << C << "].nulls[src];\n";
-                sweepRowBytes += 1;
-            }
+            const int w = cs.encoding == PGPU_ENC_VARCELL ? 16 : t.isVarWidth() ? 0 : t.width();
+            if (w != 1 && w != 4 && w != 8 && w != 16) { sweepOk = false; break; }
+            moveArray("a.c[" + C + "].values", "o.c[" + C + "].values", w);
+            if (cs.nullable) moveArray("a.c[" + C + "].nulls", "o.c[" + C + "].nulls", 1);
         }
         if (sweepOk) {
-            src << "    PGPU_DEV static void copy_row(const PageArgs<NC>& a, i64 src, const PageArgs<NC>& o, i64 dst) {\n" << cp.str() << "    }\n";
+            src << "    PGPU_DEV static void move_tile(const PageArgs<NC>& a, const PageArgs<NC>& o, i64 tbase, int nt, u32 total, const unsigned short* sidx,\n"
+                << "                                   const unsigned short* spid, const u64* gbase, const u32* lstart, unsigned char* stage) {\n"
+                << mv.str() << "    }\n";
             res.sweepOk = true;
             res.sweepRowBytes = sweepRowBytes;
+            res.sweepStageWidth = sweepStageWidth;
         }
     }
     src << "};\n\n";
@@ -1718,6 +1728,11 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";
     }
     res.source = src.str();
+    if (res.sweepOk && envInt("PGPU_TUNE_SWEEP_WT", 1024) != 1024) {  // experiment knob: rows per warp ticket of the sweep kernel (128 .. 4096, a multiple of 128)
+        const int wt = std::min(std::max(envInt("PGPU_TUNE_SWEEP_WT", 1024) / 128 * 128, 128), 4096);
+        const std::string inc = "#include \"pgpu_device.cuh\"";
+        res.source.insert(res.source.find(inc), "#define PGPU_SWEEP_WT " + std::to_string(wt) + "\n");
+    }
     if (locB > 0) {
         const std::string inc = "#include \"pgpu_device.cuh\"";
         const size_t at = res.source.find(inc);

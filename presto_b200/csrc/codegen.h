@@ -54,6 +54,7 @@ struct GenResult {
     bool rangeOk = false;          // one integer grouping key: the exchange may split groups by key range (pgpu_k_emit_range / pgpu_k_keyrange)
     bool sweepOk = false;          // partition sweep kernels were generated (pgpu_k_part_count / _scatter / pgpu_k_page_sweep)
     int sweepRowBytes = 0;         // bytes the scatter moves per row (arrays of the used channels)
+    int sweepStageWidth = 1;       // widest moved element: the scatter stages kPartTile elements of one array at a time
     int bucketKeyChannel = -1;     // input channel the key is read from as it is (-1: the key is computed), for the clustering probe
 };
 

@@ -1437,7 +1437,8 @@ PGPU_DEV void body_agg_hash(const PageArgs<P::NC>& a, const TableArgs& t, const 
 //                        (home_pos is monotone in the hash, whatever the capacity, so the order survives table growth)
 //   (k_partition_scan, tableutil.cu: counts -> first row of every partition)
 //   pgpu_k_part_scatter  copies the rows that pass the filter into partition order: the input arrays of the used channels,
-//                        same encodings, so that the reordered page goes through the ordinary page kernel
+//                        same encodings, so that the reordered page goes through the ordinary page kernel. A block ranks its
+//                        tile by slice, then moves one array at a time through shared memory (P::move_tile)
 //   pgpu_k_page_sweep    body_agg_hash over the reordered page with (a) tiles handed out by a ticket counter, so that all
 //                        blocks work within a few hundred thousand rows of each other = inside one or two table slices, and
 //                        (b) every tile pulling the table lines that the rows kSweepLookahead further on will touch into L2 with
@@ -1490,8 +1491,8 @@ PGPU_DEV void body_part_count(const PageArgs<P::NC>& a, const PartArgs& pa, cons
     if (err) atomicOr(sc.err, err);
 }
 
-// dynamic shared memory: u64 gbase[K], u32 lstart[K + 2], u32 fill[K], u16 sidx[kPartTile], u16 spid[kPartTile]
-// = 16 K + 8 + 4 kPartTile bytes (the host computes the same figure)
+// dynamic shared memory: u64 gbase[K], u32 lstart[K + 2], u32 fill[K], u16 sidx[kPartTile], u16 spid[kPartTile], then the stage of
+// P::move_tile = 16 K + 8 + 4 kPartTile + kPartTile x (widest moved element) bytes (the host computes the same figure)
 template <class P>
 PGPU_DEV void body_part_scatter(const PageArgs<P::NC>& a, const PageArgs<P::NC>& out, const PartArgs& pa) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1501,6 +1502,7 @@ PGPU_DEV void body_part_scatter(const PageArgs<P::NC>& a, const PageArgs<P::NC>&
     u32* fill = lstart + K + 2;
     unsigned short* sidx = reinterpret_cast<unsigned short*>(fill + K);
     unsigned short* spid = sidx + kPartTile;
+    unsigned char* stage = reinterpret_cast<unsigned char*>(spid + kPartTile);  // kPartTile elements of the widest moved array (16-byte aligned: K is even)
     constexpr int Q = kPartTile / (kPartThreads * 4);              // quads per thread
     const int lane = threadIdx.x & 31;
     const i64 ntiles = (a.rows + kPartTile - 1) / kPartTile;
@@ -1573,14 +1575,14 @@ PGPU_DEV void body_part_scatter(const PageArgs<P::NC>& a, const PageArgs<P::NC>&
         }
         __syncthreads();
         const u32 total = lstart[K];
-        for (u32 j = threadIdx.x; j < total; j += kPartThreads) {
-            const u32 pp = spid[j];
-            P::copy_row(a, tbase + sidx[j], out, (i64)(gbase[pp] + (j - lstart[pp])));
-        }
-        __syncthreads();
+        const i64 left = a.rows - tbase;
+        P::move_tile(a, out, tbase, (int)(left < kPartTile ? left : kPartTile), total, sidx, spid, gbase, lstart, stage);  // ends with a barrier
     }
 }
 
+#ifndef PGPU_SWEEP_WT
+#define PGPU_SWEEP_WT 1024
+#endif
 template <class P>
 PGPU_DEV void body_agg_hash_sweep(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc, const SweepArgs& sw) {
     constexpr int KW = P::KW, NHA = P::NHA;
@@ -1588,7 +1590,7 @@ PGPU_DEV void body_agg_hash_sweep(const PageArgs<P::NC>& a, const TableArgs& t, 
     HashCtx<P> cx;
     cx.init(smem_raw, P::NWARP, threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    constexpr i64 WT = 1024;  // rows per ticket: tickets go to WARPS (a block-wide hand-out costs two barriers per tile, 30 % of the kernel)
+    constexpr i64 WT = PGPU_SWEEP_WT;  // rows per ticket: tickets go to WARPS (a block-wide hand-out costs two barriers per tile, 30 % of the kernel)
     const i64 ntick = (a.rows + WT - 1) / WT;
     const u64 table_bytes = t.capacity * (u64)P::SLOTW * 8ull;
     const i64 batch_rows = (i64)sw.start[sw.K];

@@ -365,6 +365,199 @@ inline void parsePage(const uint8_t* d, const PageDesc& pd, int ptype, int maxDe
 
 }  // namespace detail
 
+// ------------------------------------------------------------------------------------------------ page decompression
+// The reference undoes the codec on the CPU, page by page (lib/trino-parquet/.../reader/PageReader.java:63-99 ->
+// ParquetCompressionUtils.decompress :43-70, airlift aircompressor). So does this ingest: byte-serial LZ77 decoding stays on the
+// host (one thread per column chunk), everything after it — levels, dictionary ids, NULL expansion — on the device.
+enum Codec { UNCOMPRESSED = 0, SNAPPY = 1, GZIP = 2, LZO = 3, BROTLI = 4, LZ4 = 5, ZSTD = 6, LZ4_RAW = 7 };  // parquet.thrift CompressionCodec
+
+// Raw Snappy block (format_description.txt of the Snappy sources): varint uncompressed length, then elements tagged by the low
+// two bits of their first byte: 00 literal, 01 / 10 / 11 copy with a 1- / 2- / 4-byte offset. Copies may overlap their output.
+inline bool snappyDecompress(const uint8_t* in, size_t n, uint8_t* out, size_t outLen) {
+    size_t ip = 0, op = 0;
+    uint64_t declared = 0;
+    for (int shift = 0;; shift += 7) {
+        if (ip >= n || shift > 35) return false;
+        const uint8_t b = in[ip++];
+        declared |= (uint64_t)(b & 0x7f) << shift;
+        if (!(b & 0x80)) break;
+    }
+    if (declared != outLen) return false;
+    while (ip < n) {
+        const uint8_t tag = in[ip++];
+        size_t len, offset;
+        if ((tag & 3) == 0) {
+            len = (size_t)(tag >> 2) + 1;
+            if (len > 60) {
+                const int extra = (int)len - 60;  // 1..4 length bytes, little endian
+                if (ip + (size_t)extra > n) return false;
+                len = 0;
+                for (int k = 0; k < extra; k++) len |= (size_t)in[ip + k] << (8 * k);
+                len += 1;
+                ip += (size_t)extra;
+            }
+            if (len > n - ip || len > outLen - op) return false;
+            memcpy(out + op, in + ip, len);
+            ip += len;
+            op += len;
+            continue;
+        }
+        if ((tag & 3) == 1) {
+            if (ip >= n) return false;
+            len = (size_t)((tag >> 2) & 7) + 4;
+            offset = ((size_t)(tag >> 5) << 8) | in[ip++];
+        } else if ((tag & 3) == 2) {
+            if (ip + 2 > n) return false;
+            len = (size_t)(tag >> 2) + 1;
+            offset = (size_t)in[ip] | ((size_t)in[ip + 1] << 8);
+            ip += 2;
+        } else {
+            if (ip + 4 > n) return false;
+            len = (size_t)(tag >> 2) + 1;
+            offset = (size_t)in[ip] | ((size_t)in[ip + 1] << 8) | ((size_t)in[ip + 2] << 16) | ((size_t)in[ip + 3] << 24);
+            ip += 4;
+        }
+        if (offset == 0 || offset > op || len > outLen - op) return false;
+        if (offset >= len) memcpy(out + op, out + op - offset, len);
+        else for (size_t k = 0; k < len; k++) out[op + k] = out[op - offset + k];  // overlapping: byte by byte
+        op += len;
+    }
+    return op == outLen;
+}
+
+// LZ4 block format (lz4_Block_format.md): sequences of [token | literal length bytes | literals | offset LE16 | match length bytes];
+// the last sequence ends after its literals.
+inline bool lz4Decompress(const uint8_t* in, size_t n, uint8_t* out, size_t outLen) {
+    size_t ip = 0, op = 0;
+    while (ip < n) {
+        const uint8_t token = in[ip++];
+        size_t lit = token >> 4;
+        if (lit == 15) {
+            uint8_t b;
+            do {
+                if (ip >= n) return false;
+                b = in[ip++];
+                lit += b;
+            } while (b == 255);
+        }
+        if (lit > n - ip || lit > outLen - op) return false;
+        memcpy(out + op, in + ip, lit);
+        ip += lit;
+        op += lit;
+        if (ip >= n) break;  // last sequence: literals only
+        if (ip + 2 > n) return false;
+        const size_t offset = (size_t)in[ip] | ((size_t)in[ip + 1] << 8);
+        ip += 2;
+        size_t len = (size_t)(token & 15) + 4;
+        if ((token & 15) == 15) {
+            uint8_t b;
+            do {
+                if (ip >= n) return false;
+                b = in[ip++];
+                len += b;
+            } while (b == 255);
+        }
+        if (offset == 0 || offset > op || len > outLen - op) return false;
+        if (offset >= len) memcpy(out + op, out + op - offset, len);
+        else for (size_t k = 0; k < len; k++) out[op + k] = out[op - offset + k];
+        op += len;
+    }
+    return op == outLen;
+}
+
+// Thrift compact protocol, just enough to write a page header
+struct HeaderWriter {
+    std::vector<uint8_t>& out;
+    int16_t last = 0;
+    void varint(uint64_t v) {
+        while (v >= 0x80) { out.push_back((uint8_t)(v | 0x80)); v >>= 7; }
+        out.push_back((uint8_t)v);
+    }
+    void fieldHeader(int fid, int type) {
+        const int delta = fid - last;
+        if (delta > 0 && delta <= 15) out.push_back((uint8_t)((delta << 4) | type));
+        else { out.push_back((uint8_t)type); varint(((uint64_t)(int64_t)fid << 1) ^ (uint64_t)((int64_t)fid >> 63)); }
+        last = (int16_t)fid;
+    }
+    void i32(int fid, int64_t v) {
+        fieldHeader(fid, 5);
+        varint(((uint64_t)v << 1) ^ (uint64_t)(v >> 63));
+    }
+    void boolean(int fid, bool v) { fieldHeader(fid, v ? 1 : 2); }
+    void stop() { out.push_back(0); }
+};
+
+// A column chunk whose pages are compressed -> the same chunk with UNCOMPRESSED pages (fresh headers that carry what parseChunk
+// reads: sizes, value counts, encodings, level byte lengths), which the rest of the ingest takes as it is.
+inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numValues, std::vector<uint8_t>& out, std::string& why) {
+    using namespace detail;
+    if (codec != SNAPPY && codec != LZ4_RAW) {
+        why = "not supported on the GPU path: Parquet compression codec " + std::to_string(codec) + " (UNCOMPRESSED, SNAPPY and LZ4_RAW pages are read)";
+        return false;
+    }
+    out.clear();
+    out.reserve(len * 3);
+    size_t pos = 0;
+    int64_t done = 0;
+    while (done < numValues) {
+        if (pos >= len) { why = "corrupt Parquet chunk: ends after " + std::to_string(done) + " of " + std::to_string(numValues) + " values"; return false; }
+        Reader r{d, len, pos};
+        PageHeader h;
+        if (!readPageHeader(r, h)) { why = "corrupt Parquet chunk: unreadable page header at byte " + std::to_string(pos); return false; }
+        const size_t body = r.pos;
+        if ((uint64_t)h.compressedSize > len - body) { why = "corrupt Parquet chunk: page exceeds the chunk"; return false; }
+        pos = body + (size_t)h.compressedSize;
+        if (h.type == INDEX_PAGE) continue;
+        if (h.type != DATA_PAGE && h.type != DATA_PAGE_V2 && h.type != DICTIONARY_PAGE) { why = "not supported on the GPU path: Parquet page type " + std::to_string(h.type); return false; }
+        if (h.uncompressedSize > (int64_t)1 << 31) { why = "corrupt Parquet chunk: page size"; return false; }
+        // data page v2 keeps its levels outside the compressed part (parquet-format DataPageHeaderV2)
+        size_t levels = 0;
+        bool packed = true;
+        if (h.type == DATA_PAGE_V2) {
+            if (h.defBytes < 0 || h.repBytes < 0 || h.defBytes + h.repBytes > h.compressedSize || h.defBytes + h.repBytes > h.uncompressedSize) { why = "corrupt Parquet chunk: level byte lengths"; return false; }
+            levels = (size_t)(h.defBytes + h.repBytes);
+            packed = h.isCompressed;
+        }
+        HeaderWriter w{out};
+        w.i32(1, h.type);
+        w.i32(2, h.uncompressedSize);
+        w.i32(3, h.uncompressedSize);
+        if (h.type == DATA_PAGE) {
+            w.fieldHeader(5, 12);
+            HeaderWriter s{out};
+            s.i32(1, h.numValues); s.i32(2, h.encoding); s.i32(3, h.defEncoding); s.i32(4, h.repEncoding);
+            s.stop();
+        } else if (h.type == DICTIONARY_PAGE) {
+            w.fieldHeader(7, 12);
+            HeaderWriter s{out};
+            s.i32(1, h.numValues); s.i32(2, h.encoding);
+            s.stop();
+        } else {
+            w.fieldHeader(8, 12);
+            HeaderWriter s{out};
+            s.i32(1, h.numValues); s.i32(2, h.numNulls < 0 ? 0 : h.numNulls); s.i32(3, h.numValues); s.i32(4, h.encoding); s.i32(5, h.defBytes); s.i32(6, h.repBytes);
+            s.boolean(7, false);
+            s.stop();
+        }
+        w.stop();
+        const size_t at = out.size();
+        out.resize(at + (size_t)h.uncompressedSize);
+        memcpy(out.data() + at, d + body, levels);
+        const uint8_t* src = d + body + levels;
+        const size_t srcLen = (size_t)h.compressedSize - levels, dstLen = (size_t)h.uncompressedSize - levels;
+        bool ok;
+        if (!packed) ok = srcLen == dstLen && (memcpy(out.data() + at + levels, src, dstLen), true);
+        else if (dstLen == 0) ok = true;  // an empty page may be stored as zero bytes
+        else ok = codec == SNAPPY ? snappyDecompress(src, srcLen, out.data() + at + levels, dstLen) : lz4Decompress(src, srcLen, out.data() + at + levels, dstLen);
+        if (!ok) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
+        if (h.type != DICTIONARY_PAGE) {
+            if (h.numValues < 0 || h.numValues > numValues - done) { why = "corrupt Parquet chunk: pages hold more values than the metadata says"; return false; }
+            done += h.numValues;
+        }
+    }
+    return true;
+}
+
 // Describes one column chunk. `why` starts with "not supported" for rejections of well-formed input. Three steps: the page
 // headers in file order (each says where the next one lies), the run headers of every data page (pages are independent:
 // `threads` > 1 walks them in parallel), then the pages' pieces put together in order (non-null prefix sums fix where each

@@ -53,16 +53,30 @@ pgpu_status pqDecodeRowGroup(const Plan& plan, const pgpu_parquet_chunk* chunks,
     // the chunks are independent and so are the pages of a chunk once their headers are known: one host thread per column chunk,
     // each sharing the remaining cores over its pages
     std::vector<std::string> whys((size_t)nchunks);
+    // compressed chunks (SNAPPY / LZ4_RAW) are inflated on the host, by the chunk's thread, into a chunk with uncompressed pages
+    std::vector<std::vector<uint8_t>> inflated((size_t)nchunks);
+    std::vector<const uint8_t*> cdata((size_t)nchunks);
+    std::vector<size_t> clen((size_t)nchunks);
     auto parseOne = [&](int c) {
         const pgpu_parquet_chunk& in = chunks[c];
         const Type& t = plan.input[c];
-        if (!pq::parseChunk(in.data, in.len, in.physical_type, in.max_definition_level, in.num_values, ck[c], whys[c], in.type_length, pageThreads)) {
+        cdata[c] = in.data;
+        clen[c] = in.len;
+        if (in.codec != pq::UNCOMPRESSED) {
+            if (!pq::inflateChunk(in.data, in.len, in.codec, in.num_values, inflated[c], whys[c])) {
+                if (whys[c].empty()) whys[c] = "corrupt Parquet chunk";
+                return;
+            }
+            cdata[c] = inflated[c].data();
+            clen[c] = inflated[c].size();
+        }
+        if (!pq::parseChunk(cdata[c], clen[c], in.physical_type, in.max_definition_level, in.num_values, ck[c], whys[c], in.type_length, pageThreads)) {
             if (whys[c].empty()) whys[c] = "corrupt Parquet chunk";
             return;
         }
         if (in.physical_type == pq::BYTE_ARRAY && ck[c].hasDictionary) {
             const int maxChars = t.kind == TypeKind::VARCHAR ? t.precision : 0;
-            if (!pq::binaryDictionary(in.data, ck[c].dictionaryOff, ck[c].dictionaryEnd, ck[c].dictionaryCount, maxChars, dictOffsets[c], dictBytes[c], whys[c]) && whys[c].empty())
+            if (!pq::binaryDictionary(cdata[c], ck[c].dictionaryOff, ck[c].dictionaryEnd, ck[c].dictionaryCount, maxChars, dictOffsets[c], dictBytes[c], whys[c]) && whys[c].empty())
                 whys[c] = "corrupt Parquet dictionary page";
         }
     };
@@ -93,7 +107,7 @@ pgpu_status pqDecodeRowGroup(const Plan& plan, const pgpu_parquet_chunk* chunks,
         const pq::Chunk& k = ck[c];
         Placed& q = at[c];
         const int W = plan.input[c].width();  // bytes per position of the block; 0 for var-width
-        q.chunk = reserve(chunks[c].len);
+        q.chunk = reserve(clen[c]);
         q.valueRuns = reserve(k.valueRuns.size() * sizeof(pq::Run));
         if (k.hasNulls()) {
             q.levelRuns = reserve(k.levelRuns.size() * sizeof(pq::Run));
@@ -138,9 +152,9 @@ pgpu_status pqDecodeRowGroup(const Plan& plan, const pgpu_parquet_chunk* chunks,
             out.launches += 1;
             return pqConvertPlain(stream, (const uint8_t*)(base + q.chunk + srcOff), Win, conv, count, dst, W);
         };
-        const size_t len = chunks[c].len;
+        const size_t len = clen[c];
         const uint8_t* dchunk = (const uint8_t*)(base + q.chunk);
-        if (len) CU(cudaMemcpyAsync(base + q.chunk, chunks[c].data, len, cudaMemcpyHostToDevice, stream));  // the whole chunk in one DMA
+        if (len) CU(cudaMemcpyAsync(base + q.chunk, cdata[c], len, cudaMemcpyHostToDevice, stream));  // the whole chunk in one DMA
         out.h2dBytes += (int64_t)len;
         if (!k.valueRuns.empty()) CU(cudaMemcpyAsync(base + q.valueRuns, k.valueRuns.data(), k.valueRuns.size() * sizeof(pq::Run), cudaMemcpyHostToDevice, stream));
         const PqRun* vruns = (const PqRun*)(base + q.valueRuns);

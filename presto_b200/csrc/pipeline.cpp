@@ -103,7 +103,7 @@ constexpr int64_t kTileRows = kThreads * 4;
 constexpr int64_t kHashChunkRows = 64ll << 20;
 // partition sweep (device header, "partition sweep"): same constants as the kernels
 constexpr int kPartMaxK = 1024, kPartTile = 4096, kPartThreads = 256;
-constexpr size_t partScatterSmem(int K) { return (size_t)16 * K + 8 + (size_t)4 * kPartTile; }
+constexpr size_t partScatterSmem(int K, int stageWidth) { return (size_t)16 * K + 8 + (size_t)4 * kPartTile + (size_t)kPartTile * stageWidth; }
 constexpr int64_t kSweepMinRows = 16ll << 20;          // shorter batches do not pay for a pass over the table
 constexpr size_t kSweepMinTableBytes = 256ull << 20;   // a table that is not much larger than L2 (126 MB) is fast as it is
 constexpr size_t kSweepSliceBytes = 32ull << 20;       // table bytes per partition: what stays L2 resident while a partition is consumed  // rows per launch of the hash-aggregation kernel (bounds the deferred-row log)
@@ -374,7 +374,7 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
                 CU(cudaLibraryGetKernel(&v.kPartCount, v.lib, "pgpu_k_part_count"));
                 CU(cudaLibraryGetKernel(&v.kPartScatter, v.lib, "pgpu_k_part_scatter"));
                 CU(cudaLibraryGetKernel(&v.kPageSweep, v.lib, "pgpu_k_page_sweep"));
-                CU(cudaFuncSetAttribute((const void*)v.kPartScatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)partScatterSmem(kPartMaxK)));
+                CU(cudaFuncSetAttribute((const void*)v.kPartScatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)partScatterSmem(kPartMaxK, v.gen.sweepStageWidth)));
                 if (v.gen.smemBytes > 48 * 1024) CU(cudaFuncSetAttribute((const void*)v.kPageSweep, cudaFuncAttributeMaxDynamicSharedMemorySize, v.gen.smemBytes));
                 int nb = 0;
                 if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v.kPageSweep, kThreads, (size_t)v.gen.smemBytes) != cudaSuccess || nb < 1) {
@@ -733,7 +733,8 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg, co
             CU(cudaMemsetAsync(sa.ticket, 0, 4, p->stream));
             void* args[] = {pa.data(), &t, &sc, &sa};
             cudaKernel_t k = v->kPageSweep;
-            const int64_t nwarpTickets = (pg.rows + 1023) / 1024;
+            static const int64_t wt = [] { const char* e = getenv("PGPU_TUNE_SWEEP_WT"); int64_t v = e ? atoll(e) : 1024; return std::min<int64_t>(std::max<int64_t>(v / 128 * 128, 128), 4096); }();
+            const int64_t nwarpTickets = (pg.rows + wt - 1) / wt;
             st = launch(p, k, (int)std::min<int64_t>((nwarpTickets + 7) / 8, (int64_t)p->numSMs * v->sweepBlocksPerSM), kThreads, (size_t)g.smemBytes, args);
         } else {
             void* args[] = {pa.data(), &t, &sc};
@@ -900,7 +901,7 @@ pgpu_status runSweep(pgpu_pipeline* p, Variant* v, const DevPage& pg, bool* swep
         {
             if (v->scatterBlocksPerSM == 1) {
                 int nb = 0;
-                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v->kPartScatter, kPartThreads, partScatterSmem(K)) != cudaSuccess || nb < 1) {
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v->kPartScatter, kPartThreads, partScatterSmem(K, g.sweepStageWidth)) != cudaSuccess || nb < 1) {
                     cudaGetLastError();
                     nb = 1;
                 }
@@ -908,7 +909,7 @@ pgpu_status runSweep(pgpu_pipeline* p, Variant* v, const DevPage& pg, bool* swep
             }
             void* args[] = {pin.data(), pout.data(), &pa};
             const int64_t ntiles = (bn + kPartTile - 1) / kPartTile;
-            if ((st = launch(p, v->kPartScatter, (int)std::min<int64_t>(ntiles, (int64_t)p->numSMs * v->scatterBlocksPerSM), kPartThreads, partScatterSmem(K), args))) return st;
+            if ((st = launch(p, v->kPartScatter, (int)std::min<int64_t>(ntiles, (int64_t)p->numSMs * v->scatterBlocksPerSM), kPartThreads, partScatterSmem(K, g.sweepStageWidth), args))) return st;
         }
         const double t2 = trace ? now() : 0;
         CU(cudaMemcpyAsync(&p->hostScalars[13], start + K, 8, cudaMemcpyDeviceToHost, p->stream));
@@ -2274,11 +2275,24 @@ pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chun
 // Host-only view of what pgpu_add_parquet_row_group reads from a chunk (no GPU needed): info[0] data pages, [1] dictionary
 // entries (-1: no dictionary page), [2] 1 if every data page is dictionary encoded, [3] non-null values, [4] definition level
 // runs kept (0 when the chunk has no NULL), [5] value runs (ids / booleans), [6] 1 if some page is dictionary encoded, [7] rows.
+// page headers + run headers of one chunk, after its pages have been decompressed if the chunk says they are compressed
+static bool parseChunkOf(const pgpu_parquet_chunk* chunk, pq::Chunk& k, std::string& why) {
+    std::vector<uint8_t> inflated;
+    const uint8_t* d = chunk->data;
+    size_t len = chunk->len;
+    if (chunk->codec != pq::UNCOMPRESSED) {
+        if (!pq::inflateChunk(chunk->data, chunk->len, chunk->codec, chunk->num_values, inflated, why)) return false;
+        d = inflated.data();
+        len = inflated.size();
+    }
+    return pq::parseChunk(d, len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length, parquetHostThreads(1));
+}
+
 pgpu_status pgpu_parquet_inspect_chunk(const pgpu_parquet_chunk* chunk, int64_t* info, char* err, size_t err_len) {
     if (!chunk || !info) return PGPU_INVALID_ARGUMENT;
     pq::Chunk k;
     std::string why;
-    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length, parquetHostThreads(1))) {
+    if (!parseChunkOf(chunk, k, why)) {
         if (err && err_len) {
             strncpy(err, why.c_str(), err_len - 1);
             err[err_len - 1] = 0;
@@ -2304,8 +2318,7 @@ pgpu_status pgpu_parquet_chunk_runs(const pgpu_parquet_chunk* chunk, int32_t whi
     if (!chunk || !n) return PGPU_INVALID_ARGUMENT;
     pq::Chunk k;
     std::string why;
-    if (!pq::parseChunk(chunk->data, chunk->len, chunk->physical_type, chunk->max_definition_level, chunk->num_values, k, why, chunk->type_length, parquetHostThreads(1)))
-        return why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT;
+    if (!parseChunkOf(chunk, k, why)) return why.rfind("not supported", 0) == 0 ? PGPU_NOT_SUPPORTED : PGPU_INVALID_ARGUMENT;
     std::vector<pq::Run> pages;
     for (const pq::DataPage& pg : k.pages) pages.push_back(pq::Run{pg.firstValue, (uint64_t)pg.valuesOff, (uint32_t)pg.nonNull, pg.dictionaryEncoded ? 1u : 0u});
     const std::vector<pq::Run>& v = which == 0 ? k.levelRuns : which == 1 ? k.valueRuns : pages;

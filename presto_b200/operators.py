@@ -134,7 +134,7 @@ class GpuPipelineOperator:
     def addParquetRowGroup(self, chunks, rows: int):
         """addInput of the Page the reference's ParquetReader.nextPage would build from one row group
         (lib/trino-parquet/.../reader/ParquetReader.java:211-268): chunks[c] = (column chunk bytes as they lie in the file,
-        uncompressed; parquet physical type; max definition level; num_values[; FIXED_LEN_BYTE_ARRAY length]) feeds input channel c. Page and run headers are
+        parquet physical type; max definition level; num_values[; FIXED_LEN_BYTE_ARRAY length[; compression codec]]) feeds input channel c. Page and run headers are
         read on the host, everything else is decoded on the device (pgpu_add_parquet_row_group)."""
         arr = (N.ParquetChunk * len(chunks))()
         keep = []
@@ -144,6 +144,7 @@ class GpuPipelineOperator:
             keep.append(data)
             arr[i].data, arr[i].len, arr[i].physical_type, arr[i].max_definition_level, arr[i].num_values = data, len(data), ptype, max_def, num_values
             arr[i].type_length = chunk[4] if len(chunk) > 4 else 0
+            arr[i].codec = chunk[5] if len(chunk) > 5 else 0
         self._check(self._lib.pgpu_add_parquet_row_group(self._h, arr, len(chunks), rows))
 
     def getSerializedOutput(self):

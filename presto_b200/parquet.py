@@ -9,7 +9,11 @@ import io
 from typing import Dict, Iterator, List, Tuple, Union
 
 PHYSICAL = {"BOOLEAN": 0, "INT32": 1, "INT64": 2, "INT96": 3, "FLOAT": 4, "DOUBLE": 5, "BYTE_ARRAY": 6, "FIXED_LEN_BYTE_ARRAY": 7}  # parquet.thrift Type
-Chunk = Tuple[bytes, int, int, int, int]   # (chunk bytes, physical type, max definition level, num_values, type_length of FIXED_LEN_BYTE_ARRAY)
+# parquet.thrift CompressionCodec, keyed by pyarrow's names: Arrow calls the raw LZ4 block codec (thrift LZ4_RAW = 7) "LZ4" and the
+# deprecated Hadoop-framed one (thrift LZ4 = 5) "LZ4_HADOOP"
+CODEC = {"UNCOMPRESSED": 0, "SNAPPY": 1, "GZIP": 2, "LZO": 3, "BROTLI": 4, "LZ4_HADOOP": 5, "ZSTD": 6, "LZ4": 7, "LZ4_RAW": 7}
+# (chunk bytes, physical type, max definition level, num_values, type_length of FIXED_LEN_BYTE_ARRAY[, compression codec if not UNCOMPRESSED])
+Chunk = Tuple
 
 
 def row_groups(source: Union[str, bytes]) -> Iterator[Tuple[int, Dict[str, Chunk]]]:
@@ -25,8 +29,10 @@ def row_groups(source: Union[str, bytes]) -> Iterator[Tuple[int, Dict[str, Chunk
             start = c.data_page_offset
             if c.has_dictionary_page and c.dictionary_page_offset:
                 start = min(start, c.dictionary_page_offset)
-            cols[c.path_in_schema] = (data[start:start + c.total_compressed_size], PHYSICAL[c.physical_type], md.schema.column(j).max_definition_level, c.num_values,
-                                       md.schema.column(j).length if c.physical_type == "FIXED_LEN_BYTE_ARRAY" else 0)
+            chunk = (data[start:start + c.total_compressed_size], PHYSICAL[c.physical_type], md.schema.column(j).max_definition_level, c.num_values,
+                     md.schema.column(j).length if c.physical_type == "FIXED_LEN_BYTE_ARRAY" else 0)
+            codec = CODEC.get(c.compression, 99)
+            cols[c.path_in_schema] = chunk + (codec,) if codec else chunk   # the codec is only spelled out for compressed chunks
         yield rg.num_rows, cols
 
 

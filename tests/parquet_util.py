@@ -70,7 +70,7 @@ def decimal_array(unscaled, precision, scale):
     return pa.Array.from_buffers(pa.decimal128(precision, scale), len(v), [None, pa.py_buffer(words.tobytes())])
 
 
-def tpch_lineitem_parquet(sf, row_group_rows, as_integer=False, first_order=0, n_orders=None):
+def tpch_lineitem_parquet(sf, row_group_rows, as_integer=False, first_order=0, n_orders=None, compression="NONE"):
     """Q1's columns of TPC-H lineitem (product-side host generator, pinned by the sf1 golden answers in test_tpch_golden.py) with
     DECIMAL(12,2) numerics, dictionary-encoded flags, DATE ship dates -> the bytes of an uncompressed Parquet file"""
     import io
@@ -87,7 +87,7 @@ def tpch_lineitem_parquet(sf, row_group_rows, as_integer=False, first_order=0, n
         "discount": decimal_array(c("discount", True), 12, 2), "tax": decimal_array(c("tax", True), 12, 2),
         "shipdate": pa.array(c("shipdate").astype(np.int32), pa.date32())})
     buf = io.BytesIO()
-    pq.write_table(t, buf, compression="NONE", use_dictionary=["returnflag", "linestatus", "quantity", "discount", "tax"], row_group_size=row_group_rows,
+    pq.write_table(t, buf, compression=compression, use_dictionary=["returnflag", "linestatus", "quantity", "discount", "tax"], row_group_size=row_group_rows,
                    write_statistics=False, store_decimal_as_integer=as_integer)
     return buf.getvalue()
 

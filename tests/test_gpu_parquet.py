@@ -212,3 +212,42 @@ def test_sf1_lineitem_parquet_file_equals_golden_answers():
     G.check_q1_decimal(got)
     got, _ = run_parquet(tpch.q6_decimal_plan(), groups, ["extendedprice", "discount", "shipdate", "quantity"])
     assert got == G.golden_rows("hive_tpch_q06.result", (4,))
+
+
+@pytest.mark.parametrize("compression,codec", [("SNAPPY", 1), ("LZ4", 7)])
+def test_compressed_lineitem_parquet_file_equals_golden_answers(compression, codec):
+    """the same golden answers off a SNAPPY- / LZ4_RAW-compressed file of the sf1 table: pages are
+    inflated on the host (ParquetCompressionUtils.java:43-70), everything else is the uncompressed path"""
+    pytest.importorskip("pyarrow")
+    import test_tpch_golden as G
+    from parquet_util import Q1_COLUMNS, tpch_lineitem_parquet
+    data = tpch_lineitem_parquet(1.0, 1_000_000, compression=compression)
+    groups = chunks_of(data)
+    assert all(len(c) == 6 and c[5] == codec for _, cols in groups for c in cols.values())
+    assert len(data) < 0.8 * len(tpch_lineitem_parquet(1.0, 1_000_000, first_order=0, n_orders=None))   # it really is compressed
+    got, st = run_parquet(tpch.q1_decimal_plan(), groups, Q1_COLUMNS)
+    G.check_q1_decimal(got)
+    got, _ = run_parquet(tpch.q6_decimal_plan(), groups, ["extendedprice", "discount", "shipdate", "quantity"])
+    assert got == G.golden_rows("hive_tpch_q06.result", (4,))
+
+
+def test_compressed_nullable_pages_equal_the_uncompressed_file():
+    """NULLs, booleans, mixed dictionary / plain chunks, data pages v1 and v2, small pages: compressed files give the blocks the
+    uncompressed file gives"""
+    pytest.importorskip("pyarrow")
+    import io
+    import pyarrow.parquet as pq
+    sys.path.insert(0, GOLDEN)
+    import make_parquet_fixtures as M
+    plan = plan_text([t for _, t in NULLABLE if t != V3], None, [field(i, t) for i, (_, t) in enumerate([c for c in NULLABLE if c[1] != V3])])
+    names = [n for n, t in NULLABLE if t != V3]
+    table = M.nullable_table(20_000, seed=9)
+    for version in ("1.0", "2.0"):
+        outs = []
+        for compression in ("NONE", "SNAPPY", "LZ4"):
+            buf = io.BytesIO()
+            pq.write_table(table, buf, compression=compression, data_page_version=version, data_page_size=3000, use_dictionary=["runs"], row_group_size=7000)
+            got, _ = run_parquet(plan, chunks_of(buf.getvalue()), names)
+            outs.append(got)
+        assert outs[0] == outs[1] == outs[2] and len(outs[0]) == 20_000
+

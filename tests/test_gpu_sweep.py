@@ -276,7 +276,7 @@ def test_sweep_kernels_compile_without_gpu():
         try:
             op.compileSignature(*sig)
             src = op.generatedSource()
-            assert "pgpu_k_part_count" in src and "pgpu_k_part_scatter" in src and "pgpu_k_page_sweep" in src and "copy_row" in src
+            assert "pgpu_k_part_count" in src and "pgpu_k_part_scatter" in src and "pgpu_k_page_sweep" in src and "move_tile" in src
         finally:
             op.close()
     # a var-width (offsets + bytes) key column cannot be moved row by row: no sweep kernels, the ordinary path stays

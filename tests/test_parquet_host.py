@@ -16,8 +16,8 @@ from parquet_util import GOLDEN, chunks_of, dictionary_chunk  # noqa: E402
 from presto_b200 import _native as N  # noqa: E402
 
 
-def inspect(buf, ptype, max_def, num_values, tl=0):
-    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values, tl, 0)
+def inspect(buf, ptype, max_def, num_values, tl=0, codec=0):
+    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values, tl, codec)
     info = (ctypes.c_int64 * 8)()
     err = ctypes.create_string_buffer(512)
     st = N.lib().pgpu_parquet_inspect_chunk(ctypes.byref(c), info, err, 512)
@@ -27,8 +27,8 @@ def inspect(buf, ptype, max_def, num_values, tl=0):
 RUN = np.dtype([("start", "<i8"), ("src", "<u8"), ("count", "<u4"), ("width", "<u4")])
 
 
-def runs_of(buf, ptype, max_def, num_values, which, tl=0):
-    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values, tl, 0)
+def runs_of(buf, ptype, max_def, num_values, which, tl=0, codec=0):
+    c = N.ParquetChunk(bytes(buf), len(buf), ptype, max_def, num_values, tl, codec)
     n = ctypes.c_int64()
     assert N.lib().pgpu_parquet_chunk_runs(ctypes.byref(c), which, None, 0, ctypes.byref(n)) == N.OK
     out = np.zeros(n.value, RUN)
@@ -131,17 +131,73 @@ def test_live_pyarrow_files(version, page_size, dict_cols):
         assert check_against_oracle(buf.getvalue()) > 0
 
 
-def test_compressed_pages_are_rejected():
-    pytest.importorskip("pyarrow")
+def _write(table, compression, version, **kw):
     import pyarrow.parquet as pq
+    buf = io.BytesIO()
+    pq.write_table(table, buf, compression=compression, data_page_version=version, **kw)
+    return buf.getvalue()
+
+
+@pytest.mark.parametrize("version", ["1.0", "2.0"])
+@pytest.mark.parametrize("compression,codec", [("SNAPPY", 1), ("LZ4", 7)])
+def test_compressed_pages_are_inflated_on_the_host(compression, codec, version):
+    """SNAPPY and LZ4_RAW pages (ParquetCompressionUtils.java:43-70): the host inflates the chunk, everything downstream sees the same
+    pages as in the uncompressed file — same page / dictionary / run counts, same run tables (up to byte offsets, headers are
+    rewritten), and the oracle, which inflates with Arrow's codecs, decodes the same values"""
+    pytest.importorskip("pyarrow")
     sys.path.insert(0, GOLDEN)
     import make_parquet_fixtures as M
-    buf = io.BytesIO()
-    pq.write_table(M.lineitem_table(3000, seed=3), buf, compression="SNAPPY")
-    rows, cols = chunks_of(buf.getvalue())[0]
-    b, pt, md, n, tl = cols["extendedprice"]
-    st, _, err = inspect(b, pt, md, n)
-    assert st == N.NOT_SUPPORTED and "compressed" in err
+    n = 0
+    for table in (M.nullable_table(3000, seed=7), M.lineitem_table(3000, seed=8)):
+        kw = dict(data_page_size=900, use_dictionary=["flag", "runs", "returnflag", "linestatus", "quantity"], write_batch_size=64)
+        packed, plain = chunks_of(_write(table, compression, version, **kw)), chunks_of(_write(table, "NONE", version, **kw))
+        for (rows, cols), (_, pcols) in zip(packed, plain):
+            for name, chunk in cols.items():
+                assert len(chunk) == 6 and chunk[5] == codec, (name, chunk[1:])
+                buf, ptype, max_def, nvals, tl = chunk[:5]
+                pbuf = pcols[name][0]
+                st, info, err = inspect(buf, ptype, max_def, nvals, tl, codec)
+                pst, pinfo, _ = inspect(pbuf, ptype, max_def, nvals, tl)
+                assert (st, info) == (pst, pinfo), (name, err)
+                if st != N.OK:
+                    continue
+                for which in (0, 1, 2):
+                    a, b = runs_of(buf, ptype, max_def, nvals, which, tl, codec), runs_of(pbuf, ptype, max_def, nvals, which, tl)
+                    assert np.array_equal(a["start"], b["start"]) and np.array_equal(a["count"], b["count"]) and np.array_equal(a["width"], b["width"]), (name, which)
+                    rle = (a["width"] >> 31) == 0
+                    if which < 2:
+                        assert np.array_equal(a["src"][rle], b["src"][rle]), (name, which)      # RLE runs carry their value, not an offset
+                got, want = PP.decode_chunk(buf, ptype, max_def, nvals, tl, codec), PP.decode_chunk(pbuf, ptype, max_def, nvals, tl)
+                assert np.array_equal(np.asarray(got[1]), np.asarray(want[1])), name
+                live = np.asarray(want[1]) == 0
+                assert list(np.asarray(got[0], dtype=object)[live]) == list(np.asarray(want[0], dtype=object)[live]), name
+                n += 1
+    assert n >= 12
+
+
+def test_other_codecs_and_corrupt_compressed_pages_are_errors():
+    pytest.importorskip("pyarrow")
+    sys.path.insert(0, GOLDEN)
+    import make_parquet_fixtures as M
+    table = M.lineitem_table(3000, seed=3)
+    for compression in ("ZSTD", "GZIP"):
+        rows, cols = chunks_of(_write(table, compression, "1.0"))[0]
+        b, pt, md, n, tl, codec = cols["extendedprice"]
+        st, _, err = inspect(b, pt, md, n, tl, codec)
+        assert st == N.NOT_SUPPORTED and "codec" in err, err
+    rows, cols = chunks_of(_write(table, "SNAPPY", "1.0", use_dictionary=False))[0]
+    b, pt, md, n, tl, codec = cols["extendedprice"]
+    assert inspect(b, pt, md, n, tl, codec)[0] == N.OK
+    assert inspect(b, pt, md, n, tl, 0)[0] == N.NOT_SUPPORTED          # compressed pages handed over as uncompressed
+    rng = np.random.default_rng(1)
+    for trial in range(40):                                            # damaged payloads: an error, never a crash
+        bad = bytearray(b)
+        for at in rng.integers(40, len(bad), 6):
+            bad[at] ^= int(rng.integers(1, 256))
+        st, _, err = inspect(bytes(bad), pt, md, n, tl, codec)
+        assert st in (N.OK, N.INVALID_ARGUMENT, N.NOT_SUPPORTED), err
+    st, _, err = inspect(b[:len(b) // 2], pt, md, n, tl, codec)
+    assert st == N.INVALID_ARGUMENT
 
 
 def test_rejections_and_corruption():

@@ -1,5 +1,5 @@
 """Host-ingest comparison on one GPU: Q1 over the same rows through pgpu_add_page (plain blocks) and through
-pgpu_add_parquet_row_group (uncompressed Parquet row groups written by pyarrow: dictionary-encoded flag / quantity / discount /
+pgpu_add_parquet_row_group (Parquet row groups written by pyarrow, COMPRESSION=NONE|SNAPPY|LZ4: dictionary-encoded flag / quantity / discount /
 tax chunks, PLAIN extendedprice / shipdate). Prints one JSON line with rows/s of both and the file bytes per row.
 Auxiliary measurement (profiles/), not the bench.py contract.   PAGE_ROWS / PAGES set the size."""
 import io
@@ -31,11 +31,12 @@ def main():
                       "quantity": pa.array(b[2].values.view("f8")), "extendedprice": pa.array(b[3].values.view("f8")), "discount": pa.array(b[4].values.view("f8")),
                       "tax": pa.array(b[5].values.view("f8")), "shipdate": pa.array(b[6].values, pa.date32())})
         buf = io.BytesIO()
-        pq.write_table(t, buf, compression="NONE", use_dictionary=["returnflag", "linestatus", "quantity", "discount", "tax"], row_group_size=rows_per_group,
+        pq.write_table(t, buf, compression=os.environ.get("COMPRESSION", "NONE"), use_dictionary=["returnflag", "linestatus", "quantity", "discount", "tax"], row_group_size=rows_per_group,
                        data_page_size=1 << 20, write_statistics=False)
         files.append(list(parquet.row_groups(buf.getvalue())))
     file_bytes = sum(len(c[0]) for f in files for _, cols in f for c in cols.values())
-    out = {"workload": "tpch_q1", "rows": total, "row_group_rows": rows_per_group, "parquet_bytes_per_row": file_bytes / total}
+    out = {"workload": "tpch_q1", "rows": total, "row_group_rows": rows_per_group, "parquet_bytes_per_row": file_bytes / total,
+           "compression": os.environ.get("COMPRESSION", "NONE")}
     results = {}
     for name in ("blocks", "parquet"):
         best = None
