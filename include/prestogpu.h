@@ -258,6 +258,8 @@ int32_t pgpu_partition_of(const int64_t* key_bits, const uint8_t* is_null, const
  * pgpu_comm_init blocks until all `nranks` ranks have called it. device < 0 joins the rendezvous only (CPU tests). */
 typedef struct pgpu_comm pgpu_comm;
 pgpu_status pgpu_comm_init(int32_t nranks, int32_t rank, int32_t device, const char* name, pgpu_comm** out);
+/* Waits (at most 30 s) until every peer has finished reading this rank's partition arena of the last exchange: destroy the
+ * communicator BEFORE the PARTIAL pipeline whose output it exchanged (the arena is that pipeline's memory). */
 void pgpu_comm_destroy(pgpu_comm* c);
 const char* pgpu_comm_last_error(const pgpu_comm* c);
 /* All ranks have arrived (host-side, through the segment). */

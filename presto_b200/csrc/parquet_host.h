@@ -489,7 +489,7 @@ struct HeaderWriter {
 
 // A column chunk whose pages are compressed -> the same chunk with UNCOMPRESSED pages (fresh headers that carry what parseChunk
 // reads: sizes, value counts, encodings, level byte lengths), which the rest of the ingest takes as it is.
-inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numValues, std::vector<uint8_t>& out, std::string& why) {
+inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numValues, std::vector<uint8_t>& out, std::string& why, int threads = 1) {
     using namespace detail;
     if (codec != SNAPPY && codec != LZ4_RAW) {
         why = "not supported on the GPU path: Parquet compression codec " + std::to_string(codec) + " (UNCOMPRESSED, SNAPPY and LZ4_RAW pages are read)";
@@ -497,6 +497,11 @@ inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numVal
     }
     out.clear();
     out.reserve(len * 3);
+    struct Task {
+        size_t src, srcLen, dst, dstLen;  // the compressed part of one page -> its place in `out`
+        bool packed;
+    };
+    std::vector<Task> tasks;  // pages are independent: headers are written in order here, bodies are inflated in parallel below
     size_t pos = 0;
     int64_t done = 0;
     while (done < numValues) {
@@ -543,18 +548,35 @@ inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numVal
         const size_t at = out.size();
         out.resize(at + (size_t)h.uncompressedSize);
         memcpy(out.data() + at, d + body, levels);
-        const uint8_t* src = d + body + levels;
-        const size_t srcLen = (size_t)h.compressedSize - levels, dstLen = (size_t)h.uncompressedSize - levels;
-        bool ok;
-        if (!packed) ok = srcLen == dstLen && (memcpy(out.data() + at + levels, src, dstLen), true);
-        else if (dstLen == 0) ok = true;  // an empty page may be stored as zero bytes
-        else ok = codec == SNAPPY ? snappyDecompress(src, srcLen, out.data() + at + levels, dstLen) : lz4Decompress(src, srcLen, out.data() + at + levels, dstLen);
-        if (!ok) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
+        tasks.push_back(Task{body + levels, (size_t)h.compressedSize - levels, at + levels, (size_t)h.uncompressedSize - levels, packed});
+        if (!packed && tasks.back().srcLen != tasks.back().dstLen) { why = "corrupt Parquet chunk: page sizes"; return false; }
         if (h.type != DICTIONARY_PAGE) {
             if (h.numValues < 0 || h.numValues > numValues - done) { why = "corrupt Parquet chunk: pages hold more values than the metadata says"; return false; }
             done += h.numValues;
         }
     }
+    std::vector<char> bad(tasks.size(), 0);
+    auto run = [&](size_t lo, size_t hi) {
+        for (size_t k = lo; k < hi; k++) {
+            const Task& t = tasks[k];
+            uint8_t* dst = out.data() + t.dst;
+            bool ok = true;
+            if (!t.packed) memcpy(dst, d + t.src, t.dstLen);
+            else if (t.dstLen) ok = codec == SNAPPY ? snappyDecompress(d + t.src, t.srcLen, dst, t.dstLen) : lz4Decompress(d + t.src, t.srcLen, dst, t.dstLen);  // (an empty page may be stored as zero bytes)
+            bad[k] = ok ? 0 : 1;
+        }
+    };
+    const size_t nt = std::min<size_t>((size_t)std::max(threads, 1), std::max<size_t>(tasks.size() / 2, 1));
+    if (nt > 1) {
+        std::vector<std::thread> workers;
+        for (size_t t = 1; t < nt; t++) workers.emplace_back(run, tasks.size() * t / nt, tasks.size() * (t + 1) / nt);
+        run(0, tasks.size() / nt);
+        for (auto& w : workers) w.join();
+    } else {
+        run(0, tasks.size());
+    }
+    for (char b : bad)
+        if (b) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
     return true;
 }
 

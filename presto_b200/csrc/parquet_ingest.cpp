@@ -63,7 +63,7 @@ pgpu_status pqDecodeRowGroup(const Plan& plan, const pgpu_parquet_chunk* chunks,
         cdata[c] = in.data;
         clen[c] = in.len;
         if (in.codec != pq::UNCOMPRESSED) {
-            if (!pq::inflateChunk(in.data, in.len, in.codec, in.num_values, inflated[c], whys[c])) {
+            if (!pq::inflateChunk(in.data, in.len, in.codec, in.num_values, inflated[c], whys[c], std::max(pageThreads, 2))) {
                 if (whys[c].empty()) whys[c] = "corrupt Parquet chunk";
                 return;
             }
