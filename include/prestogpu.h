@@ -136,9 +136,18 @@ pgpu_status pgpu_on_unblocked(pgpu_pipeline* p, pgpu_callback fn, void* user);
  * what PagesSerdeUtil.writeRawPage produces (main/execution/buffer/PagesSerdeUtil.java:45-62): int32 channel count, then per
  * block the length-prefixed encoding name and body (LONG_ARRAY / INT_ARRAY / BYTE_ARRAY / INT128_ARRAY / VARIABLE_WIDTH, and
  * DICTIONARY / RLE over those; spi/block/{Long,Int,...}ArrayBlockEncoding.java etc.). Only the block headers are read on the host: the payload goes
- * to the device in ONE copy and is decoded there (null bit stream -> flags, non-null-only values -> positions). Compressed or
- * encrypted pages (PageCodecMarker) must be decoded by the caller first. `data` may be reused when the call returns. */
+ * to the device in ONE copy and is decoded there (null bit stream -> flags, non-null-only values -> positions). Pages with codec
+ * markers go through pgpu_add_serialized_page_marked. `data` may be reused when the call returns. */
 pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size_t len, int64_t position_count);
+/* The same for a SerializedPage as it travels (main/execution/buffer/SerializedPage.java): `markers` = its PageCodecMarker set
+ * (PageCodecMarker.java:28-29: COMPRESSED = bit 0, ENCRYPTED = bit 1), `uncompressed_size` = getUncompressedSizeInBytes().
+ * COMPRESSED slices are LZ4 blocks (PagesSerde.java:156-165, airlift Lz4Decompressor) and are inflated on the host, as
+ * PagesSerde.deserialize does, before the payload goes to the device; ENCRYPTED pages are PGPU_NOT_SUPPORTED (the spill cipher
+ * is the caller's). */
+#define PGPU_PAGE_MARKER_COMPRESSED 1
+#define PGPU_PAGE_MARKER_ENCRYPTED 2
+pgpu_status pgpu_add_serialized_page_marked(pgpu_pipeline* p, const uint8_t* data, size_t len, int64_t position_count, int32_t markers,
+                                            int64_t uncompressed_size);
 /* Operator.getOutput() in the same wire format: *data / *len = the payload PagesSerdeUtil.writeRawPage would write for the
  * output page (library-owned pinned memory, valid until the next call on this pipeline), *rows = its position count, or
  * -1 when there is no output now. Null flags are bit-packed, nullable fixed-width blocks carry only their non-null values,

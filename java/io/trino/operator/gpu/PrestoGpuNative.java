@@ -39,6 +39,13 @@ final class PrestoGpuNative
     static native void addSerializedPage(long handle, long address, int length, int positionCount);
 
     /**
+     * pgpu_add_serialized_page_marked — a SerializedPage as it arrives from an output buffer: its slice, position count,
+     * PageCodecMarker byte (SerializedPage.getPageCodecMarkers()) and getUncompressedSizeInBytes(). LZ4-compressed slices are
+     * inflated natively; encrypted pages raise NOT_SUPPORTED.
+     */
+    static native void addSerializedPageMarked(long handle, long address, int length, int positionCount, int markers, int uncompressedSize);
+
+    /**
      * pgpu_add_parquet_row_group — Operator.addInput of the Page ParquetReader.nextPage would build from one row group. Per channel:
      * the column chunk's bytes as they lie in the file (ColumnChunkMetaData.getStartingPos() .. + getTotalSize(), decompressed page
      * by page if the codec is not UNCOMPRESSED) as address / length of a direct buffer, the parquet physical type ordinal

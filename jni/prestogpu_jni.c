@@ -127,6 +127,14 @@ JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addSerializedP
     if (st != PGPU_OK) throwTrino(env, st, pgpu_last_error(p));
 }
 
+/* a SerializedPage with its PageCodecMarker set and uncompressed size (PagesSerde.deserialize :131-170) */
+JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addSerializedPageMarked(JNIEnv* env, jclass cls, jlong h, jlong address, jint length, jint positionCount,
+                                                                                        jint markers, jint uncompressedSize) {
+    pgpu_pipeline* p = (pgpu_pipeline*)(intptr_t)h;
+    pgpu_status st = pgpu_add_serialized_page_marked(p, (const uint8_t*)(intptr_t)address, (size_t)length, positionCount, markers, uncompressedSize);
+    if (st != PGPU_OK) throwTrino(env, st, pgpu_last_error(p));
+}
+
 /* addParquetRowGroup: the chunks are direct (off-heap) buffers, so nothing is pinned; the small per-channel arrays are copied. */
 JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addParquetRowGroup(JNIEnv* env, jclass cls, jlong h, jlong rows, jlongArray address,
                                                                                    jlongArray length, jintArray physicalType, jintArray maxDefinitionLevel,

@@ -76,6 +76,7 @@ SYMBOLS = [
     ("pgpu_stream", ctypes.c_void_p, [_P]),
     ("pgpu_partition_output_device", ctypes.c_int32, [_P, ctypes.c_int32, _COLS, ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_add_serialized_page", ctypes.c_int32, [_P, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int64]),
+    ("pgpu_add_serialized_page_marked", ctypes.c_int32, [_P, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int64, ctypes.c_int32, ctypes.c_int64]),
     ("pgpu_get_serialized_output", ctypes.c_int32, [_P, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_int64)]),
     ("pgpu_add_parquet_row_group", ctypes.c_int32, [_P, ctypes.POINTER(ParquetChunk), ctypes.c_int32, ctypes.c_int64]),
     ("pgpu_parquet_inspect_chunk", ctypes.c_int32, [ctypes.POINTER(ParquetChunk), ctypes.POINTER(ctypes.c_int64), ctypes.c_char_p, ctypes.c_size_t]),

@@ -2072,6 +2072,18 @@ bool parseWireBlock(WireReader& r, WireBlock& b, int depth, std::string& why) {
 
 }  // namespace
 
+pgpu_status pgpu_add_serialized_page_marked(pgpu_pipeline* p, const uint8_t* data, size_t len, int64_t position_count, int32_t markers, int64_t uncompressed_size) {
+    if (!p || (!data && len)) return PGPU_INVALID_ARGUMENT;
+    if (markers & ~(PGPU_PAGE_MARKER_COMPRESSED | PGPU_PAGE_MARKER_ENCRYPTED)) return fail(p, PGPU_INVALID_ARGUMENT, "unknown page codec markers");
+    if (markers & PGPU_PAGE_MARKER_ENCRYPTED) return fail(p, PGPU_NOT_SUPPORTED, "not supported on the GPU path: encrypted pages (the spill cipher is the caller's)");
+    if (!(markers & PGPU_PAGE_MARKER_COMPRESSED)) return pgpu_add_serialized_page(p, data, len, position_count);
+    // PagesSerde.deserialize :156-165: decompress into a buffer of getUncompressedSizeInBytes(), the sizes must agree
+    if (uncompressed_size < 0 || uncompressed_size > ((int64_t)1 << 31)) return fail(p, PGPU_INVALID_ARGUMENT, "uncompressed size of a compressed page");
+    std::vector<uint8_t> raw((size_t)uncompressed_size);
+    if (!pq::lz4Decompress(data, len, raw.data(), raw.size())) return fail(p, PGPU_INVALID_ARGUMENT, "corrupt page: the LZ4 slice does not decompress to its declared size");
+    return pgpu_add_serialized_page(p, raw.data(), raw.size(), position_count);
+}
+
 pgpu_status pgpu_add_serialized_page(pgpu_pipeline* p, const uint8_t* data, size_t len, int64_t position_count) {
     if (!p || (!data && len)) return PGPU_INVALID_ARGUMENT;
     if (p->device < 0) return fail(p, PGPU_INVALID_STATE, "pipeline was created compile-only (device < 0)");

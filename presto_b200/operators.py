@@ -131,6 +131,11 @@ class GpuPipelineOperator:
         main/execution/buffer/PagesSerdeUtil.java:45-62); decoded on the device."""
         self._check(self._lib.pgpu_add_serialized_page(self._h, payload, len(payload), positionCount))
 
+    def addSerializedPage(self, slice_: bytes, positionCount: int, markers: int = 0, uncompressedSizeInBytes: int = 0):
+        """addInput of a SerializedPage as it travels (main/execution/buffer/SerializedPage.java): markers = PageCodecMarker set
+        (1 = COMPRESSED: the slice is an LZ4 block, inflated on the host as PagesSerde.deserialize does; 2 = ENCRYPTED: rejected)."""
+        self._check(self._lib.pgpu_add_serialized_page_marked(self._h, slice_, len(slice_), positionCount, markers, uncompressedSizeInBytes))
+
     def addParquetRowGroup(self, chunks, rows: int):
         """addInput of the Page the reference's ParquetReader.nextPage would build from one row group
         (lib/trino-parquet/.../reader/ParquetReader.java:211-268): chunks[c] = (column chunk bytes as they lie in the file,

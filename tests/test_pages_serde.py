@@ -324,3 +324,74 @@ def test_serialized_output_of_filter_and_project():
         finally:
             op.close()
     assert outs[0] == outs[1] and 0 < len(outs[0]) < n      # order preserving compaction: same rows in the same order
+
+
+@pytest.mark.gpu
+def test_compressed_serialized_pages():
+    """SerializedPages with the COMPRESSED marker (PagesSerde.serialize :96-118: the payload as one LZ4 block, kept only when it
+    shrinks below 80 %): inflated on the host as PagesSerde.deserialize :156-165 does. Compressed here with Arrow's LZ4 codec, an
+    implementation independent of the library's decoder."""
+    pa = pytest.importorskip("pyarrow")
+    from presto_b200.operators import GpuPipelineOperator, TrinoException
+    from util import assert_rows_equal_ignore_order
+    total = 250_000
+    pages = [tpch.q1_page(0, 100_000, total), tpch.q1_page_encoded(100_000, 150_000, total)]
+    blocks, _ = _run_both(tpch.q1_plan(), pages)
+    codec = pa.Codec("lz4_raw")
+    op = GpuPipelineOperator(tpch.q1_plan(), 0)
+    try:
+        shrunk = 0
+        for pg in pages:
+            raw = S.write_raw_page(pg.blocks)
+            packed = codec.compress(raw, asbytes=True)
+            if len(packed) <= 0.8 * len(raw):                 # PagesSerde.MINIMUM_COMPRESSION_RATIO
+                op.addSerializedPage(packed, pg.position_count, markers=1, uncompressedSizeInBytes=len(raw))
+                shrunk += 1
+            else:
+                op.addSerializedPage(raw, pg.position_count, markers=0, uncompressedSizeInBytes=len(raw))
+        assert shrunk >= 1
+        op.finish()
+        got = _drain(op)
+    finally:
+        op.close()
+    assert_rows_equal_ignore_order(got, blocks, nkeys=2, rtol=1e-12)
+    # wrong sizes, damaged slices and encrypted pages are errors
+    op = GpuPipelineOperator(tpch.q1_plan(), 0)
+    try:
+        raw = S.write_raw_page(pages[0].blocks)
+        packed = codec.compress(raw, asbytes=True)
+        for slice_, markers, size in ((packed, 1, len(raw) - 1), (packed[:len(packed) // 2], 1, len(raw)), (raw, 1, len(raw)), (raw, 2, len(raw)), (raw, 8, len(raw))):
+            with pytest.raises(TrinoException):
+                op.addSerializedPage(slice_, pages[0].position_count, markers=markers, uncompressedSizeInBytes=size)
+        assert op.needsInput()
+    finally:
+        op.close()
+
+
+def test_lz4_slices_are_decoded_on_the_host_without_a_gpu():
+    """a compile-only pipeline (device -1) gets as far as the host-side LZ4 decode: a good slice then fails with "compile-only",
+    a damaged one with "corrupt page" — pins the block decoder against Arrow's encoder on the CPU"""
+    pa = pytest.importorskip("pyarrow")
+    from presto_b200.operators import GpuPipelineOperator, TrinoException
+    rng = np.random.default_rng(3)
+    page = tpch.q1_page(0, 50_000, 50_000)
+    raw = S.write_raw_page(page.blocks)
+    packed = pa.Codec("lz4_raw").compress(raw, asbytes=True)
+    assert len(packed) < len(raw)
+    op = GpuPipelineOperator(tpch.q1_plan(), -1)
+    try:
+        with pytest.raises(TrinoException) as e:
+            op.addSerializedPage(packed, page.position_count, markers=1, uncompressedSizeInBytes=len(raw))
+        assert "compile-only" in str(e.value)
+        for trial in range(20):
+            bad = bytearray(packed)
+            for at in rng.integers(0, len(bad), 4):
+                bad[at] ^= int(rng.integers(1, 256))
+            with pytest.raises(TrinoException) as e:
+                op.addSerializedPage(bytes(bad), page.position_count, markers=1, uncompressedSizeInBytes=len(raw))
+            assert "corrupt page" in str(e.value) or "compile-only" in str(e.value)   # (a flipped literal byte still decodes)
+        with pytest.raises(TrinoException) as e:
+            op.addSerializedPage(packed, page.position_count, markers=2, uncompressedSizeInBytes=len(raw))
+        assert "encrypted" in str(e.value)
+    finally:
+        op.close()
