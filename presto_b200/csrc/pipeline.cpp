@@ -2043,6 +2043,15 @@ bool parseWireBlock(WireReader& r, WireBlock& b, int depth, std::string& why) {
         if (r.ok && b.hasNulls) b.nonNull = r.i32();
         if (!r.ok || b.nonNull < 0 || b.nonNull > b.n) { why = "corrupt " + name + " block"; return false; }
         b.valuesOff = r.skip((size_t)b.nonNull * (size_t)width);
+        // The device scatters the nonNull values to the positions whose null bit is clear: the two must agree, or the kernel would
+        // read past the values (the reference fails in readBlock with an index error instead). n / 8 bytes of popcount.
+        if (r.ok && b.hasNulls) {
+            int64_t set = 0;
+            const uint8_t* bits = r.d + b.bitsOff;
+            for (int64_t k = 0; k < b.n / 8; k++) set += __builtin_popcount(bits[k]);
+            if (b.n % 8) set += __builtin_popcount(bits[b.n / 8] >> (8 - b.n % 8));  // most significant bit first (EncoderUtil.encodeNullsAsBits)
+            if (set != b.n - b.nonNull) { why = "corrupt " + name + " block: " + std::to_string(b.nonNull) + " values for " + std::to_string(b.n - set) + " non-null positions"; return false; }
+        }
     } else if (name == "VARIABLE_WIDTH") {
         b.kind = WireBlock::VARWIDTH;
         b.offsetsOff = r.skip((size_t)b.n * 4);
@@ -2050,6 +2059,17 @@ bool parseWireBlock(WireReader& r, WireBlock& b, int depth, std::string& why) {
         b.dataLen = r.i32();
         if (!r.ok || b.dataLen < 0) { why = "corrupt VARIABLE_WIDTH block"; return false; }
         b.valuesOff = r.skip((size_t)b.dataLen);
+        if (r.ok) {  // end offsets: ascending and inside the data (VariableWidthBlockEncoding.readBlock trusts them; the device would follow them)
+            int32_t prev = 0;
+            bool sane = true;
+            for (int64_t k = 0; k < b.n; k++) {
+                int32_t e;
+                memcpy(&e, r.d + b.offsetsOff + (size_t)k * 4, 4);
+                sane &= e >= prev;
+                prev = e;
+            }
+            if (!sane || prev > b.dataLen) { why = "corrupt VARIABLE_WIDTH block: offsets are not ascending or exceed the data length"; return false; }
+        }
     } else if (name == "DICTIONARY" || name == "RLE") {
         if (depth > 0) { why = "not supported on the GPU path: nested dictionary/RLE encodings"; return false; }
         b.kind = name == "RLE" ? WireBlock::RLE : WireBlock::DICTIONARY;
@@ -2058,6 +2078,15 @@ bool parseWireBlock(WireReader& r, WireBlock& b, int depth, std::string& why) {
         if (b.kind == WireBlock::DICTIONARY) {
             b.valuesOff = r.skip((size_t)b.n * 4);
             r.skip(24);  // DictionaryId: most / least significant bits, sequence id
+            if (r.ok) {  // ids index the dictionary on the device (and its shared-memory copy): every id must be inside it
+                uint32_t worst = 0;
+                for (int64_t k = 0; k < b.n; k++) {
+                    uint32_t id;
+                    memcpy(&id, r.d + b.valuesOff + (size_t)k * 4, 4);
+                    worst = std::max(worst, id);  // a negative id is a huge unsigned one
+                }
+                if (b.n > 0 && worst >= (uint32_t)b.child->n) { why = "corrupt DICTIONARY block: id " + std::to_string((int32_t)worst) + " outside a dictionary of " + std::to_string(b.child->n) + " entries"; return false; }
+            }
         } else if (b.child->n != 1) {
             why = "RLE value block must have exactly one position";
             return false;

@@ -196,6 +196,57 @@ def test_serialized_page_errors():
         op.close()
 
 
+@pytest.mark.gpu
+def test_corrupt_serialized_blocks_are_errors_not_faults():
+    """header fields the device would follow blindly are checked on the host first: the non-null count against the null bits, the
+    end offsets of VARIABLE_WIDTH blocks, dictionary ids against the dictionary (the reference fails with index errors in readBlock)"""
+    import struct
+    from presto_b200.operators import Aggregation, GpuPipelineOperator, TrinoException, plan_text
+    n = 1000
+    rng = np.random.default_rng(1)
+    nulls = (rng.random(n) < 0.3).astype(np.uint8)
+    v8 = createVarcharType(8)
+    words = ["", "a", "bcd", "efghijkl"]
+    key = VariableWidthBlock.from_values(v8, [words[int(x)] for x in rng.integers(0, 4, n)])
+    dict_block = DictionaryBlock(LongArrayBlock(BIGINT, np.arange(10)), rng.integers(0, 10, n).astype(np.int32))
+    page = Page(key, LongArrayBlock(BIGINT, rng.integers(0, 100, n), nulls), dict_block)
+    plan = plan_text([v8, BIGINT, BIGINT], step="single", groupByChannels=[0], aggregations=[Aggregation("sum", BIGINT, 1, BIGINT), Aggregation("sum", BIGINT, 2, BIGINT)], expectedGroups=16)
+    good = bytearray(S.write_raw_page(page.blocks))
+
+    def at(name, nth=0):
+        i = -1
+        for _ in range(nth + 1):
+            i = good.index(name, i + 1)
+        return i + len(name)
+
+    cases = {}
+    # VARIABLE_WIDTH: [positionCount][n end offsets]...: a descending offset, and one beyond the data
+    vw = at(b"VARIABLE_WIDTH")
+    bad = bytearray(good); struct.pack_into("<i", bad, vw + 4 + 4 * 10, 0); cases["offsets descend"] = bad
+    bad = bytearray(good); struct.pack_into("<i", bad, vw + 4 + 4 * (n - 1), 1 << 30); cases["offset beyond the data"] = bad
+    # LONG_ARRAY with nulls: [positionCount][hasNulls = 1][bits][nonNull count]...: flip a null bit / change the count
+    la = at(b"LONG_ARRAY")
+    bad = bytearray(good); bad[la + 4 + 1 + 3] ^= 0x10; cases["null bit flipped"] = bad
+    cnt = la + 4 + 1 + (n + 7) // 8
+    bad = bytearray(good); struct.pack_into("<i", bad, cnt, struct.unpack_from("<i", good, cnt)[0] - 1); cases["non-null count lowered"] = bad
+    # DICTIONARY: [positionCount][dictionary block][n ids][24 bytes id]: an id outside the dictionary, and a negative one
+    ids = len(good) - 24 - 4 * n
+    bad = bytearray(good); struct.pack_into("<i", bad, ids + 4 * 7, 10); cases["id == dictionary size"] = bad
+    bad = bytearray(good); struct.pack_into("<i", bad, ids + 4 * 7, -1); cases["negative id"] = bad
+    op = GpuPipelineOperator(plan, 0)
+    try:
+        for name, payload in cases.items():
+            with pytest.raises(TrinoException) as e:
+                op.addSerializedInput(bytes(payload), n)
+            assert "corrupt" in str(e.value), (name, str(e.value))
+        op.addSerializedInput(bytes(good), n)     # the pipeline is still usable and the device never saw the bad pages
+        op.finish()
+        from util import assert_rows_equal_ignore_order, run_oracle
+        assert_rows_equal_ignore_order(_drain(op), run_oracle(plan, [page]), nkeys=1)
+    finally:
+        op.close()
+
+
 # ------------------------------------------------------------------------------------------- GPU output in wire format
 def _decoded_rows(blocks):
     cols = [S.block_values(b) for b in blocks]
