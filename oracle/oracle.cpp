@@ -806,6 +806,7 @@ struct AccState {
     int64_t lval = 0;
     double dval = 0.0;
     Dec128 qval;           // min / max over long DECIMAL (NullableInt128State-like: the value as the block holds it)
+    std::string sval;      // min / max over VARCHAR (SliceState)
 };
 
 struct Accumulator {
@@ -866,6 +867,13 @@ struct Accumulator {
                             take = key(v) < key(s.dval);
                         }
                         if (take) s.dval = v;
+                    } else if (t.kind == TypeKind::VARCHAR) {  // SliceState, compared with Slice.compareTo: unsigned bytes, a proper prefix first
+                        const std::string& v = arg->s[k];
+                        if (s.isNull) { s.isNull = false; s.sval = v; break; }
+                        const size_t m = std::min(v.size(), s.sval.size());
+                        int c = memcmp(v.data(), s.sval.data(), m);
+                        if (c == 0) c = v.size() < s.sval.size() ? -1 : v.size() > s.sval.size() ? 1 : 0;
+                        if (isMax ? c > 0 : c < 0) s.sval = v;
                     } else if (t.isLongDecimal()) {  // Int128 state compared with UnscaledDecimal128Arithmetic.compare (decimal128.h)
                         const Dec128& v = arg->q[k];
                         if (s.isNull) { s.isNull = false; s.qval = v; break; }
@@ -928,6 +936,7 @@ struct Accumulator {
                     v.type = ch[0]->type;
                     if (t.kind == TypeKind::DOUBLE) v.d.push_back(ch[0]->d[k]);
                     else if (t.isLongDecimal()) v.q.push_back(ch[0]->q[k]);
+                    else if (t.kind == TypeKind::VARCHAR) v.s.push_back(ch[0]->s[k]);
                     else v.i.push_back(ch[0]->i[k]);
                     addInput(&g, 1, &v, nullptr);
                     break;
@@ -1169,6 +1178,7 @@ struct Oracle {
                     case AggFn::MAX:
                         if (t.kind == TypeKind::DOUBLE) putD(result[oc++], s.dval, s.isNull);
                         else if (t.isLongDecimal()) putQ(result[oc++], s.qval, s.isNull);
+                        else if (t.kind == TypeKind::VARCHAR) putS(result[oc++], s.sval, s.isNull);
                         else putI(result[oc++], s.lval, s.isNull);
                         break;
                 }

@@ -1098,9 +1098,10 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     // aggregation's state array): a zero word is put in front when the pair would start at an odd word.
     const bool taglessByKey = res.mode == KernelMode::AGG_HASH && res.KW >= 1 && res.KW <= 2 && keyLen < res.KW * 8 && !getenv("PGPU_TUNE_TAGGED");
     const int cellBaseWord = res.mode == KernelMode::AGG_HASH ? (taglessByKey ? 0 : 1) + res.KW : 0;
-    auto minMax128Cell = [&](bool isMax, const std::string& ident, const std::string& cond, const std::string& v128) -> int {
+    // img: an unsigned 128-bit expression whose order is the values' order
+    auto decImage = [](const std::string& v128) { return "((u128)(" + v128 + ") ^ ((u128)1 << 127))"; };
+    auto minMax128Cell = [&](bool isMax, const std::string& ident, const std::string& cond, const std::string& img) -> int {
         if ((cellBaseWord + nw) & 1) getCell("pad", "pad" + std::to_string(nw), 1, {"0ull"});
-        const std::string img = "((u128)(" + v128 + ") ^ ((u128)1 << 127))";
         const std::string enc = isMax ? img : "(~" + img + ")";
         return getCell(isMax ? "max128" : "min128", ident, 2, {sel1(cond, "(u64)" + enc, "0ull"), sel1(cond, "(u64)(" + enc + " >> 64)", "0ull")});
     };
@@ -1154,7 +1155,10 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
                     } else if (t.kind == TypeKind::BOOLEAN) {
                         k = "(i64)(" + x.v + " ? 1 : 0)";
                     } else if (t.isLongDecimal()) {
-                        ac.ext = minMax128Cell(isMax, vid, cond, "(i128)" + x.v);
+                        ac.ext = minMax128Cell(isMax, vid, cond, decImage("(i128)" + x.v));
+                        break;
+                    } else if (t.kind == TypeKind::VARCHAR) {
+                        ac.ext = minMax128Cell(isMax, vid, cond, "varchar_order_image(" + x.v + ", " + x.hi + ")");
                         break;
                     } else {
                         k = "(i64)" + x.v;
@@ -1210,9 +1214,9 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
                     std::string cond = nn(x), k;
                     if (t.kind == TypeKind::DOUBLE) k = isMax ? "((" + x.v + " != " + x.v + ") ? (i64)0x8000000000000000ull : f64_order_key(" + x.v + "))" : "f64_order_key(" + x.v + ")";
                     else if (t.kind == TypeKind::BOOLEAN) k = "(i64)(" + x.v + " ? 1 : 0)";
-                    else if (t.isLongDecimal()) {
+                    else if (t.isLongDecimal() || t.kind == TypeKind::VARCHAR) {
                         ac.cnt = getCell("cnt", "F" + std::to_string(a.arg), 1, {sel1(cond, "1ull", "0ull")});
-                        ac.ext = minMax128Cell(isMax, "F" + std::to_string(a.arg), cond, "(i128)" + x.v);
+                        ac.ext = minMax128Cell(isMax, "F" + std::to_string(a.arg), cond, t.kind == TypeKind::VARCHAR ? "varchar_order_image(" + x.v + ", " + x.hi + ")" : decImage("(i128)" + x.v));
                         break;
                     } else k = "(i64)" + x.v;
                     std::string enc = isMax ? "((u64)" + k + " ^ 0x8000000000000000ull)" : "(~((u64)" + k + " ^ 0x8000000000000000ull))";
@@ -1541,6 +1545,11 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
                 return isMax ? "(i64)(" + raw + " ^ 0x8000000000000000ull)" : "(i64)((~" + raw + ") ^ 0x8000000000000000ull)";
             };
             auto storeMinMax = [&](int k, bool isMax) {
+                if (t.kind == TypeKind::VARCHAR) {  // the image back to the 16-byte cell [length | bytes]
+                    const std::string img = "(((u128)" + cw(ac.ext, 1) + " << 64) | (u128)" + cw(ac.ext, 0) + ")";
+                    L("((raw128*)out.c[" + O(k) + "].values)[pos] = varchar_from_order_image(" + std::string(isMax ? "" : "~") + img + ");");
+                    return;
+                }
                 if (t.isLongDecimal()) {  // the image back to the value, then the block's sign-magnitude words
                     const std::string img = "(((u128)" + cw(ac.ext, 1) + " << 64) | (u128)" + cw(ac.ext, 0) + ")";
                     L("{ raw128 q = dec_to_raw((i128)(" + std::string(isMax ? "" : "~") + img + " ^ ((u128)1 << 127))); u64* o = (u64*)out.c[" + O(k) + "].values + 2 * pos; o[0] = q.lo; o[1] = q.hi; }");

@@ -429,6 +429,25 @@ PGPU_DEV void max128_combine(u64& alo, u64& ahi, u64 blo, u64 bhi) {
         ahi = bhi;
     }
 }
+// VARCHAR(n <= 15) values travel as 16-byte cells [length byte | up to 15 bytes] in two words (lo = byte 0..7). Their order is
+// the unsigned byte order of the characters, a proper prefix first (Slice.compareTo): the image puts the bytes in big-endian
+// order and the length last, so that comparing the 128-bit numbers compares the strings.
+PGPU_DEV u64 bswap_u64(u64 x) {
+    return ((u64)__byte_perm((u32)x, 0, 0x0123) << 32) | (u64)__byte_perm((u32)(x >> 32), 0, 0x0123);
+}
+PGPU_DEV u128 varchar_order_image(u64 lo, u64 hi) {
+    const u64 d0 = (lo >> 8) | (hi << 56);  // characters 0..7
+    const u64 d1 = hi >> 8;                 // characters 8..14
+    return ((u128)bswap_u64(d0) << 64) | (u128)(bswap_u64(d1) | (lo & 0xffull));
+}
+PGPU_DEV raw128 varchar_from_order_image(u128 img) {
+    const u64 ilo = (u64)img, ihi = (u64)(img >> 64);
+    const u64 d0 = bswap_u64(ihi), d1 = bswap_u64(ilo & ~0xffull);
+    raw128 q;
+    q.lo = (ilo & 0xffull) | (d0 << 8);
+    q.hi = (d0 >> 56) | (d1 << 8);
+    return q;
+}
 PGPU_DEV void max128_warp_reduce(u64& lo, u64& hi);   // after shfl_xor_u64
 PGPU_DEV void max128_atomic(u64* cell, u64 lo, u64 hi);  // after ld_relaxed_u128 / cas_u128
 

@@ -558,6 +558,8 @@ void checkAgg(const AggSpec& a) {
             if (in.kind == TypeKind::BIGINT || in.kind == TypeKind::INTEGER || in.kind == TypeKind::DATE || in.kind == TypeKind::DOUBLE ||
                 in.kind == TypeKind::DECIMAL || in.kind == TypeKind::BOOLEAN)
                 return;
+            // VARCHAR(n <= 15): the value fits the 16-byte cell the GPU path keeps varchar values in (one 128-bit min / max cell)
+            if (in.kind == TypeKind::VARCHAR && in.precision >= 1 && in.precision <= 15) return;
             no();
             return;
     }

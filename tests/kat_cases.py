@@ -103,21 +103,21 @@ def global_aggregate_cases():
 def hash_aggregation_cases(number_of_rows=40_000):
     """TestHashAggregationOperator.testHashAggregation (:161-219): three sequence pages of `number_of_rows` rows whose key
     channel is the row index; expected per group i: count 3, sum 3i, avg i, count(col) 3, count(bool) 3.
-    (The reference keys on unbounded VARCHAR and also takes max(varchar); the GPU subset holds varchar(n<=15) keys and
-    numeric min/max, so the key is varchar(8) of the same digits and max runs over the BIGINT channel.)"""
+    (The reference declares its VARCHAR channels unbounded; the GPU subset holds varchar(n <= 15) values, so the key and the
+    max(varchar) channel are varchar(8) of the same digits: same rows, same expected strings.)"""
     V8 = createVarcharType(8)
     n = number_of_rows
     keys = [str(i) for i in range(n)]
     pages = []
     for base in (100_000, 200_000, 300_000):
         pages.append(Page(VariableWidthBlock.from_values(V8, keys), LongArrayBlock(BIGINT, np.arange(n)),
-                          LongArrayBlock(BIGINT, np.arange(base, base + n)),
+                          VariableWidthBlock.from_values(V8, [str(base + i) for i in range(n)]),
                           block_of(BOOLEAN, [(i + 500) % 2 == 0 for i in range(n)])))
     aggs = [Aggregation("count", BIGINT), Aggregation("sum", BIGINT, 1, BIGINT), Aggregation("avg", DOUBLE, 1, BIGINT),
-            Aggregation("max", BIGINT, 2, BIGINT), Aggregation("count", BIGINT, 0, V8), Aggregation("count", BIGINT, 3, BOOLEAN)]
-    plan = plan_text([V8, BIGINT, BIGINT, BOOLEAN], step="single", groupByChannels=[0], aggregations=aggs, expectedGroups=100_000,
+            Aggregation("max", V8, 2, V8), Aggregation("count", BIGINT, 0, V8), Aggregation("count", BIGINT, 3, BOOLEAN)]
+    plan = plan_text([V8, BIGINT, V8, BOOLEAN], step="single", groupByChannels=[0], aggregations=aggs, expectedGroups=100_000,
                      maxOutputRows=8192)
-    exp = [(str(i), 3, 3 * i, float(i), 300_000 + i, 3, 3) for i in range(n)]
+    exp = [(str(i), 3, 3 * i, float(i), str(300_000 + i), 3, 3) for i in range(n)]
     cases = [("hash_aggregation_40000x3", plan, pages, exp, 1)]
 
     # BIGINT key with a NULL group (TestGroupByHash.testNullGroup :157-185) + rehash from a tiny expected size (:225-250)
