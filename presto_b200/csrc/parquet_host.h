@@ -465,6 +465,200 @@ inline bool lz4Decompress(const uint8_t* in, size_t n, uint8_t* out, size_t outL
     return op == outLen;
 }
 
+// DEFLATE (RFC 1951) inside a gzip member (RFC 1952): what Hadoop's GzipCodec — the reference's GZIP pages — writes.
+// Canonical Huffman codes are decoded bit by bit from per-length counts and the symbols sorted by (length, value).
+struct Inflater {
+    const uint8_t* in;
+    size_t n, ip = 0;
+    uint32_t hold = 0;
+    int nbits = 0;
+    bool ok = true;
+    uint32_t bits(int need) {
+        while (nbits < need) {
+            if (ip >= n) { ok = false; return 0; }
+            hold |= (uint32_t)in[ip++] << nbits;
+            nbits += 8;
+        }
+        const uint32_t v = hold & ((1u << need) - 1u);
+        hold >>= need;
+        nbits -= need;
+        return v;
+    }
+    struct Code {
+        uint16_t count[16];
+        uint16_t symbol[288];
+    };
+    // false when the lengths over-subscribe the code space
+    static bool build(Code& c, const uint8_t* lengths, int nsym) {
+        memset(c.count, 0, sizeof c.count);
+        for (int k = 0; k < nsym; k++) c.count[lengths[k]]++;
+        int left = 1;
+        for (int len = 1; len <= 15; len++) {
+            left = (left << 1) - c.count[len];
+            if (left < 0) return false;
+        }
+        uint16_t first[16];
+        first[1] = 0;
+        for (int len = 1; len < 15; len++) first[len + 1] = (uint16_t)(first[len] + c.count[len]);
+        for (int k = 0; k < nsym; k++)
+            if (lengths[k]) c.symbol[first[lengths[k]]++] = (uint16_t)k;
+        return true;
+    }
+    int decode(const Code& c) {
+        int code = 0, first = 0, index = 0;
+        for (int len = 1; len <= 15; len++) {
+            code |= (int)bits(1);
+            if (!ok) return -1;
+            const int count = c.count[len];
+            if (code - count < first) return c.symbol[index + (code - first)];
+            index += count;
+            first = (first + count) << 1;
+            code <<= 1;
+        }
+        ok = false;
+        return -1;
+    }
+    bool codes(const Code& lit, const Code& dist, uint8_t* out, size_t outLen, size_t& op) {
+        static const uint16_t lbase[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
+        static const uint8_t lext[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
+        static const uint16_t dbase[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
+        static const uint8_t dext[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
+        for (;;) {
+            const int sym = decode(lit);
+            if (sym < 0) return false;
+            if (sym < 256) {
+                if (op >= outLen) return false;
+                out[op++] = (uint8_t)sym;
+            } else if (sym == 256) {
+                return true;
+            } else {
+                if (sym > 285) return false;
+                const size_t len = lbase[sym - 257] + bits(lext[sym - 257]);
+                const int ds = decode(dist);
+                if (ds < 0 || ds > 29) return false;
+                const size_t d = dbase[ds] + bits(dext[ds]);
+                if (!ok || d > op || len > outLen - op) return false;
+                for (size_t k = 0; k < len; k++) out[op + k] = out[op - d + k];
+                op += len;
+            }
+        }
+    }
+    bool inflate(uint8_t* out, size_t outLen, size_t& op) {
+        for (;;) {
+            const bool last = bits(1) != 0;
+            const uint32_t type = bits(2);
+            if (!ok) return false;
+            if (type == 0) {  // stored
+                hold = 0;
+                nbits = 0;
+                if (ip + 4 > n) return false;
+                const size_t len = (size_t)in[ip] | ((size_t)in[ip + 1] << 8), nlen = (size_t)in[ip + 2] | ((size_t)in[ip + 3] << 8);
+                ip += 4;
+                if ((len ^ nlen) != 0xffff || len > n - ip || len > outLen - op) return false;
+                memcpy(out + op, in + ip, len);
+                ip += len;
+                op += len;
+            } else if (type == 1) {  // fixed codes
+                uint8_t lengths[288 + 30];
+                for (int k = 0; k < 288; k++) lengths[k] = k < 144 ? 8 : k < 256 ? 9 : k < 280 ? 7 : 8;
+                for (int k = 0; k < 30; k++) lengths[288 + k] = 5;
+                Code lit, dist;
+                build(lit, lengths, 288);
+                build(dist, lengths + 288, 30);
+                if (!codes(lit, dist, out, outLen, op)) return false;
+            } else if (type == 2) {  // dynamic codes
+                static const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+                const int nlen = (int)bits(5) + 257, ndist = (int)bits(5) + 1, ncode = (int)bits(4) + 4;
+                if (!ok || nlen > 286 || ndist > 30) return false;
+                uint8_t lengths[288 + 32];
+                memset(lengths, 0, sizeof lengths);
+                for (int k = 0; k < ncode; k++) lengths[order[k]] = (uint8_t)bits(3);
+                Code lencode;
+                if (!ok || !build(lencode, lengths, 19)) return false;
+                uint8_t ll[288 + 32];
+                int idx = 0;
+                while (idx < nlen + ndist) {
+                    const int sym = decode(lencode);
+                    if (sym < 0) return false;
+                    if (sym < 16) {
+                        ll[idx++] = (uint8_t)sym;
+                        continue;
+                    }
+                    uint8_t prev = 0;
+                    int rep;
+                    if (sym == 16) {
+                        if (idx == 0) return false;
+                        prev = ll[idx - 1];
+                        rep = 3 + (int)bits(2);
+                    } else if (sym == 17) {
+                        rep = 3 + (int)bits(3);
+                    } else {
+                        rep = 11 + (int)bits(7);
+                    }
+                    if (!ok || idx + rep > nlen + ndist) return false;
+                    while (rep--) ll[idx++] = prev;
+                }
+                if (ll[256] == 0) return false;  // no end-of-block code
+                Code lit, dist;
+                if (!build(lit, ll, nlen) || !build(dist, ll + nlen, ndist)) return false;
+                if (!codes(lit, dist, out, outLen, op)) return false;
+            } else {
+                return false;
+            }
+            if (last) return ok;
+        }
+    }
+};
+
+inline uint32_t crc32Of(const uint8_t* d, size_t n) {
+    static uint32_t table[256];
+    static bool ready = [] {
+        for (uint32_t k = 0; k < 256; k++) {
+            uint32_t c = k;
+            for (int j = 0; j < 8; j++) c = (c & 1) ? 0xedb88320u ^ (c >> 1) : c >> 1;
+            table[k] = c;
+        }
+        return true;
+    }();
+    (void)ready;
+    uint32_t c = 0xffffffffu;
+    for (size_t k = 0; k < n; k++) c = table[(c ^ d[k]) & 0xff] ^ (c >> 8);
+    return c ^ 0xffffffffu;
+}
+
+// one or more gzip members -> exactly outLen bytes; CRC-32 and ISIZE of every member are checked
+inline bool gzipDecompress(const uint8_t* in, size_t n, uint8_t* out, size_t outLen) {
+    size_t ip = 0, op = 0;
+    while (ip < n) {
+        if (n - ip < 18 || in[ip] != 0x1f || in[ip + 1] != 0x8b || in[ip + 2] != 8) return false;
+        const uint8_t flg = in[ip + 3];
+        ip += 10;
+        if (flg & 4) {  // FEXTRA
+            if (ip + 2 > n) return false;
+            const size_t x = (size_t)in[ip] | ((size_t)in[ip + 1] << 8);
+            ip += 2 + x;
+        }
+        for (int f = 8; f <= 16; f <<= 1)  // FNAME, FCOMMENT: zero-terminated
+            if (flg & f) {
+                while (ip < n && in[ip]) ip++;
+                ip++;
+            }
+        if (flg & 2) ip += 2;  // FHCRC
+        if (ip >= n) return false;
+        Inflater z{in + ip, n - ip};
+        const size_t start = op;
+        if (!z.inflate(out, outLen, op)) return false;
+        ip += z.ip;  // whole bytes consumed: the trailer is byte aligned
+        if (n - ip < 8) return false;
+        uint32_t crc, isize;
+        memcpy(&crc, in + ip, 4);
+        memcpy(&isize, in + ip + 4, 4);
+        ip += 8;
+        if (isize != (uint32_t)(op - start) || crc != crc32Of(out + start, op - start)) return false;
+    }
+    return op == outLen;
+}
+
 // Thrift compact protocol, just enough to write a page header
 struct HeaderWriter {
     std::vector<uint8_t>& out;
@@ -491,8 +685,8 @@ struct HeaderWriter {
 // reads: sizes, value counts, encodings, level byte lengths), which the rest of the ingest takes as it is.
 inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numValues, std::vector<uint8_t>& out, std::string& why, int threads = 1) {
     using namespace detail;
-    if (codec != SNAPPY && codec != LZ4_RAW) {
-        why = "not supported on the GPU path: Parquet compression codec " + std::to_string(codec) + " (UNCOMPRESSED, SNAPPY and LZ4_RAW pages are read)";
+    if (codec != SNAPPY && codec != LZ4_RAW && codec != GZIP) {
+        why = "not supported on the GPU path: Parquet compression codec " + std::to_string(codec) + " (UNCOMPRESSED, SNAPPY, GZIP and LZ4_RAW pages are read)";
         return false;
     }
     out.clear();
@@ -562,7 +756,8 @@ inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numVal
             uint8_t* dst = out.data() + t.dst;
             bool ok = true;
             if (!t.packed) memcpy(dst, d + t.src, t.dstLen);
-            else if (t.dstLen) ok = codec == SNAPPY ? snappyDecompress(d + t.src, t.srcLen, dst, t.dstLen) : lz4Decompress(d + t.src, t.srcLen, dst, t.dstLen);  // (an empty page may be stored as zero bytes)
+            else if (t.dstLen)  // (an empty page may be stored as zero bytes)
+                ok = codec == SNAPPY ? snappyDecompress(d + t.src, t.srcLen, dst, t.dstLen) : codec == GZIP ? gzipDecompress(d + t.src, t.srcLen, dst, t.dstLen) : lz4Decompress(d + t.src, t.srcLen, dst, t.dstLen);
             bad[k] = ok ? 0 : 1;
         }
     };
@@ -576,7 +771,7 @@ inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numVal
         run(0, tasks.size());
     }
     for (char b : bad)
-        if (b) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
+        if (b) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : codec == GZIP ? "GZIP" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
     return true;
 }
 

@@ -139,9 +139,9 @@ def _write(table, compression, version, **kw):
 
 
 @pytest.mark.parametrize("version", ["1.0", "2.0"])
-@pytest.mark.parametrize("compression,codec", [("SNAPPY", 1), ("LZ4", 7)])
+@pytest.mark.parametrize("compression,codec", [("SNAPPY", 1), ("LZ4", 7), ("GZIP", 2)])
 def test_compressed_pages_are_inflated_on_the_host(compression, codec, version):
-    """SNAPPY and LZ4_RAW pages (ParquetCompressionUtils.java:43-70): the host inflates the chunk, everything downstream sees the same
+    """SNAPPY, GZIP and LZ4_RAW pages (ParquetCompressionUtils.java:43-70): the host inflates the chunk, everything downstream sees the same
     pages as in the uncompressed file — same page / dictionary / run counts, same run tables (up to byte offsets, headers are
     rewritten), and the oracle, which inflates with Arrow's codecs, decodes the same values"""
     pytest.importorskip("pyarrow")
@@ -180,24 +180,27 @@ def test_other_codecs_and_corrupt_compressed_pages_are_errors():
     sys.path.insert(0, GOLDEN)
     import make_parquet_fixtures as M
     table = M.lineitem_table(3000, seed=3)
-    for compression in ("ZSTD", "GZIP"):
+    for compression in ("ZSTD", "BROTLI"):
         rows, cols = chunks_of(_write(table, compression, "1.0"))[0]
         b, pt, md, n, tl, codec = cols["extendedprice"]
         st, _, err = inspect(b, pt, md, n, tl, codec)
         assert st == N.NOT_SUPPORTED and "codec" in err, err
-    rows, cols = chunks_of(_write(table, "SNAPPY", "1.0", use_dictionary=False))[0]
-    b, pt, md, n, tl, codec = cols["extendedprice"]
-    assert inspect(b, pt, md, n, tl, codec)[0] == N.OK
-    assert inspect(b, pt, md, n, tl, 0)[0] == N.NOT_SUPPORTED          # compressed pages handed over as uncompressed
     rng = np.random.default_rng(1)
-    for trial in range(40):                                            # damaged payloads: an error, never a crash
-        bad = bytearray(b)
-        for at in rng.integers(40, len(bad), 6):
-            bad[at] ^= int(rng.integers(1, 256))
-        st, _, err = inspect(bytes(bad), pt, md, n, tl, codec)
-        assert st in (N.OK, N.INVALID_ARGUMENT, N.NOT_SUPPORTED), err
-    st, _, err = inspect(b[:len(b) // 2], pt, md, n, tl, codec)
-    assert st == N.INVALID_ARGUMENT
+    for compression in ("SNAPPY", "GZIP", "LZ4"):
+        rows, cols = chunks_of(_write(table, compression, "1.0", use_dictionary=False))[0]
+        b, pt, md, n, tl, codec = cols["extendedprice"]
+        assert inspect(b, pt, md, n, tl, codec)[0] == N.OK
+        assert inspect(b, pt, md, n, tl, 0)[0] == N.NOT_SUPPORTED          # compressed pages handed over as uncompressed
+        for trial in range(40):                                            # damaged payloads: an error, never a crash
+            bad = bytearray(b)
+            for at in rng.integers(40, len(bad), 6):
+                bad[at] ^= int(rng.integers(1, 256))
+            st, _, err = inspect(bytes(bad), pt, md, n, tl, codec)
+            assert st in (N.OK, N.INVALID_ARGUMENT, N.NOT_SUPPORTED), err
+            if compression == "GZIP":
+                assert st != N.OK, "a damaged gzip member fails its CRC-32"
+        st, _, err = inspect(b[:len(b) // 2], pt, md, n, tl, codec)
+        assert st == N.INVALID_ARGUMENT
 
 
 def test_rejections_and_corruption():
