@@ -47,13 +47,13 @@ final class PrestoGpuNative
 
     /**
      * pgpu_add_parquet_row_group — Operator.addInput of the Page ParquetReader.nextPage would build from one row group. Per channel:
-     * the column chunk's bytes as they lie in the file (ColumnChunkMetaData.getStartingPos() .. + getTotalSize(), decompressed page
-     * by page if the codec is not UNCOMPRESSED) as address / length of a direct buffer, the parquet physical type ordinal
+     * the column chunk's bytes as they lie in the file (ColumnChunkMetaData.getStartingPos() .. + getTotalSize(), still
+     * compressed: `codec` = the chunk's parquet.thrift CompressionCodec, 0 UNCOMPRESSED, 1 SNAPPY, 2 GZIP, 7 LZ4_RAW) as address / length of a direct buffer, the parquet physical type ordinal
      * (PrimitiveTypeName: BOOLEAN 0, INT32 1, INT64 2, DOUBLE 5, BINARY 6, FIXED_LEN_BYTE_ARRAY 7), the column's max definition
-     * level (0 or 1), its value count and, for FIXED_LEN_BYTE_ARRAY, the type length.
+     * level (0 or 1), its value count, for FIXED_LEN_BYTE_ARRAY the type length, and the codec.
      */
     static native void addParquetRowGroup(long handle, long rows, long[] address, long[] length, int[] physicalType, int[] maxDefinitionLevel,
-            long[] valueCount, int[] typeLength);
+            long[] valueCount, int[] typeLength, int[] codec);
 
     /** pgpu_finish — Operator.finish(). */
     static native void finish(long handle);

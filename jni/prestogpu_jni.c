@@ -138,7 +138,7 @@ JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addSerializedP
 /* addParquetRowGroup: the chunks are direct (off-heap) buffers, so nothing is pinned; the small per-channel arrays are copied. */
 JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addParquetRowGroup(JNIEnv* env, jclass cls, jlong h, jlong rows, jlongArray address,
                                                                                    jlongArray length, jintArray physicalType, jintArray maxDefinitionLevel,
-                                                                                   jlongArray valueCount, jintArray typeLength) {
+                                                                                   jlongArray valueCount, jintArray typeLength, jintArray codec) {
     pgpu_pipeline* p = (pgpu_pipeline*)(intptr_t)h;
     jsize n = (*env)->GetArrayLength(env, address);
     if (n > MAX_CH) {
@@ -146,13 +146,14 @@ JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addParquetRowG
         return;
     }
     jlong addr[MAX_CH], len[MAX_CH], count[MAX_CH];
-    jint type[MAX_CH], def[MAX_CH], tl[MAX_CH];
+    jint type[MAX_CH], def[MAX_CH], tl[MAX_CH], cc[MAX_CH];
     (*env)->GetLongArrayRegion(env, address, 0, n, addr);
     (*env)->GetLongArrayRegion(env, length, 0, n, len);
     (*env)->GetLongArrayRegion(env, valueCount, 0, n, count);
     (*env)->GetIntArrayRegion(env, physicalType, 0, n, type);
     (*env)->GetIntArrayRegion(env, maxDefinitionLevel, 0, n, def);
     (*env)->GetIntArrayRegion(env, typeLength, 0, n, tl);
+    (*env)->GetIntArrayRegion(env, codec, 0, n, cc);
     pgpu_parquet_chunk chunks[MAX_CH];
     for (jsize c = 0; c < n; c++) {
         chunks[c].data = (const uint8_t*)(intptr_t)addr[c];
@@ -161,7 +162,7 @@ JNIEXPORT void JNICALL Java_io_trino_operator_gpu_PrestoGpuNative_addParquetRowG
         chunks[c].max_definition_level = def[c];
         chunks[c].num_values = count[c];
         chunks[c].type_length = tl[c];
-        chunks[c].codec = 0;  /* the Java side hands over decompressed chunks (PageReader.readPage has run) */
+        chunks[c].codec = cc[c];  /* CompressionCodecName ordinal as parquet.thrift numbers it: SNAPPY / GZIP / LZ4_RAW chunks are inflated natively */
     }
     pgpu_status st = pgpu_add_parquet_row_group(p, chunks, (int32_t)n, rows);
     if (st != PGPU_OK) throwTrino(env, st, pgpu_last_error(p));
