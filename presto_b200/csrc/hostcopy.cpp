@@ -74,8 +74,53 @@ struct Segment {
     size_t bytes;
 };
 
+inline int32_t loadI32(const char* p) {
+    int32_t v;
+    memcpy(&v, p, 4);
+    return v;
+}
+
+// src[i] >= src[i - 1] for every i of the segment; the element in front of the segment is src[-1] when `hasPred`, else 0
+bool ascending32(const char* src, size_t count, bool hasPred) {
+    if (!count) return true;
+    bool bad = loadI32(src) < (hasPred ? loadI32(src - 4) : 0);
+    size_t i = 1;
+#if PGPU_HAVE_SSE2
+    __m128i acc = _mm_setzero_si128();
+    for (; i + 4 <= count; i += 4) {
+        const __m128i cur = _mm_loadu_si128((const __m128i*)(src + 4 * i)), prv = _mm_loadu_si128((const __m128i*)(src + 4 * i - 4));
+        acc = _mm_or_si128(acc, _mm_cmplt_epi32(cur, prv));
+    }
+    bad |= _mm_movemask_epi8(acc) != 0;
+#endif
+    for (; i < count; i++) bad |= loadI32(src + 4 * i) < loadI32(src + 4 * i - 4);
+    return !bad;
+}
+
+// 0 <= src[i] < limit
+bool idsInRange32(const char* src, size_t count, int32_t limit) {
+    bool bad = false;
+    size_t i = 0;
+#if PGPU_HAVE_SSE2
+    __m128i acc = _mm_setzero_si128();
+    const __m128i zero = _mm_setzero_si128(), top = _mm_set1_epi32(limit - 1);
+    for (; i + 4 <= count; i += 4) {
+        const __m128i cur = _mm_loadu_si128((const __m128i*)(src + 4 * i));
+        acc = _mm_or_si128(acc, _mm_or_si128(_mm_cmplt_epi32(cur, zero), _mm_cmpgt_epi32(cur, top)));
+    }
+    bad |= _mm_movemask_epi8(acc) != 0;
+#endif
+    for (; i < count; i++) {
+        const int32_t v = loadI32(src + 4 * i);
+        bad |= v < 0 || v >= limit;
+    }
+    return !bad;
+}
+
 void runSegment(const Segment& s) {
     if (s.kind == CopyTask::OFFSETS32) copyOffsets((int32_t*)s.dst, s.src, s.bytes / 4, s.delta);
+    else if (s.kind == CopyTask::CHECK_ASCENDING32) { if (!ascending32(s.src, s.bytes / 4, s.delta != 0)) __atomic_store_n((int32_t*)s.dst, 1, __ATOMIC_RELAXED); }
+    else if (s.kind == CopyTask::CHECK_IDS32) { if (!idsInRange32(s.src, s.bytes / 4, s.delta)) __atomic_store_n((int32_t*)s.dst, 1, __ATOMIC_RELAXED); }
     else copyStream(s.dst, s.src, s.bytes);
 }
 
@@ -204,7 +249,9 @@ void hostCopy(const std::vector<CopyTask>& tasks) {
     for (const CopyTask& t : tasks) {
         for (size_t at = 0; at < t.bytes; at += seg) {
             const size_t n = std::min(seg, t.bytes - at);
-            segs.push_back(Segment{(int32_t)t.kind, t.delta, (char*)t.dst + at, (const char*)t.src + at, n});
+            if (t.kind == CopyTask::CHECK_ASCENDING32) segs.push_back(Segment{(int32_t)t.kind, at ? 1 : 0, (char*)t.dst, (const char*)t.src + at, n});  // delta: has a predecessor
+            else if (t.kind == CopyTask::CHECK_IDS32) segs.push_back(Segment{(int32_t)t.kind, t.delta, (char*)t.dst, (const char*)t.src + at, n});
+            else segs.push_back(Segment{(int32_t)t.kind, t.delta, (char*)t.dst + at, (const char*)t.src + at, n});
         }
     }
     if (total < kInlineBytes) {

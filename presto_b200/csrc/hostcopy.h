@@ -11,7 +11,9 @@
 namespace pgpu {
 
 struct CopyTask {
-    enum Kind : int32_t { BYTES = 0, OFFSETS32 = 1 };
+    // CHECK_*: nothing is copied; `dst` points to an int32 the task sets to 1 when the source fails the check (wire-format pages:
+    // the device follows these arrays blindly). CHECK_ASCENDING32: src[0] >= 0 and src[i] >= src[i - 1]; CHECK_IDS32: 0 <= src[i] < delta.
+    enum Kind : int32_t { BYTES = 0, OFFSETS32 = 1, CHECK_ASCENDING32 = 2, CHECK_IDS32 = 3 };
     Kind kind = BYTES;
     void* dst = nullptr;        // BYTES: destination; OFFSETS32: int32 destination (4-byte aligned)
     const void* src = nullptr;  // may be unaligned (wire-format payloads)

@@ -2059,16 +2059,11 @@ bool parseWireBlock(WireReader& r, WireBlock& b, int depth, std::string& why) {
         b.dataLen = r.i32();
         if (!r.ok || b.dataLen < 0) { why = "corrupt VARIABLE_WIDTH block"; return false; }
         b.valuesOff = r.skip((size_t)b.dataLen);
-        if (r.ok) {  // end offsets: ascending and inside the data (VariableWidthBlockEncoding.readBlock trusts them; the device would follow them)
-            int32_t prev = 0;
-            bool sane = true;
-            for (int64_t k = 0; k < b.n; k++) {
-                int32_t e;
-                memcpy(&e, r.d + b.offsetsOff + (size_t)k * 4, 4);
-                sane &= e >= prev;
-                prev = e;
-            }
-            if (!sane || prev > b.dataLen) { why = "corrupt VARIABLE_WIDTH block: offsets are not ascending or exceed the data length"; return false; }
+        if (r.ok && b.n > 0) {  // end offsets: ascending and inside the data (VariableWidthBlockEncoding.readBlock trusts them; the device would follow them)
+            int32_t bad = 0, last;
+            memcpy(&last, r.d + b.offsetsOff + (size_t)(b.n - 1) * 4, 4);
+            hostCopy({CopyTask{CopyTask::CHECK_ASCENDING32, &bad, r.d + b.offsetsOff, (size_t)b.n * 4, 0}});  // on the copy pool's threads: 4 bytes per row
+            if (bad || last > b.dataLen) { why = "corrupt VARIABLE_WIDTH block: offsets are not ascending or exceed the data length"; return false; }
         }
     } else if (name == "DICTIONARY" || name == "RLE") {
         if (depth > 0) { why = "not supported on the GPU path: nested dictionary/RLE encodings"; return false; }
@@ -2078,14 +2073,10 @@ bool parseWireBlock(WireReader& r, WireBlock& b, int depth, std::string& why) {
         if (b.kind == WireBlock::DICTIONARY) {
             b.valuesOff = r.skip((size_t)b.n * 4);
             r.skip(24);  // DictionaryId: most / least significant bits, sequence id
-            if (r.ok) {  // ids index the dictionary on the device (and its shared-memory copy): every id must be inside it
-                uint32_t worst = 0;
-                for (int64_t k = 0; k < b.n; k++) {
-                    uint32_t id;
-                    memcpy(&id, r.d + b.valuesOff + (size_t)k * 4, 4);
-                    worst = std::max(worst, id);  // a negative id is a huge unsigned one
-                }
-                if (b.n > 0 && worst >= (uint32_t)b.child->n) { why = "corrupt DICTIONARY block: id " + std::to_string((int32_t)worst) + " outside a dictionary of " + std::to_string(b.child->n) + " entries"; return false; }
+            if (r.ok && b.n > 0) {  // ids index the dictionary on the device (and its shared-memory copy): every id must be inside it
+                int32_t bad = 0;
+                hostCopy({CopyTask{CopyTask::CHECK_IDS32, &bad, r.d + b.valuesOff, (size_t)b.n * 4, (int32_t)std::min<int64_t>(b.child->n, INT32_MAX)}});
+                if (bad) { why = "corrupt DICTIONARY block: an id lies outside the dictionary of " + std::to_string(b.child->n) + " entries"; return false; }
             }
         } else if (b.child->n != 1) {
             why = "RLE value block must have exactly one position";

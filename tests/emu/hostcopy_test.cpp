@@ -53,6 +53,38 @@ static int runCaller(unsigned seed, int batches, size_t maxBytes) {
     return bad;
 }
 
+// CHECK_ASCENDING32 / CHECK_IDS32: one planted fault anywhere in a (possibly unaligned, multi-segment) array must be found,
+// a clean array must pass
+static int runChecks(unsigned seed) {
+    std::mt19937 rng(seed);
+    int bad = 0;
+    for (int trial = 0; trial < 200; trial++) {
+        const size_t n = 1 + rng() % 700000;
+        const size_t pad = rng() % 4;  // unaligned start, as inside a serialized page
+        std::vector<char> buf(pad + 4 * n);
+        std::vector<int32_t> v(n);
+        int32_t at = 0;
+        for (size_t i = 0; i < n; i++) v[i] = (at += (int32_t)(rng() % 3));
+        const bool plant = trial % 2 == 1;
+        if (plant) {
+            const size_t where = rng() % n;
+            v[where] = where ? v[where - 1] - 1 - (int32_t)(rng() % 5) : -1;
+        }
+        memcpy(buf.data() + pad, v.data(), 4 * n);
+        int32_t flag = 0;
+        hostCopy({CopyTask{CopyTask::CHECK_ASCENDING32, &flag, buf.data() + pad, 4 * n, 0}});
+        if ((flag != 0) != plant) bad++;
+        const int32_t limit = 1 + (int32_t)(rng() % 100000);
+        for (size_t i = 0; i < n; i++) v[i] = (int32_t)(rng() % (uint32_t)limit);
+        if (plant) v[rng() % n] = trial % 4 == 1 ? limit + (int32_t)(rng() % 3) : -1 - (int32_t)(rng() % 3);
+        memcpy(buf.data() + pad, v.data(), 4 * n);
+        flag = 0;
+        hostCopy({CopyTask{CopyTask::CHECK_IDS32, &flag, buf.data() + pad, 4 * n, limit}});
+        if ((flag != 0) != plant) bad++;
+    }
+    return bad;
+}
+
 int main(int argc, char** argv) {
     const int callers = argc > 1 ? atoi(argv[1]) : 1;
     const int batches = argc > 2 ? atoi(argv[2]) : 50;
@@ -61,7 +93,7 @@ int main(int argc, char** argv) {
     std::vector<std::thread> th;
     for (int c = 0; c < callers; c++) th.emplace_back([&, c] { bad[c] = runCaller(1234u + 77u * (unsigned)c, batches, maxBytes); });
     for (auto& t : th) t.join();
-    int total = 0;
+    int total = runChecks(99u);
     for (int b : bad) total += b;
     printf("threads=%d callers=%d batches=%d mismatches=%d\n", hostCopyThreads(), callers, batches, total);
     return total ? 1 : 0;
