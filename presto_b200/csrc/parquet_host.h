@@ -470,23 +470,30 @@ inline bool lz4Decompress(const uint8_t* in, size_t n, uint8_t* out, size_t outL
 struct Inflater {
     const uint8_t* in;
     size_t n, ip = 0;
-    uint32_t hold = 0;
+    uint64_t hold = 0;
     int nbits = 0;
     bool ok = true;
-    uint32_t bits(int need) {
-        while (nbits < need) {
-            if (ip >= n) { ok = false; return 0; }
-            hold |= (uint32_t)in[ip++] << nbits;
+    void refill() {  // at least 56 bits in `hold` while input lasts
+        while (nbits <= 56 && ip < n) {
+            hold |= (uint64_t)in[ip++] << nbits;
             nbits += 8;
         }
-        const uint32_t v = hold & ((1u << need) - 1u);
+    }
+    uint32_t bits(int need) {
+        if (nbits < need) {
+            refill();
+            if (nbits < need) { ok = false; return 0; }
+        }
+        const uint32_t v = (uint32_t)(hold & ((1ull << need) - 1ull));
         hold >>= need;
         nbits -= need;
         return v;
     }
+    static constexpr int kFast = 10;  // codes of up to 10 bits are decoded with one table look-up
     struct Code {
         uint16_t count[16];
         uint16_t symbol[288];
+        uint16_t fast[1 << kFast];  // indexed by the next kFast stream bits: symbol << 4 | code length, 0 = longer code
     };
     // false when the lengths over-subscribe the code space
     static bool build(Code& c, const uint8_t* lengths, int nsym) {
@@ -497,14 +504,30 @@ struct Inflater {
             left = (left << 1) - c.count[len];
             if (left < 0) return false;
         }
-        uint16_t first[16];
+        uint16_t first[16], next[16];
         first[1] = 0;
         for (int len = 1; len < 15; len++) first[len + 1] = (uint16_t)(first[len] + c.count[len]);
         for (int k = 0; k < nsym; k++)
             if (lengths[k]) c.symbol[first[lengths[k]]++] = (uint16_t)k;
+        // canonical codes (RFC 1951 3.2.2), bit-reversed because the stream delivers a code's most significant bit first
+        memset(c.fast, 0, sizeof c.fast);
+        int code = 0;
+        for (int len = 1; len <= 15; len++) {  // first code of every length; unused symbols (length 0) have none
+            next[len] = (uint16_t)code;
+            code = (code + c.count[len]) << 1;
+        }
+        for (int k = 0; k < nsym; k++) {
+            const int len = lengths[k];
+            if (!len) continue;
+            const int cw = next[len]++;
+            if (len > kFast) continue;
+            int rev = 0;
+            for (int b = 0; b < len; b++) rev |= ((cw >> b) & 1) << (len - 1 - b);
+            for (int fill = rev; fill < (1 << kFast); fill += 1 << len) c.fast[fill] = (uint16_t)((k << 4) | len);
+        }
         return true;
     }
-    int decode(const Code& c) {
+    int decodeSlow(const Code& c) {
         int code = 0, first = 0, index = 0;
         for (int len = 1; len <= 15; len++) {
             code |= (int)bits(1);
@@ -517,6 +540,17 @@ struct Inflater {
         }
         ok = false;
         return -1;
+    }
+    int decode(const Code& c) {
+        if (nbits < 15) refill();
+        const uint16_t e = c.fast[hold & ((1u << kFast) - 1u)];
+        const int len = e & 15;
+        if (len && len <= nbits) {
+            hold >>= len;
+            nbits -= len;
+            return e >> 4;
+        }
+        return decodeSlow(c);
     }
     bool codes(const Code& lit, const Code& dist, uint8_t* out, size_t outLen, size_t& op) {
         static const uint16_t lbase[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
@@ -538,7 +572,8 @@ struct Inflater {
                 if (ds < 0 || ds > 29) return false;
                 const size_t d = dbase[ds] + bits(dext[ds]);
                 if (!ok || d > op || len > outLen - op) return false;
-                for (size_t k = 0; k < len; k++) out[op + k] = out[op - d + k];
+                if (d >= len) memcpy(out + op, out + op - d, len);
+                else for (size_t k = 0; k < len; k++) out[op + k] = out[op - d + k];
                 op += len;
             }
         }
@@ -548,7 +583,8 @@ struct Inflater {
             const bool last = bits(1) != 0;
             const uint32_t type = bits(2);
             if (!ok) return false;
-            if (type == 0) {  // stored
+            if (type == 0) {  // stored: the rest of the current byte is skipped, whole bytes that were read ahead go back
+                ip -= (size_t)(nbits / 8);
                 hold = 0;
                 nbits = 0;
                 if (ip + 4 > n) return false;
@@ -605,7 +641,12 @@ struct Inflater {
             } else {
                 return false;
             }
-            if (last) return ok;
+            if (last) {
+                ip -= (size_t)(nbits / 8);  // bytes read ahead but not used belong to what follows the stream (the gzip trailer)
+                nbits = 0;
+                hold = 0;
+                return ok;
+            }
         }
     }
 };
