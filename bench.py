@@ -866,7 +866,7 @@ def run_workload(args, name, device, dist, headline):
     wl = workload_def(name, rows, args.sf * world if args.data == "dbgen" else None)
     if args.data == "dbgen":
         wl["dbgen"] = args.dbgen
-    steps = args.steps if headline else max(3, min(args.steps, 5))
+    steps = args.steps if headline else max(3, min(args.steps, 10))
     warmup = args.warmup if headline else 3
     info, dp, op = run_device_steps(args, wl, device, dist, steps, warmup)
     ms_per_step = info["dev_ms"] / steps

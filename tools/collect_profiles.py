@@ -38,7 +38,7 @@ def copy(name, dst=None):
 
 
 for f in ("bench_default.json", "bench_ref.json", "bench_highcard_buckets.json", "bench_highcard_buckets_casfirst.json", "randtable.txt",
-          "bench_highcard_shuffled_nosweep.json", "parquet_ingest_NONE.json", "parquet_ingest_SNAPPY.json", "parquet_ingest_LZ4.json",
+          "bench_highcard_shuffled_nosweep.json", "parquet_ingest_NONE.json", "parquet_ingest_SNAPPY.json", "parquet_ingest_LZ4.json", "parquet_ingest_GZIP.json",
           "launches_q1.csv", "launches_highcard.csv", "ingest_serialized.json"):
     copy(f)
 for t in (16, 8, 4, 2, 1):
@@ -155,9 +155,9 @@ with open(os.path.join(P, "%s_summary.md" % tag), "w") as out:
     if os.path.exists(src) and os.path.getsize(src):
         v = json.loads(open(src).read().strip().splitlines()[-1])
         out.write("\nGROUP BY shuffled l_orderkey without the partition sweep (PGPU_TUNE_SWEEP=0): %.3f ms/step, kernel %.3f ms/step.\n" % (v["ms_per_step"], v["roofline"]["kernel_ms_per_step"]))
-    pqs = [os.path.join(G, "parquet_ingest_%s.json" % c) for c in ("NONE", "SNAPPY", "LZ4")]
+    pqs = [os.path.join(G, "parquet_ingest_%s.json" % c) for c in ("NONE", "SNAPPY", "LZ4", "GZIP")]
     if any(os.path.exists(x) and os.path.getsize(x) for x in pqs):
-        out.write("\n## Parquet ingest (tools/parquet_ingest_bench.py: Q1 over the same rows as plain blocks and as Parquet row groups, COMPRESSION = NONE / SNAPPY / LZ4)\n\n```\n")
+        out.write("\n## Parquet ingest (tools/parquet_ingest_bench.py: Q1 over the same rows as plain blocks and as Parquet row groups, COMPRESSION = NONE / SNAPPY / LZ4 / GZIP)\n\n```\n")
         for x in pqs:
             if os.path.exists(x) and os.path.getsize(x):
                 out.write(open(x).read().strip() + "\n")
