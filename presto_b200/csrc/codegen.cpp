@@ -1742,6 +1742,11 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
         const std::string inc = "#include \"pgpu_device.cuh\"";
         res.source.insert(res.source.find(inc), "#define PGPU_SWEEP_WT " + std::to_string(wt) + "\n");
     }
+    if (res.sweepOk && envInt("PGPU_TUNE_SWEEP_INFLIGHT", 2) != 2) {  // experiment knob: runs per lane in flight in the sweep kernel (1 .. 4)
+        const int inf = std::min(std::max(envInt("PGPU_TUNE_SWEEP_INFLIGHT", 2), 1), 4);
+        const std::string inc = "#include \"pgpu_device.cuh\"";
+        res.source.insert(res.source.find(inc), "#define PGPU_SWEEP_INFLIGHT " + std::to_string(inf) + "\n");
+    }
     if (locB > 0) {
         const std::string inc = "#include \"pgpu_device.cuh\"";
         const size_t at = res.source.find(inc);

@@ -1219,21 +1219,25 @@ struct HashCtx {
         return nruns;
     }
     // Must be called by all 32 lanes; `base` = global row number of the lane's first row, lanes hold consecutive rows.
+    // INF: runs a lane keeps in flight (their home-slot loads are issued before the first one is resolved) when the warp holds
+    // more than 32 runs, i.e. for keys in no order
+    template <int INF = 2>
     PGPU_DEV void consume_runs(const TableArgs& t, i64 base, bool (&sel)[4], u64 (&key)[4][KW], u64 (&cw)[4][NHA]) {
         const int lane = threadIdx.x & 31;
         const i64 wbase = base - 4 * lane;
         const int nruns = stage_runs(sel, key, cw);
         const u8* starts = reinterpret_cast<const u8*>(runsm + (KW + NHA) * 128);
-        // 3. one run per lane (two in flight when the warp holds more than 32)
+        // 3. one run per lane (INF in flight when the warp holds more than 32)
         const bool allow = table_may_insert(t);
 #pragma unroll 1
-        for (int j0 = 0; j0 < nruns; j0 += 64) {
-            Run a, b;
-            run_issue(t, starts, nruns, j0 + lane, a);
-            const bool two = j0 + 32 < nruns;  // warp-uniform
-            if (two) run_issue(t, starts, nruns, j0 + 32 + lane, b);
-            run_resolve(t, wbase, allow, a);
-            if (two) run_resolve(t, wbase, allow, b);
+        for (int j0 = 0; j0 < nruns; j0 += 32 * INF) {
+            Run r[INF];
+#pragma unroll
+            for (int q = 0; q < INF; q++)
+                if (q == 0 || j0 + 32 * q < nruns) run_issue(t, starts, nruns, j0 + 32 * q + lane, r[q]);  // (warp-uniform condition)
+#pragma unroll
+            for (int q = 0; q < INF; q++)
+                if (q == 0 || j0 + 32 * q < nruns) run_resolve(t, wbase, allow, r[q]);
         }
         if (__any_sync(FULLMASK, nins != 0)) {
             const u32 tot = __reduce_add_sync(FULLMASK, nins);
@@ -1602,6 +1606,9 @@ PGPU_DEV void body_part_scatter(const PageArgs<P::NC>& a, const PageArgs<P::NC>&
 #ifndef PGPU_SWEEP_WT
 #define PGPU_SWEEP_WT 1024
 #endif
+#ifndef PGPU_SWEEP_INFLIGHT
+#define PGPU_SWEEP_INFLIGHT 2
+#endif
 template <class P>
 PGPU_DEV void body_agg_hash_sweep(const PageArgs<P::NC>& a, const TableArgs& t, const Scratch& sc, const SweepArgs& sw) {
     constexpr int KW = P::KW, NHA = P::NHA;
@@ -1649,7 +1656,7 @@ PGPU_DEV void body_agg_hash_sweep(const PageArgs<P::NC>& a, const TableArgs& t, 
             u64 key[4][KW];
             u64 cw[4][NHA];
             P::eval_eager(a, base, a.rows, sel, key, cw, cx.err);
-            if (P::RUNS) cx.consume_runs(t, base, sel, key, cw);  // (HashCtx::consume measured no faster here, even for keys in no order)
+            if (P::RUNS) cx.template consume_runs<PGPU_SWEEP_INFLIGHT>(t, base, sel, key, cw);  // (HashCtx::consume measured no faster here, even for keys in no order)
             else cx.template consume<4>(t, base, sel, key, cw);
         }
     }
