@@ -164,7 +164,7 @@ typedef struct pgpu_parquet_chunk {
     int32_t max_definition_level; /* 0 = required, 1 = optional flat column (nested columns are rejected)     */
     int64_t num_values;           /* ColumnMetaData.num_values = rows of the row group for a flat column     */
     int32_t type_length;          /* FIXED_LEN_BYTE_ARRAY: bytes per value (1..16, a DECIMAL's unscaled value); else 0 */
-    int32_t codec;                /* parquet.thrift CompressionCodec of the chunk's pages: 0 UNCOMPRESSED, 1 SNAPPY, 2 GZIP, 7 LZ4_RAW (others:
+    int32_t codec;                /* parquet.thrift CompressionCodec of the chunk's pages: 0 UNCOMPRESSED, 1 SNAPPY, 2 GZIP, 5 LZ4 (Hadoop-framed), 7 LZ4_RAW (others:
                                    * PGPU_NOT_SUPPORTED). Compressed pages are inflated on the host, as the reference does
                                    * (ParquetCompressionUtils.java:43-70), then take the same path                          */
 } pgpu_parquet_chunk;

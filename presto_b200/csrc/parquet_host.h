@@ -427,7 +427,8 @@ inline bool snappyDecompress(const uint8_t* in, size_t n, uint8_t* out, size_t o
 
 // LZ4 block format (lz4_Block_format.md): sequences of [token | literal length bytes | literals | offset LE16 | match length bytes];
 // the last sequence ends after its literals.
-inline bool lz4Decompress(const uint8_t* in, size_t n, uint8_t* out, size_t outLen) {
+// `produced` given: the block may fill less than outLen (a chunk of a Hadoop frame, whose own size is not stored); else it must fill it
+inline bool lz4Decompress(const uint8_t* in, size_t n, uint8_t* out, size_t outLen, size_t* produced = nullptr) {
     size_t ip = 0, op = 0;
     while (ip < n) {
         const uint8_t token = in[ip++];
@@ -461,6 +462,35 @@ inline bool lz4Decompress(const uint8_t* in, size_t n, uint8_t* out, size_t outL
         if (offset >= len) memcpy(out + op, out + op - offset, len);
         else for (size_t k = 0; k < len; k++) out[op + k] = out[op - offset + k];
         op += len;
+    }
+    if (produced) {
+        *produced = op;
+        return true;
+    }
+    return op == outLen;
+}
+
+// The deprecated Parquet codec LZ4 (5) as Hadoop's Lz4Codec frames it and the reference reads it (ParquetCompressionUtils.java:
+// 104-135 decompressFramed): [uncompressed length of a block, big endian][compressed length of a chunk, big endian][LZ4 block]...,
+// a block may come in several chunks.
+inline bool lz4HadoopDecompress(const uint8_t* in, size_t n, uint8_t* out, size_t outLen) {
+    auto be32 = [&](size_t at) { return ((size_t)in[at] << 24) | ((size_t)in[at + 1] << 16) | ((size_t)in[at + 2] << 8) | (size_t)in[at + 3]; };
+    size_t ip = 0, op = 0, blockEnd = 0;
+    while (op < outLen) {
+        if (op == blockEnd) {
+            if (ip + 4 > n) return false;
+            blockEnd += be32(ip);
+            ip += 4;
+            if (blockEnd > outLen) return false;
+        }
+        if (ip + 4 > n) return false;
+        const size_t chunk = be32(ip);
+        ip += 4;
+        if (chunk > n - ip) return false;
+        size_t got = 0;
+        if (!lz4Decompress(in + ip, chunk, out + op, blockEnd - op, &got) || got == 0) return false;
+        op += got;
+        ip += chunk;
     }
     return op == outLen;
 }
@@ -726,8 +756,8 @@ struct HeaderWriter {
 // reads: sizes, value counts, encodings, level byte lengths), which the rest of the ingest takes as it is.
 inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numValues, std::vector<uint8_t>& out, std::string& why, int threads = 1) {
     using namespace detail;
-    if (codec != SNAPPY && codec != LZ4_RAW && codec != GZIP) {
-        why = "not supported on the GPU path: Parquet compression codec " + std::to_string(codec) + " (UNCOMPRESSED, SNAPPY, GZIP and LZ4_RAW pages are read)";
+    if (codec != SNAPPY && codec != LZ4_RAW && codec != GZIP && codec != LZ4) {
+        why = "not supported on the GPU path: Parquet compression codec " + std::to_string(codec) + " (UNCOMPRESSED, SNAPPY, GZIP, LZ4 and LZ4_RAW pages are read)";
         return false;
     }
     out.clear();
@@ -798,7 +828,8 @@ inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numVal
             bool ok = true;
             if (!t.packed) memcpy(dst, d + t.src, t.dstLen);
             else if (t.dstLen)  // (an empty page may be stored as zero bytes)
-                ok = codec == SNAPPY ? snappyDecompress(d + t.src, t.srcLen, dst, t.dstLen) : codec == GZIP ? gzipDecompress(d + t.src, t.srcLen, dst, t.dstLen) : lz4Decompress(d + t.src, t.srcLen, dst, t.dstLen);
+                ok = codec == SNAPPY ? snappyDecompress(d + t.src, t.srcLen, dst, t.dstLen) : codec == GZIP ? gzipDecompress(d + t.src, t.srcLen, dst, t.dstLen)
+                     : codec == LZ4 ? lz4HadoopDecompress(d + t.src, t.srcLen, dst, t.dstLen) : lz4Decompress(d + t.src, t.srcLen, dst, t.dstLen);
             bad[k] = ok ? 0 : 1;
         }
     };
@@ -812,7 +843,7 @@ inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numVal
         run(0, tasks.size());
     }
     for (char b : bad)
-        if (b) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : codec == GZIP ? "GZIP" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
+        if (b) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : codec == GZIP ? "GZIP" : codec == LZ4 ? "LZ4" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
     return true;
 }
 

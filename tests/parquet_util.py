@@ -34,9 +34,9 @@ def _zz(v):
     return _varint((v << 1) ^ (v >> 63))
 
 
-def page_header(page_type, size, num_values, encoding):
+def page_header(page_type, size, num_values, encoding, compressed_size=None):
     """parquet.thrift PageHeader for a dictionary page (type 2) or a v1 data page (type 0; RLE levels)"""
-    h = b"\x15" + _zz(page_type) + b"\x15" + _zz(size) + b"\x15" + _zz(size)
+    h = b"\x15" + _zz(page_type) + b"\x15" + _zz(size) + b"\x15" + _zz(size if compressed_size is None else compressed_size)
     if page_type == 2:
         return h + b"\x4c" + b"\x15" + _zz(num_values) + b"\x15" + _zz(encoding) + b"\x00" + b"\x00"
     return h + b"\x2c" + b"\x15" + _zz(num_values) + b"\x15" + _zz(encoding) + b"\x15" + _zz(3) + b"\x15" + _zz(3) + b"\x00" + b"\x00"
@@ -57,6 +57,35 @@ def dictionary_chunk(dictionary, ids, width):
     d = np.asarray(dictionary, "<i8").tobytes()
     body = bytes([width]) + bit_packed(ids, width)
     return page_header(2, len(d), len(dictionary), 0) + d + page_header(0, len(body), len(ids), 8) + body
+
+
+def lz4_hadoop_frame(raw, blocks=2, chunks_per_block=2):
+    """Hadoop Lz4Codec framing, the deprecated Parquet codec LZ4 (5) as ParquetCompressionUtils.decompressFramed reads it:
+    per block [uncompressed length, big endian] then per chunk [compressed length, big endian][raw LZ4 block]"""
+    import struct
+    import pyarrow as pa
+    codec = pa.Codec("lz4_raw")
+    out = bytearray()
+    cut = [len(raw) * k // blocks for k in range(blocks + 1)]
+    for a, b in zip(cut, cut[1:]):
+        out += struct.pack(">i", b - a)
+        sub = [a + (b - a) * k // chunks_per_block for k in range(chunks_per_block + 1)]
+        for c, d in zip(sub, sub[1:]):
+            packed = codec.compress(raw[c:d], asbytes=True)
+            out += struct.pack(">i", len(packed)) + packed
+    return bytes(out)
+
+
+def plain_int64_chunk(values, lz4_hadoop=False, pages=3):
+    """required INT64 column, PLAIN v1 data pages; with lz4_hadoop the page bodies are Hadoop-framed LZ4"""
+    values = np.asarray(values, "<i8")
+    out = b""
+    cut = [len(values) * k // pages for k in range(pages + 1)]
+    for a, b in zip(cut, cut[1:]):
+        raw = values[a:b].tobytes()
+        body = lz4_hadoop_frame(raw) if lz4_hadoop else raw
+        out += page_header(0, len(raw), b - a, 0, len(body)) + body
+    return out
 
 
 # ---- the tpch connector's lineitem rows as a Parquet file (pyarrow's writer) ------------------------------------------------

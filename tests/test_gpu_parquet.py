@@ -251,3 +251,26 @@ def test_compressed_nullable_pages_equal_the_uncompressed_file():
             outs.append(got)
         assert outs[0] == outs[1] == outs[2] == outs[3] and len(outs[0]) == 20_000
 
+
+def test_hadoop_framed_lz4_chunk_values():
+    """codec LZ4 (5), Hadoop framing: the values that reach the kernels are the values that were written"""
+    pytest.importorskip("pyarrow")
+    from parquet_util import plain_int64_chunk
+    rng = np.random.default_rng(6)
+    values = np.repeat(rng.integers(-10**9, 10**9, 20_000), 7)
+    chunk = plain_int64_chunk(values, True, pages=5)
+    plan = plan_text([BIGINT], step="single", aggregations=[Aggregation("sum", BIGINT, 0, BIGINT), Aggregation("min", BIGINT, 0, BIGINT),
+                                                            Aggregation("max", BIGINT, 0, BIGINT), Aggregation("count", BIGINT)])
+    op = GpuPipelineOperator(plan, 0)
+    try:
+        op.addParquetRowGroup([(chunk, 2, 0, len(values), 0, 5)], len(values))
+        op.finish()
+        out = []
+        while not op.isFinished():
+            p = op.getOutput()
+            if p is not None:
+                out.append(p)
+    finally:
+        op.close()
+    assert rows_of(out) == [(int(values.sum()), int(values.min()), int(values.max()), len(values))]
+

@@ -175,6 +175,26 @@ def test_compressed_pages_are_inflated_on_the_host(compression, codec, version):
     assert n >= 12
 
 
+def test_hadoop_framed_lz4_pages():
+    """the deprecated codec LZ4 (5) = Hadoop's framing around raw LZ4 blocks, several chunks per block, several blocks per page
+    (what the reference's decompressFramed reads); no writer here produces it, so the chunk is built by hand"""
+    pytest.importorskip("pyarrow")
+    from parquet_util import plain_int64_chunk
+    rng = np.random.default_rng(4)
+    values = np.repeat(rng.integers(-10**12, 10**12, 3000), 5)          # runs: compressible
+    packed, plain = plain_int64_chunk(values, True), plain_int64_chunk(values, False)
+    assert len(packed) < len(plain)
+    st, info, err = inspect(packed, PP.INT64, 0, len(values), 0, 5)
+    pst, pinfo, _ = inspect(plain, PP.INT64, 0, len(values))
+    assert (st, info) == (pst, pinfo) == (N.OK, pinfo), err
+    a, b = runs_of(packed, PP.INT64, 0, len(values), 2, 0, 5), runs_of(plain, PP.INT64, 0, len(values), 2)
+    assert np.array_equal(a["start"], b["start"]) and np.array_equal(a["count"], b["count"])
+    bad = bytearray(packed)
+    bad[40] ^= 0x55
+    assert inspect(bytes(bad), PP.INT64, 0, len(values), 0, 5)[0] in (N.INVALID_ARGUMENT, N.OK)
+    assert inspect(packed[:len(packed) - 9], PP.INT64, 0, len(values), 0, 5)[0] == N.INVALID_ARGUMENT
+
+
 def test_other_codecs_and_corrupt_compressed_pages_are_errors():
     pytest.importorskip("pyarrow")
     sys.path.insert(0, GOLDEN)
