@@ -164,7 +164,7 @@ typedef struct pgpu_parquet_chunk {
     int32_t max_definition_level; /* 0 = required, 1 = optional flat column (nested columns are rejected)     */
     int64_t num_values;           /* ColumnMetaData.num_values = rows of the row group for a flat column     */
     int32_t type_length;          /* FIXED_LEN_BYTE_ARRAY: bytes per value (1..16, a DECIMAL's unscaled value); else 0 */
-    int32_t codec;                /* parquet.thrift CompressionCodec of the chunk's pages: 0 UNCOMPRESSED, 1 SNAPPY, 2 GZIP, 5 LZ4 (Hadoop-framed), 7 LZ4_RAW (others:
+    int32_t codec;                /* parquet.thrift CompressionCodec of the chunk's pages: 0 UNCOMPRESSED, 1 SNAPPY, 2 GZIP, 5 LZ4 (Hadoop-framed), 6 ZSTD, 7 LZ4_RAW (others:
                                    * PGPU_NOT_SUPPORTED). Compressed pages are inflated on the host, as the reference does
                                    * (ParquetCompressionUtils.java:43-70), then take the same path                          */
 } pgpu_parquet_chunk;
@@ -178,7 +178,7 @@ typedef struct pgpu_parquet_chunk {
  * read on the host; each chunk goes to the device in ONE copy and definition levels, dictionary ids and booleans are expanded
  * there. A chunk whose data pages are all dictionary encoded is consumed as a DictionaryBlock (ids + dictionary page), never
  * materialised. Data pages v1 and v2; PLAIN, PLAIN_DICTIONARY, RLE_DICTIONARY, RLE (levels, booleans). Rejected with
- * PGPU_NOT_SUPPORTED: ZSTD / BROTLI / LZO pages, nested columns, DELTA_* / BYTE_STREAM_SPLIT encodings, INT96 / FLOAT,
+ * PGPU_NOT_SUPPORTED: BROTLI / LZO pages, nested columns, DELTA_* / BYTE_STREAM_SPLIT encodings, INT96 / FLOAT,
  * var-width chunks that are not dictionary encoded throughout. */
 pgpu_status pgpu_add_parquet_row_group(pgpu_pipeline* p, const pgpu_parquet_chunk* chunks, int32_t nchunks, int64_t rows);
 /* What pgpu_add_parquet_row_group reads on the host, without a GPU: info[0] data pages, [1] dictionary entries (-1: none), [2] every

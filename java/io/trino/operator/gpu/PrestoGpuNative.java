@@ -48,7 +48,7 @@ final class PrestoGpuNative
     /**
      * pgpu_add_parquet_row_group — Operator.addInput of the Page ParquetReader.nextPage would build from one row group. Per channel:
      * the column chunk's bytes as they lie in the file (ColumnChunkMetaData.getStartingPos() .. + getTotalSize(), still
-     * compressed: `codec` = the chunk's parquet.thrift CompressionCodec, 0 UNCOMPRESSED, 1 SNAPPY, 2 GZIP, 5 LZ4, 7 LZ4_RAW) as address / length of a direct buffer, the parquet physical type ordinal
+     * compressed: `codec` = the chunk's parquet.thrift CompressionCodec, 0 UNCOMPRESSED, 1 SNAPPY, 2 GZIP, 5 LZ4, 6 ZSTD, 7 LZ4_RAW) as address / length of a direct buffer, the parquet physical type ordinal
      * (PrimitiveTypeName: BOOLEAN 0, INT32 1, INT64 2, DOUBLE 5, BINARY 6, FIXED_LEN_BYTE_ARRAY 7), the column's max definition
      * level (0 or 1), its value count, for FIXED_LEN_BYTE_ARRAY the type length, and the codec.
      */

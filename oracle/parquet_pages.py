@@ -232,7 +232,7 @@ def plain_values(buf, pos, end, ptype, count, type_length=0):
     raise Unsupported("parquet physical type %d" % ptype)
 
 
-CODEC_NAMES = {1: "snappy", 2: "gzip", 7: "lz4_raw"}   # parquet.thrift CompressionCodec -> pyarrow codec name
+CODEC_NAMES = {1: "snappy", 2: "gzip", 6: "zstd", 7: "lz4_raw"}   # parquet.thrift CompressionCodec -> pyarrow codec name
 
 
 def _inflate(codec, raw, size):

@@ -20,6 +20,8 @@
 #include <thread>
 #include <vector>
 
+#include "zstd_decode.h"
+
 namespace pgpu {
 namespace pq {
 
@@ -492,7 +494,7 @@ inline bool lz4HadoopDecompress(const uint8_t* in, size_t n, uint8_t* out, size_
         op += got;
         ip += chunk;
     }
-    return op == outLen;
+    return op == outLen && ip == n;  // nothing may follow the last chunk
 }
 
 // DEFLATE (RFC 1951) inside a gzip member (RFC 1952): what Hadoop's GzipCodec — the reference's GZIP pages — writes.
@@ -756,8 +758,8 @@ struct HeaderWriter {
 // reads: sizes, value counts, encodings, level byte lengths), which the rest of the ingest takes as it is.
 inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numValues, std::vector<uint8_t>& out, std::string& why, int threads = 1) {
     using namespace detail;
-    if (codec != SNAPPY && codec != LZ4_RAW && codec != GZIP && codec != LZ4) {
-        why = "not supported on the GPU path: Parquet compression codec " + std::to_string(codec) + " (UNCOMPRESSED, SNAPPY, GZIP, LZ4 and LZ4_RAW pages are read)";
+    if (codec != SNAPPY && codec != LZ4_RAW && codec != GZIP && codec != LZ4 && codec != ZSTD) {
+        why = "not supported on the GPU path: Parquet compression codec " + std::to_string(codec) + " (UNCOMPRESSED, SNAPPY, GZIP, LZ4, ZSTD and LZ4_RAW pages are read)";
         return false;
     }
     out.clear();
@@ -829,7 +831,8 @@ inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numVal
             if (!t.packed) memcpy(dst, d + t.src, t.dstLen);
             else if (t.dstLen)  // (an empty page may be stored as zero bytes)
                 ok = codec == SNAPPY ? snappyDecompress(d + t.src, t.srcLen, dst, t.dstLen) : codec == GZIP ? gzipDecompress(d + t.src, t.srcLen, dst, t.dstLen)
-                     : codec == LZ4 ? lz4HadoopDecompress(d + t.src, t.srcLen, dst, t.dstLen) : lz4Decompress(d + t.src, t.srcLen, dst, t.dstLen);
+                     : codec == LZ4 ? lz4HadoopDecompress(d + t.src, t.srcLen, dst, t.dstLen) : codec == ZSTD ? zstd::decompress(d + t.src, t.srcLen, dst, t.dstLen)
+                                    : lz4Decompress(d + t.src, t.srcLen, dst, t.dstLen);
             bad[k] = ok ? 0 : 1;
         }
     };
@@ -843,7 +846,7 @@ inline bool inflateChunk(const uint8_t* d, size_t len, int codec, int64_t numVal
         run(0, tasks.size());
     }
     for (char b : bad)
-        if (b) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : codec == GZIP ? "GZIP" : codec == LZ4 ? "LZ4" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
+        if (b) { why = std::string("corrupt Parquet chunk: ") + (codec == SNAPPY ? "SNAPPY" : codec == GZIP ? "GZIP" : codec == LZ4 ? "LZ4" : codec == ZSTD ? "ZSTD" : "LZ4_RAW") + " page does not decompress to its declared size"; return false; }
     return true;
 }
 

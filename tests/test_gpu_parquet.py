@@ -214,7 +214,7 @@ def test_sf1_lineitem_parquet_file_equals_golden_answers():
     assert got == G.golden_rows("hive_tpch_q06.result", (4,))
 
 
-@pytest.mark.parametrize("compression,codec", [("SNAPPY", 1), ("LZ4", 7), ("GZIP", 2)])
+@pytest.mark.parametrize("compression,codec", [("SNAPPY", 1), ("LZ4", 7), ("GZIP", 2), ("ZSTD", 6)])
 def test_compressed_lineitem_parquet_file_equals_golden_answers(compression, codec):
     """the same golden answers off a SNAPPY- / LZ4_RAW-compressed file of the sf1 table: pages are
     inflated on the host (ParquetCompressionUtils.java:43-70), everything else is the uncompressed path"""
@@ -244,12 +244,12 @@ def test_compressed_nullable_pages_equal_the_uncompressed_file():
     table = M.nullable_table(20_000, seed=9)
     for version in ("1.0", "2.0"):
         outs = []
-        for compression in ("NONE", "SNAPPY", "LZ4", "GZIP"):
+        for compression in ("NONE", "SNAPPY", "LZ4", "GZIP", "ZSTD"):
             buf = io.BytesIO()
             pq.write_table(table, buf, compression=compression, data_page_version=version, data_page_size=3000, use_dictionary=["runs"], row_group_size=7000)
             got, _ = run_parquet(plan, chunks_of(buf.getvalue()), names)
             outs.append(got)
-        assert outs[0] == outs[1] == outs[2] == outs[3] and len(outs[0]) == 20_000
+        assert all(o == outs[0] for o in outs[1:]) and len(outs[0]) == 20_000
 
 
 def test_hadoop_framed_lz4_chunk_values():
