@@ -55,6 +55,10 @@ struct Backward {
         uint64_t w = 0;
         const int64_t byte = at >= 0 ? at >> 3 : -((-at + 7) >> 3);
         const int shift = (int)(at - byte * 8);
+        if (byte >= 0 && (size_t)byte + 8 <= n) {  // the common case: one unaligned load
+            memcpy(&w, p + byte, 8);
+            return (w >> shift) & ((1ull << k) - 1ull);
+        }
         for (int b = 0; b < 6; b++) {
             const int64_t q = byte + b;
             if (q >= 0 && (size_t)q < n) w |= (uint64_t)p[q] << (8 * b);
