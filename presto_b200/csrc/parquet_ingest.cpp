@@ -55,6 +55,9 @@ pgpu_status pqDecodeRowGroup(const Plan& plan, const pgpu_parquet_chunk* chunks,
     std::vector<std::string> whys((size_t)nchunks);
     // compressed chunks (SNAPPY / LZ4_RAW) are inflated on the host, by the chunk's thread, into a chunk with uncompressed pages
     std::vector<std::vector<uint8_t>> inflated((size_t)nchunks);
+    size_t compressedTotal = 0;
+    for (int c = 0; c < nchunks; c++)
+        if (chunks[c].codec != pq::UNCOMPRESSED) compressedTotal += chunks[c].len;
     std::vector<const uint8_t*> cdata((size_t)nchunks);
     std::vector<size_t> clen((size_t)nchunks);
     auto parseOne = [&](int c) {
@@ -63,7 +66,11 @@ pgpu_status pqDecodeRowGroup(const Plan& plan, const pgpu_parquet_chunk* chunks,
         cdata[c] = in.data;
         clen[c] = in.len;
         if (in.codec != pq::UNCOMPRESSED) {
-            if (!pq::inflateChunk(in.data, in.len, in.codec, in.num_values, inflated[c], whys[c], std::max(pageThreads, 2))) {
+            // threads for the pages of this chunk: its share of the compressed bytes of the row group (one wide PLAIN column usually
+            // holds most of them), out of the host's cores
+            const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+            const int share = compressedTotal ? (int)((double)hw * (double)in.len / (double)compressedTotal + 0.5) : 1;
+            if (!pq::inflateChunk(in.data, in.len, in.codec, in.num_values, inflated[c], whys[c], std::min(16, std::max(share, std::max(pageThreads, 2))))) {
                 if (whys[c].empty()) whys[c] = "corrupt Parquet chunk";
                 return;
             }
