@@ -235,6 +235,8 @@ typedef struct pgpu_stats {
                              * buffer instead of going out on their own (MergePages.java:147 appendPage) */
     int64_t partition_sweeps; /* long device-resident pages whose rows were reordered by table slice before the hash-aggregation
                                * kernel ran (tables far larger than L2; DESIGN.md "partition sweep") */
+    int64_t streamed_runs;    /* rows of the run buffer: device pages whose keys arrive in key order are aggregated run by run,
+                               * without a hash table (DESIGN.md "streaming runs"); 0 = the table path */
 } pgpu_stats;
 pgpu_status pgpu_get_stats(const pgpu_pipeline* p, pgpu_stats* out);
 pgpu_status pgpu_set_timing(pgpu_pipeline* p, int32_t enabled);

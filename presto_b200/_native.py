@@ -42,7 +42,7 @@ class Stats(ctypes.Structure):
     _fields_ = [("kernel_launches", ctypes.c_int64), ("h2d_bytes", ctypes.c_int64), ("d2h_bytes", ctypes.c_int64),
                 ("input_rows", ctypes.c_int64), ("input_pages", ctypes.c_int64), ("jit_compiles", ctypes.c_int64),
                 ("jit_cache_hits", ctypes.c_int64), ("device_ms", ctypes.c_double), ("table_capacity", ctypes.c_int64),
-                ("table_rehashes", ctypes.c_int64), ("super_pages", ctypes.c_int64), ("table_bucketed", ctypes.c_int64), ("table_slots_claimed", ctypes.c_int64), ("bucket_offset", ctypes.c_int64), ("pages_merged", ctypes.c_int64), ("partition_sweeps", ctypes.c_int64)]
+                ("table_rehashes", ctypes.c_int64), ("super_pages", ctypes.c_int64), ("table_bucketed", ctypes.c_int64), ("table_slots_claimed", ctypes.c_int64), ("bucket_offset", ctypes.c_int64), ("pages_merged", ctypes.c_int64), ("partition_sweeps", ctypes.c_int64), ("streamed_runs", ctypes.c_int64)]
 
 
 # every symbol include/prestogpu.h declares: (name, restype, argtypes)

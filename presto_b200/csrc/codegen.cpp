@@ -1417,6 +1417,20 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
     }
     src << "    }\n";
 
+    // cells (+) cells: merging two partial states of one group (streaming runs: pieces of a run, rows into the table)
+    src << "    PGPU_DEV static void combine_cells(u64* a, const u64* b) {\n";
+    for (int w = 0; w < NW; w++) {
+        if (res.cellKinds[w] == 4) src << "        max128_combine(a[" << w << "], a[" << w + 1 << "], b[" << w << "], b[" << w + 1 << "]);\n";
+        else if (res.cellKinds[w] != 5) src << "        a[" << w << "] = cell_combine<" << kindName(res.cellKinds[w]) << ">(a[" << w << "], b[" << w << "]);\n";
+    }
+    src << "    }\n";
+    src << "    PGPU_DEV static void atomic_cells_from(u64* cells, const u64* b) {\n";
+    for (int w = 0; w < NW; w++) {
+        if (res.cellKinds[w] == 4) src << "        max128_atomic(cells + " << w << ", b[" << w << "], b[" << w + 1 << "]);\n";
+        else if (res.cellKinds[w] != 5) src << "        cell_atomic<" << kindName(res.cellKinds[w]) << ">(cells + " << w << ", b[" << w << "]);\n";
+    }
+    src << "    }\n";
+
     // ---- eval
     // eval: filter channels first, the remaining channels only when some row of the thread passed (selective filters
     // never read them: Q6 skips most of extendedprice). eval_eager: every load issued up front, one memory round trip
@@ -1728,6 +1742,17 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
                 src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_emit_probe(TableArgs t, OutArgs<P::NO> out, Scratch sc, ProbeArgs pa) { body_emit_probe<P>(t, out, sc, pa); }\n";
             }
         }
+        // streaming runs (device header, "streaming runs"): SINGLE step over a one-key-per-slot tagless table
+        res.streamOk = highCard && !res.buckets && plan.step == Step::SINGLE && plan.maxPartialGroups == 0 && envInt("PGPU_TUNE_STREAM", 1) != 0;
+        if (res.streamOk) {
+            // registers: 4 rows x (key + hot cells) stay live through the scan
+            res.streamSub = std::min(std::max(envInt("PGPU_TUNE_STREAM_SUB", 1), 1), 4);
+            const int streamMinBlocks = envInt("PGPU_TUNE_STREAM_MINBLOCKS", (KW + NHA) * res.streamSub <= 4 ? 4 : (KW + NHA) * res.streamSub <= 8 ? 3 : 2);
+            src << "extern \"C\" __global__ void __launch_bounds__(256, " << streamMinBlocks << ") pgpu_k_runs_count(PageArgs<P::NC> a, u32* counts, Scratch sc) { body_runs_count<P>(a, counts, sc); }\n";
+            src << "extern \"C\" __global__ void __launch_bounds__(256, " << streamMinBlocks << ") pgpu_k_runs_write(PageArgs<P::NC> a, const u64* offsets, RunArgs ra, Scratch sc) { body_runs_write<P>(a, offsets, ra, sc); }\n";
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_runs_emit(const u64* buf, i64 nrows, OutArgs<P::NO> out, Scratch sc, u32* violations) { body_runs_emit<P>(buf, nrows, out, sc, violations); }\n";
+            src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_runs_to_table(const u64* buf, u64 nrows, TableArgs to, Scratch sc) { body_runs_to_table<P>(buf, nrows, to, sc); }\n";
+        }
         if (res.sweepOk) {
             src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_part_count(PageArgs<P::NC> a, PartArgs pa, Scratch sc) { body_part_count<P>(a, pa, sc); }\n";
             src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_part_scatter(PageArgs<P::NC> a, PageArgs<P::NC> out, PartArgs pa) { body_part_scatter<P>(a, out, pa); }\n";
@@ -1737,6 +1762,10 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
         src << "extern \"C\" __global__ void __launch_bounds__(256) pgpu_k_replay(PageArgs<P::NC> a, TableArgs t, Scratch sc, const u64* rows, u64 n) { body_replay<P>(a, t, sc, rows, n); }\n";
     }
     res.source = src.str();
+    if (res.streamOk && res.streamSub != 1) {  // experiment knob: rows per thread of the streaming-runs kernels = 4 * streamSub
+        const std::string inc = "#include \"pgpu_device.cuh\"";
+        res.source.insert(res.source.find(inc), "#define PGPU_STREAM_SUB " + std::to_string(res.streamSub) + "\n");
+    }
     if (res.sweepOk && envInt("PGPU_TUNE_SWEEP_WT", 1024) != 1024) {  // experiment knob: rows per warp ticket of the sweep kernel (128 .. 4096, a multiple of 128)
         const int wt = std::min(std::max(envInt("PGPU_TUNE_SWEEP_WT", 1024) / 128 * 128, 128), 4096);
         const std::string inc = "#include \"pgpu_device.cuh\"";

@@ -52,6 +52,8 @@ struct GenResult {
     bool buckets = false;          // this source was generated for the bucketed table: SLOTW = words per BUCKET
     bool rangeNullable = false;    // ... and that key may be NULL (the NULL group is always exchanged)
     bool rangeOk = false;          // one integer grouping key: the exchange may split groups by key range (pgpu_k_emit_range / pgpu_k_keyrange)
+    int streamSub = 1;             // row quads per thread of pgpu_k_runs_count / _write (a warp unit = 32 x 4 streamSub rows)
+    bool streamOk = false;         // streaming-runs kernels were generated (pgpu_k_runs_count / _write / _emit / _to_table)
     bool sweepOk = false;          // partition sweep kernels were generated (pgpu_k_part_count / _scatter / pgpu_k_page_sweep)
     int sweepRowBytes = 0;         // bytes the scatter moves per row (arrays of the used channels)
     int sweepStageWidth = 1;       // widest moved element: the scatter stages kPartTile elements of one array at a time

@@ -468,6 +468,7 @@ PGPU_DEV u64 ld_acquire_u64(const u64* p) {
 }
 PGPU_DEV void st_release_u64(u64* p, u64 v) { asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 
+PGPU_DEV void st_relaxed_u64(u64* p, u64 v) { asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 PGPU_DEV u64 ld_relaxed_u64(const u64* p) {
     u64 v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -1662,6 +1663,331 @@ PGPU_DEV void body_agg_hash_sweep(const PageArgs<P::NC>& a, const TableArgs& t, 
     }
     cx.flush(t, P::NWARP);
     if (cx.err) atomicOr(sc.err, cx.err);
+}
+
+// ------------------------------------------------------------------------------------------------ streaming runs
+// Keys that arrive in key order (GROUP BY l_orderkey over lineitem as the table lies) need no hash table: a group is a run of
+// adjacent rows. pgpu_k_runs_stream writes one slot-format row [key | cells] per run into a linear buffer IN ROW ORDER (tiles
+// are ordered by the decoupled look-back of body_compact; a run that crosses a warp boundary leaves adjacent rows with the same
+// key); pgpu_k_runs_emit merges such neighbours, finalises every group straight into the output buffers and counts the places
+// where the key order DEcreases. A decrease means a key may reappear later: the host then merges the buffered rows into the hash
+// table (pgpu_k_runs_to_table) and takes the ordinary path — the buffer holds partial states, nothing is lost. Any total order
+// serves; the packed key words are compared as unsigned integers, last word first.
+struct RunArgs {
+    u64* buf;           // slot-format rows, 32-byte aligned
+    u64 capacity_rows;
+    u64 base_rows;      // rows the buffer already holds (earlier launches)
+};
+
+PGPU_DEV u64 shfl_up_u64(u64 v, int d) {
+    return ((u64)__shfl_up_sync(FULLMASK, (u32)(v >> 32), d) << 32) | (u64)__shfl_up_sync(FULLMASK, (u32)v, d);
+}
+
+#ifndef PGPU_STREAM_SUB
+#define PGPU_STREAM_SUB 1
+#endif
+// Two passes, no ordering between warps. One thread = R = 4 * PGPU_STREAM_SUB consecutive rows, a warp's unit = 32 R consecutive rows.
+// pgpu_k_runs_count evaluates the rows and stores how many live runs end in each unit; the host side scans the counts
+// (tableutil.cu runsScan) and sizes the buffer exactly; pgpu_k_runs_write evaluates the rows again and writes every unit's rows at
+// its offset. A run is a maximal stretch of rows with the same key and the same filter outcome (rows the filter rejects form
+// "dead" runs that are not written; keys are compared among selected rows only). Runs are cut at unit boundaries (lane 0's first
+// row always starts one). Inside a thread the rows fold forwards, so that a run's total stands at its LAST row; across the lanes
+// a segmented inclusive scan carries the partial total of an open run to the lane where it ends. Everything stays in registers.
+// (A one-pass form, tiles ordered by tickets and a decoupled look-back, read the rows once but spent half its time in the
+// look-back: 7.3 ms against 4.3 ms for 600 M rows, DESIGN.md "streaming runs".)
+template <class P>
+struct RunsRows {
+    static constexpr int KW = P::KW, NHA = P::NHA, SUB = PGPU_STREAM_SUB, R = 4 * SUB;
+    bool sel[SUB][4];
+    u64 key[SUB][4][KW];
+    u64 cw[SUB][4][NHA];
+    u32 head, tail;
+
+    PGPU_DEV void load(const PageArgs<P::NC>& a, i64 base, u32& err) {
+#pragma unroll
+        for (int q = 0; q < SUB; q++) P::eval_eager(a, base + 4 * q, a.rows, sel[q], key[q], cw[q], err);
+    }
+    // head bit r: row r starts a run; tail bit r: a LIVE run ends at row r
+    PGPU_DEV void find_runs(int lane) {
+        const bool psel = __shfl_up_sync(FULLMASK, sel[SUB - 1][3] ? 1 : 0, 1) != 0;
+        bool differs = false;
+#pragma unroll
+        for (int w = 0; w < KW; w++) differs |= shfl_up_u64(key[SUB - 1][3][w], 1) != key[0][0][w];
+        head = (lane == 0 || psel != sel[0][0] || (sel[0][0] && differs)) ? 1u : 0u;
+#pragma unroll
+        for (int r = 1; r < R; r++) {
+            bool d = false;
+#pragma unroll
+            for (int w = 0; w < KW; w++) d |= key[(r - 1) >> 2][(r - 1) & 3][w] != key[r >> 2][r & 3][w];
+            head |= (sel[(r - 1) >> 2][(r - 1) & 3] != sel[r >> 2][r & 3] || (sel[r >> 2][r & 3] && d)) ? 1u << r : 0u;
+        }
+        tail = head >> 1;
+        if (__shfl_down_sync(FULLMASK, head & 1u, 1) != 0u || lane == 31) tail |= 1u << (R - 1);
+#pragma unroll
+        for (int r = 0; r < R; r++)
+            if (!sel[r >> 2][r & 3]) tail &= ~(1u << r);
+    }
+    // after this the total of every run stands in the cells of its last row
+    PGPU_DEV void fold(int lane) {
+#pragma unroll
+        for (int r = 0; r < R; r++)
+            if (!sel[r >> 2][r & 3]) {
+#pragma unroll
+                for (int i = 0; i < NHA; i++) cw[r >> 2][r & 3][i] = 0ull;  // the identity of every cell kind
+            }
+#pragma unroll
+        for (int r = 1; r < R; r++)
+            if (!((head >> r) & 1u)) P::combine(cw[r >> 2][r & 3], cw[(r - 1) >> 2][(r - 1) & 3]);
+        u64 val[NHA];
+#pragma unroll
+        for (int i = 0; i < NHA; i++) val[i] = cw[SUB - 1][3][i];
+        bool flag = head != 0;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            u64 o[NHA];
+#pragma unroll
+            for (int i = 0; i < NHA; i++) o[i] = shfl_up_u64(val[i], d);
+            const bool of = __shfl_up_sync(FULLMASK, flag ? 1 : 0, d) != 0;
+            if (lane >= d && !flag) {
+                P::combine(val, o);
+                flag = of;
+            }
+        }
+        u64 carry[NHA];
+#pragma unroll
+        for (int i = 0; i < NHA; i++) carry[i] = shfl_up_u64(val[i], 1);
+        const int f = head ? __ffs(head) - 1 : R;
+#pragma unroll
+        for (int r = 0; r < R - 1; r++)
+            if (f == r + 1) P::combine(cw[r >> 2][r & 3], carry);
+        if (f == R) {
+#pragma unroll
+            for (int i = 0; i < NHA; i++) cw[SUB - 1][3][i] = val[i];
+        }
+    }
+    // the live tails -> buffer rows pos, pos + 1, ...
+    PGPU_DEV void write(const RunArgs& ra, u64 pos, u32& err) {
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            if (!((tail >> r) & 1u)) continue;
+            if (pos < ra.capacity_rows) {
+                u64 row[P::SLOTW];
+#pragma unroll
+                for (int w = 0; w < P::SLOTW; w++) row[w] = 0ull;
+#pragma unroll
+                for (int w = 0; w < KW; w++) row[P::KOFF + w] = key[r >> 2][r & 3][w];
+                row[P::KOFF + KW - 1] |= KEY_MARK;
+                P::merge_cells(row + P::KOFF + KW, cw[r >> 2][r & 3]);
+                ulonglong2* o = reinterpret_cast<ulonglong2*>(ra.buf + pos * P::SLOTW);  // rows are 32-byte aligned (SLOTW is a multiple of 4)
+#pragma unroll
+                for (int w = 0; w < P::SLOTW / 2; w++) o[w] = make_ulonglong2(row[2 * w], row[2 * w + 1]);
+            } else {
+                err |= PGPU_ERR_OUTPUT_FULL;
+            }
+            pos++;
+        }
+    }
+};
+
+template <class P>
+PGPU_DEV void body_runs_count(const PageArgs<P::NC>& a, u32* counts, const Scratch& sc) {
+    constexpr int R = RunsRows<P>::R;
+    const int lane = threadIdx.x & 31;
+    const i64 unit_rows = 32 * R, nunits = (a.rows + unit_rows - 1) / unit_rows;
+    const i64 nw = ((i64)gridDim.x * blockDim.x) >> 5;
+    u32 err = 0;
+    for (i64 u = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5; u < nunits; u += nw) {
+        RunsRows<P> t;
+        t.load(a, u * unit_rows + (i64)lane * R, err);
+        t.find_runs(lane);
+        const u32 total = __reduce_add_sync(FULLMASK, (u32)__popc(t.tail));
+        if (lane == 0) counts[u] = total;
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
+template <class P>
+PGPU_DEV void body_runs_write(const PageArgs<P::NC>& a, const u64* offsets, const RunArgs& ra, const Scratch& sc) {
+    constexpr int R = RunsRows<P>::R;
+    const int lane = threadIdx.x & 31;
+    const i64 unit_rows = 32 * R, nunits = (a.rows + unit_rows - 1) / unit_rows;
+    const i64 nw = ((i64)gridDim.x * blockDim.x) >> 5;
+    u32 err = 0;
+    for (i64 u = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5; u < nunits; u += nw) {
+        RunsRows<P> t;
+        t.load(a, u * unit_rows + (i64)lane * R, err);
+        t.find_runs(lane);
+        t.fold(lane);
+        const u32 cnt = (u32)__popc(t.tail);
+        u32 incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const u32 n = __shfl_up_sync(FULLMASK, incl, d);
+            if (lane >= d) incl += n;
+        }
+        t.write(ra, ra.base_rows + offsets[u] + (incl - cnt), err);
+    }
+    if (err) atomicOr(sc.err, err);
+}
+
+// rows i - 1 and i of the buffer: same key? does the order decrease?
+template <class P>
+PGPU_DEV void runs_compare(const u64* prev, const u64* cur, bool& same, bool& decreases) {
+    same = true;
+    decreases = false;
+    bool decided = false;
+#pragma unroll
+    for (int w = P::KW - 1; w >= 0; w--) {
+        const u64 x = prev[P::KOFF + w], y = cur[P::KOFF + w];
+        same &= x == y;
+        if (!decided && x != y) {
+            decided = true;
+            decreases = y < x;
+        }
+    }
+}
+
+constexpr i64 kRunsMaxPieces = 64;  // buffer rows of one key the emit kernel merges serially (a piece = the key's rows inside one warp's 128)
+constexpr int kRunsEmitPer = 4;     // buffer rows per thread and block chunk
+
+// Two passes over a block's chunk of blockDim.x * kRunsEmitPer buffer rows, thread t taking rows t, t + blockDim.x, ... (a warp
+// reads 32 neighbouring rows at a time). Pass 1 reads the keys (every load issued before the first use): a row is a HEAD when its
+// key differs from the row before (that key comes from the lane below, lane 0 reads it), and the head's run CONTINUES when the
+// row after it is no head. One atomic per chunk reserves the output rows. Pass 2 reads the heads' rows again (L2), merges the
+// continuation rows and finalises.
+template <class P>
+PGPU_DEV void body_runs_emit(const u64* buf, i64 nrows, const OutArgs<P::NO>& out, const Scratch& sc, u32* violations) {
+    constexpr int PER = kRunsEmitPer, KW = P::KW;
+    __shared__ u32 s_warp[32];
+    __shared__ u64 s_base;
+    u32 err = 0, bad = 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    const i64 chunk = (i64)blockDim.x * PER;
+    for (i64 c0 = (i64)blockIdx.x * chunk; c0 < nrows; c0 += (i64)gridDim.x * chunk) {
+        u64 cur[PER][KW], before[PER][KW], after[PER][KW];
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            const i64 i = c0 + (i64)k * blockDim.x + threadIdx.x;
+#pragma unroll
+            for (int w = 0; w < KW; w++) {
+                cur[k][w] = i < nrows ? buf[(u64)i * P::SLOTW + P::KOFF + w] : 0ull;
+                before[k][w] = (lane == 0 && i > 0 && i < nrows) ? buf[(u64)(i - 1) * P::SLOTW + P::KOFF + w] : 0ull;
+                after[k][w] = (lane == 31 && i + 1 < nrows) ? buf[(u64)(i + 1) * P::SLOTW + P::KOFF + w] : 0ull;
+            }
+        }
+        u32 headmask = 0, contmask = 0;
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            const i64 i = c0 + (i64)k * blockDim.x + threadIdx.x;
+            const bool valid = i < nrows;
+            u64 prev[KW];
+#pragma unroll
+            for (int w = 0; w < KW; w++) {
+                prev[w] = shfl_up_u64(cur[k][w], 1);
+                if (lane == 0) prev[w] = before[k][w];
+            }
+            bool same = true, dec = false, decided = false;
+#pragma unroll
+            for (int w = KW - 1; w >= 0; w--) {
+                same &= prev[w] == cur[k][w];
+                if (!decided && prev[w] != cur[k][w]) {
+                    decided = true;
+                    dec = cur[k][w] < prev[w];
+                }
+            }
+            const bool head = valid && (i == 0 || !same);
+            bad += (valid && i > 0 && dec) ? 1u : 0u;
+            // the row after this one: the next lane's (lane 31: the next warp's first row, read above)
+            bool next_follows = __shfl_down_sync(FULLMASK, (valid && !head) ? 1 : 0, 1) != 0;
+            if (lane == 31) {
+                next_follows = i + 1 < nrows;
+#pragma unroll
+                for (int w = 0; w < KW; w++) next_follows &= after[k][w] == cur[k][w];
+            }
+            headmask |= head ? 1u << k : 0u;
+            contmask |= (head && next_follows) ? 1u << k : 0u;
+        }
+        const u32 cnt = (u32)__popc(headmask);
+        u32 incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const u32 n = __shfl_up_sync(FULLMASK, incl, d);
+            if (lane >= d) incl += n;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const u32 w = lane < nwarps ? s_warp[lane] : 0u;
+            u32 wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const u32 n = __shfl_up_sync(FULLMASK, wi, d);
+                if (lane >= d) wi += n;
+            }
+            s_warp[lane] = wi - w;
+            if (lane == 31) s_base = wi ? atomicAdd(sc.out_count, (u64)wi) : 0ull;
+        }
+        __syncthreads();
+        i64 pos = (i64)(s_base + s_warp[warp] + incl - cnt);
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            if (!((headmask >> k) & 1u)) continue;
+            const i64 i = c0 + (i64)k * blockDim.x + threadIdx.x;
+            const u64* row = buf + (u64)i * P::SLOTW;
+            u64 r[P::SLOTW];
+            const ulonglong2* rv = reinterpret_cast<const ulonglong2*>(row);
+#pragma unroll
+            for (int w = 0; w < P::SLOTW / 2; w++) {
+                const ulonglong2 q = rv[w];
+                r[2 * w] = q.x;
+                r[2 * w + 1] = q.y;
+            }
+            u64* c = r + P::KOFF + KW;
+            if ((contmask >> k) & 1u) {
+                for (i64 j = i + 1; j < nrows; j++) {  // the pieces of a run that was cut (warp boundaries, dead rows) follow it directly
+                    const u64* nx = buf + (u64)j * P::SLOTW;
+                    bool same, dec;
+                    runs_compare<P>(row, nx, same, dec);
+                    if (!same) break;
+                    if (j - i > kRunsMaxPieces) {  // a group of thousands of rows: one thread must not walk it. The table path takes over
+                        bad++;
+                        break;
+                    }
+                    P::combine_cells(c, nx + P::KOFF + KW);
+                }
+            }
+            if (pos < out.capacity) {
+                u64 key[KW > 0 ? KW : 1];
+#pragma unroll
+                for (int w = 0; w < KW; w++) key[w] = r[P::KOFF + w];
+                if (P::TAGLESS) key[KW - 1] &= ~KEY_MARK;
+                P::emit(key, c, out, pos, err);
+            } else {
+                err |= PGPU_ERR_OUTPUT_FULL;
+            }
+            pos++;
+        }
+        __syncthreads();
+    }
+    bad = __reduce_add_sync(FULLMASK, bad);
+    if (lane == 0 && bad) atomicAdd(violations, bad);
+    if (err) atomicOr(sc.err, err);
+}
+
+// the buffered rows -> the hash table (the keys turned out not to be in order): rows of one key merge
+template <class P>
+PGPU_DEV void body_runs_to_table(const u64* buf, u64 nrows, const TableArgs& to, const Scratch& sc) {
+    u32 err = 0, nins = 0;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < nrows; i += (u64)gridDim.x * blockDim.x) {
+        const u64* row = buf + i * P::SLOTW;
+        u64 key[P::KW > 0 ? P::KW : 1];
+        slot_key<P>(row, key);
+        u64* d = table_upsert<P::KW, P::SLOTW, P::TAGLESS>(to, key, hash_key<P::KW>(key), true, nins);
+        if (!d) { err |= PGPU_ERR_TABLE_FULL; continue; }
+        P::atomic_cells_from(d + P::KOFF + P::KW, row + P::KOFF + P::KW);
+    }
+    flush_inserts(to, nins);
+    if (err) atomicOr(sc.err, err);
 }
 
 // ------------------------------------------------------------------------------------------------ staged variant

@@ -77,6 +77,11 @@ struct ProbeArgs {
     int64_t lo[64], hi[64], start[65];
     int32_t n, probe_null;
 };
+struct RunArgs {
+    uint64_t* buf;
+    uint64_t capacity_rows;
+    uint64_t base_rows;
+};
 struct PartArgs {
     uint32_t* hist;
     uint64_t* cursor;
@@ -116,6 +121,8 @@ struct Variant {
     cudaLibrary_t lib = nullptr;
     cudaKernel_t kPage = nullptr, kEmit = nullptr, kRehash = nullptr, kReplay = nullptr, kPageStaged = nullptr, kCount = nullptr, kGather = nullptr, kEmitRange = nullptr, kKeyRange = nullptr, kEmitProbe = nullptr;
     cudaKernel_t kPartCount = nullptr, kPartScatter = nullptr, kPageSweep = nullptr;  // partition sweep (gen.sweepOk)
+    cudaKernel_t kRunsCount = nullptr, kRunsWrite = nullptr, kRunsEmit = nullptr, kRunsToTable = nullptr;   // streaming runs (gen.streamOk)
+    int streamBlocksPerSM = 1;
     int sweepBlocksPerSM = 1, scatterBlocksPerSM = 1;
     int blocksPerSM = 1;
     int stagedStages = 0;      // stages of the shared-memory ring (0 = staged variant unavailable)
@@ -222,6 +229,12 @@ struct pgpu_pipeline {
     size_t partialsCap = 0;
     DeviceBuf tileStatus;
     DeviceBuf failLog;   // deferred rows of the current hash-aggregation chunk
+    // streaming runs (device header, "streaming runs"): keys in key order are aggregated run by run into a linear buffer of
+    // slot-format rows, no hash table. STREAM_OFF once the order was seen to break (the buffer then went into the table).
+    enum StreamMode { STREAM_UNDECIDED, STREAM_ON, STREAM_OFF } streamMode = STREAM_UNDECIDED;
+    DeviceBuf runBuf, runCounts, runOffsets;
+    int64_t runRows = 0;          // rows the buffer holds
+    uint32_t* dViolations = nullptr;
     DeviceBuf sweepBuf;  // partition sweep: the reordered arrays of one batch
     DeviceBuf sweepMeta; // ... [hist u32 x K | ticket u32 x 64 | cursor u64 x K | start u64 x (K + 1)]
     uint64_t* hostScalars = nullptr;  // pinned, 32 words: [0] out_count, [1..2] counters, [3] err, [4..12] key-clustering probe
@@ -370,6 +383,18 @@ pgpu_status getVariant(pgpu_pipeline* p, const std::vector<ColSig>& sig, Variant
             }
             if (v.gen.mode != KernelMode::COMPACT && p->plan->hasAgg && inputIsIntermediate(p->plan->step))
                 CU(cudaLibraryGetKernel(&v.kGather, v.lib, "pgpu_k_gather"));
+            if (v.gen.streamOk) {
+                CU(cudaLibraryGetKernel(&v.kRunsCount, v.lib, "pgpu_k_runs_count"));
+                CU(cudaLibraryGetKernel(&v.kRunsWrite, v.lib, "pgpu_k_runs_write"));
+                CU(cudaLibraryGetKernel(&v.kRunsEmit, v.lib, "pgpu_k_runs_emit"));
+                CU(cudaLibraryGetKernel(&v.kRunsToTable, v.lib, "pgpu_k_runs_to_table"));
+                int nb = 0;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)v.kRunsWrite, kThreads, 0) != cudaSuccess || nb < 1) {
+                    cudaGetLastError();
+                    nb = 2;
+                }
+                v.streamBlocksPerSM = nb;
+            }
             if (v.gen.sweepOk) {
                 CU(cudaLibraryGetKernel(&v.kPartCount, v.lib, "pgpu_k_part_count"));
                 CU(cudaLibraryGetKernel(&v.kPartScatter, v.lib, "pgpu_k_part_scatter"));
@@ -583,11 +608,11 @@ pgpu_status decideTableMode(pgpu_pipeline* p, Variant* v, const DevPage& pg, Var
         const Type& t = p->plan->input[g.bucketKeyChannel];
         if (ca.values && !ca.ids && !ca.dvalues && !t.isVarWidth() && (t.width() == 4 || t.width() == 8)) {
             unsigned long long* dOut = (unsigned long long*)p->dState;  // 64 words of scratch the hash path does not use
-            CU(cudaMemsetAsync(dOut, 0, 72, p->stream));
+            CU(cudaMemsetAsync(dOut, 0, 80, p->stream));
             CU(keyClustering(p->stream, ca.values, t.width(), std::min<int64_t>(pg.rows, 1 << 16), dOut));
-            CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 72, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 80, cudaMemcpyDeviceToHost, p->stream));
             CU(cudaStreamSynchronize(p->stream));
-            CU(cudaMemsetAsync(dOut, 0, 72, p->stream));
+            CU(cudaMemsetAsync(dOut, 0, 80, p->stream));
             p->stats.kernel_launches++;
             const uint64_t changes = p->hostScalars[4];
             int best = 0;
@@ -626,9 +651,46 @@ uint64_t initialTableCapacity(pgpu_pipeline* p, Variant* v) {
     return cap;
 }
 
+// the variant that buffered the runs (its merge / emit kernels share the run buffer's row format)
+Variant* streamVariant(pgpu_pipeline* p) {
+    for (auto& kv : p->variants)
+        if (kv.second.kRunsEmit) return &kv.second;
+    return nullptr;
+}
+
+// Streaming runs: the buffered rows go into the hash table (the key order broke, or a page arrives that the streaming kernel does
+// not take); from here on the pipeline aggregates through the table.
+pgpu_status streamToTable(pgpu_pipeline* p, Variant* v) {
+    p->streamMode = pgpu_pipeline::STREAM_OFF;
+    if (p->runRows == 0) return PGPU_OK;
+    if (!v || !v->kRunsToTable) v = streamVariant(p);
+    if (!v || !v->kRunsToTable) return fail(p, PGPU_CUDA_ERROR, "internal: buffered runs without a variant that can merge them");
+    const uint64_t need = (uint64_t)((double)(p->slotsKnown + p->rowsSinceKnown + p->runRows) / 0.6) + 4096;
+    pgpu_status st;
+    if (!p->dSlots) {
+        if ((st = growTable(p, v, std::max<uint64_t>(need, initialTableCapacity(p, v))))) return st;
+    } else if (p->capacity < need) {
+        if ((st = growTable(p, v, need))) return st;
+    }
+    TableArgs t = tableOf(p);
+    Scratch sc = scratchOf(p);
+    uint64_t* buf = (uint64_t*)p->runBuf.ptr;
+    uint64_t n = (uint64_t)p->runRows;
+    void* args[] = {&buf, &n, &t, &sc};
+    int grid = (int)std::min<uint64_t>((n + kThreads - 1) / kThreads, (uint64_t)p->numSMs * 8);
+    if ((st = launch(p, v->kRunsToTable, grid, kThreads, 0, args))) return st;
+    p->rowsSinceKnown += p->runRows;
+    p->runRows = 0;
+    return PGPU_OK;
+}
+
 // sw: the page is a chunk of a partition-ordered batch (runSweep): the sweep kernel takes it
 pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg, const SweepArgs* sw = nullptr) {
     const GenResult& g = v->gen;
+    if (g.mode == KernelMode::AGG_HASH && p->streamMode == pgpu_pipeline::STREAM_ON) {  // a page the streaming kernel does not take
+        pgpu_status st = streamToTable(p, v);
+        if (st) return st;
+    }
     // kernel parameter block: PageArgs<NC> = ColArg[NC] + rows
     std::vector<unsigned char> pa(sizeof(ColArg) * g.NC + 8);
     memcpy(pa.data(), pg.cols.data(), sizeof(ColArg) * g.NC);
@@ -765,6 +827,102 @@ pgpu_status launchPageKernel(pgpu_pipeline* p, Variant* v, const DevPage& pg, co
     return fail(p, PGPU_INVALID_STATE, "internal: launchPageKernel in COMPACT mode");
 }
 
+// Streaming runs over a device-resident page (device header, "streaming runs"). *done = false when the page is left to the
+// other paths: keys not in order (clustering probe of the first 65 536 keys, or seen to break earlier), small tables, short pages.
+constexpr int64_t kStreamMinRows = 1ll << 20;
+pgpu_status runStream(pgpu_pipeline* p, Variant* v, const DevPage& pg, bool* done) {
+    *done = false;
+    const GenResult& g = v->gen;
+    if (!v->kRunsWrite || p->streamMode == pgpu_pipeline::STREAM_OFF || p->dSlots) return PGPU_OK;
+    auto knob = [](const char* name, int64_t dflt) { const char* e = getenv(name); return e ? (int64_t)atoll(e) : dflt; };
+    double runsPerRow = 0.5;
+    if (p->streamMode == pgpu_pipeline::STREAM_UNDECIDED) {
+        p->streamMode = pgpu_pipeline::STREAM_OFF;
+        if (pg.rows < knob("PGPU_TUNE_STREAM_MIN_ROWS", kStreamMinRows)) return PGPU_OK;
+        if ((size_t)initialTableCapacity(p, v) * g.SLOTW * 8 < (size_t)knob("PGPU_TUNE_STREAM_MIN_TABLE_MB", (int64_t)(kSweepMinTableBytes >> 20)) << 20) return PGPU_OK;
+        if (p->tableMode == pgpu_pipeline::TABLE_BUCKETS || g.bucketKeyChannel < 0) return PGPU_OK;
+        const ColArg& ca = pg.cols[g.bucketKeyChannel];
+        const Type& t = p->plan->input[g.bucketKeyChannel];
+        if (!(ca.values && !ca.ids && !ca.dvalues && !t.isVarWidth() && (t.width() == 4 || t.width() == 8))) return PGPU_OK;
+        unsigned long long* dOut = (unsigned long long*)p->dState;  // 64 words of scratch the hash path does not use
+        const int64_t n = std::min<int64_t>(pg.rows, 1 << 16);
+        CU(cudaMemsetAsync(dOut, 0, 80, p->stream));
+        CU(keyClustering(p->stream, ca.values, t.width(), n, dOut));
+        CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 80, cudaMemcpyDeviceToHost, p->stream));
+        CU(cudaStreamSynchronize(p->stream));
+        CU(cudaMemsetAsync(dOut, 0, 80, p->stream));
+        p->stats.kernel_launches++;
+        const uint64_t changes = p->hostScalars[4], descents = p->hostScalars[13];
+        // in order, and in runs or at least dense enough that the buffer stays well below a hash table's size
+        // (long groups belong to the table: its run compaction folds them per warp, and the emit kernel here walks a group serially)
+        if ((descents != 0 || (changes + 1) * 32 < (uint64_t)n) && !knob("PGPU_TUNE_STREAM_FORCE", 0)) return PGPU_OK;
+        runsPerRow = std::min(1.0, (double)(changes + 1) / (double)n * 1.3 + 0.02);
+        p->streamMode = pgpu_pipeline::STREAM_ON;
+    }
+    if (!p->dViolations) CU(cudaMalloc((void**)&p->dViolations, 256));
+    pgpu_status st;
+    Scratch sc = scratchOf(p);
+    const size_t rowBytes = (size_t)g.SLOTW * 8;
+    // the buffer holds at least `needRows` rows (the rows it has are kept)
+    auto ensureRunRows = [&](int64_t needRows, int64_t wantRows) -> pgpu_status {
+        if (p->runBuf.cap >= (size_t)needRows * rowBytes) return PGPU_OK;
+        DeviceBuf old = p->runBuf;
+        p->runBuf = DeviceBuf();
+        // (pages keep coming: grow by half at least, so that the rows kept are not copied once per page)
+        pgpu_status e = ensureDev(p, p->runBuf, std::max((size_t)std::max(needRows, wantRows) * rowBytes, old.cap + old.cap / 2));
+        if (e) return e;
+        if (old.ptr) {
+            if (p->runRows) CU(cudaMemcpyAsync(p->runBuf.ptr, old.ptr, (size_t)p->runRows * rowBytes, cudaMemcpyDeviceToDevice, p->stream));
+            CU(cudaStreamSynchronize(p->stream));
+            CU(cudaFree(old.ptr));
+        }
+        return PGPU_OK;
+    };
+    const int64_t chunkRows = (int64_t)1 << 30;  // (the unit counts of a launch stay below 2^32)
+    for (int64_t r0 = 0; r0 < pg.rows; r0 += chunkRows) {
+        const int64_t n = std::min(chunkRows, pg.rows - r0);
+        std::vector<ColArg> cols = pg.cols;
+        for (int c : g.usedChannels) {
+            const Type& t = p->plan->input[c];
+            ColArg& ca = cols[c];
+            if (ca.ids) ca.ids += r0;
+            if (ca.offsets) ca.offsets += r0;
+            else if (ca.values) ca.values = (const char*)ca.values + (size_t)r0 * (t.isVarWidth() ? 16 : t.width());
+            if (ca.nulls) ca.nulls += r0;
+        }
+        std::vector<unsigned char> pa(sizeof(ColArg) * g.NC + 8);
+        memcpy(pa.data(), cols.data(), sizeof(ColArg) * g.NC);
+        memcpy(pa.data() + sizeof(ColArg) * g.NC, &n, 8);
+        const int grid = p->numSMs * v->streamBlocksPerSM;
+        {
+            // count the runs per warp unit, scan, size the buffer exactly, write
+            const int64_t unitRows = 32 * 4 * g.streamSub, units = (n + unitRows - 1) / unitRows;
+            if ((st = ensureDev(p, p->runCounts, (size_t)units * 4))) return st;
+            if ((st = ensureDev(p, p->runOffsets, (size_t)(units + 1024) * 8))) return st;
+            uint32_t* counts = (uint32_t*)p->runCounts.ptr;
+            unsigned long long* offsets = (unsigned long long*)p->runOffsets.ptr;
+            {
+                void* args[] = {pa.data(), &counts, &sc};
+                if ((st = launch(p, v->kRunsCount, (int)std::min<int64_t>((units + 7) / 8, grid), kThreads, 0, args))) return st;
+            }
+            CU(runsScan(p->stream, counts, units, offsets, offsets + units, p->numSMs * 4, (unsigned long long*)p->dOutCount));
+            p->stats.kernel_launches += 2;
+            CU(cudaMemcpyAsync(&p->hostScalars[0], p->dOutCount, 8, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaStreamSynchronize(p->stream));
+            const int64_t live = (int64_t)p->hostScalars[0];
+            if ((st = ensureRunRows(p->runRows + live, p->runRows + live + (int64_t)((double)(pg.rows - r0 - n) * runsPerRow)))) return st;
+            RunArgs ra{(uint64_t*)p->runBuf.ptr, (uint64_t)(p->runBuf.cap / rowBytes), (uint64_t)p->runRows};
+            const unsigned long long* coffsets = offsets;
+            void* args[] = {pa.data(), &coffsets, &ra, &sc};
+            if ((st = launch(p, v->kRunsWrite, (int)std::min<int64_t>((units + 7) / 8, grid), kThreads, 0, args))) return st;
+            p->runRows += live;
+        }
+    }
+    p->stats.streamed_runs = p->runRows;
+    *done = true;
+    return PGPU_OK;
+}
+
 // Partition sweep (device header, "partition sweep") over a long device-resident page: count rows per table slice, scatter the
 // used channels' arrays into slice order, run the page kernel's sweep variant over the reordered rows. *swept = false when the
 // page is left to the ordinary path (table not much larger than L2, no memory for the reordered copy, bucketed table).
@@ -799,11 +957,11 @@ pgpu_status runSweep(pgpu_pipeline* p, Variant* v, const DevPage& pg, bool* swep
         if (ca.values && !ca.ids && !ca.dvalues && !t.isVarWidth() && (t.width() == 4 || t.width() == 8)) {
             unsigned long long* dOut = (unsigned long long*)p->dState;  // 64 words of scratch the hash path does not use
             const int64_t n = std::min<int64_t>(pg.rows, 1 << 16);
-            CU(cudaMemsetAsync(dOut, 0, 72, p->stream));
+            CU(cudaMemsetAsync(dOut, 0, 80, p->stream));
             CU(keyClustering(p->stream, ca.values, t.width(), n, dOut));
-            CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 72, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaMemcpyAsync(&p->hostScalars[4], dOut, 80, cudaMemcpyDeviceToHost, p->stream));
             CU(cudaStreamSynchronize(p->stream));
-            CU(cudaMemsetAsync(dOut, 0, 72, p->stream));
+            CU(cudaMemsetAsync(dOut, 0, 80, p->stream));
             p->stats.kernel_launches++;
             uint64_t near = 0;
             for (int d = 0; d < 8; d++) near = std::max<uint64_t>(near, p->hostScalars[5 + d]);
@@ -1071,6 +1229,15 @@ pgpu_status processDevicePage(pgpu_pipeline* p, Variant* v, const pgpu_column* c
     }
     int64_t chunk = g.mode == KernelMode::AGG_HASH ? kHashChunkRows : rows;
     if (v->kPageStaged) chunk = chunk / g.stagedTile * g.stagedTile;  // inner chunks are whole tiles: only the page's end is ragged
+    if (g.mode == KernelMode::AGG_HASH && v->kRunsWrite && p->streamMode != pgpu_pipeline::STREAM_OFF && !p->dSlots) {
+        DevPage whole;
+        whole.rows = rows;
+        colArgsFor(0, whole.cols);
+        bool done = false;
+        pgpu_status st = runStream(p, v, whole, &done);
+        if (st) return st;
+        if (done) return PGPU_OK;
+    }
     for (int64_t r0 = 0; r0 < rows; r0 += chunk) {
         if (v->kPageSweep) {
             // a long device-resident page and a table far larger than L2: reorder the rest of the page by table slice first
@@ -1696,6 +1863,36 @@ pgpu_status buildAggOutput(pgpu_pipeline* p) {
         if (st) return st;
         p->outRowsTotal = 1;
     } else {
+        if (p->streamMode == pgpu_pipeline::STREAM_ON && p->runRows > 0 && !p->dSlots) {
+            // streaming runs: neighbours with the same key merge, every group is finalised straight out of the buffer
+            v = streamVariant(p);
+            if (!v) return fail(p, PGPU_CUDA_ERROR, "internal: buffered runs without an emit kernel");
+            pgpu_status st = ensureOutBuffers(p, p->runRows + p->extraOutRows);
+            if (st) return st;
+            CU(cudaMemsetAsync(p->dViolations, 0, 4, p->stream));
+            std::vector<unsigned char> oa = outArgsBlock(p);
+            Scratch sc = scratchOf(p);
+            const uint64_t* buf = (const uint64_t*)p->runBuf.ptr;
+            int64_t n = p->runRows;
+            void* args[] = {&buf, &n, oa.data(), &sc, &p->dViolations};
+            int grid = (int)std::min<int64_t>((n + kThreads * 4 - 1) / (kThreads * 4), (int64_t)p->numSMs * 8);  // 4 = kRunsEmitPer
+            st = launch(p, v->kRunsEmit, grid, kThreads, 0, args);
+            if (st) return st;
+            CU(cudaMemcpyAsync(&p->hostScalars[0], p->dOutCount, 8, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaMemcpyAsync(&p->hostScalars[14], p->dViolations, 4, cudaMemcpyDeviceToHost, p->stream));
+            CU(cudaStreamSynchronize(p->stream));
+            if ((uint32_t)p->hostScalars[14] == 0) {
+                p->outRowsTotal = p->groupsKnown = (int64_t)p->hostScalars[0];
+                st = checkDeviceErrors(p);
+                if (st) return st;
+                p->outputReady = true;
+                p->outRowsServed = 0;
+                return PGPU_OK;
+            }
+            // the key order decreases somewhere: a key may occur in two places. Everything goes through the table after all.
+            if ((st = streamToTable(p, v))) return st;
+            CU(cudaMemsetAsync(p->dOutCount, 0, 8, p->stream));
+        }
         if (!p->dSlots) {
             p->outRowsTotal = 0;
         } else {
@@ -1870,6 +2067,10 @@ void pgpu_pipeline_destroy(pgpu_pipeline* p) {
         if (p->tileStatus.ptr) cudaFree(p->tileStatus.ptr);
         if (p->failLog.ptr) cudaFree(p->failLog.ptr);
         if (p->sweepBuf.ptr) cudaFree(p->sweepBuf.ptr);
+        if (p->runBuf.ptr) cudaFree(p->runBuf.ptr);
+        if (p->runCounts.ptr) cudaFree(p->runCounts.ptr);
+        if (p->runOffsets.ptr) cudaFree(p->runOffsets.ptr);
+        if (p->dViolations) cudaFree(p->dViolations);
         if (p->sweepMeta.ptr) cudaFree(p->sweepMeta.ptr);
         if (p->dSlots) cudaFree(p->dSlots);
         if (p->hostScalars) cudaFreeHost(p->hostScalars);
@@ -2708,6 +2909,7 @@ pgpu_status pgpu_reset(pgpu_pipeline* p) {
         CU(cudaStreamSynchronize(p->stream));
         for (auto& s : p->slots) s.inFlight = false;
     }
+    p->runRows = 0;  // (the streaming decision stays: STREAM_OFF once the keys were seen out of order)
     p->finishing = p->finished = p->sawInput = p->outputReady = p->compactPending = false;
     p->outRowsTotal = p->outRowsServed = p->mergeRows = p->outBoundary = 0;
     int64_t cap = p->stats.table_capacity, bucketed = p->stats.table_bucketed;
