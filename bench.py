@@ -710,7 +710,7 @@ def run_device_steps(args, wl, device, dist, steps, warmup):
     info = dict(dev_ms=dev_ms, wall_s=wall, launches=nl, clocks=clocks, kern_ms=kern_ms, kern_launches=kern_launches,
                 kern_steps=ksteps, result_rows=state["result_rows"], table_capacity=op.stats().table_capacity,
                 exchange_bytes=state["exchange_bytes"], private_groups=state.get("private_groups", 0),
-                partition_sweeps=op.stats().partition_sweeps)
+                partition_sweeps=op.stats().partition_sweeps, streamed_runs=op.stats().streamed_runs)
     if repart is not None and not hasattr(repart, "exchange"):
         repart.close()
     if final is not None:
@@ -889,6 +889,9 @@ def run_workload(args, name, device, dist, headline):
     kname = "pgpu_k_page_staged (cp.async.bulk ring + register-resident groups)" if name in ("q1", "q1dict") else "pgpu_k_page (fused scan+filter+project+aggregate, direct loads)"
     if info.get("partition_sweeps"):
         kname = "pgpu_k_part_count + pgpu_k_part_scatter + pgpu_k_page_sweep (rows reordered by table slice, then the fused kernel with L2-resident table slices; kernel_ms_per_step is the sum of the three)"
+    if info.get("streamed_runs"):
+        kname = ("pgpu_k_runs_count + pgpu_k_runs_write (streaming runs: the keys arrive in key order, one buffer row per run, no hash table; "
+                 "kernel_ms_per_step is the sum of the two and of the offsets scan between them; they read the rows twice, the algorithmic bytes count them once)")
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "bytes_per_launch": alg_bytes_step / max(launches_step, 1), "avg_launch_ms": kern_ms_step / max(launches_step, 1),
                 "kernel_ms_per_step": kern_ms_step, "launches_per_step": launches_step, "kernel": kname, "peak_source": peak_src,
@@ -909,7 +912,7 @@ def run_workload(args, name, device, dist, headline):
     rec = {"metric": "lineitem_rows_per_second", "value": value, "unit": "rows/s", "ms_per_step": ms_per_step, "steps": steps, "warmup": warmup,
            "gb_per_s": value * wl["bytes_per_row"] / 1e9, "roofline": roofline, "config": config, "gpu_launches": info["launches"],
            "clocks": info["clocks"], "table_capacity_slots": info["table_capacity"], "result_rows": info["result_rows"],
-           "partition_sweeps_per_step": info.get("partition_sweeps", 0)}
+           "partition_sweeps_per_step": info.get("partition_sweeps", 0), "streamed_runs_per_step": info.get("streamed_runs", 0)}
     if world > 1:
         small = name in ("q1", "q1dict", "q6")
         rec["exchange"] = {"shape": ("gather: push kernel stores the partial rows into every rank's inbox over NVLink, FINAL gather kernel merges them; no host round trip (pgpu_exchange_partial)" if args.exchange == "peer" else "gather: one NCCL all-gather of packed partial pages, FINAL on every rank") if small else ("hash repartition; FINAL kernel reads each peer's partition over NVLink (CUDA IPC peer memory, pgpu_exchange_partial)" if args.exchange == "peer" else "hash repartition + all_to_all_single per column + FINAL per rank"),

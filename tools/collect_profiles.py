@@ -18,10 +18,11 @@ os.makedirs(P, exist_ok=True)
 # rows of the captured (steady-state, full-chunk) launch: hash-aggregation pages are launched in chunks of kHashChunkRows = 64 Mi rows
 # (csrc/pipeline.cpp), rounded down to whole staged tiles (Q1: 1920 rows, dictionary Q1: 960); a global aggregation is one launch
 CHUNK = 64 << 20
-LAUNCH_ROWS = {"q1": CHUNK // 1920 * 1920, "q1dict": CHUNK // 960 * 960, "q6": 600_037_902, "highcard": CHUNK, "highcard_shuffled": CHUNK,
-               "highcard_buckets": CHUNK, "highcard_shuffled_scatter": 600_037_902, "highcard_shuffled_plain": CHUNK}
-ALG_BYTES = {"q1": 46, "q1dict": 32, "q6": 28, "highcard": 16, "highcard_shuffled": 16, "highcard_buckets": 16, "highcard_shuffled_scatter": 32,
-             "highcard_shuffled_plain": 16}
+LAUNCH_ROWS = {"q1": CHUNK // 1920 * 1920, "q1dict": CHUNK // 960 * 960, "q6": 600_037_902, "highcard_table": CHUNK, "highcard_shuffled": CHUNK,
+               "highcard_buckets": CHUNK, "highcard_shuffled_scatter": 600_037_902, "highcard_shuffled_plain": CHUNK,
+               "highcard_runs_count": 600_037_902, "highcard_runs_write": 600_037_902}
+ALG_BYTES = {"q1": 46, "q1dict": 32, "q6": 28, "highcard_table": 16, "highcard_shuffled": 16, "highcard_buckets": 16, "highcard_shuffled_scatter": 32,
+             "highcard_shuffled_plain": 16, "highcard_runs_count": 16, "highcard_runs_write": 16}
 KEEP = ("Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread",
         "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic", "smsp__inst_executed.sum",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -47,7 +48,8 @@ for t in (16, 8, 4, 2, 1):
 traffic = {}
 peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
 lines = []
-for name in ("q1", "q6", "q1dict", "highcard", "highcard_shuffled", "highcard_shuffled_scatter", "highcard_shuffled_plain", "highcard_buckets", "highcard_emit"):
+for name in ("q1", "q6", "q1dict", "highcard_table", "highcard_shuffled", "highcard_shuffled_scatter", "highcard_shuffled_plain", "highcard_buckets", "highcard_emit",
+             "highcard_runs_count", "highcard_runs_write", "highcard_runs_emit"):
     rep = os.path.join(G, name + "_full.ncu-rep")
     if not os.path.exists(rep):
         continue
@@ -84,41 +86,55 @@ for name in ("q1", "q6", "q1dict", "highcard", "highcard_shuffled", "highcard_sh
                          "source": "profiles/%s_%s_ncu_raw.txt (ncu --set full --clock-control none, one steady-state launch)" % (tag, name)}
         lines.append("| %s | %.0f M | %.3f | %.2f | %.2f | %.2f | %.0f | %.2f |" % (name, rows / 1e6, ms, dram / 1e9, dram / rows, dram / rows / ALG_BYTES[name],
                                                                                  dram / ms / 1e6, dram / ms / 1e6 / peak))
-# GROUP BY over keys in no order runs as three kernels (partition sweep): DRAM bytes of one whole step from the launch list
-# (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum over bench.py --workload highcard_shuffled --steps 1)
-ll = os.path.join(G, "launches_highcard_shuffled.csv")
-if os.path.exists(ll):
-    shutil.copy(ll, os.path.join(P, "%s_launches_highcard_shuffled.csv" % tag))
+# Workloads whose step is several kernels: DRAM bytes of one whole step from the launch list
+# (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum over bench.py --workload W --steps 1):
+# GROUP BY over keys in no order = partition sweep (count + scan + scatter + sweeps), GROUP BY over keys in key order = streaming
+# runs (count + 2 scan kernels + write). The emit kernel of finish() is not part of either.
+def step_traffic(name, first, last, must, what):
+    global lines
+    ll = os.path.join(G, "launches_%s.csv" % name)
+    if not os.path.exists(ll):
+        return
+    shutil.copy(ll, os.path.join(P, "%s_launches_%s.csv" % (tag, name)))
     rr = [r for r in csv.reader(open(ll)) if len(r) > 10]
+    if not rr or "Metric Name" not in rr[0]:
+        return
     hdr = rr[0]
     ik, im, iv, iid = hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Value"), hdr.index("ID")
     launches = {}
     for r_ in rr[1:]:
         launches.setdefault(int(r_[iid]), {"kernel": r_[ik]})[r_[im]] = float(r_[iv].replace(",", ""))
     ids = sorted(launches)
-    starts = [i for i in ids if launches[i]["kernel"].startswith("pgpu_k_part_count")]
+    starts = [i for i in ids if launches[i]["kernel"].startswith(first)]
     step = []
     for st_ in reversed(starts):  # the last COMPLETE step (the capture may end inside one)
         step, complete = [], False
         for i in ids[ids.index(st_):]:
-            if launches[i]["kernel"].startswith("pgpu_k_emit"):
+            if launches[i]["kernel"].startswith(last):
                 complete = True
                 break
             step.append(launches[i])
         if complete:
             break
         step = []
-    if starts:
-        if step and any(x["kernel"].startswith("pgpu_k_page_sweep") for x in step):
-            dram = sum(x.get("dram__bytes_read.sum", 0) + x.get("dram__bytes_write.sum", 0) for x in step)
-            ms = sum(x.get("gpu__time_duration.sum", 0) for x in step) / 1e6
-            rows = LAUNCH_ROWS["q6"]
-            traffic["highcard_shuffled"] = {"dram_bytes_per_row": dram / rows, "dram_bytes_per_launch": dram / len(step), "launch_rows": rows, "launch_ms_under_ncu": ms,
-                                            "algorithmic_bytes_per_row": 16, "ratio_to_algorithmic": dram / rows / 16, "dram_gbs_under_ncu": dram / ms / 1e6,
-                                            "launches": len(step),
-                                            "source": "profiles/%s_launches_highcard_shuffled.csv (ncu launch list of one step: pgpu_k_part_count + k_partition_scan + pgpu_k_part_scatter + %d x pgpu_k_page_sweep)" % (tag, sum(1 for x in step if x["kernel"].startswith("pgpu_k_page_sweep")))}
-            lines = [l for l in lines if not l.startswith("| highcard_shuffled |")]
-            lines.append("| highcard_shuffled (whole step: count + scatter + sweeps) | %.0f M | %.3f | %.2f | %.2f | %.2f | %.0f | %.2f |" % (rows / 1e6, ms, dram / 1e9, dram / rows, dram / rows / 16, dram / ms / 1e6, dram / ms / 1e6 / peak))
+    if not step or not any(x["kernel"].startswith(must) for x in step) or "dram__bytes_read.sum" not in step[0]:
+        return
+    dram = sum(x.get("dram__bytes_read.sum", 0) + x.get("dram__bytes_write.sum", 0) for x in step)
+    ms = sum(x.get("gpu__time_duration.sum", 0) for x in step) / 1e6
+    rows = LAUNCH_ROWS["q6"]
+    kernels = {}
+    for x in step:
+        kernels[x["kernel"]] = kernels.get(x["kernel"], 0) + 1
+    traffic[name] = {"dram_bytes_per_row": dram / rows, "dram_bytes_per_launch": dram / len(step), "launch_rows": rows, "launch_ms_under_ncu": ms,
+                     "algorithmic_bytes_per_row": 16, "ratio_to_algorithmic": dram / rows / 16, "dram_gbs_under_ncu": dram / ms / 1e6,
+                     "launches": len(step),
+                     "source": "profiles/%s_launches_%s.csv (ncu launch list of one step: %s)" % (tag, name, " + ".join("%d x %s" % (n, k) for k, n in kernels.items()))}
+    lines = [l for l in lines if not l.startswith("| %s |" % name)]
+    lines.append("| %s (whole step: %s) | %.0f M | %.3f | %.2f | %.2f | %.2f | %.0f | %.2f |" % (name, what, rows / 1e6, ms, dram / 1e9, dram / rows, dram / rows / 16, dram / ms / 1e6, dram / ms / 1e6 / peak))
+
+
+step_traffic("highcard_shuffled", "pgpu_k_part_count", "pgpu_k_emit", "pgpu_k_page_sweep", "count + scatter + sweeps")
+step_traffic("highcard", "pgpu_k_runs_count", "pgpu_k_runs_emit", "pgpu_k_runs_write", "streaming runs: count + scan + write")
 with open(os.path.join(P, "traffic.json"), "w") as f:
     json.dump(traffic, f, indent=1, sort_keys=True)
     f.write("\n")
