@@ -1669,6 +1669,67 @@ GenResult generate(const Plan& plan, const std::vector<ColSig>& sig, const GenOp
         src << em.str();
         src << "    }\n";
     }
+    // ---- key_order (streaming runs): the order the rows of a run buffer are expected in = the order of a table sorted by the
+    // grouping fields, first field first, every field as its SQL type orders it (signed integers, doubles by value), NULLs last.
+    // < 0: a before b, 0: the same key, > 0: a after b. The words are taken without the slot's occupied mark.
+    if (res.mode == KernelMode::AGG_HASH && !fields.empty()) {
+        std::ostringstream ko;
+        auto L = [&](const std::string& s) { ko << "        " << s << "\n"; };
+        auto getOf = [&](const std::string& arr, int byteOff, int nbytes) -> std::string {
+            int w = byteOff / 8, sh = (byteOff % 8) * 8;
+            std::string e = "(" + arr + "[" + std::to_string(w) + "]" + (sh ? " >> " + std::to_string(sh) : "") + ")";
+            if (sh + nbytes * 8 > 64) e = "(" + e + " | (" + arr + "[" + std::to_string(w + 1) + "] << " + std::to_string(64 - sh) + "))";
+            if (nbytes < 8) e = "(" + e + " & " + maskOf(nbytes) + ")";
+            return e;
+        };
+        for (auto& f : fields) {
+            L("{");
+            if (f.nullable) {
+                L("    const u32 na = (u32)(" + getOf("a", f.nullBit / 8, 1) + " >> " + std::to_string(f.nullBit % 8) + ") & 1u, nb = (u32)(" + getOf("b", f.nullBit / 8, 1) + " >> " +
+                  std::to_string(f.nullBit % 8) + ") & 1u;");
+                L("    if (na != nb) return na < nb ? -1 : 1;");
+            }
+            const int n0 = std::min(8, f.nbytes);
+            std::string la = getOf("a", f.byteOffset, n0), lb = getOf("b", f.byteOffset, n0);
+            switch (f.type.kind) {
+                case TypeKind::INTEGER:
+                case TypeKind::DATE:
+                    L("    const i32 x = (i32)(u32)" + la + ", y = (i32)(u32)" + lb + ";");
+                    break;
+                case TypeKind::BIGINT:
+                    L("    const i64 x = (i64)" + la + ", y = (i64)" + lb + ";");
+                    break;
+                case TypeKind::DOUBLE:  // the group bits of a double as a sign-magnitude integer: -x before +x, NaN after everything
+                    L("    const u64 xa = " + la + ", xb = " + lb + ";");
+                    L("    const u64 x = (xa >> 63) ? ~xa : (xa | 0x8000000000000000ull), y = (xb >> 63) ? ~xb : (xb | 0x8000000000000000ull);");
+                    break;
+                case TypeKind::DECIMAL:
+                    if (f.type.isShortDecimal()) {
+                        L("    const i64 x = (i64)" + la + ", y = (i64)" + lb + ";");
+                    } else {  // 16 value bytes: the high half decides (signed), then the low half
+                        L("    const i64 xh = (i64)" + getOf("a", f.byteOffset + 8, f.nbytes - 8) + ", yh = (i64)" + getOf("b", f.byteOffset + 8, f.nbytes - 8) + ";");
+                        L("    if (xh != yh) return xh < yh ? -1 : 1;");
+                        L("    const u64 x = " + la + ", y = " + lb + ";");
+                    }
+                    break;
+                default:  // BOOLEAN, packed VARCHAR: any fixed order of the bytes
+                    if (f.nbytes > 8) {
+                        L("    const u64 xh = " + getOf("a", f.byteOffset + 8, f.nbytes - 8) + ", yh = " + getOf("b", f.byteOffset + 8, f.nbytes - 8) + ";");
+                        L("    if (xh != yh) return xh < yh ? -1 : 1;");
+                    }
+                    L("    const u64 x = " + la + ", y = " + lb + ";");
+                    break;
+            }
+            L("    if (x != y) return x < y ? -1 : 1;");
+            L("}");
+        }
+        L("return 0;");
+        src << "    PGPU_DEV static int key_order(const u64* a, const u64* b) {\n" << ko.str() << "    }\n";
+        const Expr& ke = *plan.projections[fields[0].projChannel];
+        const TypeKind k0 = fields[0].type.kind;
+        if (ke.kind == ExprKind::INPUT && (k0 == TypeKind::BIGINT || k0 == TypeKind::INTEGER || k0 == TypeKind::DATE || (k0 == TypeKind::DECIMAL && fields[0].type.isShortDecimal())))
+            res.streamKeyChannel = ke.channel;
+    }
     // partition sweep (device header, "partition sweep"): the rows of the used channels can be moved one by one when every
     // array is fixed width per position: plain values / 16-byte varchar cells / dictionary ids (+ null flags); RLE blocks have
     // nothing to move

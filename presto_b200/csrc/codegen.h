@@ -57,6 +57,7 @@ struct GenResult {
     bool sweepOk = false;          // partition sweep kernels were generated (pgpu_k_part_count / _scatter / pgpu_k_page_sweep)
     int sweepRowBytes = 0;         // bytes the scatter moves per row (arrays of the used channels)
     int sweepStageWidth = 1;       // widest moved element: the scatter stages kPartTile elements of one array at a time
+    int streamKeyChannel = -1;     // input channel the FIRST grouping field is read from as it is, an integer type (-1: none): the streaming-runs probe
     int bucketKeyChannel = -1;     // input channel the key is read from as it is (-1: the key is computed), for the clustering probe
 };
 

@@ -1672,7 +1672,7 @@ PGPU_DEV void body_agg_hash_sweep(const PageArgs<P::NC>& a, const TableArgs& t, 
 // key); pgpu_k_runs_emit merges such neighbours, finalises every group straight into the output buffers and counts the places
 // where the key order DEcreases. A decrease means a key may reappear later: the host then merges the buffered rows into the hash
 // table (pgpu_k_runs_to_table) and takes the ordinary path — the buffer holds partial states, nothing is lost. Any total order
-// serves; the packed key words are compared as unsigned integers, last word first.
+// serves; P::key_order is the one a table sorted by the grouping fields comes in (first field first, SQL type order, NULLs last).
 struct RunArgs {
     u64* buf;           // slot-format rows, 32-byte aligned
     u64 capacity_rows;
@@ -1830,21 +1830,12 @@ PGPU_DEV void body_runs_write(const PageArgs<P::NC>& a, const u64* offsets, cons
     if (err) atomicOr(sc.err, err);
 }
 
-// rows i - 1 and i of the buffer: same key? does the order decrease?
+// rows i - 1 and i of the buffer: same key? does the order decrease? (P::key_order: the grouping fields as SQL orders them)
 template <class P>
 PGPU_DEV void runs_compare(const u64* prev, const u64* cur, bool& same, bool& decreases) {
-    same = true;
-    decreases = false;
-    bool decided = false;
-#pragma unroll
-    for (int w = P::KW - 1; w >= 0; w--) {
-        const u64 x = prev[P::KOFF + w], y = cur[P::KOFF + w];
-        same &= x == y;
-        if (!decided && x != y) {
-            decided = true;
-            decreases = y < x;
-        }
-    }
+    const int o = P::key_order(prev + P::KOFF, cur + P::KOFF);
+    same = o == 0;
+    decreases = o > 0;
 }
 
 constexpr i64 kRunsMaxPieces = 64;  // buffer rows of one key the emit kernel merges serially (a piece = the key's rows inside one warp's 128)
@@ -1886,15 +1877,8 @@ PGPU_DEV void body_runs_emit(const u64* buf, i64 nrows, const OutArgs<P::NO>& ou
                 prev[w] = shfl_up_u64(cur[k][w], 1);
                 if (lane == 0) prev[w] = before[k][w];
             }
-            bool same = true, dec = false, decided = false;
-#pragma unroll
-            for (int w = KW - 1; w >= 0; w--) {
-                same &= prev[w] == cur[k][w];
-                if (!decided && prev[w] != cur[k][w]) {
-                    decided = true;
-                    dec = cur[k][w] < prev[w];
-                }
-            }
+            const int order = P::key_order(prev, cur[k]);
+            const bool same = order == 0, dec = order > 0;
             const bool head = valid && (i == 0 || !same);
             bad += (valid && i > 0 && dec) ? 1u : 0u;
             // the row after this one: the next lane's (lane 31: the next warp's first row, read above)

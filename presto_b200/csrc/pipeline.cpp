@@ -840,11 +840,11 @@ pgpu_status runStream(pgpu_pipeline* p, Variant* v, const DevPage& pg, bool* don
         p->streamMode = pgpu_pipeline::STREAM_OFF;
         if (pg.rows < knob("PGPU_TUNE_STREAM_MIN_ROWS", kStreamMinRows)) return PGPU_OK;
         if ((size_t)initialTableCapacity(p, v) * g.SLOTW * 8 < (size_t)knob("PGPU_TUNE_STREAM_MIN_TABLE_MB", (int64_t)(kSweepMinTableBytes >> 20)) << 20) return PGPU_OK;
-        if (p->tableMode == pgpu_pipeline::TABLE_BUCKETS || g.bucketKeyChannel < 0) return PGPU_OK;
+        if (p->tableMode == pgpu_pipeline::TABLE_BUCKETS || g.streamKeyChannel < 0) return PGPU_OK;
         if (const char* force = getenv("PGPU_TUNE_BUCKETS"))
             if (*force && strcmp(force, "0")) return PGPU_OK;  // the bucketed-table experiment was asked for: its probe decides, on the table path
-        const ColArg& ca = pg.cols[g.bucketKeyChannel];
-        const Type& t = p->plan->input[g.bucketKeyChannel];
+        const ColArg& ca = pg.cols[g.streamKeyChannel];  // the first grouping field: in order it must be, whatever the others do
+        const Type& t = p->plan->input[g.streamKeyChannel];
         if (!(ca.values && !ca.ids && !ca.dvalues && !t.isVarWidth() && (t.width() == 4 || t.width() == 8))) return PGPU_OK;
         unsigned long long* dOut = (unsigned long long*)p->dState;  // 64 words of scratch the hash path does not use
         const int64_t n = std::min<int64_t>(pg.rows, 1 << 16);

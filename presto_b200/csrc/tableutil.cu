@@ -9,7 +9,7 @@ __global__ void k_key_clustering(const T* __restrict__ keys, long long n, unsign
     unsigned changes = 0, descents = 0, near[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (long long i = 1 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const long long a = (long long)keys[i - 1], b = (long long)keys[i];
-        if ((unsigned long long)b < (unsigned long long)a) descents++;  // the order the streaming-runs path relies on: packed key words as unsigned integers
+        if (b < a) descents++;  // the order the streaming-runs path expects of its first grouping field (P::key_order: signed)
         if (a != b) {
             changes++;
 #pragma unroll

@@ -9,7 +9,7 @@ namespace pgpu {
 // integer key column, out[0] = positions whose key differs from its predecessor's, out[1 + d] (d = 0..7) = those of them whose
 // predecessor lies in the same bucket of 8 when buckets are cut at 8n - d ((key + d) >> 3 equal): clusters of 8 keys need not
 // start at a multiple of 8 (TPC-H order keys start at 8n + 1). out[9] = positions whose key is smaller than its predecessor's, compared
-// as unsigned integers (the streaming-runs path needs keys in that order). `width` = 4 or 8 bytes per key. out[0..9] zeroed by the caller.
+// as signed integers (the streaming-runs path expects its first grouping field in that order). `width` = 4 or 8 bytes per key. out[0..9] zeroed by the caller.
 cudaError_t keyClustering(cudaStream_t stream, const void* keys, int width, int64_t n, unsigned long long* out);
 
 // Partition sweep (device/pgpu_device.cuh "partition sweep"): rows per partition -> first row of every partition.

@@ -146,6 +146,32 @@ def test_stream_filter_null_keys_and_long_groups(monkeypatch):
 
 
 @pytest.mark.gpu
+def test_stream_signed_keys_nulls_last_and_sorted_two_field_keys(monkeypatch):
+    """the expected order is the one a sorted table comes in (P::key_order): signed integers through zero, NULLs after the values,
+    the first grouping field first. None of these falls back to the table (no rehash, no table at all)."""
+    plan = sum_plan()
+    page = sorted_page(200_000, start=-100_000, key_nulls=True)
+    act, st = run_streamed(plan, [page], monkeypatch, expect_streamed=True)
+    assert st.table_capacity == 0, "fell back to the table"
+    assert_rows_equal_ignore_order(act, run_oracle(plan, [page]), nkeys=1, rtol=0.0)
+    # (orderkey, linenumber): sorted by both, every row its own group, the second field restarts at 1 in every order
+    rng = np.random.default_rng(5)
+    n = 150_000
+    lens = rng.integers(1, 8, n)
+    k1 = np.repeat(np.cumsum(rng.integers(1, 5, n)) - 70_000, lens)[:n].astype(np.int64)
+    k2 = (np.arange(n) - np.repeat(np.concatenate([[0], np.cumsum(lens)[:-1]]), lens)[:n] + 1).astype(np.int32)
+    q = rng.integers(1, 51, n).astype(np.float64)
+    page = Page(LongArrayBlock(BIGINT, k1), IntArrayBlock(INTEGER, k2), LongArrayBlock(DOUBLE, q))
+    plan = plan_text([BIGINT, INTEGER, DOUBLE], step="single", groupByChannels=[0, 1],
+                     aggregations=[Aggregation("sum", DOUBLE, 2, DOUBLE), Aggregation("count", BIGINT)], expectedGroups=NO_DIRECTORY)
+    act, st = run_streamed(plan, [page], monkeypatch, expect_streamed=True)
+    assert st.table_capacity == 0, "fell back to the table"
+    exp = run_oracle(plan, [page])
+    assert len(exp) == n
+    assert_rows_equal_ignore_order(act, exp, nkeys=2, rtol=0.0)
+
+
+@pytest.mark.gpu
 def test_stream_two_key_fields_and_int_keys(monkeypatch):
     rng = np.random.default_rng(11)
     n = 180_000

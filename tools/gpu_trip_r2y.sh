@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 exec > gpurun_out/r2y.log 2>&1
 timeout 900 python -m pytest tests/test_gpu_stream.py -q -m gpu 2>&1 | tail -8
-for cfg in "1 4" "1 5" "1 3" "2 3"; do
+for cfg in "1 4"; do
   set -- $cfg
   PGPU_TUNE_STREAM_SUB=$1 PGPU_TUNE_STREAM_MINBLOCKS=$2 timeout 300 python bench.py --workload highcard --steps 5 --no-e2e --no-cpu > gpurun_out/hc_y.json 2>gpurun_out/hc_y.err || tail -5 gpurun_out/hc_y.err
   python - <<PY
