@@ -28,6 +28,19 @@ def test_library_exports_every_declared_symbol():
     assert declared == bound, "ctypes binding and header disagree: %s" % sorted(declared ^ bound)
 
 
+def test_stats_struct_mirrors_the_header_field_by_field():
+    """pgpu_get_stats fills the caller's struct: the ctypes mirror must name the header's fields in the header's order"""
+    h = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "prestogpu.h")).read()
+    body = h[h.index("typedef struct pgpu_stats"):h.index("} pgpu_stats;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    declared = re.findall(r"\b(int64_t|double)\s+(\w+);", body)
+    mirror = [(name, ct) for name, ct in N.Stats._fields_]
+    assert [n for _, n in declared] == [n for n, _ in mirror]
+    for (ctype, name), (_, ct) in zip(declared, mirror):
+        assert ct is (ctypes.c_double if ctype == "double" else ctypes.c_int64), name
+    assert "streamed_runs" in [n for n, _ in mirror] and "partition_sweeps" in [n for n, _ in mirror]
+
+
 def test_bench_plumbing_lives_in_its_own_library():
     """generators, synchronous copies and the L2 flush are not part of the drop-in boundary (include/prestogpu_bench.h,
     libprestogpu_bench.so): the product library exports none of them"""
