@@ -117,3 +117,51 @@ def test_key_order_is_the_sql_order_of_the_grouping_fields(kinds):
                 continue
             assert lib.key_order(packed[i], packed[j]) < 0, (rows[i], rows[j])
             assert lib.key_order(packed[j], packed[i]) > 0, (rows[j], rows[i])
+
+
+KEY_BYTES = {"date": 4, "integer": 4, "bigint": 8, "boolean": 1, "dec10": 8, "dec30": 16, "varchar5": 6}
+
+
+@pytest.mark.parametrize("kinds", [("date", "dec10"), ("integer", "varchar5"), ("bigint", "boolean"), ("dec30",), ("boolean", "varchar5", "date")])
+def test_key_order_is_a_total_order_that_separates_different_keys(kinds):
+    """what the emit kernel relies on for ANY key type: key_order(a, b) == 0 exactly when the key bytes are equal (else two groups
+    would merge), it is antisymmetric and transitive (else a key could reappear unnoticed). Value bytes are arbitrary bit patterns
+    here (non-NULL fields; the layout is 1 byte of null bits, then the fields back to back)."""
+    from presto_b200.spi import BOOLEAN, DATE, createDecimalType, createVarcharType
+    types = {"date": DATE, "integer": INTEGER, "bigint": BIGINT, "boolean": BOOLEAN, "dec10": createDecimalType(10, 2),
+             "dec30": createDecimalType(30, 2), "varchar5": createVarcharType(5)}
+    inputs = [types[k] for k in kinds] + [DOUBLE]
+    plan = plan_text(inputs, step="single", groupByChannels=list(range(len(kinds))),
+                     aggregations=[Aggregation("sum", DOUBLE, len(kinds), DOUBLE)], expectedGroups=NO_DIRECTORY)
+    lib = key_order_lib(source_of(plan, len(inputs)), "total_" + "_".join(kinds))
+    rng = np.random.default_rng(7)
+    alphabet = np.array([0x00, 0x01, 0x7f, 0x80, 0xff], np.uint8)   # sign bits, carries between bytes
+
+    def random_key():
+        raw = bytes([0])
+        for k in kinds:
+            n = KEY_BYTES[k]
+            b = alphabet[rng.integers(0, len(alphabet), n)].tobytes() if k != "boolean" else bytes([int(rng.integers(0, 2))])
+            raw += b
+        raw += b"\0" * (-len(raw) % 8)
+        if len(raw) == 1 + sum(KEY_BYTES[k] for k in kinds):   # the key fills its words: (not a tagless layout; no mark to put)
+            return raw, (ctypes.c_uint64 * (len(raw) // 8))(*struct.unpack("<%dQ" % (len(raw) // 8), raw))
+        words = list(struct.unpack("<%dQ" % (len(raw) // 8), raw))
+        words[-1] |= 1 << 63
+        return raw, (ctypes.c_uint64 * len(words))(*words)
+
+    keys = [random_key() for _ in range(300)]
+    keys += keys[:40]                                            # equal keys occur
+    import functools
+    order = sorted(range(len(keys)), key=functools.cmp_to_key(lambda i, j: lib.key_order(keys[i][1], keys[j][1])))
+    for a, b in zip(order, order[1:]):                           # sorted by key_order: neighbours never decrease, equal only if the same bytes
+        o = lib.key_order(keys[a][1], keys[b][1])
+        assert o <= 0 and lib.key_order(keys[b][1], keys[a][1]) == -o
+        assert (o == 0) == (keys[a][0] == keys[b][0]), (keys[a][0].hex(), keys[b][0].hex())
+    for _ in range(3000):                                        # and any pair agrees with its position in that order
+        i, j = (int(x) for x in rng.integers(0, len(order), 2))
+        o = lib.key_order(keys[order[i]][1], keys[order[j]][1])
+        if keys[order[i]][0] == keys[order[j]][0]:
+            assert o == 0
+        else:
+            assert (o < 0) == (i < j), (keys[order[i]][0].hex(), keys[order[j]][0].hex())
