@@ -1667,9 +1667,9 @@ PGPU_DEV void body_agg_hash_sweep(const PageArgs<P::NC>& a, const TableArgs& t, 
 
 // ------------------------------------------------------------------------------------------------ streaming runs
 // Keys that arrive in key order (GROUP BY l_orderkey over lineitem as the table lies) need no hash table: a group is a run of
-// adjacent rows. pgpu_k_runs_stream writes one slot-format row [key | cells] per run into a linear buffer IN ROW ORDER (tiles
-// are ordered by the decoupled look-back of body_compact; a run that crosses a warp boundary leaves adjacent rows with the same
-// key); pgpu_k_runs_emit merges such neighbours, finalises every group straight into the output buffers and counts the places
+// adjacent rows. pgpu_k_runs_count + pgpu_k_runs_write put one slot-format row [key | cells] per run into a linear buffer IN ROW
+// ORDER (a warp's 128 rows at the offset the scanned counts give it; a run that crosses a warp boundary leaves adjacent rows with the
+// same key); pgpu_k_runs_emit merges such neighbours, finalises every group straight into the output buffers and counts the places
 // where the key order DEcreases. A decrease means a key may reappear later: the host then merges the buffered rows into the hash
 // table (pgpu_k_runs_to_table) and takes the ordinary path — the buffer holds partial states, nothing is lost. Any total order
 // serves; P::key_order is the one a table sorted by the grouping fields comes in (first field first, SQL type order, NULLs last).

@@ -1,4 +1,4 @@
-"""Streaming runs (DESIGN.md "streaming runs"; csrc/device/pgpu_device.cuh body_runs_stream / body_runs_emit /
+"""Streaming runs (DESIGN.md "streaming runs"; csrc/device/pgpu_device.cuh body_runs_count / body_runs_write / body_runs_emit /
 body_runs_to_table): a long device-resident page whose group keys arrive in key order is aggregated run by run into a linear
 buffer, without a hash table; a key order that breaks later sends the buffered partial states into the table. Which path took
 the rows is never observable: every case equals the CPU oracle bit for bit (quantities are integer-valued DOUBLEs, sums are
